@@ -1,0 +1,261 @@
+/* gigaenv.h — C ABI of libgigaenv_cuda.so, the B200-native rollout hot path.
+ *
+ * Every entry point replaces one piece of the reference's CPU path (paths relative to
+ * /root/reference/GigaLearnCPP):
+ *
+ *   ggl_envset_create            RLGymCPP/src/RLGymCPP/EnvSet/EnvSet.cpp:46-111   (EnvSet ctor)
+ *   ggl_envset_step_first_half   EnvSet.cpp:113-130   (StepFirstHalf: snapshot prev, Arena::Step(actionDelay))
+ *   ggl_envset_step_second_half  EnvSet.cpp:132-273   (parse actions, Arena::Step(rest), events, GameState,
+ *                                                       terminals, weighted rewards, obs, masks)
+ *   ggl_envset_reset             EnvSet.cpp:275-354   (Reset / ResetArena for arenas with terminal != 0)
+ *   ggl_envset_sync              EnvSet.h:107         (Sync)
+ *   ggl_envset_views             EnvSet.h:35-60       (EnvState buffers; here device pointers)
+ *   ggl_envset_set_state/get_state   RocketSim Car::SetState/GetState (Sim/Car/Car.cpp:10-36),
+ *                                Ball::SetState/GetState (Sim/Ball/Ball.cpp:27-49), BoostPad::SetState
+ *   ggl_arena_step               RocketSim Arena::Step (Sim/Arena/Arena.cpp:716-812) — raw ticks, for parity tests
+ *   ggl_gae_compute              src/private/GigaLearnCPP/PPO/GAE.cpp:7-208  (GAE::Compute)
+ *   ggl_action_table             RLGymCPP/src/RLGymCPP/ActionParsers/DefaultAction.cpp:3-89
+ *
+ * Conventions: plain pointers and sizes only; every function returns 0 on success or a
+ * negative ggl_status; nothing throws across the boundary; ggl_last_error() gives the text.
+ * All `d_` pointers are DEVICE pointers on the envset's device; `stream` is a cudaStream_t
+ * passed as void* (NULL = legacy default stream).
+ *
+ * The host-side state structs (ggl_car_state, ggl_arena_state) are in Unreal units exactly
+ * like RocketSim's CarState/BallState; the device keeps Bullet units (uu/50) internally and
+ * converts with the same float operations the reference uses, so set→get round-trips match
+ * the reference bit for bit.
+ */
+#ifndef GIGAENV_H
+#define GIGAENV_H
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GGL_MAX_CARS      6      /* 3v3 */
+#define GGL_NUM_PADS      34     /* soccar boost pads, RLConst.h:192-253 */
+#define GGL_NUM_ACTIONS   90     /* DefaultAction table */
+#define GGL_MAX_REWARDS   16
+#define GGL_MAX_TERMINALS 4
+
+typedef enum ggl_status {
+    GGL_OK = 0,
+    GGL_ERR_INVALID = -1,       /* bad argument */
+    GGL_ERR_CUDA = -2,          /* CUDA runtime error, see ggl_last_error */
+    GGL_ERR_UNSUPPORTED = -3,   /* plugin/descriptor kind with no device implementation */
+    GGL_ERR_NOMEM = -4
+} ggl_status;
+
+/* ---- plugin descriptors (device translations of the RLGC plugin objects) ------------- */
+
+typedef enum ggl_obs_kind {
+    GGL_OBS_DEFAULT = 0,    /* RLGC::DefaultObs   (ObsBuilders/DefaultObs.cpp:4-54)   51+19*P floats */
+    GGL_OBS_ADVANCED = 1    /* RLGC::AdvancedObs  (ObsBuilders/AdvancedObs.cpp:193-270) 51+29*P floats */
+} ggl_obs_kind;
+
+typedef enum ggl_reward_kind {   /* Rewards/CommonRewards.h */
+    GGL_REW_PLAYER_GOAL = 0, GGL_REW_ASSIST, GGL_REW_SHOT, GGL_REW_SHOT_PASS, GGL_REW_SAVE,
+    GGL_REW_BUMP, GGL_REW_BUMPED_PENALTY, GGL_REW_DEMO, GGL_REW_DEMOED_PENALTY,   /* :7-28 event rewards */
+    GGL_REW_GOAL,                   /* :32-44  params[0]=concedeScale */
+    GGL_REW_VELOCITY,               /* :47-54  params[0]=isNegative */
+    GGL_REW_VELOCITY_BALL_TO_GOAL,  /* :57-72  params[0]=ownGoal */
+    GGL_REW_VELOCITY_PLAYER_TO_BALL,/* :75-82 */
+    GGL_REW_FACE_BALL,              /* :85-91 */
+    GGL_REW_TOUCH_BALL,             /* :93-98 */
+    GGL_REW_SPEED,                  /* :100-105 */
+    GGL_REW_WAVEDASH,               /* :107-119 */
+    GGL_REW_PICKUP_BOOST,           /* :121-133 */
+    GGL_REW_SAVE_BOOST,             /* :136-144 params[0]=exponent */
+    GGL_REW_AIR,                    /* :147-152 */
+    GGL_REW_TOUCH_ACCEL,            /* :157-178 */
+    GGL_REW_STRONG_TOUCH,           /* :180-202 params[0]=minRewardedVel params[1]=maxRewardedVel (uu/s) */
+    GGL_REW_KIND_COUNT
+} ggl_reward_kind;
+
+typedef struct ggl_reward_desc {
+    int32_t kind;           /* ggl_reward_kind */
+    float   weight;         /* WeightedReward::weight (Reward.h:84-90) */
+    float   params[4];
+    int32_t zero_sum;       /* wrapped in RLGC::ZeroSumReward: a pass-through in the EnvSet path */
+} ggl_reward_desc;
+
+typedef enum ggl_terminal_kind {
+    GGL_TERM_GOAL_SCORE = 0,    /* TerminalConditions/GoalScoreCondition.h:8-14   NORMAL */
+    GGL_TERM_NO_TOUCH = 1       /* TerminalConditions/NoTouchCondition.h:18-28    TRUNCATED, params[0]=maxTime */
+} ggl_terminal_kind;
+
+typedef struct ggl_terminal_desc {
+    int32_t kind;
+    float   params[2];
+} ggl_terminal_desc;
+
+typedef enum ggl_state_setter_kind {
+    GGL_SETTER_KICKOFF = 0,     /* StateSetters/KickoffState.h → Arena::ResetToRandomKickoff (Arena.cpp:112-216) */
+    GGL_SETTER_INJECTED = 1     /* reset states are supplied by the host through ggl_envset_set_reset_state */
+} ggl_state_setter_kind;
+
+/* Arena collision meshes: the reference's .cmf layout (CollisionMeshFile.cpp:11-35):
+ * int32 numTris, int32 numVerts, int32 tri[numTris][3], float vert[numVerts][3] (Bullet units). */
+typedef struct ggl_mesh_blob {
+    const uint8_t* data;
+    size_t         size;
+} ggl_mesh_blob;
+
+typedef struct ggl_envset_desc {
+    int32_t device;             /* CUDA device ordinal */
+    int32_t num_arenas;
+    int32_t players_per_team;   /* 1..3 (blue cars are added first, then orange: carId 1..P blue, P+1..2P orange) */
+    int32_t tick_skip;          /* EnvSetConfig::tickSkip */
+    int32_t action_delay;       /* EnvSetConfig::actionDelay */
+    int32_t obs_kind;           /* ggl_obs_kind */
+    int32_t num_rewards;
+    ggl_reward_desc rewards[GGL_MAX_REWARDS];
+    int32_t num_terminals;
+    ggl_terminal_desc terminals[GGL_MAX_TERMINALS];
+    int32_t state_setter;       /* ggl_state_setter_kind */
+    int32_t num_meshes;
+    const ggl_mesh_blob* meshes;
+    uint64_t seed;              /* device RNG seed (kickoff permutation, respawn slot) */
+    int32_t slot_order_reversed;/* default players[] slot order: 1 = reverse AddCar order, 0 = AddCar order. The reference's
+                                   order is the iteration order of std::unordered_set<Car*> — it depends on heap
+                                   addresses and differs per arena, so it is DATA: override with ggl_envset_set_slot_order */
+} ggl_envset_desc;
+
+/* ---- host-visible state (mirrors RocketSim CarState/BallState/BoostPadState + hidden wheel state) ---- */
+
+typedef struct ggl_controls {   /* Sim/CarControls.h */
+    float throttle, steer, pitch, yaw, roll;
+    uint8_t jump, boost, handbrake, _pad;
+} ggl_controls;
+
+typedef struct ggl_wheel_state { /* btWheelInfoRL fields that survive from one tick to the next */
+    float steer_angle, engine_force, brake, lat_friction, long_friction, extra_pushback;
+} ggl_wheel_state;
+
+typedef struct ggl_car_state {   /* Sim/Car/Car.h:17-115 */
+    float pos[3];
+    float rot[9];                /* forward, right, up (RotMat, column vectors of the Bullet basis) */
+    float vel[3];
+    float ang_vel[3];
+    float flip_rel_torque[3];
+    float jump_time, flip_time, air_time, air_time_since_jump;
+    float boost, time_spent_boosting, supersonic_time, handbrake_val;
+    float auto_flip_timer, auto_flip_torque_scale;
+    float world_contact_normal[3];
+    float car_contact_cooldown;
+    float demo_respawn_timer;
+    float hit_rel_pos[3], hit_ball_pos[3], hit_extra_vel[3];   /* BallHitInfo */
+    uint64_t hit_tick, hit_tick_extra;                         /* ~0 when never */
+    uint32_t car_contact_other_id;
+    uint32_t id;
+    uint8_t team;
+    uint8_t is_on_ground, has_jumped, has_double_jumped, has_flipped, is_flipping, is_jumping;
+    uint8_t is_supersonic, is_auto_flipping, world_contact_has, is_demoed, hit_valid;
+    uint8_t wheels_with_contact[4];
+    ggl_controls last_controls;
+    ggl_controls controls;
+    ggl_wheel_state wheels[4];
+    uint64_t update_counter;
+} ggl_car_state;
+
+typedef struct ggl_ball_state {  /* Sim/Ball/Ball.h:16-41 (soccar: no heatseeker info) */
+    float pos[3], vel[3], ang_vel[3];
+    uint64_t update_counter;
+} ggl_ball_state;
+
+typedef struct ggl_pad_state {   /* Sim/BoostPad/BoostPad.h:23-34, RocketSim pad order (6 big then 28 small) */
+    uint8_t  is_active;
+    uint8_t  _pad[3];
+    float    cooldown;
+    uint32_t prev_locked_car_id;
+} ggl_pad_state;
+
+typedef struct ggl_arena_state {
+    uint64_t tick_count;
+    int32_t  num_cars;
+    int32_t  _pad;
+    ggl_ball_state ball;
+    ggl_car_state  cars[GGL_MAX_CARS];      /* AddCar order: index = carId-1 */
+    ggl_pad_state  pads[GGL_NUM_PADS];
+} ggl_arena_state;
+
+/* ---- device views of EnvState (EnvSet.h:35-60) ---- */
+typedef struct ggl_envset_views {
+    int32_t num_arenas, num_players, obs_size, num_actions, players_per_arena;
+    float*   d_obs;          /* [num_players, obs_size] row-major */
+    uint8_t* d_action_masks; /* [num_players, num_actions] */
+    float*   d_rewards;      /* [num_players] */
+    uint8_t* d_terminals;    /* [num_arenas] 0 / 1 NORMAL / 2 TRUNCATED */
+    int32_t* d_slot_car_id;  /* [num_players] carId of players[] slot */
+    uint8_t* d_slot_team;    /* [num_players] */
+    uint8_t* d_events;       /* [num_players, 9] PlayerEventState: goal,save,assist,shot,shotPass,bump,bumped,demo,demoed */
+    float*   d_last_rewards; /* [num_arenas, num_rewards] raw (unweighted) reward of slot 0 per reward fn */
+} ggl_envset_views;
+
+typedef struct ggl_envset ggl_envset;
+
+int  ggl_envset_create(const ggl_envset_desc* desc, ggl_envset** out);
+int  ggl_envset_destroy(ggl_envset* env);
+int  ggl_envset_step_first_half(ggl_envset* env, void* stream);
+int  ggl_envset_step_second_half(ggl_envset* env, const int32_t* d_actions, void* stream);
+/* One fused launch = Reset + StepFirstHalf + StepSecondHalf (the Learner loop of Learner.cpp:669-793 with
+ * the action indices already on the device). */
+int  ggl_envset_step(ggl_envset* env, const int32_t* d_actions, void* stream);
+int  ggl_envset_reset(ggl_envset* env, void* stream);
+int  ggl_envset_sync(ggl_envset* env);
+int  ggl_envset_views_get(ggl_envset* env, ggl_envset_views* out);
+int  ggl_envset_set_state(ggl_envset* env, int arena, const ggl_arena_state* host_state);
+int  ggl_envset_get_state(ggl_envset* env, int arena, ggl_arena_state* host_state);
+/* players[] slot order of every arena: car_ids[num_players], car_ids[arena*P + slot] = carId (1-based AddCar order)
+ * occupying GameState.players[slot] (GameState.cpp:82-86). Takes effect at the next reset/step. */
+int  ggl_envset_set_slot_order(ggl_envset* env, const int32_t* h_car_ids);
+/* state the next reset of `arena` will install when state_setter == GGL_SETTER_INJECTED */
+int  ggl_envset_set_reset_state(ggl_envset* env, int arena, const ggl_arena_state* host_state);
+/* raw Arena::Step(ticks) on every arena with the cars' current `controls` (no env bookkeeping) */
+int  ggl_arena_step(ggl_envset* env, int ticks, void* stream);
+/* device-side uniformly random mask-valid actions (bench / smoke helper; Philox-free LCG hash on (seed, step, slot)) */
+int  ggl_envset_random_actions(ggl_envset* env, int32_t* d_actions, uint64_t seed, void* stream);
+
+/* Host-convenience wrappers through HOST buffers (the reference-facing call: EnvState vectors live on the host,
+ * EnvSet.h:35-60). actions: int32[num_players]; outputs may be NULL to skip the copy. */
+int  ggl_envset_step_host(ggl_envset* env, const int32_t* h_actions,
+                          float* h_obs, uint8_t* h_masks, float* h_rewards, uint8_t* h_terminals);
+
+/* ---- DefaultAction ---- */
+/* table: float[90*8] (throttle, steer, pitch, yaw, roll, jump, boost, handbrake) */
+int  ggl_action_table(float* out_table, int* out_num_actions);
+
+/* ---- GAE (GAE.cpp:7-208) ----
+ * d_rews f32[L], d_terminals i8[L] (0 / 1 NORMAL / 2 TRUNCATED), d_val_preds f32[L],
+ * d_trunc_val_preds f32[K] or NULL (then truncated steps bootstrap from val_preds[i+1] like non-terminal ones),
+ * outputs f32[L]; d_out_clip_portion f32[1] (may be NULL).
+ * d_workspace: ggl_gae_workspace_bytes(L) bytes of device scratch.
+ * Returns GGL_ERR_INVALID if K != number of TRUNCATED entries is detected (checked asynchronously: the count
+ * is written to d_out_trunc_count i32[1] when non-NULL, mirroring GAE.cpp:196-197). */
+size_t ggl_gae_workspace_bytes(int64_t L);
+int  ggl_gae_compute(const float* d_rews, const int8_t* d_terminals, const float* d_val_preds,
+                     const float* d_trunc_val_preds, int64_t L, int64_t K,
+                     float gamma, float lambda, float return_std, float clip_range,
+                     float* d_out_advantages, float* d_out_returns, float* d_out_target_values,
+                     float* d_out_clip_portion, int32_t* d_out_trunc_count,
+                     void* d_workspace, void* stream);
+/* Host-buffer wrapper (the reference-facing call: GAE::Compute takes CPU tensors). */
+int  ggl_gae_compute_host(const float* h_rews, const int8_t* h_terminals, const float* h_val_preds,
+                          const float* h_trunc_val_preds, int64_t L, int64_t K,
+                          float gamma, float lambda, float return_std, float clip_range,
+                          float* h_out_advantages, float* h_out_returns, float* h_out_target_values,
+                          float* h_out_clip_portion);
+
+/* kernels launched by this library since load (bench.py's gpu_launches) */
+uint64_t ggl_launch_count(void);
+const char* ggl_last_error(void);
+const char* ggl_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GIGAENV_H */
