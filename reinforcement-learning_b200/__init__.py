@@ -1,0 +1,121 @@
+"""gigaenv-b200: B200-native rollout hot path (arena stepping, obs/reward/terminal, GAE) behind a C ABI.
+
+This Python module is a thin ctypes binding over ``libgigaenv_cuda.so`` (include/gigaenv.h) used by the test
+suite and bench.py; the product is the shared library and the C++ host headers under ``host/``.
+There is NO CPU fallback: if the CUDA library is missing, loading fails loudly.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import abi
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libgigaenv_cuda.so")
+_lib = None
+
+
+class GigaEnvError(RuntimeError):
+    pass
+
+
+def lib():
+    """Loads libgigaenv_cuda.so (raises if it has not been built: run ``python __graft_entry__.py``)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise GigaEnvError("libgigaenv_cuda.so not built (%s): no CPU fallback exists" % LIB_PATH)
+        L = C.CDLL(LIB_PATH)
+        L.ggl_last_error.restype = C.c_char_p
+        L.ggl_version.restype = C.c_char_p
+        L.ggl_launch_count.restype = C.c_uint64
+        L.ggl_gae_workspace_bytes.restype = C.c_size_t
+        L.ggl_gae_workspace_bytes.argtypes = [C.c_int64]
+        L.ggl_gae_compute.argtypes = ([C.c_void_p] * 4 + [C.c_int64, C.c_int64] + [C.c_float] * 4 +
+                                      [C.c_void_p] * 7)
+        L.ggl_gae_compute_host.argtypes = ([C.c_void_p] * 4 + [C.c_int64, C.c_int64] + [C.c_float] * 4 +
+                                           [C.c_void_p] * 3 + [C.POINTER(C.c_float)])
+        if hasattr(L, "ggl_envset_create"):
+            L.ggl_envset_create.argtypes = [C.POINTER(abi.EnvSetDesc), C.POINTER(C.c_void_p)]
+            L.ggl_envset_destroy.argtypes = [C.c_void_p]
+            L.ggl_envset_step_first_half.argtypes = [C.c_void_p, C.c_void_p]
+            L.ggl_envset_step_second_half.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+            L.ggl_envset_step.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+            L.ggl_envset_reset.argtypes = [C.c_void_p, C.c_void_p]
+            L.ggl_envset_sync.argtypes = [C.c_void_p]
+            L.ggl_envset_views_get.argtypes = [C.c_void_p, C.POINTER(abi.EnvSetViews)]
+            L.ggl_envset_set_state.argtypes = [C.c_void_p, C.c_int, C.POINTER(abi.ArenaState)]
+            L.ggl_envset_get_state.argtypes = [C.c_void_p, C.c_int, C.POINTER(abi.ArenaState)]
+            L.ggl_envset_set_reset_state.argtypes = [C.c_void_p, C.c_int, C.POINTER(abi.ArenaState)]
+            L.ggl_envset_set_slot_order.argtypes = [C.c_void_p, C.c_void_p]
+            L.ggl_arena_step.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+            L.ggl_envset_random_actions.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
+            L.ggl_envset_step_host.argtypes = [C.c_void_p] * 6
+            L.ggl_action_table.argtypes = [C.c_void_p, C.POINTER(C.c_int)]
+        _lib = L
+    return _lib
+
+
+def _check(rc):
+    if rc != 0:
+        raise GigaEnvError("gigaenv error %d: %s" % (rc, lib().ggl_last_error().decode()))
+
+
+def launch_count():
+    return int(lib().ggl_launch_count())
+
+
+# ----------------------------------------------------------------------------------------------- GAE
+def gae_compute_host(rews, terminals, val_preds, trunc_val_preds=None, gamma=0.99, lam=0.95, return_std=0.0,
+                     clip_range=10.0, out=None):
+    """GAE::Compute through HOST buffers (numpy arrays or anything exposing ``.ctypes``), mirroring the reference
+    call at Learner.cpp:949-953 where all tensors live on the CPU. Returns (advantages, returns, target_values,
+    clip_portion)."""
+    rews = np.ascontiguousarray(rews, np.float32)
+    terminals = np.ascontiguousarray(terminals, np.int8)
+    val_preds = np.ascontiguousarray(val_preds, np.float32)
+    L = rews.shape[0]
+    if out is None:
+        out = tuple(np.empty(L, np.float32) for _ in range(3))
+    tv, K = None, 0
+    if trunc_val_preds is not None:
+        tvv = np.ascontiguousarray(trunc_val_preds, np.float32)
+        K = tvv.shape[0]
+        tv = tvv.ctypes.data if K > 0 else rews.ctypes.data  # non-NULL marks "defined tensor"
+    clip = C.c_float()
+    _check(lib().ggl_gae_compute_host(rews.ctypes.data, terminals.ctypes.data, val_preds.ctypes.data, tv, L, K,
+                                      gamma, lam, return_std, clip_range,
+                                      out[0].ctypes.data, out[1].ctypes.data, out[2].ctypes.data, C.byref(clip)))
+    return out[0], out[1], out[2], clip.value
+
+
+def gae_compute_device(rews, terminals, val_preds, trunc_val_preds=None, gamma=0.99, lam=0.95, return_std=0.0,
+                       clip_range=10.0, out=None, workspace=None, stream=None):
+    """Device-resident GAE on torch CUDA tensors (zero-copy: raw pointers go straight to the C ABI).
+    Returns (advantages, returns, target_values, clip_portion[1], trunc_count[1]) as CUDA tensors."""
+    import torch
+    L = rews.numel()
+    dev = rews.device
+    assert rews.dtype == torch.float32 and val_preds.dtype == torch.float32 and terminals.dtype == torch.int8
+    if out is None:
+        out = tuple(torch.empty(L, dtype=torch.float32, device=dev) for _ in range(3))
+    scal = torch.zeros(2, dtype=torch.float32, device=dev)
+    need = lib().ggl_gae_workspace_bytes(L)
+    if workspace is None or workspace.numel() < need:
+        workspace = torch.empty(need, dtype=torch.uint8, device=dev)
+    K = 0 if trunc_val_preds is None else trunc_val_preds.numel()
+    tv = None if trunc_val_preds is None else (trunc_val_preds.data_ptr() if K > 0 else rews.data_ptr())
+    s = torch.cuda.current_stream(dev).cuda_stream if stream is None else stream
+    _check(lib().ggl_gae_compute(rews.data_ptr(), terminals.data_ptr(), val_preds.data_ptr(), tv, L, K,
+                                 gamma, lam, return_std, clip_range,
+                                 out[0].data_ptr(), out[1].data_ptr(), out[2].data_ptr(),
+                                 scal.data_ptr(), scal.data_ptr() + 4, workspace.data_ptr(), s))
+    return out[0], out[1], out[2], scal[:1], scal[1:].view(torch.int32), workspace
+
+
+def action_table():
+    t = np.empty((abi.GGL_NUM_ACTIONS, 8), np.float32)
+    n = C.c_int()
+    _check(lib().ggl_action_table(t.ctypes.data, C.byref(n)))
+    return t[:n.value]
