@@ -1,0 +1,416 @@
+#!/usr/bin/env python
+"""Benchmark of the B200-native rollout hot path (BASELINE.json metric: agent-steps/s, whole box; GAE GB/s).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload env|gae]
+
+One "step" = one env step (Reset + StepFirstHalf + StepSecondHalf, tick_skip 8) of every arena on the rank, on
+BASELINE.json configs[1]: soccar 2v2, 4096 arenas per GPU, AdvancedObs + {VelocityPlayerToBall, TouchBall, Goal},
+device-side random mask-valid actions.  Arenas shard across ranks with no data-path collective ("weak" scaling:
+4096 arenas per GPU).  `value` = agent-steps of all ranks / max-over-ranks device time (CUDA events on the launch
+stream, L2 flushed between steps).  `e2e` = the same metric through the host-buffer C-ABI call
+(ggl_envset_step_host: pinned H2D of actions, D2H of obs/masks/rewards/terminals inside the timed region).
+`--workload gae` benches the GAE scan instead (config C4: T=256 x N=65536 stream, GB/s at 21 B/element).
+`--impl reference` times the UNMODIFIED reference's CPU EnvSet (oracle/_ref, all host threads) on the same config.
+"""
+import argparse
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+PKG = "reinforcement-learning_b200"
+
+ARENAS_PER_GPU = 4096
+PLAYERS_PER_TEAM = 2
+OBS_SIZE_ADV_2V2 = 167
+# algorithmic bytes per agent-step of the fused env step, 2v2 AdvancedObs:
+# obs 668 + mask 90 + reward 4 + state share ~260 + action 4
+ENV_BYTES_PER_AGENT_STEP = 1026
+GAE_BYTES_PER_ELEM = 21
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)."""
+
+    def __init__(self, index):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+             "clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx = float(f[1])
+            except ValueError:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def dist_setup(n_gpus):
+    import torch
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    return rank, world, local
+
+
+def barrier_sync(world):
+    import torch
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+    torch.cuda.synchronize()
+
+
+def max_over_ranks(x, world):
+    import torch
+    if world == 1:
+        return x
+    import torch.distributed as dist
+    t = torch.tensor([x], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def sum_over_ranks(x, world):
+    import torch
+    if world == 1:
+        return x
+    import torch.distributed as dist
+    t = torch.tensor([x], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    return float(t.item())
+
+
+# ------------------------------------------------------------------------------------------------ env workload
+def bench_env(args, rank, world, local):
+    import numpy as np
+    import torch
+    ggl = importlib.import_module(PKG)
+    dev = torch.device("cuda", local)
+    env = ggl.EnvSet(ARENAS_PER_GPU, PLAYERS_PER_TEAM, obs_kind=ggl.abi.OBS_ADVANCED, seed=123 + rank, device=local)
+    assert env.obs_size == OBS_SIZE_ADV_2V2
+    acts = torch.zeros(env.num_players, dtype=torch.int32, device=dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    stream = torch.cuda.current_stream(dev)
+
+    def one(i):
+        env.random_actions(acts, seed=1000 + i)
+        env.step(acts)
+
+    for i in range(args.warmup):
+        one(i)
+    # ---- device-timed region: K steps, CUDA events on the launch stream, L2 flushed between steps
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = ggl.launch_count()
+    barrier_sync(world)
+    t_wall0 = time.perf_counter()
+    for i in range(args.steps):
+        flush.fill_(i & 0xff)
+        evs[i][0].record(stream)
+        env.random_actions(acts, seed=5000 + i)
+        kev[i][0].record(stream)
+        env.step(acts)
+        kev[i][1].record(stream)
+        evs[i][1].record(stream)
+    barrier_sync(world)
+    t_wall = time.perf_counter() - t_wall0
+    launches = ggl.launch_count() - l0
+    clocks = sampler.stop() if rank == 0 else None
+    dev_ms = sum(a.elapsed_time(b) for a, b in evs)
+    kern_ms = sum(a.elapsed_time(b) for a, b in kev) / args.steps
+    dev_ms = max_over_ranks(dev_ms, world)
+    agent_steps = sum_over_ranks(float(env.num_players) * args.steps, world)
+    value = agent_steps / (dev_ms * 1e-3)
+
+    # ---- e2e: host-buffer C-ABI call (pinned), H2D + D2H inside the timed region
+    h_act = torch.zeros(env.num_players, dtype=torch.int32).pin_memory()
+    h_obs = torch.empty(env.num_players, env.obs_size, dtype=torch.float32).pin_memory()
+    h_mask = torch.empty(env.num_players, env.num_actions, dtype=torch.uint8).pin_memory()
+    h_rew = torch.empty(env.num_players, dtype=torch.float32).pin_memory()
+    h_term = torch.empty(env.num_arenas, dtype=torch.uint8).pin_memory()
+    rng = np.random.default_rng(7 + rank)
+
+    def one_host():
+        # host-side mask-valid random action per agent from the masks the previous step returned
+        m = h_mask.numpy()
+        u = rng.random(env.num_players)
+        cnt = m.sum(1)
+        k = np.minimum((u * cnt).astype(np.int64), np.maximum(cnt - 1, 0))
+        cs = np.cumsum(m, 1)
+        h_act.numpy()[:] = (cs > k[:, None]).argmax(1).astype(np.int32)
+        env.step_host(h_act, h_obs, h_mask, h_rew, h_term)
+
+    env.step_host(h_act, h_obs, h_mask, h_rew, h_term)
+    e2e_steps = max(3, min(args.steps, 50))
+    for _ in range(3):
+        one_host()
+    barrier_sync(world)
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        one_host()
+    barrier_sync(world)
+    e2e_s = max_over_ranks(time.perf_counter() - t0, world)
+    e2e_val = sum_over_ranks(float(env.num_players) * e2e_steps, world) / e2e_s
+    h2d = env.num_players * 4
+    d2h = env.num_players * (env.obs_size * 4 + env.num_actions + 4) + env.num_arenas
+
+    peak, peak_src = peaks()
+    achieved = ENV_BYTES_PER_AGENT_STEP * env.num_players / (kern_ms * 1e-3) / 1e9
+    line = {
+        "metric": "agent-steps/sec", "value": value, "unit": "agent-steps/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "soccar 2v2, %d arenas per GPU, AdvancedObs(167) + DefaultAction(90) + "
+                               "{VelocityPlayerToBall,TouchBall,Goal} + {GoalScore,NoTouch(10)}, tick_skip 8, "
+                               "device random mask-valid actions (BASELINE.json configs[1])" % ARENAS_PER_GPU,
+                   "arenas_per_gpu": ARENAS_PER_GPU, "agents_per_gpu": env.num_players, "l2": "flushed between steps (256 MiB write)",
+                   "arena_mesh": "synthetic soccar (real .cmf meshes are not redistributable)"},
+        "e2e": {"value": e2e_val, "unit": "agent-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "steps": e2e_steps, "api": "ggl_envset_step_host (pinned host buffers)"},
+        "gpu_launches": int(launches),
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": None, "kernel": "env_step_kernel", "peak_source": peak_src,
+                     "algorithmic_bytes_per_launch": ENV_BYTES_PER_AGENT_STEP * env.num_players,
+                     "note": "physics ticks are FP32/latency bound; the HBM floor is the obs/mask/reward write (SURVEY 8d)"},
+        "wall_s": t_wall,
+    }
+    if rank == 0:
+        line["clocks"] = clocks
+        if world == 1:
+            line["cpu_baseline"] = cpu_baseline_env()
+            line["gae"] = gae_numbers(ggl, dev, steps=10, warmup=3)
+    env.close()
+    return line
+
+
+def cpu_baseline_env(arenas=None, steps=30, warmup=5, threads=0):
+    """The UNMODIFIED reference EnvSet (oracle/_ref/libref_oracle.so) on the host cores; falls back to saying so
+    when the compiled reference did not travel to this box."""
+    try:
+        import oracle_ref
+        if not oracle_ref.available():
+            return {"value": None, "unit": "agent-steps/s", "cores": 0, "kind": "reference",
+                    "sample": "oracle/_ref/libref_oracle.so not present on this box"}
+        L = oracle_ref.lib()
+        L.ref_set_threads(threads)
+        cores = L.ref_num_threads()
+        arenas = arenas or ARENAS_PER_GPU
+        env = oracle_ref.RefEnvSet(arenas, PLAYERS_PER_TEAM, obs_kind=oracle_ref.abi.OBS_ADVANCED)
+        sec = env.bench(steps, warmup, 123)
+        v = env.num_players * steps / sec
+        env.close()
+        return {"value": v, "unit": "agent-steps/s", "cores": cores, "kind": "reference",
+                "sample": "%d arenas 2v2 AdvancedObs, %d warm-up + %d timed env steps, reference thread pool" % (arenas, warmup, steps)}
+    except Exception as e:  # noqa
+        return {"value": None, "unit": "agent-steps/s", "cores": 0, "kind": "reference", "sample": "failed: %r" % (e,)}
+
+
+# ------------------------------------------------------------------------------------------------ GAE workload
+def gae_inputs(torch, dev, T=256, N=65536, seed=7):
+    g = torch.Generator(device=dev); g.manual_seed(seed)
+    L = T * N
+    r = torch.randn(L, device=dev, generator=g)
+    v = torch.randn(L, device=dev, generator=g)
+    t = torch.zeros(L, dtype=torch.int8, device=dev)
+    kinds = torch.randint(1, 3, (N,), device=dev, generator=g).to(torch.int8)
+    t[T - 1::T] = kinds
+    K = int((t == 2).sum().item())
+    tv = torch.randn(max(K, 1), device=dev, generator=g)[:K]
+    return r, t, v, tv
+
+
+def gae_numbers(ggl, dev, steps, warmup, T=256, N=65536):
+    import torch
+    r, t, v, tv = gae_inputs(torch, dev, T, N)
+    L = r.numel()
+    out = tuple(torch.empty(L, device=dev) for _ in range(3))
+    ws = None
+    for _ in range(warmup):
+        *_, ws = ggl.gae_compute_device(r, t, v, tv, 0.99, 0.95, 1.7, 10.0, out=out, workspace=ws)
+    s = torch.cuda.current_stream(dev)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record(s)
+    for _ in range(steps):
+        ggl.gae_compute_device(r, t, v, tv, 0.99, 0.95, 1.7, 10.0, out=out, workspace=ws)
+    e1.record(s)
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    peak, src = peaks()
+    gbs = GAE_BYTES_PER_ELEM * L / (ms * 1e-3) / 1e9
+    return {"L": L, "T": T, "N": N, "ms": ms, "elements_per_s": L / (ms * 1e-3), "GB/s": gbs, "peak": peak,
+            "frac": gbs / peak, "bytes_per_element": GAE_BYTES_PER_ELEM, "peak_source": src,
+            "inputs": "%d MB stream > L2 (126 MB), no flush needed" % (GAE_BYTES_PER_ELEM * L >> 20)}
+
+
+def bench_gae(args, rank, world, local):
+    import numpy as np
+    import torch
+    ggl = importlib.import_module(PKG)
+    dev = torch.device("cuda", local)
+    T, N = 256, 65536
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = ggl.launch_count()
+    barrier_sync(world)
+    g = gae_numbers(ggl, dev, args.steps, args.warmup, T, N)
+    barrier_sync(world)
+    launches = ggl.launch_count() - l0
+    clocks = sampler.stop() if rank == 0 else None
+    ms = max_over_ranks(g["ms"], world)
+    L = g["L"]
+    value = GAE_BYTES_PER_ELEM * L * world / (ms * 1e-3) / 1e9
+    # e2e through host buffers (the reference call takes CPU tensors: Learner.cpp:949-953)
+    r, t, v, tv = [x.cpu().numpy() for x in gae_inputs(torch, dev, T, N)]
+    hr, ht, hv = [torch.from_numpy(x).pin_memory().numpy() for x in (r, t, v)]
+    outs = tuple(torch.empty(L).pin_memory().numpy() for _ in range(3))
+    ggl.gae_compute_host(hr, ht, hv, tv, 0.99, 0.95, 1.7, 10.0, out=outs)
+    t0 = time.perf_counter()
+    n_e2e = 3
+    for _ in range(n_e2e):
+        ggl.gae_compute_host(hr, ht, hv, tv, 0.99, 0.95, 1.7, 10.0, out=outs)
+    e2e_s = max_over_ranks((time.perf_counter() - t0) / n_e2e, world)
+    line = {
+        "metric": "GAE GB/s", "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": {"workload": "GAE/returns over a flat stream of N=65536 segments x T=256 (L=2^24), mixed NORMAL/TRUNCATED "
+                               "terminals, gamma .99 lambda .95 returnStd 1.7 clip 10 (BASELINE.json configs[3])",
+                   "l2": "inputs+outputs 352 MB > L2"},
+        "e2e": {"value": GAE_BYTES_PER_ELEM * L * world / e2e_s / 1e9, "unit": "GB/s", "h2d_bytes_per_step": 9 * L + 4 * len(tv),
+                "d2h_bytes_per_step": 12 * L + 8, "api": "ggl_gae_compute_host"},
+        "gpu_launches": int(launches),
+        "roofline": {"bound": "hbm", "achieved": g["GB/s"], "peak": g["peak"], "unit": "GB/s", "frac": g["frac"],
+                     "traffic": None, "kernel": "gae_scan_kernel", "peak_source": g["peak_source"],
+                     "algorithmic_bytes_per_launch": GAE_BYTES_PER_ELEM * L},
+    }
+    if rank == 0:
+        line["clocks"] = clocks
+        if world == 1:
+            import oracle_c
+            Ls = 1 << 22
+            t0 = time.perf_counter()
+            oracle_c.gae(r[:Ls], t[:Ls], v[:Ls], None, 0.99, 0.95, 1.7, 10.0)
+            dt = time.perf_counter() - t0
+            line["cpu_baseline"] = {"value": GAE_BYTES_PER_ELEM * Ls / dt / 1e9, "unit": "GB/s", "cores": 1, "kind": "port",
+                                    "sample": "first 2^22 elements of the same stream, C restatement of GAE.cpp, 1 thread"}
+    return line
+
+
+# ------------------------------------------------------------------------------------------------ reference arm
+def bench_reference(args):
+    """Times the reference's own CPU EnvSet on this box's host cores (oracle/_ref). Rank 0 only."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return None
+    n = max(1, args.gpus)
+    cb = cpu_baseline_env(arenas=ARENAS_PER_GPU, steps=max(1, args.steps), warmup=max(1, args.warmup))
+    v = cb["value"]
+    line = {"impl": "reference", "metric": "agent-steps/sec", "value": v, "unit": "agent-steps/s", "n_gpus": n,
+            "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": (ARENAS_PER_GPU * 2 * PLAYERS_PER_TEAM / v * 1e3) if v else None,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "soccar 2v2, %d arenas, AdvancedObs(167) + DefaultAction(90), tick_skip 8, random mask-valid "
+                                   "actions: the reference RLGC::EnvSet on the host thread pool (CPU only; the reference has no "
+                                   "multi-GPU path, so the same CPU number stands at every N)" % ARENAS_PER_GPU,
+                       "arena_mesh": "synthetic soccar"},
+            "cpu_baseline": cb,
+            "e2e": {"value": v, "unit": "agent-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    if v is None:
+        line = {"impl": "reference", "unavailable": cb["sample"]}
+    return line
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=None)
+    ap.add_argument("--warmup", type=int, default=None)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default=None, choices=["env", "gae"])
+    args = ap.parse_args()
+    if args.impl == "reference":
+        args.steps = args.steps if args.steps is not None else 30
+        args.warmup = args.warmup if args.warmup is not None else 5
+        line = bench_reference(args)
+        if line is not None:
+            print(json.dumps(line))
+        return
+    ggl = importlib.import_module(PKG)
+    ggl.lib()   # fail loudly if the CUDA library is missing
+    workload = args.workload or ("env" if hasattr(ggl, "EnvSet") else "gae")
+    if args.steps is None:
+        args.steps = 200 if workload == "env" else 20
+    if args.warmup is None:
+        args.warmup = 20 if workload == "env" else 5
+    args.warmup = max(args.warmup, 3)
+    rank, world, local = dist_setup(args.gpus)
+    line = bench_env(args, rank, world, local) if workload == "env" else bench_gae(args, rank, world, local)
+    if rank == 0:
+        print(json.dumps(line))
+    if world > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
