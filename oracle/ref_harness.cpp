@@ -447,4 +447,69 @@ double ref_envset_bench(void* p, int steps, int warmup, uint32_t seed) {
     return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
 }
 
+
+// ---- debugging aids for the parity tests: contact manifolds of the last tick and shape constants ----
+static int BodyCode(const btCollisionObject* o) {
+    if (o->getUserIndex() == BT_USERINFO_TYPE_CAR) return (int)((Car*)o->getUserPointer())->id;
+    if (o->getUserIndex() == BT_USERINFO_TYPE_BALL) return 0;
+    return -1;
+}
+// out: [max][20] floats per contact point: bodyA, bodyB, normalOnB xyz, posA xyz, posB xyz, distance, friction,
+// restitution, isSpecial, localA xyz, appliedImpulse.   Returns the number of points.
+int ref_arena_contacts(void* p, int arena, float* out, int max) {
+    Arena* a = ((RefEnv*)p)->envSet->arenas[arena];
+    auto* disp = a->_bulletWorld.getDispatcher();
+    int n = 0;
+    for (int i = 0; i < disp->getNumManifolds(); i++) {
+        btPersistentManifold* m = disp->getManifoldByIndexInternal(i);
+        for (int j = 0; j < m->getNumContacts() && n < max; j++) {
+            const btManifoldPoint& cp = m->getContactPoint(j);
+            float* o = out + 20 * n++;
+            o[0] = (float)BodyCode(m->getBody0()); o[1] = (float)BodyCode(m->getBody1());
+            o[2] = cp.m_normalWorldOnB.x(); o[3] = cp.m_normalWorldOnB.y(); o[4] = cp.m_normalWorldOnB.z();
+            o[5] = cp.m_positionWorldOnA.x(); o[6] = cp.m_positionWorldOnA.y(); o[7] = cp.m_positionWorldOnA.z();
+            o[8] = cp.m_positionWorldOnB.x(); o[9] = cp.m_positionWorldOnB.y(); o[10] = cp.m_positionWorldOnB.z();
+            o[11] = cp.m_distance1; o[12] = cp.m_combinedFriction; o[13] = cp.m_combinedRestitution; o[14] = cp.m_isSpecial ? 1.f : 0.f;
+            o[15] = cp.m_localPointA.x(); o[16] = cp.m_localPointA.y(); o[17] = cp.m_localPointA.z();
+            o[18] = cp.m_appliedImpulse; o[19] = (float)i;
+        }
+    }
+    return n;
+}
+
+// out[0..2] car invInertiaDiagLocal, [3] car invMass, [4..6] ball invInertiaDiagLocal, [7] ball invMass, [8] ball shape radius,
+// [9] ball shape margin, [10] car compound contact-breaking threshold, [11] ball contact-breaking threshold,
+// [12] box margin, [13..15] box half extents with margin, [16] solver erp2, [17] solver erp, [18] linearSlop, [19] restitution vel threshold
+void ref_debug_constants(void* p, float* out) {
+    Arena* a = ((RefEnv*)p)->envSet->arenas[0];
+    Car* car = *a->_cars.begin();
+    btVector3 ci = car->_rigidBody.getInvInertiaDiagLocal();
+    out[0] = ci.x(); out[1] = ci.y(); out[2] = ci.z(); out[3] = car->_rigidBody.getInvMass();
+    btVector3 bi = a->ball->_rigidBody.getInvInertiaDiagLocal();
+    out[4] = bi.x(); out[5] = bi.y(); out[6] = bi.z(); out[7] = a->ball->_rigidBody.getInvMass();
+    out[8] = a->ball->GetRadiusBullet(); out[9] = a->ball->_collisionShape->getMargin();
+    out[10] = car->_compoundShape.getContactBreakingThreshold(gContactBreakingThreshold);
+    out[11] = a->ball->_collisionShape->getContactBreakingThreshold(gContactBreakingThreshold);
+    out[12] = car->_childHitboxShape.getMargin();
+    btVector3 he = car->_childHitboxShape.getHalfExtentsWithMargin();
+    out[13] = he.x(); out[14] = he.y(); out[15] = he.z();
+    auto& si = a->_bulletWorld.getSolverInfo();
+    out[16] = si.m_erp2; out[17] = si.m_erp; out[18] = si.m_linearSlop; out[19] = si.m_restitutionVelocityThreshold;
+    out[20] = (float)si.m_numIterations; out[21] = (float)si.m_solverMode; out[22] = si.m_splitImpulsePenetrationThreshold;
+    out[23] = si.m_splitImpulseTurnErp; out[24] = (float)a->_bulletWorld.getDispatchInfo().m_useContinuous;
+    out[25] = a->_worldCollisionRBAmount > 0 ? a->_worldCollisionBvhShapes[0].getMargin() : -1.f;
+    out[26] = a->_worldCollisionRBAmount > 0 ? a->_worldCollisionRBs[0].getFriction() : -1.f;
+    out[27] = (float)a->_worldCollisionRBAmount;
+}
+
+
+// only the cars' `controls` of a host state (leaves everything else untouched)
+void ref_envset_set_controls(void* p, int arena, const ggl_arena_state* st) {
+    Arena* a = ((RefEnv*)p)->envSet->arenas[arena];
+    for (int i = 0; i < st->num_cars; i++) {
+        Car* car = CarById(a, i + 1);
+        if (car) car->controls = ToControls(st->cars[i].controls);
+    }
+}
+
 } // extern "C"

@@ -1,0 +1,764 @@
+// Per-car part of one 120 Hz tick: suspension ray casts, wheel friction, and the car control state machine
+// (throttle / steer / jump / flip / air control / boost / auto-flip / auto-roll).
+//
+// Reference behaviour restated (paths under GigaLearnCPP/RLGymCPP/RocketSim/src):
+//   Sim/Car/Car.cpp:58-131        Car::_PreTickUpdate           -> car_pre_tick
+//   Sim/Car/Car.cpp:330-475       _UpdateWheels                  -> update_wheels
+//   Sim/Car/Car.cpp:477-505       _UpdateBoost                   -> update_boost
+//   Sim/Car/Car.cpp:507-554       _UpdateJump                    -> update_jump
+//   Sim/Car/Car.cpp:556-641       _UpdateAirTorque               -> update_air_torque
+//   Sim/Car/Car.cpp:643-761       _UpdateDoubleJumpOrFlip        -> update_double_jump_or_flip
+//   Sim/Car/Car.cpp:763-798       _UpdateAutoFlip                -> update_auto_flip
+//   Sim/Car/Car.cpp:800-833       _UpdateAutoRoll                -> update_auto_roll
+//   Sim/Car/Car.cpp:133-193       _PostTickUpdate/_FinishPhysicsTick -> car_post_tick
+//   Sim/btVehicleRL/btVehicleRL.cpp:64-92,118-212,277-402  wheel transform, ray cast, suspension, friction
+//   libsrc/bullet3-3.24/BulletDynamics/ConstraintSolver/btContactConstraint.cpp:60-150 resolveSingleCollision/Bilateral
+//   libsrc/bullet3-3.24/BulletCollision/NarrowPhaseCollision/btRaycastCallback.cpp:34-110 ray vs triangle
+#pragma once
+#include "sim_types.cuh"
+
+namespace ggl {
+
+// ---------------------------------------------------------------------------------------------- curves
+// LinearPieceCurve::GetOutput (Math/Math.cpp:5-35) over the tables of RLConst.h:340-437
+template <int N>
+GGL_HD float curve_eval(const float (&xs)[N], const float (&ys)[N], float in) {
+    if (in <= xs[0]) return ys[0];
+#pragma unroll
+    for (int i = 1; i < N; i++) {
+        if (xs[i] > in) {
+            float range = xs[i] - xs[i - 1];
+            float diff = ys[i] - ys[i - 1];
+            float f = (in - xs[i - 1]) / range;
+            return ys[i - 1] + diff * f;
+        }
+    }
+    return ys[N - 1];
+}
+GGL_HD float curve_steer_angle(float s) {
+    const float x[6] = {0, 500, 1000, 1500, 1750, 3000}, y[6] = {0.53356f, 0.31930f, 0.18203f, 0.10570f, 0.08507f, 0.03454f};
+    return curve_eval(x, y, s);
+}
+GGL_HD float curve_powerslide_steer(float s) {
+    const float x[2] = {0, 2500}, y[2] = {0.39235f, 0.12610f};
+    return curve_eval(x, y, s);
+}
+GGL_HD float curve_drive_torque(float s) {
+    const float x[3] = {0, 1400, 1410}, y[3] = {1.0f, 0.1f, 0.0f};
+    return curve_eval(x, y, s);
+}
+GGL_HD float curve_non_sticky(float z) {
+    const float x[3] = {0, 0.7075f, 1}, y[3] = {0.1f, 0.5f, 1.0f};
+    return curve_eval(x, y, z);
+}
+GGL_HD float curve_lat_friction(float v) {
+    const float x[2] = {0, 1}, y[2] = {1.0f, 0.2f};
+    return curve_eval(x, y, v);
+}
+GGL_HD float curve_handbrake_long(float v) {
+    const float x[2] = {0, 1}, y[2] = {0.5f, 0.9f};
+    return curve_eval(x, y, v);
+}
+GGL_HD float curve_ball_extra_impulse(float v) {
+    const float x[4] = {0, 500.f, 2300.f, 4600.f}, y[4] = {0.65f, 0.65f, 0.55f, 0.30f};
+    return curve_eval(x, y, v);
+}
+GGL_HD float curve_bump_ground(float v) {
+    const float x[3] = {0.f, 1400.f, 2200.f}, y[3] = {(5.f / 6.f), 1100.f, 1530.f};
+    return curve_eval(x, y, v);
+}
+GGL_HD float curve_bump_air(float v) {
+    const float x[3] = {0.f, 1400.f, 2200.f}, y[3] = {(5.f / 6.f), 1390.f, 1945.f};
+    return curve_eval(x, y, v);
+}
+GGL_HD float curve_bump_up(float v) {
+    const float x[3] = {0.f, 1400.f, 2200.f}, y[3] = {(2.f / 6.f), 278.f, 417.f};
+    return curve_eval(x, y, v);
+}
+
+// ---------------------------------------------------------------------------------------------- car constants
+GGL_HD V3 car_half_extents() { return v3(rl::HITBOX_X * kUU2BT / 2, rl::HITBOX_Y * kUU2BT / 2, rl::HITBOX_Z * kUU2BT / 2); }
+GGL_HD V3 car_hitbox_offset() { return v3(rl::HITBOX_OFF_X * kUU2BT, rl::HITBOX_OFF_Y * kUU2BT, rl::HITBOX_OFF_Z * kUU2BT); }
+// btBoxShape::calculateLocalInertia on the full half extents, then 1/x (btRigidBody::setMassProps)
+GGL_HD V3 car_inv_inertia_local() {
+    V3 he = v3(rl::HITBOX_X, rl::HITBOX_Y, rl::HITBOX_Z) * kUU2BT / 2.f;
+    // the box stores (he - margin) and adds the margin back when asked for the extents with margin
+    V3 m = v3(rl::CONVEX_MARGIN, rl::CONVEX_MARGIN, rl::CONVEX_MARGIN);
+    he = (he - m) + m;
+    float lx = 2.f * he.x, ly = 2.f * he.y, lz = 2.f * he.z;
+    V3 in = v3(rl::CAR_MASS / 12.f * (ly * ly + lz * lz), rl::CAR_MASS / 12.f * (lx * lx + lz * lz), rl::CAR_MASS / 12.f * (lx * lx + ly * ly));
+    return v3(1.f / in.x, 1.f / in.y, 1.f / in.z);
+}
+GGL_HD void car_update_inertia(CarDev& c) {
+    c.invInertiaW = mul(scaled(c.basis, car_inv_inertia_local()), transpose(c.basis));
+}
+GGL_HD V3 car_fwd(const CarDev& c) { return col(c.basis, 0); }
+GGL_HD V3 car_right(const CarDev& c) { return col(c.basis, 1); }
+GGL_HD V3 car_up(const CarDev& c) { return col(c.basis, 2); }
+GGL_HD V3 vel_at(const V3& vel, const V3& angVel, V3 rel) { return vel + cross(angVel, rel); }
+GGL_HD void car_apply_central_impulse(CarDev& c, V3 imp) { c.vel += imp * (1.f / rl::CAR_MASS); }
+GGL_HD void car_apply_impulse(CarDev& c, V3 imp, V3 rel) {
+    car_apply_central_impulse(c, imp);
+    c.angVel += mul(c.invInertiaW, cross(rel, imp));
+}
+// btRigidBody::computeImpulseDenominator
+GGL_HD float impulse_denominator(float invMass, const M3& invInertiaW, V3 r0, V3 n) {
+    V3 c0 = cross(r0, n);
+    V3 vec = cross(tmul(invInertiaW, c0), r0);
+    return invMass + dot(n, vec);
+}
+
+struct WheelGeom {
+    V3 conn;            // chassis connection point (car space, bt)
+    float restLen, radius, forceScale;
+};
+GGL_HD WheelGeom wheel_geom(int i) {
+    const bool front = i < 2;
+    const bool left = (i % 2) != 0;
+    WheelGeom g;
+    float x = front ? rl::FRONT_WHEEL_X : rl::BACK_WHEEL_X;
+    float y = front ? rl::FRONT_WHEEL_Y : rl::BACK_WHEEL_Y;
+    float z = front ? rl::FRONT_WHEEL_Z : rl::BACK_WHEEL_Z;
+    if (left) y *= -1;
+    g.conn = v3(x, y, z) * kUU2BT;
+    float rest = front ? rl::FRONT_SUS_REST : rl::BACK_SUS_REST;
+    rest -= rl::MAX_SUSP_TRAVEL;
+    g.restLen = rest * kUU2BT;
+    g.radius = (front ? rl::FRONT_WHEEL_RAD : rl::BACK_WHEEL_RAD) * kUU2BT;
+    g.forceScale = front ? rl::SUSP_FORCE_SCALE_FRONT : rl::SUSP_FORCE_SCALE_BACK;
+    return g;
+}
+constexpr float kSuspTravel = ((rl::MAX_SUSP_TRAVEL * kUU2BT) * 100) / 100;
+
+// ---------------------------------------------------------------------------------------------- ray casting
+struct RayHit {
+    float t;
+    V3 normal;
+    int ground;   // GroundKind
+};
+
+GGL_HD void ray_vs_plane(V3 from, V3 to, V3 n, float c, RayHit& h) {
+    float da = dot(n, from) - c;
+    float db = dot(n, to) - c;
+    if (da * db >= 0.f) return;
+    float t = da / (da - db);
+    if (t < h.t) {
+        h.t = t;
+        h.normal = (da <= 0.f) ? -n : n;
+        h.ground = GROUND_WORLD;
+    }
+}
+
+GGL_HD void ray_vs_tri(V3 from, V3 to, const Tri& tr, RayHit& h) {
+    V3 v10 = tr.v1 - tr.v0, v20 = tr.v2 - tr.v0;
+    V3 tn = cross(v10, v20);
+    float dist = dot(tr.v0, tn);
+    float da = dot(tn, from) - dist;
+    float db = dot(tn, to) - dist;
+    if (da * db >= 0.f) return;
+    float t = da / (da - db);
+    if (t < h.t) {
+        float tol = len2(tn) * -0.0001f;
+        float s = 1.f - t;
+        V3 p = v3(s * from.x + t * to.x, s * from.y + t * to.y, s * from.z + t * to.z);
+        V3 v0p = tr.v0 - p, v1p = tr.v1 - p;
+        if (dot(cross(v0p, v1p), tn) >= tol) {
+            V3 v2p = tr.v2 - p;
+            if (dot(cross(v1p, v2p), tn) >= tol && dot(cross(v2p, v0p), tn) >= tol) {
+                V3 nn = normalized(tn);
+                h.t = t;
+                h.normal = (da <= 0.f) ? -nn : nn;
+                h.ground = GROUND_WORLD;
+            }
+        }
+    }
+}
+
+GGL_HD void ray_vs_sphere(V3 from, V3 to, V3 center, float radius, int kind, RayHit& h) {
+    V3 d = to - from, m = from - center;
+    float a = dot(d, d), b = dot(m, d), c = dot(m, m) - radius * radius;
+    if (a <= 0.f) return;
+    if (c > 0.f && b > 0.f) return;
+    float disc = b * b - a * c;
+    if (disc < 0.f) return;
+    float t = (-b - sqrtf(disc)) / a;
+    if (t < 0.f) t = 0.f;
+    if (t < h.t) {
+        V3 p = from + d * t;
+        h.t = t;
+        h.normal = safe_normalized(p - center);
+        h.ground = kind;
+    }
+}
+
+GGL_HD void ray_vs_car_box(V3 from, V3 to, const CarDev& oc, int kind, RayHit& h) {
+    // into the hitbox frame
+    V3 o = tmul(oc.basis, from - oc.pos) - car_hitbox_offset();
+    V3 e = tmul(oc.basis, to - oc.pos) - car_hitbox_offset();
+    V3 d = e - o, he = car_half_extents();
+    float t0 = 0.f, t1 = 1.f;
+    int axis = -1; float sign = 0.f;
+    for (int i = 0; i < 3; i++) {
+        float oi = comp(o, i), di = comp(d, i), hi = comp(he, i);
+        if (fabsf(di) < 1e-12f) {
+            if (oi < -hi || oi > hi) return;
+        } else {
+            float inv = 1.f / di;
+            float ta = (-hi - oi) * inv, tb = (hi - oi) * inv;
+            float s = -1.f;
+            if (ta > tb) { float tmp = ta; ta = tb; tb = tmp; s = 1.f; }
+            if (ta > t0) { t0 = ta; axis = i; sign = s; }
+            if (tb < t1) t1 = tb;
+            if (t0 > t1) return;
+        }
+    }
+    if (axis < 0) return;   // starts inside
+    if (t0 < h.t) {
+        V3 nl = v3(0, 0, 0);
+        set_comp(nl, axis, sign);
+        h.t = t0;
+        h.normal = mul(oc.basis, nl);
+        h.ground = kind;
+    }
+}
+
+GGL_HD int grid_coord(float v, float mn, float inv, int n) {
+    int c = (int)floorf((v - mn) * inv);
+    return c < 0 ? 0 : (c >= n ? n - 1 : c);
+}
+
+// Closest hit of the segment from->to against the arena (4 planes + mesh), the ball and the other cars.
+GGL_HD void ray_cast_world(const ArenaDev& A, const WorldDev& W, int selfCar, V3 from, V3 to, RayHit& h) {
+    h.t = 1.f; h.ground = GROUND_NONE; h.normal = v3(0, 0, 0);
+    const float ex = rl::ARENA_EXTENT_X * kUU2BT, hz = rl::ARENA_HEIGHT * kUU2BT;
+    // static planes (Arena.cpp:1060-1101): floor, ceiling, -x wall, +x wall
+    ray_vs_plane(from, to, v3(0, 0, 1), 0.f, h);
+    ray_vs_plane(from - v3(0, 0, hz), to - v3(0, 0, hz), v3(0, 0, -1), 0.f, h);
+    ray_vs_plane(from - v3(-ex, 0, hz / 2), to - v3(-ex, 0, hz / 2), v3(1, 0, 0), 0.f, h);
+    ray_vs_plane(from - v3(ex, 0, hz / 2), to - v3(ex, 0, hz / 2), v3(-1, 0, 0), 0.f, h);
+    // mesh triangles through the uniform grid
+    if (W.numTris > 0) {
+        V3 mn = vmin(from, to), mx = vmax(from, to);
+        int x0 = grid_coord(mn.x, W.gridMin.x, W.invCellSize, W.gx), x1 = grid_coord(mx.x, W.gridMin.x, W.invCellSize, W.gx);
+        int y0 = grid_coord(mn.y, W.gridMin.y, W.invCellSize, W.gy), y1 = grid_coord(mx.y, W.gridMin.y, W.invCellSize, W.gy);
+        int z0 = grid_coord(mn.z, W.gridMin.z, W.invCellSize, W.gz), z1 = grid_coord(mx.z, W.gridMin.z, W.invCellSize, W.gz);
+        for (int z = z0; z <= z1; z++)
+            for (int y = y0; y <= y1; y++)
+                for (int x = x0; x <= x1; x++) {
+                    int cell = (z * W.gy + y) * W.gx + x;
+                    for (int k = W.cellStart[cell]; k < W.cellStart[cell + 1]; k++) ray_vs_tri(from, to, W.tris[W.cellTris[k]], h);
+                }
+    }
+    // dynamic bodies
+    ray_vs_sphere(from, to, A.ball.pos, rl::BALL_RADIUS * kUU2BT, GROUND_BALL, h);
+    for (int c = 0; c < A.numCars; c++)
+        if (c != selfCar) ray_vs_car_box(from, to, A.cars[c], GROUND_CAR0 + c, h);
+    // a hit on a body without contact response (a demolished car) reports nothing at all
+    // (btDefaultVehicleRaycaster::castRay, BulletDynamics/Vehicle/btDefaultVehicleRaycaster.cpp)
+    if (h.ground >= GROUND_CAR0 && A.cars[h.ground - GROUND_CAR0].isDemoed) h.ground = GROUND_NONE;
+}
+
+// ---------------------------------------------------------------------------------------------- vehicle
+GGL_HD void vehicle_first(ArenaDev& A, const WorldDev& W, int ci) {
+    CarDev& c = A.cars[ci];
+    const V3 up = car_up(c), right = car_right(c);
+    for (int i = 0; i < 4; i++) {
+        Wheel& w = c.w[i];
+        const WheelGeom g = wheel_geom(i);
+        // wheel frame with LAST tick's steer angle
+        Q4 q = quat_axis_angle(up, w.steerAngle);
+        w.latDir = mul(m3_from_quat(q), right);
+        w.hardPoint = c.pos + mul(c.basis, g.conn);
+        const V3 wheelDir = -up;
+        const float rayLen = g.restLen + kSuspTravel + g.radius - rl::SUSP_SUBTRACTION;
+        const V3 source = w.hardPoint;
+        const V3 target = source + wheelDir * rayLen;
+        w.contactPoint = target;
+        RayHit h;
+        ray_cast_world(A, W, ci, source, target, h);
+        w.ground = h.ground;
+        if (h.ground != GROUND_NONE) {
+            float s = 1.f - h.t;
+            w.contactPoint = v3(s * source.x + h.t * target.x, s * source.y + h.t * target.y, s * source.z + h.t * target.z);
+            w.contactNormal = normalized(h.normal);
+            float traceLen = dot(w.hardPoint - w.contactPoint, up);
+            w.suspLen = fclamp(traceLen - g.radius, g.restLen - kSuspTravel, g.restLen + kSuspTravel);
+            float denom = dot(w.contactNormal, up);
+            V3 relpos = w.contactPoint - c.pos;
+            V3 velAt = vel_at(c.vel, c.angVel, relpos);
+            float projVel = dot(w.contactNormal, velAt);
+            if (denom > 0.1f) {
+                float inv = 1.f / denom;
+                w.suspRelVel = projVel * inv;
+                w.clippedInv = inv;
+            } else {
+                w.suspRelVel = 0.f;
+                w.clippedInv = 10.f;
+            }
+            if (h.ground == GROUND_WORLD) {
+                float thresh = (g.restLen + g.radius) - rl::SUSP_SUBTRACTION;
+                if (traceLen < thresh) {
+                    float delta = traceLen - thresh;
+                    // resolveSingleCollision(chassis, static body, hit, normal, distance = delta, applyImpulses = false)
+                    float relVel = dot(w.contactNormal, velAt);
+                    float posErr = 0.2f * -delta / kTick;
+                    float velErr = -(1.0f + 0.f) * relVel;
+                    float denom0 = impulse_denominator(1.f / rl::CAR_MASS, c.invInertiaW, w.contactPoint - c.pos, w.contactNormal);
+                    float jacInv = 1.f / (denom0 + 0.f);
+                    float imp = posErr * jacInv + velErr * jacInv;
+                    imp = 0.f > imp ? 0.f : imp;
+                    w.extraPushback = imp / 4;
+                }
+            }
+        } else {
+            w.suspLen = g.restLen + kSuspTravel;
+            w.suspRelVel = 0.f;
+            w.contactNormal = -wheelDir;
+            w.clippedInv = 1.f;
+            w.extraPushback = 0.f;
+        }
+    }
+    // calcFrictionImpulses (btVehicleRL.cpp:313-387) with LAST tick's engine force / brake / friction factors
+    const float frictionScale = rl::CAR_MASS / 3;
+    for (int i = 0; i < 4; i++) {
+        Wheel& w = c.w[i];
+        if (w.ground == GROUND_NONE) { w.impulse = v3(0, 0, 0); continue; }
+        V3 axle = w.latDir;
+        V3 n = w.contactNormal;
+        float proj = dot(axle, n);
+        axle -= n * proj;
+        axle = safe_normalized(axle);
+        V3 fwd = safe_normalized(cross(n, axle));
+        // the body the wheel stands on
+        V3 gPos = v3(0, 0, 0), gVel = v3(0, 0, 0), gAng = v3(0, 0, 0);
+        float gInvMass = 0.f; M3 gInvI; gInvI.r0 = gInvI.r1 = gInvI.r2 = v3(0, 0, 0);
+        if (w.ground == GROUND_BALL) {
+            gPos = A.ball.pos; gVel = A.ball.vel; gAng = A.ball.angVel; gInvMass = 1.f / rl::BALL_MASS;
+            float r = rl::BALL_RADIUS * kUU2BT;
+            float ii = 1.f / (0.4f * rl::BALL_MASS * r * r);
+            gInvI.r0 = v3(ii, 0, 0); gInvI.r1 = v3(0, ii, 0); gInvI.r2 = v3(0, 0, ii);
+        } else if (w.ground >= GROUND_CAR0) {
+            const CarDev& oc = A.cars[w.ground - GROUND_CAR0];
+            gPos = oc.pos; gVel = oc.velSnap; gAng = oc.angVelSnap; gInvMass = 1.f / rl::CAR_MASS; gInvI = oc.invInertiaW;
+        }
+        // resolveSingleBilateral(chassis, cp, ground, cp, 0, axle) -> side impulse
+        V3 rel1 = w.contactPoint - c.pos, rel2 = w.contactPoint - gPos;
+        V3 v1 = vel_at(c.vel, c.angVel, rel1), v2 = vel_at(gVel, gAng, rel2);
+        V3 vrel = v1 - v2;
+        float diag = impulse_denominator(1.f / rl::CAR_MASS, c.invInertiaW, rel1, axle) + impulse_denominator(gInvMass, gInvI, rel2, axle);
+        float sideImpulse = -0.2f * dot(axle, vrel) * (1.f / diag);
+        float rolling;
+        if (w.engineForce == 0.f) {
+            if (w.brake != 0.f) {
+                V3 carRel = w.contactPoint - c.pos;
+                V3 cv = vel_at(c.vel, c.angVel, carRel) - vel_at(gVel, gAng, carRel);
+                float rv = dot(cv, fwd);
+                rolling = fclamp(-rv * 113.73963f, -w.brake, w.brake);
+            } else {
+                rolling = 0.f;
+            }
+        } else {
+            rolling = -w.engineForce / frictionScale;
+        }
+        V3 total = (fwd * rolling * w.longFriction) + (axle * sideImpulse * w.latFriction);
+        w.impulse = total * frictionScale;
+    }
+}
+
+GGL_HD V3 upwards_dir_from_wheels(const CarDev& c) {
+    V3 sum = v3(0, 0, 0);
+    for (int i = 0; i < 4; i++)
+        if (c.w[i].ground != GROUND_NONE) sum += c.w[i].contactNormal;
+    if (is_zero(sum)) return car_up(c);
+    return safe_normalized(sum);
+}
+
+GGL_HD void vehicle_second(CarDev& c) {
+    float force[4];
+    for (int i = 0; i < 4; i++) {
+        Wheel& w = c.w[i];
+        const WheelGeom g = wheel_geom(i);
+        if (w.ground != GROUND_NONE) {
+            float f = (g.restLen - w.suspLen) * rl::SUSP_STIFFNESS * w.clippedInv;
+            float damp = (w.suspRelVel < 0.f) ? rl::DAMP_COMPRESSION : rl::DAMP_RELAXATION;
+            f = f - (damp * w.suspRelVel);
+            f *= g.forceScale;
+            if (f < 0.f) f = 0.f;
+            force[i] = f;
+        } else {
+            force[i] = 0.f;
+        }
+        w.suspForce = force[i];
+    }
+    for (int i = 0; i < 4; i++) {
+        Wheel& w = c.w[i];
+        if (force[i] != 0.f) {
+            V3 off = w.contactPoint - c.pos;
+            float scale = (force[i] * kTick) + w.extraPushback;
+            car_apply_impulse(c, w.contactNormal * scale, off);
+        }
+    }
+    // applyFrictionImpulses
+    V3 up = car_up(c);
+    for (int i = 0; i < 4; i++) {
+        Wheel& w = c.w[i];
+        if (!is_zero(w.impulse)) {
+            V3 off = w.contactPoint - c.pos;
+            float upDot = dot(up, off);
+            V3 rel = off - up * upDot;
+            car_apply_impulse(c, w.impulse * kTick, rel);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------- car logic
+GGL_HD void update_wheels(CarDev& c, int numWheels, float fwdSpeedUU) {
+    const float absSpeed = fabsf(fwdSpeedUU);
+    bool worldContact = false;
+    for (int i = 0; i < 4; i++) worldContact |= (c.w[i].ground == GROUND_WORLD);
+    if (c.controls.handbrake) c.handbrakeVal += rl::POWERSLIDE_RISE_RATE * kTick;
+    else c.handbrakeVal -= rl::POWERSLIDE_FALL_RATE * kTick;
+    c.handbrakeVal = fclamp(c.handbrakeVal, 0.f, 1.f);
+
+    float realThrottle = c.controls.throttle;
+    float realBrake = 0.f;
+    if (c.controls.boost && c.boost > 0.f) realThrottle = 1.f;
+    {
+        float driveScale = curve_drive_torque(absSpeed);
+        float engineThrottle = realThrottle;
+        if (!c.controls.handbrake) {
+            float absThrottle = fabsf(realThrottle);
+            if (absThrottle >= rl::THROTTLE_DEADZONE) {
+                if (absSpeed > rl::STOPPING_FORWARD_VEL && fsgn(realThrottle) != fsgn(fwdSpeedUU)) {
+                    realBrake = 1.f;
+                    if (absSpeed > rl::BRAKING_NO_THROTTLE_SPEED_THRESH) engineThrottle = 0.f;
+                }
+            } else {
+                engineThrottle = 0.f;
+                realBrake = (absSpeed < rl::STOPPING_FORWARD_VEL) ? 1.f : rl::COASTING_BRAKE_FACTOR;
+            }
+        }
+        if (numWheels < 3) driveScale /= 4;
+        float engineForce = engineThrottle * (rl::THROTTLE_TORQUE_AMOUNT * kUU2BT) * driveScale;
+        float brakeForce = realBrake * (rl::BRAKE_TORQUE_AMOUNT * kUU2BT);
+        for (int i = 0; i < 4; i++) { c.w[i].engineForce = engineForce; c.w[i].brake = brakeForce; }
+    }
+    {
+        float steer = curve_steer_angle(absSpeed);
+        if (c.handbrakeVal != 0.f) steer += (curve_powerslide_steer(absSpeed) - steer) * c.handbrakeVal;
+        steer *= c.controls.steer;
+        c.w[0].steerAngle = steer;
+        c.w[1].steerAngle = steer;
+    }
+    for (int i = 0; i < 4; i++) {
+        Wheel& w = c.w[i];
+        if (w.ground == GROUND_NONE) continue;
+        V3 latDir = w.latDir;
+        V3 longDir = cross(latDir, w.contactNormal);
+        float input = 0.f;
+        V3 delta = w.hardPoint - c.pos;
+        V3 cv = (cross(c.angVel, delta) + c.vel) * kBT2UU;
+        float base = fabsf(dot(cv, latDir));
+        if (base > 5.f) input = base / (fabsf(dot(cv, longDir)) + base);
+        float lat = curve_lat_friction(input);
+        float lng = 1.f;   // LONG_FRICTION_CURVE is empty -> default output 1
+        if (c.handbrakeVal != 0.f) {
+            float hb = c.handbrakeVal;
+            lat *= (0.1f - 1.f) * hb + 1.f;     // HANDBRAKE_LAT_FRICTION_FACTOR_CURVE is the constant 0.1
+            lng *= (curve_handbrake_long(input) - 1.f) * hb + 1.f;
+        } else {
+            lng = 1.f;
+        }
+        if (realThrottle == 0.f) {
+            float ns = curve_non_sticky(w.contactNormal.z);
+            lat *= ns;
+            lng *= ns;
+        }
+        w.latFriction = lat;
+        w.longFriction = lng;
+    }
+    if (worldContact) {
+        V3 upDir = upwards_dir_from_wheels(c);
+        bool fullStick = (realThrottle != 0.f) || (absSpeed > rl::STOPPING_FORWARD_VEL);
+        float stick = 0.5f;
+        if (fullStick) stick += 1.f - fabsf(upDir.z);
+        c.force += upDir * stick * (rl::GRAVITY_Z * kUU2BT) * rl::CAR_MASS;
+    }
+}
+
+GGL_HD void update_boost(CarDev& c) {
+    if (c.timeSpentBoosting > 0.f) {
+        if (!c.controls.boost && c.timeSpentBoosting >= rl::BOOST_MIN_TIME) c.timeSpentBoosting = 0.f;
+        else c.timeSpentBoosting += kTick;
+    } else if (c.controls.boost) {
+        c.timeSpentBoosting = kTick;
+    }
+    if (c.boost > 0.f && c.timeSpentBoosting > 0.f) {
+        c.boost = fmaxf(c.boost - rl::BOOST_USED_PER_SECOND * kTick, 0.f);
+        float accel = (c.isOnGround ? rl::BOOST_ACCEL_GROUND : rl::BOOST_ACCEL_AIR) * kUU2BT;
+        c.force += accel * car_fwd(c) * rl::CAR_MASS;
+    }
+    c.boost = fminf(c.boost, rl::BOOST_MAX);
+}
+
+GGL_HD void update_jump(CarDev& c, bool jumpPressed) {
+    if (c.isOnGround && !c.isJumping) {
+        if (!(c.hasJumped && c.jumpTime < rl::JUMP_MIN_TIME + rl::JUMP_RESET_TIME_PAD)) {
+            c.hasJumped = 0;
+            c.jumpTime = 0.f;
+        }
+    }
+    if (c.isJumping) {
+        c.isJumping = (c.jumpTime < rl::JUMP_MIN_TIME || (c.controls.jump && c.jumpTime < rl::JUMP_MAX_TIME)) ? 1 : 0;
+    } else if (c.isOnGround && jumpPressed) {
+        c.isJumping = 1;
+        c.jumpTime = 0.f;
+        V3 f = car_up(c) * rl::JUMP_IMMEDIATE_FORCE * kUU2BT * rl::CAR_MASS;
+        car_apply_central_impulse(c, f);
+    }
+    if (c.isJumping) {
+        c.hasJumped = 1;
+        V3 f = car_up(c) * rl::JUMP_ACCEL;
+        if (c.jumpTime < rl::JUMP_MIN_TIME) f *= 0.62f;
+        c.force += f * kUU2BT * rl::CAR_MASS;
+    }
+    if (c.isJumping || c.hasJumped) c.jumpTime += kTick;
+}
+
+GGL_HD void update_air_torque(CarDev& c, bool updateAirControl) {
+    V3 dirPitch = -car_right(c), dirYaw = car_up(c), dirRoll = -car_fwd(c);
+    bool doAir = false;
+    if (c.isFlipping) c.isFlipping = (c.hasFlipped && c.flipTime < rl::FLIP_TORQUE_TIME) ? 1 : 0;
+    if (c.isFlipping) {
+        V3 rel = c.flipRelTorque;
+        if (!is_zero(c.flipRelTorque)) {
+            float pitchScale = 1.f;
+            if (rel.y != 0.f && c.controls.pitch != 0.f) {
+                if (fsgn(rel.y) == fsgn(c.controls.pitch)) {
+                    pitchScale = 1.f - fminf(fabsf(c.controls.pitch), 1.f);
+                    doAir = true;
+                }
+            }
+            rel.y *= pitchScale;
+            V3 dodge = rel * v3(rl::FLIP_TORQUE_X, rl::FLIP_TORQUE_Y, 0.f);
+            M3 m = mul(inverse(c.invInertiaW), c.basis);
+            c.torque += mul(m, dodge);
+        } else {
+            doAir = true;
+        }
+    } else {
+        doAir = true;
+    }
+    doAir = doAir && !c.isAutoFlipping;
+    doAir = doAir && updateAirControl;
+    if (doAir) {
+        float pitchTorqueScale = 1.f;
+        V3 torque;
+        if (c.controls.pitch != 0.f || c.controls.yaw != 0.f || c.controls.roll != 0.f) {
+            if (c.isFlipping) pitchTorqueScale = 0.f;
+            else if (c.hasFlipped && c.flipTime < rl::FLIP_TORQUE_TIME + rl::FLIP_PITCHLOCK_EXTRA_TIME) pitchTorqueScale = 0.f;
+            torque = (c.controls.pitch * dirPitch * pitchTorqueScale * rl::AIR_TORQUE_X) +
+                     (c.controls.yaw * dirYaw * rl::AIR_TORQUE_Y) +
+                     (c.controls.roll * dirRoll * rl::AIR_TORQUE_Z);
+        } else {
+            torque = v3(0, 0, 0);
+        }
+        V3 av = c.angVel;
+        float dampPitch = dot(dirPitch, av) * rl::AIR_DAMP_X * (1.f - fabsf(c.controls.pitch * pitchTorqueScale));
+        float dampYaw = dot(dirYaw, av) * rl::AIR_DAMP_Y * (1.f - fabsf(c.controls.yaw));
+        float dampRoll = dot(dirRoll, av) * rl::AIR_DAMP_Z;
+        V3 damping = (dirYaw * dampYaw) + (dirPitch * dampPitch) + (dirRoll * dampRoll);
+        c.torque += mul(inverse(c.invInertiaW), torque - damping) * rl::CAR_TORQUE_SCALE;
+    }
+    if (c.controls.throttle != 0.f) c.force += car_fwd(c) * c.controls.throttle * rl::THROTTLE_AIR_ACCEL * kUU2BT * rl::CAR_MASS;
+}
+
+GGL_HD void update_double_jump_or_flip(CarDev& c, bool jumpPressed, float fwdSpeedUU) {
+    if (c.isOnGround) {
+        c.hasDoubleJumped = 0; c.hasFlipped = 0;
+        c.airTime = 0.f; c.airTimeSinceJump = 0.f; c.flipTime = 0.f;
+    } else {
+        c.airTime += kTick;
+        if (c.hasJumped && !c.isJumping) c.airTimeSinceJump += kTick;
+        else c.airTimeSinceJump = 0.f;
+        if (jumpPressed && c.airTimeSinceJump < rl::DOUBLEJUMP_MAX_DELAY) {
+            float mag = fabsf(c.controls.yaw) + fabsf(c.controls.pitch) + fabsf(c.controls.roll);
+            bool isFlipInput = mag >= rl::DODGE_DEADZONE;
+            bool canUse = (!c.hasDoubleJumped && !c.hasFlipped);
+            if (c.isAutoFlipping) canUse = false;
+            if (canUse) {
+                if (isFlipInput) {
+                    c.flipTime = 0.f; c.hasFlipped = 1; c.isFlipping = 1;
+                    float ratio = fabsf(fwdSpeedUU) / rl::CAR_MAX_SPEED;
+                    V3 dd = v3(-c.controls.pitch, c.controls.yaw + c.controls.roll, 0.f);
+                    if (fabsf(c.controls.yaw + c.controls.roll) < 0.1f && fabsf(c.controls.pitch) < 0.1f) dd = v3(0, 0, 0);
+                    else dd = safe_normalized(dd);
+                    c.flipRelTorque = v3(-dd.y, dd.x, 0.f);
+                    if (fabsf(dd.x) < 0.1f) dd.x = 0.f;
+                    if (fabsf(dd.y) < 0.1f) dd.y = 0.f;
+                    if (!(len2(dd) < kEps * kEps)) {
+                        bool backwards;
+                        if (fabsf(fwdSpeedUU) < 100.0f) backwards = dd.x < 0.0f;
+                        else backwards = (dd.x >= 0.0f) != (fwdSpeedUU >= 0.0f);
+                        V3 dv = dd * rl::FLIP_INITIAL_VEL_SCALE;
+                        float maxScaleX = backwards ? rl::FLIP_BACKWARD_IMPULSE_MAX_SPEED_SCALE : rl::FLIP_FORWARD_IMPULSE_MAX_SPEED_SCALE;
+                        dv.x *= ((maxScaleX - 1.f) * ratio) + 1.f;
+                        dv.y *= ((rl::FLIP_SIDE_IMPULSE_MAX_SPEED_SCALE - 1.f) * ratio) + 1.f;
+                        if (backwards) dv.x *= rl::FLIP_BACKWARD_IMPULSE_SCALE_X;
+                        V3 f = car_fwd(c);
+                        float ang = atan2f(f.y, f.x);
+                        V3 xd = v3(cosf(ang), -sinf(ang), 0.f), yd = v3(sinf(ang), cosf(ang), 0.f);
+                        V3 fin = v3(dot(dv, xd), dot(dv, yd), 0.f);
+                        car_apply_central_impulse(c, fin * kUU2BT * rl::CAR_MASS);
+                    }
+                } else {
+                    V3 f = car_up(c) * rl::JUMP_IMMEDIATE_FORCE * kUU2BT * rl::CAR_MASS;
+                    car_apply_central_impulse(c, f);
+                    c.hasDoubleJumped = 1;
+                }
+            }
+        }
+    }
+    if (c.isFlipping) {
+        c.flipTime += kTick;
+        if (c.flipTime <= rl::FLIP_TORQUE_TIME) {
+            if (c.flipTime >= rl::FLIP_Z_DAMP_START && (c.vel.z < 0.f || c.flipTime < rl::FLIP_Z_DAMP_END))
+                c.vel.z *= powf(1.f - rl::FLIP_Z_DAMP_120, kTick / (1 / 120.f));
+        }
+    } else if (c.hasFlipped) {
+        c.flipTime += kTick;
+    }
+}
+
+GGL_HD void update_auto_flip(CarDev& c, bool jumpPressed) {
+    if (jumpPressed && c.worldContactHas && c.worldContactNormal.z > rl::CAR_AUTOFLIP_NORMZ_THRESH) {
+        float yaw, pitch, roll;
+        euler_ypr_from_m3(c.basis, yaw, pitch, roll);
+        roll *= -1.f;
+        float absRoll = fabsf(roll);
+        if (absRoll > rl::CAR_AUTOFLIP_ROLL_THRESH) {
+            c.autoFlipTimer = rl::CAR_AUTOFLIP_TIME * (absRoll / kPi);
+            c.autoFlipTorqueScale = (roll > 0.f) ? 1.f : -1.f;
+            c.isAutoFlipping = 1;
+            car_apply_central_impulse(c, -car_up(c) * rl::CAR_AUTOFLIP_IMPULSE * kUU2BT * rl::CAR_MASS);
+        }
+    }
+    if (c.isAutoFlipping) {
+        if (c.autoFlipTimer <= 0.f) {
+            c.isAutoFlipping = 0;
+            c.autoFlipTimer = 0.f;
+        } else {
+            c.angVel += car_fwd(c) * rl::CAR_AUTOFLIP_TORQUE * c.autoFlipTorqueScale * kTick;
+            c.autoFlipTimer -= kTick;
+        }
+    }
+}
+
+GGL_HD void update_auto_roll(CarDev& c, int numWheels) {
+    V3 groundUp = (numWheels > 0) ? upwards_dir_from_wheels(c) : c.worldContactNormal;
+    V3 groundDown = -groundUp;
+    V3 f = car_fwd(c), r = car_right(c);
+    V3 crossRight = cross(groundUp, f);
+    V3 crossFwd = cross(groundDown, crossRight);
+    float rightFactor = 1.f - fclamp(dot(r, crossRight), 0.f, 1.f);
+    float fwdFactor = 1.f - fclamp(dot(f, crossFwd), 0.f, 1.f);
+    V3 torqueDirRight = f * (dot(r, groundUp) >= 0.f ? -1.f : 1.f);
+    V3 torqueDirFwd = r * (dot(f, groundUp) >= 0.f ? 1.f : -1.f);
+    V3 tr = torqueDirRight * rightFactor, tf = torqueDirFwd * fwdFactor;
+    c.force += groundDown * rl::CAR_AUTOROLL_FORCE * kUU2BT * rl::CAR_MASS;
+    c.torque += mul(inverse(c.invInertiaW), tf + tr) * rl::CAR_AUTOROLL_TORQUE;
+}
+
+// minstd_rand0 (libstdc++ std::default_random_engine): x <- 16807 x mod (2^31 - 1)
+GGL_HD uint32_t minstd_next(uint32_t& s) {
+    uint64_t p = (uint64_t)s * 16807ull;
+    s = (uint32_t)(p % 2147483647ull);
+    return s;
+}
+
+// Car::SetState(CarState()) part of Car::Respawn (Car.cpp:43-56, 20-36)
+GGL_HD void car_reset_state_defaults(CarDev& c) {
+    c.vel = v3(0, 0, 0); c.angVel = v3(0, 0, 0); c.velImpulseCache = v3(0, 0, 0);
+    c.flipRelTorque = v3(0, 0, 0); c.worldContactNormal = v3(0, 0, 0);
+    c.jumpTime = c.flipTime = c.airTime = c.airTimeSinceJump = 0.f;
+    c.boost = rl::BOOST_SPAWN_AMOUNT; c.timeSpentBoosting = 0.f; c.supersonicTime = 0.f; c.handbrakeVal = 0.f;
+    c.autoFlipTimer = 0.f; c.autoFlipTorqueScale = 0.f; c.carContactCooldown = 0.f; c.demoRespawnTimer = 0.f;
+    c.hitRelPos = c.hitBallPos = c.hitExtraVel = v3(0, 0, 0);
+    c.hitTick = ~0ull; c.hitTickExtra = ~0ull; c.updateCounter = 0;
+    c.carContactOtherId = 0;
+    c.isOnGround = 1; c.hasJumped = c.hasDoubleJumped = c.hasFlipped = c.isFlipping = c.isJumping = 0;
+    c.isSupersonic = c.isAutoFlipping = c.worldContactHas = c.isDemoed = c.hitValid = 0;
+    for (int i = 0; i < 4; i++) c.wheelsWithContact[i] = 0;
+    Controls z; z.throttle = z.steer = z.pitch = z.yaw = z.roll = 0.f; z.jump = z.boost = z.handbrake = z._pad = 0;
+    c.lastControls = z;
+}
+
+GGL_HD void car_respawn(ArenaDev& A, CarDev& c) {
+    const float rx[4] = {-2304, -2688, 2304, 2688};
+    int idx = (int)(minstd_next(A.rng) % 4u);
+    car_reset_state_defaults(c);
+    float sy = (c.team == 0) ? 1.f : -1.f;
+    c.pos = v3(rx[idx], -4608.f * sy, rl::CAR_RESPAWN_Z) * kUU2BT;
+    float yaw = (float)(3.14159265358979323846 / 2) + (c.team == 0 ? 0.f : kPi);
+    c.basis = m3_from_euler_ypr(yaw, -0.f, -0.f);
+    car_update_inertia(c);
+}
+
+GGL_HD void clamp_controls(Controls& k) {
+    k.throttle = fclamp(k.throttle, -1.f, 1.f); k.steer = fclamp(k.steer, -1.f, 1.f);
+    k.pitch = fclamp(k.pitch, -1.f, 1.f); k.yaw = fclamp(k.yaw, -1.f, 1.f); k.roll = fclamp(k.roll, -1.f, 1.f);
+}
+
+GGL_HD void car_pre_tick(ArenaDev& A, const WorldDev& W, int ci) {
+    CarDev& c = A.cars[ci];
+    clamp_controls(c.controls);
+    if (c.isDemoed) {
+        c.demoRespawnTimer = fmaxf(c.demoRespawnTimer - kTick, 0.f);
+        if (c.demoRespawnTimer == 0.f) car_respawn(A, c);
+    }
+    if (c.isDemoed) return;
+    vehicle_first(A, W, ci);
+    bool jumpPressed = c.controls.jump && !c.lastControls.jump;
+    int numWheels = 0;
+    for (int i = 0; i < 4; i++) {
+        uint8_t in = c.w[i].ground != GROUND_NONE;
+        c.wheelsWithContact[i] = in;
+        numWheels += in;
+    }
+    c.isOnGround = numWheels >= 3;
+    float fwdSpeedUU = dot(c.vel, car_fwd(c)) * kBT2UU;
+    update_wheels(c, numWheels, fwdSpeedUU);
+    if (numWheels < 3) update_air_torque(c, numWheels == 0);
+    else c.isFlipping = 0;
+    update_jump(c, jumpPressed);
+    update_auto_flip(c, jumpPressed);
+    update_double_jump_or_flip(c, jumpPressed, fwdSpeedUU);
+    if (c.controls.throttle != 0.f && ((numWheels > 0 && numWheels < 4) || c.worldContactHas)) update_auto_roll(c, numWheels);
+    c.worldContactHas = 0;
+    vehicle_second(c);
+    update_boost(c);
+}
+
+GGL_HD void car_post_tick(CarDev& c) {
+    if (c.isDemoed) return;
+    // _PostTickUpdate
+    float speed2 = len2(c.vel * kBT2UU);
+    if (c.isSupersonic && c.supersonicTime < rl::SUPERSONIC_MAINTAIN_MAX_TIME)
+        c.isSupersonic = speed2 >= rl::SUPERSONIC_MAINTAIN_MIN_SPEED * rl::SUPERSONIC_MAINTAIN_MIN_SPEED;
+    else
+        c.isSupersonic = speed2 >= rl::SUPERSONIC_START_SPEED * rl::SUPERSONIC_START_SPEED;
+    if (c.isSupersonic) c.supersonicTime += kTick; else c.supersonicTime = 0.f;
+    if (c.carContactCooldown > 0.f) c.carContactCooldown = fmaxf(c.carContactCooldown - kTick, 0.f);
+    c.lastControls = c.controls;
+    // _FinishPhysicsTick
+    if (!is_zero(c.velImpulseCache)) {
+        c.vel += c.velImpulseCache;
+        c.velImpulseCache = v3(0, 0, 0);
+    }
+    const float maxV = rl::CAR_MAX_SPEED * kUU2BT;
+    if (len2(c.vel) > maxV * maxV) c.vel = normalized(c.vel) * maxV;
+    if (len2(c.angVel) > rl::CAR_MAX_ANG_SPEED * rl::CAR_MAX_ANG_SPEED) c.angVel = normalized(c.angVel) * rl::CAR_MAX_ANG_SPEED;
+    c.updateCounter++;
+}
+
+}  // namespace ggl

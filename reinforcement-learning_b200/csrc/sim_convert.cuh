@@ -1,0 +1,195 @@
+// Host-side conversion between the C-ABI state structs (Unreal units, include/gigaenv.h) and the device arena blob
+// (Bullet units), plus the triangle-grid builder for the arena meshes.  The float operations are the ones the
+// reference performs in Car::SetState/GetState (Sim/Car/Car.cpp:10-36) and Ball::SetState/GetState
+// (Sim/Ball/Ball.cpp:27-49): pos * UU_TO_BT on the way in, * BT_TO_UU on the way out.
+#pragma once
+#include <string.h>
+#include <vector>
+#include "../../include/gigaenv.h"
+#include "sim_tick.cuh"
+
+namespace ggl {
+
+inline V3 v3p(const float* f) { return v3(f[0], f[1], f[2]); }
+inline void put3(float* o, V3 v) { o[0] = v.x; o[1] = v.y; o[2] = v.z; }
+
+inline Controls controls_from_host(const ggl_controls& k) {
+    Controls c;
+    c.throttle = k.throttle; c.steer = k.steer; c.pitch = k.pitch; c.yaw = k.yaw; c.roll = k.roll;
+    c.jump = k.jump; c.boost = k.boost; c.handbrake = k.handbrake; c._pad = 0;
+    return c;
+}
+inline ggl_controls controls_to_host(const Controls& c) {
+    ggl_controls k;
+    k.throttle = c.throttle; k.steer = c.steer; k.pitch = c.pitch; k.yaw = c.yaw; k.roll = c.roll;
+    k.jump = c.jump; k.boost = c.boost; k.handbrake = c.handbrake; k._pad = 0;
+    return k;
+}
+
+inline void car_from_host(const ggl_car_state& s, CarDev& c, int index, int numCars) {
+    memset(&c, 0, sizeof(c));
+    c.pos = v3p(s.pos) * kUU2BT;
+    // host rot = forward, right, up (columns of the basis)
+    V3 f = v3p(s.rot), r = v3p(s.rot + 3), u = v3p(s.rot + 6);
+    c.basis.r0 = v3(f.x, r.x, u.x); c.basis.r1 = v3(f.y, r.y, u.y); c.basis.r2 = v3(f.z, r.z, u.z);
+    c.vel = v3p(s.vel) * kUU2BT;
+    c.angVel = v3p(s.ang_vel);
+    car_update_inertia(c);
+    c.flipRelTorque = v3p(s.flip_rel_torque);
+    c.worldContactNormal = v3p(s.world_contact_normal);
+    c.jumpTime = s.jump_time; c.flipTime = s.flip_time; c.airTime = s.air_time; c.airTimeSinceJump = s.air_time_since_jump;
+    c.boost = s.boost; c.timeSpentBoosting = s.time_spent_boosting; c.supersonicTime = s.supersonic_time;
+    c.handbrakeVal = s.handbrake_val; c.autoFlipTimer = s.auto_flip_timer; c.autoFlipTorqueScale = s.auto_flip_torque_scale;
+    c.carContactCooldown = s.car_contact_cooldown; c.demoRespawnTimer = s.demo_respawn_timer;
+    c.hitRelPos = v3p(s.hit_rel_pos); c.hitBallPos = v3p(s.hit_ball_pos); c.hitExtraVel = v3p(s.hit_extra_vel);
+    c.hitTick = s.hit_tick; c.hitTickExtra = s.hit_tick_extra; c.updateCounter = s.update_counter;
+    c.carContactOtherId = s.car_contact_other_id;
+    c.id = (uint32_t)(index + 1);
+    c.team = (index < numCars / 2) ? 0 : 1;
+    c.isOnGround = s.is_on_ground; c.hasJumped = s.has_jumped; c.hasDoubleJumped = s.has_double_jumped;
+    c.hasFlipped = s.has_flipped; c.isFlipping = s.is_flipping; c.isJumping = s.is_jumping;
+    c.isSupersonic = s.is_supersonic; c.isAutoFlipping = s.is_auto_flipping; c.worldContactHas = s.world_contact_has;
+    c.isDemoed = s.is_demoed; c.hitValid = s.hit_valid;
+    for (int i = 0; i < 4; i++) c.wheelsWithContact[i] = s.wheels_with_contact[i];
+    c.controls = controls_from_host(s.controls);
+    c.lastControls = controls_from_host(s.last_controls);
+    for (int i = 0; i < 4; i++) {
+        Wheel& w = c.w[i];
+        w.steerAngle = s.wheels[i].steer_angle; w.engineForce = s.wheels[i].engine_force; w.brake = s.wheels[i].brake;
+        w.latFriction = s.wheels[i].lat_friction; w.longFriction = s.wheels[i].long_friction;
+        w.extraPushback = s.wheels[i].extra_pushback;
+        w.ground = GROUND_NONE;
+    }
+}
+
+inline void car_to_host(const CarDev& c, ggl_car_state& s) {
+    memset(&s, 0, sizeof(s));
+    put3(s.pos, c.pos * kBT2UU);
+    put3(s.rot, col(c.basis, 0)); put3(s.rot + 3, col(c.basis, 1)); put3(s.rot + 6, col(c.basis, 2));
+    put3(s.vel, c.vel * kBT2UU);
+    put3(s.ang_vel, c.angVel);
+    put3(s.flip_rel_torque, c.flipRelTorque);
+    put3(s.world_contact_normal, c.worldContactNormal);
+    s.jump_time = c.jumpTime; s.flip_time = c.flipTime; s.air_time = c.airTime; s.air_time_since_jump = c.airTimeSinceJump;
+    s.boost = c.boost; s.time_spent_boosting = c.timeSpentBoosting; s.supersonic_time = c.supersonicTime;
+    s.handbrake_val = c.handbrakeVal; s.auto_flip_timer = c.autoFlipTimer; s.auto_flip_torque_scale = c.autoFlipTorqueScale;
+    s.car_contact_cooldown = c.carContactCooldown; s.demo_respawn_timer = c.demoRespawnTimer;
+    put3(s.hit_rel_pos, c.hitRelPos); put3(s.hit_ball_pos, c.hitBallPos); put3(s.hit_extra_vel, c.hitExtraVel);
+    s.hit_tick = c.hitTick; s.hit_tick_extra = c.hitTickExtra; s.update_counter = c.updateCounter;
+    s.car_contact_other_id = c.carContactOtherId; s.id = c.id; s.team = c.team;
+    s.is_on_ground = c.isOnGround; s.has_jumped = c.hasJumped; s.has_double_jumped = c.hasDoubleJumped;
+    s.has_flipped = c.hasFlipped; s.is_flipping = c.isFlipping; s.is_jumping = c.isJumping;
+    s.is_supersonic = c.isSupersonic; s.is_auto_flipping = c.isAutoFlipping; s.world_contact_has = c.worldContactHas;
+    s.is_demoed = c.isDemoed; s.hit_valid = c.hitValid;
+    for (int i = 0; i < 4; i++) s.wheels_with_contact[i] = c.wheelsWithContact[i];
+    s.controls = controls_to_host(c.controls);
+    s.last_controls = controls_to_host(c.lastControls);
+    for (int i = 0; i < 4; i++) {
+        const Wheel& w = c.w[i];
+        s.wheels[i].steer_angle = w.steerAngle; s.wheels[i].engine_force = w.engineForce; s.wheels[i].brake = w.brake;
+        s.wheels[i].lat_friction = w.latFriction; s.wheels[i].long_friction = w.longFriction;
+        s.wheels[i].extra_pushback = w.extraPushback;
+    }
+}
+
+// Physical state only; env-layer bookkeeping (GameState, trackers) is left untouched.
+inline void arena_phys_from_host(const ggl_arena_state& st, ArenaDev& A) {
+    A.tickCount = st.tick_count;
+    A.numCars = st.num_cars;
+    BallDev& b = A.ball;
+    memset(&b, 0, sizeof(b));
+    b.pos = v3p(st.ball.pos) * kUU2BT;
+    b.vel = v3p(st.ball.vel) * kUU2BT;
+    b.angVel = v3p(st.ball.ang_vel);
+    b.updateCounter = st.ball.update_counter;
+    for (int i = 0; i < st.num_cars && i < kMaxCars; i++) car_from_host(st.cars[i], A.cars[i], i, st.num_cars);
+    for (int p = 0; p < kNumPads; p++) {
+        A.pads[p].isActive = st.pads[p].is_active;
+        A.pads[p].cooldown = st.pads[p].cooldown;
+        A.pads[p].prevLockedCarId = st.pads[p].prev_locked_car_id;
+        A.pads[p].curLockedCarId = 0;
+    }
+}
+
+inline void arena_phys_to_host(const ArenaDev& A, ggl_arena_state& st) {
+    memset(&st, 0, sizeof(st));
+    st.tick_count = A.tickCount;
+    st.num_cars = A.numCars;
+    put3(st.ball.pos, A.ball.pos * kBT2UU);
+    put3(st.ball.vel, A.ball.vel * kBT2UU);
+    put3(st.ball.ang_vel, A.ball.angVel);
+    st.ball.update_counter = A.ball.updateCounter;
+    for (int i = 0; i < A.numCars && i < kMaxCars; i++) car_to_host(A.cars[i], st.cars[i]);
+    for (int p = 0; p < kNumPads; p++) {
+        st.pads[p].is_active = A.pads[p].isActive;
+        st.pads[p].cooldown = A.pads[p].cooldown;
+        st.pads[p].prev_locked_car_id = A.pads[p].prevLockedCarId;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------- arena meshes
+struct WorldHost {
+    std::vector<Tri> tris;
+    std::vector<int> cellStart, cellTris;
+    int gx = 1, gy = 1, gz = 1;
+    V3 gridMin = v3(0, 0, 0);
+    float cellSize = 1.f;
+};
+
+// .cmf layout (CollisionMeshFile.cpp:11-35): int32 numTris, int32 numVerts, int32 tri[numTris][3], float vert[numVerts][3]
+inline bool world_add_cmf(WorldHost& W, const uint8_t* data, size_t size) {
+    if (size < 8) return false;
+    int32_t nt, nv;
+    memcpy(&nt, data, 4); memcpy(&nv, data + 4, 4);
+    if (nt < 0 || nv < 0 || size < 8 + (size_t)nt * 12 + (size_t)nv * 12) return false;
+    const int32_t* idx = (const int32_t*)(data + 8);
+    const float* vert = (const float*)(data + 8 + (size_t)nt * 12);
+    for (int i = 0; i < nt; i++) {
+        int a = idx[3 * i], b = idx[3 * i + 1], c = idx[3 * i + 2];
+        if (a < 0 || b < 0 || c < 0 || a >= nv || b >= nv || c >= nv) return false;
+        Tri t;
+        t.v0 = v3p(vert + 3 * a); t.v1 = v3p(vert + 3 * b); t.v2 = v3p(vert + 3 * c);
+        W.tris.push_back(t);
+    }
+    return true;
+}
+
+// Uniform grid (cell = 5 bt = 250 uu) over the triangles; a triangle is listed in every cell its AABB (+0.1) touches.
+inline void world_build_grid(WorldHost& W) {
+    W.cellSize = 5.f;
+    W.gridMin = v3(-4500.f * kUU2BT, -6200.f * kUU2BT, -100.f * kUU2BT);
+    V3 gmax = v3(4500.f * kUU2BT, 6200.f * kUU2BT, 2200.f * kUU2BT);
+    W.gx = (int)ceilf((gmax.x - W.gridMin.x) / W.cellSize);
+    W.gy = (int)ceilf((gmax.y - W.gridMin.y) / W.cellSize);
+    W.gz = (int)ceilf((gmax.z - W.gridMin.z) / W.cellSize);
+    const int nc = W.gx * W.gy * W.gz;
+    std::vector<std::vector<int>> cells(nc);
+    const float inv = 1.f / W.cellSize;
+    for (size_t i = 0; i < W.tris.size(); i++) {
+        const Tri& t = W.tris[i];
+        V3 mn = vmin(t.v0, vmin(t.v1, t.v2)) - v3(0.1f, 0.1f, 0.1f), mx = vmax(t.v0, vmax(t.v1, t.v2)) + v3(0.1f, 0.1f, 0.1f);
+        int x0 = grid_coord(mn.x, W.gridMin.x, inv, W.gx), x1 = grid_coord(mx.x, W.gridMin.x, inv, W.gx);
+        int y0 = grid_coord(mn.y, W.gridMin.y, inv, W.gy), y1 = grid_coord(mx.y, W.gridMin.y, inv, W.gy);
+        int z0 = grid_coord(mn.z, W.gridMin.z, inv, W.gz), z1 = grid_coord(mx.z, W.gridMin.z, inv, W.gz);
+        for (int z = z0; z <= z1; z++)
+            for (int y = y0; y <= y1; y++)
+                for (int x = x0; x <= x1; x++) cells[(z * W.gy + y) * W.gx + x].push_back((int)i);
+    }
+    W.cellStart.assign(nc + 1, 0);
+    W.cellTris.clear();
+    for (int c = 0; c < nc; c++) {
+        W.cellStart[c] = (int)W.cellTris.size();
+        W.cellTris.insert(W.cellTris.end(), cells[c].begin(), cells[c].end());
+    }
+    W.cellStart[nc] = (int)W.cellTris.size();
+}
+
+inline WorldDev world_view(const WorldHost& W) {
+    WorldDev d;
+    d.tris = W.tris.data(); d.numTris = (int)W.tris.size();
+    d.cellStart = W.cellStart.data(); d.cellTris = W.cellTris.data();
+    d.gx = W.gx; d.gy = W.gy; d.gz = W.gz; d.gridMin = W.gridMin; d.cellSize = W.cellSize; d.invCellSize = 1.f / W.cellSize;
+    return d;
+}
+
+}  // namespace ggl

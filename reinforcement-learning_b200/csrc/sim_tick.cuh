@@ -1,0 +1,166 @@
+// One 120 Hz arena tick and its phase structure (Arena::Step, RocketSim/src/Sim/Arena/Arena.cpp:716-812).
+//
+// The tick is written as PHASES so that the lanes of the group that owns an arena can share the work:
+//   phase_cars_pre   per car   : Car::_PreTickUpdate (rays, friction, control logic, suspension, boost)
+//   phase_world      leader    : pads pre-tick, gravity, damping, contacts, solver, integration
+//   phase_cars_post  per car   : Car::_PostTickUpdate + _FinishPhysicsTick
+//   phase_finish     leader    : boost pad pickup, ball finish, tick counter
+// `Exec` tells a lane which cars it owns and how to synchronise the group (host build: one lane, no-op sync).
+#pragma once
+#include "sim_world.cuh"
+#include "sim_boxbox.cuh"
+#include "sim_boxtri.cuh"
+
+namespace ggl {
+
+struct ExecSerial {
+    GGL_HD int lane() const { return 0; }
+    GGL_HD int lanes() const { return 1; }
+    GGL_HD void sync() const {}
+};
+
+GGL_HD V3 pad_pos_uu(int i) {
+    // RocketSim order: 6 big pads then 28 small ones (RLConst.h:192-253)
+    const float big[6][3] = {{-3584.f, 0.f, 73.f}, {3584.f, 0.f, 73.f}, {-3072.f, 4096.f, 73.f}, {3072.f, 4096.f, 73.f}, {-3072.f, -4096.f, 73.f}, {3072.f, -4096.f, 73.f}};
+    const float sm[28][2] = {{0.f, -4240.f}, {-1792.f, -4184.f}, {1792.f, -4184.f}, {-940.f, -3308.f}, {940.f, -3308.f}, {0.f, -2816.f}, {-3584.f, -2484.f},
+                             {3584.f, -2484.f}, {-1788.f, -2300.f}, {1788.f, -2300.f}, {-2048.f, -1036.f}, {0.f, -1024.f}, {2048.f, -1036.f}, {-1024.f, 0.f},
+                             {1024.f, 0.f}, {-2048.f, 1036.f}, {0.f, 1024.f}, {2048.f, 1036.f}, {-1788.f, 2300.f}, {1788.f, 2300.f}, {-3584.f, 2484.f},
+                             {3584.f, 2484.f}, {0.f, 2816.f}, {-940.f, 3308.f}, {940.f, 3308.f}, {-1792.f, 4184.f}, {1792.f, 4184.f}, {0.f, 4240.f}};
+    if (i < 6) return v3(big[i][0], big[i][1], big[i][2]);
+    return v3(sm[i - 6][0], sm[i - 6][1], 70.f);
+}
+
+// world AABB of the car's compound shape (btCompoundShape::getAabb over the child box AABB)
+GGL_HD void car_aabb(const CarDev& c, V3& mn, V3& mx) {
+    const BoxGeom bg = car_box();
+    V3 off = car_hitbox_offset();
+    V3 lmin = off - bg.full, lmax = off + bg.full;
+    V3 lhe = (lmax - lmin) * 0.5f, lc = (lmax + lmin) * 0.5f;
+    V3 centre = c.pos + mul(c.basis, lc);
+    V3 ext = v3(dot(vabs(c.basis.r0), lhe), dot(vabs(c.basis.r1), lhe), dot(vabs(c.basis.r2), lhe));
+    mn = centre - ext; mx = centre + ext;
+}
+
+// BoostPad::_CheckCollide (Sim/BoostPad/BoostPad.cpp:62-86) reached through BoostPadGrid::CheckCollision
+GGL_HD void pads_check_car(ArenaDev& A, int ci) {
+    const CarDev& car = A.cars[ci];
+    if (car.isDemoed || car.boost >= 100.f) return;
+    V3 posUU = car.pos * kBT2UU;
+    if (posUU.z > rl::PAD_CYL_HEIGHT + 250.f) return;
+    // 8 x 10 grid of 1024 uu cells, 3x3 neighbourhood of the car's cell
+    int ix = (int)(posUU.x / 1024 + 4), iy = (int)(posUU.y / 1024 + 5);
+    V3 amin, amax; bool haveAabb = false;
+    for (int p = 0; p < kNumPads; p++) {
+        V3 pp = pad_pos_uu(p);
+        int px = (int)(pp.x / 1024 + 4), py = (int)(pp.y / 1024 + 5);
+        int lx0 = ix - 1 < 0 ? 0 : ix - 1, lx1 = ix + 1 > 7 ? 7 : ix + 1, ly0 = iy - 1 < 0 ? 0 : iy - 1, ly1 = iy + 1 > 9 ? 9 : iy + 1;
+        if (px < lx0 || px > lx1 || py < ly0 || py > ly1) continue;
+        const bool big = p < 6;
+        V3 pbt = pp * kUU2BT;
+        bool colliding = false;
+        if (A.pads[p].prevLockedCarId == car.id) {
+            if (!haveAabb) { car_aabb(car, amin, amax); haveAabb = true; }
+            float boxRad = (big ? rl::PAD_BOX_RAD_BIG : rl::PAD_BOX_RAD_SMALL) * kUU2BT;
+            V3 bmin = pbt - v3(boxRad, boxRad, 0), bmax = pbt + v3(boxRad, boxRad, rl::PAD_BOX_HEIGHT * kUU2BT);
+            colliding = (bmax.x > amin.x && bmax.y > amin.y && bmax.z > amin.z) && (bmin.x < amax.x && bmin.y < amax.y && bmin.z < amax.z);
+        } else {
+            float rad = (big ? rl::PAD_CYL_RAD_BIG : rl::PAD_CYL_RAD_SMALL) * kUU2BT;
+            float dx = car.pos.x - pbt.x, dy = car.pos.y - pbt.y;
+            if (dx * dx + dy * dy < rad * rad) colliding = fabsf(car.pos.z - pbt.z) < (rl::PAD_CYL_HEIGHT * kUU2BT);
+        }
+        if (colliding) A.pads[p].curLockedCarId = car.id;
+    }
+}
+
+GGL_HD void phase_world(ArenaDev& A, const WorldDev& W) {
+    // boost pads pre-tick (BoostPad.cpp:51-59)
+    if (A.numCars > 0)
+        for (int p = 0; p < kNumPads; p++) {
+            PadDev& pd = A.pads[p];
+            if (pd.cooldown > 0.f) pd.cooldown = fmaxf(pd.cooldown - kTick, 0.f);
+            pd.isActive = (pd.cooldown == 0.f);
+            pd.curLockedCarId = 0;
+        }
+    // gravity on active bodies, then damping (ball only has any)
+    const V3 g = v3(0, 0, rl::GRAVITY_Z * kUU2BT);
+    if (A.ball.active) A.ball.force += g * (1.f / kBallInvMass);
+    for (int i = 0; i < A.numCars; i++)
+        if (!A.cars[i].isDemoed) A.cars[i].force += g * (1.f / (1.f / rl::CAR_MASS));
+    A.ball.vel *= powf(1.f - rl::BALL_DRAG, kTick);
+    A.ball.angVel *= powf(1.f - 0.f, kTick);
+    // contacts at the CURRENT transforms, then the solver
+    collide_all(A, W);
+    bool ballAwake = A.ball.active != 0;
+    if (!ballAwake) {
+        for (int k = 0; k < A.numContacts; k++)
+            if (A.contacts[k].bodyB == 0) ballAwake = true;      // touched by an active car: the island wakes it up
+        if (!ballAwake) {
+            int w = 0;
+            for (int k = 0; k < A.numContacts; k++)
+                if (A.contacts[k].bodyA != 0) A.contacts[w++] = A.contacts[k];
+            A.numContacts = w;
+        }
+    }
+    uint32_t wasActive = A.ball.active;
+    A.ball.active = ballAwake ? 1u : 0u;
+    solve_contacts(A);
+    // integrate transforms with the solved velocities, clear forces
+    if (ballAwake) A.ball.pos = A.ball.pos + A.ball.vel * kTick;
+    A.ball.active = wasActive;
+    A.ball.force = v3(0, 0, 0); A.ball.torque = v3(0, 0, 0);
+    for (int i = 0; i < A.numCars; i++) {
+        CarDev& c = A.cars[i];
+        if (!c.isDemoed) {
+            V3 np; M3 nb;
+            integrate_transform(c.pos, c.basis, c.vel, c.angVel, kTick, np, nb);
+            c.pos = np; c.basis = nb;
+            car_update_inertia(c);
+        }
+        c.force = v3(0, 0, 0); c.torque = v3(0, 0, 0);
+    }
+}
+
+GGL_HD void phase_finish(ArenaDev& A) {
+    // boost pad pickup: cars in players[] slot order (the reference iterates its car set), then pads post-tick
+    for (int s = 0; s < A.numCars; s++) pads_check_car(A, A.slotCar[s]);
+    if (A.numCars > 0)
+        for (int p = 0; p < kNumPads; p++) {
+            PadDev& pd = A.pads[p];
+            uint32_t locked = 0;
+            if (pd.curLockedCarId) {
+                locked = pd.curLockedCarId;
+                if (pd.isActive) {
+                    CarDev& c = A.cars[locked - 1];
+                    c.boost = fminf(c.boost + (p < 6 ? rl::PAD_BOOST_BIG : rl::PAD_BOOST_SMALL), rl::BOOST_MAX);
+                    pd.isActive = 0;
+                    pd.cooldown = p < 6 ? rl::PAD_COOLDOWN_BIG : rl::PAD_COOLDOWN_SMALL;
+                }
+            }
+            pd.prevLockedCarId = locked;
+        }
+    // Ball::_FinishPhysicsTick
+    BallDev& b = A.ball;
+    if (!is_zero(b.velImpulseCache)) { b.vel += b.velImpulseCache; b.velImpulseCache = v3(0, 0, 0); }
+    const float maxV = rl::BALL_MAX_SPEED * kUU2BT;
+    if (len2(b.vel) > maxV * maxV) b.vel = normalized(b.vel) * maxV;
+    if (len2(b.angVel) > rl::BALL_MAX_ANG_SPEED * rl::BALL_MAX_ANG_SPEED) b.angVel = normalized(b.angVel) * rl::BALL_MAX_ANG_SPEED;
+    b.updateCounter++;
+    A.tickCount++;
+}
+
+template <class Exec>
+GGL_HD void arena_tick(ArenaDev& A, const WorldDev& W, const Exec& ex) {
+    if (ex.lane() == 0) A.ball.active = (len2(A.ball.vel) == 0.f && len2(A.ball.angVel) == 0.f) ? 0u : 1u;
+    for (int c = ex.lane(); c < A.numCars; c += ex.lanes()) { A.cars[c].velSnap = A.cars[c].vel; A.cars[c].angVelSnap = A.cars[c].angVel; }
+    ex.sync();
+    for (int c = ex.lane(); c < A.numCars; c += ex.lanes()) car_pre_tick(A, W, c);
+    ex.sync();
+    if (ex.lane() == 0) phase_world(A, W);
+    ex.sync();
+    for (int c = ex.lane(); c < A.numCars; c += ex.lanes()) car_post_tick(A.cars[c]);
+    ex.sync();
+    if (ex.lane() == 0) phase_finish(A);
+    ex.sync();
+}
+
+}  // namespace ggl

@@ -1,0 +1,554 @@
+// The rigid-body part of one tick: gravity, damping, contact generation for the fixed scene
+// "<= 6 boxes + 1 sphere + 4 planes + triangle meshes", the game-logic contact callbacks, a projected Gauss-Seidel
+// solver with split-impulse penetration recovery, and transform integration.
+//
+// It is a fixed-function restatement of what the reference obtains from its vendored Bullet 3.24 (paths under
+// GigaLearnCPP/RLGymCPP/RocketSim/libsrc/bullet3-3.24 unless noted):
+//   BulletDynamics/Dynamics/btDiscreteDynamicsWorld.cpp:325-431,985-1044   step / predict / integrate
+//   BulletCollision/CollisionDispatch/btConvexPlaneCollisionAlgorithm.cpp:92-131 convex vs plane (deepest support vertex)
+//   BulletCollision/CollisionDispatch/SphereTriangleDetector.cpp:28-236     sphere vs triangle
+//   BulletCollision/NarrowPhaseCollision/btGjkPairDetector.cpp              closest points box/sphere, box/triangle (margins)
+//   BulletCollision/CollisionDispatch/btBoxBoxDetector.cpp:267              box vs box SAT
+//   BulletCollision/CollisionDispatch/btManifoldResult.cpp:56-77,109-206    material combine + contact callback
+//   BulletCollision/NarrowPhaseCollision/btPersistentManifold.cpp:110-227   4-point manifold reduction
+//   BulletDynamics/ConstraintSolver/btSequentialImpulseConstraintSolver.cpp:795-990,1071-1211,1601-1830,1878-1904
+//   RocketSim/src/Sim/Arena/Arena.cpp:218-427                                contact callbacks (car-ball, car-car, car-world, ball-world)
+#pragma once
+#include "sim_car.cuh"
+
+namespace ggl {
+
+constexpr float kBallRadiusBT = rl::BALL_RADIUS * kUU2BT;
+constexpr float kBallCBT = (rl::BALL_RADIUS * kUU2BT + 0.08f) * 0.02f;     // contact breaking threshold of the ball shape
+constexpr float kBallInvMass = 1.f / rl::BALL_MASS;
+
+// box shape of the car as the reference builds it: implicit half extents = he - 0.04, margin limited to 10% of the
+// smallest half extent (btBoxShape ctor + setSafeMargin)
+struct BoxGeom {
+    V3 core;        // half extents without margin
+    float margin;
+    V3 full;        // core + margin
+};
+GGL_HD BoxGeom car_box() {
+    BoxGeom b;
+    V3 he = car_half_extents();
+    b.core = he - v3(rl::CONVEX_MARGIN, rl::CONVEX_MARGIN, rl::CONVEX_MARGIN);
+    float mn = fminf(he.x, fminf(he.y, he.z));
+    float safe = 0.1f * mn;
+    b.margin = safe < rl::CONVEX_MARGIN ? safe : rl::CONVEX_MARGIN;
+    b.full = b.core + v3(b.margin, b.margin, b.margin);
+    return b;
+}
+// contact breaking threshold of the car's compound shape: 0.02 * (bounding sphere radius + |centre|) of its local AABB
+GGL_HD float car_cbt() {
+    BoxGeom b = car_box();
+    V3 off = car_hitbox_offset();
+    V3 mn = off - b.full, mx = off + b.full;
+    float radius = len(mx - mn) * 0.5f;
+    V3 centre = (mn + mx) * 0.5f;
+    return (radius + len(centre)) * 0.02f;
+}
+
+GGL_HD float ball_inv_inertia() { return 1.f / (0.4f * rl::BALL_MASS * kBallRadiusBT * kBallRadiusBT); }
+
+// ---------------------------------------------------------------------------------------------- contact emission
+struct ManifoldCtx {     // <= 4 points per body pair, rebuilt each tick
+    int first;           // index of the manifold's first row in A.contacts
+    int count;
+    V3 localA[4];
+};
+
+GGL_HD float area3(V3 p, V3 q, V3 r, V3 s) { return len2(cross(p - q, s - r)); }
+
+// Adds a point to the manifold (replacement policy of btPersistentManifold::sortCachedPoints). Returns the row index.
+GGL_HD int manifold_add(ArenaDev& A, ManifoldCtx& m, const Contact& c, V3 localA) {
+    int idx;
+    if (m.count < 4) {
+        if (A.numContacts >= kMaxContacts) return -1;
+        idx = m.count++;
+        A.numContacts++;
+    } else {
+        int deepest = -1;
+        float maxPen = c.dist;
+        for (int i = 0; i < 4; i++)
+            if (A.contacts[m.first + i].dist < maxPen) { deepest = i; maxPen = A.contacts[m.first + i].dist; }
+        float r0 = 0, r1 = 0, r2 = 0, r3 = 0;
+        if (deepest != 0) r0 = area3(localA, m.localA[1], m.localA[2], m.localA[3]);
+        if (deepest != 1) r1 = area3(localA, m.localA[0], m.localA[2], m.localA[3]);
+        if (deepest != 2) r2 = len2(cross(localA - m.localA[0], m.localA[3] - m.localA[1]));
+        if (deepest != 3) r3 = len2(cross(localA - m.localA[0], m.localA[2] - m.localA[1]));
+        float best = fabsf(r0); idx = 0;
+        if (fabsf(r1) > best) { best = fabsf(r1); idx = 1; }
+        if (fabsf(r2) > best) { best = fabsf(r2); idx = 2; }
+        if (fabsf(r3) > best) { best = fabsf(r3); idx = 3; }
+    }
+    A.contacts[m.first + idx] = c;
+    m.localA[idx] = localA;
+    return m.first + idx;
+}
+
+GGL_HD ManifoldCtx manifold_begin(const ArenaDev& A) { ManifoldCtx m; m.first = A.numContacts; m.count = 0; return m; }
+
+// ---------------------------------------------------------------------------------------------- narrow phase
+// ball vs the 4 planes and the mesh; every contact is flagged special (Arena.cpp:265-273)
+GGL_HD void collide_ball_plane(ArenaDev& A, V3 n, V3 origin) {
+    const BallDev& b = A.ball;
+    V3 vtx = (-n) * kBallRadiusBT;            // support point of the sphere towards the plane
+    V3 inPlane = (b.pos - origin) + vtx;
+    float dist = dot(n, inPlane);
+    if (dist < kBallCBT) {
+        V3 proj = inPlane - dist * n;
+        V3 pOnB = origin + proj;
+        ManifoldCtx m = manifold_begin(A);
+        Contact c;
+        c.normal = n; c.dist = dist;
+        V3 pA = pOnB + n * dist;
+        c.relA = pA - b.pos; c.relB = pOnB - origin;
+        c.friction = rl::BALL_FRICTION < rl::WORLD_FRICTION ? rl::BALL_FRICTION : rl::WORLD_FRICTION;
+        c.restitution = rl::BALL_RESTITUTION > rl::WORLD_RESTITUTION ? rl::BALL_RESTITUTION : rl::WORLD_RESTITUTION;
+        c.bodyA = 0; c.bodyB = -1; c.special = 1; c._pad = 0;
+        manifold_add(A, m, c, pA - b.pos);
+    }
+}
+
+GGL_HD V3 closest_point_triangle(V3 p, V3 a, V3 b, V3 c) {
+    V3 ab = b - a, ac = c - a, ap = p - a;
+    float d1 = dot(ab, ap), d2 = dot(ac, ap);
+    if (d1 <= 0.f && d2 <= 0.f) return a;
+    V3 bp = p - b;
+    float d3 = dot(ab, bp), d4 = dot(ac, bp);
+    if (d3 >= 0.f && d4 <= d3) return b;
+    V3 cp = p - c;
+    float d5 = dot(ab, cp), d6 = dot(ac, cp);
+    if (d6 >= 0.f && d5 <= d6) return c;
+    float vc = d1 * d4 - d3 * d2;
+    if (vc <= 0.f && d1 >= 0.f && d3 <= 0.f) { float v = d1 / (d1 - d3); return a + v * ab; }
+    float vb = d5 * d2 - d1 * d6;
+    if (vb <= 0.f && d2 >= 0.f && d6 <= 0.f) { float v = d2 / (d2 - d6); return a + v * ac; }
+    float va = d3 * d6 - d5 * d4;
+    if (va <= 0.f && (d4 - d3) >= 0.f && (d5 - d6) >= 0.f) { float v = (d4 - d3) / ((d4 - d3) + (d5 - d6)); return b + v * (c - b); }
+    float denom = 1.f / (va + vb + vc);
+    float v = vb * denom, w = vc * denom;
+    return a + v * ab + w * ac;
+}
+
+GGL_HD bool sphere_triangle(V3 centre, const Tri& t, float radius, float cbt, V3& point, V3& normalOut, float& depth) {
+    float rt = radius + cbt;
+    V3 normal = cross(t.v1 - t.v0, t.v2 - t.v0);
+    float l2 = len2(normal);
+    bool has = false;
+    V3 cp = v3(0, 0, 0);
+    if (l2 >= kEps * kEps) {
+        normal = normal / sqrtf(l2);
+        float dplane = dot(centre - t.v0, normal);
+        if (dplane < 0.f) { dplane *= -1.f; normal = normal * -1.f; }
+        if (dplane < rt) {
+            // barycentric point-in-triangle test
+            V3 u = t.v1 - t.v0, v = t.v2 - t.v0, n = cross(u, v), w = centre - t.v0;
+            float nl = dot(n, n);
+            float gamma = dot(cross(u, w), n) / nl, beta = dot(cross(w, v), n) / nl, alpha = 1 - gamma - beta;
+            if (0 <= alpha && alpha <= 1 && 0 <= beta && beta <= 1 && 0 <= gamma && gamma <= 1) {
+                has = true;
+                cp = centre - normal * dplane;
+            } else {
+                V3 near = closest_point_triangle(centre, t.v0, t.v1, t.v2);
+                if (len2(near - centre) < rt * rt) { has = true; cp = near; }
+            }
+        }
+    }
+    if (has) {
+        V3 toC = centre - cp;
+        float d2 = len2(toC);
+        if (d2 < rt * rt) {
+            if (d2 > kEps) {
+                float d = sqrtf(d2);
+                normalOut = normalized(toC);
+                point = cp;
+                depth = -(radius - d);
+            } else {
+                normalOut = normal; point = cp; depth = -radius;
+            }
+            return true;
+        }
+    }
+    return false;
+}
+
+GGL_HD void collide_ball_mesh(ArenaDev& A, const WorldDev& W) {
+    if (W.numTris <= 0) return;
+    const BallDev& b = A.ball;
+    float ext = kBallRadiusBT + 0.08f;
+    V3 mn = b.pos - v3(ext, ext, ext), mx = b.pos + v3(ext, ext, ext);
+    int x0 = grid_coord(mn.x, W.gridMin.x, W.invCellSize, W.gx), x1 = grid_coord(mx.x, W.gridMin.x, W.invCellSize, W.gx);
+    int y0 = grid_coord(mn.y, W.gridMin.y, W.invCellSize, W.gy), y1 = grid_coord(mx.y, W.gridMin.y, W.invCellSize, W.gy);
+    int z0 = grid_coord(mn.z, W.gridMin.z, W.invCellSize, W.gz), z1 = grid_coord(mx.z, W.gridMin.z, W.invCellSize, W.gz);
+    ManifoldCtx m = manifold_begin(A);
+    int seen[16]; int nseen = 0;
+    for (int z = z0; z <= z1; z++)
+        for (int y = y0; y <= y1; y++)
+            for (int x = x0; x <= x1; x++) {
+                int cell = (z * W.gy + y) * W.gx + x;
+                for (int k = W.cellStart[cell]; k < W.cellStart[cell + 1]; k++) {
+                    int ti = W.cellTris[k];
+                    bool dup = false;
+                    for (int s = 0; s < nseen; s++) dup |= (seen[s] == ti);
+                    if (dup) continue;
+                    V3 p, n; float depth;
+                    if (sphere_triangle(b.pos, W.tris[ti], kBallRadiusBT, kBallCBT, p, n, depth)) {
+                        if (nseen < 16) seen[nseen++] = ti;
+                        if (depth > kBallCBT) continue;
+                        Contact c;
+                        c.normal = n; c.dist = depth;
+                        V3 pA = p + n * depth;
+                        c.relA = pA - b.pos; c.relB = p;
+                        c.friction = rl::BALL_FRICTION < rl::WORLD_FRICTION ? rl::BALL_FRICTION : rl::WORLD_FRICTION;
+                        c.restitution = rl::BALL_RESTITUTION > rl::WORLD_RESTITUTION ? rl::BALL_RESTITUTION : rl::WORLD_RESTITUTION;
+                        c.bodyA = 0; c.bodyB = -1; c.special = 1; c._pad = 0;
+                        manifold_add(A, m, c, pA - b.pos);
+                    }
+                }
+            }
+}
+
+// car hitbox vs plane: the single deepest support vertex (perturbation iterations are off in the reference)
+GGL_HD void collide_car_plane(ArenaDev& A, int ci, V3 n, V3 origin) {
+    CarDev& car = A.cars[ci];
+    const BoxGeom bg = car_box();
+    V3 boxPos = car.pos + mul(car.basis, car_hitbox_offset());
+    V3 dirLocal = tmul(car.basis, -n);
+    V3 vtx = v3(dirLocal.x >= 0.f ? bg.full.x : -bg.full.x, dirLocal.y >= 0.f ? bg.full.y : -bg.full.y, dirLocal.z >= 0.f ? bg.full.z : -bg.full.z);
+    V3 inPlane = (boxPos - origin) + mul(car.basis, vtx);
+    float dist = dot(n, inPlane);
+    if (dist < car_cbt()) {
+        V3 pOnB = origin + (inPlane - dist * n);
+        V3 pA = pOnB + n * dist;
+        ManifoldCtx m = manifold_begin(A);
+        Contact c;
+        c.normal = n; c.dist = dist;
+        c.relA = pA - car.pos; c.relB = pOnB - origin;
+        c.friction = rl::CARWORLD_FRICTION; c.restitution = rl::CARWORLD_RESTITUTION;
+        c.bodyA = (int16_t)(1 + ci); c.bodyB = -1; c.special = 0; c._pad = 0;
+        if (manifold_add(A, m, c, tmul(car.basis, pA - car.pos)) >= 0) {
+            car.worldContactHas = 1;
+            car.worldContactNormal = n;
+        }
+    }
+}
+
+// car hitbox (core box + margin) vs ball (point + radius): closest points, GJK margin convention
+GGL_HD void collide_car_ball(ArenaDev& A, int ci) {
+    CarDev& car = A.cars[ci];
+    BallDev& ball = A.ball;
+    const BoxGeom bg = car_box();
+    V3 boxPos = car.pos + mul(car.basis, car_hitbox_offset());
+    V3 cl = tmul(car.basis, ball.pos - boxPos);
+    V3 q = v3(fclamp(cl.x, -bg.core.x, bg.core.x), fclamp(cl.y, -bg.core.y, bg.core.y), fclamp(cl.z, -bg.core.z, bg.core.z));
+    V3 vl = q - cl;                         // from the sphere centre to the box core (B -> A)
+    float d2 = len2(vl);
+    float margins = bg.margin + kBallRadiusBT;
+    float maxd = margins + kBallCBT;
+    V3 nl; float dist;
+    if (d2 > kEps * kEps) {
+        if (d2 > maxd * maxd) return;
+        float d = sqrtf(d2);
+        nl = vl * (1.f / d);
+        dist = d - margins;
+    } else {
+        // centre inside the core box: axis of least penetration
+        float px = bg.core.x - fabsf(cl.x), py = bg.core.y - fabsf(cl.y), pz = bg.core.z - fabsf(cl.z);
+        if (px <= py && px <= pz) { nl = v3(cl.x >= 0.f ? -1.f : 1.f, 0, 0); dist = -px - margins; }
+        else if (py <= pz) { nl = v3(0, cl.y >= 0.f ? -1.f : 1.f, 0); dist = -py - margins; }
+        else { nl = v3(0, 0, cl.z >= 0.f ? -1.f : 1.f); dist = -pz - margins; }
+    }
+    if (dist > kBallCBT) return;
+    V3 n = mul(car.basis, nl);
+    V3 pOnB = ball.pos + n * kBallRadiusBT;
+    V3 pA = pOnB + n * dist;
+    ManifoldCtx m = manifold_begin(A);
+    Contact c;
+    c.normal = n; c.dist = dist;
+    c.relA = pA - car.pos; c.relB = pOnB - ball.pos;
+    c.friction = rl::CARBALL_FRICTION; c.restitution = rl::CARBALL_RESTITUTION;
+    c.bodyA = (int16_t)(1 + ci); c.bodyB = 0; c.special = 0; c._pad = 0;
+    if (manifold_add(A, m, c, tmul(car.basis, pA - car.pos)) < 0) return;
+
+    // Arena::_BtCallback_OnCarBallCollision (Arena.cpp:283-334)
+    V3 carPosUU = car.pos * kBT2UU, carVelUU = car.vel * kBT2UU;
+    V3 ballPosUU = ball.pos * kBT2UU, ballVelUU = ball.vel * kBT2UU;
+    car.hitValid = 1;
+    car.hitRelPos = c.relB * kBT2UU;
+    car.hitTick = A.tickCount;
+    car.hitBallPos = ballPosUU;
+    car.hitExtraVel = v3(0, 0, 0);
+    if ((A.tickCount > car.hitTickExtra + 1) || (car.hitTickExtra > A.tickCount)) {
+        car.hitTickExtra = A.tickCount;
+    } else {
+        return;
+    }
+    V3 fwd = car_fwd(car);
+    V3 relPos = ballPosUU - carPosUU, relVel = ballVelUU - carVelUU;
+    float relSpeed = fminf(len(relVel), rl::BALL_CAR_EXTRA_IMPULSE_MAXDELTAVEL);
+    if (relSpeed > 0.f) {
+        V3 hitDir = safe_normalized(relPos * v3(1, 1, rl::BALL_CAR_EXTRA_IMPULSE_Z_SCALE));
+        V3 adj = fwd * dot(hitDir, fwd) * (1 - rl::BALL_CAR_EXTRA_IMPULSE_FORWARD_SCALE);
+        hitDir = safe_normalized(hitDir - adj);
+        V3 added = (hitDir * relSpeed) * curve_ball_extra_impulse(relSpeed) * 1.f;
+        car.hitExtraVel = added;
+        ball.velImpulseCache += added * kUU2BT;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------- solver
+struct SolverBody {
+    V3 dv, dw, push, turn, extF, extT, vel, angVel;
+    float invMass;
+    M3 invI;
+    V3 pos;
+    int active;
+};
+
+struct Row {
+    V3 n1, rxn1, angA, n2, rxn2, angB;
+    float jacInv, rhs, rhsPen, applied, appliedPush, friction, lower, upper;
+    int a, b;          // solver body indices (b = -1: fixed)
+    int special, frictionOf;
+};
+
+GGL_HD void sb_apply(SolverBody& s, V3 lin, V3 ang, float mag) { s.dv += lin * mag; s.dw += ang * mag; }
+GGL_HD void sb_push(SolverBody& s, V3 lin, V3 ang, float mag) { s.push += lin * mag; s.turn += ang * mag; }
+
+GGL_HD void setup_contact_row(Row& r, const SolverBody* sb, int a, int b, V3 n, V3 rel1, V3 rel2, float dist, float friction,
+                              float restitutionCoef, int special) {
+    const float invDt = 1.f / kTick;
+    const SolverBody& A = sb[a];
+    V3 t0 = cross(rel1, n);
+    r.angA = mul(A.invI, t0);
+    V3 t1 = cross(rel2, n);
+    r.angB = (b >= 0) ? mul(sb[b].invI, -t1) : v3(0, 0, 0);
+    float denom0 = A.invMass + dot(n, cross(r.angA, rel1));
+    float denom1 = 0.f;
+    if (b >= 0) denom1 = sb[b].invMass + dot(n, cross(-r.angB, rel2));
+    r.jacInv = 1.f / (denom0 + denom1 + 0.f);
+    r.n1 = n; r.rxn1 = t0;
+    if (b >= 0) { r.n2 = -n; r.rxn2 = -t1; } else { r.n2 = v3(0, 0, 0); r.rxn2 = v3(0, 0, 0); }
+    float penetration = dist + 0.f;
+    V3 vel1 = vel_at(A.vel, A.angVel, rel1);
+    V3 vel2 = (b >= 0) ? vel_at(sb[b].vel, sb[b].angVel, rel2) : v3(0, 0, 0);
+    float relVel0 = dot(n, vel1 - vel2);
+    float restitution = (fabsf(relVel0) < 0.2f) ? 0.f : restitutionCoef * -relVel0;
+    if (restitution <= 0.f) restitution = 0.f;
+    r.friction = friction;
+    r.applied = 0.f; r.appliedPush = 0.f;
+    V3 zero = v3(0, 0, 0);
+    float v1n = dot(r.n1, A.vel + A.extF) + dot(r.rxn1, A.angVel + A.extT);
+    float v2n = (b >= 0) ? dot(r.n2, sb[b].vel + sb[b].extF) + dot(r.rxn2, sb[b].angVel + sb[b].extT) : dot(r.n2, zero);
+    float relVel = v1n + v2n;
+    float posErr = 0.f;
+    float velErr = restitution - relVel;
+    if (penetration > 0.f) posErr = 0.f;
+    else posErr = -penetration * 0.8f * invDt;
+    r.rhs = velErr * r.jacInv;
+    r.rhsPen = posErr * r.jacInv;
+    r.lower = 0.f; r.upper = 1e10f;
+    r.a = a; r.b = b; r.special = special; r.frictionOf = -1;
+}
+
+GGL_HD void setup_friction_row(Row& r, const SolverBody* sb, int a, int b, V3 axis, V3 rel1, V3 rel2, float friction, int of) {
+    const SolverBody& A = sb[a];
+    r.n1 = axis;
+    r.rxn1 = cross(rel1, axis);
+    r.angA = mul(A.invI, r.rxn1);
+    if (b >= 0) {
+        r.n2 = -axis;
+        r.rxn2 = cross(rel2, r.n2);
+        r.angB = mul(sb[b].invI, r.rxn2);
+    } else {
+        r.n2 = r.rxn2 = r.angB = v3(0, 0, 0);
+    }
+    float denom0 = A.invMass + dot(axis, cross(r.angA, rel1));
+    float denom1 = (b >= 0) ? sb[b].invMass + dot(axis, cross(-r.angB, rel2)) : 0.f;
+    r.jacInv = 1.f / (denom0 + denom1);
+    float v1n = dot(r.n1, A.vel + A.extF) + dot(r.rxn1, A.angVel);
+    float v2n = (b >= 0) ? dot(r.n2, sb[b].vel + sb[b].extF) + dot(r.rxn2, sb[b].angVel) : 0.f;
+    float relVel = v1n + v2n;
+    r.rhs = (0.f - relVel) * r.jacInv;
+    r.rhsPen = 0.f;
+    r.applied = 0.f; r.appliedPush = 0.f;
+    r.friction = friction;
+    r.lower = -friction; r.upper = friction;
+    r.a = a; r.b = b; r.special = 0; r.frictionOf = of;
+}
+
+GGL_HD void friction_dir(const SolverBody* sb, int a, int b, V3 n, V3 rel1, V3 rel2, V3& dir) {
+    // btSolverBody::getVelocityInLocalPointNoDelta: velocities including the external force/torque impulses
+    V3 vel1 = vel_at(sb[a].vel + sb[a].extF, sb[a].angVel + sb[a].extT, rel1);
+    V3 vel2 = (b >= 0) ? vel_at(sb[b].vel + sb[b].extF, sb[b].angVel + sb[b].extT, rel2) : v3(0, 0, 0);
+    V3 vel = vel1 - vel2;
+    float rv = dot(n, vel);
+    dir = vel - n * rv;
+    float l2 = len2(dir);
+    if (l2 > kEps) {
+        dir *= 1.f / sqrtf(l2);
+    } else {
+        V3 q;
+        plane_space(n, dir, q);
+    }
+}
+
+GGL_HD void resolve_row(Row& c, SolverBody* sb, bool lowerOnly) {
+    float delta = c.rhs - c.applied * 0.f;
+    SolverBody& A = sb[c.a];
+    float d1 = dot(c.n1, A.dv) + dot(c.rxn1, A.dw);
+    float d2 = (c.b >= 0) ? dot(c.n2, sb[c.b].dv) + dot(c.rxn2, sb[c.b].dw) : 0.f;
+    delta -= d1 * c.jacInv;
+    delta -= d2 * c.jacInv;
+    float sum = c.applied + delta;
+    if (sum < c.lower) { delta = c.lower - c.applied; c.applied = c.lower; }
+    else if (!lowerOnly && sum > c.upper) { delta = c.upper - c.applied; c.applied = c.upper; }
+    else c.applied = sum;
+    sb_apply(A, c.n1 * A.invMass, c.angA, delta);
+    if (c.b >= 0) sb_apply(sb[c.b], c.n2 * sb[c.b].invMass, c.angB, delta);
+}
+
+GGL_HD void resolve_push(Row& c, SolverBody* sb) {
+    if (c.rhsPen == 0.f) return;
+    float delta = c.rhsPen - c.appliedPush * 0.f;
+    SolverBody& A = sb[c.a];
+    float d1 = dot(c.n1, A.push) + dot(c.rxn1, A.turn);
+    float d2 = (c.b >= 0) ? dot(c.n2, sb[c.b].push) + dot(c.rxn2, sb[c.b].turn) : 0.f;
+    delta -= d1 * c.jacInv;
+    delta -= d2 * c.jacInv;
+    float sum = c.appliedPush + delta;
+    if (sum < c.lower) { delta = c.lower - c.appliedPush; c.appliedPush = c.lower; }
+    else c.appliedPush = sum;
+    sb_push(A, c.n1 * A.invMass, c.angA, delta);
+    if (c.b >= 0) sb_push(sb[c.b], c.n2 * sb[c.b].invMass, c.angB, delta);
+}
+
+constexpr int kMaxRows = kMaxContacts + 1;
+
+// Solves all contact rows of the arena and writes velocities (and push-corrected positions) back.
+GGL_HDN void solve_contacts(ArenaDev& A) {
+    SolverBody sb[1 + kMaxCars];
+    const int nb = 1 + A.numCars;
+    // ball
+    {
+        SolverBody& s = sb[0];
+        s.dv = s.dw = s.push = s.turn = v3(0, 0, 0);
+        s.active = (int)A.ball.active;
+        s.invMass = kBallInvMass;
+        float ii = ball_inv_inertia();
+        s.invI.r0 = v3(ii, 0, 0); s.invI.r1 = v3(0, ii, 0); s.invI.r2 = v3(0, 0, ii);
+        s.vel = A.ball.vel; s.angVel = A.ball.angVel; s.pos = A.ball.pos;
+        s.extF = A.ball.force * kBallInvMass * kTick;
+        s.extT = tmul(s.invI, A.ball.torque) * kTick;
+    }
+    for (int i = 0; i < A.numCars; i++) {
+        SolverBody& s = sb[1 + i];
+        const CarDev& c = A.cars[i];
+        s.dv = s.dw = s.push = s.turn = v3(0, 0, 0);
+        s.active = !c.isDemoed;
+        s.invMass = 1.f / rl::CAR_MASS;
+        s.invI = c.invInertiaW;
+        s.vel = c.vel; s.angVel = c.angVel; s.pos = c.pos;
+        s.extF = c.force * s.invMass * kTick;
+        s.extT = tmul(c.invInertiaW, c.torque) * kTick;
+    }
+    Row rows[kMaxRows];
+    Row fr[kMaxRows];
+    int nr = 0;
+    // special (ball-world) accumulation
+    int nSpecial = 0; V3 spNormal = v3(0, 0, 0); float spDist = 0.f, spFriction = 0.f, spRest = 0.f;
+    for (int k = 0; k < A.numContacts; k++) {
+        const Contact& c = A.contacts[k];
+        int a = c.bodyA, b = c.bodyB;
+        setup_contact_row(rows[nr], sb, a, b, c.normal, c.relA, c.relB, c.dist, c.friction, c.restitution, c.special);
+        if (c.special) {
+            nSpecial++; spFriction = c.friction; spRest = c.restitution; spNormal += c.normal; spDist += len(c.relA);
+        }
+        V3 dir;
+        friction_dir(sb, a, b, c.normal, c.relA, c.relB, dir);
+        setup_friction_row(fr[nr], sb, a, b, dir, c.relA, c.relB, c.friction, nr);
+        nr++;
+    }
+    if (nSpecial > 0) {
+        // averaged ball-world contact against a fixed body (convertContactSpecial)
+        float distance = spDist / nSpecial;
+        V3 normal = spNormal / (float)nSpecial;
+        V3 rel1 = normal * -distance, rel2 = v3(0, 0, 0);
+        setup_contact_row(rows[nr], sb, 0, -1, normal, rel1, rel2, distance, spFriction, spRest, 0);
+        V3 dir;
+        friction_dir(sb, 0, -1, normal, rel1, rel2, dir);
+        setup_friction_row(fr[nr], sb, 0, -1, dir, rel1, rel2, spFriction, nr);
+        nr++;
+    }
+    if (nr > 0) {
+        for (int it = 0; it < 10; it++) {
+            bool any = false;
+            for (int k = 0; k < nr; k++) { any |= rows[k].rhsPen != 0.f; resolve_push(rows[k], sb); }
+            if (!any) break;
+        }
+        for (int it = 0; it < 10; it++) {
+            for (int k = 0; k < nr; k++)
+                if (!rows[k].special) resolve_row(rows[k], sb, true);
+            for (int k = 0; k < nr; k++) {
+                float tot = rows[fr[k].frictionOf].applied;
+                if (tot > 0.f) {
+                    fr[k].lower = -(fr[k].friction * tot);
+                    fr[k].upper = fr[k].friction * tot;
+                    resolve_row(fr[k], sb, false);
+                }
+            }
+        }
+    }
+    // write back
+    for (int i = 0; i < nb; i++) {
+        SolverBody& s = sb[i];
+        if (!s.active) continue;
+        V3 v = (s.vel + s.dv) + s.extF;
+        V3 w = (s.angVel + s.dw) + s.extT;
+        bool pushed = !(is_zero(s.push) && is_zero(s.turn));
+        if (i == 0) {
+            A.ball.vel = v; A.ball.angVel = w;
+            if (pushed) A.ball.pos = s.pos + s.push * kTick;
+        } else {
+            CarDev& c = A.cars[i - 1];
+            c.vel = v; c.angVel = w;
+            if (pushed) {
+                V3 np; M3 nbasis;
+                integrate_transform(c.pos, c.basis, s.push, s.turn * 0.1f, kTick, np, nbasis);
+                c.pos = np; c.basis = nbasis;
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------- world step
+// defined in sim_boxbox.cuh / sim_boxtri.cuh
+GGL_HD void collide_car_car(ArenaDev& A, int i, int j);
+GGL_HD void collide_car_mesh(ArenaDev& A, const WorldDev& W, int ci);
+
+GGL_HDN void collide_all(ArenaDev& A, const WorldDev& W) {
+    const float ex = rl::ARENA_EXTENT_X * kUU2BT, hz = rl::ARENA_HEIGHT * kUU2BT;
+    A.numContacts = 0;
+    if (A.ball.active) {
+        collide_ball_mesh(A, W);
+        collide_ball_plane(A, v3(0, 0, 1), v3(0, 0, 0));
+        collide_ball_plane(A, v3(0, 0, -1), v3(0, 0, hz));
+        collide_ball_plane(A, v3(1, 0, 0), v3(-ex, 0, hz / 2));
+        collide_ball_plane(A, v3(-1, 0, 0), v3(ex, 0, hz / 2));
+    }
+    for (int i = 0; i < A.numCars; i++)
+        if (!A.cars[i].isDemoed) collide_car_ball(A, i);
+    for (int i = 0; i < A.numCars; i++) {
+        if (A.cars[i].isDemoed) continue;
+        collide_car_mesh(A, W, i);
+        collide_car_plane(A, i, v3(0, 0, 1), v3(0, 0, 0));
+        collide_car_plane(A, i, v3(0, 0, -1), v3(0, 0, hz));
+        collide_car_plane(A, i, v3(1, 0, 0), v3(-ex, 0, hz / 2));
+        collide_car_plane(A, i, v3(-1, 0, 0), v3(ex, 0, hz / 2));
+        for (int j = i + 1; j < A.numCars; j++) collide_car_car(A, i, j);
+    }
+}
+
+}  // namespace ggl

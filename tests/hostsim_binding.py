@@ -1,0 +1,81 @@
+"""TEST INFRASTRUCTURE: ctypes binding to tests/hostsim/_build/libhostsim.so — the g++ compile of the device simulator
+headers, used to lock-step the tick logic against the compiled reference in a container without a GPU."""
+import ctypes as C
+import importlib
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+abi = importlib.import_module("reinforcement-learning_b200.abi")
+arena_mesh = importlib.import_module("reinforcement-learning_b200.arena_mesh")
+_DIR = os.path.join(ROOT, "tests", "hostsim")
+_SO = os.path.join(_DIR, "_build", "libhostsim.so")
+_lib = None
+
+
+def build():
+    os.makedirs(os.path.join(_DIR, "_build"), exist_ok=True)
+    csrc = os.path.join(ROOT, "reinforcement-learning_b200", "csrc")
+    deps = [os.path.join(csrc, f) for f in os.listdir(csrc) if f.endswith(".cuh")] + [os.path.join(_DIR, "hostsim.cpp")]
+    if os.path.exists(_SO) and all(os.path.getmtime(d) <= os.path.getmtime(_SO) for d in deps):
+        return
+    subprocess.check_call(["g++", "-O2", "-ffp-contract=off", "-std=c++17", "-shared", "-fPIC", "-w",
+                           os.path.join(_DIR, "hostsim.cpp"), "-o", _SO])
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        build()
+        L = C.CDLL(_SO)
+        L.hostsim_create.restype = C.c_void_p
+        L.hostsim_create.argtypes = [C.c_void_p, C.c_int]
+        L.hostsim_destroy.argtypes = [C.c_void_p]
+        L.hostsim_set_state.argtypes = [C.c_void_p, C.POINTER(abi.ArenaState)]
+        L.hostsim_get_state.argtypes = [C.c_void_p, C.POINTER(abi.ArenaState)]
+        L.hostsim_step.argtypes = [C.c_void_p, C.c_int]
+        L.hostsim_set_controls.argtypes = [C.c_void_p, C.POINTER(abi.ArenaState)]
+        L.hostsim_seed.argtypes = [C.c_void_p, C.c_uint32]
+        L.hostsim_contacts.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
+        L.hostsim_sizeof_arena.restype = C.c_size_t
+        _lib = L
+    return _lib
+
+
+class HostSim:
+    def __init__(self, meshes=None):
+        L = lib()
+        meshes = arena_mesh.soccar_meshes() if meshes is None else meshes
+        arr = (abi.MeshBlob * max(1, len(meshes)))()
+        self._keep = []
+        for i, b in enumerate(meshes):
+            buf = C.create_string_buffer(b, len(b))
+            self._keep.append(buf)
+            arr[i].data = C.cast(buf, C.c_void_p)
+            arr[i].size = len(b)
+        self.h = L.hostsim_create(arr, len(meshes))
+        assert self.h
+
+    def set_state(self, st):
+        lib().hostsim_set_state(self.h, C.byref(st))
+
+    def get_state(self):
+        st = abi.ArenaState()
+        lib().hostsim_get_state(self.h, C.byref(st))
+        return st
+
+    def set_controls(self, st):
+        lib().hostsim_set_controls(self.h, C.byref(st))
+
+    def step(self, ticks=1):
+        lib().hostsim_step(self.h, ticks)
+
+    def seed(self, s):
+        lib().hostsim_seed(self.h, s)
+
+    def contacts(self, maxn=64):
+        out = np.zeros((maxn, 20), np.float32)
+        n = lib().hostsim_contacts(self.h, out.ctypes.data, maxn)
+        return out[:n]

@@ -47,6 +47,7 @@ def lib():
         L.ref_envset_set_state.argtypes = [C.c_void_p, C.c_int, C.POINTER(abi.ArenaState)]
         L.ref_envset_set_reset_state.argtypes = [C.c_void_p, C.c_int, C.POINTER(abi.ArenaState)]
         L.ref_arena_step.argtypes = [C.c_void_p, C.c_int, C.c_int]
+        L.ref_envset_set_controls.argtypes = [C.c_void_p, C.c_int, C.POINTER(abi.ArenaState)]
         L.ref_action_table.argtypes = [C.c_void_p, C.POINTER(C.c_int)]
         meshes = arena_mesh.soccar_meshes()
         arr = (abi.MeshBlob * len(meshes))()
@@ -129,6 +130,9 @@ class RefEnvSet:
 
     def set_state(self, arena, st):
         lib().ref_envset_set_state(self.h, arena, C.byref(st))
+
+    def set_controls(self, arena, st):
+        lib().ref_envset_set_controls(self.h, arena, C.byref(st))
 
     def set_reset_state(self, arena, st):
         lib().ref_envset_set_reset_state(self.h, arena, C.byref(st))
