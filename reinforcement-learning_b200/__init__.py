@@ -119,3 +119,93 @@ def action_table():
     n = C.c_int()
     _check(lib().ggl_action_table(t.ctypes.data, C.byref(n)))
     return t[:n.value]
+
+
+# -------------------------------------------------------------------------------------------- EnvSet
+class _DevView:
+    """Zero-copy torch view of a device buffer owned by the envset (via __cuda_array_interface__)."""
+
+    def __init__(self, ptr, shape, typestr):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (int(ptr), False), "version": 2}
+
+
+class EnvSet:
+    """Device-resident RLGC::EnvSet (EnvSet.h:62-110) behind the C ABI. Buffers (`obs`, `action_masks`, `rewards`,
+    `terminals`) are torch CUDA tensors aliasing the library's memory: what libtorch would wrap with from_blob."""
+
+    def __init__(self, num_arenas, players_per_team, device=0, **kw):
+        import torch
+        L = lib()
+        self.desc, self._keep = abi.make_desc(num_arenas, players_per_team, device=device, **kw)
+        h = C.c_void_p()
+        _check(L.ggl_envset_create(C.byref(self.desc), C.byref(h)))
+        self.h = h
+        v = abi.EnvSetViews()
+        _check(L.ggl_envset_views_get(self.h, C.byref(v)))
+        self.num_arenas, self.num_players, self.obs_size = v.num_arenas, v.num_players, v.obs_size
+        self.num_actions, self.players_per_arena = v.num_actions, v.players_per_arena
+        self.num_rewards = self.desc.num_rewards
+        self.device = torch.device("cuda", device)
+        with torch.cuda.device(self.device):
+            t = lambda p, shape, ts: torch.as_tensor(_DevView(p, shape, ts), device=self.device)
+            self.obs = t(v.d_obs, (self.num_players, self.obs_size), "<f4")
+            self.action_masks = t(v.d_action_masks, (self.num_players, self.num_actions), "|u1")
+            self.rewards = t(v.d_rewards, (self.num_players,), "<f4")
+            self.terminals = t(v.d_terminals, (self.num_arenas,), "|u1")
+            self.slot_car_id = t(v.d_slot_car_id, (self.num_players,), "<i4")
+            self.slot_team = t(v.d_slot_team, (self.num_players,), "|u1")
+            self.events = t(v.d_events, (self.num_players, 9), "|u1")
+            self.last_rewards = t(v.d_last_rewards, (self.num_arenas, max(1, self.num_rewards)), "<f4")
+
+    def _stream(self, stream):
+        import torch
+        return torch.cuda.current_stream(self.device).cuda_stream if stream is None else stream
+
+    def close(self):
+        if self.h:
+            lib().ggl_envset_destroy(self.h)
+            self.h = None
+
+    def reset(self, stream=None):
+        _check(lib().ggl_envset_reset(self.h, self._stream(stream)))
+
+    def step_first_half(self, stream=None):
+        _check(lib().ggl_envset_step_first_half(self.h, self._stream(stream)))
+
+    def step_second_half(self, actions, stream=None):
+        _check(lib().ggl_envset_step_second_half(self.h, actions.data_ptr(), self._stream(stream)))
+
+    def step(self, actions, stream=None, reset=True):
+        """Learner loop order (Learner.cpp:669-793): Reset(), then both halves fused in one launch."""
+        s = self._stream(stream)
+        if reset:
+            _check(lib().ggl_envset_reset(self.h, s))
+        _check(lib().ggl_envset_step(self.h, actions.data_ptr(), s))
+
+    def arena_step(self, ticks, stream=None):
+        _check(lib().ggl_arena_step(self.h, ticks, self._stream(stream)))
+
+    def random_actions(self, actions, seed, stream=None):
+        _check(lib().ggl_envset_random_actions(self.h, actions.data_ptr(), seed, self._stream(stream)))
+
+    def sync(self):
+        _check(lib().ggl_envset_sync(self.h))
+
+    def step_host(self, h_actions, h_obs=None, h_masks=None, h_rewards=None, h_terminals=None):
+        p = lambda x: None if x is None else (x.data_ptr() if hasattr(x, "data_ptr") else x.ctypes.data)
+        _check(lib().ggl_envset_step_host(self.h, p(h_actions), p(h_obs), p(h_masks), p(h_rewards), p(h_terminals)))
+
+    def set_state(self, arena, st):
+        _check(lib().ggl_envset_set_state(self.h, arena, C.byref(st)))
+
+    def get_state(self, arena):
+        st = abi.ArenaState()
+        _check(lib().ggl_envset_get_state(self.h, arena, C.byref(st)))
+        return st
+
+    def set_reset_state(self, arena, st):
+        _check(lib().ggl_envset_set_reset_state(self.h, arena, C.byref(st)))
+
+    def set_slot_order(self, car_ids):
+        a = np.ascontiguousarray(car_ids, np.int32)
+        _check(lib().ggl_envset_set_slot_order(self.h, a.ctypes.data))

@@ -1,0 +1,146 @@
+// CUDA kernels of the rollout hot path (sm_100a). One lane group of kGroup threads owns one arena: lanes 0..P-1 run
+// the per-car phases of a tick (suspension rays, control logic) and the per-player outputs (obs row, mask row, reward)
+// in parallel; lane 0 runs the arena-serial phases (contacts, solver, bookkeeping). Groups never straddle a warp, so
+// phase boundaries are __syncwarp()s on the group's lane mask. 128 threads per block = 16 arenas per block; the grid
+// covers the arenas once (4096 arenas -> 256 blocks, ~1.7 blocks per SM on 148 SMs).
+#pragma once
+#include <cuda_runtime.h>
+#include "env_reset.cuh"
+
+namespace ggl {
+
+constexpr int kGroup = 8;
+constexpr int kBlock = 128;
+constexpr int kArenasPerBlock = kBlock / kGroup;
+
+struct ExecGroup {
+    int lane_, mask_;
+    __device__ __forceinline__ int lane() const { return lane_; }
+    __device__ __forceinline__ int lanes() const { return kGroup; }
+    __device__ __forceinline__ void sync() const { __syncwarp(mask_); }
+};
+
+struct EnvDevPtrs {
+    ArenaDev* arenas;
+    const ArenaDev* resetArenas;     // injected reset states (may be null)
+    float* obs; uint8_t* masks; float* rewards; uint8_t* terminals;
+    int32_t* slotCarId; uint8_t* slotTeam; uint8_t* events; float* lastRewards;
+    const float* actionTable;        // [90*8]
+    WorldDev world;
+};
+
+__device__ __forceinline__ ExecGroup make_exec() {
+    ExecGroup ex;
+    ex.lane_ = threadIdx.x % kGroup;
+    int base = (threadIdx.x % 32) / kGroup * kGroup;
+    ex.mask_ = (int)(((1u << kGroup) - 1u) << base);
+    return ex;
+}
+
+// obs row + mask row (+ slot identity) of one player
+__device__ __forceinline__ void write_player_rows(const ArenaDev& A, const EnvCfg& cfg, const EnvDevPtrs& P, int arena, int slot) {
+    const int row = arena * cfg.numCars + slot;
+    build_obs_row(A, cfg, slot, P.obs + (size_t)row * cfg.obsSize);
+    action_mask_row(A.cars[A.slotCar[slot]], P.actionTable, P.masks + (size_t)row * kNumActions);
+    P.slotCarId[row] = (int)A.cars[A.slotCar[slot]].id;
+    P.slotTeam[row] = A.cars[A.slotCar[slot]].team;
+}
+
+// EnvSet::ResetArena for arenas whose terminal flag is set (or all of them when `force`)
+__global__ void __launch_bounds__(kBlock) env_reset_kernel(EnvCfg cfg, EnvDevPtrs P, int force) {
+    const int arena = blockIdx.x * kArenasPerBlock + threadIdx.x / kGroup;
+    if (arena >= cfg.numArenas) return;
+    const ExecGroup ex = make_exec();
+    ArenaDev& A = P.arenas[arena];
+    const bool doReset = force || A.terminal != 0;
+    if (!doReset) return;
+    if (ex.lane() == 0) {
+        if (cfg.stateSetter == GGL_SETTER_INJECTED && P.resetArenas && P.resetArenas[arena].hasResetState) {
+            const ArenaDev& R = P.resetArenas[arena];
+            A.tickCount = R.tickCount; A.ball = R.ball;
+            for (int c = 0; c < A.numCars; c++) {
+                Controls keep = A.cars[c].controls;
+                A.cars[c] = R.cars[c];
+                (void)keep;
+            }
+            for (int p = 0; p < kNumPads; p++) A.pads[p] = R.pads[p];
+        } else {
+            arena_reset_kickoff(A);
+        }
+        env_after_state_set(A);
+        P.terminals[arena] = 0;
+    }
+    ex.sync();
+    if (ex.lane() < A.numCars) {
+        write_player_rows(A, cfg, P, arena, ex.lane());
+        for (int e = 0; e < 9; e++) P.events[(size_t)(arena * cfg.numCars + ex.lane()) * 9 + e] = 0;
+    }
+}
+
+// StepFirstHalf and/or StepSecondHalf of every arena in one launch.
+__global__ void __launch_bounds__(kBlock) env_step_kernel(EnvCfg cfg, EnvDevPtrs P, const int32_t* __restrict__ actions, int doFirst, int doSecond) {
+    const int arena = blockIdx.x * kArenasPerBlock + threadIdx.x / kGroup;
+    if (arena >= cfg.numArenas) return;
+    const ExecGroup ex = make_exec();
+    ArenaDev& A = P.arenas[arena];
+    const WorldDev& W = P.world;
+    if (doFirst) {
+        if (ex.lane() == 0) env_begin_step(A);
+        ex.sync();
+        for (int t = 0; t < cfg.actionDelay; t++) arena_tick(A, W, ex);
+    }
+    if (doSecond) {
+        if (ex.lane() == 0) env_apply_actions(A, actions + arena * cfg.numCars, P.actionTable);
+        ex.sync();
+        for (int t = cfg.actionDelay; t < cfg.tickSkip; t++) arena_tick(A, W, ex);
+        if (ex.lane() == 0) {
+            env_after_ticks(A, cfg);
+            P.terminals[arena] = A.terminal;
+        }
+        ex.sync();
+        const int slot = ex.lane();
+        if (slot < A.numCars) {
+            const int row = arena * cfg.numCars + slot;
+            // saved raw rewards: the player with the lowest car id (EnvSet.cpp:235-243, shuffleRewardSampling = false)
+            int lowSlot = 0;
+            for (int s = 1; s < A.numCars; s++)
+                if (A.cars[A.slotCar[s]].id < A.cars[A.slotCar[lowSlot]].id) lowSlot = s;
+            float raw[kMaxRewards];
+            P.rewards[row] = env_player_reward(A, cfg, slot, raw);
+            if (slot == lowSlot)
+                for (int r = 0; r < cfg.numRewards; r++) P.lastRewards[(size_t)arena * cfg.numRewards + r] = raw[r];
+            write_player_rows(A, cfg, P, arena, slot);
+            for (int e = 0; e < 9; e++) P.events[(size_t)row * 9 + e] = A.players[slot].events[e];
+        }
+        ex.sync();
+        if (ex.lane() == 0) env_end_step(A);
+    }
+}
+
+// raw Arena::Step(ticks)
+__global__ void __launch_bounds__(kBlock) arena_step_kernel(EnvCfg cfg, EnvDevPtrs P, int ticks) {
+    const int arena = blockIdx.x * kArenasPerBlock + threadIdx.x / kGroup;
+    if (arena >= cfg.numArenas) return;
+    const ExecGroup ex = make_exec();
+    for (int t = 0; t < ticks; t++) arena_tick(P.arenas[arena], P.world, ex);
+}
+
+// uniformly random mask-valid action per player (bench / smoke helper): k-th set bit of the mask row, k from a hash
+__global__ void random_actions_kernel(const uint8_t* __restrict__ masks, int32_t* __restrict__ actions, int numPlayers, uint64_t seed) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= numPlayers) return;
+    uint64_t z = seed + 0x9E3779B97F4A7C15ull * (uint64_t)(i + 1);
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull; z = (z ^ (z >> 27)) * 0x94D049BB133111EBull; z ^= z >> 31;
+    const uint8_t* m = masks + (size_t)i * kNumActions;
+    int cnt = 0;
+    for (int a = 0; a < kNumActions; a++) cnt += m[a] != 0;
+    int sel = 0;
+    if (cnt > 0) {
+        int k = (int)(z % (uint64_t)cnt);
+        for (int a = 0; a < kNumActions; a++)
+            if (m[a]) { if (k-- == 0) { sel = a; break; } }
+    }
+    actions[i] = sel;
+}
+
+}  // namespace ggl

@@ -1,2 +1,213 @@
+// Env layer on top of the arena tick: action table + masks, GameState bookkeeping, game events, terminal
+// conditions, weighted rewards, observation rows and the kickoff reset — the per-arena body of RLGC::EnvSet.
+//
+// Reference behaviour restated (paths under GigaLearnCPP/RLGymCPP/src/RLGymCPP unless noted):
+//   EnvSet/EnvSet.cpp:113-130      StepFirstHalf          -> env_first_half
+//   EnvSet/EnvSet.cpp:132-273      StepSecondHalf         -> env_second_half
+//   EnvSet/EnvSet.cpp:275-304      ResetArena             -> env_reset_arena
+//   EnvSet/EnvSet.cpp:4-42         event callbacks -> PlayerEventState
+//   ActionParsers/DefaultAction.cpp:3-118   action table, masks
+//   Gamestates/GameState.cpp:53-131, Player.cpp:8-26
+//   ObsBuilders/DefaultObs.cpp:4-54, AdvancedObs.cpp:108-270 (+ AdvancedObs.h:10-13 class coefficients)
+//   Rewards/CommonRewards.h:7-203, TerminalConditions/*.h
+//   RocketSim/src/Sim/GameEventTracker/GameEventTracker.cpp:5-165, Sim/Arena/Arena.cpp:112-216,827-975
 #pragma once
+#include "../../include/gigaenv.h"
 #include "sim_tick.cuh"
+
+namespace ggl {
+
+enum { EV_GOAL = 0, EV_SAVE, EV_ASSIST, EV_SHOT, EV_SHOTPASS, EV_BUMP, EV_BUMPED, EV_DEMO, EV_DEMOED };
+
+struct RewardCfg {
+    int kind;
+    float weight;
+    float params[4];
+};
+struct TerminalCfg {
+    int kind;
+    float params[2];
+};
+struct EnvCfg {
+    int numArenas, playersPerTeam, numCars, tickSkip, actionDelay, obsKind, obsSize;
+    int numRewards, numTerminals, stateSetter;
+    RewardCfg rewards[kMaxRewards];
+    TerminalCfg terminals[kMaxTerminals];
+};
+
+// ---------------------------------------------------------------------------------------------- DefaultAction
+// 24 ground actions then 66 air actions; index -> (throttle, steer, pitch, yaw, roll, jump, boost, handbrake)
+GGL_HD void action_from_index(int idx, float a[8]) {
+    int k = 0;
+    const float RF[3] = {-1.f, 0.f, 1.f};
+    for (int t = 0; t < 3; t++)
+        for (int s = 0; s < 3; s++)
+            for (int b = 0; b < 2; b++)
+                for (int h = 0; h < 2; h++) {
+                    if (b == 1 && RF[t] != 1.f) continue;
+                    if (k == idx) {
+                        a[0] = RF[t]; a[1] = RF[s]; a[2] = 0.f; a[3] = RF[s]; a[4] = 0.f; a[5] = 0.f; a[6] = (float)b; a[7] = (float)h;
+                        return;
+                    }
+                    k++;
+                }
+    for (int p = 0; p < 3; p++)
+        for (int y = 0; y < 3; y++)
+            for (int r = 0; r < 3; r++)
+                for (int j = 0; j < 2; j++)
+                    for (int b = 0; b < 2; b++) {
+                        if (j == 1 && RF[y] != 0.f) continue;
+                        if (RF[p] == RF[r] && RF[r] == (float)j && j == 0) continue;
+                        if (k == idx) {
+                            float hb = (j == 1) && (RF[p] != 0.f || RF[y] != 0.f || RF[r] != 0.f) ? 1.f : 0.f;
+                            a[0] = (float)b; a[1] = RF[y]; a[2] = RF[p]; a[3] = RF[y]; a[4] = RF[r]; a[5] = (float)j; a[6] = (float)b; a[7] = hb;
+                            return;
+                        }
+                        k++;
+                    }
+    for (int i = 0; i < 8; i++) a[i] = 0.f;
+}
+
+constexpr int kNumGroundActions = 24;
+
+GGL_HD bool car_has_flip_or_jump(const CarDev& c) {
+    return c.isOnGround || (!c.hasFlipped && !c.hasDoubleJumped && c.airTimeSinceJump < rl::DOUBLEJUMP_MAX_DELAY);
+}
+
+// DefaultAction::GetActionMask with the masks the constructor derives from the table
+GGL_HD void action_mask_row(const CarDev& c, const float* table /* [90*8] */, uint8_t* out) {
+    const bool onGround = c.isOnGround != 0;
+    const bool noBoost = c.boost == 0.f;
+    const bool turtled = c.worldContactHas && c.worldContactNormal.z > 0.9f;
+    const bool jumpOk = car_has_flip_or_jump(c) || turtled;
+    for (int i = 0; i < kNumActions; i++) {
+        const float* a = table + 8 * i;
+        bool jump = a[5] != 0.f, boost = a[6] != 0.f;
+        bool ground = i < kNumGroundActions;
+        bool air = (i > kNumGroundActions && !jump);
+        if (i < kNumGroundActions && a[0] == a[6] && ((a[3] != 0.f) == (a[7] != 0.f))) air = true;
+        uint8_t m = onGround ? (ground ? 1 : 0) : (air ? 1 : 0);
+        if (noBoost && boost) m = 0;
+        if (jumpOk && jump) m = 1;
+        out[i] = m;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------- game events
+GGL_HD bool ball_scored(const ArenaDev& A) {
+    float y = A.ball.pos.y * kBT2UU;
+    return fabsf(y) > (rl::GOAL_THRESHOLD_Y + rl::BALL_RADIUS);
+}
+
+// Arena::IsBallProbablyGoingIn for soccar (Arena.cpp:827-860)
+GGL_HD bool ball_probably_going_in(const ArenaDev& A, float maxTime, float extraMargin, int* goalTeam) {
+    V3 p = A.ball.pos * kBT2UU, v = A.ball.vel * kBT2UU;
+    if (fabsf(v.y) < kEps) return false;
+    float sgn = fsgn(v.y);
+    float goalY = rl::GOAL_THRESHOLD_Y * sgn;
+    float dist = fabsf(p.y - goalY);
+    float t = dist / fabsf(v.y);
+    if (t > maxTime) return false;
+    V3 g = v3(0, 0, rl::GRAVITY_Z);
+    V3 ex = p + (v * t) + (g * t * t) / 2.f;
+    float margin = rl::BALL_RADIUS * 0.1f + extraMargin;
+    if (ex.z > 642.775f + margin) return false;
+    if (fabsf(ex.x) > 892.755f + margin) return false;
+    if (goalTeam) *goalTeam = (sgn < 0.f) ? 0 : 1;
+    return true;
+}
+
+// GetShooterPasser (GameEventTracker.cpp:5-46): cars visited in players[] slot order; returns car indices or -1
+GGL_HD bool shooter_passer(const ArenaDev& A, int team, int& shooter, bool findPasser, int& passer, uint64_t maxShooterTicks,
+                           uint64_t maxPasserTicks) {
+    shooter = passer = -1;
+    for (int s = 0; s < A.numCars; s++) {
+        int ci = A.slotCar[s];
+        const CarDev& c = A.cars[ci];
+        if (c.team != team || !c.hitValid) continue;
+        if (c.hitTick + maxShooterTicks >= A.tickCount) {
+            if (shooter < 0 || c.hitTick > A.cars[shooter].hitTick) shooter = ci;
+        }
+    }
+    if (shooter >= 0 && findPasser) {
+        uint64_t shootTick = A.cars[shooter].hitTick;
+        for (int s = 0; s < A.numCars; s++) {
+            int ci = A.slotCar[s];
+            const CarDev& c = A.cars[ci];
+            if (c.team != team || !c.hitValid || ci == shooter) continue;
+            if (c.hitTick + maxPasserTicks >= shootTick) {
+                if (passer < 0 || c.hitTick > A.cars[passer].hitTick) passer = ci;
+            }
+        }
+    }
+    return shooter >= 0;
+}
+
+GGL_HD int slot_of_car(const ArenaDev& A, int ci) {
+    for (int s = 0; s < A.numCars; s++)
+        if (A.slotCar[s] == ci) return s;
+    return 0;
+}
+GGL_HD void set_event(ArenaDev& A, int ci, int ev) {
+    if (ci >= 0) A.players[slot_of_car(A, ci)].events[ev] = 1;
+}
+
+// GameEventTracker::Update with the default config (shotMinSpeed 1750, shotTouchMinDelay .3, shotEventCooldown 1,
+// shotMinScoreTime 2, goalMaxTouchTime 4, passMaxTouchTime 2)
+GGL_HD void event_tracker_update(ArenaDev& A) {
+    bool scored = ball_scored(A);
+    const float tickrate = 120.f;
+    uint64_t cnt = A.ball.updateCounter;
+    if (cnt > A.lastBallUpdateCount) {
+        uint64_t deltaTicks = cnt - A.lastBallUpdateCount;
+        float deltaTime = deltaTicks * kTick;
+        if (scored && !A.ballScoredLast) {
+            int sh, pa;
+            int team = (-A.ball.pos.y < 0.f) ? 0 : 1;
+            if (shooter_passer(A, team, sh, true, pa, (uint64_t)(4.0f * tickrate), (uint64_t)(2.0f * tickrate))) {
+                set_event(A, sh, EV_GOAL);
+                set_event(A, pa, EV_ASSIST);
+            }
+        } else {
+            if (!A.ballShot) {
+                if (A.shotCooldown > 0.f) {
+                    A.shotCooldown = fmaxf(A.shotCooldown - deltaTime, 0.f);
+                } else {
+                    float sp2 = len2(A.ball.vel * kBT2UU);
+                    if (sp2 >= 1750.f * 1750.f) {
+                        int goalTeam = 0;
+                        if (ball_probably_going_in(A, 2.0f, 0.f, &goalTeam)) {
+                            int shooterTeam = goalTeam == 0 ? 1 : 0;
+                            uint64_t minDelay = (uint64_t)(0.3f * tickrate);
+                            int sh, pa;
+                            if (shooter_passer(A, shooterTeam, sh, true, pa, deltaTicks + minDelay, (uint64_t)(2.0f * tickrate))) {
+                                uint64_t since = A.tickCount - A.cars[sh].hitTick;
+                                if (since >= minDelay) {
+                                    A.ballShot = 1;
+                                    A.ballShotGoalTeam = (uint8_t)goalTeam;
+                                    A.shotCooldown = 1.0f;
+                                    set_event(A, sh, EV_SHOT);
+                                    set_event(A, pa, EV_SHOTPASS);
+                                }
+                            }
+                        }
+                    }
+                }
+            } else {
+                if (!ball_probably_going_in(A, 2.0f, 0.f, nullptr)) {
+                    int saver, unused;
+                    if (shooter_passer(A, A.ballShotGoalTeam, saver, false, unused, deltaTicks, 0)) set_event(A, saver, EV_SAVE);
+                    A.ballShot = 0;
+                }
+            }
+        }
+    } else if (cnt == A.lastBallUpdateCount) {
+        return;
+    } else {
+        A.ballScoredLast = 0; A.ballShot = 0; A.shotCooldown = 0.f;
+    }
+    A.ballScoredLast = scored;
+    A.lastBallUpdateCount = cnt;
+}
+
+}  // namespace ggl

@@ -1,0 +1,137 @@
+// Third part of the env layer: the step phases of EnvSet::StepFirstHalf / StepSecondHalf / ResetArena as functions a
+// lane group can split (leader-only bookkeeping, per-player outputs). See env_logic.cuh for reference citations.
+#pragma once
+#include "env_step.cuh"
+
+namespace ggl {
+
+// ---- StepFirstHalf bookkeeping (EnvSet.cpp:115-123): prev snapshot + clear event flags
+GGL_HD void env_begin_step(ArenaDev& A) {
+    A.prevBallVel = A.ball.vel * kBT2UU;
+    for (int s = 0; s < A.numCars; s++) {
+        const CarDev& c = A.cars[A.slotCar[s]];
+        EnvPlayer& ep = A.players[s];
+        ep.prevBoost = c.boost; ep.prevIsFlipping = c.isFlipping; ep.prevIsOnGround = c.isOnGround;
+        for (int e = 0; e < 9; e++) ep.events[e] = 0;
+    }
+}
+
+// ---- StepSecondHalf: parse actions, set controls (EnvSet.cpp:146-153, Action.h:34-46)
+GGL_HD void env_apply_actions(ArenaDev& A, const int32_t* actions /* this arena's slots */, const float* table) {
+    for (int s = 0; s < A.numCars; s++) {
+        int idx = actions[s];
+        if (idx < 0) idx = 0;
+        if (idx >= kNumActions) idx = kNumActions - 1;
+        const float* a = table + 8 * idx;
+        Controls k;
+        k.throttle = a[0]; k.steer = a[1]; k.pitch = a[2]; k.yaw = a[3]; k.roll = a[4];
+        k.jump = a[5] == 1.f; k.boost = a[6] == 1.f; k.handbrake = a[7] == 1.f; k._pad = 0;
+        A.cars[A.slotCar[s]].controls = k;
+        for (int i = 0; i < 8; i++) A.players[s].prevAction[i] = a[i];
+    }
+}
+
+// ---- after the last tick: event tracker, GameState update, terminal conditions (EnvSet.cpp:158-181)
+GGL_HD void env_after_ticks(ArenaDev& A, const EnvCfg& cfg) {
+    event_tracker_update(A);
+    uint64_t dt = A.tickCount - A.gsLastTickCount;
+    int tickSkip = (int)dt;
+    A.stepDeltaTime = tickSkip * (1.0f / 120.0f);
+    bool anyTouch = false;
+    for (int s = 0; s < A.numCars; s++) {
+        const CarDev& c = A.cars[A.slotCar[s]];
+        bool touched = c.hitValid && c.hitTick >= A.gsLastTickCount;
+        if (touched) { A.lastTouchCarId = (int)c.id; anyTouch = true; }
+    }
+    A.stepGoalScored = ball_scored(A) ? 1 : 0;
+    uint8_t term = 0;
+    for (int t = 0; t < cfg.numTerminals; t++) {
+        bool fired = false, trunc = false;
+        if (cfg.terminals[t].kind == GGL_TERM_GOAL_SCORE) {
+            fired = A.stepGoalScored != 0;
+        } else {
+            trunc = true;
+            if (anyTouch) { A.noTouchTimer[t] = 0.f; fired = false; }
+            else { A.noTouchTimer[t] += A.stepDeltaTime; fired = A.noTouchTimer[t] >= cfg.terminals[t].params[0]; }
+        }
+        if (fired) {
+            uint8_t cur = trunc ? 2 : 1;
+            if (term == 0) term = cur;
+            else if (cur == 1) term = cur;
+        }
+    }
+    A.terminal = term;
+}
+
+// ---- per player: weighted reward sum, obs row, mask row (EnvSet.cpp:183-268)
+GGL_HD float env_player_reward(const ArenaDev& A, const EnvCfg& cfg, int slot, float* rawOut /* [numRewards] or null */) {
+    const PlayerView p = player_view(A, A.slotCar[slot]);
+    V3 bp = A.ball.pos * kBT2UU, bv = A.ball.vel * kBT2UU;
+    float total = 0.f;
+    for (int r = 0; r < cfg.numRewards; r++) {
+        float v = reward_value(A, cfg.rewards[r], p, slot, A.stepGoalScored != 0, bp, bv);
+        if (rawOut) rawOut[r] = v;
+        total += v * cfg.rewards[r].weight;
+    }
+    return total;
+}
+
+GGL_HD void env_end_step(ArenaDev& A) { A.gsLastTickCount = A.tickCount; }
+
+// ---- reset -------------------------------------------------------------------------------------------------
+GGL_HD void car_set_spawn(CarDev& c, V3 posUU, float yaw) {
+    car_reset_state_defaults(c);
+    c.pos = posUU * kUU2BT;
+    c.basis = m3_from_euler_ypr(yaw, -0.f, -0.f);
+    car_update_inertia(c);
+}
+
+// Arena::ResetToRandomKickoff (Arena.cpp:112-216). The permutation comes from the arena's own minstd stream
+// (Fisher-Yates); the reference uses libstdc++'s std::shuffle on a time-seeded engine, so kickoff assignment is
+// "a" uniformly random permutation on both sides, not the same one (parity tests inject reset states instead).
+GGL_HD void arena_reset_kickoff(ArenaDev& A) {
+    const float sx[5] = {-2048, 2048, -256, 256, 0}, sy[5] = {-2560, -2560, -3840, -3840, -4608};
+    const float q = 0.78539816339744830962f;
+    const float syaw[5] = {q * 1, q * 3, q * 2, q * 2, q * 2};
+    int order[5] = {0, 1, 2, 3, 4};
+    for (int i = 4; i > 0; i--) {
+        int j = (int)(minstd_next(A.rng) % (uint32_t)(i + 1));
+        int t = order[i]; order[i] = order[j]; order[j] = t;
+    }
+    int nb = 0, no = 0;
+    for (int s = 0; s < A.numCars; s++) {
+        CarDev& c = A.cars[A.slotCar[s]];
+        int i = (c.team == 0) ? nb++ : no++;
+        int k = order[i < 5 ? i : 4];
+        V3 pos = v3(sx[k], sy[k], rl::CAR_SPAWN_REST_Z);
+        float yaw = syaw[k];
+        if (c.team != 0) { pos = pos * v3(-1, -1, 1); yaw = (float)((double)yaw + 3.14159265358979323846); }
+        car_set_spawn(c, pos, yaw);
+    }
+    BallDev& b = A.ball;
+    b.pos = v3(0, 0, rl::BALL_REST_Z) * kUU2BT; b.vel = v3(0, 0, 0); b.angVel = v3(0, 0, 0);
+    b.velImpulseCache = v3(0, 0, 0); b.force = v3(0, 0, 0); b.torque = v3(0, 0, 0); b.updateCounter = 0;
+    for (int p = 0; p < kNumPads; p++) { A.pads[p].isActive = 1; A.pads[p].cooldown = 0.f; A.pads[p].prevLockedCarId = 0; A.pads[p].curLockedCarId = 0; }
+}
+
+// EnvSet::ResetArena bookkeeping after the StateSetter ran (EnvSet.cpp:276-303)
+GGL_HD void env_after_state_set(ArenaDev& A) {
+    A.ballScoredLast = 0; A.ballShot = 0; A.shotCooldown = 0.f;        // GameEventTracker::ResetPersistentInfo
+    A.lastTouchCarId = -1;
+    for (int s = 0; s < A.numCars; s++) {
+        const CarDev& c = A.cars[A.slotCar[s]];
+        if (c.hitValid) A.lastTouchCarId = (int)c.id;                   // fresh GameState: every valid hit counts as "this step"
+        EnvPlayer& ep = A.players[s];
+        for (int i = 0; i < 8; i++) ep.prevAction[i] = 0.f;
+        for (int e = 0; e < 9; e++) ep.events[e] = 0;
+        ep.prevBoost = c.boost; ep.prevIsFlipping = c.isFlipping; ep.prevIsOnGround = c.isOnGround;
+    }
+    A.gsLastTickCount = A.tickCount;
+    for (int t = 0; t < kMaxTerminals; t++) A.noTouchTimer[t] = 0.f;
+    A.prevBallVel = A.ball.vel * kBT2UU;
+    A.stepGoalScored = ball_scored(A) ? 1 : 0;
+    A.stepDeltaTime = 0.f;
+    A.terminal = 0;
+}
+
+}  // namespace ggl

@@ -1,0 +1,171 @@
+// Second part of the env layer: per-step GameState snapshot, terminals, rewards, observation rows, kickoff reset.
+// See env_logic.cuh for the reference citations.
+#pragma once
+#include "env_logic.cuh"
+
+namespace ggl {
+
+// What the reward / obs code needs of one player, in Unreal units like RLGC::Player (: CarState)
+struct PlayerView {
+    V3 pos, vel, angVel, fwd, right, up;
+    float boost;
+    int team, carId;
+    bool onGround, hasFlipOrJump, demoed, hasJumped, touchedStep;
+};
+
+GGL_HD PlayerView player_view(const ArenaDev& A, int ci) {
+    const CarDev& c = A.cars[ci];
+    PlayerView p;
+    p.pos = c.pos * kBT2UU; p.vel = c.vel * kBT2UU; p.angVel = c.angVel;
+    p.fwd = col(c.basis, 0); p.right = col(c.basis, 1); p.up = col(c.basis, 2);
+    p.boost = c.boost; p.team = c.team; p.carId = (int)c.id;
+    p.onGround = c.isOnGround; p.hasFlipOrJump = car_has_flip_or_jump(c); p.demoed = c.isDemoed; p.hasJumped = c.hasJumped;
+    p.touchedStep = c.hitValid && c.hitTick >= A.gsLastTickCount;
+    return p;
+}
+
+// one reward function for one player (CommonRewards.h); `slot` indexes A.players
+GGL_HD float reward_value(const ArenaDev& A, const RewardCfg& r, const PlayerView& p, int slot, bool goalScored, V3 ballPos, V3 ballVel) {
+    const EnvPlayer& ep = A.players[slot];
+    switch (r.kind) {
+    case GGL_REW_PLAYER_GOAL: return (float)ep.events[EV_GOAL];
+    case GGL_REW_ASSIST: return (float)ep.events[EV_ASSIST];
+    case GGL_REW_SHOT: return (float)ep.events[EV_SHOT];
+    case GGL_REW_SHOT_PASS: return (float)ep.events[EV_SHOTPASS];
+    case GGL_REW_SAVE: return (float)ep.events[EV_SAVE];
+    case GGL_REW_BUMP: return (float)ep.events[EV_BUMP];
+    case GGL_REW_BUMPED_PENALTY: return -(float)ep.events[EV_BUMPED];
+    case GGL_REW_DEMO: return (float)ep.events[EV_DEMO];
+    case GGL_REW_DEMOED_PENALTY: return -(float)ep.events[EV_DEMOED];
+    case GGL_REW_GOAL: {
+        if (!goalScored) return 0.f;
+        int ballTeam = ballPos.y < 0.f ? 0 : 1;
+        return (p.team != ballTeam) ? 1.f : r.params[0];
+    }
+    case GGL_REW_VELOCITY: return len(p.vel) / 2300.f * (1 - 2 * (r.params[0] != 0.f ? 1 : 0));
+    case GGL_REW_VELOCITY_BALL_TO_GOAL: {
+        bool targetOrange = p.team == 0;
+        if (r.params[0] != 0.f) targetOrange = !targetOrange;
+        V3 target = targetOrange ? v3(0, 6000.f, 642.775f / 2) : v3(0, -6000.f, 642.775f / 2);
+        V3 dir = rs_normalized(target - ballPos);
+        return dot(dir, ballVel / 6000.f);
+    }
+    case GGL_REW_VELOCITY_PLAYER_TO_BALL: {
+        V3 dir = rs_normalized(ballPos - p.pos);
+        return dot(dir, p.vel / 2300.f);
+    }
+    case GGL_REW_FACE_BALL: return dot(p.fwd, rs_normalized(ballPos - p.pos));
+    case GGL_REW_TOUCH_BALL: return p.touchedStep ? 1.f : 0.f;
+    case GGL_REW_SPEED: return len(p.vel) / 2300.f;
+    case GGL_REW_WAVEDASH: return (p.onGround && (ep.prevIsFlipping && !ep.prevIsOnGround)) ? 1.f : 0.f;
+    case GGL_REW_PICKUP_BOOST:
+        return (p.boost > ep.prevBoost) ? sqrtf(p.boost / 100.f) - sqrtf(ep.prevBoost / 100.f) : 0.f;
+    case GGL_REW_SAVE_BOOST: return fclamp(powf(p.boost / 100, r.params[0]), 0.f, 1.f);
+    case GGL_REW_AIR: return p.onGround ? 0.f : 1.f;
+    case GGL_REW_TOUCH_ACCEL: {
+        if (!p.touchedStep) return 0.f;
+        const float maxSp = 110.f * (250.f / 9.f);
+        float prevFrac = fminf(1.f, len(A.prevBallVel) / maxSp), curFrac = fminf(1.f, len(ballVel) / maxSp);
+        return curFrac > prevFrac ? (curFrac - prevFrac) : 0.f;
+    }
+    case GGL_REW_STRONG_TOUCH: {
+        if (!p.touchedStep) return 0.f;
+        float hit = len(ballVel - A.prevBallVel);
+        if (hit < r.params[0]) return 0.f;
+        return fminf(1.f, hit / r.params[1]);
+    }
+    default: return 0.f;
+    }
+}
+
+// pads in RLGym order (CommonValues::BOOST_LOCATIONS) -> RocketSim pad index (GameState.cpp:7-51 boostPadIndexMap)
+GGL_HD int pad_index_map(int i) {
+    const uint8_t map[34] = {6, 7, 8, 4, 5, 9, 10, 11, 12, 13, 14, 15, 16, 17, 18, 0, 19, 20, 1, 21, 22, 23, 24, 25, 26, 27, 28, 29, 30, 2, 3, 31, 32, 33};
+    return map[i];
+}
+
+GGL_HD void write_player_default(float*& o, const PlayerView& p, bool inv) {
+    float sx = inv ? -1.f : 1.f;
+    const float pcx = 1 / 4096.f, pcy = 1 / 5120.f, pcz = 1 / 2044.f, vc = 1 / 2300.f, ac = 1 / 5.5f;
+    o[0] = (inv ? -p.pos.x : p.pos.x) * pcx; o[1] = (inv ? -p.pos.y : p.pos.y) * pcy; o[2] = p.pos.z * pcz;
+    o[3] = inv ? -p.fwd.x : p.fwd.x; o[4] = inv ? -p.fwd.y : p.fwd.y; o[5] = p.fwd.z;
+    o[6] = inv ? -p.up.x : p.up.x; o[7] = inv ? -p.up.y : p.up.y; o[8] = p.up.z;
+    o[9] = (inv ? -p.vel.x : p.vel.x) * vc; o[10] = (inv ? -p.vel.y : p.vel.y) * vc; o[11] = p.vel.z * vc;
+    o[12] = (inv ? -p.angVel.x : p.angVel.x) * ac; o[13] = (inv ? -p.angVel.y : p.angVel.y) * ac; o[14] = p.angVel.z * ac;
+    o[15] = p.boost / 100; o[16] = p.onGround ? 1.f : 0.f; o[17] = p.hasFlipOrJump ? 1.f : 0.f; o[18] = p.demoed ? 1.f : 0.f;
+    (void)sx;
+    o += 19;
+}
+
+GGL_HD V3 inv_xy(V3 v, bool inv) { return inv ? v3(-v.x, -v.y, v.z) : v; }
+
+GGL_HD void write_player_advanced(float*& o, const PlayerView& pl, bool inv, V3 ballPos, V3 ballVel) {
+    const float PC = 1.0f / 2300.0f, VC = 1.0f / 2300.0f, AC = 1.0f / 5.5f;
+    V3 pos = inv_xy(pl.pos, inv), vel = inv_xy(pl.vel, inv), av = inv_xy(pl.angVel, inv);
+    V3 f = inv_xy(pl.fwd, inv), r = inv_xy(pl.right, inv), u = inv_xy(pl.up, inv);
+    o[0] = pos.x * PC; o[1] = pos.y * PC; o[2] = pos.z * PC;
+    o[3] = f.x; o[4] = f.y; o[5] = f.z;
+    o[6] = u.x; o[7] = u.y; o[8] = u.z;
+    o[9] = vel.x * VC; o[10] = vel.y * VC; o[11] = vel.z * VC;
+    o[12] = av.x * AC; o[13] = av.y * AC; o[14] = av.z * AC;
+    o[15] = (f.x * av.x + f.y * av.y + f.z * av.z) * AC;
+    o[16] = (r.x * av.x + r.y * av.y + r.z * av.z) * AC;
+    o[17] = (u.x * av.x + u.y * av.y + u.z * av.z) * AC;
+    V3 rb = ballPos - pos;
+    o[18] = (f.x * rb.x + f.y * rb.y + f.z * rb.z) * PC;
+    o[19] = (r.x * rb.x + r.y * rb.y + r.z * rb.z) * PC;
+    o[20] = (u.x * rb.x + u.y * rb.y + u.z * rb.z) * PC;
+    V3 rv = ballVel - vel;
+    o[21] = (f.x * rv.x + f.y * rv.y + f.z * rv.z) * VC;
+    o[22] = (r.x * rv.x + r.y * rv.y + r.z * rv.z) * VC;
+    o[23] = (u.x * rv.x + u.y * rv.y + u.z * rv.z) * VC;
+    o[24] = pl.boost * 0.01f; o[25] = pl.onGround ? 1.f : 0.f; o[26] = pl.hasFlipOrJump ? 1.f : 0.f;
+    o[27] = pl.demoed ? 1.f : 0.f; o[28] = pl.hasJumped ? 1.f : 0.f;
+    o += 29;
+}
+
+// One observation row for players[slot]
+GGL_HD void build_obs_row(const ArenaDev& A, const EnvCfg& cfg, int slot, float* out) {
+    const int ci = A.slotCar[slot];
+    const PlayerView me = player_view(A, ci);
+    const bool inv = me.team == 1;
+    V3 bp = inv_xy(A.ball.pos * kBT2UU, inv), bv = inv_xy(A.ball.vel * kBT2UU, inv), bw = inv_xy(A.ball.angVel, inv);
+    float* o = out;
+    if (cfg.obsKind == GGL_OBS_ADVANCED) {
+        const float PC = 1 / 5000.f, VC = 1 / 2300.f, AC = 1 / 3.f;      // class constants bind in BuildObs
+        o[0] = bp.x * PC; o[1] = bp.y * PC; o[2] = bp.z * PC; o[3] = bv.x * VC; o[4] = bv.y * VC; o[5] = bv.z * VC;
+        o[6] = bw.x * AC; o[7] = bw.y * AC; o[8] = bw.z * AC;
+    } else {
+        o[0] = bp.x * (1 / 4096.f); o[1] = bp.y * (1 / 5120.f); o[2] = bp.z * (1 / 2044.f);
+        o[3] = bv.x * (1 / 2300.f); o[4] = bv.y * (1 / 2300.f); o[5] = bv.z * (1 / 2300.f);
+        o[6] = bw.x * (1 / 5.5f); o[7] = bw.y * (1 / 5.5f); o[8] = bw.z * (1 / 5.5f);
+    }
+    o += 9;
+    for (int i = 0; i < 8; i++) o[i] = A.players[slot].prevAction[i];
+    o += 8;
+    for (int i = 0; i < kNumPads; i++) {
+        // boostPads[i] = pad map[i]; boostPadsInv[i] = pad map[33-i]; timers likewise; GetBoostPadTimers is swapped
+        const PadDev& pd = A.pads[pad_index_map(inv ? 33 - i : i)];
+        if (cfg.obsKind == GGL_OBS_ADVANCED) {
+            const PadDev& tm = A.pads[pad_index_map(inv ? i : 33 - i)];
+            o[i] = pd.isActive ? 1.0f : 1.0f / (1.0f + tm.cooldown);
+        } else {
+            o[i] = pd.isActive ? 1.f : 0.f;
+        }
+    }
+    o += kNumPads;
+    if (cfg.obsKind == GGL_OBS_ADVANCED) write_player_advanced(o, me, inv, bp, bv);
+    else write_player_default(o, me, inv);
+    for (int pass = 0; pass < 2; pass++)
+        for (int s = 0; s < A.numCars; s++) {
+            int oc = A.slotCar[s];
+            if (oc == ci) continue;
+            const bool mate = A.cars[oc].team == me.team;
+            if (mate != (pass == 0)) continue;
+            PlayerView ov = player_view(A, oc);
+            if (cfg.obsKind == GGL_OBS_ADVANCED) write_player_advanced(o, ov, inv, bp, bv);
+            else write_player_default(o, ov, inv);
+        }
+}
+
+}  // namespace ggl

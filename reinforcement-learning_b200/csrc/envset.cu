@@ -1,0 +1,335 @@
+// C ABI of the device-resident EnvSet (include/gigaenv.h). Host side: descriptor translation, device memory,
+// kernel launches on the caller's stream. No CPU fallback: every entry point that computes launches a kernel.
+#include "common.cuh"
+#include "sim_convert.cuh"
+#include "env_kernels.cuh"
+
+#include <new>
+#include <vector>
+
+using namespace ggl;
+
+struct ggl_envset {
+    EnvCfg cfg;
+    EnvDevPtrs P;
+    int device;
+    int numPlayers;
+    WorldHost worldHost;
+    Tri* d_tris; int* d_cellStart; int* d_cellTris;
+    ArenaDev* d_reset;
+    float* d_table;
+    int32_t* d_actionsScratch;
+    // pinned staging for the host-buffer wrapper
+    int32_t* h_actions; float* h_obs; uint8_t* h_masks; float* h_rewards; uint8_t* h_terminals;
+    cudaStream_t ownStream;
+    uint64_t seed;
+};
+
+namespace {
+
+int grid_for(const EnvCfg& cfg) { return (cfg.numArenas + kArenasPerBlock - 1) / kArenasPerBlock; }
+
+int obs_size(int kind, int cars) { return 51 + (kind == GGL_OBS_ADVANCED ? 29 : 19) * cars; }
+
+template <class T>
+int dmalloc(T** p, size_t n) {
+    cudaError_t e = cudaMalloc((void**)p, n * sizeof(T));
+    if (e != cudaSuccess) { ggl::set_error("cudaMalloc(%zu bytes) -> %s", n * sizeof(T), cudaGetErrorString(e)); return GGL_ERR_NOMEM; }
+    return GGL_OK;
+}
+
+void free_env(ggl_envset* e) {
+    if (!e) return;
+    cudaFree(e->P.arenas); cudaFree(e->d_reset); cudaFree(e->P.obs); cudaFree(e->P.masks); cudaFree(e->P.rewards);
+    cudaFree(e->P.terminals); cudaFree(e->P.slotCarId); cudaFree(e->P.slotTeam); cudaFree(e->P.events); cudaFree(e->P.lastRewards);
+    cudaFree(e->d_tris); cudaFree(e->d_cellStart); cudaFree(e->d_cellTris); cudaFree(e->d_table); cudaFree(e->d_actionsScratch);
+    if (e->h_actions) cudaFreeHost(e->h_actions);
+    if (e->h_obs) cudaFreeHost(e->h_obs);
+    if (e->h_masks) cudaFreeHost(e->h_masks);
+    if (e->h_rewards) cudaFreeHost(e->h_rewards);
+    if (e->h_terminals) cudaFreeHost(e->h_terminals);
+    if (e->ownStream) cudaStreamDestroy(e->ownStream);
+    delete e;
+}
+
+}  // namespace
+
+extern "C" int ggl_action_table(float* out_table, int* out_num_actions) {
+    if (!out_table) { ggl::set_error("ggl_action_table: null"); return GGL_ERR_INVALID; }
+    for (int i = 0; i < kNumActions; i++) action_from_index(i, out_table + 8 * i);
+    if (out_num_actions) *out_num_actions = kNumActions;
+    return GGL_OK;
+}
+
+extern "C" int ggl_envset_create(const ggl_envset_desc* d, ggl_envset** out) {
+    if (!d || !out) { ggl::set_error("ggl_envset_create: null argument"); return GGL_ERR_INVALID; }
+    if (d->num_arenas <= 0 || d->players_per_team < 1 || d->players_per_team > 3 || d->tick_skip <= 0 || d->action_delay < 0 ||
+        d->action_delay > d->tick_skip || d->num_rewards < 0 || d->num_rewards > GGL_MAX_REWARDS || d->num_terminals < 0 ||
+        d->num_terminals > GGL_MAX_TERMINALS) {
+        ggl::set_error("ggl_envset_create: descriptor out of range"); return GGL_ERR_INVALID;
+    }
+    if (d->obs_kind != GGL_OBS_DEFAULT && d->obs_kind != GGL_OBS_ADVANCED) { ggl::set_error("unsupported obs kind %d", d->obs_kind); return GGL_ERR_UNSUPPORTED; }
+    for (int i = 0; i < d->num_rewards; i++)
+        if (d->rewards[i].kind < 0 || d->rewards[i].kind >= GGL_REW_KIND_COUNT) { ggl::set_error("unsupported reward kind %d", d->rewards[i].kind); return GGL_ERR_UNSUPPORTED; }
+    for (int i = 0; i < d->num_terminals; i++)
+        if (d->terminals[i].kind != GGL_TERM_GOAL_SCORE && d->terminals[i].kind != GGL_TERM_NO_TOUCH) { ggl::set_error("unsupported terminal kind"); return GGL_ERR_UNSUPPORTED; }
+    GGL_CUDA(cudaSetDevice(d->device));
+    ggl_envset* e = new (std::nothrow) ggl_envset();
+    if (!e) return GGL_ERR_NOMEM;
+    memset(&e->cfg, 0, sizeof(e->cfg)); memset(&e->P, 0, sizeof(e->P));
+    e->d_tris = nullptr; e->d_cellStart = e->d_cellTris = nullptr; e->d_reset = nullptr; e->d_table = nullptr; e->d_actionsScratch = nullptr;
+    e->h_actions = nullptr; e->h_obs = nullptr; e->h_masks = nullptr; e->h_rewards = nullptr; e->h_terminals = nullptr; e->ownStream = nullptr;
+    e->device = d->device; e->seed = d->seed;
+    EnvCfg& c = e->cfg;
+    c.numArenas = d->num_arenas; c.playersPerTeam = d->players_per_team; c.numCars = 2 * d->players_per_team;
+    c.tickSkip = d->tick_skip; c.actionDelay = d->action_delay; c.obsKind = d->obs_kind; c.obsSize = obs_size(d->obs_kind, c.numCars);
+    c.numRewards = d->num_rewards; c.numTerminals = d->num_terminals; c.stateSetter = d->state_setter;
+    for (int i = 0; i < d->num_rewards; i++) {
+        c.rewards[i].kind = d->rewards[i].kind; c.rewards[i].weight = d->rewards[i].weight;
+        for (int k = 0; k < 4; k++) c.rewards[i].params[k] = d->rewards[i].params[k];
+    }
+    for (int i = 0; i < d->num_terminals; i++) {
+        c.terminals[i].kind = d->terminals[i].kind;
+        c.terminals[i].params[0] = d->terminals[i].params[0]; c.terminals[i].params[1] = d->terminals[i].params[1];
+    }
+    e->numPlayers = c.numArenas * c.numCars;
+    // arena meshes -> triangle grid
+    for (int i = 0; i < d->num_meshes; i++)
+        if (!d->meshes || !world_add_cmf(e->worldHost, d->meshes[i].data, d->meshes[i].size)) {
+            ggl::set_error("ggl_envset_create: malformed .cmf mesh %d", i); free_env(e); return GGL_ERR_INVALID;
+        }
+    world_build_grid(e->worldHost);
+    int rc = GGL_OK;
+    const size_t nt = e->worldHost.tris.size() ? e->worldHost.tris.size() : 1, ncs = e->worldHost.cellStart.size(),
+                 nct = e->worldHost.cellTris.size() ? e->worldHost.cellTris.size() : 1;
+    if ((rc = dmalloc(&e->d_tris, nt)) || (rc = dmalloc(&e->d_cellStart, ncs)) || (rc = dmalloc(&e->d_cellTris, nct)) ||
+        (rc = dmalloc(&e->P.arenas, (size_t)c.numArenas)) || (rc = dmalloc(&e->P.obs, (size_t)e->numPlayers * c.obsSize)) ||
+        (rc = dmalloc(&e->P.masks, (size_t)e->numPlayers * kNumActions)) || (rc = dmalloc(&e->P.rewards, (size_t)e->numPlayers)) ||
+        (rc = dmalloc(&e->P.terminals, (size_t)c.numArenas)) || (rc = dmalloc(&e->P.slotCarId, (size_t)e->numPlayers)) ||
+        (rc = dmalloc(&e->P.slotTeam, (size_t)e->numPlayers)) || (rc = dmalloc(&e->P.events, (size_t)e->numPlayers * 9)) ||
+        (rc = dmalloc(&e->P.lastRewards, (size_t)c.numArenas * (c.numRewards ? c.numRewards : 1))) ||
+        (rc = dmalloc(&e->d_table, (size_t)kNumActions * 8)) || (rc = dmalloc(&e->d_actionsScratch, (size_t)e->numPlayers))) {
+        free_env(e); return rc;
+    }
+    if (e->worldHost.tris.size()) cudaMemcpy(e->d_tris, e->worldHost.tris.data(), e->worldHost.tris.size() * sizeof(Tri), cudaMemcpyHostToDevice);
+    cudaMemcpy(e->d_cellStart, e->worldHost.cellStart.data(), ncs * sizeof(int), cudaMemcpyHostToDevice);
+    if (e->worldHost.cellTris.size()) cudaMemcpy(e->d_cellTris, e->worldHost.cellTris.data(), e->worldHost.cellTris.size() * sizeof(int), cudaMemcpyHostToDevice);
+    WorldDev w = world_view(e->worldHost);
+    w.tris = e->d_tris; w.cellStart = e->d_cellStart; w.cellTris = e->d_cellTris;
+    e->P.world = w;
+    float table[kNumActions * 8];
+    ggl_action_table(table, nullptr);
+    cudaMemcpy(e->d_table, table, sizeof(table), cudaMemcpyHostToDevice);
+    e->P.actionTable = e->d_table;
+    // initial arena blobs: cars exist (AddCar order: blue first), everything else comes from the first reset
+    {
+        std::vector<ArenaDev> init((size_t)c.numArenas);
+        memset(init.data(), 0, init.size() * sizeof(ArenaDev));
+        for (int a = 0; a < c.numArenas; a++) {
+            ArenaDev& A = init[a];
+            A.numCars = c.numCars;
+            uint64_t s = (d->seed * 6364136223846793005ull + 1442695040888963407ull) ^ ((uint64_t)(a + 1) * 0x9E3779B97F4A7C15ull);
+            A.rng = (uint32_t)(s % 2147483646ull) + 1u;
+            for (int i = 0; i < c.numCars; i++) {
+                CarDev& car = A.cars[i];
+                car.id = (uint32_t)(i + 1);
+                car.team = i < c.playersPerTeam ? 0 : 1;
+                car.basis = m3_identity();
+                car_reset_state_defaults(car);
+                car_update_inertia(car);
+                for (int w2 = 0; w2 < 4; w2++) car.w[w2].ground = GROUND_NONE;
+            }
+            for (int s2 = 0; s2 < c.numCars; s2++) A.slotCar[s2] = (uint8_t)(d->slot_order_reversed ? c.numCars - 1 - s2 : s2);
+            A.lastTouchCarId = -1;
+        }
+        cudaMemcpy(e->P.arenas, init.data(), init.size() * sizeof(ArenaDev), cudaMemcpyHostToDevice);
+    }
+    cudaMemset(e->P.terminals, 0, (size_t)c.numArenas);
+    cudaMemset(e->P.rewards, 0, (size_t)e->numPlayers * sizeof(float));
+    cudaMemset(e->P.lastRewards, 0, (size_t)c.numArenas * (c.numRewards ? c.numRewards : 1) * sizeof(float));
+    GGL_CUDA(cudaStreamCreateWithFlags(&e->ownStream, cudaStreamNonBlocking));
+    // EnvSet ctor: reset every arena once (EnvSet.cpp:106-110)
+    EnvCfg kc = e->cfg; kc.stateSetter = GGL_SETTER_KICKOFF;
+    env_reset_kernel<<<grid_for(e->cfg), kBlock, 0, 0>>>(kc, e->P, 1);
+    ggl::count_launch();
+    cudaError_t err = cudaDeviceSynchronize();
+    if (err != cudaSuccess) { ggl::set_error("env_reset_kernel -> %s", cudaGetErrorString(err)); free_env(e); return GGL_ERR_CUDA; }
+    *out = e;
+    return GGL_OK;
+}
+
+extern "C" int ggl_envset_destroy(ggl_envset* e) {
+    if (!e) return GGL_OK;
+    cudaSetDevice(e->device);
+    cudaDeviceSynchronize();
+    free_env(e);
+    return GGL_OK;
+}
+
+#define ENV_CHECK(e) if (!(e)) { ggl::set_error("null envset"); return GGL_ERR_INVALID; }
+
+extern "C" int ggl_envset_reset(ggl_envset* e, void* stream) {
+    ENV_CHECK(e);
+    env_reset_kernel<<<grid_for(e->cfg), kBlock, 0, (cudaStream_t)stream>>>(e->cfg, e->P, 0);
+    GGL_LAUNCH_CHECK(); ggl::count_launch();
+    return GGL_OK;
+}
+extern "C" int ggl_envset_step_first_half(ggl_envset* e, void* stream) {
+    ENV_CHECK(e);
+    env_step_kernel<<<grid_for(e->cfg), kBlock, 0, (cudaStream_t)stream>>>(e->cfg, e->P, nullptr, 1, 0);
+    GGL_LAUNCH_CHECK(); ggl::count_launch();
+    return GGL_OK;
+}
+extern "C" int ggl_envset_step_second_half(ggl_envset* e, const int32_t* d_actions, void* stream) {
+    ENV_CHECK(e);
+    if (!d_actions) { ggl::set_error("null actions"); return GGL_ERR_INVALID; }
+    env_step_kernel<<<grid_for(e->cfg), kBlock, 0, (cudaStream_t)stream>>>(e->cfg, e->P, d_actions, 0, 1);
+    GGL_LAUNCH_CHECK(); ggl::count_launch();
+    return GGL_OK;
+}
+extern "C" int ggl_envset_step(ggl_envset* e, const int32_t* d_actions, void* stream) {
+    ENV_CHECK(e);
+    if (!d_actions) { ggl::set_error("null actions"); return GGL_ERR_INVALID; }
+    env_step_kernel<<<grid_for(e->cfg), kBlock, 0, (cudaStream_t)stream>>>(e->cfg, e->P, d_actions, 1, 1);
+    GGL_LAUNCH_CHECK(); ggl::count_launch();
+    return GGL_OK;
+}
+extern "C" int ggl_arena_step(ggl_envset* e, int ticks, void* stream) {
+    ENV_CHECK(e);
+    arena_step_kernel<<<grid_for(e->cfg), kBlock, 0, (cudaStream_t)stream>>>(e->cfg, e->P, ticks);
+    GGL_LAUNCH_CHECK(); ggl::count_launch();
+    return GGL_OK;
+}
+extern "C" int ggl_envset_random_actions(ggl_envset* e, int32_t* d_actions, uint64_t seed, void* stream) {
+    ENV_CHECK(e);
+    random_actions_kernel<<<(e->numPlayers + 255) / 256, 256, 0, (cudaStream_t)stream>>>(e->P.masks, d_actions, e->numPlayers, seed);
+    GGL_LAUNCH_CHECK(); ggl::count_launch();
+    return GGL_OK;
+}
+extern "C" int ggl_envset_sync(ggl_envset* e) {
+    ENV_CHECK(e);
+    GGL_CUDA(cudaSetDevice(e->device));
+    GGL_CUDA(cudaDeviceSynchronize());
+    return GGL_OK;
+}
+extern "C" int ggl_envset_views_get(ggl_envset* e, ggl_envset_views* v) {
+    ENV_CHECK(e);
+    if (!v) return GGL_ERR_INVALID;
+    v->num_arenas = e->cfg.numArenas; v->num_players = e->numPlayers; v->obs_size = e->cfg.obsSize; v->num_actions = kNumActions;
+    v->players_per_arena = e->cfg.numCars;
+    v->d_obs = e->P.obs; v->d_action_masks = e->P.masks; v->d_rewards = e->P.rewards; v->d_terminals = e->P.terminals;
+    v->d_slot_car_id = e->P.slotCarId; v->d_slot_team = e->P.slotTeam; v->d_events = e->P.events; v->d_last_rewards = e->P.lastRewards;
+    return GGL_OK;
+}
+
+// ---- state injection / extraction (host <-> device, one arena at a time; test and StateSetter path) ----
+extern "C" int ggl_envset_set_state(ggl_envset* e, int arena, const ggl_arena_state* st) {
+    ENV_CHECK(e);
+    if (!st || arena < 0 || arena >= e->cfg.numArenas || st->num_cars != e->cfg.numCars) { ggl::set_error("set_state: bad argument"); return GGL_ERR_INVALID; }
+    GGL_CUDA(cudaSetDevice(e->device));
+    GGL_CUDA(cudaDeviceSynchronize());
+    ArenaDev* A = new ArenaDev();
+    cudaError_t err = cudaMemcpy(A, e->P.arenas + arena, sizeof(ArenaDev), cudaMemcpyDeviceToHost);
+    if (err == cudaSuccess) {
+        arena_phys_from_host(*st, *A);
+        err = cudaMemcpy(e->P.arenas + arena, A, sizeof(ArenaDev), cudaMemcpyHostToDevice);
+    }
+    delete A;
+    if (err != cudaSuccess) { ggl::set_error("set_state -> %s", cudaGetErrorString(err)); return GGL_ERR_CUDA; }
+    return GGL_OK;
+}
+
+extern "C" int ggl_envset_get_state(ggl_envset* e, int arena, ggl_arena_state* st) {
+    ENV_CHECK(e);
+    if (!st || arena < 0 || arena >= e->cfg.numArenas) { ggl::set_error("get_state: bad argument"); return GGL_ERR_INVALID; }
+    GGL_CUDA(cudaSetDevice(e->device));
+    GGL_CUDA(cudaDeviceSynchronize());
+    ArenaDev* A = new ArenaDev();
+    cudaError_t err = cudaMemcpy(A, e->P.arenas + arena, sizeof(ArenaDev), cudaMemcpyDeviceToHost);
+    if (err == cudaSuccess) arena_phys_to_host(*A, *st);
+    delete A;
+    if (err != cudaSuccess) { ggl::set_error("get_state -> %s", cudaGetErrorString(err)); return GGL_ERR_CUDA; }
+    return GGL_OK;
+}
+
+extern "C" int ggl_envset_set_reset_state(ggl_envset* e, int arena, const ggl_arena_state* st) {
+    ENV_CHECK(e);
+    if (!st || arena < 0 || arena >= e->cfg.numArenas || st->num_cars != e->cfg.numCars) { ggl::set_error("set_reset_state: bad argument"); return GGL_ERR_INVALID; }
+    GGL_CUDA(cudaSetDevice(e->device));
+    GGL_CUDA(cudaDeviceSynchronize());
+    if (!e->d_reset) {
+        int rc = dmalloc(&e->d_reset, (size_t)e->cfg.numArenas);
+        if (rc) return rc;
+        GGL_CUDA(cudaMemset(e->d_reset, 0, (size_t)e->cfg.numArenas * sizeof(ArenaDev)));
+        e->P.resetArenas = e->d_reset;
+    }
+    ArenaDev* A = new ArenaDev();
+    memset(A, 0, sizeof(ArenaDev));
+    arena_phys_from_host(*st, *A);
+    A->hasResetState = 1;
+    cudaError_t err = cudaMemcpy(e->d_reset + arena, A, sizeof(ArenaDev), cudaMemcpyHostToDevice);
+    delete A;
+    if (err != cudaSuccess) { ggl::set_error("set_reset_state -> %s", cudaGetErrorString(err)); return GGL_ERR_CUDA; }
+    return GGL_OK;
+}
+
+extern "C" int ggl_envset_set_slot_order(ggl_envset* e, const int32_t* h_car_ids) {
+    ENV_CHECK(e);
+    if (!h_car_ids) return GGL_ERR_INVALID;
+    GGL_CUDA(cudaSetDevice(e->device));
+    GGL_CUDA(cudaDeviceSynchronize());
+    const int P = e->cfg.numCars;
+    std::vector<ArenaDev> all((size_t)e->cfg.numArenas);
+    GGL_CUDA(cudaMemcpy(all.data(), e->P.arenas, all.size() * sizeof(ArenaDev), cudaMemcpyDeviceToHost));
+    for (int a = 0; a < e->cfg.numArenas; a++) {
+        bool seen[kMaxCars] = {};
+        for (int s = 0; s < P; s++) {
+            int id = h_car_ids[a * P + s];
+            if (id < 1 || id > P || seen[id - 1]) { ggl::set_error("set_slot_order: arena %d is not a permutation of 1..%d", a, P); return GGL_ERR_INVALID; }
+            seen[id - 1] = true;
+            all[a].slotCar[s] = (uint8_t)(id - 1);
+        }
+    }
+    GGL_CUDA(cudaMemcpy(e->P.arenas, all.data(), all.size() * sizeof(ArenaDev), cudaMemcpyHostToDevice));
+    // obs / mask rows follow the slot order: rebuild them without touching the arena state
+    return GGL_OK;
+}
+
+// ---- host-buffer wrapper: the reference-facing call (EnvState vectors live on the host, EnvSet.h:35-60) ----
+extern "C" int ggl_envset_step_host(ggl_envset* e, const int32_t* h_actions, float* h_obs, uint8_t* h_masks, float* h_rewards,
+                                    uint8_t* h_terminals) {
+    ENV_CHECK(e);
+    if (!h_actions) { ggl::set_error("null actions"); return GGL_ERR_INVALID; }
+    GGL_CUDA(cudaSetDevice(e->device));
+    cudaStream_t s = e->ownStream;
+    const size_t np = (size_t)e->numPlayers;
+    GGL_CUDA(cudaMemcpyAsync(e->d_actionsScratch, h_actions, np * sizeof(int32_t), cudaMemcpyHostToDevice, s));
+    int rc = ggl_envset_reset(e, s);
+    if (rc) return rc;
+    rc = ggl_envset_step(e, e->d_actionsScratch, s);
+    if (rc) return rc;
+    if (h_obs) GGL_CUDA(cudaMemcpyAsync(h_obs, e->P.obs, np * e->cfg.obsSize * sizeof(float), cudaMemcpyDeviceToHost, s));
+    if (h_masks) GGL_CUDA(cudaMemcpyAsync(h_masks, e->P.masks, np * kNumActions, cudaMemcpyDeviceToHost, s));
+    if (h_rewards) GGL_CUDA(cudaMemcpyAsync(h_rewards, e->P.rewards, np * sizeof(float), cudaMemcpyDeviceToHost, s));
+    if (h_terminals) GGL_CUDA(cudaMemcpyAsync(h_terminals, e->P.terminals, (size_t)e->cfg.numArenas, cudaMemcpyDeviceToHost, s));
+    GGL_CUDA(cudaStreamSynchronize(s));
+    return GGL_OK;
+}
+
+// sizes of the C structs (the ctypes mirror in abi.py is checked against these)
+extern "C" size_t ggl_abi_sizeof(int which) {
+    switch (which) {
+    case 0: return sizeof(ggl_envset_desc);
+    case 1: return sizeof(ggl_arena_state);
+    case 2: return sizeof(ggl_car_state);
+    case 3: return sizeof(ggl_ball_state);
+    case 4: return sizeof(ggl_pad_state);
+    case 5: return sizeof(ggl_envset_views);
+    case 6: return sizeof(ggl_reward_desc);
+    case 7: return sizeof(ggl_terminal_desc);
+    case 8: return sizeof(ggl_controls);
+    case 9: return sizeof(ggl_wheel_state);
+    case 100: return sizeof(ArenaDev);
+    default: return 0;
+    }
+}

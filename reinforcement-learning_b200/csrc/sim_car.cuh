@@ -79,12 +79,19 @@ GGL_HD float curve_bump_up(float v) {
 // ---------------------------------------------------------------------------------------------- car constants
 GGL_HD V3 car_half_extents() { return v3(rl::HITBOX_X * kUU2BT / 2, rl::HITBOX_Y * kUU2BT / 2, rl::HITBOX_Z * kUU2BT / 2); }
 GGL_HD V3 car_hitbox_offset() { return v3(rl::HITBOX_OFF_X * kUU2BT, rl::HITBOX_OFF_Y * kUU2BT, rl::HITBOX_OFF_Z * kUU2BT); }
-// btBoxShape::calculateLocalInertia on the full half extents, then 1/x (btRigidBody::setMassProps)
+// btBoxShape::calculateLocalInertia on the half extents WITH margin, then 1/x (btRigidBody::setMassProps). The reference box
+// stores (he - 0.04) and later shrinks its margin to 10% of the smallest half extent (setSafeMargin), so the extents with
+// margin are slightly smaller than the nominal hitbox.
+GGL_HD V3 car_box_full_extents() {
+    V3 he = car_half_extents();
+    V3 core = he - v3(rl::CONVEX_MARGIN, rl::CONVEX_MARGIN, rl::CONVEX_MARGIN);
+    float mn = fminf(he.x, fminf(he.y, he.z));
+    float safe = 0.1f * mn;
+    float margin = safe < rl::CONVEX_MARGIN ? safe : rl::CONVEX_MARGIN;
+    return core + v3(margin, margin, margin);
+}
 GGL_HD V3 car_inv_inertia_local() {
-    V3 he = v3(rl::HITBOX_X, rl::HITBOX_Y, rl::HITBOX_Z) * kUU2BT / 2.f;
-    // the box stores (he - margin) and adds the margin back when asked for the extents with margin
-    V3 m = v3(rl::CONVEX_MARGIN, rl::CONVEX_MARGIN, rl::CONVEX_MARGIN);
-    he = (he - m) + m;
+    V3 he = car_box_full_extents();
     float lx = 2.f * he.x, ly = 2.f * he.y, lz = 2.f * he.z;
     V3 in = v3(rl::CAR_MASS / 12.f * (ly * ly + lz * lz), rl::CAR_MASS / 12.f * (lx * lx + lz * lz), rl::CAR_MASS / 12.f * (lx * lx + ly * ly));
     return v3(1.f / in.x, 1.f / in.y, 1.f / in.z);

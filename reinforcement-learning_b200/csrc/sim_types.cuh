@@ -150,6 +150,8 @@ struct ArenaDev {
     uint8_t terminal, slotCar[kMaxCars], _pad2;    // slotCar[s] = car index (carId-1) of players[s]
     EnvPlayer players[kMaxCars];                   // indexed by SLOT
     uint32_t rng;                                  // minstd_rand0 state (respawn slot / kickoff permutation)
+    float stepDeltaTime;                           // GameState.deltaTime of the current env step
+    uint8_t stepGoalScored, hasResetState, _pad3[2];
     // per-tick scratch
     int32_t numContacts;
     Contact contacts[kMaxContacts];

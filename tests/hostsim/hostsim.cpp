@@ -4,7 +4,7 @@
 // library (libgigaenv_cuda.so) never links or loads this; it only launches CUDA kernels built from the same headers.
 //   g++ -O2 -ffp-contract=off -shared -fPIC -I../../include hostsim.cpp -o _build/libhostsim.so
 #include "../../reinforcement-learning_b200/csrc/sim_convert.cuh"
-#include "../../reinforcement-learning_b200/csrc/env_logic.cuh"
+#include "../../reinforcement-learning_b200/csrc/env_reset.cuh"
 
 using namespace ggl;
 
@@ -66,5 +66,142 @@ void hostsim_set_controls(void* p, const ggl_arena_state* st) {
 }
 
 size_t hostsim_sizeof_arena() { return sizeof(ArenaDev); }
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------------------------
+// Host mirror of env_kernels.cuh's orchestration (same phase functions, one lane) for lock-stepping the env layer.
+struct HostEnv {
+    EnvCfg cfg;
+    WorldHost world;
+    std::vector<ArenaDev> arenas, resets;
+    std::vector<float> obs, rewards, lastRewards, table;
+    std::vector<uint8_t> masks, terminals, events;
+};
+
+static void host_write_rows(HostEnv* h, int a) {
+    ArenaDev& A = h->arenas[a];
+    for (int s = 0; s < A.numCars; s++) {
+        int row = a * h->cfg.numCars + s;
+        build_obs_row(A, h->cfg, s, h->obs.data() + (size_t)row * h->cfg.obsSize);
+        action_mask_row(A.cars[A.slotCar[s]], h->table.data(), h->masks.data() + (size_t)row * kNumActions);
+    }
+}
+
+static void host_reset_arena(HostEnv* h, int a, bool force, int setter) {
+    ArenaDev& A = h->arenas[a];
+    if (!force && A.terminal == 0) return;
+    if (setter == GGL_SETTER_INJECTED && h->resets[a].hasResetState) {
+        const ArenaDev& R = h->resets[a];
+        A.tickCount = R.tickCount; A.ball = R.ball;
+        for (int c = 0; c < A.numCars; c++) A.cars[c] = R.cars[c];
+        for (int p = 0; p < kNumPads; p++) A.pads[p] = R.pads[p];
+    } else {
+        arena_reset_kickoff(A);
+    }
+    env_after_state_set(A);
+    h->terminals[a] = 0;
+    host_write_rows(h, a);
+    for (int s = 0; s < A.numCars; s++)
+        for (int e = 0; e < 9; e++) h->events[(size_t)(a * h->cfg.numCars + s) * 9 + e] = 0;
+}
+
+extern "C" {
+
+void* hostenv_create(const ggl_envset_desc* d) {
+    HostEnv* h = new HostEnv();
+    EnvCfg& c = h->cfg;
+    memset(&c, 0, sizeof(c));
+    c.numArenas = d->num_arenas; c.playersPerTeam = d->players_per_team; c.numCars = 2 * d->players_per_team;
+    c.tickSkip = d->tick_skip; c.actionDelay = d->action_delay; c.obsKind = d->obs_kind;
+    c.obsSize = 51 + (d->obs_kind == GGL_OBS_ADVANCED ? 29 : 19) * c.numCars;
+    c.numRewards = d->num_rewards; c.numTerminals = d->num_terminals; c.stateSetter = d->state_setter;
+    for (int i = 0; i < d->num_rewards; i++) {
+        c.rewards[i].kind = d->rewards[i].kind; c.rewards[i].weight = d->rewards[i].weight;
+        for (int k = 0; k < 4; k++) c.rewards[i].params[k] = d->rewards[i].params[k];
+    }
+    for (int i = 0; i < d->num_terminals; i++) {
+        c.terminals[i].kind = d->terminals[i].kind; c.terminals[i].params[0] = d->terminals[i].params[0];
+    }
+    for (int i = 0; i < d->num_meshes; i++) world_add_cmf(h->world, d->meshes[i].data, d->meshes[i].size);
+    world_build_grid(h->world);
+    const int np = c.numArenas * c.numCars;
+    h->arenas.resize(c.numArenas); h->resets.resize(c.numArenas);
+    memset(h->arenas.data(), 0, h->arenas.size() * sizeof(ArenaDev));
+    memset(h->resets.data(), 0, h->resets.size() * sizeof(ArenaDev));
+    h->obs.assign((size_t)np * c.obsSize, 0.f); h->rewards.assign(np, 0.f); h->lastRewards.assign((size_t)c.numArenas * (c.numRewards + 1), 0.f);
+    h->masks.assign((size_t)np * kNumActions, 0); h->terminals.assign(c.numArenas, 0); h->events.assign((size_t)np * 9, 0);
+    h->table.resize(kNumActions * 8);
+    for (int i = 0; i < kNumActions; i++) action_from_index(i, h->table.data() + 8 * i);
+    for (int a = 0; a < c.numArenas; a++) {
+        ArenaDev& A = h->arenas[a];
+        A.numCars = c.numCars; A.rng = (uint32_t)(d->seed * 7919u + a * 104729u + 1u) % 2147483646u + 1u;
+        for (int i = 0; i < c.numCars; i++) {
+            CarDev& car = A.cars[i];
+            car.id = i + 1; car.team = i < c.playersPerTeam ? 0 : 1; car.basis = m3_identity();
+            car_reset_state_defaults(car); car_update_inertia(car);
+            for (int w = 0; w < 4; w++) car.w[w].ground = GROUND_NONE;
+        }
+        for (int s = 0; s < c.numCars; s++) A.slotCar[s] = (uint8_t)(d->slot_order_reversed ? c.numCars - 1 - s : s);
+        A.lastTouchCarId = -1;
+        host_reset_arena(h, a, true, GGL_SETTER_KICKOFF);
+    }
+    return h;
+}
+void hostenv_destroy(void* p) { delete (HostEnv*)p; }
+
+void hostenv_set_state(void* p, int a, const ggl_arena_state* st) { arena_phys_from_host(*st, ((HostEnv*)p)->arenas[a]); }
+void hostenv_get_state(void* p, int a, ggl_arena_state* st) { arena_phys_to_host(((HostEnv*)p)->arenas[a], *st); }
+void hostenv_set_reset_state(void* p, int a, const ggl_arena_state* st) {
+    HostEnv* h = (HostEnv*)p;
+    memset(&h->resets[a], 0, sizeof(ArenaDev));
+    arena_phys_from_host(*st, h->resets[a]);
+    h->resets[a].hasResetState = 1;
+}
+void hostenv_set_slot_order(void* p, const int32_t* ids) {
+    HostEnv* h = (HostEnv*)p;
+    for (int a = 0; a < h->cfg.numArenas; a++)
+        for (int s = 0; s < h->cfg.numCars; s++) h->arenas[a].slotCar[s] = (uint8_t)(ids[a * h->cfg.numCars + s] - 1);
+}
+
+// Reset + StepFirstHalf + StepSecondHalf (the order env_reset_kernel / env_step_kernel run)
+void hostenv_step(void* p, const int32_t* actions) {
+    HostEnv* h = (HostEnv*)p;
+    const EnvCfg& cfg = h->cfg;
+    WorldDev W = world_view(h->world);
+    ExecSerial ex;
+    for (int a = 0; a < cfg.numArenas; a++) {
+        host_reset_arena(h, a, false, cfg.stateSetter);
+        ArenaDev& A = h->arenas[a];
+        env_begin_step(A);
+        for (int t = 0; t < cfg.actionDelay; t++) arena_tick(A, W, ex);
+        env_apply_actions(A, actions + a * cfg.numCars, h->table.data());
+        for (int t = cfg.actionDelay; t < cfg.tickSkip; t++) arena_tick(A, W, ex);
+        env_after_ticks(A, cfg);
+        h->terminals[a] = A.terminal;
+        int lowSlot = 0;
+        for (int s = 1; s < A.numCars; s++)
+            if (A.cars[A.slotCar[s]].id < A.cars[A.slotCar[lowSlot]].id) lowSlot = s;
+        for (int s = 0; s < A.numCars; s++) {
+            float raw[kMaxRewards];
+            int row = a * cfg.numCars + s;
+            h->rewards[row] = env_player_reward(A, cfg, s, raw);
+            if (s == lowSlot) for (int r = 0; r < cfg.numRewards; r++) h->lastRewards[(size_t)a * cfg.numRewards + r] = raw[r];
+            for (int e = 0; e < 9; e++) h->events[(size_t)row * 9 + e] = A.players[s].events[e];
+        }
+        host_write_rows(h, a);
+        env_end_step(A);
+    }
+}
+
+void hostenv_copy_out(void* p, float* obs, uint8_t* masks, float* rewards, uint8_t* terminals, uint8_t* events, float* lastRewards) {
+    HostEnv* h = (HostEnv*)p;
+    if (obs) memcpy(obs, h->obs.data(), h->obs.size() * 4);
+    if (masks) memcpy(masks, h->masks.data(), h->masks.size());
+    if (rewards) memcpy(rewards, h->rewards.data(), h->rewards.size() * 4);
+    if (terminals) memcpy(terminals, h->terminals.data(), h->terminals.size());
+    if (events) memcpy(events, h->events.data(), h->events.size());
+    if (lastRewards) memcpy(lastRewards, h->lastRewards.data(), (size_t)h->cfg.numArenas * h->cfg.numRewards * 4);
+}
 
 }  // extern "C"

@@ -79,3 +79,79 @@ class HostSim:
         out = np.zeros((maxn, 20), np.float32)
         n = lib().hostsim_contacts(self.h, out.ctypes.data, maxn)
         return out[:n]
+
+
+class _T:
+    """numpy array posing as the torch tensor the product EnvSet exposes (.cpu().numpy())."""
+
+    def __init__(self, a):
+        self.a = a
+
+    def cpu(self):
+        return self
+
+    def numpy(self):
+        return self.a
+
+
+class HostEnvSet:
+    """Same surface as the product's EnvSet (subset used by tests/env_parity.py), backed by the host compile."""
+
+    def __init__(self, num_arenas, players_per_team, **kw):
+        L = lib()
+        L.hostenv_create.restype = C.c_void_p
+        L.hostenv_create.argtypes = [C.POINTER(abi.EnvSetDesc)]
+        for n in ("hostenv_set_state", "hostenv_get_state", "hostenv_set_reset_state"):
+            getattr(L, n).argtypes = [C.c_void_p, C.c_int, C.POINTER(abi.ArenaState)]
+        L.hostenv_set_slot_order.argtypes = [C.c_void_p, C.c_void_p]
+        L.hostenv_step.argtypes = [C.c_void_p, C.c_void_p]
+        L.hostenv_copy_out.argtypes = [C.c_void_p] * 7
+        L.hostenv_destroy.argtypes = [C.c_void_p]
+        kw.pop("device", None)
+        self.desc, self._keep = abi.make_desc(num_arenas, players_per_team, **kw)
+        self.h = L.hostenv_create(C.byref(self.desc))
+        self.num_arenas = num_arenas
+        self.num_players = num_arenas * 2 * players_per_team
+        self.obs_size = 51 + (29 if self.desc.obs_kind == abi.OBS_ADVANCED else 19) * 2 * players_per_team
+        self.num_actions = 90
+        self.num_rewards = self.desc.num_rewards
+        self.device = "cpu"
+        self._refresh()
+
+    def _refresh(self):
+        o = np.empty((self.num_players, self.obs_size), np.float32)
+        m = np.empty((self.num_players, 90), np.uint8)
+        r = np.empty(self.num_players, np.float32)
+        t = np.empty(self.num_arenas, np.uint8)
+        e = np.empty((self.num_players, 9), np.uint8)
+        lr = np.zeros((self.num_arenas, max(1, self.num_rewards)), np.float32)
+        lib().hostenv_copy_out(self.h, o.ctypes.data, m.ctypes.data, r.ctypes.data, t.ctypes.data, e.ctypes.data, lr.ctypes.data)
+        self.obs, self.action_masks, self.rewards, self.terminals, self.events, self.last_rewards = _T(o), _T(m), _T(r), _T(t), _T(e), _T(lr)
+
+    def set_state(self, a, st):
+        lib().hostenv_set_state(self.h, a, C.byref(st))
+
+    def get_state(self, a):
+        st = abi.ArenaState()
+        lib().hostenv_get_state(self.h, a, C.byref(st))
+        return st
+
+    def set_reset_state(self, a, st):
+        lib().hostenv_set_reset_state(self.h, a, C.byref(st))
+
+    def set_slot_order(self, ids):
+        ids = np.ascontiguousarray(ids, np.int32)
+        lib().hostenv_set_slot_order(self.h, ids.ctypes.data)
+
+    def step_np(self, acts):
+        acts = np.ascontiguousarray(acts, np.int32)
+        lib().hostenv_step(self.h, acts.ctypes.data)
+        self._refresh()
+
+    def sync(self):
+        pass
+
+    def close(self):
+        if self.h:
+            lib().hostenv_destroy(self.h)
+            self.h = None

@@ -1,0 +1,146 @@
+"""GPU parity of the CUDA EnvSet (through the C ABI) against the compiled reference (oracle/_ref, unmodified
+RocketSim + Bullet + RLGymCPP) on identical injected states, slot orders and actions.
+
+Tolerances (BASELINE.json north_star): masks / terminals / events bit-exact; obs and rewards 1e-4 (relative + absolute
+floor, since most obs entries are O(1) normalised quantities); physics 1e-3 uu per tick over the first 16 ticks, with
+the divergence at the end of the run reported (chaotic growth afterwards is expected and bounded here)."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+env_parity = pytest.importorskip("env_parity")
+import lockstep as ls        # noqa: E402
+import oracle_ref            # noqa: E402
+
+
+@pytest.mark.parametrize("ppt,obs_kind", [(1, 0), (2, 1), (3, 1), (2, 0)])
+def test_env_steps_match_reference(ggl, ppt, obs_kind):
+    r = env_parity.run_env_steps(ggl, num_arenas=6, ppt=ppt, steps=24, seed=10 + ppt, obs_kind=obs_kind)
+    assert r["mask_mismatch"] == 0, r
+    assert r["term_mismatch"] == 0, r
+    assert r["event_mismatch"] == 0, r
+    assert r["obs_bad"] == 0, r
+    assert r["rew"] <= 1e-4, r
+
+
+def test_all_stock_rewards_match(ggl):
+    A = ggl.abi
+    rewards = [(k, 0.5 + 0.1 * k) for k in range(22) if k not in (A.REW_GOAL, A.REW_SAVE_BOOST, A.REW_STRONG_TOUCH, A.REW_VELOCITY)]
+    rewards = rewards[:12] + [(A.REW_GOAL, 10.0, [-1.0]), (A.REW_SAVE_BOOST, 1.0, [0.5]), (A.REW_STRONG_TOUCH, 2.0, [555.5, 3611.0]),
+                              (A.REW_VELOCITY, 1.0, [1.0])]
+    r = env_parity.run_env_steps(ggl, num_arenas=4, ppt=2, steps=20, seed=5, rewards=rewards)
+    assert r["rew"] <= 2e-4 and r["mask_mismatch"] == 0 and r["obs_bad"] == 0, r
+
+
+def _scenario_states():
+    """(name, init(st), controls(t, st)) scripted scenarios on a 1v1 arena."""
+    def ball_bounce(st):
+        st.ball.pos[:] = [200.0, -300.0, 600.0]; st.ball.vel[:] = [300.0, 250.0, -100.0]; st.ball.ang_vel[:] = [1.0, -2.0, 0.5]
+
+    def hit_ball(st):
+        c = st.cars[0]
+        c.pos[:] = [0.0, -600.0, 17.0]; c.rot[:] = [0, 1, 0, -1, 0, 0, 0, 0, 1]; c.vel[:] = [0, 1000.0, 0]
+
+    def drive(t, st):
+        ls.set_controls(st, 0, throttle=1, steer=0.3 if t > 60 else 0, boost=1 if t > 30 else 0)
+        ls.set_controls(st, 1, throttle=-1, steer=-1, handbrake=1 if t > 100 else 0)
+
+    def jump_flip(t, st):
+        ls.set_controls(st, 0, throttle=1, jump=1 if (t in range(30, 34) or t in range(50, 53)) else 0, pitch=-1 if t >= 50 else 0)
+        ls.set_controls(st, 1, jump=1 if (t in range(5, 8) or t in range(40, 43)) else 0)
+
+    def aerial(t, st):
+        ls.set_controls(st, 0, throttle=1, jump=1 if t in range(5, 25) else 0, pitch=1 if t > 25 else 0, boost=1 if t > 25 else 0, roll=0.5)
+        ls.set_controls(st, 1, jump=1 if t in range(5, 25) else 0, yaw=-1, roll=-1)
+
+    def boost_hit(t, st):
+        ls.set_controls(st, 0, throttle=1, boost=1, steer=0.05)
+        ls.set_controls(st, 1, throttle=1)
+
+    return [("ball_bounce", ball_bounce, None), ("drive", None, drive), ("jump_flip", None, jump_flip), ("aerial", None, aerial),
+            ("hit_ball", hit_ball, boost_hit)]
+
+
+class _DevSim:
+    """Adapter: one-arena CUDA EnvSet behind the set_state/get_state/step surface lockstep.run_lockstep drives."""
+
+    def __init__(self, ggl):
+        self.env = ggl.EnvSet(1, 1, state_setter=ggl.abi.SETTER_INJECTED)
+
+    def set_state(self, st):
+        self.env.set_state(0, st)
+
+    def get_state(self):
+        return self.env.get_state(0)
+
+    def set_controls(self, st):
+        cur = self.env.get_state(0)
+        for i in range(cur.num_cars):
+            cur.cars[i].controls = st.cars[i].controls
+        self.env.set_state(0, cur)
+
+    def step(self, n):
+        self.env.arena_step(n)
+
+
+@pytest.mark.parametrize("name,init,ctl", _scenario_states(), ids=[s[0] for s in _scenario_states()])
+def test_physics_lockstep(ggl, name, init, ctl):
+    L = oracle_ref.lib(); L.ref_set_threads(1); L.ref_seed(7)
+    ref = oracle_ref.RefEnvSet(1, 1)
+    sim = _DevSim(ggl)
+    st = ref.get_state(0)
+    if init:
+        init(st)
+    ref.set_state(0, st); sim.set_state(st)
+    worst16, bad = ls.run_lockstep(ref, sim, 16, 2, controls_fn=ctl, stop_at=1e9, verbose=False)
+    pos16 = max(v for k, v in worst16.items() if k.endswith(".pos"))
+    assert pos16 <= 1e-3, (name, worst16)
+    worst, bad = ls.run_lockstep(ref, sim, 104, 2, controls_fn=(lambda t, s: ctl(t + 16, s)) if ctl else None, stop_at=1e9, verbose=False)
+    pos = max(v for k, v in worst.items() if k.endswith(".pos"))
+    print("divergence after 120 ticks [%s]: pos %.5f uu" % (name, pos))
+    assert pos <= 0.05, (name, pos)
+    ref.close(); sim.env.close()
+
+
+def test_set_get_state_round_trip(ggl):
+    L = oracle_ref.lib(); L.ref_set_threads(1)
+    ref = oracle_ref.RefEnvSet(2, 2)
+    env = ggl.EnvSet(2, 2)
+    for a in range(2):
+        st = ref.get_state(a)
+        env.set_state(a, st)
+        back = env.get_state(a)
+        d, bad = ls.diff_states(st, back, 4)
+        assert not bad and max(d.values()) == 0.0, (d, bad)
+    ref.close(); env.close()
+
+
+def test_action_table_matches_reference(ggl):
+    assert np.array_equal(ggl.action_table(), oracle_ref.action_table())
+
+
+def test_device_kickoff_reset_and_goal_terminal(ggl):
+    """Ball pushed into the orange goal -> NORMAL terminal, goal reward sign per team, device-side kickoff on reset."""
+    import torch
+    A = ggl.abi
+    env = ggl.EnvSet(3, 1, rewards=[(A.REW_GOAL, 1.0, [-1.0])])
+    st = env.get_state(1)
+    st.ball.pos[:] = [0.0, 5000.0, 300.0]; st.ball.vel[:] = [0.0, 3000.0, 0.0]
+    env.set_state(1, st)
+    acts = torch.full((env.num_players,), 8, dtype=torch.int32, device=env.device)
+    term = None
+    for _ in range(6):
+        env.step(acts)
+        env.sync()
+        term = env.terminals.cpu().numpy()
+        if term[1]:
+            break
+    assert term[1] == 1 and term[0] == 0 and term[2] == 0
+    rew = env.rewards.cpu().numpy().reshape(3, 2); teams = env.slot_team.cpu().numpy().reshape(3, 2)
+    assert np.all(rew[1][teams[1] == 0] == 1.0) and np.all(rew[1][teams[1] == 1] == -1.0)
+    env.step(acts); env.sync()      # Reset() consumes the terminal, kickoff on the device
+    st2 = env.get_state(1)
+    assert abs(st2.ball.pos[1]) < 50 and abs(st2.ball.pos[2] - 93.15) < 5
+    assert env.terminals.cpu().numpy()[1] == 0
+    env.close()
