@@ -17,7 +17,6 @@
 
 namespace ggl {
 
-enum { EV_GOAL = 0, EV_SAVE, EV_ASSIST, EV_SHOT, EV_SHOTPASS, EV_BUMP, EV_BUMPED, EV_DEMO, EV_DEMOED };
 
 struct RewardCfg {
     int kind;

@@ -719,6 +719,8 @@ GGL_HD void clamp_controls(Controls& k) {
 GGL_HD void car_pre_tick(ArenaDev& A, const WorldDev& W, int ci) {
     CarDev& c = A.cars[ci];
     clamp_controls(c.controls);
+    // the rigid-body flags follow isDemoed as it was on ENTRY: the tick a car respawns its body is still disabled
+    c.rbDisabled = c.isDemoed;
     if (c.isDemoed) {
         c.demoRespawnTimer = fmaxf(c.demoRespawnTimer - kTick, 0.f);
         if (c.demoRespawnTimer == 0.f) car_respawn(A, c);

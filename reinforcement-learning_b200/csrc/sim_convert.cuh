@@ -130,7 +130,8 @@ inline void arena_phys_to_host(const ArenaDev& A, ggl_arena_state& st) {
 // ---------------------------------------------------------------------------------------------- arena meshes
 struct WorldHost {
     std::vector<Tri> tris;
-    std::vector<int> cellStart, cellTris;
+    std::vector<int> cellStart, cellTris, meshStart;   // meshStart[m] = one past the last triangle of mesh m
+    int numMeshes = 0;
     int gx = 1, gy = 1, gz = 1;
     V3 gridMin = v3(0, 0, 0);
     float cellSize = 1.f;
@@ -149,13 +150,83 @@ inline bool world_add_cmf(WorldHost& W, const uint8_t* data, size_t size) {
         if (a < 0 || b < 0 || c < 0 || a >= nv || b >= nv || c >= nv) return false;
         Tri t;
         t.v0 = v3p(vert + 3 * a); t.v1 = v3p(vert + 3 * b); t.v2 = v3p(vert + 3 * c);
+        t.edgeAngle[0] = t.edgeAngle[1] = t.edgeAngle[2] = 6.283185307179586232f;      // btTriangleInfo defaults (SIMD_2_PI, flags 0)
+        t.flags = (uint32_t)W.numMeshes << TRI_MESH_SHIFT;
         W.tris.push_back(t);
     }
+    W.meshStart.push_back((int)W.tris.size());
+    W.numMeshes++;
     return true;
+}
+
+// btGenerateInternalEdgeInfo + btConnectivityProcessor::processTriangle (btInternalEdgeUtility.cpp:47-354): for every triangle,
+// every other triangle of the SAME mesh sharing exactly two vertices (by position, threshold 1e-4^2 on the squared distance)
+// defines the dihedral angle / convexity of the shared edge. The reference visits the neighbours through the mesh BVH; the
+// visiting order only matters for non-manifold edges (last neighbour wins), index order is used here.
+inline V3 tri_calc_normal(V3 a, V3 b, V3 c) { return normalized(cross(b - a, c - a)); }
+inline void world_build_edge_info(WorldHost& W) {
+    const float eqThresh = 0.0001f * 0.0001f, planarEps = 0.0001f;
+    for (int mesh = 0; mesh < W.numMeshes; mesh++) {
+        const int lo = mesh == 0 ? 0 : W.meshStart[mesh - 1], hi = W.meshStart[mesh];
+        for (int ia = lo; ia < hi; ia++) {
+            Tri& A = W.tris[ia];
+            const V3 va[3] = {A.v0, A.v1, A.v2};
+            V3 amin = vmin(va[0], vmin(va[1], va[2])), amax = vmax(va[0], vmax(va[1], va[2]));
+            for (int ib = lo; ib < hi; ib++) {
+                if (ib == ia) continue;
+                const Tri& B = W.tris[ib];
+                const V3 vb[3] = {B.v0, B.v1, B.v2};
+                V3 bmin = vmin(vb[0], vmin(vb[1], vb[2])), bmax = vmax(vb[0], vmax(vb[1], vb[2]));
+                if (bmin.x > amax.x || bmax.x < amin.x || bmin.y > amax.y || bmax.y < amin.y || bmin.z > amax.z || bmax.z < amin.z) continue;
+                if (len2(cross(vb[1] - vb[0], vb[2] - vb[0])) < eqThresh) continue;
+                if (len2(cross(va[1] - va[0], va[2] - va[0])) < eqThresh) continue;
+                int numshared = 0, sA[3] = {-1, -1, -1}, sB[3] = {-1, -1, -1};
+                bool dup = false;
+                for (int i = 0; i < 3 && !dup; i++)
+                    for (int j = 0; j < 3; j++)
+                        if (len2(va[i] - vb[j]) < eqThresh) {
+                            sA[numshared] = i; sB[numshared] = j; numshared++;
+                            if (numshared >= 3) { dup = true; break; }
+                        }
+                if (dup || numshared != 2) continue;
+                if (sA[0] == 0 && sA[1] == 2) { sA[0] = 2; sA[1] = 0; int t = sB[1]; sB[1] = sB[0]; sB[0] = t; }
+                A.flags |= TRI_HAS_INFO;
+                const int sumA = sA[0] + sA[1], otherA = 3 - sumA, otherB = 3 - (sB[0] + sB[1]);
+                V3 edge = va[sA[1]] - va[sA[0]];
+                V3 normalA = tri_calc_normal(va[0], va[1], va[2]);
+                V3 normalB = tri_calc_normal(vb[sB[1]], vb[sB[0]], vb[otherB]);
+                edge = normalized(edge);
+                V3 edgeCrossA = normalized(cross(edge, normalA));
+                if (dot(edgeCrossA, va[otherA] - va[sA[0]]) < 0.f) edgeCrossA = edgeCrossA * -1.f;
+                V3 edgeCrossB = normalized(cross(edge, normalB));
+                if (dot(edgeCrossB, vb[otherB] - vb[sB[0]]) < 0.f) edgeCrossB = edgeCrossB * -1.f;
+                float ang4 = 0.f, corrected = 0.f;
+                bool isConvex = false;
+                V3 calcEdge = cross(edgeCrossA, edgeCrossB);
+                if (!(len2(calcEdge) < planarEps)) {
+                    calcEdge = normalized(calcEdge);
+                    V3 calcNormalA = normalized(cross(calcEdge, edgeCrossA));
+                    float angle2 = edge_get_angle(calcNormalA, edgeCrossA, edgeCrossB);
+                    ang4 = kPi - angle2;
+                    isConvex = dot(normalA, edgeCrossB) < 0.f;
+                    corrected = isConvex ? ang4 : -ang4;
+                }
+                int e; V3 ev;
+                if (sumA == 1) { e = 0; ev = va[0] - va[1]; }
+                else if (sumA == 2) { e = 2; ev = va[2] - va[0]; }
+                else { e = 1; ev = va[1] - va[2]; }
+                V3 computedB = quat_rotate(quat_axis_angle(ev, -corrected), normalA);
+                if (dot(computedB, normalB) < 0.f) A.flags |= (TRI_SWAP_V0V1 << e);
+                A.edgeAngle[e] = -corrected;
+                if (isConvex) A.flags |= (TRI_CONVEX_V0V1 << e);
+            }
+        }
+    }
 }
 
 // Uniform grid (cell = 5 bt = 250 uu) over the triangles; a triangle is listed in every cell its AABB (+0.1) touches.
 inline void world_build_grid(WorldHost& W) {
+    world_build_edge_info(W);
     W.cellSize = 5.f;
     W.gridMin = v3(-4500.f * kUU2BT, -6200.f * kUU2BT, -100.f * kUU2BT);
     V3 gmax = v3(4500.f * kUU2BT, 6200.f * kUU2BT, 2200.f * kUU2BT);

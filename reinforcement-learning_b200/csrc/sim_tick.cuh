@@ -85,7 +85,7 @@ GGL_HD void phase_world(ArenaDev& A, const WorldDev& W) {
     const V3 g = v3(0, 0, rl::GRAVITY_Z * kUU2BT);
     if (A.ball.active) A.ball.force += g * (1.f / kBallInvMass);
     for (int i = 0; i < A.numCars; i++)
-        if (!A.cars[i].isDemoed) A.cars[i].force += g * (1.f / (1.f / rl::CAR_MASS));
+        if (!A.cars[i].rbDisabled) A.cars[i].force += g * (1.f / (1.f / rl::CAR_MASS));
     A.ball.vel *= powf(1.f - rl::BALL_DRAG, kTick);
     A.ball.angVel *= powf(1.f - 0.f, kTick);
     // contacts at the CURRENT transforms, then the solver
@@ -110,7 +110,7 @@ GGL_HD void phase_world(ArenaDev& A, const WorldDev& W) {
     A.ball.force = v3(0, 0, 0); A.ball.torque = v3(0, 0, 0);
     for (int i = 0; i < A.numCars; i++) {
         CarDev& c = A.cars[i];
-        if (!c.isDemoed) {
+        if (!c.rbDisabled) {
             V3 np; M3 nb;
             integrate_transform(c.pos, c.basis, c.vel, c.angVel, kTick, np, nb);
             c.pos = np; c.basis = nb;

@@ -100,6 +100,7 @@ struct CarDev {
     uint8_t team, isOnGround, hasJumped, hasDoubleJumped, hasFlipped, isFlipping, isJumping, isSupersonic;
     uint8_t isAutoFlipping, worldContactHas, isDemoed, hitValid;
     uint8_t wheelsWithContact[4];
+    uint8_t rbDisabled, _padc[3];        // rigid body has DISABLE_SIMULATION | CF_NO_CONTACT_RESPONSE this tick (Car.cpp:69-83)
     Controls controls, lastControls;
     Wheel w[4];
 };
@@ -125,6 +126,9 @@ struct Contact {
     int16_t bodyA, bodyB;    // 0 = ball, 1+c = car c, -1 = static world
     int16_t special, _pad;
 };
+
+// PlayerEventState slots (RLGymCPP Gamestates/Player.h), written by the event tracker and by the bump callback
+enum { EV_GOAL = 0, EV_SAVE, EV_ASSIST, EV_SHOT, EV_SHOTPASS, EV_BUMP, EV_BUMPED, EV_DEMO, EV_DEMOED };
 
 struct EnvPlayer {     // per players[] slot bookkeeping of the env layer (GameState / Player, RLGymCPP)
     float prevAction[8];
@@ -158,8 +162,13 @@ struct ArenaDev {
 };
 
 // ------------------------------------------------------------------ static world (shared by all arenas, read-only)
+// edgeAngle / flags = btTriangleInfo of Bullet's internal-edge utility (btTriangleInfoMap.h), generated on the host at mesh load
+enum : uint32_t { TRI_CONVEX_V0V1 = 1, TRI_CONVEX_V1V2 = 2, TRI_CONVEX_V2V0 = 4, TRI_SWAP_V0V1 = 8, TRI_SWAP_V1V2 = 16, TRI_SWAP_V2V0 = 32,
+                  TRI_HAS_INFO = 0x100, TRI_MESH_SHIFT = 16 };
 struct Tri {
     V3 v0, v1, v2;
+    float edgeAngle[3];      // V0V1, V1V2, V2V0 (2*pi = no neighbour)
+    uint32_t flags;          // TRI_* | meshIndex << TRI_MESH_SHIFT
 };
 struct WorldDev {
     const Tri* tris;       // all mesh triangles (Bullet units)

@@ -15,6 +15,7 @@
 //   RocketSim/src/Sim/Arena/Arena.cpp:218-427                                contact callbacks (car-ball, car-car, car-world, ball-world)
 #pragma once
 #include "sim_car.cuh"
+#include "sim_edge.cuh"
 
 namespace ggl {
 
@@ -182,32 +183,44 @@ GGL_HD void collide_ball_mesh(ArenaDev& A, const WorldDev& W) {
     int x0 = grid_coord(mn.x, W.gridMin.x, W.invCellSize, W.gx), x1 = grid_coord(mx.x, W.gridMin.x, W.invCellSize, W.gx);
     int y0 = grid_coord(mn.y, W.gridMin.y, W.invCellSize, W.gy), y1 = grid_coord(mx.y, W.gridMin.y, W.invCellSize, W.gy);
     int z0 = grid_coord(mn.z, W.gridMin.z, W.invCellSize, W.gz), z1 = grid_coord(mx.z, W.gridMin.z, W.invCellSize, W.gz);
-    ManifoldCtx m = manifold_begin(A);
-    int seen[16]; int nseen = 0;
+    // candidate triangles in (mesh, triangle) index order; one manifold per mesh body
+    int cand[24]; int nc = 0;
     for (int z = z0; z <= z1; z++)
         for (int y = y0; y <= y1; y++)
             for (int x = x0; x <= x1; x++) {
                 int cell = (z * W.gy + y) * W.gx + x;
                 for (int k = W.cellStart[cell]; k < W.cellStart[cell + 1]; k++) {
                     int ti = W.cellTris[k];
-                    bool dup = false;
-                    for (int s = 0; s < nseen; s++) dup |= (seen[s] == ti);
-                    if (dup) continue;
-                    V3 p, n; float depth;
-                    if (sphere_triangle(b.pos, W.tris[ti], kBallRadiusBT, kBallCBT, p, n, depth)) {
-                        if (nseen < 16) seen[nseen++] = ti;
-                        if (depth > kBallCBT) continue;
-                        Contact c;
-                        c.normal = n; c.dist = depth;
-                        V3 pA = p + n * depth;
-                        c.relA = pA - b.pos; c.relB = p;
-                        c.friction = rl::BALL_FRICTION < rl::WORLD_FRICTION ? rl::BALL_FRICTION : rl::WORLD_FRICTION;
-                        c.restitution = rl::BALL_RESTITUTION > rl::WORLD_RESTITUTION ? rl::BALL_RESTITUTION : rl::WORLD_RESTITUTION;
-                        c.bodyA = 0; c.bodyB = -1; c.special = 1; c._pad = 0;
-                        manifold_add(A, m, c, pA - b.pos);
-                    }
+                    int pos = 0; bool dup = false;
+                    while (pos < nc && cand[pos] <= ti) { dup |= cand[pos] == ti; pos++; }
+                    if (dup || nc >= 24) continue;
+                    for (int q = nc; q > pos; q--) cand[q] = cand[q - 1];
+                    cand[pos] = ti; nc++;
                 }
             }
+    int curMesh = -1;
+    ManifoldCtx m = manifold_begin(A);
+    for (int k = 0; k < nc; k++) {
+        const Tri& t = W.tris[cand[k]];
+        int mesh = (int)(t.flags >> TRI_MESH_SHIFT);
+        if (mesh != curMesh) { m = manifold_begin(A); curMesh = mesh; }
+        V3 p, n; float depth;
+        if (sphere_triangle(b.pos, t, kBallRadiusBT, kBallCBT, p, n, depth)) {
+            if (depth > kBallCBT) continue;
+            Contact c;
+            c.normal = n; c.dist = depth;
+            V3 pA = p + n * depth;
+            c.relA = pA - b.pos; c.relB = p;
+            c.friction = rl::BALL_FRICTION < rl::WORLD_FRICTION ? rl::BALL_FRICTION : rl::WORLD_FRICTION;
+            c.restitution = rl::BALL_RESTITUTION > rl::WORLD_RESTITUTION ? rl::BALL_RESTITUTION : rl::WORLD_RESTITUTION;
+            c.bodyA = 0; c.bodyB = -1; c.special = 1; c._pad = 0;
+            int row = manifold_add(A, m, c, pA - b.pos);
+            if (row < 0) continue;
+            adjust_internal_edge(t, n, p, pA, depth);
+            A.contacts[row].normal = n;
+            A.contacts[row].relB = p;
+        }
+    }
 }
 
 // car hitbox vs plane: the single deepest support vertex (perturbation iterations are off in the reference)
@@ -447,7 +460,7 @@ GGL_HDN void solve_contacts(ArenaDev& A) {
         SolverBody& s = sb[1 + i];
         const CarDev& c = A.cars[i];
         s.dv = s.dw = s.push = s.turn = v3(0, 0, 0);
-        s.active = !c.isDemoed;
+        s.active = !c.rbDisabled;
         s.invMass = 1.f / rl::CAR_MASS;
         s.invI = c.invInertiaW;
         s.vel = c.vel; s.angVel = c.angVel; s.pos = c.pos;
@@ -539,9 +552,9 @@ GGL_HDN void collide_all(ArenaDev& A, const WorldDev& W) {
         collide_ball_plane(A, v3(-1, 0, 0), v3(ex, 0, hz / 2));
     }
     for (int i = 0; i < A.numCars; i++)
-        if (!A.cars[i].isDemoed) collide_car_ball(A, i);
+        if (!A.cars[i].rbDisabled) collide_car_ball(A, i);
     for (int i = 0; i < A.numCars; i++) {
-        if (A.cars[i].isDemoed) continue;
+        if (A.cars[i].rbDisabled) continue;
         collide_car_mesh(A, W, i);
         collide_car_plane(A, i, v3(0, 0, 1), v3(0, 0, 0));
         collide_car_plane(A, i, v3(0, 0, -1), v3(0, 0, hz));
