@@ -210,6 +210,9 @@ int  ggl_envset_sync(ggl_envset* env);
 int  ggl_envset_views_get(ggl_envset* env, ggl_envset_views* out);
 int  ggl_envset_set_state(ggl_envset* env, int arena, const ggl_arena_state* host_state);
 int  ggl_envset_get_state(ggl_envset* env, int arena, ggl_arena_state* host_state);
+/* test / debug: ordered solver contact rows of `arena`'s last tick, out[max][20] floats per row (bodyA, bodyB, normal xyz,
+ * relA xyz, relB xyz, distance, friction, restitution, special); returns the row count (>= 0) or a negative ggl_status */
+int  ggl_envset_get_contacts(ggl_envset* env, int arena, float* out, int max);
 /* players[] slot order of every arena: car_ids[num_players], car_ids[arena*P + slot] = carId (1-based AddCar order)
  * occupying GameState.players[slot] (GameState.cpp:82-86). Takes effect at the next reset/step. */
 int  ggl_envset_set_slot_order(ggl_envset* env, const int32_t* h_car_ids);

@@ -48,6 +48,7 @@ def lib():
             L.ggl_envset_set_state.argtypes = [C.c_void_p, C.c_int, C.POINTER(abi.ArenaState)]
             L.ggl_envset_get_state.argtypes = [C.c_void_p, C.c_int, C.POINTER(abi.ArenaState)]
             L.ggl_envset_set_reset_state.argtypes = [C.c_void_p, C.c_int, C.POINTER(abi.ArenaState)]
+            L.ggl_envset_get_contacts.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int]
             L.ggl_envset_set_slot_order.argtypes = [C.c_void_p, C.c_void_p]
             L.ggl_arena_step.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
             L.ggl_envset_random_actions.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
@@ -202,6 +203,13 @@ class EnvSet:
         st = abi.ArenaState()
         _check(lib().ggl_envset_get_state(self.h, arena, C.byref(st)))
         return st
+
+    def get_contacts(self, arena, maxn=64):
+        out = np.zeros((maxn, 20), np.float32)
+        n = lib().ggl_envset_get_contacts(self.h, arena, out.ctypes.data, maxn)
+        if n < 0:
+            _check(n)
+        return out[:n]
 
     def set_reset_state(self, arena, st):
         _check(lib().ggl_envset_set_reset_state(self.h, arena, C.byref(st)))

@@ -252,6 +252,30 @@ extern "C" int ggl_envset_get_state(ggl_envset* e, int arena, ggl_arena_state* s
     return GGL_OK;
 }
 
+// ordered contact rows of the arena's last tick (test / debug): out[max][20] floats per row = bodyA, bodyB, normal xyz,
+// relA xyz, relB xyz, distance, friction, restitution, special; returns the row count or a negative status
+extern "C" int ggl_envset_get_contacts(ggl_envset* e, int arena, float* out, int max) {
+    ENV_CHECK(e);
+    if (!out || arena < 0 || arena >= e->cfg.numArenas) { ggl::set_error("get_contacts: bad argument"); return GGL_ERR_INVALID; }
+    GGL_CUDA(cudaSetDevice(e->device));
+    GGL_CUDA(cudaDeviceSynchronize());
+    ArenaDev* A = new ArenaDev();
+    cudaError_t err = cudaMemcpy(A, e->P.arenas + arena, sizeof(ArenaDev), cudaMemcpyDeviceToHost);
+    int n = 0;
+    if (err == cudaSuccess)
+        for (int k = 0; k < A->numContacts && n < max; k++) {
+            const Contact& c = A->contacts[k];
+            float* o = out + 20 * n++;
+            memset(o, 0, 80);
+            o[0] = c.bodyA; o[1] = c.bodyB; o[2] = c.normal.x; o[3] = c.normal.y; o[4] = c.normal.z;
+            o[5] = c.relA.x; o[6] = c.relA.y; o[7] = c.relA.z; o[8] = c.relB.x; o[9] = c.relB.y; o[10] = c.relB.z;
+            o[11] = c.dist; o[12] = c.friction; o[13] = c.restitution; o[14] = c.special;
+        }
+    delete A;
+    if (err != cudaSuccess) { ggl::set_error("get_contacts -> %s", cudaGetErrorString(err)); return GGL_ERR_CUDA; }
+    return n;
+}
+
 extern "C" int ggl_envset_set_reset_state(ggl_envset* e, int arena, const ggl_arena_state* st) {
     ENV_CHECK(e);
     if (!st || arena < 0 || arena >= e->cfg.numArenas || st->num_cars != e->cfg.numCars) { ggl::set_error("set_reset_state: bad argument"); return GGL_ERR_INVALID; }

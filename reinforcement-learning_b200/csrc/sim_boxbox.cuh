@@ -10,8 +10,16 @@
 //   RocketSim/src/Sim/Car/Car.cpp:38-41                Car::Demolish
 #pragma once
 #include "sim_world.cuh"
+#ifdef GGL_DEBUG_BOXBOX
+#include <stdio.h>
+#define GGL_DBG(...) printf(__VA_ARGS__)
+#else
+#define GGL_DBG(...)
+#endif
 
 namespace ggl {
+
+GGL_HD V3 selv(V3 a, V3 b, V3 c, int i) { return i == 0 ? a : (i == 1 ? b : c); }
 
 GGL_HD void line_closest_approach(V3 pa, V3 ua, V3 pb, V3 ub, float& alpha, float& beta) {
     V3 p = pb - pa;
@@ -142,7 +150,7 @@ GGL_HDN void box_box(V3 p1, const M3& R1, V3 A, V3 p2, const M3& R2, V3 B, BoxBo
 #undef GGL_TST
     if (!code) return;
     V3 normal;
-    if (normalR >= 0) normal = normalR < 3 ? a1c[normalR] : b1c[normalR - 3];
+    if (normalR >= 0) normal = normalR < 3 ? selv(a1c[0], a1c[1], a1c[2], normalR) : selv(b1c[0], b1c[1], b1c[2], normalR - 3);
     else normal = mul(R1, normalC);
     if (invert) normal = -normal;
     const float depth = -s;
@@ -158,42 +166,50 @@ GGL_HDN void box_box(V3 p1, const M3& R1, V3 A, V3 p2, const M3& R2, V3 B, BoxBo
             float sign = (dot(normal, b1c[j]) > 0.f) ? -1.f : 1.f;
             pb += b1c[j] * (sign * Bh[j]);
         }
-        V3 ua = a1c[(code - 7) / 3], ub = b1c[(code - 7) % 3];
+        V3 ua = selv(a1c[0], a1c[1], a1c[2], (code - 7) / 3), ub = selv(b1c[0], b1c[1], b1c[2], (code - 7) % 3);
         float alpha, beta;
         line_closest_approach(pa, ua, pb, ub, alpha, beta);
         pb += ub * beta;
         out.n = 1; out.point[0] = pb; out.depth[0] = -depth;
         return;
     }
-    // face-something contact: reference face on box a (code 1..3) or box b (4..6), incident face on the other box
-    const V3* Ra; const V3* Rb; V3 pa, pb; const float* Sa; const float* Sb;
-    if (code <= 3) { Ra = a1c; Rb = b1c; pa = p1; pb = p2; Sa = Ah; Sb = Bh; }
-    else { Ra = b1c; Rb = a1c; pa = p2; pb = p1; Sa = Bh; Sb = Ah; }
-    V3 normal2 = (code <= 3) ? normal : -normal;
-    float nr[3] = {dot(Rb[0], normal2), dot(Rb[1], normal2), dot(Rb[2], normal2)};
-    float anr[3] = {fabsf(nr[0]), fabsf(nr[1]), fabsf(nr[2])};
+    // face-something contact: reference face on box a (code 1..3) or box b (4..6), incident face on the other box.
+    // Axes / extents are picked with selects (selv/comp), never by indexing small local arrays with a run-time index:
+    // nvcc 12.9 -O3 kept the constant-indexed elements in registers and read a stale stack copy for the dynamic index.
+    const bool refA = code <= 3;
+    const V3 Ra0 = refA ? a1c[0] : b1c[0], Ra1 = refA ? a1c[1] : b1c[1], Ra2 = refA ? a1c[2] : b1c[2];
+    const V3 Rb0 = refA ? b1c[0] : a1c[0], Rb1 = refA ? b1c[1] : a1c[1], Rb2 = refA ? b1c[2] : a1c[2];
+    const V3 SaV = refA ? A : B, SbV = refA ? B : A;
+    const V3 pa = refA ? p1 : p2, pb = refA ? p2 : p1;
+    V3 normal2 = refA ? normal : -normal;
+    const V3 nrV = v3(dot(Rb0, normal2), dot(Rb1, normal2), dot(Rb2, normal2));
+    const V3 anr = vabs(nrV);
     int lanr, a1, a2;
-    if (anr[1] > anr[0]) {
-        if (anr[1] > anr[2]) { a1 = 0; lanr = 1; a2 = 2; } else { a1 = 0; a2 = 1; lanr = 2; }
+    if (anr.y > anr.x) {
+        if (anr.y > anr.z) { a1 = 0; lanr = 1; a2 = 2; } else { a1 = 0; a2 = 1; lanr = 2; }
     } else {
-        if (anr[0] > anr[2]) { lanr = 0; a1 = 1; a2 = 2; } else { a1 = 0; a2 = 1; lanr = 2; }
+        if (anr.x > anr.z) { lanr = 0; a1 = 1; a2 = 2; } else { a1 = 0; a2 = 1; lanr = 2; }
     }
+    const V3 RbL = selv(Rb0, Rb1, Rb2, lanr), RbA1 = selv(Rb0, Rb1, Rb2, a1), RbA2 = selv(Rb0, Rb1, Rb2, a2);
+    const float SbL = comp(SbV, lanr), SbA1 = comp(SbV, a1), SbA2 = comp(SbV, a2);
     V3 center;
-    if (nr[lanr] < 0.f) center = pb - pa + Rb[lanr] * Sb[lanr];
-    else center = pb - pa - Rb[lanr] * Sb[lanr];
-    int codeN = (code <= 3) ? code - 1 : code - 4, code1, code2;
+    if (comp(nrV, lanr) < 0.f) center = pb - pa + RbL * SbL;
+    else center = pb - pa - RbL * SbL;
+    int codeN = refA ? code - 1 : code - 4, code1, code2;
     if (codeN == 0) { code1 = 1; code2 = 2; } else if (codeN == 1) { code1 = 0; code2 = 2; } else { code1 = 0; code2 = 1; }
+    const V3 RaC1 = selv(Ra0, Ra1, Ra2, code1), RaC2 = selv(Ra0, Ra1, Ra2, code2);
+    const float SaN = comp(SaV, codeN);
     float quad[8];
-    float c1 = dot(center, Ra[code1]), c2 = dot(center, Ra[code2]);
-    float m11 = dot(Ra[code1], Rb[a1]), m12 = dot(Ra[code1], Rb[a2]), m21 = dot(Ra[code2], Rb[a1]), m22 = dot(Ra[code2], Rb[a2]);
+    float c1 = dot(center, RaC1), c2 = dot(center, RaC2);
+    float m11 = dot(RaC1, RbA1), m12 = dot(RaC1, RbA2), m21 = dot(RaC2, RbA1), m22 = dot(RaC2, RbA2);
     {
-        float k1 = m11 * Sb[a1], k2 = m21 * Sb[a1], k3 = m12 * Sb[a2], k4 = m22 * Sb[a2];
+        float k1 = m11 * SbA1, k2 = m21 * SbA1, k3 = m12 * SbA2, k4 = m22 * SbA2;
         quad[0] = c1 - k1 - k3; quad[1] = c2 - k2 - k4;
         quad[2] = c1 - k1 + k3; quad[3] = c2 - k2 + k4;
         quad[4] = c1 + k1 + k3; quad[5] = c2 + k2 + k4;
         quad[6] = c1 + k1 - k3; quad[7] = c2 + k2 - k4;
     }
-    float rect[2] = {Sa[code1], Sa[code2]};
+    float rect[2] = {comp(SaV, code1), comp(SaV, code2)};
     float ret[16];
     int n = intersect_rect_quad(rect, quad, ret);
     if (n < 1) return;
@@ -205,8 +221,8 @@ GGL_HDN void box_box(V3 p1, const M3& R1, V3 A, V3 p2, const M3& R2, V3 B, BoxBo
     for (int j = 0; j < n; j++) {
         float k1 = m22 * (ret[j * 2] - c1) - m12 * (ret[j * 2 + 1] - c2);
         float k2 = -m21 * (ret[j * 2] - c1) + m11 * (ret[j * 2 + 1] - c2);
-        point[cnum] = center + Rb[a1] * k1 + Rb[a2] * k2;
-        dep[cnum] = Sa[codeN] - dot(normal2, point[cnum]);
+        point[cnum] = center + RbA1 * k1 + RbA2 * k2;
+        dep[cnum] = SaN - dot(normal2, point[cnum]);
         if (dep[cnum] >= 0.f) { ret[cnum * 2] = ret[j * 2]; ret[cnum * 2 + 1] = ret[j * 2 + 1]; cnum++; }
     }
     if (cnum < 1) return;

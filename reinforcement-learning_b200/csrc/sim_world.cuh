@@ -538,8 +538,8 @@ GGL_HDN void solve_contacts(ArenaDev& A) {
 
 // ---------------------------------------------------------------------------------------------- world step
 // defined in sim_boxbox.cuh / sim_boxtri.cuh
-GGL_HD void collide_car_car(ArenaDev& A, int i, int j);
-GGL_HD void collide_car_mesh(ArenaDev& A, const WorldDev& W, int ci);
+GGL_HDN void collide_car_car(ArenaDev& A, int lo, int hi);
+GGL_HDN void collide_car_mesh(ArenaDev& A, const WorldDev& W, int ci);
 
 GGL_HDN void collide_all(ArenaDev& A, const WorldDev& W) {
     const float ex = rl::ARENA_EXTENT_X * kUU2BT, hz = rl::ARENA_HEIGHT * kUU2BT;

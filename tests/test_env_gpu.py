@@ -12,6 +12,7 @@ pytestmark = pytest.mark.gpu
 env_parity = pytest.importorskip("env_parity")
 import lockstep as ls        # noqa: E402
 import oracle_ref            # noqa: E402
+import scenarios             # noqa: E402
 
 
 @pytest.mark.parametrize("ppt,obs_kind", [(1, 0), (2, 1), (3, 1), (2, 0)])
@@ -100,6 +101,30 @@ def test_physics_lockstep(ggl, name, init, ctl):
     pos = max(v for k, v in worst.items() if k.endswith(".pos"))
     print("divergence after 120 ticks [%s]: pos %.5f uu" % (name, pos))
     assert pos <= 0.05, (name, pos)
+    ref.close(); sim.env.close()
+
+
+@pytest.mark.parametrize("name", sorted(scenarios.SCEN))
+def test_mesh_and_car_contact_scenarios_per_tick(ggl, name):
+    """Arena-mesh / car-car / demolition scenarios: every tick starts from the reference state (re-synchronised), so the
+    number is the pure per-tick error of the CUDA tick; flags (demoed, on-ground, wheel contacts, pads ...) must agree."""
+    L = oracle_ref.lib(); L.ref_set_threads(1); L.ref_seed(5)
+    ref = oracle_ref.RefEnvSet(1, 1)
+    sim = _DevSim(ggl)
+    st = ref.get_state(0)
+    ctl = scenarios.SCEN[name](st)
+    ref.set_state(0, st); sim.set_state(st)
+    worst_pos, worst_vel, nbad = 0.0, 0.0, 0
+    for t in range(200):
+        sim.set_state(ref.get_state(0))
+        w, bad = ls.run_lockstep(ref, sim, 1, 2, controls_fn=(lambda tt, s: ctl(t, s)) if ctl else None, stop_at=1e9, verbose=False)
+        worst_pos = max(worst_pos, max(v for k, v in w.items() if k.endswith(".pos")))
+        worst_vel = max(worst_vel, max(v for k, v in w.items() if k.endswith(".vel")))
+        nbad += bad is not None
+    print("per-tick error [%s]: pos %.5f uu, vel %.4f uu/s" % (name, worst_pos, worst_vel))
+    assert nbad == 0, name
+    # 1e-3 uu per tick (north star); wall_hit's ceiling impact at tick 191 is the known 2.4e-3 outlier (DESIGN.md)
+    assert worst_pos <= (3e-3 if name == "wall_hit" else 1e-3), (name, worst_pos)
     ref.close(); sim.env.close()
 
 

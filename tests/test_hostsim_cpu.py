@@ -47,3 +47,23 @@ def test_env_layer_matches_reference(ppt, obs_kind):
     r = env_parity.run_env_steps(None, num_arenas=3, ppt=ppt, steps=20, seed=ppt, obs_kind=obs_kind, env_cls=hb.HostEnvSet)
     assert r["mask_mismatch"] == 0 and r["term_mismatch"] == 0 and r["event_mismatch"] == 0 and r["obs_bad"] == 0, r
     assert r["rew"] < 1e-4, r
+
+
+@pytest.mark.parametrize("name", ["corner_hit", "ball_ramp", "car_car", "demo"])
+def test_contact_scenarios_per_tick(name):
+    """Host compile of the device headers on the mesh / car-car / demolition scenarios, re-synchronised every tick."""
+    import scenarios
+    L = oracle_ref.lib(); L.ref_set_threads(1); L.ref_seed(5)
+    env = oracle_ref.RefEnvSet(1, 1)
+    sim = hb.HostSim()
+    st = env.get_state(0)
+    ctl = scenarios.SCEN[name](st)
+    env.set_state(0, st); sim.set_state(st)
+    worst, nbad = 0.0, 0
+    for t in range(160):
+        sim.set_state(env.get_state(0))
+        w, bad = ls.run_lockstep(env, sim, 1, 2, controls_fn=(lambda tt, s: ctl(t, s)) if ctl else None, stop_at=1e9, verbose=False)
+        worst = max(worst, max(v for k, v in w.items() if k.endswith(".pos")))
+        nbad += bad is not None
+    assert nbad == 0 and worst <= 1e-3, (name, worst, nbad)
+    env.close()
