@@ -1,8 +1,12 @@
-// CUDA kernels of the rollout hot path (sm_100a). One lane group of kGroup threads owns one arena: lanes 0..P-1 run
-// the per-car phases of a tick (suspension rays, control logic) and the per-player outputs (obs row, mask row, reward)
-// in parallel; lane 0 runs the arena-serial phases (contacts, solver, bookkeeping). Groups never straddle a warp, so
-// phase boundaries are __syncwarp()s on the group's lane mask. 128 threads per block = 16 arenas per block; the grid
-// covers the arenas once (4096 arenas -> 256 blocks, ~1.7 blocks per SM on 148 SMs).
+// CUDA kernels of the rollout hot path (sm_100a).
+//
+// Mapping: one lane group of kGroup threads owns one arena; a block is ONE warp = kArenasPerBlock arenas, so that the grid
+// (4096 arenas -> 1024 blocks) spreads to ~7 warps on each of the 148 SMs in a single wave. Each arena's blob
+// ([header][cars x numCars], sim_types.cuh) is staged HBM -> shared memory with 16-byte warp-wide copies, all tick_skip
+// ticks + the env layer run out of shared memory, and the blob goes back to HBM once: one HBM round trip per env step.
+// Inside a tick, lanes 0..P-1 run the per-car phases (suspension rays, control logic) and the per-player outputs (obs row,
+// mask row, reward) in parallel; lane 0 runs the arena-serial phases (contact generation order, solver, bookkeeping);
+// pads are spread over all lanes. Groups never straddle a warp, so phase boundaries are __syncwarp()s on the group's lanes.
 #pragma once
 #include <cuda_runtime.h>
 #include "env_reset.cuh"
@@ -10,7 +14,7 @@
 namespace ggl {
 
 constexpr int kGroup = 8;
-constexpr int kBlock = 128;
+constexpr int kBlock = 32;
 constexpr int kArenasPerBlock = kBlock / kGroup;
 
 struct ExecGroup {
@@ -46,6 +50,35 @@ __device__ __forceinline__ void write_player_rows(const ArenaDev& A, const EnvCf
     P.slotTeam[row] = A.cars[A.slotCar[slot]].team;
 }
 
+// ---- blob staging: the whole warp moves each of its arenas with 16-byte accesses (512 contiguous bytes per instruction)
+extern __shared__ __align__(16) unsigned char g_arena_smem[];
+
+__device__ __forceinline__ void stage_in(const EnvCfg& cfg, const EnvDevPtrs& P, int slotBytes) {
+    const int lane = threadIdx.x, n16 = slotBytes >> 4;
+    for (int g = 0; g < kArenasPerBlock; g++) {
+        const int arena = blockIdx.x * kArenasPerBlock + g;
+        if (arena >= cfg.numArenas) break;
+        const uint4* src = reinterpret_cast<const uint4*>(P.arenas + arena);
+        uint4* dst = reinterpret_cast<uint4*>(g_arena_smem + (size_t)g * slotBytes);
+        for (int i = lane; i < n16; i += kBlock) dst[i] = __ldg(src + i);
+    }
+    __syncwarp();
+}
+__device__ __forceinline__ void stage_out(const EnvCfg& cfg, const EnvDevPtrs& P, int slotBytes) {
+    __syncwarp();
+    const int lane = threadIdx.x, n16 = slotBytes >> 4;
+    for (int g = 0; g < kArenasPerBlock; g++) {
+        const int arena = blockIdx.x * kArenasPerBlock + g;
+        if (arena >= cfg.numArenas) break;
+        uint4* dst = reinterpret_cast<uint4*>(P.arenas + arena);
+        const uint4* src = reinterpret_cast<const uint4*>(g_arena_smem + (size_t)g * slotBytes);
+        for (int i = lane; i < n16; i += kBlock) dst[i] = src[i];
+    }
+}
+__device__ __forceinline__ ArenaDev& my_arena(int slotBytes) {
+    return *reinterpret_cast<ArenaDev*>(g_arena_smem + (size_t)(threadIdx.x / kGroup) * slotBytes);
+}
+
 // EnvSet::ResetArena for arenas whose terminal flag is set (or all of them when `force`)
 __global__ void __launch_bounds__(kBlock) env_reset_kernel(EnvCfg cfg, EnvDevPtrs P, int force) {
     const int arena = blockIdx.x * kArenasPerBlock + threadIdx.x / kGroup;
@@ -58,11 +91,7 @@ __global__ void __launch_bounds__(kBlock) env_reset_kernel(EnvCfg cfg, EnvDevPtr
         if (cfg.stateSetter == GGL_SETTER_INJECTED && P.resetArenas && P.resetArenas[arena].hasResetState) {
             const ArenaDev& R = P.resetArenas[arena];
             A.tickCount = R.tickCount; A.ball = R.ball;
-            for (int c = 0; c < A.numCars; c++) {
-                Controls keep = A.cars[c].controls;
-                A.cars[c] = R.cars[c];
-                (void)keep;
-            }
+            for (int c = 0; c < A.numCars; c++) A.cars[c] = R.cars[c];
             for (int p = 0; p < kNumPads; p++) A.pads[p] = R.pads[p];
         } else {
             arena_reset_kickoff(A);
@@ -77,52 +106,61 @@ __global__ void __launch_bounds__(kBlock) env_reset_kernel(EnvCfg cfg, EnvDevPtr
     }
 }
 
-// StepFirstHalf and/or StepSecondHalf of every arena in one launch.
-__global__ void __launch_bounds__(kBlock) env_step_kernel(EnvCfg cfg, EnvDevPtrs P, const int32_t* __restrict__ actions, int doFirst, int doSecond) {
+// StepFirstHalf and/or StepSecondHalf of every arena in one launch. With doReset, arenas whose terminal flag is set are
+// reset first (EnvSet::Reset, the Learner loop order of Learner.cpp:669-793) inside the same launch.
+__global__ void __launch_bounds__(kBlock) env_step_kernel(EnvCfg cfg, EnvDevPtrs P, const int32_t* __restrict__ actions, int doFirst,
+                                                          int doSecond, int slotBytes) {
+    stage_in(cfg, P, slotBytes);
     const int arena = blockIdx.x * kArenasPerBlock + threadIdx.x / kGroup;
-    if (arena >= cfg.numArenas) return;
-    const ExecGroup ex = make_exec();
-    ArenaDev& A = P.arenas[arena];
-    const WorldDev& W = P.world;
-    if (doFirst) {
-        if (ex.lane() == 0) env_begin_step(A);
-        ex.sync();
-        for (int t = 0; t < cfg.actionDelay; t++) arena_tick(A, W, ex);
-    }
-    if (doSecond) {
-        if (ex.lane() == 0) env_apply_actions(A, actions + arena * cfg.numCars, P.actionTable);
-        ex.sync();
-        for (int t = cfg.actionDelay; t < cfg.tickSkip; t++) arena_tick(A, W, ex);
-        if (ex.lane() == 0) {
-            env_after_ticks(A, cfg);
-            P.terminals[arena] = A.terminal;
+    if (arena < cfg.numArenas) {
+        const ExecGroup ex = make_exec();
+        ArenaDev& A = my_arena(slotBytes);
+        const WorldDev& W = P.world;
+        if (doFirst) {
+            if (ex.lane() == 0) env_begin_step(A);
+            ex.sync();
+            for (int t = 0; t < cfg.actionDelay; t++) arena_tick(A, W, ex);
         }
-        ex.sync();
-        const int slot = ex.lane();
-        if (slot < A.numCars) {
-            const int row = arena * cfg.numCars + slot;
-            // saved raw rewards: the player with the lowest car id (EnvSet.cpp:235-243, shuffleRewardSampling = false)
-            int lowSlot = 0;
-            for (int s = 1; s < A.numCars; s++)
-                if (A.cars[A.slotCar[s]].id < A.cars[A.slotCar[lowSlot]].id) lowSlot = s;
-            float raw[kMaxRewards];
-            P.rewards[row] = env_player_reward(A, cfg, slot, raw);
-            if (slot == lowSlot)
-                for (int r = 0; r < cfg.numRewards; r++) P.lastRewards[(size_t)arena * cfg.numRewards + r] = raw[r];
-            write_player_rows(A, cfg, P, arena, slot);
-            for (int e = 0; e < 9; e++) P.events[(size_t)row * 9 + e] = A.players[slot].events[e];
+        if (doSecond) {
+            if (ex.lane() == 0) env_apply_actions(A, actions + arena * cfg.numCars, P.actionTable);
+            ex.sync();
+            for (int t = cfg.actionDelay; t < cfg.tickSkip; t++) arena_tick(A, W, ex);
+            if (ex.lane() == 0) {
+                env_after_ticks(A, cfg);
+                P.terminals[arena] = A.terminal;
+            }
+            ex.sync();
+            const int slot = ex.lane();
+            if (slot < A.numCars) {
+                const int row = arena * cfg.numCars + slot;
+                // saved raw rewards: the player with the lowest car id (EnvSet.cpp:235-243, shuffleRewardSampling = false)
+                int lowSlot = 0;
+                for (int s = 1; s < A.numCars; s++)
+                    if (A.cars[A.slotCar[s]].id < A.cars[A.slotCar[lowSlot]].id) lowSlot = s;
+                float raw[kMaxRewards];
+                P.rewards[row] = env_player_reward(A, cfg, slot, raw);
+                if (slot == lowSlot)
+                    for (int r = 0; r < cfg.numRewards; r++) P.lastRewards[(size_t)arena * cfg.numRewards + r] = raw[r];
+                write_player_rows(A, cfg, P, arena, slot);
+                for (int e = 0; e < 9; e++) P.events[(size_t)row * 9 + e] = A.players[slot].events[e];
+            }
+            ex.sync();
+            if (ex.lane() == 0) env_end_step(A);
         }
-        ex.sync();
-        if (ex.lane() == 0) env_end_step(A);
     }
+    stage_out(cfg, P, slotBytes);
 }
 
 // raw Arena::Step(ticks)
-__global__ void __launch_bounds__(kBlock) arena_step_kernel(EnvCfg cfg, EnvDevPtrs P, int ticks) {
+__global__ void __launch_bounds__(kBlock) arena_step_kernel(EnvCfg cfg, EnvDevPtrs P, int ticks, int slotBytes) {
+    stage_in(cfg, P, slotBytes);
     const int arena = blockIdx.x * kArenasPerBlock + threadIdx.x / kGroup;
-    if (arena >= cfg.numArenas) return;
-    const ExecGroup ex = make_exec();
-    for (int t = 0; t < ticks; t++) arena_tick(P.arenas[arena], P.world, ex);
+    if (arena < cfg.numArenas) {
+        const ExecGroup ex = make_exec();
+        ArenaDev& A = my_arena(slotBytes);
+        for (int t = 0; t < ticks; t++) arena_tick(A, P.world, ex);
+    }
+    stage_out(cfg, P, slotBytes);
 }
 
 // uniformly random mask-valid action per player (bench / smoke helper): k-th set bit of the mask row, k from a hash

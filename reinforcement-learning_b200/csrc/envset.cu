@@ -28,6 +28,8 @@ struct ggl_envset {
 namespace {
 
 int grid_for(const EnvCfg& cfg) { return (cfg.numArenas + kArenasPerBlock - 1) / kArenasPerBlock; }
+int slot_bytes(const EnvCfg& cfg) { return (int)arena_slot_bytes(cfg.numCars); }
+size_t smem_for(const EnvCfg& cfg) { return (size_t)kArenasPerBlock * slot_bytes(cfg); }
 
 int obs_size(int kind, int cars) { return 51 + (kind == GGL_OBS_ADVANCED ? 29 : 19) * cars; }
 
@@ -148,6 +150,8 @@ extern "C" int ggl_envset_create(const ggl_envset_desc* d, ggl_envset** out) {
     cudaMemset(e->P.rewards, 0, (size_t)e->numPlayers * sizeof(float));
     cudaMemset(e->P.lastRewards, 0, (size_t)c.numArenas * (c.numRewards ? c.numRewards : 1) * sizeof(float));
     GGL_CUDA(cudaStreamCreateWithFlags(&e->ownStream, cudaStreamNonBlocking));
+    GGL_CUDA(cudaFuncSetAttribute(env_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_for(e->cfg)));
+    GGL_CUDA(cudaFuncSetAttribute(arena_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_for(e->cfg)));
     // EnvSet ctor: reset every arena once (EnvSet.cpp:106-110)
     EnvCfg kc = e->cfg; kc.stateSetter = GGL_SETTER_KICKOFF;
     env_reset_kernel<<<grid_for(e->cfg), kBlock, 0, 0>>>(kc, e->P, 1);
@@ -176,27 +180,27 @@ extern "C" int ggl_envset_reset(ggl_envset* e, void* stream) {
 }
 extern "C" int ggl_envset_step_first_half(ggl_envset* e, void* stream) {
     ENV_CHECK(e);
-    env_step_kernel<<<grid_for(e->cfg), kBlock, 0, (cudaStream_t)stream>>>(e->cfg, e->P, nullptr, 1, 0);
+    env_step_kernel<<<grid_for(e->cfg), kBlock, smem_for(e->cfg), (cudaStream_t)stream>>>(e->cfg, e->P, nullptr, 1, 0, slot_bytes(e->cfg));
     GGL_LAUNCH_CHECK(); ggl::count_launch();
     return GGL_OK;
 }
 extern "C" int ggl_envset_step_second_half(ggl_envset* e, const int32_t* d_actions, void* stream) {
     ENV_CHECK(e);
     if (!d_actions) { ggl::set_error("null actions"); return GGL_ERR_INVALID; }
-    env_step_kernel<<<grid_for(e->cfg), kBlock, 0, (cudaStream_t)stream>>>(e->cfg, e->P, d_actions, 0, 1);
+    env_step_kernel<<<grid_for(e->cfg), kBlock, smem_for(e->cfg), (cudaStream_t)stream>>>(e->cfg, e->P, d_actions, 0, 1, slot_bytes(e->cfg));
     GGL_LAUNCH_CHECK(); ggl::count_launch();
     return GGL_OK;
 }
 extern "C" int ggl_envset_step(ggl_envset* e, const int32_t* d_actions, void* stream) {
     ENV_CHECK(e);
     if (!d_actions) { ggl::set_error("null actions"); return GGL_ERR_INVALID; }
-    env_step_kernel<<<grid_for(e->cfg), kBlock, 0, (cudaStream_t)stream>>>(e->cfg, e->P, d_actions, 1, 1);
+    env_step_kernel<<<grid_for(e->cfg), kBlock, smem_for(e->cfg), (cudaStream_t)stream>>>(e->cfg, e->P, d_actions, 1, 1, slot_bytes(e->cfg));
     GGL_LAUNCH_CHECK(); ggl::count_launch();
     return GGL_OK;
 }
 extern "C" int ggl_arena_step(ggl_envset* e, int ticks, void* stream) {
     ENV_CHECK(e);
-    arena_step_kernel<<<grid_for(e->cfg), kBlock, 0, (cudaStream_t)stream>>>(e->cfg, e->P, ticks);
+    arena_step_kernel<<<grid_for(e->cfg), kBlock, smem_for(e->cfg), (cudaStream_t)stream>>>(e->cfg, e->P, ticks, slot_bytes(e->cfg));
     GGL_LAUNCH_CHECK(); ggl::count_launch();
     return GGL_OK;
 }

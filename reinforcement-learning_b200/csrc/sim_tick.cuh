@@ -19,15 +19,25 @@ struct ExecSerial {
     GGL_HD void sync() const {}
 };
 
+// Boost pad table, RocketSim order: 6 big pads then 28 small ones (RLConst.h:192-253), Unreal units.
+#if defined(__CUDACC__)
+#define GGL_TABLE static __device__ __constant__
+#else
+#define GGL_TABLE static const
+#endif
+GGL_TABLE float kPadPosUU[kNumPads][3] = {
+    {-3584.f, 0.f, 73.f}, {3584.f, 0.f, 73.f}, {-3072.f, 4096.f, 73.f}, {3072.f, 4096.f, 73.f}, {-3072.f, -4096.f, 73.f}, {3072.f, -4096.f, 73.f},
+    {0.f, -4240.f, 70.f}, {-1792.f, -4184.f, 70.f}, {1792.f, -4184.f, 70.f}, {-940.f, -3308.f, 70.f}, {940.f, -3308.f, 70.f}, {0.f, -2816.f, 70.f},
+    {-3584.f, -2484.f, 70.f}, {3584.f, -2484.f, 70.f}, {-1788.f, -2300.f, 70.f}, {1788.f, -2300.f, 70.f}, {-2048.f, -1036.f, 70.f}, {0.f, -1024.f, 70.f},
+    {2048.f, -1036.f, 70.f}, {-1024.f, 0.f, 70.f}, {1024.f, 0.f, 70.f}, {-2048.f, 1036.f, 70.f}, {0.f, 1024.f, 70.f}, {2048.f, 1036.f, 70.f},
+    {-1788.f, 2300.f, 70.f}, {1788.f, 2300.f, 70.f}, {-3584.f, 2484.f, 70.f}, {3584.f, 2484.f, 70.f}, {0.f, 2816.f, 70.f}, {-940.f, 3308.f, 70.f},
+    {940.f, 3308.f, 70.f}, {-1792.f, 4184.f, 70.f}, {1792.f, 4184.f, 70.f}, {0.f, 4240.f, 70.f}};
 GGL_HD V3 pad_pos_uu(int i) {
-    // RocketSim order: 6 big pads then 28 small ones (RLConst.h:192-253)
-    const float big[6][3] = {{-3584.f, 0.f, 73.f}, {3584.f, 0.f, 73.f}, {-3072.f, 4096.f, 73.f}, {3072.f, 4096.f, 73.f}, {-3072.f, -4096.f, 73.f}, {3072.f, -4096.f, 73.f}};
-    const float sm[28][2] = {{0.f, -4240.f}, {-1792.f, -4184.f}, {1792.f, -4184.f}, {-940.f, -3308.f}, {940.f, -3308.f}, {0.f, -2816.f}, {-3584.f, -2484.f},
-                             {3584.f, -2484.f}, {-1788.f, -2300.f}, {1788.f, -2300.f}, {-2048.f, -1036.f}, {0.f, -1024.f}, {2048.f, -1036.f}, {-1024.f, 0.f},
-                             {1024.f, 0.f}, {-2048.f, 1036.f}, {0.f, 1024.f}, {2048.f, 1036.f}, {-1788.f, 2300.f}, {1788.f, 2300.f}, {-3584.f, 2484.f},
-                             {3584.f, 2484.f}, {0.f, 2816.f}, {-940.f, 3308.f}, {940.f, 3308.f}, {-1792.f, 4184.f}, {1792.f, 4184.f}, {0.f, 4240.f}};
-    if (i < 6) return v3(big[i][0], big[i][1], big[i][2]);
-    return v3(sm[i - 6][0], sm[i - 6][1], 70.f);
+#if defined(__CUDACC__) && !defined(__CUDA_ARCH__)
+    (void)i; return v3(0, 0, 0);          // host pass of nvcc: the table is device-resident; the host build of the simulator is g++
+#else
+    return v3(kPadPosUU[i][0], kPadPosUU[i][1], kPadPosUU[i][2]);
+#endif
 }
 
 // world AABB of the car's compound shape (btCompoundShape::getAabb over the child box AABB)
@@ -42,24 +52,27 @@ GGL_HD void car_aabb(const CarDev& c, V3& mn, V3& mx) {
 }
 
 // BoostPad::_CheckCollide (Sim/BoostPad/BoostPad.cpp:62-86) reached through BoostPadGrid::CheckCollision
-GGL_HD void pads_check_car(ArenaDev& A, int ci) {
-    const CarDev& car = A.cars[ci];
-    if (car.isDemoed || car.boost >= 100.f) return;
-    V3 posUU = car.pos * kBT2UU;
-    if (posUU.z > rl::PAD_CYL_HEIGHT + 250.f) return;
-    // 8 x 10 grid of 1024 uu cells, 3x3 neighbourhood of the car's cell
-    int ix = (int)(posUU.x / 1024 + 4), iy = (int)(posUU.y / 1024 + 5);
-    V3 amin, amax; bool haveAabb = false;
-    for (int p = 0; p < kNumPads; p++) {
-        V3 pp = pad_pos_uu(p);
-        int px = (int)(pp.x / 1024 + 4), py = (int)(pp.y / 1024 + 5);
+// (BoostPadGrid.cpp:5-25: 8 x 10 grid of 1024 uu cells, 3x3 neighbourhood of the car's cell), turned inside out: one pad
+// against every car in players[] slot order (the reference iterates its car set; a later car overwrites the lock), so that
+// pads can be spread over the lanes of the group.
+GGL_HD void pad_check_cars(ArenaDev& A, int p) {
+    const V3 pp = pad_pos_uu(p);
+    const int px = (int)(pp.x / 1024 + 4), py = (int)(pp.y / 1024 + 5);
+    const bool big = p < 6;
+    const V3 pbt = pp * kUU2BT;
+    PadDev& pd = A.pads[p];
+    for (int s = 0; s < A.numCars; s++) {
+        const CarDev& car = A.cars[A.slotCar[s]];
+        if (car.isDemoed || car.boost >= 100.f) continue;
+        V3 posUU = car.pos * kBT2UU;
+        if (posUU.z > rl::PAD_CYL_HEIGHT + 250.f) continue;
+        int ix = (int)(posUU.x / 1024 + 4), iy = (int)(posUU.y / 1024 + 5);
         int lx0 = ix - 1 < 0 ? 0 : ix - 1, lx1 = ix + 1 > 7 ? 7 : ix + 1, ly0 = iy - 1 < 0 ? 0 : iy - 1, ly1 = iy + 1 > 9 ? 9 : iy + 1;
         if (px < lx0 || px > lx1 || py < ly0 || py > ly1) continue;
-        const bool big = p < 6;
-        V3 pbt = pp * kUU2BT;
         bool colliding = false;
-        if (A.pads[p].prevLockedCarId == car.id) {
-            if (!haveAabb) { car_aabb(car, amin, amax); haveAabb = true; }
+        if (pd.prevLockedCarId == car.id) {
+            V3 amin, amax;
+            car_aabb(car, amin, amax);
             float boxRad = (big ? rl::PAD_BOX_RAD_BIG : rl::PAD_BOX_RAD_SMALL) * kUU2BT;
             V3 bmin = pbt - v3(boxRad, boxRad, 0), bmax = pbt + v3(boxRad, boxRad, rl::PAD_BOX_HEIGHT * kUU2BT);
             colliding = (bmax.x > amin.x && bmax.y > amin.y && bmax.z > amin.z) && (bmin.x < amax.x && bmin.y < amax.y && bmin.z < amax.z);
@@ -68,19 +81,18 @@ GGL_HD void pads_check_car(ArenaDev& A, int ci) {
             float dx = car.pos.x - pbt.x, dy = car.pos.y - pbt.y;
             if (dx * dx + dy * dy < rad * rad) colliding = fabsf(car.pos.z - pbt.z) < (rl::PAD_CYL_HEIGHT * kUU2BT);
         }
-        if (colliding) A.pads[p].curLockedCarId = car.id;
+        if (colliding) pd.curLockedCarId = car.id;
     }
 }
 
+// boost pads pre-tick (BoostPad.cpp:51-59), one pad
+GGL_HD void pad_pre_tick(PadDev& pd) {
+    if (pd.cooldown > 0.f) pd.cooldown = fmaxf(pd.cooldown - kTick, 0.f);
+    pd.isActive = (pd.cooldown == 0.f);
+    pd.curLockedCarId = 0;
+}
+
 GGL_HD void phase_world(ArenaDev& A, const WorldDev& W) {
-    // boost pads pre-tick (BoostPad.cpp:51-59)
-    if (A.numCars > 0)
-        for (int p = 0; p < kNumPads; p++) {
-            PadDev& pd = A.pads[p];
-            if (pd.cooldown > 0.f) pd.cooldown = fmaxf(pd.cooldown - kTick, 0.f);
-            pd.isActive = (pd.cooldown == 0.f);
-            pd.curLockedCarId = 0;
-        }
     // gravity on active bodies, then damping (ball only has any)
     const V3 g = v3(0, 0, rl::GRAVITY_Z * kUU2BT);
     if (A.ball.active) A.ball.force += g * (1.f / kBallInvMass);
@@ -121,8 +133,7 @@ GGL_HD void phase_world(ArenaDev& A, const WorldDev& W) {
 }
 
 GGL_HD void phase_finish(ArenaDev& A) {
-    // boost pad pickup: cars in players[] slot order (the reference iterates its car set), then pads post-tick
-    for (int s = 0; s < A.numCars; s++) pads_check_car(A, A.slotCar[s]);
+    // pads post-tick (the per-pad collision checks ran lane-parallel just before)
     if (A.numCars > 0)
         for (int p = 0; p < kNumPads; p++) {
             PadDev& pd = A.pads[p];
@@ -152,12 +163,16 @@ template <class Exec>
 GGL_HD void arena_tick(ArenaDev& A, const WorldDev& W, const Exec& ex) {
     if (ex.lane() == 0) A.ball.active = (len2(A.ball.vel) == 0.f && len2(A.ball.angVel) == 0.f) ? 0u : 1u;
     for (int c = ex.lane(); c < A.numCars; c += ex.lanes()) { A.cars[c].velSnap = A.cars[c].vel; A.cars[c].angVelSnap = A.cars[c].angVel; }
+    if (A.numCars > 0)
+        for (int p = ex.lane(); p < kNumPads; p += ex.lanes()) pad_pre_tick(A.pads[p]);
     ex.sync();
     for (int c = ex.lane(); c < A.numCars; c += ex.lanes()) car_pre_tick(A, W, c);
     ex.sync();
     if (ex.lane() == 0) phase_world(A, W);
     ex.sync();
     for (int c = ex.lane(); c < A.numCars; c += ex.lanes()) car_post_tick(A.cars[c]);
+    ex.sync();
+    for (int p = ex.lane(); p < kNumPads; p += ex.lanes()) pad_check_cars(A, p);
     ex.sync();
     if (ex.lane() == 0) phase_finish(A);
     ex.sync();

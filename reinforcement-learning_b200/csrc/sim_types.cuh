@@ -7,6 +7,7 @@
 //
 // Constants restate RocketSim/src/RLConst.h:10-437 and Sim/Car/CarConfig/CarConfig.cpp:20-86 (Octane).
 #pragma once
+#include <stddef.h>
 #include "sim_math.cuh"
 
 namespace ggl {
@@ -14,7 +15,7 @@ namespace ggl {
 constexpr int kMaxCars = 6;
 constexpr int kNumPads = 34;
 constexpr int kNumActions = 90;
-constexpr int kMaxContacts = 48;        // solver rows per arena per tick (<= 4 per manifold)
+constexpr int kMaxContacts = 24;        // solver rows per arena per tick (<= 4 per manifold); further points are dropped
 constexpr int kMaxRewards = 16;
 constexpr int kMaxTerminals = 4;
 
@@ -85,7 +86,7 @@ struct Wheel {
     int ground;   // GroundKind; GROUND_CAR0 + c for car index c
 };
 
-struct CarDev {
+struct alignas(16) CarDev {
     // rigid body (Bullet units)
     V3 pos; M3 basis; V3 vel, angVel, force, torque; M3 invInertiaW; V3 velImpulseCache;
     V3 velSnap, angVelSnap;              // velocities at the start of the pre-tick phase (read by other cars' wheels)
@@ -136,11 +137,13 @@ struct EnvPlayer {     // per players[] slot bookkeeping of the env layer (GameS
     uint8_t prevIsFlipping, prevIsOnGround, events[9], _pad;
 };
 
-struct ArenaDev {
+// Layout: [header .. contacts][cars].  cars[] is LAST so that a lane group stages only the first numCars cars of an arena in
+// shared memory (smem slot = arena_slot_bytes(numCars)); contacts[] is per-tick scratch that lives in the slot and is only
+// written back to HBM by the raw-tick kernel (tests read it through ggl_envset_get_contacts).
+struct alignas(16) ArenaDev {
     uint64_t tickCount;
     int32_t numCars, _pad0;
     BallDev ball;
-    CarDev cars[kMaxCars];
     PadDev pads[kNumPads];
     // GameEventTracker (Sim/GameEventTracker/GameEventTracker.h:78-86)
     float shotCooldown;
@@ -159,7 +162,12 @@ struct ArenaDev {
     // per-tick scratch
     int32_t numContacts;
     Contact contacts[kMaxContacts];
+    alignas(16) CarDev cars[kMaxCars];
 };
+static_assert(sizeof(CarDev) % 16 == 0, "CarDev must be a multiple of 16 bytes (vector staging)");
+static_assert(sizeof(ArenaDev) % 16 == 0, "ArenaDev must be a multiple of 16 bytes (vector staging)");
+GGL_HD size_t arena_hdr_bytes() { return offsetof(ArenaDev, cars); }
+GGL_HD size_t arena_slot_bytes(int numCars) { return offsetof(ArenaDev, cars) + (size_t)numCars * sizeof(CarDev); }
 
 // ------------------------------------------------------------------ static world (shared by all arenas, read-only)
 // edgeAngle / flags = btTriangleInfo of Bullet's internal-edge utility (btTriangleInfoMap.h), generated on the host at mesh load
