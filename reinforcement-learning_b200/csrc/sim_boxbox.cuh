@@ -294,7 +294,7 @@ GGL_HD void car_car_callback(ArenaDev& A, int i1, int i2, V3 localA, V3 localB) 
 
 // Pair (lo, hi) with lo < hi in AddCar order. The reference's manifold has body0 = the car added LATER (observed on the
 // compiled reference for 1v1/2v2/3v3: pairs come out as (2,1), (3,2), (4,2), (4,3) ...), so A = cars[hi], B = cars[lo].
-GGL_HDN void collide_car_car(ArenaDev& A, int lo, int hi) {
+GGL_HDN void collide_car_car(ArenaDev& A, ContactSink& S, int lo, int hi) {
     const int i = hi, j = lo;
     CarDev& a = A.cars[i];
     CarDev& b = A.cars[j];
@@ -310,7 +310,7 @@ GGL_HDN void collide_car_car(ArenaDev& A, int lo, int hi) {
     box_box(pa, a.basis, bg.full, pb, b.basis, bg.full, o);
     if (o.n == 0) return;
     const float cbt = car_cbt();
-    ManifoldCtx m = manifold_begin(A);
+    ManifoldCtx m = manifold_begin(S);
     for (int k = 0; k < o.n; k++) {
         if (o.depth[k] > cbt) continue;
         V3 pB = o.point[k];
@@ -320,9 +320,8 @@ GGL_HDN void collide_car_car(ArenaDev& A, int lo, int hi) {
         c.relA = pA - a.pos; c.relB = pB - b.pos;
         c.friction = rl::CARCAR_FRICTION; c.restitution = rl::CARCAR_RESTITUTION;
         c.bodyA = (int16_t)(1 + i); c.bodyB = (int16_t)(1 + j); c.special = 0; c._pad = 0;
-        V3 localA = tmul(a.basis, pA - a.pos), localB = tmul(b.basis, pB - b.pos);
-        if (manifold_add(A, m, c, localA) < 0) continue;
-        car_car_callback(A, i, j, localA, localB);
+        // the bump / demo callback of this point runs in gather_contacts (leader, solver order): it writes to BOTH cars
+        manifold_add(S, m, c, tmul(a.basis, pA - a.pos));
     }
 }
 

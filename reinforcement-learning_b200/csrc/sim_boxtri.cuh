@@ -144,7 +144,7 @@ GGL_HD bool tri_overlaps_aabb(const Tri& t, V3 mn, V3 mx) {
 }
 
 // one triangle of the (car, mesh) manifold `m`
-GGL_HDN void collide_car_tri(ArenaDev& A, ManifoldCtx& m, int ci, const Tri& t, V3 boxPos, const BoxGeom& bg, float cbt) {
+GGL_HDN void collide_car_tri(ArenaDev& A, ContactSink& S, ManifoldCtx& m, int ci, const Tri& t, V3 boxPos, const BoxGeom& bg, float cbt) {
     CarDev& car = A.cars[ci];
     // early out: hitbox fully on one side of the triangle plane, further away than the breaking threshold
     V3 tn = normalized(cross(t.v1 - t.v0, t.v2 - t.v0));
@@ -169,17 +169,17 @@ GGL_HDN void collide_car_tri(ArenaDev& A, ManifoldCtx& m, int ci, const Tri& t, 
     c.relA = pA - car.pos; c.relB = o.pointOnB;
     c.friction = rl::CARWORLD_FRICTION; c.restitution = rl::CARWORLD_RESTITUTION;
     c.bodyA = (int16_t)(1 + ci); c.bodyB = -1; c.special = 0; c._pad = 0;
-    int row = manifold_add(A, m, c, tmul(car.basis, pA - car.pos));
+    int row = manifold_add(S, m, c, tmul(car.basis, pA - car.pos));
     if (row < 0) return;
     car.worldContactHas = 1;
     car.worldContactNormal = o.normalOnB;
     V3 n = o.normalOnB, pB = o.pointOnB;
     adjust_internal_edge(t, n, pB, pA, o.distance);
-    A.contacts[row].normal = n;
-    A.contacts[row].relB = pB;
+    S.buf[row].normal = n;
+    S.buf[row].relB = pB;
 }
 
-GGL_HDN void collide_car_mesh(ArenaDev& A, const WorldDev& W, int ci) {
+GGL_HDN void collide_car_mesh(ArenaDev& A, ContactSink& S, const WorldDev& W, int ci) {
     if (W.numTris <= 0) return;
     const CarDev& car = A.cars[ci];
     const BoxGeom bg = car_box();
@@ -207,12 +207,12 @@ GGL_HDN void collide_car_mesh(ArenaDev& A, const WorldDev& W, int ci) {
                 }
             }
     int curMesh = -1;
-    ManifoldCtx m = manifold_begin(A);
+    ManifoldCtx m = manifold_begin(S);
     for (int k = 0; k < nc; k++) {
         const Tri& t = W.tris[cand[k]];
         int mesh = (int)(t.flags >> TRI_MESH_SHIFT);
-        if (mesh != curMesh) { m = manifold_begin(A); curMesh = mesh; }
-        collide_car_tri(A, m, ci, t, boxPos, bg, cbt);
+        if (mesh != curMesh) { m = manifold_begin(S); curMesh = mesh; }
+        collide_car_tri(A, S, m, ci, t, boxPos, bg, cbt);
     }
 }
 

@@ -266,10 +266,13 @@ GGL_HD void ray_cast_world(const ArenaDev& A, const WorldDev& W, int selfCar, V3
 }
 
 // ---------------------------------------------------------------------------------------------- vehicle
-GGL_HD void vehicle_first(ArenaDev& A, const WorldDev& W, int ci) {
+// updateVehicleFirst for ONE wheel: ray cast + suspension contact info (btVehicleRL.cpp:64-92,118-212), then that wheel's
+// part of calcFrictionImpulses (:313-387). Wheels are independent of each other here, so the 4 x P wheel tasks of an arena
+// are spread over the lanes of the group.
+GGL_HD void wheel_first(ArenaDev& A, const WorldDev& W, int ci, int i) {
     CarDev& c = A.cars[ci];
     const V3 up = car_up(c), right = car_right(c);
-    for (int i = 0; i < 4; i++) {
+    {
         Wheel& w = c.w[i];
         const WheelGeom g = wheel_geom(i);
         // wheel frame with LAST tick's steer angle
@@ -327,9 +330,9 @@ GGL_HD void vehicle_first(ArenaDev& A, const WorldDev& W, int ci) {
     }
     // calcFrictionImpulses (btVehicleRL.cpp:313-387) with LAST tick's engine force / brake / friction factors
     const float frictionScale = rl::CAR_MASS / 3;
-    for (int i = 0; i < 4; i++) {
+    {
         Wheel& w = c.w[i];
-        if (w.ground == GROUND_NONE) { w.impulse = v3(0, 0, 0); continue; }
+        if (w.ground == GROUND_NONE) { w.impulse = v3(0, 0, 0); return; }
         V3 axle = w.latDir;
         V3 n = w.contactNormal;
         float proj = dot(axle, n);
@@ -716,7 +719,9 @@ GGL_HD void clamp_controls(Controls& k) {
     k.pitch = fclamp(k.pitch, -1.f, 1.f); k.yaw = fclamp(k.yaw, -1.f, 1.f); k.roll = fclamp(k.roll, -1.f, 1.f);
 }
 
-GGL_HD void car_pre_tick(ArenaDev& A, const WorldDev& W, int ci) {
+// Car::_PreTickUpdate in three lane-group phases: (a) per car: controls, demolition timer / respawn; (b) per wheel:
+// wheel_first; (c) per car: everything after updateVehicleFirst.
+GGL_HD void car_pre_tick_a(ArenaDev& A, int ci) {
     CarDev& c = A.cars[ci];
     clamp_controls(c.controls);
     // the rigid-body flags follow isDemoed as it was on ENTRY: the tick a car respawns its body is still disabled
@@ -725,8 +730,11 @@ GGL_HD void car_pre_tick(ArenaDev& A, const WorldDev& W, int ci) {
         c.demoRespawnTimer = fmaxf(c.demoRespawnTimer - kTick, 0.f);
         if (c.demoRespawnTimer == 0.f) car_respawn(A, c);
     }
+}
+
+GGL_HD void car_pre_tick_c(ArenaDev& A, int ci) {
+    CarDev& c = A.cars[ci];
     if (c.isDemoed) return;
-    vehicle_first(A, W, ci);
     bool jumpPressed = c.controls.jump && !c.lastControls.jump;
     int numWheels = 0;
     for (int i = 0; i < 4; i++) {

@@ -2,7 +2,7 @@
 //
 // The tick is written as PHASES so that the lanes of the group that owns an arena can share the work:
 //   phase_cars_pre   per car   : Car::_PreTickUpdate (rays, friction, control logic, suspension, boost)
-//   phase_world      leader    : pads pre-tick, gravity, damping, contacts, solver, integration
+//   world phases     per body / leader : gravity, damping, contacts, solver, integration (see world_forces below)
 //   phase_cars_post  per car   : Car::_PostTickUpdate + _FinishPhysicsTick
 //   phase_finish     leader    : boost pad pickup, ball finish, tick counter
 // `Exec` tells a lane which cars it owns and how to synchronise the group (host build: one lane, no-op sync).
@@ -92,36 +92,29 @@ GGL_HD void pad_pre_tick(PadDev& pd) {
     pd.curLockedCarId = 0;
 }
 
-GGL_HD void phase_world(ArenaDev& A, const WorldDev& W) {
-    // gravity on active bodies, then damping (ball only has any)
+// The rigid-body part of a tick, split so that body b (0 = ball, 1 + c = car c) is handled by lane b % lanes:
+//   world_forces(b)   gravity + damping                                    per body
+//   collide_body(b)   contact generation into the body's windows           per body   (sim_world.cuh)
+//   gather_contacts   compaction to solver order + ordered callbacks       leader
+//   solve_contacts    PGS over the bodies that have rows                   leader     | body_free_velocity(b) for the others
+//   world_integrate(b) transform integration, clear forces                 per body
+GGL_HD void world_forces(ArenaDev& A, int b) {
     const V3 g = v3(0, 0, rl::GRAVITY_Z * kUU2BT);
-    if (A.ball.active) A.ball.force += g * (1.f / kBallInvMass);
-    for (int i = 0; i < A.numCars; i++)
-        if (!A.cars[i].rbDisabled) A.cars[i].force += g * (1.f / (1.f / rl::CAR_MASS));
-    A.ball.vel *= powf(1.f - rl::BALL_DRAG, kTick);
-    A.ball.angVel *= powf(1.f - 0.f, kTick);
-    // contacts at the CURRENT transforms, then the solver
-    collide_all(A, W);
-    bool ballAwake = A.ball.active != 0;
-    if (!ballAwake) {
-        for (int k = 0; k < A.numContacts; k++)
-            if (A.contacts[k].bodyB == 0) ballAwake = true;      // touched by an active car: the island wakes it up
-        if (!ballAwake) {
-            int w = 0;
-            for (int k = 0; k < A.numContacts; k++)
-                if (A.contacts[k].bodyA != 0) A.contacts[w++] = A.contacts[k];
-            A.numContacts = w;
-        }
+    if (b == 0) {
+        if (A.ball.active) A.ball.force += g * (1.f / kBallInvMass);
+        A.ball.vel *= powf(1.f - rl::BALL_DRAG, kTick);
+        A.ball.angVel *= powf(1.f - 0.f, kTick);
+    } else if (!A.cars[b - 1].rbDisabled) {
+        A.cars[b - 1].force += g * (1.f / (1.f / rl::CAR_MASS));
     }
-    uint32_t wasActive = A.ball.active;
-    A.ball.active = ballAwake ? 1u : 0u;
-    solve_contacts(A);
-    // integrate transforms with the solved velocities, clear forces
-    if (ballAwake) A.ball.pos = A.ball.pos + A.ball.vel * kTick;
-    A.ball.active = wasActive;
-    A.ball.force = v3(0, 0, 0); A.ball.torque = v3(0, 0, 0);
-    for (int i = 0; i < A.numCars; i++) {
-        CarDev& c = A.cars[i];
+}
+
+GGL_HD void world_integrate(ArenaDev& A, int b) {
+    if (b == 0) {
+        if (A.ballAwake) A.ball.pos = A.ball.pos + A.ball.vel * kTick;
+        A.ball.force = v3(0, 0, 0); A.ball.torque = v3(0, 0, 0);
+    } else {
+        CarDev& c = A.cars[b - 1];
         if (!c.rbDisabled) {
             V3 np; M3 nb;
             integrate_transform(c.pos, c.basis, c.vel, c.angVel, kTick, np, nb);
@@ -130,6 +123,15 @@ GGL_HD void phase_world(ArenaDev& A, const WorldDev& W) {
         }
         c.force = v3(0, 0, 0); c.torque = v3(0, 0, 0);
     }
+}
+
+// leader, between gather and integrate: the solver sees the ball as active when an active car touches it
+GGL_HD void world_solve(ArenaDev& A) {
+    if (A.numContacts == 0) return;
+    uint32_t wasActive = A.ball.active;
+    A.ball.active = A.ballAwake;
+    solve_contacts(A);
+    A.ball.active = wasActive;
 }
 
 GGL_HD void phase_finish(ArenaDev& A) {
@@ -166,9 +168,25 @@ GGL_HD void arena_tick(ArenaDev& A, const WorldDev& W, const Exec& ex) {
     if (A.numCars > 0)
         for (int p = ex.lane(); p < kNumPads; p += ex.lanes()) pad_pre_tick(A.pads[p]);
     ex.sync();
-    for (int c = ex.lane(); c < A.numCars; c += ex.lanes()) car_pre_tick(A, W, c);
+    for (int c = ex.lane(); c < A.numCars; c += ex.lanes()) car_pre_tick_a(A, c);
     ex.sync();
-    if (ex.lane() == 0) phase_world(A, W);
+    for (int r = ex.lane(); r < 4 * A.numCars; r += ex.lanes())
+        if (!A.cars[r >> 2].isDemoed) wheel_first(A, W, r >> 2, r & 3);
+    ex.sync();
+    for (int c = ex.lane(); c < A.numCars; c += ex.lanes()) car_pre_tick_c(A, c);
+    ex.sync();
+    const int nb = 1 + A.numCars;
+    for (int b = ex.lane(); b < nb; b += ex.lanes()) world_forces(A, b);
+    ex.sync();      // the car-ball callback reads the damped ball velocity
+    for (int b = ex.lane(); b < nb; b += ex.lanes()) collide_body(A, W, b);
+    ex.sync();
+    if (ex.lane() == 0) gather_contacts(A);
+    ex.sync();
+    if (ex.lane() == 0) world_solve(A);
+    for (int b = ex.lane(); b < nb; b += ex.lanes())
+        if (!(A.bodiesInContact & (1u << b))) body_free_velocity(A, b);
+    ex.sync();
+    for (int b = ex.lane(); b < nb; b += ex.lanes()) world_integrate(A, b);
     ex.sync();
     for (int c = ex.lane(); c < A.numCars; c += ex.lanes()) car_post_tick(A.cars[c]);
     ex.sync();

@@ -15,7 +15,7 @@ namespace ggl {
 constexpr int kMaxCars = 6;
 constexpr int kNumPads = 34;
 constexpr int kNumActions = 90;
-constexpr int kMaxContacts = 24;        // solver rows per arena per tick (<= 4 per manifold); further points are dropped
+constexpr int kMaxContacts = 32;        // solver rows per arena per tick (<= 4 per manifold); further points are dropped
 constexpr int kMaxRewards = 16;
 constexpr int kMaxTerminals = 4;
 
@@ -101,7 +101,7 @@ struct alignas(16) CarDev {
     uint8_t team, isOnGround, hasJumped, hasDoubleJumped, hasFlipped, isFlipping, isJumping, isSupersonic;
     uint8_t isAutoFlipping, worldContactHas, isDemoed, hitValid;
     uint8_t wheelsWithContact[4];
-    uint8_t rbDisabled, _padc[3];        // rigid body has DISABLE_SIMULATION | CF_NO_CONTACT_RESPONSE this tick (Car.cpp:69-83)
+    uint8_t rbDisabled, ballHitNew, _padc[2];        // rigid body has DISABLE_SIMULATION | CF_NO_CONTACT_RESPONSE this tick (Car.cpp:69-83)
     Controls controls, lastControls;
     Wheel w[4];
 };
@@ -161,6 +161,8 @@ struct alignas(16) ArenaDev {
     uint8_t stepGoalScored, hasResetState, _pad3[2];
     // per-tick scratch
     int32_t numContacts;
+    uint32_t bodiesInContact;                      // bit b: body b (0 ball, 1 + c car c) has a solver row this tick
+    uint8_t cntWorld, ballAwake, cntBall[kMaxCars], cntRest[kMaxCars], _pad4[2];
     Contact contacts[kMaxContacts];
     alignas(16) CarDev cars[kMaxCars];
 };

@@ -53,26 +53,32 @@ GGL_HD float car_cbt() {
 GGL_HD float ball_inv_inertia() { return 1.f / (0.4f * rl::BALL_MASS * kBallRadiusBT * kBallRadiusBT); }
 
 // ---------------------------------------------------------------------------------------------- contact emission
+// Where a body's contact generation writes: a private window of A.contacts (so that the lanes of a group can generate the
+// contacts of different bodies concurrently; the windows are compacted into solver order afterwards, see gather_contacts).
+struct ContactSink {
+    Contact* buf;
+    int n, cap;
+};
 struct ManifoldCtx {     // <= 4 points per body pair, rebuilt each tick
-    int first;           // index of the manifold's first row in A.contacts
+    int first;           // index of the manifold's first row in the sink
     int count;
     V3 localA[4];
 };
 
 GGL_HD float area3(V3 p, V3 q, V3 r, V3 s) { return len2(cross(p - q, s - r)); }
 
-// Adds a point to the manifold (replacement policy of btPersistentManifold::sortCachedPoints). Returns the row index.
-GGL_HD int manifold_add(ArenaDev& A, ManifoldCtx& m, const Contact& c, V3 localA) {
+// Adds a point to the manifold (replacement policy of btPersistentManifold::sortCachedPoints). Returns the row index in the sink.
+GGL_HD int manifold_add(ContactSink& S, ManifoldCtx& m, const Contact& c, V3 localA) {
     int idx;
     if (m.count < 4) {
-        if (A.numContacts >= kMaxContacts) return -1;
+        if (S.n >= S.cap) return -1;
         idx = m.count++;
-        A.numContacts++;
+        S.n++;
     } else {
         int deepest = -1;
         float maxPen = c.dist;
         for (int i = 0; i < 4; i++)
-            if (A.contacts[m.first + i].dist < maxPen) { deepest = i; maxPen = A.contacts[m.first + i].dist; }
+            if (S.buf[m.first + i].dist < maxPen) { deepest = i; maxPen = S.buf[m.first + i].dist; }
         float r0 = 0, r1 = 0, r2 = 0, r3 = 0;
         if (deepest != 0) r0 = area3(localA, m.localA[1], m.localA[2], m.localA[3]);
         if (deepest != 1) r1 = area3(localA, m.localA[0], m.localA[2], m.localA[3]);
@@ -83,16 +89,16 @@ GGL_HD int manifold_add(ArenaDev& A, ManifoldCtx& m, const Contact& c, V3 localA
         if (fabsf(r2) > best) { best = fabsf(r2); idx = 2; }
         if (fabsf(r3) > best) { best = fabsf(r3); idx = 3; }
     }
-    A.contacts[m.first + idx] = c;
+    S.buf[m.first + idx] = c;
     m.localA[idx] = localA;
     return m.first + idx;
 }
 
-GGL_HD ManifoldCtx manifold_begin(const ArenaDev& A) { ManifoldCtx m; m.first = A.numContacts; m.count = 0; return m; }
+GGL_HD ManifoldCtx manifold_begin(const ContactSink& S) { ManifoldCtx m; m.first = S.n; m.count = 0; return m; }
 
 // ---------------------------------------------------------------------------------------------- narrow phase
 // ball vs the 4 planes and the mesh; every contact is flagged special (Arena.cpp:265-273)
-GGL_HD void collide_ball_plane(ArenaDev& A, V3 n, V3 origin) {
+GGL_HD void collide_ball_plane(ArenaDev& A, ContactSink& S, V3 n, V3 origin) {
     const BallDev& b = A.ball;
     V3 vtx = (-n) * kBallRadiusBT;            // support point of the sphere towards the plane
     V3 inPlane = (b.pos - origin) + vtx;
@@ -100,7 +106,7 @@ GGL_HD void collide_ball_plane(ArenaDev& A, V3 n, V3 origin) {
     if (dist < kBallCBT) {
         V3 proj = inPlane - dist * n;
         V3 pOnB = origin + proj;
-        ManifoldCtx m = manifold_begin(A);
+        ManifoldCtx m = manifold_begin(S);
         Contact c;
         c.normal = n; c.dist = dist;
         V3 pA = pOnB + n * dist;
@@ -108,7 +114,7 @@ GGL_HD void collide_ball_plane(ArenaDev& A, V3 n, V3 origin) {
         c.friction = rl::BALL_FRICTION < rl::WORLD_FRICTION ? rl::BALL_FRICTION : rl::WORLD_FRICTION;
         c.restitution = rl::BALL_RESTITUTION > rl::WORLD_RESTITUTION ? rl::BALL_RESTITUTION : rl::WORLD_RESTITUTION;
         c.bodyA = 0; c.bodyB = -1; c.special = 1; c._pad = 0;
-        manifold_add(A, m, c, pA - b.pos);
+        manifold_add(S, m, c, pA - b.pos);
     }
 }
 
@@ -175,7 +181,7 @@ GGL_HD bool sphere_triangle(V3 centre, const Tri& t, float radius, float cbt, V3
     return false;
 }
 
-GGL_HD void collide_ball_mesh(ArenaDev& A, const WorldDev& W) {
+GGL_HD void collide_ball_mesh(ArenaDev& A, ContactSink& S, const WorldDev& W) {
     if (W.numTris <= 0) return;
     const BallDev& b = A.ball;
     float ext = kBallRadiusBT + 0.08f;
@@ -199,11 +205,11 @@ GGL_HD void collide_ball_mesh(ArenaDev& A, const WorldDev& W) {
                 }
             }
     int curMesh = -1;
-    ManifoldCtx m = manifold_begin(A);
+    ManifoldCtx m = manifold_begin(S);
     for (int k = 0; k < nc; k++) {
         const Tri& t = W.tris[cand[k]];
         int mesh = (int)(t.flags >> TRI_MESH_SHIFT);
-        if (mesh != curMesh) { m = manifold_begin(A); curMesh = mesh; }
+        if (mesh != curMesh) { m = manifold_begin(S); curMesh = mesh; }
         V3 p, n; float depth;
         if (sphere_triangle(b.pos, t, kBallRadiusBT, kBallCBT, p, n, depth)) {
             if (depth > kBallCBT) continue;
@@ -214,17 +220,17 @@ GGL_HD void collide_ball_mesh(ArenaDev& A, const WorldDev& W) {
             c.friction = rl::BALL_FRICTION < rl::WORLD_FRICTION ? rl::BALL_FRICTION : rl::WORLD_FRICTION;
             c.restitution = rl::BALL_RESTITUTION > rl::WORLD_RESTITUTION ? rl::BALL_RESTITUTION : rl::WORLD_RESTITUTION;
             c.bodyA = 0; c.bodyB = -1; c.special = 1; c._pad = 0;
-            int row = manifold_add(A, m, c, pA - b.pos);
+            int row = manifold_add(S, m, c, pA - b.pos);
             if (row < 0) continue;
             adjust_internal_edge(t, n, p, pA, depth);
-            A.contacts[row].normal = n;
-            A.contacts[row].relB = p;
+            S.buf[row].normal = n;
+            S.buf[row].relB = p;
         }
     }
 }
 
 // car hitbox vs plane: the single deepest support vertex (perturbation iterations are off in the reference)
-GGL_HD void collide_car_plane(ArenaDev& A, int ci, V3 n, V3 origin) {
+GGL_HD void collide_car_plane(ArenaDev& A, ContactSink& S, int ci, V3 n, V3 origin) {
     CarDev& car = A.cars[ci];
     const BoxGeom bg = car_box();
     V3 boxPos = car.pos + mul(car.basis, car_hitbox_offset());
@@ -235,13 +241,13 @@ GGL_HD void collide_car_plane(ArenaDev& A, int ci, V3 n, V3 origin) {
     if (dist < car_cbt()) {
         V3 pOnB = origin + (inPlane - dist * n);
         V3 pA = pOnB + n * dist;
-        ManifoldCtx m = manifold_begin(A);
+        ManifoldCtx m = manifold_begin(S);
         Contact c;
         c.normal = n; c.dist = dist;
         c.relA = pA - car.pos; c.relB = pOnB - origin;
         c.friction = rl::CARWORLD_FRICTION; c.restitution = rl::CARWORLD_RESTITUTION;
         c.bodyA = (int16_t)(1 + ci); c.bodyB = -1; c.special = 0; c._pad = 0;
-        if (manifold_add(A, m, c, tmul(car.basis, pA - car.pos)) >= 0) {
+        if (manifold_add(S, m, c, tmul(car.basis, pA - car.pos)) >= 0) {
             car.worldContactHas = 1;
             car.worldContactNormal = n;
         }
@@ -249,7 +255,7 @@ GGL_HD void collide_car_plane(ArenaDev& A, int ci, V3 n, V3 origin) {
 }
 
 // car hitbox (core box + margin) vs ball (point + radius): closest points, GJK margin convention
-GGL_HD void collide_car_ball(ArenaDev& A, int ci) {
+GGL_HD void collide_car_ball(ArenaDev& A, ContactSink& S, int ci) {
     CarDev& car = A.cars[ci];
     BallDev& ball = A.ball;
     const BoxGeom bg = car_box();
@@ -277,13 +283,13 @@ GGL_HD void collide_car_ball(ArenaDev& A, int ci) {
     V3 n = mul(car.basis, nl);
     V3 pOnB = ball.pos + n * kBallRadiusBT;
     V3 pA = pOnB + n * dist;
-    ManifoldCtx m = manifold_begin(A);
+    ManifoldCtx m = manifold_begin(S);
     Contact c;
     c.normal = n; c.dist = dist;
     c.relA = pA - car.pos; c.relB = pOnB - ball.pos;
     c.friction = rl::CARBALL_FRICTION; c.restitution = rl::CARBALL_RESTITUTION;
     c.bodyA = (int16_t)(1 + ci); c.bodyB = 0; c.special = 0; c._pad = 0;
-    if (manifold_add(A, m, c, tmul(car.basis, pA - car.pos)) < 0) return;
+    if (manifold_add(S, m, c, tmul(car.basis, pA - car.pos)) < 0) return;
 
     // Arena::_BtCallback_OnCarBallCollision (Arena.cpp:283-334)
     V3 carPosUU = car.pos * kBT2UU, carVelUU = car.vel * kBT2UU;
@@ -307,7 +313,7 @@ GGL_HD void collide_car_ball(ArenaDev& A, int ci) {
         hitDir = safe_normalized(hitDir - adj);
         V3 added = (hitDir * relSpeed) * curve_ball_extra_impulse(relSpeed) * 1.f;
         car.hitExtraVel = added;
-        ball.velImpulseCache += added * kUU2BT;
+        car.ballHitNew = 1;         // ball.velImpulseCache += added: done in car order by gather_contacts
     }
 }
 
@@ -444,8 +450,9 @@ constexpr int kMaxRows = kMaxContacts + 1;
 GGL_HDN void solve_contacts(ArenaDev& A) {
     SolverBody sb[1 + kMaxCars];
     const int nb = 1 + A.numCars;
+    const uint32_t inContact = A.bodiesInContact;      // bodies without a row integrate their velocity on their own lane
     // ball
-    {
+    if (inContact & 1u) {
         SolverBody& s = sb[0];
         s.dv = s.dw = s.push = s.turn = v3(0, 0, 0);
         s.active = (int)A.ball.active;
@@ -457,6 +464,7 @@ GGL_HDN void solve_contacts(ArenaDev& A) {
         s.extT = tmul(s.invI, A.ball.torque) * kTick;
     }
     for (int i = 0; i < A.numCars; i++) {
+        if (!(inContact & (2u << i))) continue;
         SolverBody& s = sb[1 + i];
         const CarDev& c = A.cars[i];
         s.dv = s.dw = s.push = s.turn = v3(0, 0, 0);
@@ -516,6 +524,7 @@ GGL_HDN void solve_contacts(ArenaDev& A) {
     }
     // write back
     for (int i = 0; i < nb; i++) {
+        if (!(inContact & (1u << i))) continue;
         SolverBody& s = sb[i];
         if (!s.active) continue;
         V3 v = (s.vel + s.dv) + s.extF;
@@ -538,30 +547,107 @@ GGL_HDN void solve_contacts(ArenaDev& A) {
 
 // ---------------------------------------------------------------------------------------------- world step
 // defined in sim_boxbox.cuh / sim_boxtri.cuh
-GGL_HDN void collide_car_car(ArenaDev& A, int lo, int hi);
-GGL_HDN void collide_car_mesh(ArenaDev& A, const WorldDev& W, int ci);
+GGL_HDN void collide_car_car(ArenaDev& A, ContactSink& S, int lo, int hi);
+GGL_HDN void collide_car_mesh(ArenaDev& A, ContactSink& S, const WorldDev& W, int ci);
+GGL_HD void car_car_callback(ArenaDev& A, int i1, int i2, V3 localA, V3 localB);
 
-GGL_HDN void collide_all(ArenaDev& A, const WorldDev& W) {
+// Contact windows inside A.contacts: [0,4) ball-world, [4,4+P) one car-ball row per car, then P windows of
+// (kMaxContacts-4-P)/P rows for each car's world + car-car rows. Window order = solver row order of the reference
+// (pair-cache insertion order, SURVEY 7: ball's pairs first, then each car's statics, then its car-car pairs).
+GGL_HD int contact_car_window(int numCars) { return (kMaxContacts - 4 - numCars) / numCars; }
+
+// Velocity update of a body that no contact row touches: what the solver's write-back does with zero delta impulses.
+GGL_HD void body_free_velocity(ArenaDev& A, int b) {
+    if (b == 0) {
+        if (!A.ball.active) return;
+        const float ii = ball_inv_inertia();
+        M3 invI; invI.r0 = v3(ii, 0, 0); invI.r1 = v3(0, ii, 0); invI.r2 = v3(0, 0, ii);
+        A.ball.vel = (A.ball.vel + v3(0, 0, 0)) + A.ball.force * kBallInvMass * kTick;
+        A.ball.angVel = (A.ball.angVel + v3(0, 0, 0)) + tmul(invI, A.ball.torque) * kTick;
+    } else {
+        CarDev& c = A.cars[b - 1];
+        if (c.rbDisabled) return;
+        const float invMass = 1.f / rl::CAR_MASS;
+        c.vel = (c.vel + v3(0, 0, 0)) + c.force * invMass * kTick;
+        c.angVel = (c.angVel + v3(0, 0, 0)) + tmul(c.invInertiaW, c.torque) * kTick;
+    }
+}
+
+// All contacts body `b` (0 = ball, 1 + c = car c) is the first body of, written into that body's windows.
+GGL_HDN void collide_body(ArenaDev& A, const WorldDev& W, int b) {
     const float ex = rl::ARENA_EXTENT_X * kUU2BT, hz = rl::ARENA_HEIGHT * kUU2BT;
-    A.numContacts = 0;
-    if (A.ball.active) {
-        collide_ball_mesh(A, W);
-        collide_ball_plane(A, v3(0, 0, 1), v3(0, 0, 0));
-        collide_ball_plane(A, v3(0, 0, -1), v3(0, 0, hz));
-        collide_ball_plane(A, v3(1, 0, 0), v3(-ex, 0, hz / 2));
-        collide_ball_plane(A, v3(-1, 0, 0), v3(ex, 0, hz / 2));
+    if (b == 0) {
+        ContactSink S; S.buf = A.contacts; S.n = 0; S.cap = 4;
+        if (A.ball.active) {
+            collide_ball_mesh(A, S, W);
+            collide_ball_plane(A, S, v3(0, 0, 1), v3(0, 0, 0));
+            collide_ball_plane(A, S, v3(0, 0, -1), v3(0, 0, hz));
+            collide_ball_plane(A, S, v3(1, 0, 0), v3(-ex, 0, hz / 2));
+            collide_ball_plane(A, S, v3(-1, 0, 0), v3(ex, 0, hz / 2));
+        }
+        A.cntWorld = (uint8_t)S.n;
+        return;
     }
-    for (int i = 0; i < A.numCars; i++)
-        if (!A.cars[i].rbDisabled) collide_car_ball(A, i);
-    for (int i = 0; i < A.numCars; i++) {
-        if (A.cars[i].rbDisabled) continue;
-        collide_car_mesh(A, W, i);
-        collide_car_plane(A, i, v3(0, 0, 1), v3(0, 0, 0));
-        collide_car_plane(A, i, v3(0, 0, -1), v3(0, 0, hz));
-        collide_car_plane(A, i, v3(1, 0, 0), v3(-ex, 0, hz / 2));
-        collide_car_plane(A, i, v3(-1, 0, 0), v3(ex, 0, hz / 2));
-        for (int j = i + 1; j < A.numCars; j++) collide_car_car(A, i, j);
+    const int i = b - 1, P = A.numCars, R = contact_car_window(P);
+    A.cars[i].ballHitNew = 0;
+    ContactSink SB; SB.buf = A.contacts + 4 + i; SB.n = 0; SB.cap = 1;
+    ContactSink S; S.buf = A.contacts + 4 + P + i * R; S.n = 0; S.cap = R;
+    if (!A.cars[i].rbDisabled) {
+        collide_car_ball(A, SB, i);
+        collide_car_mesh(A, S, W, i);
+        collide_car_plane(A, S, i, v3(0, 0, 1), v3(0, 0, 0));
+        collide_car_plane(A, S, i, v3(0, 0, -1), v3(0, 0, hz));
+        collide_car_plane(A, S, i, v3(1, 0, 0), v3(-ex, 0, hz / 2));
+        collide_car_plane(A, S, i, v3(-1, 0, 0), v3(ex, 0, hz / 2));
+        for (int j = i + 1; j < P; j++) collide_car_car(A, S, i, j);
     }
+    A.cntBall[i] = (uint8_t)SB.n;
+    A.cntRest[i] = (uint8_t)S.n;
+}
+
+// Leader: compacts the windows into solver order, runs the order-dependent contact callbacks (ball extra impulse in car
+// order, car-car bump/demo logic per point), the ball wake-up rule, and marks the bodies that have a row.
+GGL_HDN void gather_contacts(ArenaDev& A) {
+    const int P = A.numCars, R = contact_car_window(P);
+    int n = A.cntWorld;
+    for (int i = 0; i < P; i++)
+        if (A.cntBall[i]) {
+            if (n != 4 + i) A.contacts[n] = A.contacts[4 + i];
+            n++;
+            if (A.cars[i].ballHitNew) A.ball.velImpulseCache += A.cars[i].hitExtraVel * kUU2BT;
+        }
+    for (int i = 0; i < P; i++)
+        for (int k = 0; k < A.cntRest[i]; k++) {
+            const int src = 4 + P + i * R + k;
+            if (n != src) A.contacts[n] = A.contacts[src];
+            const Contact& c = A.contacts[n];
+            n++;
+            if (c.bodyA > 0 && c.bodyB > 0) {
+                const CarDev& a = A.cars[c.bodyA - 1];
+                const CarDev& b = A.cars[c.bodyB - 1];
+                car_car_callback(A, c.bodyA - 1, c.bodyB - 1, tmul(a.basis, c.relA), tmul(b.basis, c.relB));
+            }
+        }
+    A.numContacts = n;
+    bool ballAwake = A.ball.active != 0;
+    if (!ballAwake) {
+        for (int k = 0; k < n; k++)
+            if (A.contacts[k].bodyB == 0) ballAwake = true;      // touched by an active car: the island wakes it up
+        if (!ballAwake) {
+            int w = 0;
+            for (int k = 0; k < n; k++)
+                if (A.contacts[k].bodyA != 0) A.contacts[w++] = A.contacts[k];
+            A.numContacts = w;
+        }
+    }
+    A.ballAwake = ballAwake ? 1 : 0;
+    uint32_t mask = 0;
+    for (int k = 0; k < A.numContacts; k++) {
+        const Contact& c = A.contacts[k];
+        mask |= 1u << c.bodyA;
+        if (c.bodyB >= 0) mask |= 1u << c.bodyB;
+    }
+    A.bodiesInContact = mask;
 }
 
 }  // namespace ggl
