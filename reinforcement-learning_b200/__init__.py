@@ -12,7 +12,7 @@ import numpy as np
 from . import abi
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libgigaenv_cuda.so")
+LIB_PATH = os.environ.get("GGL_LIB_PATH") or os.path.join(_HERE, "libgigaenv_cuda.so")   # GGL_LIB_PATH: profiling build
 _lib = None
 
 

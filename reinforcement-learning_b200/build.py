@@ -27,6 +27,20 @@ def _stale(src, obj, extra_deps):
     return any(os.path.getmtime(d) > t for d in [src] + extra_deps)
 
 
+def build_prof():
+    """Profiling variant (per-phase cycle counters in the tick, tools/phase_profile.py): libgigaenv_cuda_prof.so."""
+    nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+    out = os.path.join(HERE, "libgigaenv_cuda_prof.so")
+    os.makedirs(OBJ, exist_ok=True)
+    objs = []
+    for name, extra in SOURCES.items():
+        obj = os.path.join(OBJ, name.replace(".cu", ".prof.o"))
+        subprocess.check_call([nvcc] + COMMON + extra + ["-DGGL_PHASE_TIMING", "-c", os.path.join(CSRC, name), "-o", obj])
+        objs.append(obj)
+    subprocess.check_call([nvcc, "-shared", "-o", out] + ARCH + objs + ["-lcudart"])
+    return out
+
+
 def build(verbose=False, force=False):
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
     os.makedirs(OBJ, exist_ok=True)
@@ -59,4 +73,7 @@ def build(verbose=False, force=False):
 
 
 if __name__ == "__main__":
-    print(build(verbose="-v" in sys.argv, force="-f" in sys.argv))
+    if "--prof" in sys.argv:
+        print(build_prof())
+    else:
+        print(build(verbose="-v" in sys.argv, force="-f" in sys.argv))

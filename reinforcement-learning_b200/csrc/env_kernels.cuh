@@ -13,12 +13,21 @@
 
 namespace ggl {
 
+#ifndef GGL_KBLOCK
+#define GGL_KBLOCK 32
+#endif
+#ifndef GGL_MINBLOCKS
+#define GGL_MINBLOCKS 1
+#endif
 constexpr int kGroup = 8;
-constexpr int kBlock = 32;
+constexpr int kBlock = GGL_KBLOCK;
 constexpr int kArenasPerBlock = kBlock / kGroup;
 
 struct ExecGroup {
     int lane_, mask_;
+#if defined(GGL_PHASE_TIMING)
+    int arena_;
+#endif
     __device__ __forceinline__ int lane() const { return lane_; }
     __device__ __forceinline__ int lanes() const { return kGroup; }
     __device__ __forceinline__ void sync() const { __syncwarp(mask_); }
@@ -38,6 +47,9 @@ __device__ __forceinline__ ExecGroup make_exec() {
     ex.lane_ = threadIdx.x % kGroup;
     int base = (threadIdx.x % 32) / kGroup * kGroup;
     ex.mask_ = (int)(((1u << kGroup) - 1u) << base);
+#if defined(GGL_PHASE_TIMING)
+    ex.arena_ = blockIdx.x * kArenasPerBlock + threadIdx.x / kGroup;
+#endif
     return ex;
 }
 
@@ -108,23 +120,39 @@ __global__ void __launch_bounds__(kBlock) env_reset_kernel(EnvCfg cfg, EnvDevPtr
 
 // StepFirstHalf and/or StepSecondHalf of every arena in one launch. With doReset, arenas whose terminal flag is set are
 // reset first (EnvSet::Reset, the Learner loop order of Learner.cpp:669-793) inside the same launch.
-__global__ void __launch_bounds__(kBlock) env_step_kernel(EnvCfg cfg, EnvDevPtrs P, const int32_t* __restrict__ actions, int doFirst,
+__global__ void __launch_bounds__(kBlock, GGL_MINBLOCKS) env_step_kernel(EnvCfg cfg, EnvDevPtrs P, const int32_t* __restrict__ actions, int doFirst,
                                                           int doSecond, int slotBytes) {
+    GGL_PH_BEGIN();
     stage_in(cfg, P, slotBytes);
     const int arena = blockIdx.x * kArenasPerBlock + threadIdx.x / kGroup;
     if (arena < cfg.numArenas) {
         const ExecGroup ex = make_exec();
         ArenaDev& A = my_arena(slotBytes);
         const WorldDev& W = P.world;
+        GGL_PH(13);
+        // ONE tick loop (a single inlined copy of arena_tick keeps the kernel's code half the size, which matters at ~7 warps
+        // per SM that all sit in different places of it): the parsed actions take effect at tick `actionDelay`.
+        const int tBegin = doFirst ? 0 : cfg.actionDelay, tEnd = doSecond ? cfg.tickSkip : cfg.actionDelay;
         if (doFirst) {
             if (ex.lane() == 0) env_begin_step(A);
             ex.sync();
-            for (int t = 0; t < cfg.actionDelay; t++) arena_tick(A, W, ex);
+        }
+        bool applied = !doSecond;
+#pragma unroll 1
+        for (int t = tBegin; t < tEnd; t++) {
+            if (!applied && t == cfg.actionDelay) {
+                if (ex.lane() == 0) env_apply_actions(A, actions + arena * cfg.numCars, P.actionTable);
+                ex.sync();
+                applied = true;
+            }
+            arena_tick(A, W, ex);
         }
         if (doSecond) {
-            if (ex.lane() == 0) env_apply_actions(A, actions + arena * cfg.numCars, P.actionTable);
-            ex.sync();
-            for (int t = cfg.actionDelay; t < cfg.tickSkip; t++) arena_tick(A, W, ex);
+            if (!applied) {      // actionDelay == tickSkip: nothing left to tick after the actions are parsed
+                if (ex.lane() == 0) env_apply_actions(A, actions + arena * cfg.numCars, P.actionTable);
+                ex.sync();
+            }
+            GGL_PH_RESET();
             if (ex.lane() == 0) {
                 env_after_ticks(A, cfg);
                 P.terminals[arena] = A.terminal;
@@ -146,6 +174,7 @@ __global__ void __launch_bounds__(kBlock) env_step_kernel(EnvCfg cfg, EnvDevPtrs
             }
             ex.sync();
             if (ex.lane() == 0) env_end_step(A);
+            GGL_PH(12);
         }
     }
     stage_out(cfg, P, slotBytes);

@@ -344,6 +344,39 @@ extern "C" int ggl_envset_step_host(ggl_envset* e, const int32_t* h_actions, flo
     return GGL_OK;
 }
 
+// profiling build only (-DGGL_PHASE_TIMING): per-phase SM cycles summed over arena leaders; zeros in the product library
+extern "C" int ggl_debug_phase_cycles(uint64_t* out16, int reset) {
+    if (!out16) return GGL_ERR_INVALID;
+    memset(out16, 0, 16 * sizeof(uint64_t));
+#if defined(GGL_PHASE_TIMING)
+    GGL_CUDA(cudaDeviceSynchronize());
+    GGL_CUDA(cudaMemcpyFromSymbol(out16, g_phase_cycles, 16 * sizeof(uint64_t)));
+    if (reset) { uint64_t z[16] = {}; GGL_CUDA(cudaMemcpyToSymbol(g_phase_cycles, z, sizeof(z))); }
+    return 1;
+#else
+    (void)reset;
+    return 0;
+#endif
+}
+
+// profiling build only: per-arena phase cycles of the first `n` (<= 8192) arenas, out[n][16]
+extern "C" int ggl_debug_arena_phase_cycles(uint64_t* out, int n, int reset) {
+#if defined(GGL_PHASE_TIMING)
+    if (!out || n < 1 || n > 8192) return GGL_ERR_INVALID;
+    GGL_CUDA(cudaDeviceSynchronize());
+    GGL_CUDA(cudaMemcpyFromSymbol(out, g_arena_phase_cycles, (size_t)n * 16 * sizeof(uint64_t)));
+    if (reset) {
+        void* p = nullptr;
+        GGL_CUDA(cudaGetSymbolAddress(&p, g_arena_phase_cycles));
+        GGL_CUDA(cudaMemset(p, 0, sizeof(uint64_t) * 8192 * 16));
+    }
+    return 1;
+#else
+    (void)out; (void)n; (void)reset;
+    return 0;
+#endif
+}
+
 // sizes of the C structs (the ctypes mirror in abi.py is checked against these)
 extern "C" size_t ggl_abi_sizeof(int which) {
     switch (which) {

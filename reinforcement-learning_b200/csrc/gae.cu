@@ -12,9 +12,11 @@
 // Both recurrences are first-order linear, x_i = a_i * x_{i+1} + b_i, so a span of elements is the affine
 // map (A, B) and spans compose associatively.  The kernel is a decoupled-look-back chained scan running from
 // the END of the stream: tiles of 4096 elements are handed out through an atomic ticket in scan order (so a
-// tile's predecessors are always already running), each tile reads its 9 B/element once through coalesced
-// streaming loads into padded shared memory, scans with warp shuffles, publishes its aggregate, resolves its
-// carry-in from predecessor tiles, and writes 12 B/element once.  Algorithmic traffic = 21 B/element — the
+// tile's predecessors are always already running; the next ticket is requested while the current tile is processed), each
+// tile reads its 9 B/element once through coalesced streaming loads (held in registers while the integer chain
+// resolves, then transposed through padded shared memory), scans with warp shuffles, publishes its aggregate as a
+// self-validating 16-byte record, resolves its carry-in with 128-tile look-back windows (one global round trip per
+// window), and writes 12 B/element once.  Algorithmic traffic = 21 B/element — the
 // HBM roofline of this path.  The truncation rank is obtained in the same pass as
 // K - (suffix count of TRUNCATED entries), a second (integer) chain with single-word status records.
 //
@@ -76,33 +78,169 @@ struct GaeParams {
     // workspace
     GaeHeader* hdr;
     unsigned long long* cnt_status;   // [tiles]  status<<62 | count
-    unsigned int* val_flag;           // [tiles]  0 none, 1 aggregate, 2 inclusive
-    float4* val_agg;                  // [tiles]
-    float4* val_inc;                  // [tiles]
+    ulonglong2* val_rec;              // [tiles]  self-validating (advantage, return) records, see enc_agg / enc_inc
     int num_tiles;
 };
 
 __device__ __forceinline__ int pidx(int i) { return i + (i >> 5); }
 
-__device__ __forceinline__ unsigned long long ld_relaxed_u64(const unsigned long long* p) {
+__device__ __forceinline__ unsigned long long ld_volatile_u64(const unsigned long long* p) {
     unsigned long long v;
-    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
     return v;
 }
-__device__ __forceinline__ void st_relaxed_u64(unsigned long long* p, unsigned long long v) {
-    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+__device__ __forceinline__ void st_volatile_u64(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
-__device__ __forceinline__ unsigned int ld_acquire_u32(const unsigned int* p) {
-    unsigned int v;
-    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+__device__ __forceinline__ ulonglong2 ld_volatile_rec(const ulonglong2* p) {
+    ulonglong2 v;
+    asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(p) : "memory");
     return v;
 }
-__device__ __forceinline__ void st_release_u32(unsigned int* p, unsigned int v) {
-    asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+__device__ __forceinline__ void st_volatile_rec(ulonglong2* p, ulonglong2 v) {
+    asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(p), "l"(v.x), "l"(v.y) : "memory");
 }
 
 constexpr unsigned long long ST_AGG = 1ull << 62;
 constexpr unsigned long long ST_INC = 2ull << 62;
+
+// Look-back records of the (advantage, return) chain. One record = two 64-bit words, word0 = (Aa | Ba<<32) for the
+// advantage recurrence and word1 = (Ar | Br<<32) for the return recurrence. The multiplier A of a span is a product of
+// gamma*lambda*nd >= 0, so its sign bit is free: an AGGREGATE word carries A with the sign bit set (never 0), an
+// INCLUSIVE word carries 0xFFFFFFFF in the A half (B = the finished prefix value), and an all-zero word means "not
+// published yet". Each 64-bit half is written atomically, so a record validates itself: one global round trip per
+// look-back window instead of flag-then-data.
+constexpr unsigned int REC_INC = 0xFFFFFFFFu;
+#ifndef GAE_LB_K0
+#define GAE_LB_K0 1
+#endif
+#ifndef GAE_LB_K
+#define GAE_LB_K 1
+#endif
+#ifndef GAE_SLEEP_NS
+#define GAE_SLEEP_NS 100
+#endif
+constexpr int LB_K0 = GAE_LB_K0;              // records per lane in the first (nearest) look-back window
+constexpr int LB_K = GAE_LB_K;                // records per lane in the deeper windows (128 tiles per poll)
+constexpr int LB_BIG = 1 << 20;
+
+__device__ __forceinline__ ulonglong2 enc_agg(const Lin2& m) {
+    ulonglong2 w;
+    w.x = (unsigned long long)(__float_as_uint(m.Aa) | 0x80000000u) | ((unsigned long long)__float_as_uint(m.Ba) << 32);
+    w.y = (unsigned long long)(__float_as_uint(m.Ar) | 0x80000000u) | ((unsigned long long)__float_as_uint(m.Br) << 32);
+    return w;
+}
+__device__ __forceinline__ ulonglong2 enc_inc(float adv, float ret) {
+    ulonglong2 w;
+    w.x = (unsigned long long)REC_INC | ((unsigned long long)__float_as_uint(adv) << 32);
+    w.y = (unsigned long long)REC_INC | ((unsigned long long)__float_as_uint(ret) << 32);
+    return w;
+}
+// 0 = not ready (or torn between two states), 1 = aggregate, 2 = inclusive
+__device__ __forceinline__ int rec_state(const ulonglong2& w) {
+    if (w.x == 0ull || w.y == 0ull) return 0;
+    const bool i0 = (unsigned int)w.x == REC_INC, i1 = (unsigned int)w.y == REC_INC;
+    if (i0 != i1) return 0;
+    return i0 ? 2 : 1;
+}
+__device__ __forceinline__ Lin2 rec_decode(const ulonglong2& w, int state) {
+    Lin2 m;
+    m.Aa = (state == 2) ? 0.f : __uint_as_float((unsigned int)w.x & 0x7FFFFFFFu);
+    m.Ba = __uint_as_float((unsigned int)(w.x >> 32));
+    m.Ar = (state == 2) ? 0.f : __uint_as_float((unsigned int)w.y & 0x7FFFFFFFu);
+    m.Br = __uint_as_float((unsigned int)(w.y >> 32));
+    return m;
+}
+
+// One look-back window of K records per lane starting at tile `win` and going down; composes the records up to the first
+// INCLUSIVE one into `acc` (valid on lane 0) and returns true when it found one. Spins (with a short back-off, so that
+// ~600 polling warps do not eat the L2 bandwidth the streaming loads need) while a record it needs is unpublished.
+template <int K>
+__device__ __forceinline__ bool lb_vals_window(const ulonglong2* rec, int win, int lane, Lin2& acc) {
+    for (;;) {
+        ulonglong2 w[K];
+        int st[K];
+        int my_inc = LB_BIG, my_none = LB_BIG;
+#pragma unroll
+        for (int j = 0; j < K; j++) {
+            const int q = win - (lane * K + j);
+            if (q >= 0) w[j] = ld_volatile_rec(rec + q);
+            else { w[j].x = (unsigned long long)REC_INC; w[j].y = (unsigned long long)REC_INC; }   // before the stream end: x = 0
+        }
+#pragma unroll
+        for (int j = K - 1; j >= 0; j--) {
+            st[j] = rec_state(w[j]);
+            if (st[j] == 2) my_inc = lane * K + j;
+            if (st[j] == 0) my_none = lane * K + j;
+        }
+        const int first_inc = __reduce_min_sync(0xffffffffu, my_inc);
+        const int first_none = __reduce_min_sync(0xffffffffu, my_none);
+        if (first_none < first_inc) { __nanosleep(GAE_SLEEP_NS); continue; }
+        Lin2 c = lin_identity();
+#pragma unroll
+        for (int j = 0; j < K; j++)
+            if (lane * K + j <= first_inc) c = compose(c, rec_decode(w[j], st[j]));
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const Lin2 o = shfl_down_lin(c, off);
+            if (lane + off < 32) c = compose(c, o);
+        }
+        acc = compose(acc, c);
+        return first_inc < LB_BIG;
+    }
+}
+
+// warp 0: carry-in (advantage, return) of tile t from the tiles before it in scan order (valid on lane 0). The nearest
+// 32*LB_K0 tiles are polled first (they are the ones still being computed); deeper windows are 32*LB_K wide.
+__device__ __forceinline__ void lookback_vals(const ulonglong2* rec, int t, int lane, float& adv_in, float& ret_in) {
+    Lin2 acc = lin_identity();
+    int win = t - 1;
+    if (!lb_vals_window<LB_K0>(rec, win, lane, acc)) {
+        win -= 32 * LB_K0;
+        while (!lb_vals_window<LB_K>(rec, win, lane, acc)) win -= 32 * LB_K;
+    }
+    adv_in = acc.Ba;
+    ret_in = acc.Br;
+}
+
+template <int K>
+__device__ __forceinline__ bool lb_count_window(const unsigned long long* status, int win, int lane, int& acc) {
+    for (;;) {
+        unsigned long long s[K];
+        int my_inc = LB_BIG, my_none = LB_BIG;
+#pragma unroll
+        for (int j = 0; j < K; j++) {
+            const int q = win - (lane * K + j);
+            s[j] = (q >= 0) ? ld_volatile_u64(status + q) : ST_INC;
+        }
+#pragma unroll
+        for (int j = K - 1; j >= 0; j--) {
+            const unsigned int stt = (unsigned int)(s[j] >> 62);
+            if (stt == 2u) my_inc = lane * K + j;
+            if (stt == 0u) my_none = lane * K + j;
+        }
+        const int first_inc = __reduce_min_sync(0xffffffffu, my_inc);
+        const int first_none = __reduce_min_sync(0xffffffffu, my_none);
+        if (first_none < first_inc) { __nanosleep(GAE_SLEEP_NS); continue; }
+        int contrib = 0;
+#pragma unroll
+        for (int j = 0; j < K; j++)
+            if (lane * K + j <= first_inc) contrib += (int)(unsigned int)(s[j] & 0xffffffffull);
+        acc += __reduce_add_sync(0xffffffffu, contrib);
+        return first_inc < LB_BIG;
+    }
+}
+
+// warp 0: number of TRUNCATED entries in the tiles before t in scan order (valid on every lane)
+__device__ __forceinline__ int lookback_count(const unsigned long long* status, int t, int lane) {
+    int acc = 0;
+    int win = t - 1;
+    if (!lb_count_window<LB_K0>(status, win, lane, acc)) {
+        win -= 32 * LB_K0;
+        while (!lb_count_window<LB_K>(status, win, lane, acc)) win -= 32 * LB_K;
+    }
+    return acc;
+}
 
 template <bool HAS_TRUNC, bool NORM, bool CLIP>
 __global__ void __launch_bounds__(GAE_THREADS, 4) gae_scan_kernel(GaeParams p) {
@@ -110,7 +248,6 @@ __global__ void __launch_bounds__(GAE_THREADS, 4) gae_scan_kernel(GaeParams p) {
     float* s_r = reinterpret_cast<float*>(smem_raw);                 // rewards -> advantages
     float* s_v = s_r + (GAE_TILE + GAE_PAD + 4);                     // values (+1 lookahead) -> returns
     float* s_o = s_v + (GAE_TILE + GAE_PAD + 4);                     // b_adv -> target values
-    uint4* s_t = reinterpret_cast<uint4*>(s_o + (GAE_TILE + GAE_PAD + 4));   // terminals, 16 per thread
 
     __shared__ int s_tile;
     __shared__ Lin2 s_warp[GAE_WARPS];
@@ -124,22 +261,25 @@ __global__ void __launch_bounds__(GAE_THREADS, 4) gae_scan_kernel(GaeParams p) {
     const int warp = tid >> 5;
     const float g = p.gamma, gl = p.gamma_lambda;
 
+    if (tid == 0) s_tile = (int)atomicAdd(&p.hdr->tile_ticket, 1u);
+    __syncthreads();
     for (;;) {
-        if (tid == 0) s_tile = (int)atomicAdd(&p.hdr->tile_ticket, 1u);
-        __syncthreads();
         const int t = s_tile;
         if (t >= p.num_tiles) break;
         const long long base = (long long)(p.num_tiles - 1 - t) * GAE_TILE;
+        // the NEXT ticket is requested now and consumed at the bottom of the loop: its round trip hides behind this tile
+        unsigned int next_ticket = 0;
+        if (tid == 0) next_ticket = atomicAdd(&p.hdr->tile_ticket, 1u);
 
-        // ---- coalesced streaming loads into padded shared memory ----
+        // ---- coalesced streaming loads, issued up front into registers (they stay in flight during the count chain) ----
+        float4 r4[GAE_ITEMS / 4], v4[GAE_ITEMS / 4];
 #pragma unroll
         for (int c = 0; c < GAE_ITEMS / 4; c++) {
             const int li = (c * GAE_THREADS + tid) * 4;
             const long long gi = base + li;
-            float4 r4, v4;
             if (gi + 3 < p.L) {
-                r4 = __ldcs(reinterpret_cast<const float4*>(p.rews + gi));
-                v4 = __ldcs(reinterpret_cast<const float4*>(p.vals + gi));
+                r4[c] = __ldcs(reinterpret_cast<const float4*>(p.rews + gi));
+                v4[c] = __ldcs(reinterpret_cast<const float4*>(p.vals + gi));
             } else {
                 float rr[4], vv[4];
 #pragma unroll
@@ -148,16 +288,14 @@ __global__ void __launch_bounds__(GAE_THREADS, 4) gae_scan_kernel(GaeParams p) {
                     rr[e] = ok ? p.rews[gi + e] : 0.f;
                     vv[e] = ok ? p.vals[gi + e] : 0.f;
                 }
-                r4 = make_float4(rr[0], rr[1], rr[2], rr[3]);
-                v4 = make_float4(vv[0], vv[1], vv[2], vv[3]);
+                r4[c] = make_float4(rr[0], rr[1], rr[2], rr[3]);
+                v4[c] = make_float4(vv[0], vv[1], vv[2], vv[3]);
             }
-            const int pi = pidx(li);
-            s_r[pi] = r4.x; s_r[pi + 1] = r4.y; s_r[pi + 2] = r4.z; s_r[pi + 3] = r4.w;
-            s_v[pi] = v4.x; s_v[pi + 1] = v4.y; s_v[pi + 2] = v4.z; s_v[pi + 3] = v4.w;
         }
+        // every thread owns GAE_ITEMS consecutive elements; the HIGHEST thread id comes first in scan order
+        uint4 tw;
         {
             const long long gi = base + (long long)tid * 16;
-            uint4 tw;
             if (gi + 15 < p.L) {
                 tw = __ldcs(reinterpret_cast<const uint4*>(p.terms + gi));
             } else {
@@ -166,16 +304,12 @@ __global__ void __launch_bounds__(GAE_THREADS, 4) gae_scan_kernel(GaeParams p) {
                     if (gi + e < p.L) w[e >> 2] |= (unsigned int)(unsigned char)p.terms[gi + e] << (8 * (e & 3));
                 tw = make_uint4(w[0], w[1], w[2], w[3]);
             }
-            s_t[tid] = tw;
         }
+        float v_look = 0.f;
         if (tid == 0) {
             const long long gi = base + GAE_TILE;
-            s_v[pidx(GAE_TILE)] = (gi < p.L) ? p.vals[gi] : 0.f;
+            v_look = (gi < p.L) ? p.vals[gi] : 0.f;
         }
-        __syncthreads();
-
-        // every thread owns GAE_ITEMS consecutive elements; the HIGHEST thread id comes first in scan order
-        const uint4 tw = s_t[tid];
         const unsigned int tword[4] = {tw.x, tw.y, tw.z, tw.w};
 
         // ---- chain 1 (integer): suffix count of TRUNCATED entries -> truncValPreds rank ----
@@ -183,7 +317,12 @@ __global__ void __launch_bounds__(GAE_THREADS, 4) gae_scan_kernel(GaeParams p) {
         if (HAS_TRUNC) {
             int c_loc = 0;
 #pragma unroll
-            for (int j = 0; j < 16; j++) c_loc += (((tword[j >> 2] >> (8 * (j & 3))) & 0xffu) == 2u);
+            for (int j = 0; j < 4; j++) {
+                // bytes equal to 2: (x ^ 0x02020202) has a zero byte there
+                const unsigned int x = tword[j] ^ 0x02020202u;
+                const unsigned int z = ~(((x & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | x | 0x7F7F7F7Fu);   // 0x80 in every zero byte of x
+                c_loc += __popc(z);
+            }
             int c = c_loc;
 #pragma unroll
             for (int off = 1; off < 32; off <<= 1) {
@@ -201,33 +340,27 @@ __global__ void __launch_bounds__(GAE_THREADS, 4) gae_scan_kernel(GaeParams p) {
             if (warp == 0) {
                 int acc = 0;
                 if (t > 0) {
-                    if (lane == 0) st_relaxed_u64(&p.cnt_status[t], ST_AGG | (unsigned long long)(unsigned int)total);
-                    int win = t - 1;
-                    for (;;) {
-                        const int q = win - lane;
-                        unsigned long long s = (q >= 0) ? ld_relaxed_u64(&p.cnt_status[q]) : ST_INC;
-                        const unsigned int st = (unsigned int)(s >> 62);
-                        const unsigned int inc_mask = __ballot_sync(0xffffffffu, st == 2u);
-                        const unsigned int none_mask = __ballot_sync(0xffffffffu, st == 0u);
-                        const int first_inc = inc_mask ? (__ffs(inc_mask) - 1) : 32;
-                        const unsigned int relevant = (first_inc >= 31) ? 0xffffffffu : ((2u << first_inc) - 1u);
-                        if (none_mask & relevant) continue;
-                        int contrib = (lane <= first_inc) ? (int)(unsigned int)(s & 0xffffffffull) : 0;
-#pragma unroll
-                        for (int off = 16; off > 0; off >>= 1) contrib += __shfl_xor_sync(0xffffffffu, contrib, off);
-                        acc += contrib;
-                        if (first_inc < 32) break;
-                        win -= 32;
-                    }
+                    if (lane == 0) st_volatile_u64(&p.cnt_status[t], ST_AGG | (unsigned long long)(unsigned int)total);
+                    acc = lookback_count(p.cnt_status, t, lane);
                 }
                 if (lane == 0) {
-                    st_relaxed_u64(&p.cnt_status[t], ST_INC | (unsigned long long)(unsigned int)(acc + total));
+                    st_volatile_u64(&p.cnt_status[t], ST_INC | (unsigned long long)(unsigned int)(acc + total));
                     s_cnt_in = acc;
                 }
             }
             __syncthreads();
             cnt_before = s_cnt_in + wcarry + (c - c_loc);
         }
+
+        // ---- transpose through padded shared memory ----
+#pragma unroll
+        for (int c = 0; c < GAE_ITEMS / 4; c++) {
+            const int pi = pidx((c * GAE_THREADS + tid) * 4);
+            s_r[pi] = r4[c].x; s_r[pi + 1] = r4[c].y; s_r[pi + 2] = r4[c].z; s_r[pi + 3] = r4[c].w;
+            s_v[pi] = v4[c].x; s_v[pi + 1] = v4[c].y; s_v[pi + 2] = v4[c].z; s_v[pi + 3] = v4[c].w;
+        }
+        if (tid == 0) s_v[pidx(GAE_TILE)] = v_look;
+        __syncthreads();
 
         // ---- per-thread pass 1: build (a, b) of every element and the thread's affine map ----
         Lin2 loc = lin_identity();
@@ -288,52 +421,18 @@ __global__ void __launch_bounds__(GAE_THREADS, 4) gae_scan_kernel(GaeParams p) {
 
         // ---- chain 2 (float): carry-in of (advantage, return) from the tiles after this one ----
         if (warp == 0) {
-            Lin2 acc = lin_identity();
-            bool resolved = (t == 0);
+            float adv_in = 0.f, ret_in = 0.f;
             if (t > 0) {
-                if (lane == 0) {
-                    __stcg(&p.val_agg[t], make_float4(tile_agg.Aa, tile_agg.Ba, tile_agg.Ar, tile_agg.Br));
-                    st_release_u32(&p.val_flag[t], 1u);
-                }
-                int win = t - 1;
-                for (;;) {
-                    const int q = win - lane;
-                    const unsigned int f = (q >= 0) ? ld_acquire_u32(&p.val_flag[q]) : 2u;
-                    const unsigned int inc_mask = __ballot_sync(0xffffffffu, f == 2u);
-                    const unsigned int none_mask = __ballot_sync(0xffffffffu, f == 0u);
-                    const int first_inc = inc_mask ? (__ffs(inc_mask) - 1) : 32;
-                    const unsigned int relevant = (first_inc >= 31) ? 0xffffffffu : ((2u << first_inc) - 1u);
-                    if (none_mask & relevant) continue;
-                    Lin2 c = lin_identity();
-                    if (lane <= first_inc) {
-                        if (q < 0) {
-                            c = Lin2{0.f, 0.f, 0.f, 0.f};
-                        } else {
-                            const float4 d = __ldcg((f == 2u) ? &p.val_inc[q] : &p.val_agg[q]);
-                            c = Lin2{d.x, d.y, d.z, d.w};
-                        }
-                    }
-#pragma unroll
-                    for (int off = 1; off < 32; off <<= 1) {
-                        const Lin2 o = shfl_down_lin(c, off);
-                        if (lane + off < 32) c = compose(c, o);
-                    }
-                    acc = compose(acc, c);   // valid on lane 0
-                    if (first_inc < 32) { resolved = true; break; }
-                    win -= 32;
-                }
+                if (lane == 0) st_volatile_rec(&p.val_rec[t], enc_agg(tile_agg));
+                lookback_vals(p.val_rec, t, lane, adv_in, ret_in);
             }
             if (lane == 0) {
-                const float adv_in = (t == 0) ? 0.f : acc.Ba;
-                const float ret_in = (t == 0) ? 0.f : acc.Br;
                 const float adv_out = tile_agg.Aa * adv_in + tile_agg.Ba;
                 const float ret_out = tile_agg.Ar * ret_in + tile_agg.Br;
-                __stcg(&p.val_inc[t], make_float4(0.f, adv_out, 0.f, ret_out));
-                st_release_u32(&p.val_flag[t], 2u);
+                st_volatile_rec(&p.val_rec[t], enc_inc(adv_out, ret_out));
                 s_x_in[0] = adv_in;
                 s_x_in[1] = ret_in;
             }
-            (void)resolved;
         }
         __syncthreads();
 
@@ -388,15 +487,15 @@ __global__ void __launch_bounds__(GAE_THREADS, 4) gae_scan_kernel(GaeParams p) {
                 b += __shfl_xor_sync(0xffffffffu, b, off);
             }
             if (lane == 0) { s_red[0][warp] = a; s_red[1][warp] = b; }
-            __syncthreads();
-            if (tid == 0) {
-                double ta = 0, tb = 0;
-                for (int w = 0; w < GAE_WARPS; w++) { ta += s_red[0][w]; tb += s_red[1][w]; }
-                atomicAdd(&p.hdr->sum_abs, ta);
-                atomicAdd(&p.hdr->sum_abs_clipped, tb);
-            }
         }
-        __syncthreads();   // shared tiles are reused by the next ticket
+        if (tid == 0) s_tile = (int)next_ticket;
+        __syncthreads();   // shared tiles are reused by the next ticket; s_tile / s_red are visible
+        if (NORM && tid == 0) {
+            double ta = 0, tb = 0;
+            for (int w = 0; w < GAE_WARPS; w++) { ta += s_red[0][w]; tb += s_red[1][w]; }
+            atomicAdd(&p.hdr->sum_abs, ta);
+            atomicAdd(&p.hdr->sum_abs_clipped, tb);
+        }
     }
 
     // ---- the last CTA to leave finalises the scalars (GAE.cpp:196-207) ----
@@ -417,28 +516,26 @@ __global__ void __launch_bounds__(GAE_THREADS, 4) gae_scan_kernel(GaeParams p) {
             if (p.out_trunc_count) {
                 int n = -1;
                 if (HAS_TRUNC && p.num_tiles > 0)
-                    n = (int)(unsigned int)(ld_relaxed_u64(&p.cnt_status[p.num_tiles - 1]) & 0xffffffffull);
+                    n = (int)(unsigned int)(ld_volatile_u64(&p.cnt_status[p.num_tiles - 1]) & 0xffffffffull);
                 *p.out_trunc_count = n;
             }
         }
     }
 }
 
-constexpr size_t gae_smem_bytes() { return 3 * (size_t)(GAE_TILE + GAE_PAD + 4) * sizeof(float) + GAE_TILE; }
+constexpr size_t gae_smem_bytes() { return 3 * (size_t)(GAE_TILE + GAE_PAD + 4) * sizeof(float); }
 
 size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 struct WsLayout {
-    size_t off_cnt, off_flag, off_agg, off_inc, total;
+    size_t off_cnt, off_rec, total;
 };
 WsLayout ws_layout(long long L) {
     const size_t tiles = (size_t)((L + GAE_TILE - 1) / GAE_TILE);
     WsLayout w;
     size_t o = align_up(sizeof(GaeHeader), 16);
     w.off_cnt = o;  o += align_up(tiles * sizeof(unsigned long long), 16);
-    w.off_flag = o; o += align_up(tiles * sizeof(unsigned int), 16);
-    w.off_agg = o;  o += tiles * sizeof(float4);
-    w.off_inc = o;  o += tiles * sizeof(float4);
+    w.off_rec = o;  o += tiles * sizeof(ulonglong2);
     w.total = align_up(o, 256);
     return w;
 }
@@ -475,6 +572,9 @@ extern "C" int ggl_gae_compute(const float* d_rews, const int8_t* d_terminals, c
                                void* d_workspace, void* stream) {
     cudaStream_t s = (cudaStream_t)stream;
     if (L < 0 || K < 0) { ggl::set_error("ggl_gae_compute: negative size"); return GGL_ERR_INVALID; }
+    if (!(gamma >= 0.f) || !(lambda >= 0.f)) {   // the look-back records keep their state in the sign bit of gamma*lambda products
+        ggl::set_error("ggl_gae_compute: gamma and lambda must be >= 0"); return GGL_ERR_INVALID;
+    }
     if (L == 0) {   // GAE.cpp:14-20
         if (d_out_clip_portion) GGL_CUDA(cudaMemsetAsync(d_out_clip_portion, 0, sizeof(float), s));
         return GGL_OK;
@@ -487,7 +587,7 @@ extern "C" int ggl_gae_compute(const float* d_rews, const int8_t* d_terminals, c
         ggl::set_error("ggl_gae_compute: buffers must be 16-byte aligned"); return GGL_ERR_INVALID;
     }
     const WsLayout w = ws_layout(L);
-    GGL_CUDA(cudaMemsetAsync(d_workspace, 0, w.off_agg, s));   // header + status words + flags
+    GGL_CUDA(cudaMemsetAsync(d_workspace, 0, w.total, s));   // header + count status words + value records
     ggl::count_launch();
 
     GaeParams p;
@@ -503,9 +603,7 @@ extern "C" int ggl_gae_compute(const float* d_rews, const int8_t* d_terminals, c
     unsigned char* wsb = (unsigned char*)d_workspace;
     p.hdr = (GaeHeader*)wsb;
     p.cnt_status = (unsigned long long*)(wsb + w.off_cnt);
-    p.val_flag = (unsigned int*)(wsb + w.off_flag);
-    p.val_agg = (float4*)(wsb + w.off_agg);
-    p.val_inc = (float4*)(wsb + w.off_inc);
+    p.val_rec = (ulonglong2*)(wsb + w.off_rec);
     p.num_tiles = (int)((L + GAE_TILE - 1) / GAE_TILE);
 
     int dev = 0, sms = 148;

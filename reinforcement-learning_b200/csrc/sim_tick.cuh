@@ -13,6 +13,24 @@
 
 namespace ggl {
 
+// Phase timing (profiling build only, -DGGL_PHASE_TIMING -> libgigaenv_cuda_prof.so): the leader lane of every arena adds
+// the SM cycles it spent in each tick phase (including the time its warp ran other arenas' divergent paths) to a global
+// table read back with ggl_debug_phase_cycles. Compiled out of the product library.
+#if defined(GGL_PHASE_TIMING) && defined(__CUDACC__)
+__device__ unsigned long long g_phase_cycles[16];
+__device__ unsigned long long g_arena_phase_cycles[8192][16];     // per-arena breakdown of the first 8192 arenas
+#endif
+#if defined(GGL_PHASE_TIMING) && defined(__CUDA_ARCH__)
+#define GGL_PH_BEGIN() long long _ph_t = clock64()
+#define GGL_PH_RESET() _ph_t = clock64()
+#define GGL_PH(k) do { long long _n = clock64(); if (ex.lane() == 0) { atomicAdd(&g_phase_cycles[k], (unsigned long long)(_n - _ph_t)); \
+        if (ex.arena_ < 8192) g_arena_phase_cycles[ex.arena_][k] += (unsigned long long)(_n - _ph_t); } _ph_t = _n; } while (0)
+#else
+#define GGL_PH_BEGIN() do {} while (0)
+#define GGL_PH_RESET() do {} while (0)
+#define GGL_PH(k) do {} while (0)
+#endif
+
 struct ExecSerial {
     GGL_HD int lane() const { return 0; }
     GGL_HD int lanes() const { return 1; }
@@ -163,37 +181,50 @@ GGL_HD void phase_finish(ArenaDev& A) {
 
 template <class Exec>
 GGL_HD void arena_tick(ArenaDev& A, const WorldDev& W, const Exec& ex) {
+    GGL_PH_BEGIN();
     if (ex.lane() == 0) A.ball.active = (len2(A.ball.vel) == 0.f && len2(A.ball.angVel) == 0.f) ? 0u : 1u;
     for (int c = ex.lane(); c < A.numCars; c += ex.lanes()) { A.cars[c].velSnap = A.cars[c].vel; A.cars[c].angVelSnap = A.cars[c].angVel; }
     if (A.numCars > 0)
         for (int p = ex.lane(); p < kNumPads; p += ex.lanes()) pad_pre_tick(A.pads[p]);
     ex.sync();
+    GGL_PH(0);
     for (int c = ex.lane(); c < A.numCars; c += ex.lanes()) car_pre_tick_a(A, c);
     ex.sync();
+    GGL_PH(1);
     for (int r = ex.lane(); r < 4 * A.numCars; r += ex.lanes())
         if (!A.cars[r >> 2].isDemoed) wheel_first(A, W, r >> 2, r & 3);
     ex.sync();
+    GGL_PH(2);
     for (int c = ex.lane(); c < A.numCars; c += ex.lanes()) car_pre_tick_c(A, c);
     ex.sync();
+    GGL_PH(3);
     const int nb = 1 + A.numCars;
     for (int b = ex.lane(); b < nb; b += ex.lanes()) world_forces(A, b);
     ex.sync();      // the car-ball callback reads the damped ball velocity
+    GGL_PH(4);
     for (int b = ex.lane(); b < nb; b += ex.lanes()) collide_body(A, W, b);
     ex.sync();
+    GGL_PH(5);
     if (ex.lane() == 0) gather_contacts(A);
     ex.sync();
+    GGL_PH(6);
     if (ex.lane() == 0) world_solve(A);
     for (int b = ex.lane(); b < nb; b += ex.lanes())
         if (!(A.bodiesInContact & (1u << b))) body_free_velocity(A, b);
     ex.sync();
+    GGL_PH(7);
     for (int b = ex.lane(); b < nb; b += ex.lanes()) world_integrate(A, b);
     ex.sync();
+    GGL_PH(8);
     for (int c = ex.lane(); c < A.numCars; c += ex.lanes()) car_post_tick(A.cars[c]);
     ex.sync();
+    GGL_PH(9);
     for (int p = ex.lane(); p < kNumPads; p += ex.lanes()) pad_check_cars(A, p);
     ex.sync();
+    GGL_PH(10);
     if (ex.lane() == 0) phase_finish(A);
     ex.sync();
+    GGL_PH(11);
 }
 
 }  // namespace ggl
