@@ -27,6 +27,10 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 PKG = "reinforcement-learning_b200"
 
 ARENAS_PER_GPU = 4096
+# Both arms are pre-rolled this many env steps from the kickoff reset before warm-up, so that the timed steps see the
+# steady-state mix of driving / aerial / wall / car-car contact states (episodes end on a goal or after the 10 s no-touch
+# timeout = 150 env steps): the cost of a step grows ~5x from the kickoff state to steady state on both arms.
+PREROLL_STEPS = 160
 PLAYERS_PER_TEAM = 2
 OBS_SIZE_ADV_2V2 = 167
 # algorithmic bytes per agent-step of the fused env step, 2v2 AdvancedObs:
@@ -141,7 +145,11 @@ def bench_env(args, rank, world, local):
     import torch
     ggl = importlib.import_module(PKG)
     dev = torch.device("cuda", local)
-    env = ggl.EnvSet(ARENAS_PER_GPU, PLAYERS_PER_TEAM, obs_kind=ggl.abi.OBS_ADVANCED, seed=123 + rank, device=local)
+    par = importlib.import_module(PKG + ".parallel")
+    # weak scaling: every rank owns ARENAS_PER_GPU arenas of the world*ARENAS_PER_GPU arena set; no data-path collective
+    _, my_arenas = par.shard_arenas(ARENAS_PER_GPU * world, world, rank)
+    env = ggl.EnvSet(my_arenas, PLAYERS_PER_TEAM, obs_kind=ggl.abi.OBS_ADVANCED, seed=par.rank_seed(123, rank) & 0x7FFFFFFFFFFFFFFF,
+                     device=local)
     assert env.obs_size == OBS_SIZE_ADV_2V2
     acts = torch.zeros(env.num_players, dtype=torch.int32, device=dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
@@ -151,6 +159,8 @@ def bench_env(args, rank, world, local):
         env.random_actions(acts, seed=1000 + i)
         env.step(acts)
 
+    for i in range(PREROLL_STEPS):
+        one(100000 + i)
     for i in range(args.warmup):
         one(i)
     # ---- device-timed region: K steps, CUDA events on the launch stream, L2 flushed between steps
@@ -186,20 +196,16 @@ def bench_env(args, rank, world, local):
     h_mask = torch.empty(env.num_players, env.num_actions, dtype=torch.uint8).pin_memory()
     h_rew = torch.empty(env.num_players, dtype=torch.float32).pin_memory()
     h_term = torch.empty(env.num_arenas, dtype=torch.uint8).pin_memory()
-    rng = np.random.default_rng(7 + rank)
+    e2e_i = [0]
 
     def one_host():
-        # host-side mask-valid random action per agent from the masks the previous step returned
-        m = h_mask.numpy()
-        u = rng.random(env.num_players)
-        cnt = m.sum(1)
-        k = np.minimum((u * cnt).astype(np.int64), np.maximum(cnt - 1, 0))
-        cs = np.cumsum(m, 1)
-        h_act.numpy()[:] = (cs > k[:, None]).argmax(1).astype(np.int32)
+        # the policy stand-in: a mask-valid random action per agent from the HOST masks the previous step returned
+        e2e_i[0] += 1
+        env.host_random_actions(h_mask, h_act, 7000 + 1000003 * rank + e2e_i[0])
         env.step_host(h_act, h_obs, h_mask, h_rew, h_term)
 
     env.step_host(h_act, h_obs, h_mask, h_rew, h_term)
-    e2e_steps = max(3, min(args.steps, 50))
+    e2e_steps = max(3, min(args.steps, 200))
     for _ in range(3):
         one_host()
     barrier_sync(world)
@@ -222,6 +228,7 @@ def bench_env(args, rank, world, local):
                                "{VelocityPlayerToBall,TouchBall,Goal} + {GoalScore,NoTouch(10)}, tick_skip 8, "
                                "device random mask-valid actions (BASELINE.json configs[1])" % ARENAS_PER_GPU,
                    "arenas_per_gpu": ARENAS_PER_GPU, "agents_per_gpu": env.num_players, "l2": "flushed between steps (256 MiB write)",
+                   "preroll_steps": PREROLL_STEPS,
                    "arena_mesh": "synthetic soccar (real .cmf meshes are not redistributable)"},
         "e2e": {"value": e2e_val, "unit": "agent-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "steps": e2e_steps, "api": "ggl_envset_step_host (pinned host buffers)"},
@@ -254,11 +261,12 @@ def cpu_baseline_env(arenas=None, steps=30, warmup=5, threads=0):
         cores = L.ref_num_threads()
         arenas = arenas or ARENAS_PER_GPU
         env = oracle_ref.RefEnvSet(arenas, PLAYERS_PER_TEAM, obs_kind=oracle_ref.abi.OBS_ADVANCED)
-        sec = env.bench(steps, warmup, 123)
+        sec = env.bench(steps, warmup + PREROLL_STEPS, 123)
         v = env.num_players * steps / sec
         env.close()
         return {"value": v, "unit": "agent-steps/s", "cores": cores, "kind": "reference",
-                "sample": "%d arenas 2v2 AdvancedObs, %d warm-up + %d timed env steps, reference thread pool" % (arenas, warmup, steps)}
+                "sample": "%d arenas 2v2 AdvancedObs, %d pre-roll + %d warm-up + %d timed env steps, reference thread pool"
+                          % (arenas, PREROLL_STEPS, warmup, steps)}
     except Exception as e:  # noqa
         return {"value": None, "unit": "agent-steps/s", "cores": 0, "kind": "reference", "sample": "failed: %r" % (e,)}
 
@@ -371,7 +379,7 @@ def bench_reference(args):
             "config": {"workload": "soccar 2v2, %d arenas, AdvancedObs(167) + DefaultAction(90), tick_skip 8, random mask-valid "
                                    "actions: the reference RLGC::EnvSet on the host thread pool (CPU only; the reference has no "
                                    "multi-GPU path, so the same CPU number stands at every N)" % ARENAS_PER_GPU,
-                       "arena_mesh": "synthetic soccar"},
+                       "arena_mesh": "synthetic soccar", "preroll_steps": PREROLL_STEPS},
             "cpu_baseline": cb,
             "e2e": {"value": v, "unit": "agent-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}

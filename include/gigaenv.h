@@ -223,10 +223,19 @@ int  ggl_arena_step(ggl_envset* env, int ticks, void* stream);
 /* device-side uniformly random mask-valid actions (bench / smoke helper; Philox-free LCG hash on (seed, step, slot)) */
 int  ggl_envset_random_actions(ggl_envset* env, int32_t* d_actions, uint64_t seed, void* stream);
 
+/* the same rule on HOST mask rows (policy stand-in for the host-buffer benchmark / examples; no device work) */
+int  ggl_host_random_actions(const uint8_t* h_masks, int32_t* h_actions, int num_players, int num_actions, uint64_t seed);
+
 /* Host-convenience wrappers through HOST buffers (the reference-facing call: EnvState vectors live on the host,
  * EnvSet.h:35-60). actions: int32[num_players]; outputs may be NULL to skip the copy. */
 int  ggl_envset_step_host(ggl_envset* env, const int32_t* h_actions,
                           float* h_obs, uint8_t* h_masks, float* h_rewards, uint8_t* h_terminals);
+
+/* StepSecondHalf with HOST action indices (EnvSet.cpp:132: `const IList& actionIndices`): H2D of the actions, the second-half
+ * launch, and a wait for it. Outputs are then fetched with ggl_envset_read_host. */
+int  ggl_envset_step_second_half_host(ggl_envset* env, const int32_t* h_actions);
+/* copies the EnvState buffers to HOST memory (any pointer may be NULL to skip it) after waiting for pending work */
+int  ggl_envset_read_host(ggl_envset* env, float* h_obs, uint8_t* h_masks, float* h_rewards, uint8_t* h_terminals);
 
 /* ---- DefaultAction ---- */
 /* table: float[90*8] (throttle, steer, pitch, yaw, roll, jump, boost, handbrake) */

@@ -54,6 +54,7 @@ def lib():
             L.ggl_envset_random_actions.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
             L.ggl_envset_step_host.argtypes = [C.c_void_p] * 6
             L.ggl_action_table.argtypes = [C.c_void_p, C.POINTER(C.c_int)]
+            L.ggl_host_random_actions.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_uint64]
         _lib = L
     return _lib
 
@@ -188,6 +189,10 @@ class EnvSet:
 
     def random_actions(self, actions, seed, stream=None):
         _check(lib().ggl_envset_random_actions(self.h, actions.data_ptr(), seed, self._stream(stream)))
+
+    def host_random_actions(self, h_masks, h_actions, seed):
+        p = lambda x: x.data_ptr() if hasattr(x, "data_ptr") else x.ctypes.data
+        _check(lib().ggl_host_random_actions(p(h_masks), p(h_actions), self.num_players, self.num_actions, seed))
 
     def sync(self):
         _check(lib().ggl_envset_sync(self.h))

@@ -18,3 +18,24 @@ void set_error(const char* fmt, ...) {
 extern "C" const char* ggl_last_error(void) { return ggl::g_err; }
 extern "C" uint64_t ggl_launch_count(void) { return ggl::g_launches.load(); }
 extern "C" const char* ggl_version(void) { return "gigaenv-b200 0.1 (sm_100a)"; }
+
+// Host-side stand-in for the policy in benchmarks and examples: one uniformly random mask-valid action per player from
+// host-resident mask rows (the same k-th-set-bit rule and hash as the device helper ggl_envset_random_actions).
+extern "C" int ggl_host_random_actions(const uint8_t* h_masks, int32_t* h_actions, int num_players, int num_actions, uint64_t seed) {
+    if (!h_masks || !h_actions || num_players < 0 || num_actions <= 0) { ggl::set_error("ggl_host_random_actions: bad argument"); return GGL_ERR_INVALID; }
+    for (int i = 0; i < num_players; i++) {
+        uint64_t z = seed + 0x9E3779B97F4A7C15ull * (uint64_t)(i + 1);
+        z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull; z = (z ^ (z >> 27)) * 0x94D049BB133111EBull; z ^= z >> 31;
+        const uint8_t* m = h_masks + (size_t)i * num_actions;
+        int cnt = 0;
+        for (int a = 0; a < num_actions; a++) cnt += m[a] != 0;
+        int sel = 0;
+        if (cnt > 0) {
+            int k = (int)(z % (uint64_t)cnt);
+            for (int a = 0; a < num_actions; a++)
+                if (m[a]) { if (k-- == 0) { sel = a; break; } }
+        }
+        h_actions[i] = sel;
+    }
+    return GGL_OK;
+}

@@ -344,6 +344,30 @@ extern "C" int ggl_envset_step_host(ggl_envset* e, const int32_t* h_actions, flo
     return GGL_OK;
 }
 
+// StepSecondHalf with host action indices + host read-back of the EnvState buffers (the C++ host mirror's path). Work is
+// issued on the legacy default stream like the stream-less calls of the mirror (StepFirstHalf(nullptr)), so it orders after them.
+extern "C" int ggl_envset_step_second_half_host(ggl_envset* e, const int32_t* h_actions) {
+    ENV_CHECK(e);
+    if (!h_actions) { ggl::set_error("null actions"); return GGL_ERR_INVALID; }
+    GGL_CUDA(cudaSetDevice(e->device));
+    GGL_CUDA(cudaMemcpyAsync(e->d_actionsScratch, h_actions, (size_t)e->numPlayers * sizeof(int32_t), cudaMemcpyHostToDevice, 0));
+    int rc = ggl_envset_step_second_half(e, e->d_actionsScratch, nullptr);
+    if (rc) return rc;
+    GGL_CUDA(cudaStreamSynchronize(0));
+    return GGL_OK;
+}
+extern "C" int ggl_envset_read_host(ggl_envset* e, float* h_obs, uint8_t* h_masks, float* h_rewards, uint8_t* h_terminals) {
+    ENV_CHECK(e);
+    GGL_CUDA(cudaSetDevice(e->device));
+    GGL_CUDA(cudaDeviceSynchronize());
+    const size_t np = (size_t)e->numPlayers;
+    if (h_obs) GGL_CUDA(cudaMemcpy(h_obs, e->P.obs, np * e->cfg.obsSize * sizeof(float), cudaMemcpyDeviceToHost));
+    if (h_masks) GGL_CUDA(cudaMemcpy(h_masks, e->P.masks, np * kNumActions, cudaMemcpyDeviceToHost));
+    if (h_rewards) GGL_CUDA(cudaMemcpy(h_rewards, e->P.rewards, np * sizeof(float), cudaMemcpyDeviceToHost));
+    if (h_terminals) GGL_CUDA(cudaMemcpy(h_terminals, e->P.terminals, (size_t)e->cfg.numArenas, cudaMemcpyDeviceToHost));
+    return GGL_OK;
+}
+
 // profiling build only (-DGGL_PHASE_TIMING): per-phase SM cycles summed over arena leaders; zeros in the product library
 extern "C" int ggl_debug_phase_cycles(uint64_t* out16, int reset) {
     if (!out16) return GGL_ERR_INVALID;

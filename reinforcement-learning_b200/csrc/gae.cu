@@ -26,8 +26,17 @@
 
 namespace {
 
-constexpr int GAE_THREADS = 256;
-constexpr int GAE_ITEMS = 16;
+#ifndef GAE_CFG_THREADS
+#define GAE_CFG_THREADS 256
+#endif
+#ifndef GAE_CFG_ITEMS
+#define GAE_CFG_ITEMS 16
+#endif
+#ifndef GAE_CFG_MINBLOCKS
+#define GAE_CFG_MINBLOCKS 4
+#endif
+constexpr int GAE_THREADS = GAE_CFG_THREADS;
+constexpr int GAE_ITEMS = GAE_CFG_ITEMS;                // multiple of 16 (terminals are fetched 16 per load)
 constexpr int GAE_TILE = GAE_THREADS * GAE_ITEMS;       // 4096 elements
 constexpr int GAE_PAD = GAE_TILE / 32;
 constexpr int GAE_WARPS = GAE_THREADS / 32;
@@ -58,6 +67,8 @@ __device__ __forceinline__ Lin2 shfl_down_lin(const Lin2& v, int off) {
 struct GaeHeader {
     unsigned int tile_ticket;
     unsigned int done_ctas;
+    unsigned int pre_done;            // blocks of the count pre-pass that have finished
+    unsigned int trunc_total;         // number of TRUNCATED entries in the stream
     double sum_abs;
     double sum_abs_clipped;
 };
@@ -77,7 +88,7 @@ struct GaeParams {
     int* out_trunc_count;
     // workspace
     GaeHeader* hdr;
-    unsigned long long* cnt_status;   // [tiles]  status<<62 | count
+    const unsigned int* cnt_in;       // [tiles]  TRUNCATED entries in the tiles before this one in scan order (pre-pass)
     ulonglong2* val_rec;              // [tiles]  self-validating (advantage, return) records, see enc_agg / enc_inc
     int num_tiles;
 };
@@ -101,8 +112,6 @@ __device__ __forceinline__ void st_volatile_rec(ulonglong2* p, ulonglong2 v) {
     asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(p), "l"(v.x), "l"(v.y) : "memory");
 }
 
-constexpr unsigned long long ST_AGG = 1ull << 62;
-constexpr unsigned long long ST_INC = 2ull << 62;
 
 // Look-back records of the (advantage, return) chain. One record = two 64-bit words, word0 = (Aa | Ba<<32) for the
 // advantage recurrence and word1 = (Ar | Br<<32) for the return recurrence. The multiplier A of a span is a product of
@@ -203,47 +212,66 @@ __device__ __forceinline__ void lookback_vals(const ulonglong2* rec, int t, int 
     ret_in = acc.Br;
 }
 
-template <int K>
-__device__ __forceinline__ bool lb_count_window(const unsigned long long* status, int win, int lane, int& acc) {
-    for (;;) {
-        unsigned long long s[K];
-        int my_inc = LB_BIG, my_none = LB_BIG;
-#pragma unroll
-        for (int j = 0; j < K; j++) {
-            const int q = win - (lane * K + j);
-            s[j] = (q >= 0) ? ld_volatile_u64(status + q) : ST_INC;
-        }
-#pragma unroll
-        for (int j = K - 1; j >= 0; j--) {
-            const unsigned int stt = (unsigned int)(s[j] >> 62);
-            if (stt == 2u) my_inc = lane * K + j;
-            if (stt == 0u) my_none = lane * K + j;
-        }
-        const int first_inc = __reduce_min_sync(0xffffffffu, my_inc);
-        const int first_none = __reduce_min_sync(0xffffffffu, my_none);
-        if (first_none < first_inc) { __nanosleep(GAE_SLEEP_NS); continue; }
-        int contrib = 0;
-#pragma unroll
-        for (int j = 0; j < K; j++)
-            if (lane * K + j <= first_inc) contrib += (int)(unsigned int)(s[j] & 0xffffffffull);
-        acc += __reduce_add_sync(0xffffffffu, contrib);
-        return first_inc < LB_BIG;
-    }
+// ---- truncation ranks: a pre-pass over the terminals only (1 B/element, +4.8 % traffic) ----
+// truncValPreds[rank] needs, for every TRUNCATED element, the number of TRUNCATED elements after it in the stream
+// (GAE.cpp:68-95). Resolving that count with a second look-back chain inside the scan kernel made 7 of 8 warps of every tile
+// wait at a barrier for it (ncu: 42 % of all stall samples), because the tiles in flight all reach that point together and
+// none of them is inclusive yet. Here every warp counts whole tiles, and the last block to finish turns the per-tile counts
+// into exclusive suffix counts in scan order; the scan kernel then reads one word per tile.
+constexpr int CNT_THREADS = 256;
+__device__ __forceinline__ int count_twos(unsigned int w) {
+    const unsigned int x = w ^ 0x02020202u;                                                   // bytes equal to 2 become 0
+    const unsigned int z = ~(((x & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | x | 0x7F7F7F7Fu);           // 0x80 in every zero byte of x
+    return __popc(z);
 }
-
-// warp 0: number of TRUNCATED entries in the tiles before t in scan order (valid on every lane)
-__device__ __forceinline__ int lookback_count(const unsigned long long* status, int t, int lane) {
-    int acc = 0;
-    int win = t - 1;
-    if (!lb_count_window<LB_K0>(status, win, lane, acc)) {
-        win -= 32 * LB_K0;
-        while (!lb_count_window<LB_K>(status, win, lane, acc)) win -= 32 * LB_K;
+__global__ void __launch_bounds__(CNT_THREADS) gae_trunc_count_kernel(const int8_t* __restrict__ terms, long long L, int num_tiles,
+                                                                       unsigned int* tile_cnt, unsigned int* cnt_in, GaeHeader* hdr) {
+    const int lane = threadIdx.x & 31;
+    const int wid = (blockIdx.x * CNT_THREADS + threadIdx.x) >> 5, nw = (gridDim.x * CNT_THREADS) >> 5;
+    for (int t = wid; t < num_tiles; t += nw) {
+        const long long base = (long long)(num_tiles - 1 - t) * GAE_TILE;
+        int c = 0;
+#pragma unroll
+        for (int k = 0; k < GAE_TILE / (32 * 16); k++) {
+            const long long gi = base + ((long long)k * 32 + lane) * 16;
+            if (gi + 15 < L) {
+                const uint4 w = __ldcs(reinterpret_cast<const uint4*>(terms + gi));
+                c += count_twos(w.x) + count_twos(w.y) + count_twos(w.z) + count_twos(w.w);
+            } else {
+                for (int e = 0; e < 16; e++)
+                    if (gi + e < L) c += terms[gi + e] == 2;
+            }
+        }
+        c = __reduce_add_sync(0xffffffffu, c);
+        if (lane == 0) __stcg(&tile_cnt[t], (unsigned int)c);
     }
-    return acc;
+    // last block: exclusive prefix over the tiles in scan order
+    __shared__ unsigned int s_last;
+    __shared__ unsigned int s_part[CNT_THREADS];
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) s_last = (atomicAdd(&hdr->pre_done, 1u) == gridDim.x - 1) ? 1u : 0u;
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    const int per = (num_tiles + CNT_THREADS - 1) / CNT_THREADS;
+    const int b0 = threadIdx.x * per, b1 = min(num_tiles, b0 + per);
+    unsigned int sum = 0;
+    for (int t = b0; t < b1; t++) sum += __ldcg(&tile_cnt[t]);
+    s_part[threadIdx.x] = sum;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned int run = 0;
+        for (int i = 0; i < CNT_THREADS; i++) { const unsigned int v = s_part[i]; s_part[i] = run; run += v; }
+        hdr->trunc_total = run;
+    }
+    __syncthreads();
+    unsigned int run = s_part[threadIdx.x];
+    for (int t = b0; t < b1; t++) { cnt_in[t] = run; run += __ldcg(&tile_cnt[t]); }
 }
 
 template <bool HAS_TRUNC, bool NORM, bool CLIP>
-__global__ void __launch_bounds__(GAE_THREADS, 4) gae_scan_kernel(GaeParams p) {
+__global__ void __launch_bounds__(GAE_THREADS, GAE_CFG_MINBLOCKS) gae_scan_kernel(GaeParams p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float* s_r = reinterpret_cast<float*>(smem_raw);                 // rewards -> advantages
     float* s_v = s_r + (GAE_TILE + GAE_PAD + 4);                     // values (+1 lookahead) -> returns
@@ -252,7 +280,6 @@ __global__ void __launch_bounds__(GAE_THREADS, 4) gae_scan_kernel(GaeParams p) {
     __shared__ int s_tile;
     __shared__ Lin2 s_warp[GAE_WARPS];
     __shared__ int s_wcnt[GAE_WARPS];
-    __shared__ int s_cnt_in;
     __shared__ float s_x_in[2];
     __shared__ double s_red[2][GAE_WARPS];
 
@@ -271,6 +298,23 @@ __global__ void __launch_bounds__(GAE_THREADS, 4) gae_scan_kernel(GaeParams p) {
         unsigned int next_ticket = 0;
         if (tid == 0) next_ticket = atomicAdd(&p.hdr->tile_ticket, 1u);
 
+        // terminals first (1 B/element): the integer chain below only needs them, and resolves while the 8 B/element of
+        // rewards and values are still in flight. Every thread owns GAE_ITEMS consecutive elements; the HIGHEST thread id comes first in scan order
+        unsigned int tword[GAE_ITEMS / 4];
+#pragma unroll
+        for (int k = 0; k < GAE_ITEMS / 16; k++) {
+            const long long gi = base + (long long)tid * GAE_ITEMS + 16 * k;
+            uint4 tw;
+            if (gi + 15 < p.L) {
+                tw = __ldcs(reinterpret_cast<const uint4*>(p.terms + gi));
+            } else {
+                unsigned int w[4] = {0, 0, 0, 0};
+                for (int e = 0; e < 16; e++)
+                    if (gi + e < p.L) w[e >> 2] |= (unsigned int)(unsigned char)p.terms[gi + e] << (8 * (e & 3));
+                tw = make_uint4(w[0], w[1], w[2], w[3]);
+            }
+            tword[4 * k] = tw.x; tword[4 * k + 1] = tw.y; tword[4 * k + 2] = tw.z; tword[4 * k + 3] = tw.w;
+        }
         // ---- coalesced streaming loads, issued up front into registers (they stay in flight during the count chain) ----
         float4 r4[GAE_ITEMS / 4], v4[GAE_ITEMS / 4];
 #pragma unroll
@@ -292,37 +336,18 @@ __global__ void __launch_bounds__(GAE_THREADS, 4) gae_scan_kernel(GaeParams p) {
                 v4[c] = make_float4(vv[0], vv[1], vv[2], vv[3]);
             }
         }
-        // every thread owns GAE_ITEMS consecutive elements; the HIGHEST thread id comes first in scan order
-        uint4 tw;
-        {
-            const long long gi = base + (long long)tid * 16;
-            if (gi + 15 < p.L) {
-                tw = __ldcs(reinterpret_cast<const uint4*>(p.terms + gi));
-            } else {
-                unsigned int w[4] = {0, 0, 0, 0};
-                for (int e = 0; e < 16; e++)
-                    if (gi + e < p.L) w[e >> 2] |= (unsigned int)(unsigned char)p.terms[gi + e] << (8 * (e & 3));
-                tw = make_uint4(w[0], w[1], w[2], w[3]);
-            }
-        }
         float v_look = 0.f;
         if (tid == 0) {
             const long long gi = base + GAE_TILE;
             v_look = (gi < p.L) ? p.vals[gi] : 0.f;
         }
-        const unsigned int tword[4] = {tw.x, tw.y, tw.z, tw.w};
 
-        // ---- chain 1 (integer): suffix count of TRUNCATED entries -> truncValPreds rank ----
+        // ---- truncation rank: tile offset from the pre-pass + suffix count inside the tile ----
         int cnt_before = 0;   // TRUNCATED entries at higher stream indices than this thread's span
         if (HAS_TRUNC) {
             int c_loc = 0;
 #pragma unroll
-            for (int j = 0; j < 4; j++) {
-                // bytes equal to 2: (x ^ 0x02020202) has a zero byte there
-                const unsigned int x = tword[j] ^ 0x02020202u;
-                const unsigned int z = ~(((x & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | x | 0x7F7F7F7Fu);   // 0x80 in every zero byte of x
-                c_loc += __popc(z);
-            }
+            for (int k = 0; k < GAE_ITEMS / 4; k++) c_loc += count_twos(tword[k]);
             int c = c_loc;
 #pragma unroll
             for (int off = 1; off < 32; off <<= 1) {
@@ -331,25 +356,11 @@ __global__ void __launch_bounds__(GAE_THREADS, 4) gae_scan_kernel(GaeParams p) {
             }
             if (lane == 0) s_wcnt[warp] = c;
             __syncthreads();
-            int wcarry = 0, total = 0;
+            int wcarry = 0;
 #pragma unroll
-            for (int w = 0; w < GAE_WARPS; w++) {
-                total += s_wcnt[w];
+            for (int w = 0; w < GAE_WARPS; w++)
                 if (w > warp) wcarry += s_wcnt[w];
-            }
-            if (warp == 0) {
-                int acc = 0;
-                if (t > 0) {
-                    if (lane == 0) st_volatile_u64(&p.cnt_status[t], ST_AGG | (unsigned long long)(unsigned int)total);
-                    acc = lookback_count(p.cnt_status, t, lane);
-                }
-                if (lane == 0) {
-                    st_volatile_u64(&p.cnt_status[t], ST_INC | (unsigned long long)(unsigned int)(acc + total));
-                    s_cnt_in = acc;
-                }
-            }
-            __syncthreads();
-            cnt_before = s_cnt_in + wcarry + (c - c_loc);
+            cnt_before = (int)__ldg(&p.cnt_in[t]) + wcarry + (c - c_loc);
         }
 
         // ---- transpose through padded shared memory ----
@@ -420,16 +431,24 @@ __global__ void __launch_bounds__(GAE_THREADS, 4) gae_scan_kernel(GaeParams p) {
         const Lin2 thread_in = compose(excl, wcarry);
 
         // ---- chain 2 (float): carry-in of (advantage, return) from the tiles after this one ----
+        // A tile that contains a terminal has multiplier 0 in both recurrences: what it hands on does not depend on its own
+        // carry-in, so it publishes its INCLUSIVE record at once and later tiles stop their look-back right there (with
+        // episodes shorter than a tile -- the usual PPO stream -- every look-back is one window deep).
         if (warp == 0) {
             float adv_in = 0.f, ret_in = 0.f;
+            const bool closed = (tile_agg.Aa == 0.f && tile_agg.Ar == 0.f);
             if (t > 0) {
-                if (lane == 0) st_volatile_rec(&p.val_rec[t], enc_agg(tile_agg));
+                if (lane == 0) st_volatile_rec(&p.val_rec[t], closed ? enc_inc(tile_agg.Ba, tile_agg.Br) : enc_agg(tile_agg));
+#ifndef GAE_DBG_NOCHAIN2
                 lookback_vals(p.val_rec, t, lane, adv_in, ret_in);
+#endif
             }
             if (lane == 0) {
-                const float adv_out = tile_agg.Aa * adv_in + tile_agg.Ba;
-                const float ret_out = tile_agg.Ar * ret_in + tile_agg.Br;
-                st_volatile_rec(&p.val_rec[t], enc_inc(adv_out, ret_out));
+                if (!closed || t == 0) {
+                    const float adv_out = tile_agg.Aa * adv_in + tile_agg.Ba;
+                    const float ret_out = tile_agg.Ar * ret_in + tile_agg.Br;
+                    st_volatile_rec(&p.val_rec[t], enc_inc(adv_out, ret_out));
+                }
                 s_x_in[0] = adv_in;
                 s_x_in[1] = ret_in;
             }
@@ -515,8 +534,7 @@ __global__ void __launch_bounds__(GAE_THREADS, 4) gae_scan_kernel(GaeParams p) {
             }
             if (p.out_trunc_count) {
                 int n = -1;
-                if (HAS_TRUNC && p.num_tiles > 0)
-                    n = (int)(unsigned int)(ld_volatile_u64(&p.cnt_status[p.num_tiles - 1]) & 0xffffffffull);
+                if (HAS_TRUNC) n = (int)*((volatile unsigned int*)&p.hdr->trunc_total);
                 *p.out_trunc_count = n;
             }
         }
@@ -528,14 +546,16 @@ constexpr size_t gae_smem_bytes() { return 3 * (size_t)(GAE_TILE + GAE_PAD + 4) 
 size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 struct WsLayout {
-    size_t off_cnt, off_rec, total;
+    size_t off_rec, off_tcnt, off_cin, zero_bytes, total;
 };
 WsLayout ws_layout(long long L) {
     const size_t tiles = (size_t)((L + GAE_TILE - 1) / GAE_TILE);
     WsLayout w;
     size_t o = align_up(sizeof(GaeHeader), 16);
-    w.off_cnt = o;  o += align_up(tiles * sizeof(unsigned long long), 16);
     w.off_rec = o;  o += tiles * sizeof(ulonglong2);
+    w.zero_bytes = o;                                   // header + look-back records start as zeros
+    w.off_tcnt = o; o += align_up(tiles * sizeof(unsigned int), 16);
+    w.off_cin = o;  o += align_up(tiles * sizeof(unsigned int), 16);
     w.total = align_up(o, 256);
     return w;
 }
@@ -587,7 +607,7 @@ extern "C" int ggl_gae_compute(const float* d_rews, const int8_t* d_terminals, c
         ggl::set_error("ggl_gae_compute: buffers must be 16-byte aligned"); return GGL_ERR_INVALID;
     }
     const WsLayout w = ws_layout(L);
-    GGL_CUDA(cudaMemsetAsync(d_workspace, 0, w.total, s));   // header + count status words + value records
+    GGL_CUDA(cudaMemsetAsync(d_workspace, 0, w.zero_bytes, s));   // header + value records
     ggl::count_launch();
 
     GaeParams p;
@@ -602,17 +622,34 @@ extern "C" int ggl_gae_compute(const float* d_rews, const int8_t* d_terminals, c
     p.out_clip_portion = d_out_clip_portion; p.out_trunc_count = d_out_trunc_count;
     unsigned char* wsb = (unsigned char*)d_workspace;
     p.hdr = (GaeHeader*)wsb;
-    p.cnt_status = (unsigned long long*)(wsb + w.off_cnt);
+    p.cnt_in = (const unsigned int*)(wsb + w.off_cin);
     p.val_rec = (ulonglong2*)(wsb + w.off_rec);
     p.num_tiles = (int)((L + GAE_TILE - 1) / GAE_TILE);
 
     int dev = 0, sms = 148;
     GGL_CUDA(cudaGetDevice(&dev));
     GGL_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    const int grid = p.num_tiles < sms * 4 ? p.num_tiles : sms * 4;   // persistent: 4 resident CTAs per SM
+    int per_sm = GAE_CFG_MINBLOCKS;                                    // persistent: as many CTAs as stay resident
+    {
+        static int occ = 0;
+        if (!occ) {
+            GGL_CUDA(cudaFuncSetAttribute(gae_scan_kernel<true, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gae_smem_bytes()));
+            GGL_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, gae_scan_kernel<true, true, true>, GAE_THREADS, gae_smem_bytes()));
+            if (occ < 1) occ = 1;
+        }
+        per_sm = occ;
+    }
+    const int grid = p.num_tiles < sms * per_sm ? p.num_tiles : sms * per_sm;
 
     const bool ht = d_trunc_val_preds != nullptr;
     if (ht) {
+        const int warps_per_block = CNT_THREADS / 32;
+        int cgrid = (p.num_tiles + warps_per_block - 1) / warps_per_block;
+        if (cgrid > sms * 8) cgrid = sms * 8;
+        gae_trunc_count_kernel<<<cgrid, CNT_THREADS, 0, s>>>(d_terminals, L, p.num_tiles, (unsigned int*)(wsb + w.off_tcnt),
+                                                            (unsigned int*)(wsb + w.off_cin), p.hdr);
+        GGL_LAUNCH_CHECK();
+        ggl::count_launch();
         if (norm) return clip ? launch<true, true, true>(p, grid, s) : launch<true, true, false>(p, grid, s);
         return launch<true, false, false>(p, grid, s);
     }

@@ -1,2 +1,3 @@
-ncu --set full --clock-control none --import-source on -k regex:gae_scan -s 6 -c 1 -f -o gpurun_out/gae_scan python bench.py --workload gae --steps 5 --warmup 3 > gpurun_out/ncu_gae.log 2>&1
-tail -2 gpurun_out/ncu_gae.log
+python -m pytest tests -m gpu -x -q 2>&1 | tail -4
+python bench.py --steps 100 --warmup 10 > gpurun_out/bench_env2.json 2> gpurun_out/bench_env2.err; cat gpurun_out/bench_env2.json; tail -3 gpurun_out/bench_env2.err
+python bench.py --impl reference --steps 10 --warmup 3 > gpurun_out/bench_ref2.json 2>/dev/null; cat gpurun_out/bench_ref2.json
