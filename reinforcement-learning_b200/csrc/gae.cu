@@ -260,10 +260,24 @@ __global__ void __launch_bounds__(CNT_THREADS) gae_trunc_count_kernel(const int8
     for (int t = b0; t < b1; t++) sum += __ldcg(&tile_cnt[t]);
     s_part[threadIdx.x] = sum;
     __syncthreads();
-    if (threadIdx.x == 0) {
-        unsigned int run = 0;
-        for (int i = 0; i < CNT_THREADS; i++) { const unsigned int v = s_part[i]; s_part[i] = run; run += v; }
-        hdr->trunc_total = run;
+    {   // exclusive scan of the CNT_THREADS partial sums: warp shuffles + one pass over the warp totals
+        __shared__ unsigned int s_wsum[CNT_THREADS / 32];
+        unsigned int inc = sum;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const unsigned int o = __shfl_up_sync(0xffffffffu, inc, off);
+            if (lane >= off) inc += o;
+        }
+        if (lane == 31) s_wsum[threadIdx.x >> 5] = inc;
+        __syncthreads();
+        unsigned int wbase = 0, total = 0;
+#pragma unroll
+        for (int w = 0; w < CNT_THREADS / 32; w++) {
+            if (w < (int)(threadIdx.x >> 5)) wbase += s_wsum[w];
+            total += s_wsum[w];
+        }
+        s_part[threadIdx.x] = wbase + inc - sum;
+        if (threadIdx.x == 0) hdr->trunc_total = total;
     }
     __syncthreads();
     unsigned int run = s_part[threadIdx.x];

@@ -114,7 +114,7 @@ GGL_HD void pad_pre_tick(PadDev& pd) {
 //   world_forces(b)   gravity + damping                                    per body
 //   collide_body(b)   contact generation into the body's windows           per body   (sim_world.cuh)
 //   gather_contacts   compaction to solver order + ordered callbacks       leader
-//   solve_contacts    PGS over the bodies that have rows                   leader     | body_free_velocity(b) for the others
+//   solve_island      PGS over one contact island                          per island | body_free_velocity(b) for bodies without rows
 //   world_integrate(b) transform integration, clear forces                 per body
 GGL_HD void world_forces(ArenaDev& A, int b) {
     const V3 g = v3(0, 0, rl::GRAVITY_Z * kUU2BT);
@@ -141,15 +141,6 @@ GGL_HD void world_integrate(ArenaDev& A, int b) {
         }
         c.force = v3(0, 0, 0); c.torque = v3(0, 0, 0);
     }
-}
-
-// leader, between gather and integrate: the solver sees the ball as active when an active car touches it
-GGL_HD void world_solve(ArenaDev& A) {
-    if (A.numContacts == 0) return;
-    uint32_t wasActive = A.ball.active;
-    A.ball.active = A.ballAwake;
-    solve_contacts(A);
-    A.ball.active = wasActive;
 }
 
 GGL_HD void phase_finish(ArenaDev& A) {
@@ -208,9 +199,11 @@ GGL_HD void arena_tick(ArenaDev& A, const WorldDev& W, const Exec& ex) {
     if (ex.lane() == 0) gather_contacts(A);
     ex.sync();
     GGL_PH(6);
-    if (ex.lane() == 0) world_solve(A);
-    for (int b = ex.lane(); b < nb; b += ex.lanes())
+    // one lane per contact island (its lowest body index); bodies without a row take the free-body path on their own lane
+    for (int b = ex.lane(); b < nb; b += ex.lanes()) {
         if (!(A.bodiesInContact & (1u << b))) body_free_velocity(A, b);
+        else if (A.island[b] == b) solve_island(A, b);
+    }
     ex.sync();
     GGL_PH(7);
     for (int b = ex.lane(); b < nb; b += ex.lanes()) world_integrate(A, b);

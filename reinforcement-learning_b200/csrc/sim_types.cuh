@@ -163,6 +163,7 @@ struct alignas(16) ArenaDev {
     int32_t numContacts;
     uint32_t bodiesInContact;                      // bit b: body b (0 ball, 1 + c car c) has a solver row this tick
     uint8_t cntWorld, ballAwake, cntBall[kMaxCars], cntRest[kMaxCars], _pad4[2];
+    uint8_t island[8], _pad5[8];                   // island[b] = lowest body index of the contact island body b belongs to
     Contact contacts[kMaxContacts];
     alignas(16) CarDev cars[kMaxCars];
 };

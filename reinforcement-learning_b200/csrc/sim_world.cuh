@@ -446,16 +446,22 @@ GGL_HD void resolve_push(Row& c, SolverBody* sb) {
 
 constexpr int kMaxRows = kMaxContacts + 1;
 
-// Solves all contact rows of the arena and writes velocities (and push-corrected positions) back.
-GGL_HDN void solve_contacts(ArenaDev& A) {
+// Solves the contact rows of ONE island (the bodies whose island label is `rep`, A.island[] from gather_contacts) and writes
+// their velocities (and push-corrected positions) back. Projected Gauss-Seidel is sequential over rows, but a row only reads
+// and writes the solver bodies it connects, so islands that share no dynamic body are independent: solving them on
+// different lanes, each in the reference's row order restricted to the island, gives bit-identical results to the single
+// sequential sweep of btSequentialImpulseConstraintSolver (the host build does the same thing island after island).
+GGL_HDN void solve_island(ArenaDev& A, int rep) {
     SolverBody sb[1 + kMaxCars];
     const int nb = 1 + A.numCars;
-    const uint32_t inContact = A.bodiesInContact;      // bodies without a row integrate their velocity on their own lane
+    uint32_t inContact = 0;                            // bodies of this island that have a row
+    for (int b = 0; b < nb; b++)
+        if (A.island[b] == rep && (A.bodiesInContact & (1u << b))) inContact |= 1u << b;
     // ball
     if (inContact & 1u) {
         SolverBody& s = sb[0];
         s.dv = s.dw = s.push = s.turn = v3(0, 0, 0);
-        s.active = (int)A.ball.active;
+        s.active = (int)A.ballAwake;                   // the solver sees the ball as active when an active car touches it
         s.invMass = kBallInvMass;
         float ii = ball_inv_inertia();
         s.invI.r0 = v3(ii, 0, 0); s.invI.r1 = v3(0, ii, 0); s.invI.r2 = v3(0, 0, ii);
@@ -483,6 +489,7 @@ GGL_HDN void solve_contacts(ArenaDev& A) {
     for (int k = 0; k < A.numContacts; k++) {
         const Contact& c = A.contacts[k];
         int a = c.bodyA, b = c.bodyB;
+        if (A.island[a] != rep) continue;
         setup_contact_row(rows[nr], sb, a, b, c.normal, c.relA, c.relB, c.dist, c.friction, c.restitution, c.special);
         if (c.special) {
             nSpecial++; spFriction = c.friction; spRest = c.restitution; spNormal += c.normal; spDist += len(c.relA);
@@ -648,6 +655,18 @@ GGL_HDN void gather_contacts(ArenaDev& A) {
         if (c.bodyB >= 0) mask |= 1u << c.bodyB;
     }
     A.bodiesInContact = mask;
+    // contact islands: bodies connected through rows between two dynamic bodies (car-ball, car-car) share a label
+    for (int b = 0; b < 8; b++) A.island[b] = (uint8_t)b;
+    for (int pass = 0; pass < kMaxCars; pass++) {
+        bool changed = false;
+        for (int k = 0; k < A.numContacts; k++) {
+            const Contact& c = A.contacts[k];
+            if (c.bodyB < 0) continue;
+            const uint8_t la = A.island[c.bodyA], lb = A.island[c.bodyB];
+            if (la != lb) { const uint8_t m = la < lb ? la : lb; A.island[c.bodyA] = m; A.island[c.bodyB] = m; changed = true; }
+        }
+        if (!changed) break;
+    }
 }
 
 }  // namespace ggl

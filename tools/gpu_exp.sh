@@ -1,3 +1,5 @@
-python -m pytest tests -m gpu -x -q 2>&1 | tail -4
-python bench.py --steps 100 --warmup 10 > gpurun_out/bench_env2.json 2> gpurun_out/bench_env2.err; cat gpurun_out/bench_env2.json; tail -3 gpurun_out/bench_env2.err
-python bench.py --impl reference --steps 10 --warmup 3 > gpurun_out/bench_ref2.json 2>/dev/null; cat gpurun_out/bench_ref2.json
+P=reinforcement-learning_b200
+for v in pn; do
+echo "=== gae variant $v"
+GGL_LIB_PATH=$P/libgigaenv_var_$v.so timeout 300 python bench.py --workload gae 2>&1 | python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('GAE ms', d['ms_per_step'], 'frac', d['roofline']['frac'])"
+done
