@@ -7,8 +7,9 @@ One "step" = one env step (Reset + StepFirstHalf + StepSecondHalf, tick_skip 8) 
 BASELINE.json configs[1]: soccar 2v2, 4096 arenas per GPU, AdvancedObs + {VelocityPlayerToBall, TouchBall, Goal},
 device-side random mask-valid actions.  Arenas shard across ranks with no data-path collective ("weak" scaling:
 4096 arenas per GPU).  `value` = agent-steps of all ranks / max-over-ranks device time (CUDA events on the launch
-stream, L2 flushed between steps).  `e2e` = the same metric through the host-buffer C-ABI call
-(ggl_envset_step_host: pinned H2D of actions, D2H of obs/masks/rewards/terminals inside the timed region).
+stream, L2 flushed between steps).  `e2e` = the same metric through the host-buffer C-ABI calls in the Learner's order
+(ggl_envset_begin_step_host: Reset + D2H of obs/masks + first half launched; host action pick; ggl_envset_finish_step_host:
+pinned H2D of actions, second half, D2H of rewards/terminals -- all inside the timed wall-clock region).
 `--workload gae` benches the GAE scan instead (config C4: T=256 x N=65536 stream, GB/s at 21 B/element).
 `--impl reference` times the UNMODIFIED reference's CPU EnvSet (oracle/_ref, all host threads) on the same config.
 """
@@ -200,9 +201,12 @@ def bench_env(args, rank, world, local):
 
     def one_host():
         # the policy stand-in: a mask-valid random action per agent from the HOST masks the previous step returned
+        # Learner loop (Learner.cpp:669-793): Reset + StepFirstHalf(async), policy on the host copies of obs / masks while
+        # the first half runs, then StepSecondHalf with the host action indices and the rewards / terminals read back.
         e2e_i[0] += 1
+        env.begin_step_host(h_obs, h_mask)
         env.host_random_actions(h_mask, h_act, 7000 + 1000003 * rank + e2e_i[0])
-        env.step_host(h_act, h_obs, h_mask, h_rew, h_term)
+        env.finish_step_host(h_act, h_rew, h_term)
 
     env.step_host(h_act, h_obs, h_mask, h_rew, h_term)
     e2e_steps = max(3, min(args.steps, 200))
@@ -231,7 +235,7 @@ def bench_env(args, rank, world, local):
                    "preroll_steps": PREROLL_STEPS,
                    "arena_mesh": "synthetic soccar (real .cmf meshes are not redistributable)"},
         "e2e": {"value": e2e_val, "unit": "agent-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "steps": e2e_steps, "api": "ggl_envset_step_host (pinned host buffers)"},
+                "steps": e2e_steps, "api": "ggl_envset_begin_step_host + host action pick + ggl_envset_finish_step_host (pinned host buffers)"},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": None, "kernel": "env_step_kernel", "peak_source": peak_src,

@@ -237,6 +237,16 @@ int  ggl_envset_step_second_half_host(ggl_envset* env, const int32_t* h_actions)
 /* copies the EnvState buffers to HOST memory (any pointer may be NULL to skip it) after waiting for pending work */
 int  ggl_envset_read_host(ggl_envset* env, float* h_obs, uint8_t* h_masks, float* h_rewards, uint8_t* h_terminals);
 
+/* The Learner's loop through HOST buffers, pipelined like the reference (Learner.cpp:669-793: Reset, StepFirstHalf(async),
+ * policy inference on state.obs while the first half runs, Sync, StepSecondHalf):
+ *   begin  = Reset + copy of the post-reset obs / action masks to the host + launch of the first half; returns as soon as
+ *            obs and masks have landed, with the first half still running (it never writes obs or masks, EnvSet.cpp:113-130)
+ *   finish = H2D of the action indices, second half, D2H of rewards / terminals (and, when h_final_obs is not NULL, of the
+ *            obs rows as they stand after the step = the final obs of episodes that just ended); waits for completion.
+ * Host pointers should be pinned for the copies to overlap. */
+int  ggl_envset_begin_step_host(ggl_envset* env, float* h_obs, uint8_t* h_masks);
+int  ggl_envset_finish_step_host(ggl_envset* env, const int32_t* h_actions, float* h_rewards, uint8_t* h_terminals, float* h_final_obs);
+
 /* ---- DefaultAction ---- */
 /* table: float[90*8] (throttle, steer, pitch, yaw, roll, jump, boost, handbrake) */
 int  ggl_action_table(float* out_table, int* out_num_actions);

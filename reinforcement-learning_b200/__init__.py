@@ -53,6 +53,8 @@ def lib():
             L.ggl_arena_step.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
             L.ggl_envset_random_actions.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
             L.ggl_envset_step_host.argtypes = [C.c_void_p] * 6
+            L.ggl_envset_begin_step_host.argtypes = [C.c_void_p] * 3
+            L.ggl_envset_finish_step_host.argtypes = [C.c_void_p] * 5
             L.ggl_action_table.argtypes = [C.c_void_p, C.POINTER(C.c_int)]
             L.ggl_host_random_actions.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_uint64]
         _lib = L
@@ -200,6 +202,15 @@ class EnvSet:
     def step_host(self, h_actions, h_obs=None, h_masks=None, h_rewards=None, h_terminals=None):
         p = lambda x: None if x is None else (x.data_ptr() if hasattr(x, "data_ptr") else x.ctypes.data)
         _check(lib().ggl_envset_step_host(self.h, p(h_actions), p(h_obs), p(h_masks), p(h_rewards), p(h_terminals)))
+
+    def begin_step_host(self, h_obs=None, h_masks=None):
+        """Reset + post-reset obs/masks to the host + first half launched (still running on return)."""
+        p = lambda x: None if x is None else (x.data_ptr() if hasattr(x, "data_ptr") else x.ctypes.data)
+        _check(lib().ggl_envset_begin_step_host(self.h, p(h_obs), p(h_masks)))
+
+    def finish_step_host(self, h_actions, h_rewards=None, h_terminals=None, h_final_obs=None):
+        p = lambda x: None if x is None else (x.data_ptr() if hasattr(x, "data_ptr") else x.ctypes.data)
+        _check(lib().ggl_envset_finish_step_host(self.h, p(h_actions), p(h_rewards), p(h_terminals), p(h_final_obs)))
 
     def set_state(self, arena, st):
         _check(lib().ggl_envset_set_state(self.h, arena, C.byref(st)))

@@ -21,7 +21,8 @@ struct ggl_envset {
     int32_t* d_actionsScratch;
     // pinned staging for the host-buffer wrapper
     int32_t* h_actions; float* h_obs; uint8_t* h_masks; float* h_rewards; uint8_t* h_terminals;
-    cudaStream_t ownStream;
+    cudaStream_t ownStream, copyStream;
+    cudaEvent_t evReset, evCopied;
     uint64_t seed;
 };
 
@@ -51,6 +52,9 @@ void free_env(ggl_envset* e) {
     if (e->h_rewards) cudaFreeHost(e->h_rewards);
     if (e->h_terminals) cudaFreeHost(e->h_terminals);
     if (e->ownStream) cudaStreamDestroy(e->ownStream);
+    if (e->copyStream) cudaStreamDestroy(e->copyStream);
+    if (e->evReset) cudaEventDestroy(e->evReset);
+    if (e->evCopied) cudaEventDestroy(e->evCopied);
     delete e;
 }
 
@@ -80,7 +84,7 @@ extern "C" int ggl_envset_create(const ggl_envset_desc* d, ggl_envset** out) {
     if (!e) return GGL_ERR_NOMEM;
     memset(&e->cfg, 0, sizeof(e->cfg)); memset(&e->P, 0, sizeof(e->P));
     e->d_tris = nullptr; e->d_cellStart = e->d_cellTris = nullptr; e->d_reset = nullptr; e->d_table = nullptr; e->d_actionsScratch = nullptr;
-    e->h_actions = nullptr; e->h_obs = nullptr; e->h_masks = nullptr; e->h_rewards = nullptr; e->h_terminals = nullptr; e->ownStream = nullptr;
+    e->h_actions = nullptr; e->h_obs = nullptr; e->h_masks = nullptr; e->h_rewards = nullptr; e->h_terminals = nullptr; e->ownStream = nullptr; e->copyStream = nullptr; e->evReset = nullptr; e->evCopied = nullptr;
     e->device = d->device; e->seed = d->seed;
     EnvCfg& c = e->cfg;
     c.numArenas = d->num_arenas; c.playersPerTeam = d->players_per_team; c.numCars = 2 * d->players_per_team;
@@ -150,6 +154,9 @@ extern "C" int ggl_envset_create(const ggl_envset_desc* d, ggl_envset** out) {
     cudaMemset(e->P.rewards, 0, (size_t)e->numPlayers * sizeof(float));
     cudaMemset(e->P.lastRewards, 0, (size_t)c.numArenas * (c.numRewards ? c.numRewards : 1) * sizeof(float));
     GGL_CUDA(cudaStreamCreateWithFlags(&e->ownStream, cudaStreamNonBlocking));
+    GGL_CUDA(cudaStreamCreateWithFlags(&e->copyStream, cudaStreamNonBlocking));
+    GGL_CUDA(cudaEventCreateWithFlags(&e->evReset, cudaEventDisableTiming));
+    GGL_CUDA(cudaEventCreateWithFlags(&e->evCopied, cudaEventDisableTiming));
     GGL_CUDA(cudaFuncSetAttribute(env_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_for(e->cfg)));
     GGL_CUDA(cudaFuncSetAttribute(arena_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_for(e->cfg)));
     // EnvSet ctor: reset every arena once (EnvSet.cpp:106-110)
@@ -340,6 +347,39 @@ extern "C" int ggl_envset_step_host(ggl_envset* e, const int32_t* h_actions, flo
     if (h_masks) GGL_CUDA(cudaMemcpyAsync(h_masks, e->P.masks, np * kNumActions, cudaMemcpyDeviceToHost, s));
     if (h_rewards) GGL_CUDA(cudaMemcpyAsync(h_rewards, e->P.rewards, np * sizeof(float), cudaMemcpyDeviceToHost, s));
     if (h_terminals) GGL_CUDA(cudaMemcpyAsync(h_terminals, e->P.terminals, (size_t)e->cfg.numArenas, cudaMemcpyDeviceToHost, s));
+    GGL_CUDA(cudaStreamSynchronize(s));
+    return GGL_OK;
+}
+
+// Pipelined host-buffer step (the Learner loop): the obs/mask copy and the caller's policy overlap the first half.
+extern "C" int ggl_envset_begin_step_host(ggl_envset* e, float* h_obs, uint8_t* h_masks) {
+    ENV_CHECK(e);
+    GGL_CUDA(cudaSetDevice(e->device));
+    const size_t np = (size_t)e->numPlayers;
+    int rc = ggl_envset_reset(e, e->ownStream);
+    if (rc) return rc;
+    GGL_CUDA(cudaEventRecord(e->evReset, e->ownStream));
+    rc = ggl_envset_step_first_half(e, e->ownStream);                 // runs while the copies below are in flight
+    if (rc) return rc;
+    GGL_CUDA(cudaStreamWaitEvent(e->copyStream, e->evReset, 0));
+    if (h_obs) GGL_CUDA(cudaMemcpyAsync(h_obs, e->P.obs, np * e->cfg.obsSize * sizeof(float), cudaMemcpyDeviceToHost, e->copyStream));
+    if (h_masks) GGL_CUDA(cudaMemcpyAsync(h_masks, e->P.masks, np * kNumActions, cudaMemcpyDeviceToHost, e->copyStream));
+    GGL_CUDA(cudaEventRecord(e->evCopied, e->copyStream));
+    GGL_CUDA(cudaEventSynchronize(e->evCopied));
+    return GGL_OK;
+}
+extern "C" int ggl_envset_finish_step_host(ggl_envset* e, const int32_t* h_actions, float* h_rewards, uint8_t* h_terminals, float* h_final_obs) {
+    ENV_CHECK(e);
+    if (!h_actions) { ggl::set_error("null actions"); return GGL_ERR_INVALID; }
+    GGL_CUDA(cudaSetDevice(e->device));
+    cudaStream_t s = e->ownStream;
+    const size_t np = (size_t)e->numPlayers;
+    GGL_CUDA(cudaMemcpyAsync(e->d_actionsScratch, h_actions, np * sizeof(int32_t), cudaMemcpyHostToDevice, s));
+    int rc = ggl_envset_step_second_half(e, e->d_actionsScratch, s);
+    if (rc) return rc;
+    if (h_rewards) GGL_CUDA(cudaMemcpyAsync(h_rewards, e->P.rewards, np * sizeof(float), cudaMemcpyDeviceToHost, s));
+    if (h_terminals) GGL_CUDA(cudaMemcpyAsync(h_terminals, e->P.terminals, (size_t)e->cfg.numArenas, cudaMemcpyDeviceToHost, s));
+    if (h_final_obs) GGL_CUDA(cudaMemcpyAsync(h_final_obs, e->P.obs, np * e->cfg.obsSize * sizeof(float), cudaMemcpyDeviceToHost, s));
     GGL_CUDA(cudaStreamSynchronize(s));
     return GGL_OK;
 }

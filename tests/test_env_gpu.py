@@ -169,3 +169,31 @@ def test_device_kickoff_reset_and_goal_terminal(ggl):
     assert abs(st2.ball.pos[1]) < 50 and abs(st2.ball.pos[2] - 93.15) < 5
     assert env.terminals.cpu().numpy()[1] == 0
     env.close()
+
+
+def test_pipelined_host_step_matches_device_path(ggl):
+    """ggl_envset_begin_step_host / finish_step_host (Reset + first half overlapped with the host policy, then second half)
+    must produce exactly what Reset + the fused device step produce from the same state and actions."""
+    import torch
+    A = ggl.EnvSet(32, 2, obs_kind=ggl.abi.OBS_ADVANCED, seed=5)
+    B = ggl.EnvSet(32, 2, obs_kind=ggl.abi.OBS_ADVANCED, seed=5)
+    n, na = A.num_players, A.num_actions
+    h_obs = np.zeros((n, A.obs_size), np.float32); h_mask = np.zeros((n, na), np.uint8)
+    h_rew = np.zeros(n, np.float32); h_term = np.zeros(A.num_arenas, np.uint8); h_fin = np.zeros((n, A.obs_size), np.float32)
+    h_act = np.zeros(n, np.int32)
+    acts = torch.zeros(n, dtype=torch.int32, device="cuda")
+    terms = 0
+    for i in range(170):
+        A.reset(); A.sync()
+        B.begin_step_host(h_obs, h_mask)
+        assert np.array_equal(A.obs.cpu().numpy(), h_obs) and np.array_equal(A.action_masks.cpu().numpy(), h_mask)
+        B.host_random_actions(h_mask, h_act, 900 + i)
+        assert h_mask[np.arange(n), h_act].all()
+        acts.copy_(torch.from_numpy(h_act))
+        A.step(acts, reset=False); A.sync()
+        B.finish_step_host(h_act, h_rew, h_term, h_fin)
+        assert np.array_equal(A.rewards.cpu().numpy(), h_rew) and np.array_equal(A.terminals.cpu().numpy(), h_term)
+        assert np.array_equal(A.obs.cpu().numpy(), h_fin)
+        terms += int((h_term != 0).sum())
+    assert terms > 0          # the no-touch timeout (150 steps) fired, so the Reset branch was exercised
+    A.close(); B.close()

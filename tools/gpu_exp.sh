@@ -1,5 +1,2 @@
-P=reinforcement-learning_b200
-for v in pn; do
-echo "=== gae variant $v"
-GGL_LIB_PATH=$P/libgigaenv_var_$v.so timeout 300 python bench.py --workload gae 2>&1 | python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('GAE ms', d['ms_per_step'], 'frac', d['roofline']['frac'])"
-done
+python -m pytest tests/test_env_gpu.py -m gpu -x -q 2>&1 | tail -3
+python bench.py --steps 100 --warmup 10 2>&1 | tail -1 | python -c "import sys,json; d=json.loads(sys.stdin.read()); print('value', d['value'], 'ms', d['ms_per_step'], 'e2e', d['e2e']['value'], 'cpu', d['cpu_baseline']['value'])"
