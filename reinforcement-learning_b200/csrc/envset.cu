@@ -415,6 +415,11 @@ extern "C" int ggl_debug_phase_cycles(uint64_t* out16, int reset) {
 #if defined(GGL_PHASE_TIMING)
     GGL_CUDA(cudaDeviceSynchronize());
     GGL_CUDA(cudaMemcpyFromSymbol(out16, g_phase_cycles, 16 * sizeof(uint64_t)));
+    if (reset == 2) {      // sub-phase table instead (collide_body: car-ball, car-mesh, car-planes, car-car, ball-mesh)
+        GGL_CUDA(cudaMemcpyFromSymbol(out16, g_sub_cycles, 16 * sizeof(uint64_t)));
+        uint64_t z[16] = {}; GGL_CUDA(cudaMemcpyToSymbol(g_sub_cycles, z, sizeof(z)));
+        return 1;
+    }
     if (reset) { uint64_t z[16] = {}; GGL_CUDA(cudaMemcpyToSymbol(g_phase_cycles, z, sizeof(z))); }
     return 1;
 #else

@@ -143,9 +143,8 @@ GGL_HD bool tri_overlaps_aabb(const Tri& t, V3 mn, V3 mx) {
     return true;
 }
 
-// one triangle of the (car, mesh) manifold `m`
-GGL_HDN void collide_car_tri(ArenaDev& A, ContactSink& S, ManifoldCtx& m, int ci, const Tri& t, V3 boxPos, const BoxGeom& bg, float cbt) {
-    CarDev& car = A.cars[ci];
+// Narrow phase of one (car, triangle) pair: pure function of the car's transform and the triangle. False = no contact point.
+GGL_HDN bool car_tri_narrow(const CarDev& car, const Tri& t, V3 boxPos, const BoxGeom& bg, float cbt, ClosestOut& o) {
     // early out: hitbox fully on one side of the triangle plane, further away than the breaking threshold
     V3 tn = normalized(cross(t.v1 - t.v0, t.v2 - t.v0));
     const M3 invB = inverse(car.basis);
@@ -153,16 +152,21 @@ GGL_HDN void collide_car_tri(ArenaDev& A, ContactSink& S, ManifoldCtx& m, int ci
         V3 lp = box_support(bg.full, mul(invB, tn));
         V3 wp = mul(car.basis, lp) + boxPos;
         float dist = dot(tn, t.v0) - dot(tn, wp);
-        if (dist > cbt) return;
+        if (dist > cbt) return false;
         tn = tn * -1.f;
     }
     BoxTri s;
     s.basisA = car.basis; s.posA = boxPos; s.he = bg.core; s.marginA = bg.margin;
     s.t0 = t.v0; s.t1 = t.v1; s.t2 = t.v2; s.posB = v3(0, 0, 0);
     float md = bg.margin + 0.f + cbt;
-    ClosestOut o;
-    if (!box_tri_closest(s, md * md, o)) return;
-    if (o.distance > cbt) return;
+    if (!box_tri_closest(s, md * md, o)) return false;
+    if (o.distance > cbt) return false;
+    return true;
+}
+
+// Adds the contact point of a narrow-phase hit to the (car, mesh) manifold `m` (order-dependent: replacement policy)
+GGL_HD void car_tri_emit(ArenaDev& A, ContactSink& S, ManifoldCtx& m, int ci, const Tri& t, const ClosestOut& o) {
+    CarDev& car = A.cars[ci];
     V3 pA = o.pointOnB + o.normalOnB * o.distance;
     Contact c;
     c.normal = o.normalOnB; c.dist = o.distance;
@@ -179,19 +183,23 @@ GGL_HDN void collide_car_tri(ArenaDev& A, ContactSink& S, ManifoldCtx& m, int ci
     S.buf[row].relB = pB;
 }
 
-GGL_HDN void collide_car_mesh(ArenaDev& A, ContactSink& S, const WorldDev& W, int ci) {
-    if (W.numTris <= 0) return;
+GGL_HD V3 car_box_pos(const CarDev& car) { return car.pos + mul(car.basis, car_hitbox_offset()); }
+
+// Stage 1 (the car's lane): candidate triangles of car `ci`, de-duplicated and in (mesh, triangle) index order -- one
+// manifold per mesh body, visited in the reference's order.
+GGL_HDN void car_mesh_gather(ArenaDev& A, const WorldDev& W, int ci) {
+    A.meshCandN[ci] = 0; A.meshHitN[ci] = 0; A.meshHitOverflow[ci] = 0;
+    if (W.numTris <= 0 || A.cars[ci].rbDisabled) return;
     const CarDev& car = A.cars[ci];
     const BoxGeom bg = car_box();
-    const float cbt = car_cbt();
-    V3 boxPos = car.pos + mul(car.basis, car_hitbox_offset());
+    V3 boxPos = car_box_pos(car);
     V3 ext = v3(dot(vabs(car.basis.r0), bg.full), dot(vabs(car.basis.r1), bg.full), dot(vabs(car.basis.r2), bg.full));
     V3 mn = boxPos - ext, mx = boxPos + ext;
     int x0 = grid_coord(mn.x, W.gridMin.x, W.invCellSize, W.gx), x1 = grid_coord(mx.x, W.gridMin.x, W.invCellSize, W.gx);
     int y0 = grid_coord(mn.y, W.gridMin.y, W.invCellSize, W.gy), y1 = grid_coord(mx.y, W.gridMin.y, W.invCellSize, W.gy);
     int z0 = grid_coord(mn.z, W.gridMin.z, W.invCellSize, W.gz), z1 = grid_coord(mx.z, W.gridMin.z, W.invCellSize, W.gz);
-    // candidate triangles, de-duplicated and in (mesh, triangle) index order: one manifold per mesh body
-    int cand[24]; int nc = 0;
+    uint16_t* cand = A.meshCand[ci];
+    int nc = 0;
     for (int z = z0; z <= z1; z++)
         for (int y = y0; y <= y1; y++)
             for (int x = x0; x <= x1; x++) {
@@ -200,19 +208,61 @@ GGL_HDN void collide_car_mesh(ArenaDev& A, ContactSink& S, const WorldDev& W, in
                     int ti = W.cellTris[k];
                     if (!tri_overlaps_aabb(W.tris[ti], mn, mx)) continue;
                     int pos = 0; bool dup = false;
-                    while (pos < nc && cand[pos] <= ti) { dup |= cand[pos] == ti; pos++; }
-                    if (dup || nc >= 24) continue;
+                    while (pos < nc && (int)cand[pos] <= ti) { dup |= (int)cand[pos] == ti; pos++; }
+                    if (dup || nc >= kMaxMeshCand) continue;
                     for (int q = nc; q > pos; q--) cand[q] = cand[q - 1];
-                    cand[pos] = ti; nc++;
+                    cand[pos] = (uint16_t)ti; nc++;
                 }
             }
+    A.meshCandN[ci] = (uint8_t)nc;
+}
+
+// Stage 2 (any lane): narrow phase of candidate `k` of car `ci`; a hit is appended to the car's hit list (any order).
+GGL_HD void car_mesh_narrow(ArenaDev& A, const WorldDev& W, int ci, int k) {
+    const CarDev& car = A.cars[ci];
+    ClosestOut o;
+    if (!car_tri_narrow(car, W.tris[A.meshCand[ci][k]], car_box_pos(car), car_box(), car_cbt(), o)) return;
+#if defined(__CUDA_ARCH__)
+    const uint32_t slot = atomicAdd(&A.meshHitN[ci], 1u);
+#else
+    const uint32_t slot = A.meshHitN[ci]++;
+#endif
+    if (slot >= (uint32_t)kMaxMeshHit) { A.meshHitOverflow[ci] = 1; return; }
+    CarTriHit& h = A.meshHit[ci][slot];
+    h.normalOnB = o.normalOnB; h.pointOnB = o.pointOnB; h.distance = o.distance; h.cand = (uint32_t)k;
+}
+
+// Stage 3 (the car's lane): contact points into the car's manifolds in candidate order.
+GGL_HDN void car_mesh_emit(ArenaDev& A, ContactSink& S, const WorldDev& W, int ci) {
+    const int nc = A.meshCandN[ci];
+    if (nc == 0) return;
     int curMesh = -1;
     ManifoldCtx m = manifold_begin(S);
-    for (int k = 0; k < nc; k++) {
-        const Tri& t = W.tris[cand[k]];
+    if (A.meshHitOverflow[ci]) {
+        // more hits than the staging holds: redo this car serially (same results, candidate order)
+        const CarDev& car = A.cars[ci];
+        for (int k = 0; k < nc; k++) {
+            const Tri& t = W.tris[A.meshCand[ci][k]];
+            int mesh = (int)(t.flags >> TRI_MESH_SHIFT);
+            if (mesh != curMesh) { m = manifold_begin(S); curMesh = mesh; }
+            ClosestOut o;
+            if (car_tri_narrow(car, t, car_box_pos(car), car_box(), car_cbt(), o)) car_tri_emit(A, S, m, ci, t, o);
+        }
+        return;
+    }
+    const int nh = (int)A.meshHitN[ci];
+    uint32_t done = 0;
+    for (int n = 0; n < nh; n++) {
+        int best = -1;                                   // next hit in candidate order
+        for (int q = 0; q < nh; q++)
+            if (!(done & (1u << q)) && (best < 0 || A.meshHit[ci][q].cand < A.meshHit[ci][best].cand)) best = q;
+        done |= 1u << best;
+        const CarTriHit& h = A.meshHit[ci][best];
+        const Tri& t = W.tris[A.meshCand[ci][h.cand]];
         int mesh = (int)(t.flags >> TRI_MESH_SHIFT);
         if (mesh != curMesh) { m = manifold_begin(S); curMesh = mesh; }
-        collide_car_tri(A, S, m, ci, t, boxPos, bg, cbt);
+        ClosestOut o; o.normalOnB = h.normalOnB; o.pointOnB = h.pointOnB; o.distance = h.distance;
+        car_tri_emit(A, S, m, ci, t, o);
     }
 }
 

@@ -13,24 +13,6 @@
 
 namespace ggl {
 
-// Phase timing (profiling build only, -DGGL_PHASE_TIMING -> libgigaenv_cuda_prof.so): the leader lane of every arena adds
-// the SM cycles it spent in each tick phase (including the time its warp ran other arenas' divergent paths) to a global
-// table read back with ggl_debug_phase_cycles. Compiled out of the product library.
-#if defined(GGL_PHASE_TIMING) && defined(__CUDACC__)
-__device__ unsigned long long g_phase_cycles[16];
-__device__ unsigned long long g_arena_phase_cycles[8192][16];     // per-arena breakdown of the first 8192 arenas
-#endif
-#if defined(GGL_PHASE_TIMING) && defined(__CUDA_ARCH__)
-#define GGL_PH_BEGIN() long long _ph_t = clock64()
-#define GGL_PH_RESET() _ph_t = clock64()
-#define GGL_PH(k) do { long long _n = clock64(); if (ex.lane() == 0) { atomicAdd(&g_phase_cycles[k], (unsigned long long)(_n - _ph_t)); \
-        if (ex.arena_ < 8192) g_arena_phase_cycles[ex.arena_][k] += (unsigned long long)(_n - _ph_t); } _ph_t = _n; } while (0)
-#else
-#define GGL_PH_BEGIN() do {} while (0)
-#define GGL_PH_RESET() do {} while (0)
-#define GGL_PH(k) do {} while (0)
-#endif
-
 struct ExecSerial {
     GGL_HD int lane() const { return 0; }
     GGL_HD int lanes() const { return 1; }
@@ -193,6 +175,20 @@ GGL_HD void arena_tick(ArenaDev& A, const WorldDev& W, const Exec& ex) {
     for (int b = ex.lane(); b < nb; b += ex.lanes()) world_forces(A, b);
     ex.sync();      // the car-ball callback reads the damped ball velocity
     GGL_PH(4);
+    // car vs mesh in three stages: candidates per car, narrow phase (GJK/EPA, the expensive part) of ALL (car, triangle)
+    // pairs of the arena spread over the lanes of the group, then the order-dependent manifold updates per car
+    for (int c = ex.lane(); c < A.numCars; c += ex.lanes()) car_mesh_gather(A, W, c);
+    ex.sync();
+    {
+        int total = 0;
+        for (int c = 0; c < A.numCars; c++) total += A.meshCandN[c];
+        for (int p = ex.lane(); p < total; p += ex.lanes()) {
+            int c = 0, k = p;
+            while (k >= (int)A.meshCandN[c]) { k -= A.meshCandN[c]; c++; }
+            car_mesh_narrow(A, W, c, k);
+        }
+    }
+    ex.sync();
     for (int b = ex.lane(); b < nb; b += ex.lanes()) collide_body(A, W, b);
     ex.sync();
     GGL_PH(5);

@@ -140,6 +140,11 @@ struct EnvPlayer {     // per players[] slot bookkeeping of the env layer (GameS
 // Layout: [header .. contacts][cars].  cars[] is LAST so that a lane group stages only the first numCars cars of an arena in
 // shared memory (smem slot = arena_slot_bytes(numCars)); contacts[] is per-tick scratch that lives in the slot and is only
 // written back to HBM by the raw-tick kernel (tests read it through ggl_envset_get_contacts).
+// narrow-phase result of one (car, mesh triangle) candidate that produced a contact point (see sim_boxtri.cuh)
+constexpr int kMaxMeshCand = 24;        // candidate triangles per car per tick
+constexpr int kMaxMeshHit = 8;          // stored narrow-phase hits per car; more fall back to the serial path
+struct CarTriHit { V3 normalOnB, pointOnB; float distance; uint32_t cand; };
+
 struct alignas(16) ArenaDev {
     uint64_t tickCount;
     int32_t numCars, _pad0;
@@ -165,6 +170,12 @@ struct alignas(16) ArenaDev {
     uint8_t cntWorld, ballAwake, cntBall[kMaxCars], cntRest[kMaxCars], _pad4[2];
     uint8_t island[8], _pad5[8];                   // island[b] = lowest body index of the contact island body b belongs to
     Contact contacts[kMaxContacts];
+    // car-vs-mesh staging: candidates per car (gathered by the car's lane), hits found by all lanes of the group
+    uint16_t meshCand[kMaxCars][kMaxMeshCand];
+    uint8_t meshCandN[kMaxCars], meshHitOverflow[kMaxCars];
+    uint32_t meshHitN[kMaxCars];
+    uint8_t _pad6[12];
+    CarTriHit meshHit[kMaxCars][kMaxMeshHit];
     alignas(16) CarDev cars[kMaxCars];
 };
 static_assert(sizeof(CarDev) % 16 == 0, "CarDev must be a multiple of 16 bytes (vector staging)");

@@ -15,6 +15,7 @@
 //   RocketSim/src/Sim/Arena/Arena.cpp:218-427                                contact callbacks (car-ball, car-car, car-world, ball-world)
 #pragma once
 #include "sim_car.cuh"
+#include "sim_prof.cuh"
 #include "sim_edge.cuh"
 
 namespace ggl {
@@ -555,7 +556,7 @@ GGL_HDN void solve_island(ArenaDev& A, int rep) {
 // ---------------------------------------------------------------------------------------------- world step
 // defined in sim_boxbox.cuh / sim_boxtri.cuh
 GGL_HDN void collide_car_car(ArenaDev& A, ContactSink& S, int lo, int hi);
-GGL_HDN void collide_car_mesh(ArenaDev& A, ContactSink& S, const WorldDev& W, int ci);
+GGL_HDN void car_mesh_emit(ArenaDev& A, ContactSink& S, const WorldDev& W, int ci);
 GGL_HD void car_car_callback(ArenaDev& A, int i1, int i2, V3 localA, V3 localB);
 
 // Contact windows inside A.contacts: [0,4) ball-world, [4,4+P) one car-ball row per car, then P windows of
@@ -586,7 +587,9 @@ GGL_HDN void collide_body(ArenaDev& A, const WorldDev& W, int b) {
     if (b == 0) {
         ContactSink S; S.buf = A.contacts; S.n = 0; S.cap = 4;
         if (A.ball.active) {
+            GGL_SUB_BEGIN();
             collide_ball_mesh(A, S, W);
+            GGL_SUB(4);
             collide_ball_plane(A, S, v3(0, 0, 1), v3(0, 0, 0));
             collide_ball_plane(A, S, v3(0, 0, -1), v3(0, 0, hz));
             collide_ball_plane(A, S, v3(1, 0, 0), v3(-ex, 0, hz / 2));
@@ -600,13 +603,18 @@ GGL_HDN void collide_body(ArenaDev& A, const WorldDev& W, int b) {
     ContactSink SB; SB.buf = A.contacts + 4 + i; SB.n = 0; SB.cap = 1;
     ContactSink S; S.buf = A.contacts + 4 + P + i * R; S.n = 0; S.cap = R;
     if (!A.cars[i].rbDisabled) {
+        GGL_SUB_BEGIN();
         collide_car_ball(A, SB, i);
-        collide_car_mesh(A, S, W, i);
+        GGL_SUB(0);
+        car_mesh_emit(A, S, W, i);             // candidates and narrow phase ran in the two stages before (sim_tick.cuh)
+        GGL_SUB(1);
         collide_car_plane(A, S, i, v3(0, 0, 1), v3(0, 0, 0));
         collide_car_plane(A, S, i, v3(0, 0, -1), v3(0, 0, hz));
         collide_car_plane(A, S, i, v3(1, 0, 0), v3(-ex, 0, hz / 2));
         collide_car_plane(A, S, i, v3(-1, 0, 0), v3(ex, 0, hz / 2));
+        GGL_SUB(2);
         for (int j = i + 1; j < P; j++) collide_car_car(A, S, i, j);
+        GGL_SUB(3);
     }
     A.cntBall[i] = (uint8_t)SB.n;
     A.cntRest[i] = (uint8_t)S.n;

@@ -1,2 +1,4 @@
-python -m pytest tests/test_env_gpu.py -m gpu -x -q 2>&1 | tail -3
-python bench.py --steps 100 --warmup 10 2>&1 | tail -1 | python -c "import sys,json; d=json.loads(sys.stdin.read()); print('value', d['value'], 'ms', d['ms_per_step'], 'e2e', d['e2e']['value'], 'cpu', d['cpu_baseline']['value'])"
+P=reinforcement-learning_b200
+python -m pytest tests/test_env_gpu.py tests/test_host_mirror.py -m gpu -x -q 2>&1 | tail -3
+python tools/phase_profile.py 160 20 2>&1 | head -1
+GGL_LIB_PATH=$P/libgigaenv_cuda_prof.so python tools/phase_profile.py 160 20 2>&1 | tail -38

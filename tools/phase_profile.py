@@ -49,6 +49,10 @@ def main():
             print("%-18s %6.2f %%   %.0f cycles/arena/step" % (n, 100.0 * v / tot, v / arenas / steps))
 
 
+    sub = (C.c_uint64 * 16)()
+    if L.ggl_debug_phase_cycles(sub, 2) == 1:
+        print("collide_body sub-phases (cycles summed over lanes, per arena-step): " +
+              ", ".join("%s %.0f" % (n, v / arenas / steps) for n, v in zip(["car-ball", "car-mesh", "car-planes", "car-car", "ball-mesh"], sub)))
     if L.ggl_debug_arena_phase_cycles(C.c_void_p(per.ctypes.data), na, 1) == 1:
         per = per.astype(np.float64) / steps
         tot_a = per.sum(1)
