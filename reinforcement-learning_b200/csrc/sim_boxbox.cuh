@@ -301,6 +301,12 @@ GGL_HDN void collide_car_car(ArenaDev& A, ContactSink& S, int lo, int hi) {
     if (a.rbDisabled || b.rbDisabled) return;      // CF_NO_CONTACT_RESPONSE: the manifold is never solved (needsResponse)
     const BoxGeom bg = car_box();
     V3 pa = a.pos + mul(a.basis, car_hitbox_offset()), pb = b.pos + mul(b.basis, car_hitbox_offset());
+    // cull (exact): boxes inside disjoint bounding spheres are disjoint, so the SAT below would find a separating axis
+    // and report no point (btBoxBoxDetector has no margin)
+    {
+        const float r2 = 2.0002f * len(bg.full);
+        if (len2(pa - pb) > r2 * r2) return;
+    }
     // child AABB overlap test of the compound-compound algorithm
     V3 ea = v3(dot(vabs(a.basis.r0), bg.full), dot(vabs(a.basis.r1), bg.full), dot(vabs(a.basis.r2), bg.full));
     V3 eb = v3(dot(vabs(b.basis.r0), bg.full), dot(vabs(b.basis.r1), bg.full), dot(vabs(b.basis.r2), bg.full));

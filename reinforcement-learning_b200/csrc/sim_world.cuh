@@ -235,6 +235,8 @@ GGL_HD void collide_car_plane(ArenaDev& A, ContactSink& S, int ci, V3 n, V3 orig
     CarDev& car = A.cars[ci];
     const BoxGeom bg = car_box();
     V3 boxPos = car.pos + mul(car.basis, car_hitbox_offset());
+    // cull (exact): the support vertex is never further inside than the box centre minus the half diagonal
+    if (dot(n, boxPos - origin) - len(bg.full) * 1.0001f > car_cbt()) return;
     V3 dirLocal = tmul(car.basis, -n);
     V3 vtx = v3(dirLocal.x >= 0.f ? bg.full.x : -bg.full.x, dirLocal.y >= 0.f ? bg.full.y : -bg.full.y, dirLocal.z >= 0.f ? bg.full.z : -bg.full.z);
     V3 inPlane = (boxPos - origin) + mul(car.basis, vtx);
