@@ -65,26 +65,32 @@ __device__ __forceinline__ void write_player_rows(const ArenaDev& A, const EnvCf
 // ---- blob staging: the whole warp moves each of its arenas with 16-byte accesses (512 contiguous bytes per instruction)
 extern __shared__ __align__(16) unsigned char g_arena_smem[];
 
-__device__ __forceinline__ void stage_in(const EnvCfg& cfg, const EnvDevPtrs& P, int slotBytes) {
+// `full` = 0 skips the per-tick scratch in the middle of the blob (contact rows, car-mesh staging: ~3.9 KB of 7 KB for 2v2), which
+// is dead between env steps; the raw-tick debug path (ggl_arena_step + ggl_envset_get_contacts) moves everything.
+__device__ __forceinline__ void stage_in(const EnvCfg& cfg, const EnvDevPtrs& P, int slotBytes, int full) {
     const int lane = threadIdx.x, n16 = slotBytes >> 4;
+    const int s0 = full ? n16 : (int)(arena_persist_bytes() >> 4), s1 = (int)(arena_hdr_bytes() >> 4);
     for (int g = 0; g < kArenasPerBlock; g++) {
         const int arena = blockIdx.x * kArenasPerBlock + g;
         if (arena >= cfg.numArenas) break;
         const uint4* src = reinterpret_cast<const uint4*>(P.arenas + arena);
         uint4* dst = reinterpret_cast<uint4*>(g_arena_smem + (size_t)g * slotBytes);
-        for (int i = lane; i < n16; i += kBlock) dst[i] = __ldg(src + i);
+        for (int i = lane; i < s0; i += kBlock) dst[i] = __ldg(src + i);
+        for (int i = s1 + lane; i < n16; i += kBlock) dst[i] = __ldg(src + i);
     }
     __syncwarp();
 }
-__device__ __forceinline__ void stage_out(const EnvCfg& cfg, const EnvDevPtrs& P, int slotBytes) {
+__device__ __forceinline__ void stage_out(const EnvCfg& cfg, const EnvDevPtrs& P, int slotBytes, int full) {
     __syncwarp();
     const int lane = threadIdx.x, n16 = slotBytes >> 4;
+    const int s0 = full ? n16 : (int)(arena_persist_bytes() >> 4), s1 = (int)(arena_hdr_bytes() >> 4);
     for (int g = 0; g < kArenasPerBlock; g++) {
         const int arena = blockIdx.x * kArenasPerBlock + g;
         if (arena >= cfg.numArenas) break;
         uint4* dst = reinterpret_cast<uint4*>(P.arenas + arena);
         const uint4* src = reinterpret_cast<const uint4*>(g_arena_smem + (size_t)g * slotBytes);
-        for (int i = lane; i < n16; i += kBlock) dst[i] = src[i];
+        for (int i = lane; i < s0; i += kBlock) dst[i] = src[i];
+        for (int i = s1 + lane; i < n16; i += kBlock) dst[i] = src[i];
     }
 }
 __device__ __forceinline__ ArenaDev& my_arena(int slotBytes) {
@@ -123,7 +129,7 @@ __global__ void __launch_bounds__(kBlock) env_reset_kernel(EnvCfg cfg, EnvDevPtr
 __global__ void __launch_bounds__(kBlock, GGL_MINBLOCKS) env_step_kernel(EnvCfg cfg, EnvDevPtrs P, const int32_t* __restrict__ actions, int doFirst,
                                                           int doSecond, int slotBytes) {
     GGL_PH_BEGIN();
-    stage_in(cfg, P, slotBytes);
+    stage_in(cfg, P, slotBytes, 0);
     const int arena = blockIdx.x * kArenasPerBlock + threadIdx.x / kGroup;
     if (arena < cfg.numArenas) {
         const ExecGroup ex = make_exec();
@@ -177,19 +183,19 @@ __global__ void __launch_bounds__(kBlock, GGL_MINBLOCKS) env_step_kernel(EnvCfg 
             GGL_PH(12);
         }
     }
-    stage_out(cfg, P, slotBytes);
+    stage_out(cfg, P, slotBytes, 0);
 }
 
 // raw Arena::Step(ticks)
 __global__ void __launch_bounds__(kBlock) arena_step_kernel(EnvCfg cfg, EnvDevPtrs P, int ticks, int slotBytes) {
-    stage_in(cfg, P, slotBytes);
+    stage_in(cfg, P, slotBytes, 1);
     const int arena = blockIdx.x * kArenasPerBlock + threadIdx.x / kGroup;
     if (arena < cfg.numArenas) {
         const ExecGroup ex = make_exec();
         ArenaDev& A = my_arena(slotBytes);
         for (int t = 0; t < ticks; t++) arena_tick(A, P.world, ex);
     }
-    stage_out(cfg, P, slotBytes);
+    stage_out(cfg, P, slotBytes, 1);
 }
 
 // uniformly random mask-valid action per player (bench / smoke helper): k-th set bit of the mask row, k from a hash

@@ -169,7 +169,7 @@ struct alignas(16) ArenaDev {
     uint32_t bodiesInContact;                      // bit b: body b (0 ball, 1 + c car c) has a solver row this tick
     uint8_t cntWorld, ballAwake, cntBall[kMaxCars], cntRest[kMaxCars], _pad4[2];
     uint8_t island[8], _pad5[8];                   // island[b] = lowest body index of the contact island body b belongs to
-    Contact contacts[kMaxContacts];
+    alignas(16) Contact contacts[kMaxContacts];    // from here to cars[]: per-tick scratch that never needs to travel to HBM
     // car-vs-mesh staging: candidates per car (gathered by the car's lane), hits found by all lanes of the group
     uint16_t meshCand[kMaxCars][kMaxMeshCand];
     uint8_t meshCandN[kMaxCars], meshHitOverflow[kMaxCars];
@@ -181,6 +181,7 @@ struct alignas(16) ArenaDev {
 static_assert(sizeof(CarDev) % 16 == 0, "CarDev must be a multiple of 16 bytes (vector staging)");
 static_assert(sizeof(ArenaDev) % 16 == 0, "ArenaDev must be a multiple of 16 bytes (vector staging)");
 GGL_HD size_t arena_hdr_bytes() { return offsetof(ArenaDev, cars); }
+GGL_HD size_t arena_persist_bytes() { return offsetof(ArenaDev, contacts); }     // header part that is state, not scratch
 GGL_HD size_t arena_slot_bytes(int numCars) { return offsetof(ArenaDev, cars) + (size_t)numCars * sizeof(CarDev); }
 
 // ------------------------------------------------------------------ static world (shared by all arenas, read-only)
