@@ -9,11 +9,14 @@
 
 using namespace ggl;
 
+struct LaunchGeom { int warps, grid; size_t smem; };
+
 struct ggl_envset {
     EnvCfg cfg;
     EnvDevPtrs P;
     int device;
     int numPlayers;
+    LaunchGeom geom;
     WorldHost worldHost;
     Tri* d_tris; int* d_cellStart; int* d_cellTris;
     ArenaDev* d_reset;
@@ -28,9 +31,26 @@ struct ggl_envset {
 
 namespace {
 
-int grid_for(const EnvCfg& cfg) { return (cfg.numArenas + kArenasPerBlock - 1) / kArenasPerBlock; }
+int grid_for(const EnvCfg& cfg) { return (cfg.numArenas + kArenasPerBlock - 1) / kArenasPerBlock; }   // reset kernel
 int slot_bytes(const EnvCfg& cfg) { return (int)arena_slot_bytes(cfg.numCars); }
-size_t smem_for(const EnvCfg& cfg) { return (size_t)kArenasPerBlock * slot_bytes(cfg); }
+
+// Launch geometry of the step kernels: as many warps per block (<= kMaxWarps, <= what fits in 227 KB of shared memory) as it
+// takes to cover the arenas with one block per SM, so that 4096 arenas of 2v2 run as 147 blocks of 7 warps in a single wave.
+LaunchGeom launch_geom(const EnvCfg& cfg, int numSMs) {
+    const int totalWarps = (cfg.numArenas + kArenasPerWarp - 1) / kArenasPerWarp;
+    const size_t perWarp = (size_t)kArenasPerWarp * slot_bytes(cfg);
+    int fit = (int)((227 * 1024 - 1024) / perWarp);
+    if (fit > kMaxWarps) fit = kMaxWarps;
+    if (fit < 1) fit = 1;
+    int warps = (totalWarps + numSMs - 1) / numSMs;
+    if (warps > fit) warps = fit;
+    if (warps < 1) warps = 1;
+    LaunchGeom g;
+    g.warps = warps;
+    g.grid = (totalWarps + warps - 1) / warps;
+    g.smem = perWarp * warps;
+    return g;
+}
 
 int obs_size(int kind, int cars) { return 51 + (kind == GGL_OBS_ADVANCED ? 29 : 19) * cars; }
 
@@ -157,8 +177,14 @@ extern "C" int ggl_envset_create(const ggl_envset_desc* d, ggl_envset** out) {
     GGL_CUDA(cudaStreamCreateWithFlags(&e->copyStream, cudaStreamNonBlocking));
     GGL_CUDA(cudaEventCreateWithFlags(&e->evReset, cudaEventDisableTiming));
     GGL_CUDA(cudaEventCreateWithFlags(&e->evCopied, cudaEventDisableTiming));
-    GGL_CUDA(cudaFuncSetAttribute(env_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_for(e->cfg)));
-    GGL_CUDA(cudaFuncSetAttribute(arena_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_for(e->cfg)));
+    {
+        int sms = 148;
+        GGL_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, d->device));
+        e->geom = launch_geom(e->cfg, sms);
+        // the attribute is per function, not per envset: always allow the largest block any envset may ask for
+        GGL_CUDA(cudaFuncSetAttribute(env_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024));
+        GGL_CUDA(cudaFuncSetAttribute(arena_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024));
+    }
     // EnvSet ctor: reset every arena once (EnvSet.cpp:106-110)
     EnvCfg kc = e->cfg; kc.stateSetter = GGL_SETTER_KICKOFF;
     env_reset_kernel<<<grid_for(e->cfg), kBlock, 0, 0>>>(kc, e->P, 1);
@@ -187,27 +213,27 @@ extern "C" int ggl_envset_reset(ggl_envset* e, void* stream) {
 }
 extern "C" int ggl_envset_step_first_half(ggl_envset* e, void* stream) {
     ENV_CHECK(e);
-    env_step_kernel<<<grid_for(e->cfg), kBlock, smem_for(e->cfg), (cudaStream_t)stream>>>(e->cfg, e->P, nullptr, 1, 0, slot_bytes(e->cfg));
+    env_step_kernel<<<e->geom.grid, 32 * e->geom.warps, e->geom.smem, (cudaStream_t)stream>>>(e->cfg, e->P, nullptr, 1, 0, slot_bytes(e->cfg));
     GGL_LAUNCH_CHECK(); ggl::count_launch();
     return GGL_OK;
 }
 extern "C" int ggl_envset_step_second_half(ggl_envset* e, const int32_t* d_actions, void* stream) {
     ENV_CHECK(e);
     if (!d_actions) { ggl::set_error("null actions"); return GGL_ERR_INVALID; }
-    env_step_kernel<<<grid_for(e->cfg), kBlock, smem_for(e->cfg), (cudaStream_t)stream>>>(e->cfg, e->P, d_actions, 0, 1, slot_bytes(e->cfg));
+    env_step_kernel<<<e->geom.grid, 32 * e->geom.warps, e->geom.smem, (cudaStream_t)stream>>>(e->cfg, e->P, d_actions, 0, 1, slot_bytes(e->cfg));
     GGL_LAUNCH_CHECK(); ggl::count_launch();
     return GGL_OK;
 }
 extern "C" int ggl_envset_step(ggl_envset* e, const int32_t* d_actions, void* stream) {
     ENV_CHECK(e);
     if (!d_actions) { ggl::set_error("null actions"); return GGL_ERR_INVALID; }
-    env_step_kernel<<<grid_for(e->cfg), kBlock, smem_for(e->cfg), (cudaStream_t)stream>>>(e->cfg, e->P, d_actions, 1, 1, slot_bytes(e->cfg));
+    env_step_kernel<<<e->geom.grid, 32 * e->geom.warps, e->geom.smem, (cudaStream_t)stream>>>(e->cfg, e->P, d_actions, 1, 1, slot_bytes(e->cfg));
     GGL_LAUNCH_CHECK(); ggl::count_launch();
     return GGL_OK;
 }
 extern "C" int ggl_arena_step(ggl_envset* e, int ticks, void* stream) {
     ENV_CHECK(e);
-    arena_step_kernel<<<grid_for(e->cfg), kBlock, smem_for(e->cfg), (cudaStream_t)stream>>>(e->cfg, e->P, ticks, slot_bytes(e->cfg));
+    arena_step_kernel<<<e->geom.grid, 32 * e->geom.warps, e->geom.smem, (cudaStream_t)stream>>>(e->cfg, e->P, ticks, slot_bytes(e->cfg));
     GGL_LAUNCH_CHECK(); ggl::count_launch();
     return GGL_OK;
 }

@@ -17,6 +17,7 @@ struct ExecSerial {
     GGL_HD int lane() const { return 0; }
     GGL_HD int lanes() const { return 1; }
     GGL_HD void sync() const {}
+    GGL_HD void phase_sync() const {}
 };
 
 // Boost pad table, RocketSim order: 6 big pads then 28 small ones (RLConst.h:192-253), Unreal units.
@@ -167,6 +168,7 @@ GGL_HD void arena_tick(ArenaDev& A, const WorldDev& W, const Exec& ex) {
     for (int r = ex.lane(); r < 4 * A.numCars; r += ex.lanes())
         if (!A.cars[r >> 2].isDemoed) wheel_first(A, W, r >> 2, r & 3);
     ex.sync();
+    ex.phase_sync();
     GGL_PH(2);
     for (int c = ex.lane(); c < A.numCars; c += ex.lanes()) car_pre_tick_c(A, c);
     ex.sync();
@@ -191,6 +193,7 @@ GGL_HD void arena_tick(ArenaDev& A, const WorldDev& W, const Exec& ex) {
     ex.sync();
     for (int b = ex.lane(); b < nb; b += ex.lanes()) collide_body(A, W, b);
     ex.sync();
+    ex.phase_sync();
     GGL_PH(5);
     if (ex.lane() == 0) gather_contacts(A);
     ex.sync();
@@ -201,6 +204,7 @@ GGL_HD void arena_tick(ArenaDev& A, const WorldDev& W, const Exec& ex) {
         else if (A.island[b] == b) solve_island(A, b);
     }
     ex.sync();
+    ex.phase_sync();
     GGL_PH(7);
     for (int b = ex.lane(); b < nb; b += ex.lanes()) world_integrate(A, b);
     ex.sync();
@@ -213,6 +217,7 @@ GGL_HD void arena_tick(ArenaDev& A, const WorldDev& W, const Exec& ex) {
     GGL_PH(10);
     if (ex.lane() == 0) phase_finish(A);
     ex.sync();
+    ex.phase_sync();
     GGL_PH(11);
 }
 

@@ -142,7 +142,8 @@ struct EnvPlayer {     // per players[] slot bookkeeping of the env layer (GameS
 // written back to HBM by the raw-tick kernel (tests read it through ggl_envset_get_contacts).
 // narrow-phase result of one (car, mesh triangle) candidate that produced a contact point (see sim_boxtri.cuh)
 constexpr int kMaxMeshCand = 24;        // candidate triangles per car per tick
-constexpr int kMaxMeshHit = 8;          // stored narrow-phase hits per car; more fall back to the serial path
+constexpr int kMaxMeshHit = 6;          // stored narrow-phase hits per car; more fall back to the serial path (6 keeps the 2v2
+                                        // slot at 7.7 KB = 7 one-warp blocks per SM, i.e. 4096 arenas in a single wave)
 struct CarTriHit { V3 normalOnB, pointOnB; float distance; uint32_t cand; };
 
 struct alignas(16) ArenaDev {
