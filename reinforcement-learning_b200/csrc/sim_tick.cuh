@@ -13,6 +13,11 @@
 
 namespace ggl {
 
+// block-level meeting points of the tick (bit k = after phase k, see ExecGroup::phase_sync): rays, contacts, solver, end
+#ifndef GGL_PSYNC_MASK
+#define GGL_PSYNC_MASK (4 | 32 | 128 | 2048)
+#endif
+
 struct ExecSerial {
     GGL_HD int lane() const { return 0; }
     GGL_HD int lanes() const { return 1; }
@@ -164,14 +169,16 @@ GGL_HD void arena_tick(ArenaDev& A, const WorldDev& W, const Exec& ex) {
     GGL_PH(0);
     for (int c = ex.lane(); c < A.numCars; c += ex.lanes()) car_pre_tick_a(A, c);
     ex.sync();
+    if (GGL_PSYNC_MASK & 2) ex.phase_sync();
     GGL_PH(1);
     for (int r = ex.lane(); r < 4 * A.numCars; r += ex.lanes())
         if (!A.cars[r >> 2].isDemoed) wheel_first(A, W, r >> 2, r & 3);
     ex.sync();
-    ex.phase_sync();
+    if (GGL_PSYNC_MASK & 4) ex.phase_sync();
     GGL_PH(2);
     for (int c = ex.lane(); c < A.numCars; c += ex.lanes()) car_pre_tick_c(A, c);
     ex.sync();
+    if (GGL_PSYNC_MASK & 8) ex.phase_sync();
     GGL_PH(3);
     const int nb = 1 + A.numCars;
     for (int b = ex.lane(); b < nb; b += ex.lanes()) world_forces(A, b);
@@ -193,10 +200,11 @@ GGL_HD void arena_tick(ArenaDev& A, const WorldDev& W, const Exec& ex) {
     ex.sync();
     for (int b = ex.lane(); b < nb; b += ex.lanes()) collide_body(A, W, b);
     ex.sync();
-    ex.phase_sync();
+    if (GGL_PSYNC_MASK & 32) ex.phase_sync();
     GGL_PH(5);
     if (ex.lane() == 0) gather_contacts(A);
     ex.sync();
+    if (GGL_PSYNC_MASK & 64) ex.phase_sync();
     GGL_PH(6);
     // one lane per contact island (its lowest body index); bodies without a row take the free-body path on their own lane
     for (int b = ex.lane(); b < nb; b += ex.lanes()) {
@@ -204,20 +212,23 @@ GGL_HD void arena_tick(ArenaDev& A, const WorldDev& W, const Exec& ex) {
         else if (A.island[b] == b) solve_island(A, b);
     }
     ex.sync();
-    ex.phase_sync();
+    if (GGL_PSYNC_MASK & 128) ex.phase_sync();
     GGL_PH(7);
     for (int b = ex.lane(); b < nb; b += ex.lanes()) world_integrate(A, b);
     ex.sync();
+    if (GGL_PSYNC_MASK & 256) ex.phase_sync();
     GGL_PH(8);
     for (int c = ex.lane(); c < A.numCars; c += ex.lanes()) car_post_tick(A.cars[c]);
     ex.sync();
+    if (GGL_PSYNC_MASK & 512) ex.phase_sync();
     GGL_PH(9);
     for (int p = ex.lane(); p < kNumPads; p += ex.lanes()) pad_check_cars(A, p);
     ex.sync();
+    if (GGL_PSYNC_MASK & 1024) ex.phase_sync();
     GGL_PH(10);
     if (ex.lane() == 0) phase_finish(A);
     ex.sync();
-    ex.phase_sync();
+    if (GGL_PSYNC_MASK & 2048) ex.phase_sync();
     GGL_PH(11);
 }
 
