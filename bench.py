@@ -38,6 +38,13 @@ OBS_SIZE_ADV_2V2 = 167
 # obs 668 + mask 90 + reward 4 + state share ~260 + action 4
 ENV_BYTES_PER_AGENT_STEP = 1026
 GAE_BYTES_PER_ELEM = 21
+# DRAM traffic per launch of the dominant kernels from one `ncu --set full` capture each (dram__bytes_read.sum +
+# dram__bytes_write.sum; profiles/r1h_env_step_ncu_summary.txt, profiles/r1h_gae_scan_ncu_summary.txt). Env step: 30.4 + 5.9 MB
+# at 4096 arenas 2v2 (state blobs in and out, outputs, mesh and instruction fetch) against 16.8 MB algorithmic; GAE scan:
+# 151.3 + 145.4 MB at L = 2^24 against 352 MB algorithmic (part of the 201 MB of outputs is still in the 126 MB L2 when the
+# kernel ends).
+ENV_TRAFFIC_BYTES_NCU = 36.2e6
+GAE_TRAFFIC_BYTES_NCU = 296.7e6
 
 
 def peaks():
@@ -238,9 +245,10 @@ def bench_env(args, rank, world, local):
                 "steps": e2e_steps, "api": "ggl_envset_begin_step_host + host action pick + ggl_envset_finish_step_host (pinned host buffers)"},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "kernel": "env_step_kernel", "peak_source": peak_src,
+                     "traffic": ENV_TRAFFIC_BYTES_NCU, "kernel": "env_step_kernel", "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": ENV_BYTES_PER_AGENT_STEP * env.num_players,
-                     "note": "physics ticks are FP32/latency bound; the HBM floor is the obs/mask/reward write (SURVEY 8d)"},
+                     "note": "physics ticks are FP32-issue / barrier-latency bound (ncu: 11% issue utilisation, 50% of stall samples "
+                             "at the per-phase block barriers); the HBM floor is the obs/mask/reward write (SURVEY 8d)"},
         "wall_s": t_wall,
     }
     if rank == 0:
@@ -352,7 +360,7 @@ def bench_gae(args, rank, world, local):
                 "d2h_bytes_per_step": 12 * L + 8, "api": "ggl_gae_compute_host"},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "achieved": g["GB/s"], "peak": g["peak"], "unit": "GB/s", "frac": g["frac"],
-                     "traffic": None, "kernel": "gae_scan_kernel", "peak_source": g["peak_source"],
+                     "traffic": GAE_TRAFFIC_BYTES_NCU, "kernel": "gae_scan_kernel", "peak_source": g["peak_source"],
                      "algorithmic_bytes_per_launch": GAE_BYTES_PER_ELEM * L},
     }
     if rank == 0:

@@ -256,8 +256,18 @@ __global__ void __launch_bounds__(CNT_THREADS) gae_trunc_count_kernel(const int8
     __threadfence();
     const int per = (num_tiles + CNT_THREADS - 1) / CNT_THREADS;
     const int b0 = threadIdx.x * per, b1 = min(num_tiles, b0 + per);
+    // the thread's run of per-tile counts: up to 32 of them are fetched as independent loads and kept in registers
+    unsigned int vals[32];
     unsigned int sum = 0;
-    for (int t = b0; t < b1; t++) sum += __ldcg(&tile_cnt[t]);
+    if (per <= 32) {
+#pragma unroll
+        for (int k = 0; k < 32; k++) vals[k] = (b0 + k < b1) ? __ldcg(&tile_cnt[b0 + k]) : 0u;
+#pragma unroll
+        for (int k = 0; k < 32; k++) sum += vals[k];
+    } else {
+#pragma unroll 8
+        for (int t = b0; t < b1; t++) sum += __ldcg(&tile_cnt[t]);
+    }
     s_part[threadIdx.x] = sum;
     __syncthreads();
     {   // exclusive scan of the CNT_THREADS partial sums: warp shuffles + one pass over the warp totals
@@ -281,7 +291,14 @@ __global__ void __launch_bounds__(CNT_THREADS) gae_trunc_count_kernel(const int8
     }
     __syncthreads();
     unsigned int run = s_part[threadIdx.x];
-    for (int t = b0; t < b1; t++) { cnt_in[t] = run; run += __ldcg(&tile_cnt[t]); }
+    if (per <= 32) {
+#pragma unroll
+        for (int k = 0; k < 32; k++)
+            if (b0 + k < b1) { cnt_in[b0 + k] = run; run += vals[k]; }
+    } else {
+        for (int t = b0; t < b1; t++) { cnt_in[t] = run; run += __ldcg(&tile_cnt[t]); }
+    }
+}
 }
 
 template <bool HAS_TRUNC, bool NORM, bool CLIP>
