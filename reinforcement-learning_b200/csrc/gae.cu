@@ -299,7 +299,6 @@ __global__ void __launch_bounds__(CNT_THREADS) gae_trunc_count_kernel(const int8
         for (int t = b0; t < b1; t++) { cnt_in[t] = run; run += __ldcg(&tile_cnt[t]); }
     }
 }
-}
 
 template <bool HAS_TRUNC, bool NORM, bool CLIP>
 __global__ void __launch_bounds__(GAE_THREADS, GAE_CFG_MINBLOCKS) gae_scan_kernel(GaeParams p) {
