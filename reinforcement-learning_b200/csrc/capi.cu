@@ -40,14 +40,14 @@ extern "C" int ggl_host_random_actions(const uint8_t* h_masks, int32_t* h_action
         uint64_t words[32];
         int cnt = 0;
         const int nwc = nw < 32 ? nw : 0;       // wide rows fall back to the byte loop
-        for (int w = 0; w < nwc; w++) { uint64_t x; memcpy(&x, m + 8 * w, 8); words[w] = nonzero_bytes(x); cnt += __builtin_popcountll(words[w]); }
+        for (int w = 0; w < nwc; w++) { uint64_t x; memcpy(&x, m + 8 * w, 8); words[w] = nonzero_bytes(x); cnt += (int)((words[w] * 0x0101010101010101ull) >> 56); }
         for (int a = 8 * nwc; a < num_actions; a++) cnt += m[a] != 0;
         int sel = 0;
         if (cnt > 0) {
             int k = (int)(z % (uint64_t)cnt);
             int a = 0;
             for (int w = 0; w < nwc; w++) {
-                const int c = __builtin_popcountll(words[w]);
+                const int c = (int)((words[w] * 0x0101010101010101ull) >> 56);     // bytes are 0/1: their sum lands in the top byte
                 if (k >= c) { k -= c; a += 8; continue; }
                 uint64_t x = words[w];
                 while (k-- > 0) x &= x - 1;                       // drop the k lowest set bytes

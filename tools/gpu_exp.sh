@@ -1,6 +1,3 @@
-P=reinforcement-learning_b200
-python tools/phase_profile.py 160 40 2>&1 | head -1
-for v in m2080 m2088 m2220 m4094; do
-echo "=== $v"
-GGL_LIB_PATH=$P/libgigaenv_var_$v.so timeout 300 python tools/phase_profile.py 160 40 2>&1 | head -1
-done
+python -m pytest tests/test_gae_gpu.py -m gpu -x -q 2>&1 | tail -2
+python bench.py --workload gae 2>&1 | python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('GAE ms', d['ms_per_step'], 'frac', d['roofline']['frac'])"
+python tools/e2e_breakdown.py 2>&1 | tail -7
