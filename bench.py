@@ -25,6 +25,7 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
+sys.path.insert(0, os.path.join(ROOT, "oracle"))
 PKG = "reinforcement-learning_b200"
 
 ARENAS_PER_GPU = 4096
@@ -376,6 +377,77 @@ def bench_gae(args, rank, world, local):
     return line
 
 
+# ------------------------------------------------------------------------------------------------ ExperienceBuffer workload
+def bench_expbuf(args, rank, world, local):
+    """One epoch's worth of minibatches = one fused permuted gather of the experience stream:
+    2^20 samples, obs 167, 90 actions; bytes = 2 x (4*obs + 90 + 16) + 8 per sample."""
+    import numpy as np
+    import torch
+    ggl = importlib.import_module(PKG)
+    dev = torch.device("cuda", local)
+    n, obs, na = 1 << 20, OBS_SIZE_ADV_2V2, 90
+    g = torch.Generator(device=dev); g.manual_seed(3 + rank)
+    data = {"states": torch.randn(n, obs, device=dev, generator=g), "actions": torch.randint(0, na, (n,), device=dev, generator=g, dtype=torch.int32),
+            "log_probs": torch.randn(n, device=dev, generator=g), "target_values": torch.randn(n, device=dev, generator=g),
+            "action_masks": (torch.rand(n, na, device=dev, generator=g) < 0.5).to(torch.uint8), "advantages": torch.randn(n, device=dev, generator=g)}
+    perms = [torch.randperm(n, device=dev, generator=g) for _ in range(4)]
+    out = ggl.expbuf_gather(data, perms[0])
+    bytes_per_sample = 2 * (4 * obs + na + 16) + 8
+    s = torch.cuda.current_stream(dev)
+    for i in range(args.warmup):
+        ggl.expbuf_gather(data, perms[i % 4], out=out)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = ggl.launch_count()
+    barrier_sync(world)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(s)
+    for i in range(args.steps):
+        ggl.expbuf_gather(data, perms[i % 4], out=out)
+    e1.record(s)
+    barrier_sync(world)
+    launches = ggl.launch_count() - l0
+    clocks = sampler.stop() if rank == 0 else None
+    ms = max_over_ranks(e0.elapsed_time(e1) / args.steps, world)
+    gbs = bytes_per_sample * n / (ms * 1e-3) / 1e9
+    peak, src = peaks()
+    # e2e: the permutation comes from the host every epoch (std::shuffle stays on the host) and the result is read back
+    h_perm = torch.randperm(n).pin_memory()
+    h_adv = torch.empty(n).pin_memory()
+    d_perm = torch.empty(n, dtype=torch.int64, device=dev)
+    t0 = time.perf_counter()
+    n_e2e = 5
+    for _ in range(n_e2e):
+        d_perm.copy_(h_perm, non_blocking=True)
+        ggl.expbuf_gather(data, d_perm, out=out)
+        h_adv.copy_(out["advantages"], non_blocking=True)
+        torch.cuda.synchronize()
+    e2e_s = max_over_ranks((time.perf_counter() - t0) / n_e2e, world)
+    line = {"metric": "ExperienceBuffer gather GB/s", "value": gbs * world, "unit": "GB/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": "ExperienceBuffer epoch: fused permuted gather of 2^20 samples x (obs 167 f32, 90 mask bytes, 4 scalars)",
+                       "l2": "sources + destinations 1.6 GB > L2"},
+            "e2e": {"value": bytes_per_sample * n * world / e2e_s / 1e9, "unit": "GB/s", "h2d_bytes_per_step": 8 * n, "d2h_bytes_per_step": 4 * n,
+                    "api": "H2D permutation + ggl_expbuf_gather + D2H advantages"},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak, "traffic": None,
+                         "kernel": "expbuf_gather_kernel", "peak_source": src, "algorithmic_bytes_per_launch": bytes_per_sample * n}}
+    if rank == 0:
+        line["clocks"] = clocks
+        if world == 1:
+            import expbuf_oracle as eo
+            ns = 1 << 17
+            hd = {k: v[:ns].cpu().numpy() for k, v in data.items()}
+            p = np.random.default_rng(0).permutation(ns)
+            t0 = time.perf_counter()
+            eo.get_samples(hd, p, -1)
+            dt = time.perf_counter() - t0
+            line["cpu_baseline"] = {"value": bytes_per_sample * ns / dt / 1e9, "unit": "GB/s", "cores": 1, "kind": "port",
+                                    "sample": "2^17 samples of the same shape, numpy restatement of _GetSamples (six fancy-index gathers)"}
+    return line
+
+
 # ------------------------------------------------------------------------------------------------ reference arm
 def bench_reference(args):
     """Times the reference's own CPU EnvSet on this box's host cores (oracle/_ref). Rank 0 only."""
@@ -406,7 +478,7 @@ def main():
     ap.add_argument("--steps", type=int, default=None)
     ap.add_argument("--warmup", type=int, default=None)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default=None, choices=["env", "gae"])
+    ap.add_argument("--workload", default=None, choices=["env", "gae", "expbuf"])
     args = ap.parse_args()
     if args.impl == "reference":
         args.steps = args.steps if args.steps is not None else 30
@@ -424,7 +496,7 @@ def main():
         args.warmup = 20 if workload == "env" else 5
     args.warmup = max(args.warmup, 3)
     rank, world, local = dist_setup(args.gpus)
-    line = bench_env(args, rank, world, local) if workload == "env" else bench_gae(args, rank, world, local)
+    line = {"env": bench_env, "gae": bench_gae, "expbuf": bench_expbuf}[workload](args, rank, world, local)
     if rank == 0:
         print(json.dumps(line))
     if world > 1:

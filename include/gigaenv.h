@@ -15,6 +15,7 @@
  *   ggl_arena_step               RocketSim Arena::Step (Sim/Arena/Arena.cpp:716-812) — raw ticks, for parity tests
  *   ggl_gae_compute              src/private/GigaLearnCPP/PPO/GAE.cpp:7-208  (GAE::Compute)
  *   ggl_action_table             RLGymCPP/src/RLGymCPP/ActionParsers/DefaultAction.cpp:3-89
+ *   ggl_expbuf_plan_batches / ggl_expbuf_gather   src/private/GigaLearnCPP/PPO/ExperienceBuffer.cpp:100-163 / :15-98
  *
  * Conventions: plain pointers and sizes only; every function returns 0 on success or a
  * negative ggl_status; nothing throws across the boundary; ggl_last_error() gives the text.
@@ -271,6 +272,29 @@ int  ggl_gae_compute_host(const float* h_rews, const int8_t* h_terminals, const 
                           float gamma, float lambda, float return_std, float clip_range,
                           float* h_out_advantages, float* h_out_returns, float* h_out_target_values,
                           float* h_out_clip_portion);
+
+/* ---- ExperienceBuffer batching (ExperienceBuffer.cpp:15-163) ----
+ * The six experience tensors (ExperienceBuffer.h:8-15, set at Learner.cpp:975-980); a NULL member is an undefined tensor.
+ * const-ness is nominal: the same struct describes the sources and the destinations. */
+typedef struct ggl_expbuf_tensors {
+    float*   states;         /* [rows, obs_size] */
+    int32_t* actions;        /* [rows_actions] */
+    float*   log_probs;      /* [rows] */
+    float*   target_values;  /* [rows] */
+    uint8_t* action_masks;   /* [rows, num_actions] */
+    float*   advantages;     /* [rows] */
+} ggl_expbuf_tensors;
+/* GetAllBatchesShuffled's partition (:143-160) of a permuted stream of exp_size = min(rows of states, rows of actions) samples
+ * into minibatches: fills out_starts/out_sizes (up to max_batches entries, either may be NULL) and returns the number of
+ * batches (>= 0) or a negative ggl_status. Pure host arithmetic. */
+int64_t ggl_expbuf_plan_batches(int64_t exp_size, int64_t batch_size, int overbatching, int64_t* out_starts, int64_t* out_sizes,
+                                int64_t max_batches);
+/* One fused gather of `count` samples: dst.X[i] = src.X[d_indices[i]] for every defined tensor, indices >= the row limit clamped
+ * to the last row (:42-69), actions clamped to [0, max_action_index] when max_action_index >= 0 (:88-90). All pointers are
+ * DEVICE pointers; d_indices is int64 like the reference's index vector and must be >= 0. Minibatch b of the epoch is the
+ * view [start_b, start_b + size_b) of the destinations. */
+int  ggl_expbuf_gather(const ggl_expbuf_tensors* src, int64_t rows_states, int64_t rows_actions, int32_t obs_size, int32_t num_actions,
+                       const int64_t* d_indices, int64_t count, int64_t max_action_index, const ggl_expbuf_tensors* dst, void* stream);
 
 /* kernels launched by this library since load (bench.py's gpu_launches) */
 uint64_t ggl_launch_count(void);

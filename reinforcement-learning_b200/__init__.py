@@ -36,6 +36,11 @@ def lib():
                                       [C.c_void_p] * 7)
         L.ggl_gae_compute_host.argtypes = ([C.c_void_p] * 4 + [C.c_int64, C.c_int64] + [C.c_float] * 4 +
                                            [C.c_void_p] * 3 + [C.POINTER(C.c_float)])
+        if hasattr(L, "ggl_expbuf_gather"):
+            L.ggl_expbuf_plan_batches.restype = C.c_int64
+            L.ggl_expbuf_plan_batches.argtypes = [C.c_int64, C.c_int64, C.c_int, C.c_void_p, C.c_void_p, C.c_int64]
+            L.ggl_expbuf_gather.argtypes = [C.POINTER(abi.ExpBufTensors), C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.c_void_p,
+                                            C.c_int64, C.c_int64, C.POINTER(abi.ExpBufTensors), C.c_void_p]
         if hasattr(L, "ggl_envset_create"):
             L.ggl_envset_create.argtypes = [C.POINTER(abi.EnvSetDesc), C.POINTER(C.c_void_p)]
             L.ggl_envset_destroy.argtypes = [C.c_void_p]
@@ -123,6 +128,51 @@ def action_table():
     n = C.c_int()
     _check(lib().ggl_action_table(t.ctypes.data, C.byref(n)))
     return t[:n.value]
+
+
+# ------------------------------------------------------------------------------------ ExperienceBuffer
+EXPBUF_FIELDS = ("states", "actions", "log_probs", "target_values", "action_masks", "advantages")
+
+
+def expbuf_plan_batches(exp_size, batch_size, overbatching):
+    """[(start, size)] of GetAllBatchesShuffled's minibatches over the permuted stream (ExperienceBuffer.cpp:143-160)."""
+    L = lib()
+    n = L.ggl_expbuf_plan_batches(exp_size, batch_size, int(bool(overbatching)), None, None, 0)
+    if n < 0:
+        _check(int(n))
+    starts = np.zeros(max(n, 1), np.int64); sizes = np.zeros(max(n, 1), np.int64)
+    L.ggl_expbuf_plan_batches(exp_size, batch_size, int(bool(overbatching)), starts.ctypes.data, sizes.ctypes.data, n)
+    return [(int(starts[i]), int(sizes[i])) for i in range(n)]
+
+
+def expbuf_gather(data, indices, max_action_index=-1, out=None, stream=None):
+    """One fused permuted gather of the experience tensors on the device. data: dict over EXPBUF_FIELDS of CUDA tensors (or
+    None); indices: CUDA int64 tensor. Returns the dict of gathered tensors (minibatches are slices of them)."""
+    import torch
+    L = lib()
+    states = data.get("states")
+    dev = indices.device
+    count = int(indices.numel())
+    src, dst = abi.ExpBufTensors(), abi.ExpBufTensors()
+    res = {}
+    for f in EXPBUF_FIELDS:
+        t = data.get(f)
+        if t is None:
+            res[f] = None
+            continue
+        assert t.is_cuda and t.is_contiguous()
+        o = None if out is None else out.get(f)
+        if o is None:
+            o = torch.empty((count,) + tuple(t.shape[1:]), dtype=t.dtype, device=dev)
+        res[f] = o
+        setattr(src, f, t.data_ptr()); setattr(dst, f, o.data_ptr())
+    rows = 0 if states is None else int(states.shape[0])
+    rows_a = rows if data.get("actions") is None else int(data["actions"].shape[0])
+    obs = 1 if states is None else int(states.shape[1])
+    na = 1 if data.get("action_masks") is None else int(data["action_masks"].shape[1])
+    s = torch.cuda.current_stream(dev).cuda_stream if stream is None else stream
+    _check(L.ggl_expbuf_gather(C.byref(src), rows, rows_a, obs, na, indices.data_ptr(), count, max_action_index, C.byref(dst), s))
+    return res
 
 
 # -------------------------------------------------------------------------------------------- EnvSet

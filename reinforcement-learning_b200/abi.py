@@ -89,6 +89,11 @@ class ArenaState(C.Structure):
                 ("cars", CarState * GGL_MAX_CARS), ("pads", PadState * GGL_NUM_PADS)]
 
 
+class ExpBufTensors(C.Structure):
+    _fields_ = [("states", C.c_void_p), ("actions", C.c_void_p), ("log_probs", C.c_void_p), ("target_values", C.c_void_p),
+                ("action_masks", C.c_void_p), ("advantages", C.c_void_p)]
+
+
 class EnvSetViews(C.Structure):
     _fields_ = [("num_arenas", C.c_int32), ("num_players", C.c_int32), ("obs_size", C.c_int32),
                 ("num_actions", C.c_int32), ("players_per_arena", C.c_int32),

@@ -17,6 +17,7 @@ SOURCES = {
     "capi.cu": [],
     "gae.cu": ["-fmad=false"],
     "envset.cu": ["-fmad=false"],
+    "expbuf.cu": [],
 }
 
 

@@ -175,3 +175,51 @@ def gae(rews, terms, vals, trunc_vals, gamma=0.99, lam=0.95, return_std=0.0, cli
     if rc != 0:
         raise RuntimeError("ref_gae_compute failed")
     return adv, ret, tgt, clip.value
+
+
+# ---- the reference ExperienceBuffer (oracle/_ref/libref_expbuf.so)
+_expbuf = None
+
+
+def expbuf_available():
+    return os.path.exists(os.path.join(_REF_DIR, "libref_expbuf.so"))
+
+
+class RefExpBuf:
+    """GGL::ExperienceBuffer on CPU tensors; keeps its shuffled index vector between epochs like the reference."""
+
+    def __init__(self, seed, max_action_index=-1):
+        global _expbuf
+        if _expbuf is None:
+            _expbuf = C.CDLL(os.path.join(_REF_DIR, "libref_expbuf.so"))
+            _expbuf.ref_expbuf_create.restype = C.c_void_p
+            _expbuf.ref_expbuf_create.argtypes = [C.c_int, C.c_int64]
+            _expbuf.ref_expbuf_destroy.argtypes = [C.c_void_p]
+            _expbuf.ref_expbuf_set_data.argtypes = [C.c_void_p] + [C.c_int64] * 4 + [C.c_void_p] * 6
+            _expbuf.ref_expbuf_get_batches.restype = C.c_int64
+            _expbuf.ref_expbuf_get_batches.argtypes = [C.c_void_p, C.c_int64, C.c_int, C.c_int64] + [C.c_void_p] * 7
+        self.h = _expbuf.ref_expbuf_create(seed, max_action_index)
+
+    def close(self):
+        if self.h:
+            _expbuf.ref_expbuf_destroy(self.h)
+            self.h = None
+
+    def set_data(self, d):
+        self.rows, self.obs = d["states"].shape
+        self.na = d["action_masks"].shape[1]
+        a = [np.ascontiguousarray(d[k]) for k in ("states", "actions", "log_probs", "target_values", "action_masks", "advantages")]
+        _expbuf.ref_expbuf_set_data(self.h, self.rows, a[1].shape[0], self.obs, self.na, *[x.ctypes.data for x in a])
+
+    def get_batches(self, batch_size, overbatching):
+        n = self.rows
+        sizes = np.zeros(n + 2, np.int64)
+        out = {"states": np.zeros((n, self.obs), np.float32), "actions": np.zeros(n, np.int32), "log_probs": np.zeros(n, np.float32),
+               "target_values": np.zeros(n, np.float32), "action_masks": np.zeros((n, self.na), np.uint8), "advantages": np.zeros(n, np.float32)}
+        nb = _expbuf.ref_expbuf_get_batches(self.h, batch_size, int(overbatching), n + 2, sizes.ctypes.data,
+                                            *[out[k].ctypes.data for k in ("states", "actions", "log_probs", "target_values", "action_masks", "advantages")])
+        if nb < 0:
+            raise RuntimeError("ref_expbuf_get_batches failed")
+        sizes = sizes[:nb]
+        used = int(sizes.sum())
+        return sizes, {k: v[:used] for k, v in out.items()}
