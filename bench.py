@@ -391,6 +391,8 @@ def bench_expbuf(args, rank, world, local):
             "log_probs": torch.randn(n, device=dev, generator=g), "target_values": torch.randn(n, device=dev, generator=g),
             "action_masks": (torch.rand(n, na, device=dev, generator=g) < 0.5).to(torch.uint8), "advantages": torch.randn(n, device=dev, generator=g)}
     perms = [torch.randperm(n, device=dev, generator=g) for _ in range(4)]
+    if os.environ.get("GGL_EXPBUF_IDENTITY"):          # experiment knob: sequential rows = the streaming-copy ceiling of this kernel
+        perms = [torch.arange(n, device=dev) for _ in range(4)]
     out = ggl.expbuf_gather(data, perms[0])
     bytes_per_sample = 2 * (4 * obs + na + 16) + 8
     s = torch.cuda.current_stream(dev)

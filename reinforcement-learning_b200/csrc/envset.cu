@@ -1,5 +1,6 @@
 // C ABI of the device-resident EnvSet (include/gigaenv.h). Host side: descriptor translation, device memory,
 // kernel launches on the caller's stream. No CPU fallback: every entry point that computes launches a kernel.
+#include <cstdlib>
 #include "common.cuh"
 #include "sim_convert.cuh"
 #include "env_kernels.cuh"
@@ -44,6 +45,10 @@ LaunchGeom launch_geom(const EnvCfg& cfg, int numSMs) {
     if (fit < 1) fit = 1;
     int warps = (totalWarps + numSMs - 1) / numSMs;
     if (warps > fit) warps = fit;
+    if (const char* cap = getenv("GGL_DEBUG_MAX_BLOCK_WARPS")) {     // test hook: same arenas under another block geometry
+        const int c = atoi(cap);
+        if (c >= 1 && c < warps) warps = c;
+    }
     if (warps < 1) warps = 1;
     LaunchGeom g;
     g.warps = warps;

@@ -9,7 +9,8 @@
 //     out.actions[i] = clamp(actions[perm[i]])   and the three f32 scalars per sample
 // HBM-bound: 2 x (4*obs + numActions + 16) + 8 bytes per sample (read + write + the index), e.g. 1556 B at obs 167.
 // One warp moves one sample: 32 lanes x 4 B over the row (rows are only 4-byte aligned: obs is odd), 2-byte lanes over the
-// mask row, lanes 0..3 the scalars; a grid-stride loop of 148 x 16 blocks keeps ~6 KB of loads in flight per warp.
+// mask row, lanes 0..3 the scalars; all of a sample's loads are issued before its first store, and the next pass's row index is
+// prefetched, so a warp pays one HBM round trip per sample (grid-stride loop over 148 x 16 blocks).
 // The permutation is an input: std::shuffle over std::default_random_engine is libstdc++'s, the host keeps producing it.
 #include "common.cuh"
 
@@ -20,82 +21,122 @@ struct ExpPtrs {
     float* oStates; int32_t* oActions; float* oLogProbs; float* oTargetValues; uint8_t* oMasks; float* oAdvantages;
 };
 
-// copies one sample's scalars (lanes 0..3) and mask row
-__device__ __forceinline__ void copy_small(const ExpPtrs& p, long long r, long long i, int lane, int numActions, long long maxAction) {
-    if (p.masks) {
+#ifndef EXP_UNROLL_CFG
+#define EXP_UNROLL_CFG 2
+#endif
+constexpr int EXP_UNROLL = EXP_UNROLL_CFG;      // samples a warp has in flight (strided by the number of warps)
+constexpr int EXP_KMAX = 8;        // 32-float chunks of a state row held in registers (obs <= 256; wider rows loop)
+#ifndef EXP_MMAX_CFG
+#define EXP_MMAX_CFG 2
+#endif
+constexpr int EXP_MMAX = EXP_MMAX_CFG;   // mask units (halfwords for even rows, bytes for odd ones) per lane held in registers
+
+// Everything one sample needs is LOADED before anything is stored: the source and destination pointers may alias as far as the
+// compiler knows, so a store between two loads would put one HBM round trip per tensor on the warp's critical path
+// (ncu r1i: 62 % long-scoreboard stalls, the six tensors' latencies back to back).
+template <int K>
+struct Sample {
+    float st[K];
+    unsigned short mk[EXP_MMAX];
+    uint32_t scalar;               // lane 0: action, lane 1: log prob, lane 2: target value, lane 3: advantage (raw 32 bits)
+};
+
+template <int K>
+__device__ __forceinline__ void load_sample(Sample<K>& S, const ExpPtrs& p, long long r, int lane, int obs, int numActions, bool regStates,
+                                            bool regMasks) {
+    if (p.states && regStates) {
+        const float* __restrict__ s = p.states + r * obs;
+#pragma unroll
+        for (int k = 0; k < K; k++) S.st[k] = (k * 32 + lane < obs) ? __ldcs(s + k * 32 + lane) : 0.f;
+    }
+    if (p.masks && regMasks) {
         const uint8_t* s = p.masks + r * numActions;
-        uint8_t* d = p.oMasks + i * numActions;
         if ((numActions & 1) == 0) {                        // even rows are 2-byte aligned: move halfwords
             const unsigned short* s2 = reinterpret_cast<const unsigned short*>(s);
-            unsigned short* d2 = reinterpret_cast<unsigned short*>(d);
-            for (int k = lane; k < (numActions >> 1); k += 32) d2[k] = s2[k];
+#pragma unroll
+            for (int k = 0; k < EXP_MMAX; k++) S.mk[k] = (k * 32 + lane < (numActions >> 1)) ? __ldcs(s2 + k * 32 + lane) : 0;
         } else {
+#pragma unroll
+            for (int k = 0; k < EXP_MMAX; k++) S.mk[k] = (k * 32 + lane < numActions) ? s[k * 32 + lane] : 0;
+        }
+    }
+    const void* sp = lane == 0 ? (const void*)p.actions : lane == 1 ? (const void*)p.logProbs : lane == 2 ? (const void*)p.targetValues
+                   : lane == 3 ? (const void*)p.advantages : nullptr;
+    S.scalar = sp ? __ldcs(reinterpret_cast<const uint32_t*>(sp) + r) : 0u;
+}
+
+template <int K>
+__device__ __forceinline__ void store_sample(const Sample<K>& S, const ExpPtrs& p, long long r, long long i, int lane, int obs, int numActions,
+                                             long long maxAction, bool regStates, bool regMasks) {
+    if (p.states) {
+        float* __restrict__ d = p.oStates + i * obs;
+        if (regStates) {
+#pragma unroll
+            for (int k = 0; k < K; k++)
+                if (k * 32 + lane < obs) __stcs(d + k * 32 + lane, S.st[k]);
+        } else {
+            const float* __restrict__ s = p.states + r * obs;
+            for (int k = lane; k < obs; k += 32) __stcs(d + k, __ldcs(s + k));
+        }
+    }
+    if (p.masks) {
+        uint8_t* d = p.oMasks + i * numActions;
+        if (regMasks) {
+            if ((numActions & 1) == 0) {
+                unsigned short* d2 = reinterpret_cast<unsigned short*>(d);
+#pragma unroll
+                for (int k = 0; k < EXP_MMAX; k++)
+                    if (k * 32 + lane < (numActions >> 1)) __stcs(d2 + k * 32 + lane, S.mk[k]);
+            } else {
+#pragma unroll
+                for (int k = 0; k < EXP_MMAX; k++)
+                    if (k * 32 + lane < numActions) d[k * 32 + lane] = (uint8_t)S.mk[k];
+            }
+        } else {
+            const uint8_t* s = p.masks + r * numActions;
             for (int k = lane; k < numActions; k += 32) d[k] = s[k];
         }
     }
     if (lane == 0 && p.actions) {
-        long long a = p.actions[r];
+        long long a = (int32_t)S.scalar;
         if (maxAction >= 0) a = a < 0 ? 0 : (a > maxAction ? maxAction : a);     // ExperienceBuffer.cpp:88-90
         p.oActions[i] = (int32_t)a;
     }
-    if (lane == 1 && p.logProbs) p.oLogProbs[i] = p.logProbs[r];
-    if (lane == 2 && p.targetValues) p.oTargetValues[i] = p.targetValues[r];
-    if (lane == 3 && p.advantages) p.oAdvantages[i] = p.advantages[r];
+    if (lane == 1 && p.logProbs) reinterpret_cast<uint32_t*>(p.oLogProbs)[i] = S.scalar;
+    if (lane == 2 && p.targetValues) reinterpret_cast<uint32_t*>(p.oTargetValues)[i] = S.scalar;
+    if (lane == 3 && p.advantages) reinterpret_cast<uint32_t*>(p.oAdvantages)[i] = S.scalar;
 }
 
-#ifndef EXP_UNROLL_CFG
-#define EXP_UNROLL_CFG 1
-#endif
-constexpr int EXP_UNROLL = EXP_UNROLL_CFG;      // samples a warp has in flight (4 x 668 B of state rows at obs 167)
-constexpr int EXP_KMAX = 8;        // 32-float chunks of a state row held in registers (obs <= 256; wider rows loop)
-
+// K = 32-float chunks per state row kept in registers (2, 4, 6 or 8: the register count, and with it the number of resident
+// warps, follows the row width)
+template <int K>
 __global__ void __launch_bounds__(256) expbuf_gather_kernel(ExpPtrs p, const int64_t* __restrict__ idx, long long count, long long rowLimit,
                                                             int obs, int numActions, long long maxAction) {
     const int lane = threadIdx.x & 31;
     const long long warp = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
-    // a warp takes EXP_UNROLL CONSECUTIVE samples per pass, so that what it writes is one contiguous piece of every destination
-    for (long long i0 = warp * EXP_UNROLL; i0 < count; i0 += EXP_UNROLL * nwarps) {
+    const bool regStates = obs <= 32 * K;
+    const bool regMasks = ((numActions & 1) == 0 ? (numActions >> 1) : numActions) <= 32 * EXP_MMAX;
+    // the row index of the NEXT pass is fetched while this pass's rows are in flight
+    long long rn[EXP_UNROLL];
+#pragma unroll
+    for (int u = 0; u < EXP_UNROLL; u++) { const long long i = warp + u * nwarps; rn[u] = i < count ? __ldg(idx + i) : 0; }
+    for (long long i0 = warp; i0 < count; i0 += EXP_UNROLL * nwarps) {
         long long r[EXP_UNROLL];
+        Sample<K> S[EXP_UNROLL];
 #pragma unroll
         for (int u = 0; u < EXP_UNROLL; u++) {
-            const long long i = i0 + u;
-            long long v = (i < count) ? __ldg(idx + i) : 0;
-            r[u] = v >= rowLimit ? rowLimit - 1 : v;            // ExperienceBuffer.cpp:42-69
+            r[u] = rn[u] >= rowLimit ? rowLimit - 1 : rn[u];            // ExperienceBuffer.cpp:42-69
+            const long long in = i0 + (u + EXP_UNROLL) * nwarps;
+            rn[u] = in < count ? __ldg(idx + in) : 0;
         }
-        if (p.states) {
-            if (obs <= 32 * EXP_KMAX) {
-                float v[EXP_UNROLL][EXP_KMAX];
 #pragma unroll
-                for (int u = 0; u < EXP_UNROLL; u++) {
-                    const float* __restrict__ s = p.states + r[u] * obs;
-                    const bool ok = i0 + u < count;
-#pragma unroll
-                    for (int k = 0; k < EXP_KMAX; k++) v[u][k] = (ok && k * 32 + lane < obs) ? __ldcs(s + k * 32 + lane) : 0.f;
-                }
-#pragma unroll
-                for (int u = 0; u < EXP_UNROLL; u++) {
-                    const long long i = i0 + u;
-                    if (i >= count) break;
-                    float* __restrict__ d = p.oStates + i * obs;
-#pragma unroll
-                    for (int k = 0; k < EXP_KMAX; k++)
-                        if (k * 32 + lane < obs) __stcs(d + k * 32 + lane, v[u][k]);
-                }
-            } else {
-                for (int u = 0; u < EXP_UNROLL; u++) {
-                    const long long i = i0 + u;
-                    if (i >= count) break;
-                    const float* __restrict__ s = p.states + r[u] * obs;
-                    float* __restrict__ d = p.oStates + i * obs;
-                    for (int k = lane; k < obs; k += 32) __stcs(d + k, __ldcs(s + k));
-                }
-            }
-        }
+        for (int u = 0; u < EXP_UNROLL; u++)
+            if (i0 + u * nwarps < count) load_sample(S[u], p, r[u], lane, obs, numActions, regStates, regMasks);
 #pragma unroll
         for (int u = 0; u < EXP_UNROLL; u++) {
-            const long long i = i0 + u;
-            if (i < count) copy_small(p, r[u], i, lane, numActions, maxAction);
+            const long long i = i0 + u * nwarps;
+            if (i < count) store_sample(S[u], p, r[u], i, lane, obs, numActions, maxAction, regStates, regMasks);
         }
     }
 }
@@ -138,9 +179,11 @@ extern "C" int ggl_expbuf_gather(const ggl_expbuf_tensors* src, int64_t rows_sta
     int dev = 0, sms = 148;
     GGL_CUDA(cudaGetDevice(&dev));
     GGL_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    long long blocks = (count + 8 * EXP_UNROLL - 1) / (8 * EXP_UNROLL);           // 8 warps x EXP_UNROLL samples per block pass
+    long long blocks = (count + 7) / 8;                                          // 8 warps per block, a sample per warp per pass
     if (blocks > (long long)sms * 16) blocks = (long long)sms * 16;
-    expbuf_gather_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(p, d_indices, count, rowLimit, obs_size, num_actions, max_action_index);
+    auto kern = obs_size <= 64 ? expbuf_gather_kernel<2> : obs_size <= 128 ? expbuf_gather_kernel<4>
+              : obs_size <= 192 ? expbuf_gather_kernel<6> : expbuf_gather_kernel<EXP_KMAX>;
+    kern<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(p, d_indices, count, rowLimit, obs_size, num_actions, max_action_index);
     GGL_LAUNCH_CHECK();
     ggl::count_launch();
     return GGL_OK;

@@ -39,7 +39,9 @@ def run_env_steps(ggl, num_arenas=8, ppt=2, steps=40, seed=0, obs_kind=1, verbos
         dev.set_reset_state(a, st)
     rng = np.random.default_rng(seed)
     res = {"obs": 0.0, "rew": 0.0, "mask_mismatch": 0, "term_mismatch": 0, "event_mismatch": 0, "obs_bad": 0, "steps": 0,
-           "terminals_seen": 0, "touches": 0}
+           "terminals_seen": 0, "touches": 0, "bad_arenas": 0}
+    bad_arenas = set()
+    ppa = 2 * ppt
     host_mode = hasattr(dev, "step_np")
     acts_d = None if host_mode else torch.zeros(dev.num_players, dtype=torch.int32, device=dev.device)
     # first step: masks from the reference reset
@@ -60,6 +62,9 @@ def run_env_steps(ggl, num_arenas=8, ppt=2, steps=40, seed=0, obs_kind=1, verbos
         ok = close_rel(obs_d, obs_r)
         res["obs"] = max(res["obs"], float(np.max(np.abs(obs_d - obs_r))))
         res["obs_bad"] += int((~ok).sum())
+        if not ok.all():
+            bad_arenas.update((np.argwhere(~ok)[:, 0] // ppa).tolist())
+            res["bad_arenas"] = len(bad_arenas)
         res["rew"] = max(res["rew"], float(np.max(np.abs(rew_d - rew_r))))
         res["mask_mismatch"] += int((masks_d != masks_r).sum())
         res["term_mismatch"] += int((term_d != term_r).sum())
