@@ -12,6 +12,7 @@
 // mask row, lanes 0..3 the scalars; all of a sample's loads are issued before its first store, and the next pass's row index is
 // prefetched, so a warp pays one HBM round trip per sample (grid-stride loop over 148 x 16 blocks).
 // The permutation is an input: std::shuffle over std::default_random_engine is libstdc++'s, the host keeps producing it.
+#include <cstdlib>
 #include "common.cuh"
 
 namespace {
@@ -141,6 +142,200 @@ __global__ void __launch_bounds__(256) expbuf_gather_kernel(ExpPtrs p, const int
     }
 }
 
+
+// ---- staged variant: aligned 16-byte copies in, packed tiles out -----------------------------------------------------------------
+// The register kernel above is bound by the load/store unit, not by HBM: rows start on 4-byte boundaries, so every 128-byte warp
+// request of it straddles two cache lines (stores-only 0.19 ms + loads-only 0.22 ms = the 0.42 ms it takes, gpurun_out/exp36).
+// Here a block owns a TILE of 32 consecutive output samples. The 16-byte-aligned span that contains each source row is copied to
+// shared memory with cp.async (16 bytes per lane, no registers held, a whole tile in flight per stage while the previous one is
+// written), and the tile, contiguous in every destination and 128-byte aligned (32 rows), leaves as whole-line stores.
+constexpr int EXP_TILE = 32;
+constexpr int EXP_STAGES = 2;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, int srcBytes) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(dst), "l"(src), "r"(srcBytes) : "memory");
+}
+__device__ __forceinline__ void cp_async4(uint32_t dst, const void* src) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
+
+struct StagedGeom {
+    int slotS, slotM;          // bytes per staged state / mask row (aligned span, multiple of 16)
+    int stageBytes;            // one stage: EXP_TILE state slots, EXP_TILE mask slots, 4 x EXP_TILE scalars, 2 x (EXP_TILE + 4) row bases
+};
+
+__host__ __device__ inline StagedGeom staged_geom(int obs, int numActions) {
+    StagedGeom g;
+    g.slotS = (obs * 4 + 12 + 15) & ~15;
+    g.slotM = (numActions + 15 + 15) & ~15;
+    g.stageBytes = EXP_TILE * (g.slotS + g.slotM) + 4 * EXP_TILE * 4 + 2 * (EXP_TILE + 4) * 4;
+    return g;
+}
+
+__global__ void __launch_bounds__(256) expbuf_gather_staged_kernel(ExpPtrs p, const int64_t* __restrict__ idx, long long count, long long rowLimit,
+                                                                   int obs, int numActions, long long maxAction) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    const StagedGeom G = staged_geom(obs, numActions);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const long long tiles = (count + EXP_TILE - 1) / EXP_TILE;
+    constexpr int PER_WARP = EXP_TILE / 8;                       // samples a warp stages
+    auto stage_ptr = [&](int st) { return smem + (size_t)st * G.stageBytes; };
+
+    // lanes 0..PER_WARP-1 of each warp hold the row index of "their" sample of the tile after next
+    auto fetch_row = [&](long long tile) -> long long {
+        const long long i = tile * EXP_TILE + warp * PER_WARP + lane;
+        if (lane < PER_WARP && tile < tiles && i < count) { const long long v = __ldg(idx + i); return v >= rowLimit ? rowLimit - 1 : v; }   // ExperienceBuffer.cpp:42-69
+        return -1;
+    };
+    auto issue = [&](int st, long long rowMine) {
+        unsigned char* base = stage_ptr(st);
+        unsigned char* sS = base;
+        unsigned char* sM = base + EXP_TILE * G.slotS;
+        uint32_t* sScal = reinterpret_cast<uint32_t*>(sM + EXP_TILE * G.slotM);          // [4][EXP_TILE]
+        int* sOffS = reinterpret_cast<int*>(sScal + 4 * EXP_TILE);
+        int* sOffM = sOffS + EXP_TILE + 4;
+#pragma unroll
+        for (int q = 0; q < PER_WARP; q++) {
+            const long long r = __shfl_sync(0xffffffffu, rowMine, q);
+            const int s = warp * PER_WARP + q;
+            if (r < 0) continue;
+            if (p.states) {
+                const unsigned char* g0 = reinterpret_cast<const unsigned char*>(p.states + r * obs);
+                const int off = (int)(reinterpret_cast<uintptr_t>(g0) & 15);
+                const unsigned char* a0 = g0 - off;
+                const int span = off + obs * 4;                       // bytes from a0 to the end of the row
+                const uint32_t d0 = smem_u32(sS + s * G.slotS);
+                for (int v = lane; v * 16 < span; v += 32) cp_async16(d0 + v * 16, a0 + v * 16, min(16, span - v * 16));
+                if (lane == 0) sOffS[s] = s * G.slotS + off;           // byte position of the row inside the state slots
+            }
+        }
+        if (p.masks) {                                                 // 8 lanes per sample: spans of up to 128 bytes
+            const int q = lane >> 3, v0 = lane & 7;
+            const long long r = __shfl_sync(0xffffffffu, rowMine, q < PER_WARP ? q : 0);
+            if (q < PER_WARP && r >= 0) {
+                const int s = warp * PER_WARP + q;
+                const unsigned char* g0 = p.masks + r * numActions;
+                const int off = (int)(reinterpret_cast<uintptr_t>(g0) & 15);
+                const unsigned char* a0 = g0 - off;
+                const int span = off + numActions;
+                const uint32_t d0 = smem_u32(sM + s * G.slotM);
+                for (int v = v0; v * 16 < span; v += 8) cp_async16(d0 + v * 16, a0 + v * 16, min(16, span - v * 16));
+                if (v0 == 0) sOffM[s] = s * G.slotM + off;
+            }
+        }
+        {                                                               // 4 lanes per sample: the four scalars
+            const int q = lane >> 2, which = lane & 3;
+            const long long r = __shfl_sync(0xffffffffu, rowMine, q < PER_WARP ? q : 0);
+            const void* sp = which == 0 ? (const void*)p.actions : which == 1 ? (const void*)p.logProbs : which == 2 ? (const void*)p.targetValues
+                                                                                                        : (const void*)p.advantages;
+            if (q < PER_WARP && r >= 0 && sp) cp_async4(smem_u32(sScal + which * EXP_TILE + warp * PER_WARP + q), reinterpret_cast<const uint32_t*>(sp) + r);
+        }
+        cp_async_commit();
+    };
+
+    // floor(n / d) = umulhi(n, ceil(2^32 / d)) for n * d < 2^32, which the shared-memory limit of this kernel guarantees
+    const unsigned magicObs = 0xFFFFFFFFu / (unsigned)obs + 1u, magicAct = 0xFFFFFFFFu / (unsigned)numActions + 1u;
+    const bool dstMask16 = (reinterpret_cast<uintptr_t>(p.oMasks) & 15) == 0;
+    long long tile = blockIdx.x;
+    if (tile >= tiles) return;
+    long long rowCur = fetch_row(tile);
+    long long rowNext = fetch_row(tile + gridDim.x);
+    issue(0, rowCur);
+    int st = 0;
+    for (; tile < tiles; tile += gridDim.x, st ^= 1) {
+        const long long rowAfter = fetch_row(tile + 2 * (long long)gridDim.x);
+        if (tile + gridDim.x < tiles) { issue(st ^ 1, rowNext); cp_async_wait<1>(); } else { cp_async_wait<0>(); }
+        __syncthreads();
+        // ---- write the tile out: every destination range of the tile is contiguous
+        const unsigned char* base = stage_ptr(st);
+        const unsigned char* sS = base;
+        const unsigned char* sM = base + EXP_TILE * G.slotS;
+        const uint32_t* sScal = reinterpret_cast<const uint32_t*>(sM + EXP_TILE * G.slotM);
+        const int* sOffS = reinterpret_cast<const int*>(sScal + 4 * EXP_TILE);
+        const int* sOffM = sOffS + EXP_TILE + 4;
+        const long long i0 = tile * EXP_TILE;
+        const int nvalid = (int)min((long long)EXP_TILE, count - i0);
+        if (p.states) {
+            float* __restrict__ d = p.oStates + i0 * obs;
+            const int W = nvalid * obs;
+            if (nvalid == EXP_TILE) {
+                // whole tile: 16 bytes per thread per pass; a float4 crosses a row boundary at most once (obs >= 4 here)
+                for (int q = tid; q * 4 < W; q += 256) {
+                    const int e = q * 4, r0 = (int)__umulhi((unsigned)e, magicObs), col = e - r0 * obs;
+                    const int b0 = sOffS[r0] + col * 4, b1 = sOffS[r0 + 1] - (obs - col) * 4;      // sOffS has slack entries past the tile
+                    float4 v;
+                    v.x = *reinterpret_cast<const float*>(sS + b0);
+                    v.y = *reinterpret_cast<const float*>(sS + (col + 1 < obs ? b0 : b1) + 4);
+                    v.z = *reinterpret_cast<const float*>(sS + (col + 2 < obs ? b0 : b1) + 8);
+                    v.w = *reinterpret_cast<const float*>(sS + (col + 3 < obs ? b0 : b1) + 12);
+                    __stcs(reinterpret_cast<float4*>(d) + q, v);
+                }
+            } else {
+                int r0 = tid / obs, col = tid - r0 * obs;
+                for (int w = tid; w < W; w += 256) {
+                    __stcs(d + w, *reinterpret_cast<const float*>(sS + sOffS[r0] + col * 4));
+                    col += 256;
+                    while (col >= obs) { col -= obs; r0++; }
+                }
+            }
+        }
+        if (p.masks) {
+            uint8_t* d = p.oMasks + i0 * numActions;
+            const int B = nvalid * numActions;                       // bytes of the tile; the tile starts 32-byte aligned
+            if (nvalid == EXP_TILE && dstMask16) {
+                for (int q = tid; q * 16 < B; q += 256) {            // 32 rows: B is a multiple of 16
+                    int b = q * 16, r0 = (int)__umulhi((unsigned)b, magicAct), col = b - r0 * numActions;
+                    int pos = sOffM[r0] + col;
+                    uint32_t wds[4];
+#pragma unroll
+                    for (int k = 0; k < 16; k++) {
+                        if ((k & 3) == 0) wds[k >> 2] = 0;
+                        wds[k >> 2] |= (uint32_t)sM[pos] << (8 * (k & 3));
+                        pos++;
+                        if (++col == numActions) { col = 0; r0++; pos = sOffM[r0]; }
+                    }
+                    __stcs(reinterpret_cast<uint4*>(d) + q, make_uint4(wds[0], wds[1], wds[2], wds[3]));
+                }
+            } else {
+                for (int w = tid; w * 4 < B; w += 256) {
+                    uint32_t word = 0;
+                    int b = w * 4, r0 = b / numActions, col = b - r0 * numActions;
+#pragma unroll
+                    for (int k = 0; k < 4; k++) {
+                        if (b + k < B) word |= (uint32_t)sM[sOffM[r0] + col] << (8 * k);
+                        if (++col == numActions) { col = 0; r0++; }
+                    }
+                    if (b + 4 <= B) __stcs(reinterpret_cast<uint32_t*>(d) + w, word);
+                    else for (int k = 0; b + k < B; k++) d[b + k] = (uint8_t)(word >> (8 * k));
+                }
+            }
+        }
+        if (tid < 4 * EXP_TILE) {
+            const int which = tid >> 5, j = tid & 31;                 // EXP_TILE == 32
+            if (j < nvalid) {
+                const uint32_t v = sScal[which * EXP_TILE + j];
+                if (which == 0) {
+                    if (p.actions) {
+                        long long a = (int32_t)v;
+                        if (maxAction >= 0) a = a < 0 ? 0 : (a > maxAction ? maxAction : a);     // ExperienceBuffer.cpp:88-90
+                        p.oActions[i0 + j] = (int32_t)a;
+                    }
+                } else {
+                    uint32_t* o = reinterpret_cast<uint32_t*>(which == 1 ? (void*)p.oLogProbs : which == 2 ? (void*)p.oTargetValues : (void*)p.oAdvantages);
+                    const void* sp = which == 1 ? (const void*)p.logProbs : which == 2 ? (const void*)p.targetValues : (const void*)p.advantages;
+                    if (sp) o[i0 + j] = v;
+                }
+            }
+        }
+        __syncthreads();                                               // the stage may be refilled
+        rowNext = rowAfter;
+    }
+}
+
 }  // namespace
 
 // GetAllBatchesShuffled's partition of the permuted stream (ExperienceBuffer.cpp:143-160). Host arithmetic, no device work.
@@ -179,6 +374,25 @@ extern "C" int ggl_expbuf_gather(const ggl_expbuf_tensors* src, int64_t rows_sta
     int dev = 0, sms = 148;
     GGL_CUDA(cudaGetDevice(&dev));
     GGL_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    // staged kernel: needs 16-byte-aligned source bases (its aligned spans then never leave the tensors) and two stages in shared memory
+    const StagedGeom G = staged_geom(obs_size, num_actions);
+    const size_t stagedSmem = (size_t)EXP_STAGES * G.stageBytes;
+    const bool aligned = ((uintptr_t)src->states & 15) == 0 && ((uintptr_t)src->action_masks & 15) == 0 && ((uintptr_t)dst->states & 15) == 0 &&
+                         ((uintptr_t)dst->action_masks & 3) == 0;
+    const bool forceRegs = getenv("GGL_EXPBUF_REGISTER_KERNEL") != nullptr;      // test hook: exercise the general kernel
+    if (aligned && !forceRegs && stagedSmem <= 100 * 1024 && count >= EXP_TILE && obs_size >= 4) {
+        GGL_CUDA(cudaFuncSetAttribute(expbuf_gather_staged_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+        const long long tiles = (count + EXP_TILE - 1) / EXP_TILE;
+        int perSM = (int)((227 * 1024) / (stagedSmem + 1024));
+        if (perSM > 8) perSM = 8;
+        if (perSM < 1) perSM = 1;
+        long long grid = (long long)sms * perSM;
+        if (grid > tiles) grid = tiles;
+        expbuf_gather_staged_kernel<<<(int)grid, 256, stagedSmem, (cudaStream_t)stream>>>(p, d_indices, count, rowLimit, obs_size, num_actions, max_action_index);
+        GGL_LAUNCH_CHECK();
+        ggl::count_launch();
+        return GGL_OK;
+    }
     long long blocks = (count + 7) / 8;                                          // 8 warps per block, a sample per warp per pass
     if (blocks > (long long)sms * 16) blocks = (long long)sms * 16;
     auto kern = obs_size <= 64 ? expbuf_gather_kernel<2> : obs_size <= 128 ? expbuf_gather_kernel<4>

@@ -15,6 +15,17 @@ import expbuf_cases as ec       # noqa: E402
 import oracle_ref               # noqa: E402
 
 
+@pytest.fixture(params=["staged", "registers"], autouse=True)
+def kernel_choice(request, monkeypatch):
+    """Every test runs twice: through the staged kernel (aligned tensors, count >= 32) and through the general register kernel
+    the library falls back to for unaligned tensors, very wide rows and tiny gathers (GGL_EXPBUF_REGISTER_KERNEL test hook)."""
+    if request.param == "registers":
+        monkeypatch.setenv("GGL_EXPBUF_REGISTER_KERNEL", "1")
+    else:
+        monkeypatch.delenv("GGL_EXPBUF_REGISTER_KERNEL", raising=False)
+    return request.param
+
+
 def _to_dev(data):
     import torch
     return {k: (None if v is None else torch.from_numpy(np.ascontiguousarray(v)).cuda()) for k, v in data.items()}
@@ -62,6 +73,13 @@ def test_edge_cases(ggl):
     import torch
     empty = ggl.expbuf_gather(_to_dev(data), torch.zeros(0, dtype=torch.int64, device="cuda"))
     assert empty["states"].shape == (0, 167)
+    # tensors that do not start on a 16-byte boundary take the general kernel: same results
+    dev = _to_dev(data)
+    big = torch.empty(300 * 167 + 1, device="cuda"); big[1:].copy_(dev["states"].flatten())
+    dev["states"] = big[1:].view(300, 167)
+    perm = rng.permutation(300)
+    got = ggl.expbuf_gather(dev, torch.from_numpy(perm).cuda())
+    assert np.array_equal(got["states"].cpu().numpy(), data["states"][perm])
 
 
 @pytest.mark.skipif(not oracle_ref.expbuf_available(), reason="compiled reference not present on this box")
