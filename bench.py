@@ -46,6 +46,10 @@ GAE_BYTES_PER_ELEM = 21
 # kernel ends).
 ENV_TRAFFIC_BYTES_NCU = 36.2e6
 GAE_TRAFFIC_BYTES_NCU = 296.7e6
+# ExperienceBuffer gather (staged kernel, profiles/r1j_expbuf_ncu_summary.txt): 1.202 GB read + 0.773 GB written at 2^20 samples against
+# 1.63 GB algorithmic: a random row drags in whole 64-byte DRAM bursts around its unaligned ends, and each of the four scalars
+# costs a burst of its own.
+EXPBUF_TRAFFIC_BYTES_NCU = 1.975e9
 
 
 def peaks():
@@ -433,8 +437,8 @@ def bench_expbuf(args, rank, world, local):
             "e2e": {"value": bytes_per_sample * n * world / e2e_s / 1e9, "unit": "GB/s", "h2d_bytes_per_step": 8 * n, "d2h_bytes_per_step": 4 * n,
                     "api": "H2D permutation + ggl_expbuf_gather + D2H advantages"},
             "gpu_launches": int(launches),
-            "roofline": {"bound": "hbm", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak, "traffic": None,
-                         "kernel": "expbuf_gather_kernel", "peak_source": src, "algorithmic_bytes_per_launch": bytes_per_sample * n}}
+            "roofline": {"bound": "hbm", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak, "traffic": EXPBUF_TRAFFIC_BYTES_NCU if n == (1 << 20) else None,
+                         "kernel": "expbuf_gather_staged_kernel", "peak_source": src, "algorithmic_bytes_per_launch": bytes_per_sample * n}}
     if rank == 0:
         line["clocks"] = clocks
         if world == 1:

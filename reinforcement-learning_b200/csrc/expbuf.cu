@@ -188,10 +188,11 @@ __global__ void __launch_bounds__(256) expbuf_gather_staged_kernel(ExpPtrs p, co
     // lanes 0..PER_WARP-1 of each warp hold the row index of "their" sample of the tile after next
     auto fetch_row = [&](long long tile) -> long long {
         const long long i = tile * EXP_TILE + warp * PER_WARP + lane;
-        if (lane < PER_WARP && tile < tiles && i < count) { const long long v = __ldg(idx + i); return v >= rowLimit ? rowLimit - 1 : v; }   // ExperienceBuffer.cpp:42-69
+        if (lane < PER_WARP && tile < tiles && i < count) return __ldg(idx + i);      // clamped where it is used: no wait on the load here
         return -1;
     };
     auto issue = [&](int st, long long rowMine) {
+        if (rowMine >= rowLimit) rowMine = rowLimit - 1;              // ExperienceBuffer.cpp:42-69
         unsigned char* base = stage_ptr(st);
         unsigned char* sS = base;
         unsigned char* sM = base + EXP_TILE * G.slotS;
@@ -202,7 +203,7 @@ __global__ void __launch_bounds__(256) expbuf_gather_staged_kernel(ExpPtrs p, co
         for (int q = 0; q < PER_WARP; q++) {
             const long long r = __shfl_sync(0xffffffffu, rowMine, q);
             const int s = warp * PER_WARP + q;
-            if (r < 0) continue;
+            if (r < 0) continue;                                      // (rowMine was clamped by the caller)
             if (p.states) {
                 const unsigned char* g0 = reinterpret_cast<const unsigned char*>(p.states + r * obs);
                 const int off = (int)(reinterpret_cast<uintptr_t>(g0) & 15);
@@ -286,17 +287,21 @@ __global__ void __launch_bounds__(256) expbuf_gather_staged_kernel(ExpPtrs p, co
         if (p.masks) {
             uint8_t* d = p.oMasks + i0 * numActions;
             const int B = nvalid * numActions;                       // bytes of the tile; the tile starts 32-byte aligned
-            if (nvalid == EXP_TILE && dstMask16) {
-                for (int q = tid; q * 16 < B; q += 256) {            // 32 rows: B is a multiple of 16
-                    int b = q * 16, r0 = (int)__umulhi((unsigned)b, magicAct), col = b - r0 * numActions;
-                    int pos = sOffM[r0] + col;
-                    uint32_t wds[4];
+            if (nvalid == EXP_TILE && dstMask16 && numActions >= 16) {
+                // 32 rows: B is a multiple of 16; 16 output bytes cross a row boundary at most once
+                const bool even = (numActions & 1) == 0;             // then every row starts on a 2-byte boundary
+                for (int q = tid; q * 16 < B; q += 256) {
+                    const int b = q * 16, r0 = (int)__umulhi((unsigned)b, magicAct), col = b - r0 * numActions;
+                    const int kx = numActions - col;                 // first byte of the 16 that belongs to the next row
+                    const int pos0 = sOffM[r0] + col, pos1 = sOffM[r0 + 1] - kx;
+                    uint32_t wds[4] = {0, 0, 0, 0};
+                    if (even) {
 #pragma unroll
-                    for (int k = 0; k < 16; k++) {
-                        if ((k & 3) == 0) wds[k >> 2] = 0;
-                        wds[k >> 2] |= (uint32_t)sM[pos] << (8 * (k & 3));
-                        pos++;
-                        if (++col == numActions) { col = 0; r0++; pos = sOffM[r0]; }
+                        for (int k = 0; k < 16; k += 2)
+                            wds[k >> 2] |= (uint32_t)*reinterpret_cast<const unsigned short*>(sM + (k < kx ? pos0 : pos1) + k) << (8 * (k & 3));
+                    } else {
+#pragma unroll
+                        for (int k = 0; k < 16; k++) wds[k >> 2] |= (uint32_t)sM[(k < kx ? pos0 : pos1) + k] << (8 * (k & 3));
                     }
                     __stcs(reinterpret_cast<uint4*>(d) + q, make_uint4(wds[0], wds[1], wds[2], wds[3]));
                 }
