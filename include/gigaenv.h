@@ -16,6 +16,7 @@
  *   ggl_gae_compute              src/private/GigaLearnCPP/PPO/GAE.cpp:7-208  (GAE::Compute)
  *   ggl_action_table             RLGymCPP/src/RLGymCPP/ActionParsers/DefaultAction.cpp:3-89
  *   ggl_expbuf_plan_batches / ggl_expbuf_gather   src/private/GigaLearnCPP/PPO/ExperienceBuffer.cpp:100-163 / :15-98
+ *   ggl_traj_*                                     src/public/GigaLearnCPP/Learner.cpp:504-547, 701-712, 823-863 (trajectory assembly)
  *
  * Conventions: plain pointers and sizes only; every function returns 0 on success or a
  * negative ggl_status; nothing throws across the boundary; ggl_last_error() gives the text.
@@ -295,6 +296,50 @@ int64_t ggl_expbuf_plan_batches(int64_t exp_size, int64_t batch_size, int overba
  * view [start_b, start_b + size_b) of the destinations. */
 int  ggl_expbuf_gather(const ggl_expbuf_tensors* src, int64_t rows_states, int64_t rows_actions, int32_t obs_size, int32_t num_actions,
                        const int64_t* d_indices, int64_t count, int64_t max_action_index, const ggl_expbuf_tensors* dst, void* stream);
+
+/* ---- Trajectory assembly: the order of the flat experience stream (src/public/GigaLearnCPP/Learner.cpp:504-547, 701-712, 823-863) ----
+ * The Learner keeps one growing buffer per player (`trajectories[p]`), appends it to `combinedTraj` in player order whenever that
+ * player's episode ends (arena terminal, or forced TRUNCATED once the buffer holds maxEpisodeLength steps, :848-850) and stops
+ * collecting at the first step after which combinedTraj holds >= tsPerItr timesteps (:665). Here both levels live on the device:
+ * per-player buffers [num_players][max_episode_length] and the combined stream; a finished segment is moved by a device copy at
+ * the step it finishes, so the combined tensors are at any time exactly what the reference's vectors would hold. */
+typedef struct ggl_traj ggl_traj;
+typedef struct ggl_traj_desc {
+    int32_t device;
+    int32_t num_players;          /* envSet->state.numPlayers */
+    int32_t players_per_arena;    /* terminals are per arena (EnvSet.h:35-60); player p sits in arena p / players_per_arena */
+    int32_t obs_size, num_actions;
+    int32_t max_episode_length;   /* (int)(maxEpisodeDuration * 120 / tickSkip), Learner.cpp:550; also the per-player buffer depth */
+    int64_t capacity_timesteps;   /* rows of the combined stream: >= tsPerItr + what one step can append */
+    int64_t capacity_truncated;   /* rows of nextStates */
+} ggl_traj_desc;
+typedef struct ggl_traj_views {   /* DEVICE pointers into the combined stream, valid until destroy; rows [0, length) are defined */
+    float*   states;        /* [capacity_timesteps, obs_size]   Trajectory::states      */
+    uint8_t* action_masks;  /* [capacity_timesteps, num_actions]            actionMasks */
+    int32_t* actions;       /* [capacity_timesteps]                          actions     */
+    float*   log_probs;     /* [capacity_timesteps]                          logProbs    */
+    float*   rewards;       /* [capacity_timesteps]                          rewards     */
+    int8_t*  terminals;     /* [capacity_timesteps]  0 / 1 NORMAL / 2 TRUNCATED          */
+    float*   next_states;   /* [capacity_truncated, obs_size]   final obs of every TRUNCATED segment, in stream order (:855-858) */
+} ggl_traj_views;
+int  ggl_traj_create(const ggl_traj_desc* d, ggl_traj** out);
+int  ggl_traj_destroy(ggl_traj* t);
+int  ggl_traj_views_get(ggl_traj* t, ggl_traj_views* out);
+/* Start of a collection iteration: combinedTraj.Clear() (:631). Per-player buffers keep their unfinished episodes. */
+int  ggl_traj_begin_iteration(ggl_traj* t, void* stream);
+/* Before the env step (:701-712): append every player's current obs row and mask row to its buffer. d_obs f32[num_players,
+ * obs_size], d_masks u8[num_players, num_actions] are the envset's output buffers after Reset. */
+int  ggl_traj_push_obs(ggl_traj* t, const float* d_obs, const uint8_t* d_masks, void* stream);
+/* After the env step (:823-863): append action, reward, log prob and the terminal type (arena terminal, else TRUNCATED when the
+ * buffer reached max_episode_length); move finished buffers to the combined stream in player order, push the final obs row of
+ * TRUNCATED ones (d_obs_final = the envset's obs after the step) to next_states. d_terminals u8[num_arenas]. */
+int  ggl_traj_push_result(ggl_traj* t, const int32_t* d_actions, const float* d_log_probs, const float* d_rewards,
+                          const uint8_t* d_terminals, const float* d_obs_final, void* stream);
+/* combinedTraj.Length() and the number of next_states rows after the pushes queued so far on `stream` (synchronises it).
+ * GGL_ERR_INVALID if a push ran out of capacity (nothing is written past the end). */
+int  ggl_traj_counts(ggl_traj* t, void* stream, int64_t* out_length, int64_t* out_truncated);
+/* debug / tests: current length of every player's unfinished buffer (host int32[num_players]) */
+int  ggl_traj_player_lengths(ggl_traj* t, int32_t* h_out);
 
 /* kernels launched by this library since load (bench.py's gpu_launches) */
 uint64_t ggl_launch_count(void);

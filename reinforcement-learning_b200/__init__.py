@@ -41,6 +41,15 @@ def lib():
             L.ggl_expbuf_plan_batches.argtypes = [C.c_int64, C.c_int64, C.c_int, C.c_void_p, C.c_void_p, C.c_int64]
             L.ggl_expbuf_gather.argtypes = [C.POINTER(abi.ExpBufTensors), C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.c_void_p,
                                             C.c_int64, C.c_int64, C.POINTER(abi.ExpBufTensors), C.c_void_p]
+        if hasattr(L, "ggl_traj_create"):
+            L.ggl_traj_create.argtypes = [C.POINTER(abi.TrajDesc), C.POINTER(C.c_void_p)]
+            L.ggl_traj_destroy.argtypes = [C.c_void_p]
+            L.ggl_traj_views_get.argtypes = [C.c_void_p, C.POINTER(abi.TrajViews)]
+            L.ggl_traj_begin_iteration.argtypes = [C.c_void_p, C.c_void_p]
+            L.ggl_traj_push_obs.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+            L.ggl_traj_push_result.argtypes = [C.c_void_p] * 7
+            L.ggl_traj_counts.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
+            L.ggl_traj_player_lengths.argtypes = [C.c_void_p, C.c_void_p]
         if hasattr(L, "ggl_envset_create"):
             L.ggl_envset_create.argtypes = [C.POINTER(abi.EnvSetDesc), C.POINTER(C.c_void_p)]
             L.ggl_envset_destroy.argtypes = [C.c_void_p]
@@ -283,3 +292,63 @@ class EnvSet:
     def set_slot_order(self, car_ids):
         a = np.ascontiguousarray(car_ids, np.int32)
         _check(lib().ggl_envset_set_slot_order(self.h, a.ctypes.data))
+
+
+class TrajectoryStore:
+    """Device-side `trajectories[]` + `combinedTraj` of Learner::Start (Learner.cpp:504-547, 701-712, 823-863) over ggl_traj_*.
+    `tensors()` returns torch views of the first `length` rows of the combined stream (zero-copy)."""
+
+    def __init__(self, num_players, players_per_arena, obs_size, num_actions, max_episode_length, capacity_timesteps,
+                 capacity_truncated=None, device=0):
+        import torch
+        d = abi.TrajDesc()
+        d.device, d.num_players, d.players_per_arena, d.obs_size, d.num_actions = device, num_players, players_per_arena, obs_size, num_actions
+        d.max_episode_length, d.capacity_timesteps = max_episode_length, capacity_timesteps
+        d.capacity_truncated = capacity_truncated if capacity_truncated is not None else capacity_timesteps
+        self.desc = d
+        self.device = torch.device("cuda", device)
+        h = C.c_void_p()
+        _check(lib().ggl_traj_create(C.byref(d), C.byref(h)))
+        self.h = h
+        v = abi.TrajViews()
+        _check(lib().ggl_traj_views_get(self.h, C.byref(v)))
+        self.views = v
+
+    def _stream(self, stream):
+        import torch
+        return C.c_void_p(stream if stream is not None else torch.cuda.current_stream(self.device).cuda_stream)
+
+    def begin_iteration(self, stream=None):
+        _check(lib().ggl_traj_begin_iteration(self.h, self._stream(stream)))
+
+    def push_obs(self, obs, masks, stream=None):
+        _check(lib().ggl_traj_push_obs(self.h, obs.data_ptr(), masks.data_ptr(), self._stream(stream)))
+
+    def push_result(self, actions, log_probs, rewards, terminals, obs_final, stream=None):
+        _check(lib().ggl_traj_push_result(self.h, actions.data_ptr(), log_probs.data_ptr(), rewards.data_ptr(), terminals.data_ptr(),
+                                          obs_final.data_ptr(), self._stream(stream)))
+
+    def counts(self, stream=None):
+        a, b = C.c_int64(), C.c_int64()
+        _check(lib().ggl_traj_counts(self.h, self._stream(stream), C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    def player_lengths(self):
+        out = np.zeros(self.desc.num_players, np.int32)
+        _check(lib().ggl_traj_player_lengths(self.h, out.ctypes.data))
+        return out
+
+    def tensors(self, stream=None):
+        import torch
+        L, K = self.counts(stream)
+        d, v = self.desc, self.views
+        t = lambda p, shape, ts: (torch.as_tensor(_DevView(p, shape, ts), device=self.device) if shape[0] > 0 else
+                                  torch.empty(shape, dtype={"<f4": torch.float32, "|u1": torch.uint8, "<i4": torch.int32, "|i1": torch.int8}[ts], device=self.device))
+        return {"states": t(v.states, (L, d.obs_size), "<f4"), "action_masks": t(v.action_masks, (L, d.num_actions), "|u1"),
+                "actions": t(v.actions, (L,), "<i4"), "log_probs": t(v.log_probs, (L,), "<f4"), "rewards": t(v.rewards, (L,), "<f4"),
+                "terminals": t(v.terminals, (L,), "|i1"), "next_states": t(v.next_states, (K, d.obs_size), "<f4")}
+
+    def close(self):
+        if self.h:
+            lib().ggl_traj_destroy(self.h)
+            self.h = None

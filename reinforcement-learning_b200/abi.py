@@ -94,6 +94,17 @@ class ExpBufTensors(C.Structure):
                 ("action_masks", C.c_void_p), ("advantages", C.c_void_p)]
 
 
+class TrajDesc(C.Structure):
+    _fields_ = [("device", C.c_int32), ("num_players", C.c_int32), ("players_per_arena", C.c_int32), ("obs_size", C.c_int32),
+                ("num_actions", C.c_int32), ("max_episode_length", C.c_int32), ("capacity_timesteps", C.c_int64),
+                ("capacity_truncated", C.c_int64)]
+
+
+class TrajViews(C.Structure):
+    _fields_ = [("states", C.c_void_p), ("action_masks", C.c_void_p), ("actions", C.c_void_p), ("log_probs", C.c_void_p),
+                ("rewards", C.c_void_p), ("terminals", C.c_void_p), ("next_states", C.c_void_p)]
+
+
 class EnvSetViews(C.Structure):
     _fields_ = [("num_arenas", C.c_int32), ("num_players", C.c_int32), ("obs_size", C.c_int32),
                 ("num_actions", C.c_int32), ("players_per_arena", C.c_int32),

@@ -18,6 +18,7 @@ SOURCES = {
     "gae.cu": ["-fmad=false"],
     "envset.cu": ["-fmad=false"],
     "expbuf.cu": [],
+    "traj.cu": [],
 }
 
 
