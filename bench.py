@@ -454,6 +454,119 @@ def bench_expbuf(args, rank, world, local):
     return line
 
 
+
+# ------------------------------------------------------------------------------------------------ trajectory-assembly workload
+def bench_traj(args, rank, world, local):
+    """Trajectory assembly at config C2's shape: 16 384 players (4 096 arenas 2v2), obs 167, 90 actions,
+    maxEpisodeLength 1800 (120 s at tick_skip 8), arena terminals with probability 1/150 per step (mean episode = the no-touch
+    timeout). A step = push_obs + push_result; bytes = every appended row in and out, plus every moved row in and out."""
+    import numpy as np
+    import torch
+    ggl = importlib.import_module(PKG)
+    dev = torch.device("cuda", local)
+    arenas, ppa, obs, na, max_len = ARENAS_PER_GPU, 2 * PLAYERS_PER_TEAM, OBS_SIZE_ADV_2V2, 90, 1800
+    n = arenas * ppa
+    ts_per_itr = 1 << 20
+    store = ggl.TrajectoryStore(n, ppa, obs, na, max_len, capacity_timesteps=ts_per_itr + (3 << 20), device=local)
+    g = torch.Generator(device=dev); g.manual_seed(11 + rank)
+    obs_d = torch.randn(n, obs, device=dev, generator=g); obs_f = torch.randn(n, obs, device=dev, generator=g)
+    masks = (torch.rand(n, na, device=dev, generator=g) < 0.5).to(torch.uint8)
+    acts = torch.randint(0, na, (n,), device=dev, generator=g, dtype=torch.int32)
+    logp = torch.randn(n, device=dev, generator=g); rew = torch.randn(n, device=dev, generator=g)
+    nterm = 64
+    u = torch.rand(nterm, arenas, device=dev, generator=g)
+    terms = torch.where(u < 0.5 / 150, 1, torch.where(u < 1.0 / 150, 2, 0)).to(torch.uint8)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    s = torch.cuda.current_stream(dev)
+    row_bytes = 4 * obs + na + 13
+
+    def one(i):
+        store.push_obs(obs_d, masks)
+        store.push_result(acts, logp, rew, terms[i % nterm], obs_f)
+
+    store.begin_iteration()
+    for i in range(300 + args.warmup):                  # pre-roll: episode lengths reach their steady-state mix
+        one(i)
+        if store.counts()[0] >= ts_per_itr:
+            store.begin_iteration()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = ggl.launch_count()
+    barrier_sync(world)
+    # the four launches of a step replayed as one CUDA graph per terminal pattern (a launch-bound inner loop: 32 MB per step)
+    graphs = []
+    side = torch.cuda.Stream(dev)
+    side.wait_stream(s)
+    with torch.cuda.stream(side):
+        for j in range(nterm):
+            gr = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gr, stream=side):
+                one(j)
+            graphs.append(gr)
+    s.wait_stream(side)
+    torch.cuda.synchronize()
+    total_ms, moved, trunc = 0.0, 0, 0
+    for i in range(args.steps):
+        L0, K0 = store.counts()
+        if L0 >= ts_per_itr:
+            store.begin_iteration(); L0, K0 = 0, 0
+        flush.zero_()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(s); graphs[i % nterm].replay(); e1.record(s)
+        L1, K1 = store.counts()
+        total_ms += e0.elapsed_time(e1); moved += L1 - L0; trunc += K1 - K0
+    barrier_sync(world)
+    launches = ggl.launch_count() - l0
+    clocks = sampler.stop() if rank == 0 else None
+    ms = max_over_ranks(total_ms / args.steps, world)
+    bytes_step = 2 * row_bytes * n + (2 * row_bytes * moved + 8 * obs * trunc) / args.steps
+    gbs = bytes_step / (ms * 1e-3) / 1e9
+    peak, src = peaks()
+    # e2e: the env outputs arrive in pinned host buffers (a host-side env), the stream length goes back to the host every step
+    hb = [x.cpu().pin_memory() for x in (obs_d, masks, acts, logp, rew, terms[0], obs_f)]
+    db = [torch.empty_like(x, device=dev) for x in hb]
+    torch.cuda.synchronize()
+    n_e2e = max(5, args.steps)
+    t0 = time.perf_counter()
+    for i in range(n_e2e):
+        for d, h in zip(db, hb):
+            d.copy_(h, non_blocking=True)
+        store.push_obs(db[0], db[1]); store.push_result(db[2], db[3], db[4], db[5], db[6])
+        if store.counts()[0] >= ts_per_itr:
+            store.begin_iteration()
+    e2e_s = max_over_ranks((time.perf_counter() - t0) / n_e2e, world)
+    h2d = sum(h.numel() * h.element_size() for h in hb)
+    line = {"metric": "trajectory assembly GB/s", "value": gbs * world, "unit": "GB/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": "trajectory assembly, %d players (2v2 x %d arenas), obs 167, 90 actions, maxEpisodeLength 1800, arena terminal "
+                                   "probability 1/150 per step, tsPerItr 2^20" % (n, arenas),
+                       "l2": "256 MB flush before every timed step", "launch": "CUDA graph replay of the step's three launches", "agent_steps_per_s": n * world / (ms * 1e-3)},
+            "e2e": {"value": bytes_step * world / e2e_s / 1e9, "unit": "GB/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 32,
+                    "api": "H2D env outputs + ggl_traj_push_obs + ggl_traj_push_result + ggl_traj_counts"},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak, "traffic": None,
+                         "kernel": "traj_push_obs_kernel + traj_push_scalars_kernel + traj_scan_kernel + traj_move_kernel (one graph replay per step)", "peak_source": src,
+                         "algorithmic_bytes_per_launch": bytes_step}}
+    if rank == 0:
+        line["clocks"] = clocks
+        if world == 1:
+            import traj_oracle as to
+            pn, steps_cpu = 1024, 60
+            o = to.TrajOracle(pn, ppa, 25)
+            ho, hm = hb[0][:pn].numpy(), hb[1][:pn].numpy()
+            ha, hl, hr, hf = hb[2][:pn].numpy(), hb[3][:pn].numpy(), hb[4][:pn].numpy(), hb[6][:pn].numpy()
+            ht = np.zeros(pn // ppa, np.uint8)
+            o.begin_iteration()
+            t0 = time.perf_counter()
+            for i in range(steps_cpu):
+                o.push_obs(ho, hm); o.push_result(ha, hl, hr, ht, hf)
+            dt = time.perf_counter() - t0
+            line["cpu_baseline"] = {"value": 4 * row_bytes * pn * steps_cpu / dt / 1e9, "unit": "GB/s", "cores": 1, "kind": "port",
+                                    "sample": "1024 players x 60 steps, maxEpisodeLength 25, Python restatement of Learner.cpp:701-712/823-863"}
+    store.close()
+    return line
+
 # ------------------------------------------------------------------------------------------------ reference arm
 def bench_reference(args):
     """Times the reference's own CPU EnvSet on this box's host cores (oracle/_ref). Rank 0 only."""
@@ -484,7 +597,7 @@ def main():
     ap.add_argument("--steps", type=int, default=None)
     ap.add_argument("--warmup", type=int, default=None)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default=None, choices=["env", "gae", "expbuf"])
+    ap.add_argument("--workload", default=None, choices=["env", "gae", "expbuf", "traj"])
     args = ap.parse_args()
     if args.impl == "reference":
         args.steps = args.steps if args.steps is not None else 30
@@ -502,7 +615,7 @@ def main():
         args.warmup = 20 if workload == "env" else 5
     args.warmup = max(args.warmup, 3)
     rank, world, local = dist_setup(args.gpus)
-    line = {"env": bench_env, "gae": bench_gae, "expbuf": bench_expbuf}[workload](args, rank, world, local)
+    line = {"env": bench_env, "gae": bench_gae, "expbuf": bench_expbuf, "traj": bench_traj}[workload](args, rank, world, local)
     if rank == 0:
         print(json.dumps(line))
     if world > 1:

@@ -7,9 +7,9 @@
 // Here the per-player buffers and the combined stream are device tensors:
 //   per player   pStates f32[N][cap][obs]  pMasks u8[N][cap][A]  pActions i32 / pLogProbs f32 / pRewards f32 / pTerminals i8 [N][cap]
 //   combined     the same six tensors with capacity_timesteps rows + nextStates f32[capacity_truncated][obs]
-// and a step costs three small launches: append (HBM-bound, one row in and out per player), an ordered scan over the players
-// that finished this step (segment offsets in player order, exactly the order of the reference's loop at :844-862), and the
-// segment copy (HBM-bound, every row moves once more, like the reference's second copy).
+// and a step costs four small launches: the row append (HBM-bound, one row in and out per player), the scalar append, an
+// ordered scan over the players that finished this step (segment offsets in player order, exactly the order of the
+// reference's loop at :844-862), and the segment copy (HBM-bound, every row moves once more, like the reference's second copy).
 #include <cstdlib>
 #include "common.cuh"
 
@@ -21,11 +21,30 @@ struct TrajDev {
     int N, ppa, obs, A, cap, maxEpLen;
     long long capL, capK;
     float* pStates; uint8_t* pMasks; int32_t* pActions; float* pLogProbs; float* pRewards; int8_t* pTerminals; int* pLen;
-    int* segLen; int8_t* segTerm;                       // per player, this step: length of the finished buffer (0 = still running), terminal type
+    int* segLen;                                        // per player, this step: length of the finished buffer (0 = still running)
     int* finList; long long* finOff; long long* finNext;  // per finished player in player order: id, first row in the stream, nextStates row or -1
     float* cStates; uint8_t* cMasks; int32_t* cActions; float* cLogProbs; float* cRewards; int8_t* cTerminals; float* cNext;
     long long* counts;                                  // [0] combined length, [1] nextStates rows, [2] overflow flag, [3] finished this step
 };
+
+// warp copy of n 4-byte (or 2-byte) words, eight loads in flight per lane before the first store (source and destination may
+// alias as far as the compiler knows, so a plain loop would pay one HBM round trip per word)
+template <class W>
+__device__ __forceinline__ void warp_copy(W* __restrict__ d, const W* __restrict__ s, int n, int lane) {
+    for (int base = 0; base < n; base += 256) {
+        W v[8];
+#pragma unroll
+        for (int j = 0; j < 8; j++) { const int i = base + j * 32 + lane; v[j] = i < n ? __ldcs(s + i) : W(0); }
+#pragma unroll
+        for (int j = 0; j < 8; j++) { const int i = base + j * 32 + lane; if (i < n) __stcs(d + i, v[j]); }
+    }
+}
+__device__ __forceinline__ void warp_copy_bytes(uint8_t* d, const uint8_t* s, int n, int lane) {
+    if ((n & 1) == 0 && ((reinterpret_cast<uintptr_t>(d) | reinterpret_cast<uintptr_t>(s)) & 1) == 0)
+        warp_copy(reinterpret_cast<unsigned short*>(d), reinterpret_cast<const unsigned short*>(s), n >> 1, lane);
+    else
+        warp_copy(d, s, n, lane);
+}
 
 // :701-712 — one warp per player appends the obs row and the mask row at that player's current length
 __global__ void __launch_bounds__(256) traj_push_obs_kernel(TrajDev T, const float* __restrict__ obs, const uint8_t* __restrict__ masks) {
@@ -33,23 +52,13 @@ __global__ void __launch_bounds__(256) traj_push_obs_kernel(TrajDev T, const flo
     const int p = (int)(((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
     if (p >= T.N) return;
     const long long row = (long long)p * T.cap + T.pLen[p];
-    const float* s = obs + (long long)p * T.obs;
-    float* d = T.pStates + row * T.obs;
-    for (int k = lane; k < T.obs; k += 32) d[k] = __ldcs(s + k);
-    const uint8_t* sm = masks + (long long)p * T.A;
-    uint8_t* dm = T.pMasks + row * T.A;
-    if ((T.A & 1) == 0) {
-        for (int k = lane; k < (T.A >> 1); k += 32) reinterpret_cast<unsigned short*>(dm)[k] = reinterpret_cast<const unsigned short*>(sm)[k];
-    } else {
-        for (int k = lane; k < T.A; k += 32) dm[k] = sm[k];
-    }
+    warp_copy(T.pStates + row * T.obs, obs + (long long)p * T.obs, T.obs, lane);
+    warp_copy_bytes(T.pMasks + row * T.A, masks + (long long)p * T.A, T.A, lane);
 }
 
-// :823-850 — one thread per player: scalars, terminal type, forced truncation
-__global__ void __launch_bounds__(256) traj_push_scalars_kernel(TrajDev T, const int32_t* __restrict__ actions, const float* __restrict__ logProbs,
-                                                                 const float* __restrict__ rewards, const uint8_t* __restrict__ terminals) {
-    const int p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= T.N) return;
+// :823-850 — per player: scalars, terminal type, forced truncation; returns the length of the finished buffer (0 = still running)
+__device__ __forceinline__ int traj_push_scalars(const TrajDev& T, int p, const int32_t* __restrict__ actions, const float* __restrict__ logProbs,
+                                                 const float* __restrict__ rewards, const uint8_t* __restrict__ terminals, int8_t& termOut) {
     const int len = T.pLen[p];
     const long long row = (long long)p * T.cap + len;
     T.pActions[row] = actions[p];
@@ -59,9 +68,17 @@ __global__ void __launch_bounds__(256) traj_push_scalars_kernel(TrajDev T, const
     int8_t term = (int8_t)terminals[p / T.ppa];                     // :831-841
     if (!term && newLen >= T.maxEpLen) term = 2;                    // :848-850 forced TRUNCATED
     T.pTerminals[row] = term;
-    T.segLen[p] = term ? newLen : 0;
-    T.segTerm[p] = term;
+    T.segLen[p] = term == 2 ? -newLen : (term ? newLen : 0);        // TRUNCATED rides in the sign
     T.pLen[p] = term ? 0 : newLen;                                  // traj.Clear() at :861
+    termOut = term;
+    return term ? newLen : 0;
+}
+
+__global__ void __launch_bounds__(256) traj_push_scalars_kernel(TrajDev T, const int32_t* __restrict__ actions, const float* __restrict__ logProbs,
+                                                                 const float* __restrict__ rewards, const uint8_t* __restrict__ terminals) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    int8_t term;
+    if (p < T.N) traj_push_scalars(T, p, actions, logProbs, rewards, terminals, term);
 }
 
 // :844-862 — where each finished buffer lands: exclusive sums over the players in index order. One block; N is at most ~1e5.
@@ -75,8 +92,8 @@ __global__ void __launch_bounds__(1024) traj_scan_kernel(TrajDev T) {
     const long long baseLen = T.counts[0], baseK = T.counts[1];
     for (int c0 = 0; c0 < T.N; c0 += 1024) {
         const int p = c0 + tid;
-        const int len = p < T.N ? T.segLen[p] : 0;
-        const int fin = len > 0, tr = fin && T.segTerm[p] == 2;
+        const int sl = p < T.N ? T.segLen[p] : 0;
+        const int len = abs(sl), fin = sl != 0, tr = sl < 0;
         int sLen = len, sFin = fin, sTr = tr;                       // inclusive warp scans
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
@@ -129,27 +146,13 @@ __global__ void __launch_bounds__(256) traj_move_kernel(TrajDev T, const float* 
     for (long long item = warp; item < items; item += nwarps) {
         const int k = (int)(item / chunks), c = (int)(item - (long long)k * chunks);
         const int p = T.finList[k];
-        const int len = T.segLen[p];
+        const int len = abs(T.segLen[p]);
         const int r0 = c * TRAJ_ROWS;
         if (r0 >= len) continue;
         const int rows = min(TRAJ_ROWS, len - r0);
         const long long src = (long long)p * T.cap + r0, dst = T.finOff[k] + r0;
-        {
-            const float* s = T.pStates + src * T.obs;
-            float* d = T.cStates + dst * T.obs;
-            const int n = rows * T.obs;
-            for (int w = lane; w < n; w += 32) __stcs(d + w, __ldcs(s + w));
-        }
-        {
-            const uint8_t* s = T.pMasks + src * T.A;
-            uint8_t* d = T.cMasks + dst * T.A;
-            const int n = rows * T.A;
-            if ((T.A & 1) == 0) {
-                for (int w = lane; w < (n >> 1); w += 32) reinterpret_cast<unsigned short*>(d)[w] = reinterpret_cast<const unsigned short*>(s)[w];
-            } else {
-                for (int w = lane; w < n; w += 32) d[w] = s[w];
-            }
-        }
+        warp_copy(T.cStates + dst * T.obs, T.pStates + src * T.obs, rows * T.obs, lane);
+        warp_copy_bytes(T.cMasks + dst * T.A, T.pMasks + src * T.A, rows * T.A, lane);
         if (lane < rows) {
             T.cActions[dst + lane] = T.pActions[src + lane];
             T.cLogProbs[dst + lane] = T.pLogProbs[src + lane];
@@ -159,7 +162,7 @@ __global__ void __launch_bounds__(256) traj_move_kernel(TrajDev T, const float* 
         if (c == 0 && T.finNext[k] >= 0) {
             const float* s = obsFinal + (long long)p * T.obs;
             float* d = T.cNext + T.finNext[k] * T.obs;
-            for (int w = lane; w < T.obs; w += 32) d[w] = s[w];
+            warp_copy(d, s, T.obs, lane);
         }
     }
 }
@@ -212,7 +215,7 @@ extern "C" int ggl_traj_create(const ggl_traj_desc* d, ggl_traj** out) {
     const size_t rows = (size_t)T.N * T.cap;
     TRAJ_TRY(talloc(t, &T.pStates, rows * T.obs)); TRAJ_TRY(talloc(t, &T.pMasks, rows * T.A)); TRAJ_TRY(talloc(t, &T.pActions, rows));
     TRAJ_TRY(talloc(t, &T.pLogProbs, rows)); TRAJ_TRY(talloc(t, &T.pRewards, rows)); TRAJ_TRY(talloc(t, &T.pTerminals, rows));
-    TRAJ_TRY(talloc(t, &T.pLen, (size_t)T.N)); TRAJ_TRY(talloc(t, &T.segLen, (size_t)T.N)); TRAJ_TRY(talloc(t, &T.segTerm, (size_t)T.N));
+    TRAJ_TRY(talloc(t, &T.pLen, (size_t)T.N)); TRAJ_TRY(talloc(t, &T.segLen, (size_t)T.N));
     TRAJ_TRY(talloc(t, &T.finList, (size_t)T.N)); TRAJ_TRY(talloc(t, &T.finOff, (size_t)T.N)); TRAJ_TRY(talloc(t, &T.finNext, (size_t)T.N));
     TRAJ_TRY(talloc(t, &T.cStates, (size_t)T.capL * T.obs)); TRAJ_TRY(talloc(t, &T.cMasks, (size_t)T.capL * T.A));
     TRAJ_TRY(talloc(t, &T.cActions, (size_t)T.capL)); TRAJ_TRY(talloc(t, &T.cLogProbs, (size_t)T.capL)); TRAJ_TRY(talloc(t, &T.cRewards, (size_t)T.capL));
