@@ -591,7 +591,25 @@ def bench_reference(args):
     return line
 
 
+_REAL_STDOUT = None
+
+
+def _claim_stdout():
+    """stdout carries exactly ONE line, the JSON: anything a library writes to fd 1 meanwhile (NCCL prints its version there
+    when NCCL_DEBUG is set on the box) goes to stderr instead."""
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
+
+
+def _emit(line):
+    sys.stdout.flush()
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
+
+
 def main():
+    _claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=None)
@@ -604,7 +622,7 @@ def main():
         args.warmup = args.warmup if args.warmup is not None else 5
         line = bench_reference(args)
         if line is not None:
-            print(json.dumps(line))
+            _emit(line)
         return
     ggl = importlib.import_module(PKG)
     ggl.lib()   # fail loudly if the CUDA library is missing
@@ -617,7 +635,7 @@ def main():
     rank, world, local = dist_setup(args.gpus)
     line = {"env": bench_env, "gae": bench_gae, "expbuf": bench_expbuf, "traj": bench_traj}[workload](args, rank, world, local)
     if rank == 0:
-        print(json.dumps(line))
+        _emit(line)
     if world > 1:
         import torch.distributed as dist
         dist.destroy_process_group()
