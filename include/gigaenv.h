@@ -341,6 +341,13 @@ int  ggl_traj_counts(ggl_traj* t, void* stream, int64_t* out_length, int64_t* ou
 /* debug / tests: current length of every player's unfinished buffer (host int32[num_players]) */
 int  ggl_traj_player_lengths(ggl_traj* t, int32_t* h_out);
 
+/* Device-memory plumbing for host code that links this library and nothing of CUDA (the g++-only mirrors under host/):
+ * cudaMalloc / cudaFree / cudaMemcpyAsync H2D (asynchronous on `stream`) / D2H (synchronises `stream`). */
+int  ggl_dev_malloc(int device, size_t bytes, void** out);
+int  ggl_dev_free(void* p);
+int  ggl_dev_upload(void* d_dst, const void* h_src, size_t bytes, void* stream);
+int  ggl_dev_download(void* h_dst, const void* d_src, size_t bytes, void* stream);
+
 /* kernels launched by this library since load (bench.py's gpu_launches) */
 uint64_t ggl_launch_count(void);
 const char* ggl_last_error(void);

@@ -63,3 +63,25 @@ extern "C" int ggl_host_random_actions(const uint8_t* h_masks, int32_t* h_action
     }
     return GGL_OK;
 }
+
+// Device-memory plumbing for host code that sees the GPU through this C ABI alone (the g++-only C++ mirrors under host/).
+extern "C" int ggl_dev_malloc(int device, size_t bytes, void** out) {
+    if (!out) { ggl::set_error("ggl_dev_malloc: null output"); return GGL_ERR_INVALID; }
+    GGL_CUDA(cudaSetDevice(device));
+    cudaError_t e = cudaMalloc(out, bytes ? bytes : 1);
+    if (e != cudaSuccess) { ggl::set_error("ggl_dev_malloc(%zu bytes) -> %s", bytes, cudaGetErrorString(e)); return GGL_ERR_NOMEM; }
+    return GGL_OK;
+}
+extern "C" int ggl_dev_free(void* p) {
+    if (p) GGL_CUDA(cudaFree(p));
+    return GGL_OK;
+}
+extern "C" int ggl_dev_upload(void* d_dst, const void* h_src, size_t bytes, void* stream) {
+    GGL_CUDA(cudaMemcpyAsync(d_dst, h_src, bytes, cudaMemcpyHostToDevice, (cudaStream_t)stream));
+    return GGL_OK;
+}
+extern "C" int ggl_dev_download(void* h_dst, const void* d_src, size_t bytes, void* stream) {
+    GGL_CUDA(cudaMemcpyAsync(h_dst, d_src, bytes, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    GGL_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    return GGL_OK;
+}

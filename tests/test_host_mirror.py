@@ -28,6 +28,33 @@ def build_host_test():
     return OUT
 
 
+def build_experience_test():
+    src = os.path.join(ROOT, "tests", "host", "test_experience_host.cpp")
+    out = os.path.join(ROOT, "tests", "host", "_build", "test_experience_host")
+    deps = [src, os.path.join(PKG, "host", "GigaLearnCPP", "Experience.h"), os.path.join(ROOT, "include", "gigaenv.h"), os.path.join(PKG, "libgigaenv_cuda.so")]
+    if os.path.exists(out) and all(os.path.getmtime(out) >= os.path.getmtime(d) for d in deps):
+        return out
+    os.makedirs(os.path.dirname(out), exist_ok=True)
+    subprocess.check_call(["g++", "-std=c++17", "-O1", "-Wall", "-I", os.path.join(PKG, "host"), src, "-o", out,
+                           "-L", PKG, "-lgigaenv_cuda", "-Wl,-rpath," + PKG, "-Wl,-rpath,/usr/local/cuda/lib64"])
+    return out
+
+
+def test_learner_side_mirror_compiles_without_cuda_headers(ggl):
+    ggl.lib()
+    assert os.path.exists(build_experience_test())
+
+
+@pytest.mark.gpu
+def test_learner_side_mirror_on_gpu(ggl):
+    """GGL::ExperienceBuffer (two epochs against std::shuffle of the same engine and seed) and GGL::TrajectoryStore (the
+    hand-checked order of tests/test_traj_oracle_cpu.py) through the C++ mirror."""
+    exe = build_experience_test()
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "experience ok=1" in r.stdout and "trajectory ok=1 bad_desc_throws=1" in r.stdout
+
+
 def test_mirror_translates_plugins_and_rejects_user_subclasses(ggl):
     ggl.lib()
     exe = build_host_test()
