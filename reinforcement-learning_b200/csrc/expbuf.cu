@@ -149,8 +149,14 @@ __global__ void __launch_bounds__(256) expbuf_gather_kernel(ExpPtrs p, const int
 // Here a block owns a TILE of 32 consecutive output samples. The 16-byte-aligned span that contains each source row is copied to
 // shared memory with cp.async (16 bytes per lane, no registers held, a whole tile in flight per stage while the previous one is
 // written), and the tile, contiguous in every destination and 128-byte aligned (32 rows), leaves as whole-line stores.
-constexpr int EXP_TILE = 32;
-constexpr int EXP_STAGES = 2;
+#ifndef EXP_TILE_CFG
+#define EXP_TILE_CFG 32
+#endif
+#ifndef EXP_STAGES_CFG
+#define EXP_STAGES_CFG 2
+#endif
+constexpr int EXP_TILE = EXP_TILE_CFG;        // 16 or 32 samples: the tile starts 16-byte aligned in every destination
+constexpr int EXP_STAGES = EXP_STAGES_CFG;    // tiles in flight per block = EXP_STAGES - 1 while one is written out
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, int srcBytes) {
@@ -243,14 +249,18 @@ __global__ void __launch_bounds__(256) expbuf_gather_staged_kernel(ExpPtrs p, co
     const bool dstMask16 = (reinterpret_cast<uintptr_t>(p.oMasks) & 15) == 0;
     long long tile = blockIdx.x;
     if (tile >= tiles) return;
-    long long rowCur = fetch_row(tile);
-    long long rowNext = fetch_row(tile + gridDim.x);
-    issue(0, rowCur);
+    const long long stride = gridDim.x;
+    // prologue: EXP_STAGES - 1 tiles in flight (tiles past the end issue nothing but still commit a group)
+#pragma unroll
+    for (int j = 0; j < EXP_STAGES - 1; j++) issue(j, fetch_row(tile + j * stride));
+    long long rowPref = fetch_row(tile + (EXP_STAGES - 1) * stride);
     int st = 0;
-    for (; tile < tiles; tile += gridDim.x, st ^= 1) {
-        const long long rowAfter = fetch_row(tile + 2 * (long long)gridDim.x);
-        if (tile + gridDim.x < tiles) { issue(st ^ 1, rowNext); cp_async_wait<1>(); } else { cp_async_wait<0>(); }
-        __syncthreads();
+    for (; tile < tiles; tile += stride, st = (st + 1 == EXP_STAGES ? 0 : st + 1)) {
+        const long long rowLater = fetch_row(tile + EXP_STAGES * stride);
+        cp_async_wait<EXP_STAGES - 2>();                               // this tile's group has landed (for this thread)
+        __syncthreads();                                               // ... for every thread; and everyone is done with the previous tile
+        issue(st == 0 ? EXP_STAGES - 1 : st - 1, rowPref);             // refill the stage the previous iteration read
+        rowPref = rowLater;
         // ---- write the tile out: every destination range of the tile is contiguous
         const unsigned char* base = stage_ptr(st);
         const unsigned char* sS = base;
@@ -320,7 +330,7 @@ __global__ void __launch_bounds__(256) expbuf_gather_staged_kernel(ExpPtrs p, co
             }
         }
         if (tid < 4 * EXP_TILE) {
-            const int which = tid >> 5, j = tid & 31;                 // EXP_TILE == 32
+            const int which = tid / EXP_TILE, j = tid % EXP_TILE;
             if (j < nvalid) {
                 const uint32_t v = sScal[which * EXP_TILE + j];
                 if (which == 0) {
@@ -336,9 +346,8 @@ __global__ void __launch_bounds__(256) expbuf_gather_staged_kernel(ExpPtrs p, co
                 }
             }
         }
-        __syncthreads();                                               // the stage may be refilled
-        rowNext = rowAfter;
     }
+    cp_async_wait<0>();
 }
 
 }  // namespace

@@ -8,6 +8,7 @@ CASES = [
     (8, 6, 225, 90, 1000, 40, 0.05, 0.05), # 3v3, no forced truncation inside the run
     (64, 2, 89, 90, 7, 30, 0.0, 0.0),      # only forced truncations: every buffer flushes at 7
     (40, 4, 33, 8, 9, 50, 0.2, 0.0),       # frequent NORMAL terminals
+    (750, 4, 9, 6, 5, 14, 0.1, 0.1),       # 3000 players: the ordered scan runs over several 1024-player chunks
 ]
 
 
