@@ -17,6 +17,7 @@
  *   ggl_action_table             RLGymCPP/src/RLGymCPP/ActionParsers/DefaultAction.cpp:3-89
  *   ggl_expbuf_plan_batches / ggl_expbuf_gather   src/private/GigaLearnCPP/PPO/ExperienceBuffer.cpp:100-163 / :15-98
  *   ggl_traj_*                                     src/public/GigaLearnCPP/Learner.cpp:504-547, 701-712, 823-863 (trajectory assembly)
+ *   ggl_obsstat_*                                  src/private/GigaLearnCPP/Util/WelfordStat.h:69-243 (BatchedWelfordStat), Learner.cpp:680-694
  *
  * Conventions: plain pointers and sizes only; every function returns 0 on success or a
  * negative ggl_status; nothing throws across the boundary; ggl_last_error() gives the text.
@@ -340,6 +341,20 @@ int  ggl_traj_push_result(ggl_traj* t, const int32_t* d_actions, const float* d_
 int  ggl_traj_counts(ggl_traj* t, void* stream, int64_t* out_length, int64_t* out_truncated);
 /* debug / tests: current length of every player's unfinished buffer (host int32[num_players]) */
 int  ggl_traj_player_lengths(ggl_traj* t, int32_t* h_out);
+
+/* ---- Running obs statistics + in-place normalisation (src/private/GigaLearnCPP/Util/WelfordStat.h:69-243 BatchedWelfordStat, as
+ * used every collection step at src/public/GigaLearnCPP/Learner.cpp:680-694) ----
+ * increment_rows = IncrementRow (:89-97) over d_obs[d_row_indices[k]] for k = 0..n-1 IN ORDER (the row choice, Math::RandInt on the
+ * host, is an input); normalize = NormalizeInPlace (:131-216): no-op while count < 2, else obs[i][j] = obs[i][j] * inv[j] + neg[j]
+ * with the clamped-mean / floored-std coefficients. Double-precision state, bit-exact against the reference. */
+typedef struct ggl_obsstat ggl_obsstat;
+int  ggl_obsstat_create(int device, int width, ggl_obsstat** out);
+int  ggl_obsstat_destroy(ggl_obsstat* s);
+int  ggl_obsstat_increment_rows(ggl_obsstat* s, const float* d_obs, const int32_t* d_row_indices, int32_t n, void* stream);
+int  ggl_obsstat_normalize(ggl_obsstat* s, float* d_obs, int64_t num_rows, double mean_clamp, double min_std, void* stream);
+/* runningMeans / runningVariances / count to and from the host (ToJSON / ReadFromJSON, :218-232) */
+int  ggl_obsstat_get(ggl_obsstat* s, double* h_means, double* h_vars, int64_t* h_count);
+int  ggl_obsstat_set(ggl_obsstat* s, const double* h_means, const double* h_vars, int64_t count);
 
 /* Device-memory plumbing for host code that links this library and nothing of CUDA (the g++-only mirrors under host/):
  * cudaMalloc / cudaFree / cudaMemcpyAsync H2D (asynchronous on `stream`) / D2H (synchronises `stream`). */

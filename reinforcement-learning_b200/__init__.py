@@ -41,6 +41,13 @@ def lib():
             L.ggl_expbuf_plan_batches.argtypes = [C.c_int64, C.c_int64, C.c_int, C.c_void_p, C.c_void_p, C.c_int64]
             L.ggl_expbuf_gather.argtypes = [C.POINTER(abi.ExpBufTensors), C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.c_void_p,
                                             C.c_int64, C.c_int64, C.POINTER(abi.ExpBufTensors), C.c_void_p]
+        if hasattr(L, "ggl_obsstat_create"):
+            L.ggl_obsstat_create.argtypes = [C.c_int, C.c_int, C.POINTER(C.c_void_p)]
+            L.ggl_obsstat_destroy.argtypes = [C.c_void_p]
+            L.ggl_obsstat_increment_rows.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p]
+            L.ggl_obsstat_normalize.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_double, C.c_double, C.c_void_p]
+            L.ggl_obsstat_get.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_int64)]
+            L.ggl_obsstat_set.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64]
         if hasattr(L, "ggl_traj_create"):
             L.ggl_traj_create.argtypes = [C.POINTER(abi.TrajDesc), C.POINTER(C.c_void_p)]
             L.ggl_traj_destroy.argtypes = [C.c_void_p]
@@ -351,4 +358,39 @@ class TrajectoryStore:
     def close(self):
         if self.h:
             lib().ggl_traj_destroy(self.h)
+            self.h = None
+
+
+class ObsStat:
+    """Device-side GGL::BatchedWelfordStat (WelfordStat.h:69-243) as the Learner uses it (Learner.cpp:680-694)."""
+
+    def __init__(self, width, device=0):
+        import torch
+        self.width, self.device = width, torch.device("cuda", device)
+        h = C.c_void_p()
+        _check(lib().ggl_obsstat_create(device, width, C.byref(h)))
+        self.h = h
+
+    def _stream(self, stream):
+        import torch
+        return C.c_void_p(stream if stream is not None else torch.cuda.current_stream(self.device).cuda_stream)
+
+    def increment_rows(self, obs, row_indices, stream=None):
+        _check(lib().ggl_obsstat_increment_rows(self.h, obs.data_ptr(), row_indices.data_ptr(), int(row_indices.numel()), self._stream(stream)))
+
+    def normalize_in_place(self, obs, mean_clamp, min_std, stream=None):
+        _check(lib().ggl_obsstat_normalize(self.h, obs.data_ptr(), int(obs.shape[0]), float(mean_clamp), float(min_std), self._stream(stream)))
+
+    def state(self):
+        m, v, c = np.zeros(self.width), np.zeros(self.width), C.c_int64()
+        _check(lib().ggl_obsstat_get(self.h, m.ctypes.data, v.ctypes.data, C.byref(c)))
+        return m, v, c.value
+
+    def set_state(self, means, variances, count):
+        m, v = np.ascontiguousarray(means, np.float64), np.ascontiguousarray(variances, np.float64)
+        _check(lib().ggl_obsstat_set(self.h, m.ctypes.data, v.ctypes.data, int(count)))
+
+    def close(self):
+        if self.h:
+            lib().ggl_obsstat_destroy(self.h)
             self.h = None

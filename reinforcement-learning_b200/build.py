@@ -19,6 +19,7 @@ SOURCES = {
     "envset.cu": ["-fmad=false"],
     "expbuf.cu": [],
     "traj.cu": [],
+    "obsstat.cu": ["-fmad=false"],
 }
 
 

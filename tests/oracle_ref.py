@@ -223,3 +223,46 @@ class RefExpBuf:
         sizes = sizes[:nb]
         used = int(sizes.sum())
         return sizes, {k: v[:used] for k, v in out.items()}
+
+
+# ---- the reference BatchedWelfordStat (oracle/_ref/libref_welford.so)
+_welford = None
+
+
+def welford_available():
+    return os.path.exists(os.path.join(_REF_DIR, "libref_welford.so"))
+
+
+class RefWelford:
+    """GGL::BatchedWelfordStat, unmodified (WelfordStat.h:69-243)."""
+
+    def __init__(self, width):
+        global _welford
+        if _welford is None:
+            _welford = C.CDLL(os.path.join(_REF_DIR, "libref_welford.so"))
+            _welford.ref_welford_create.restype = C.c_void_p
+            _welford.ref_welford_create.argtypes = [C.c_int]
+            _welford.ref_welford_destroy.argtypes = [C.c_void_p]
+            _welford.ref_welford_increment_rows.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int]
+            _welford.ref_welford_normalize.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_double, C.c_double]
+            _welford.ref_welford_state.restype = C.c_int64
+            _welford.ref_welford_state.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        self.width = width
+        self.h = C.c_void_p(_welford.ref_welford_create(width))
+
+    def increment_rows(self, obs, idx):
+        idx = np.ascontiguousarray(idx, np.int32)
+        _welford.ref_welford_increment_rows(self.h, obs.ctypes.data, self.width, idx.ctypes.data, len(idx))
+
+    def normalize_in_place(self, obs, mean_clamp, min_std):
+        _welford.ref_welford_normalize(self.h, obs.ctypes.data, obs.shape[0], self.width, mean_clamp, min_std)
+
+    def state(self):
+        m, v = np.zeros(self.width), np.zeros(self.width)
+        c = _welford.ref_welford_state(self.h, m.ctypes.data, v.ctypes.data)
+        return m, v, int(c)
+
+    def close(self):
+        if self.h:
+            _welford.ref_welford_destroy(self.h)
+            self.h = None
