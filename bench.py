@@ -567,6 +567,91 @@ def bench_traj(args, rank, world, local):
     store.close()
     return line
 
+
+# ------------------------------------------------------------------------------------------------ obs-statistics workload
+def bench_obsstat(args, rank, world, local):
+    """Obs statistics + in-place normalisation at config C2's shape: 16 384 rows x 167, 100 sampled rows per step
+    (Learner defaults). Bytes = 8 per obs element (read + write) + the sampled rows."""
+    import numpy as np
+    import torch
+    ggl = importlib.import_module(PKG)
+    dev = torch.device("cuda", local)
+    rows, width, ns = ARENAS_PER_GPU * 2 * PLAYERS_PER_TEAM, OBS_SIZE_ADV_2V2, 100
+    g = torch.Generator(device=dev); g.manual_seed(5 + rank)
+    src = torch.randn(rows, width, device=dev, generator=g) * 3 + 1
+    obs = src.clone()
+    idx = torch.randint(0, rows, (ns,), device=dev, generator=g, dtype=torch.int32)
+    stat = ggl.ObsStat(width, device=local)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    s = torch.cuda.current_stream(dev)
+
+    def one():
+        stat.increment_rows(obs, idx)
+        stat.normalize_in_place(obs, 3.0, 0.1)
+
+    for _ in range(args.warmup):
+        obs.copy_(src); one()
+    gr = torch.cuda.CUDAGraph()
+    side = torch.cuda.Stream(dev); side.wait_stream(s)
+    with torch.cuda.stream(side):
+        with torch.cuda.graph(gr, stream=side):
+            one()
+    s.wait_stream(side); torch.cuda.synchronize()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = ggl.launch_count()
+    barrier_sync(world)
+    total_ms = 0.0
+    for i in range(args.steps):
+        obs.copy_(src); flush.zero_()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(s); gr.replay(); e1.record(s)
+        torch.cuda.synchronize()
+        total_ms += e0.elapsed_time(e1)
+    barrier_sync(world)
+    launches = 2 * args.steps + (ggl.launch_count() - l0)
+    clocks = sampler.stop() if rank == 0 else None
+    ms = max_over_ranks(total_ms / args.steps, world)
+    bytes_step = 8 * rows * width + 4 * ns * width
+    gbs = bytes_step / (ms * 1e-3) / 1e9
+    peak, psrc = peaks()
+    h_obs = src.cpu().pin_memory(); h_out = torch.empty_like(h_obs).pin_memory(); h_idx = idx.cpu().pin_memory()
+    torch.cuda.synchronize()
+    n_e2e = max(5, args.steps)
+    t0 = time.perf_counter()
+    for i in range(n_e2e):
+        obs.copy_(h_obs, non_blocking=True); idx.copy_(h_idx, non_blocking=True)
+        one()
+        h_out.copy_(obs, non_blocking=True)
+        torch.cuda.synchronize()
+    e2e_s = max_over_ranks((time.perf_counter() - t0) / n_e2e, world)
+    line = {"metric": "obs normalisation GB/s", "value": gbs * world, "unit": "GB/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64 statistics / f32 obs", "data": "synthetic",
+            "config": {"workload": "BatchedWelfordStat: 100 sampled rows + NormalizeInPlace over %d x %d obs" % (rows, width),
+                       "l2": "256 MB flush before every timed step", "launch": "CUDA graph replay of the step's two launches"},
+            "e2e": {"value": bytes_step * world / e2e_s / 1e9, "unit": "GB/s", "h2d_bytes_per_step": 4 * rows * width + 4 * ns,
+                    "d2h_bytes_per_step": 4 * rows * width, "api": "H2D obs + ggl_obsstat_increment_rows + ggl_obsstat_normalize + D2H obs"},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak, "traffic": None,
+                         "kernel": "obsstat_increment_kernel + obsstat_apply_kernel", "peak_source": psrc,
+                         "algorithmic_bytes_per_launch": bytes_step}}
+    if rank == 0:
+        line["clocks"] = clocks
+        if world == 1:
+            import welford_oracle as wo
+            st = wo.BatchedWelfordStat(width)
+            ho, hi = src.cpu().numpy(), idx.cpu().numpy()
+            t0 = time.perf_counter()
+            reps = 10
+            for _ in range(reps):
+                o = ho.copy(); st.increment_rows(o, hi); st.normalize_in_place(o, 3.0, 0.1)
+            dt = (time.perf_counter() - t0) / reps
+            line["cpu_baseline"] = {"value": bytes_step / dt / 1e9, "unit": "GB/s", "cores": 1, "kind": "port",
+                                    "sample": "10 steps of the same shape, numpy restatement of WelfordStat.h:89-216 (bit-exact against the compiled reference)"}
+    stat.close()
+    return line
+
 # ------------------------------------------------------------------------------------------------ reference arm
 def bench_reference(args):
     """Times the reference's own CPU EnvSet on this box's host cores (oracle/_ref). Rank 0 only."""
@@ -615,7 +700,7 @@ def main():
     ap.add_argument("--steps", type=int, default=None)
     ap.add_argument("--warmup", type=int, default=None)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default=None, choices=["env", "gae", "expbuf", "traj"])
+    ap.add_argument("--workload", default=None, choices=["env", "gae", "expbuf", "traj", "obsstat"])
     args = ap.parse_args()
     if args.impl == "reference":
         args.steps = args.steps if args.steps is not None else 30
@@ -633,7 +718,7 @@ def main():
         args.warmup = 20 if workload == "env" else 5
     args.warmup = max(args.warmup, 3)
     rank, world, local = dist_setup(args.gpus)
-    line = {"env": bench_env, "gae": bench_gae, "expbuf": bench_expbuf, "traj": bench_traj}[workload](args, rank, world, local)
+    line = {"env": bench_env, "gae": bench_gae, "expbuf": bench_expbuf, "traj": bench_traj, "obsstat": bench_obsstat}[workload](args, rank, world, local)
     if rank == 0:
         _emit(line)
     if world > 1:

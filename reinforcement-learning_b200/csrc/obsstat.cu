@@ -17,48 +17,61 @@ namespace {
 struct StatDev {
     int width;
     double* means; double* vars; long long* count;
-    float* inv; float* neg;             // coefficients of the last normalise call
 };
 
 // WelfordStat.h:89-97 for every sampled row, in order
 __global__ void obsstat_increment_kernel(StatDev S, const float* __restrict__ obs, const int32_t* __restrict__ idx, int n) {
-    const int j = blockIdx.x * blockDim.x + threadIdx.x;
     const long long count0 = *S.count;
-    if (j < S.width) {
+    __syncthreads();                                       // everyone has read the count before thread 0 moves it
+    if (threadIdx.x == 0) *S.count = count0 + n;           // count++ per row (:96)
+    // row offsets once into shared memory (one round trip instead of one per sample)
+    extern __shared__ long long rowOff[];
+    for (int k = threadIdx.x; k < n; k += blockDim.x) rowOff[k] = (long long)__ldg(idx + k) * S.width;
+    __syncthreads();
+    for (int j = threadIdx.x; j < S.width; j += blockDim.x) {
         double mean = S.means[j], var = S.vars[j];
-        for (int k = 0; k < n; k++) {
-            const long long count = count0 + k;
-            const double sample = (double)obs[(long long)idx[k] * S.width + j];
-            const double delta = sample - mean;
-            const double deltaN = delta / (double)(count + 1);
-            mean += deltaN;
-            var += delta * deltaN * (double)count;
+        // the samples of 16 rows are fetched together and one chunk ahead (independent loads), then folded in one after the
+        // other: the update chain is serial by definition, the HBM round trips need not be
+        float x[16], xn[16];
+#pragma unroll
+        for (int u = 0; u < 16; u++) x[u] = (u < n) ? __ldg(obs + rowOff[u] + j) : 0.f;
+        for (int k0 = 0; k0 < n; k0 += 16) {
+#pragma unroll
+            for (int u = 0; u < 16; u++) xn[u] = (k0 + 16 + u < n) ? __ldg(obs + rowOff[k0 + 16 + u] + j) : 0.f;
+#pragma unroll
+            for (int u = 0; u < 16; u++) {
+                if (k0 + u < n) {
+                    const long long count = count0 + k0 + u;
+                    const double delta = (double)x[u] - mean;
+                    const double deltaN = delta / (double)(count + 1);
+                    mean += deltaN;
+                    var += delta * deltaN * (double)count;
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < 16; u++) x[u] = xn[u];
         }
         S.means[j] = mean; S.vars[j] = var;
     }
 }
-__global__ void obsstat_bump_count_kernel(StatDev S, int n) { *S.count += n; }
 
-// WelfordStat.h:107-127 (GetSTD) and :135-160 (clamps and float coefficients)
-__global__ void obsstat_coeff_kernel(StatDev S, double meanClamp, double minSTD) {
-    const int j = blockIdx.x * blockDim.x + threadIdx.x;
-    const long long count = *S.count;
-    if (j >= S.width || count < 2) return;
+// WelfordStat.h:107-127 (GetSTD) and :135-160 (clamps and float coefficients) for column j
+__device__ __forceinline__ void obsstat_coeff(const StatDev& S, int j, long long count, double meanClamp, double minSTD, float& inv, float& neg) {
     const double var = S.vars[j] / (double)(count - 1);
     const double sd = (var > 0) ? sqrt(var) : 1.0;
     const double m = S.means[j];
     const double cm = m < -meanClamp ? -meanClamp : (m > meanClamp ? meanClamp : m);       // RS_CLAMP
     const double cs = sd > minSTD ? sd : minSTD;                                           // RS_MAX
-    const float inv = 1.0f / (float)cs;
-    S.inv[j] = inv;
-    S.neg[j] = -(float)cm * inv;
+    inv = 1.0f / (float)cs;
+    neg = -(float)cm * inv;
 }
 
 // :163-216 — every element once; 16 bytes per thread
-__global__ void __launch_bounds__(256) obsstat_apply_kernel(StatDev S, float* __restrict__ obs, long long total) {
-    extern __shared__ float coef[];                      // inv[width], neg[width]
-    if (*S.count < 2) return;                            // :133 — not enough data: the obs stay as they are, bit for bit
-    for (int j = threadIdx.x; j < S.width; j += blockDim.x) { coef[j] = S.inv[j]; coef[S.width + j] = S.neg[j]; }
+__global__ void __launch_bounds__(256) obsstat_apply_kernel(StatDev S, float* __restrict__ obs, long long total, double meanClamp, double minSTD) {
+    extern __shared__ float coef[];                      // inv[width], neg[width]: every block derives them itself (a few hundred sqrt)
+    const long long count = *S.count;
+    if (count < 2) return;                               // :133 — not enough data: the obs stay as they are, bit for bit
+    for (int j = threadIdx.x; j < S.width; j += blockDim.x) obsstat_coeff(S, j, count, meanClamp, minSTD, coef[j], coef[S.width + j]);
     __syncthreads();
     const float* inv = coef; const float* neg = coef + S.width;
     const long long nvec = total >> 2;
@@ -103,8 +116,6 @@ extern "C" int ggl_obsstat_create(int device, int width, ggl_obsstat** out) {
     s->S.means = static_cast<double*>(blob);
     s->S.vars = s->S.means + width;
     s->S.count = reinterpret_cast<long long*>(s->S.vars + width);
-    s->S.inv = reinterpret_cast<float*>(s->S.count + 1);
-    s->S.neg = s->S.inv + width;
     GGL_CUDA(cudaDeviceSynchronize());
     *out = s;
     return GGL_OK;
@@ -125,10 +136,11 @@ extern "C" int ggl_obsstat_increment_rows(ggl_obsstat* s, const float* d_obs, co
     STAT_CHECK(s);
     if (n < 0 || (n > 0 && (!d_obs || !d_row_indices))) { ggl::set_error("ggl_obsstat_increment_rows: bad argument"); return GGL_ERR_INVALID; }
     if (n == 0) return GGL_OK;
-    obsstat_increment_kernel<<<(s->S.width + 63) / 64, 64, 0, (cudaStream_t)stream>>>(s->S, d_obs, d_row_indices, n);
-    GGL_LAUNCH_CHECK();
-    obsstat_bump_count_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(s->S, n);
-    GGL_LAUNCH_CHECK(); ggl::count_launch(2);
+    const int threads = s->S.width >= 1024 ? 1024 : ((s->S.width + 31) / 32) * 32;
+    if ((size_t)n * sizeof(long long) > 200 * 1024) { ggl::set_error("ggl_obsstat_increment_rows: at most 25600 rows per call"); return GGL_ERR_INVALID; }
+    if ((size_t)n * sizeof(long long) > 48 * 1024) GGL_CUDA(cudaFuncSetAttribute(obsstat_increment_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    obsstat_increment_kernel<<<1, threads, (size_t)n * sizeof(long long), (cudaStream_t)stream>>>(s->S, d_obs, d_row_indices, n);
+    GGL_LAUNCH_CHECK(); ggl::count_launch();
     return GGL_OK;
 }
 
@@ -137,13 +149,11 @@ extern "C" int ggl_obsstat_normalize(ggl_obsstat* s, float* d_obs, int64_t num_r
     if (num_rows <= 0) return GGL_OK;                                                     // :133
     if (!d_obs || ((uintptr_t)d_obs & 15)) { ggl::set_error("ggl_obsstat_normalize: obs must be a 16-byte aligned device pointer"); return GGL_ERR_INVALID; }
     const long long total = (long long)num_rows * s->S.width;
-    obsstat_coeff_kernel<<<(s->S.width + 63) / 64, 64, 0, (cudaStream_t)stream>>>(s->S, mean_clamp, min_std);
-    GGL_LAUNCH_CHECK();
     long long blocks = ((total >> 2) + 255) / 256;
     if (blocks > (long long)s->sms * 8) blocks = (long long)s->sms * 8;
     if (blocks < 1) blocks = 1;
-    obsstat_apply_kernel<<<(int)blocks, 256, sizeof(float) * 2 * s->S.width, (cudaStream_t)stream>>>(s->S, d_obs, total);
-    GGL_LAUNCH_CHECK(); ggl::count_launch(2);
+    obsstat_apply_kernel<<<(int)blocks, 256, sizeof(float) * 2 * s->S.width, (cudaStream_t)stream>>>(s->S, d_obs, total, mean_clamp, min_std);
+    GGL_LAUNCH_CHECK(); ggl::count_launch();
     return GGL_OK;
 }
 

@@ -5,6 +5,7 @@ python bench.py --steps 200 --warmup 20 > gpurun_out/bench_env.json 2> gpurun_ou
 python bench.py --workload gae > gpurun_out/bench_gae.json 2> gpurun_out/bench_gae.err
 python bench.py --workload expbuf > gpurun_out/bench_expbuf.json 2> gpurun_out/bench_expbuf.err
 python bench.py --workload traj > gpurun_out/bench_traj.json 2> gpurun_out/bench_traj.err
+python bench.py --workload obsstat > gpurun_out/bench_obsstat.json 2> gpurun_out/bench_obsstat.err
 python bench.py --impl reference --steps 10 --warmup 3 > gpurun_out/bench_ref.json 2>/dev/null
 python -c 'import __graft_entry__ as g; g.smoke()' > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?"
 ncu --metrics gpu__time_duration.sum --clock-control none -c 700 --csv --log-file gpurun_out/launches.csv python bench.py --steps 5 --warmup 3 > gpurun_out/ncu1.log 2>&1
