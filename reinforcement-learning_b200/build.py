@@ -75,8 +75,28 @@ def build(verbose=False, force=False):
     return OUT
 
 
+def build_variant(tag, defines):
+    """Experiment variant: libgigaenv_cuda_<tag>.so with extra -D flags (selected at run time through GGL_LIB_PATH)."""
+    nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+    out = os.path.join(HERE, "libgigaenv_cuda_%s.so" % tag)
+    os.makedirs(OBJ, exist_ok=True)
+    objs, procs = [], []
+    for name, extra in SOURCES.items():
+        obj = os.path.join(OBJ, name.replace(".cu", ".%s.o" % tag))
+        objs.append(obj)
+        procs.append(subprocess.Popen([nvcc] + COMMON + extra + list(defines) + ["-c", os.path.join(CSRC, name), "-o", obj]))
+    for p in procs:
+        if p.wait() != 0:
+            raise RuntimeError("nvcc failed (variant %s)" % tag)
+    subprocess.check_call([nvcc, "-shared", "-o", out] + ARCH + objs + ["-lcudart"])
+    return out
+
+
 if __name__ == "__main__":
-    if "--prof" in sys.argv:
+    if "--variant" in sys.argv:
+        i = sys.argv.index("--variant")
+        print(build_variant(sys.argv[i + 1], sys.argv[i + 2:]))
+    elif "--prof" in sys.argv:
         print(build_prof())
     else:
         print(build(verbose="-v" in sys.argv, force="-f" in sys.argv))

@@ -16,9 +16,12 @@
 
 namespace ggl {
 
-constexpr int kGroup = 8;
+#ifndef GGL_GROUP
+#define GGL_GROUP 8
+#endif
+constexpr int kGroup = GGL_GROUP;                // lanes per arena (8 or 16)
 constexpr int kArenasPerWarp = 32 / kGroup;
-constexpr int kMaxWarps = 7;                     // warps per block of the step kernels (chosen per launch, see launch_geom)
+constexpr int kMaxWarps = 7 * kGroup / 8;        // warps per block of the step kernels (chosen per launch, see launch_geom)
 constexpr int kBlock = 32;                       // the reset kernel: one warp per block
 constexpr int kArenasPerBlock = kBlock / kGroup;
 

@@ -494,3 +494,41 @@ extern "C" size_t ggl_abi_sizeof(int which) {
     default: return 0;
     }
 }
+
+// Workload census of the last raw tick (debug; call after ggl_arena_step(e, 1, ...), which writes the per-tick scratch back):
+// out[8][40] histograms over arenas: 0 solver rows, 1 rows of the largest island, 2 (car, triangle) candidates, 3 islands
+// with rows, 4 wheels in contact, 5 cars with world / car-car rows, 6 mesh hits, 7 largest per-car row window
+namespace {
+__global__ void tick_stats_kernel(const ArenaDev* arenas, int numArenas, unsigned* out) {
+    const int a = blockIdx.x * blockDim.x + threadIdx.x;
+    if (a >= numArenas) return;
+    const ArenaDev& A = arenas[a];
+    auto bump = [&](int h, int v) { atomicAdd(out + h * 40 + (v < 0 ? 0 : v > 39 ? 39 : v), 1u); };
+    bump(0, A.numContacts);
+    int rowsOf[8] = {}, nIsl = 0, maxRows = 0;
+    for (int k = 0; k < A.numContacts; k++) rowsOf[A.island[A.contacts[k].bodyA]]++;
+    for (int b = 0; b < 8; b++) { if (rowsOf[b]) nIsl++; if (rowsOf[b] > maxRows) maxRows = rowsOf[b]; }
+    bump(1, maxRows); bump(3, nIsl);
+    int cand = 0, wheels = 0, carsRest = 0, hits = 0, maxWin = 0;
+    for (int c = 0; c < A.numCars; c++) {
+        cand += A.meshCandN[c]; hits += (int)A.meshHitN[c];
+        for (int w = 0; w < 4; w++) wheels += A.cars[c].w[w].ground != GROUND_NONE;
+        carsRest += A.cntRest[c] != 0;
+        if (A.cntRest[c] > maxWin) maxWin = A.cntRest[c];
+    }
+    bump(2, cand); bump(4, wheels); bump(5, carsRest); bump(6, hits); bump(7, maxWin);
+}
+}  // namespace
+extern "C" int ggl_debug_tick_stats(ggl_envset* e, uint32_t* out320) {
+    ENV_CHECK(e);
+    if (!out320) return GGL_ERR_INVALID;
+    GGL_CUDA(cudaSetDevice(e->device));
+    unsigned* d = nullptr;
+    GGL_CUDA(cudaMalloc(&d, 320 * sizeof(unsigned)));
+    GGL_CUDA(cudaMemset(d, 0, 320 * sizeof(unsigned)));
+    tick_stats_kernel<<<(e->cfg.numArenas + 127) / 128, 128>>>(e->P.arenas, e->cfg.numArenas, d);
+    cudaError_t err = cudaMemcpy(out320, d, 320 * sizeof(unsigned), cudaMemcpyDeviceToHost);
+    cudaFree(d);
+    if (err != cudaSuccess) { ggl::set_error("tick_stats -> %s", cudaGetErrorString(err)); return GGL_ERR_CUDA; }
+    return GGL_OK;
+}
