@@ -209,6 +209,9 @@ int  ggl_envset_step_second_half(ggl_envset* env, const int32_t* d_actions, void
  * the action indices already on the device). */
 int  ggl_envset_step(ggl_envset* env, const int32_t* d_actions, void* stream);
 int  ggl_envset_reset(ggl_envset* env, void* stream);
+/* EnvSet::ResetArena(index) called directly (EnvSet.h:108, EnvSet.cpp:275-331): resets `arena` whatever its terminal flag
+ * (state setter, tracker and plugin resets, obs + mask rows rebuilt, terminal cleared); arena = -1 resets every arena. */
+int  ggl_envset_reset_arena(ggl_envset* env, int arena, void* stream);
 int  ggl_envset_sync(ggl_envset* env);
 int  ggl_envset_views_get(ggl_envset* env, ggl_envset_views* out);
 int  ggl_envset_set_state(ggl_envset* env, int arena, const ggl_arena_state* host_state);
@@ -216,6 +219,10 @@ int  ggl_envset_get_state(ggl_envset* env, int arena, ggl_arena_state* host_stat
 /* test / debug: ordered solver contact rows of `arena`'s last tick, out[max][20] floats per row (bodyA, bodyB, normal xyz,
  * relA xyz, relB xyz, distance, friction, restitution, special); returns the row count (>= 0) or a negative ggl_status */
 int  ggl_envset_get_contacts(ggl_envset* env, int arena, float* out, int max);
+/* Contact points dropped since create because an arena's contact rows were exhausted (per-body windows + shared overflow pool,
+ * 36 rows per arena and tick), summed over the arenas. The reference has no such limit (btPersistentManifold pool); a non-zero
+ * value means some arena's solver saw fewer rows than the reference's would. Synchronises the device. */
+int  ggl_envset_contact_overflow(ggl_envset* env, uint64_t* out_dropped);
 /* players[] slot order of every arena: car_ids[num_players], car_ids[arena*P + slot] = carId (1-based AddCar order)
  * occupying GameState.players[slot] (GameState.cpp:82-86). Takes effect at the next reset/step. */
 int  ggl_envset_set_slot_order(ggl_envset* env, const int32_t* h_car_ids);

@@ -477,6 +477,64 @@ int ref_arena_contacts(void* p, int arena, float* out, int max) {
     return n;
 }
 
+// wheels of car `carId` after the last tick: out[4][12] = contact normal xyz, contact point xyz, suspension length,
+// ground kind (-1 none, 0 static world, 1 ball, 2 + carId-1 car), impulse xyz, suspension relative velocity
+void ref_arena_wheel_info(void* p, int arena, int carId, float* out) {
+    Arena* a = ((RefEnv*)p)->envSet->arenas[arena];
+    Car* car = CarById(a, carId);
+    for (int i = 0; i < 4; i++) {
+        auto& w = car->_bulletVehicle.m_wheelInfo[i];
+        float* o = out + 12 * i;
+        o[0] = w.m_raycastInfo.m_contactNormalWS.x(); o[1] = w.m_raycastInfo.m_contactNormalWS.y(); o[2] = w.m_raycastInfo.m_contactNormalWS.z();
+        o[3] = w.m_raycastInfo.m_contactPointWS.x(); o[4] = w.m_raycastInfo.m_contactPointWS.y(); o[5] = w.m_raycastInfo.m_contactPointWS.z();
+        o[6] = w.m_raycastInfo.m_suspensionLength;
+        float kind = -1;
+        const btCollisionObject* g = (const btCollisionObject*)w.m_raycastInfo.m_groundObject;
+        if (g) {
+            if (g == &a->ball->_rigidBody) kind = 1;
+            else if (g->isStaticObject()) kind = 0;
+            else for (Car* c : a->_cars) if (g == &c->_rigidBody) kind = 2 + (float)(c->id - 1);
+        }
+        o[7] = kind;
+        o[8] = w.m_impulse.x(); o[9] = w.m_impulse.y(); o[10] = w.m_impulse.z(); o[11] = w.m_suspensionRelativeVelocity;
+    }
+}
+
+// The convex ray cast a suspension ray runs against a car's hitbox child (kind 0) or the ball's sphere (kind 1), with the
+// reference's own shapes: btCollisionWorld::rayTestSingle on a temporary transform (pos, row-major basis). out = fraction,
+// normal xyz (as ClosestRayResultCallback stores it); returns 1 on a hit.
+int ref_convex_ray_cast(void* p, int kind, const float* from, const float* to, const float* pos, const float* basis, float* out) {
+    Arena* a = ((RefEnv*)p)->envSet->arenas[0];
+    Car* car = *a->_cars.begin();
+    btTransform tf;
+    tf.setOrigin(btVector3(pos[0], pos[1], pos[2]));
+    tf.setBasis(btMatrix3x3(basis[0], basis[1], basis[2], basis[3], basis[4], basis[5], basis[6], basis[7], basis[8]));
+    btTransform rf, rt; rf.setIdentity(); rt.setIdentity();
+    btVector3 f(from[0], from[1], from[2]), t(to[0], to[1], to[2]);
+    rf.setOrigin(f); rt.setOrigin(t);
+    btCollisionWorld::ClosestRayResultCallback cb(f, t, nullptr);
+    btCollisionObject* obj = kind == 0 ? (btCollisionObject*)&car->_rigidBody : (btCollisionObject*)&a->ball->_rigidBody;
+    btCollisionShape* shape = kind == 0 ? (btCollisionShape*)&car->_compoundShape : (btCollisionShape*)a->ball->_collisionShape;
+    btCollisionWorld::rayTestSingle(rf, rt, obj, shape, tf, cb);
+    if (!cb.hasHit()) return 0;
+    out[0] = cb.m_closestHitFraction; out[1] = cb.m_hitNormalWorld.x(); out[2] = cb.m_hitNormalWorld.y(); out[3] = cb.m_hitNormalWorld.z();
+    return 1;
+}
+
+// Triangle indices of mesh `mesh` in the order its quantized BVH stores the leaves (= the order queries report them).
+// Returns the triangle count; out may be NULL.
+int ref_mesh_leaf_order(int mesh, int* out, int max) {
+    auto shapes = RocketSim::GetArenaCollisionShapes(GameMode::SOCCAR);
+    if (mesh < 0 || mesh >= (int)shapes.size()) return -1;
+    btOptimizedBvh* bvh = shapes[mesh]->getOptimizedBvh();
+    const QuantizedNodeArray& nodes = bvh->getQuantizedNodeArray();
+    // the array is sized 2 n; a tree of n leaves uses the first 2 n - 1 entries
+    int n = 0;
+    for (int i = 0; i < nodes.size() - 1; i++)
+        if (nodes[i].isLeafNode()) { if (out && n < max) out[n] = nodes[i].getTriangleIndex(); n++; }
+    return n;
+}
+
 // out[0..2] car invInertiaDiagLocal, [3] car invMass, [4..6] ball invInertiaDiagLocal, [7] ball invMass, [8] ball shape radius,
 // [9] ball shape margin, [10] car compound contact-breaking threshold, [11] ball contact-breaking threshold,
 // [12] box margin, [13..15] box half extents with margin, [16] solver erp2, [17] solver erp, [18] linearSlop, [19] restitution vel threshold

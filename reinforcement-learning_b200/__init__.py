@@ -64,6 +64,8 @@ def lib():
             L.ggl_envset_step_second_half.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
             L.ggl_envset_step.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
             L.ggl_envset_reset.argtypes = [C.c_void_p, C.c_void_p]
+            L.ggl_envset_reset_arena.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+            L.ggl_envset_contact_overflow.argtypes = [C.c_void_p, C.POINTER(C.c_uint64)]
             L.ggl_envset_sync.argtypes = [C.c_void_p]
             L.ggl_envset_views_get.argtypes = [C.c_void_p, C.POINTER(abi.EnvSetViews)]
             L.ggl_envset_set_state.argtypes = [C.c_void_p, C.c_int, C.POINTER(abi.ArenaState)]
@@ -238,6 +240,16 @@ class EnvSet:
 
     def reset(self, stream=None):
         _check(lib().ggl_envset_reset(self.h, self._stream(stream)))
+
+    def contact_overflow(self):
+        """contact points dropped since create because an arena ran out of contact rows (0 = none)"""
+        n = C.c_uint64()
+        _check(lib().ggl_envset_contact_overflow(self.h, C.byref(n)))
+        return int(n.value)
+
+    def reset_arena(self, arena=-1, stream=None):
+        """EnvSet::ResetArena(arena) whatever the terminal flag; -1 = every arena."""
+        _check(lib().ggl_envset_reset_arena(self.h, int(arena), self._stream(stream)))
 
     def step_first_half(self, stream=None):
         _check(lib().ggl_envset_step_first_half(self.h, self._stream(stream)))

@@ -95,13 +95,14 @@ __device__ __forceinline__ ArenaDev& my_arena(int slotBytes) {
     return *reinterpret_cast<ArenaDev*>(g_arena_smem + (size_t)(threadIdx.x / kGroup) * slotBytes);
 }
 
-// EnvSet::ResetArena for arenas whose terminal flag is set (or all of them when `force`)
+// EnvSet::ResetArena for arenas whose terminal flag is set; `force` = 1 resets every arena (EnvSet ctor), `force` = 2 + i
+// resets arena i whatever its terminal flag (EnvSet::ResetArena(i), EnvSet.cpp:275-331, called directly)
 __global__ void __launch_bounds__(kBlock) env_reset_kernel(EnvCfg cfg, EnvDevPtrs P, int force) {
     const int arena = blockIdx.x * kArenasPerBlock + threadIdx.x / kGroup;
     if (arena >= cfg.numArenas) return;
     const ExecGroup ex = make_exec();
     ArenaDev& A = P.arenas[arena];
-    const bool doReset = force || A.terminal != 0;
+    const bool doReset = force == 1 || (force >= 2 && arena == force - 2) || (force == 0 && A.terminal != 0);
     if (!doReset) return;
     if (ex.lane() == 0) {
         if (cfg.stateSetter == GGL_SETTER_INJECTED && P.resetArenas && P.resetArenas[arena].hasResetState) {

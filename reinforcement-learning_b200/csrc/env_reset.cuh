@@ -84,6 +84,7 @@ GGL_HD void car_set_spawn(CarDev& c, V3 posUU, float yaw) {
     c.pos = posUU * kUU2BT;
     c.basis = m3_from_euler_ypr(yaw, -0.f, -0.f);
     car_update_inertia(c);
+    c.aabbMin = c.aabbMax = v3(0, 0, 0);
 }
 
 // Arena::ResetToRandomKickoff (Arena.cpp:112-216). The permutation comes from the arena's own minstd stream

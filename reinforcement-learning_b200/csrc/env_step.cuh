@@ -17,7 +17,8 @@ GGL_HD PlayerView player_view(const ArenaDev& A, int ci) {
     const CarDev& c = A.cars[ci];
     PlayerView p;
     p.pos = c.pos * kBT2UU; p.vel = c.vel * kBT2UU; p.angVel = c.angVel;
-    p.fwd = col(c.basis, 0); p.right = col(c.basis, 1); p.up = col(c.basis, 2);
+    const M3 rb = car_reported_basis(c);
+    p.fwd = col(rb, 0); p.right = col(rb, 1); p.up = col(rb, 2);
     p.boost = c.boost; p.team = c.team; p.carId = (int)c.id;
     p.onGround = c.isOnGround; p.hasFlipOrJump = car_has_flip_or_jump(c); p.demoed = c.isDemoed; p.hasJumped = c.hasJumped;
     p.touchedStep = c.hitValid && c.hitTick >= A.gsLastTickCount;

@@ -216,6 +216,13 @@ extern "C" int ggl_envset_reset(ggl_envset* e, void* stream) {
     GGL_LAUNCH_CHECK(); ggl::count_launch();
     return GGL_OK;
 }
+extern "C" int ggl_envset_reset_arena(ggl_envset* e, int arena, void* stream) {
+    ENV_CHECK(e);
+    if (arena < -1 || arena >= e->cfg.numArenas) { ggl::set_error("reset_arena: arena %d out of range", arena); return GGL_ERR_INVALID; }
+    env_reset_kernel<<<grid_for(e->cfg), kBlock, 0, (cudaStream_t)stream>>>(e->cfg, e->P, arena < 0 ? 1 : 2 + arena);
+    GGL_LAUNCH_CHECK(); ggl::count_launch();
+    return GGL_OK;
+}
 extern "C" int ggl_envset_step_first_half(ggl_envset* e, void* stream) {
     ENV_CHECK(e);
     env_step_kernel<<<e->geom.grid, 32 * e->geom.warps, e->geom.smem, (cudaStream_t)stream>>>(e->cfg, e->P, nullptr, 1, 0, slot_bytes(e->cfg));
@@ -306,7 +313,7 @@ extern "C" int ggl_envset_get_contacts(ggl_envset* e, int arena, float* out, int
     int n = 0;
     if (err == cudaSuccess)
         for (int k = 0; k < A->numContacts && n < max; k++) {
-            const Contact& c = A->contacts[k];
+            const Contact& c = A->contacts[A->contactOrder[k]];
             float* o = out + 20 * n++;
             memset(o, 0, 80);
             o[0] = c.bodyA; o[1] = c.bodyB; o[2] = c.normal.x; o[3] = c.normal.y; o[4] = c.normal.z;
@@ -506,7 +513,7 @@ __global__ void tick_stats_kernel(const ArenaDev* arenas, int numArenas, unsigne
     auto bump = [&](int h, int v) { atomicAdd(out + h * 40 + (v < 0 ? 0 : v > 39 ? 39 : v), 1u); };
     bump(0, A.numContacts);
     int rowsOf[8] = {}, nIsl = 0, maxRows = 0;
-    for (int k = 0; k < A.numContacts; k++) rowsOf[A.island[A.contacts[k].bodyA]]++;
+    for (int k = 0; k < A.numContacts; k++) rowsOf[A.island[A.contacts[A.contactOrder[k]].bodyA]]++;
     for (int b = 0; b < 8; b++) { if (rowsOf[b]) nIsl++; if (rowsOf[b] > maxRows) maxRows = rowsOf[b]; }
     bump(1, maxRows); bump(3, nIsl);
     int cand = 0, wheels = 0, carsRest = 0, hits = 0, maxWin = 0;
@@ -519,6 +526,32 @@ __global__ void tick_stats_kernel(const ArenaDev* arenas, int numArenas, unsigne
     bump(2, cand); bump(4, wheels); bump(5, carsRest); bump(6, hits); bump(7, maxWin);
 }
 }  // namespace
+// Contact points dropped since create because an arena's windows and overflow pool were full (ArenaDev::contactOverflow,
+// sticky), summed over the arenas. 0 = every contact the narrow phase found reached the solver.
+namespace {
+__global__ void overflow_sum_kernel(const ArenaDev* arenas, int numArenas, unsigned long long* out) {
+    const int a = blockIdx.x * blockDim.x + threadIdx.x;
+    if (a < numArenas && arenas[a].contactOverflow) atomicAdd(out, (unsigned long long)arenas[a].contactOverflow);
+}
+}  // namespace
+extern "C" int ggl_envset_contact_overflow(ggl_envset* e, uint64_t* out) {
+    ENV_CHECK(e);
+    if (!out) { ggl::set_error("contact_overflow: null output"); return GGL_ERR_INVALID; }
+    unsigned long long* d = nullptr;
+    GGL_CUDA(cudaSetDevice(e->device));
+    GGL_CUDA(cudaDeviceSynchronize());
+    GGL_CUDA(cudaMalloc(&d, sizeof(*d)));
+    GGL_CUDA(cudaMemset(d, 0, sizeof(*d)));
+    overflow_sum_kernel<<<(e->cfg.numArenas + 255) / 256, 256>>>(e->P.arenas, e->cfg.numArenas, d);
+    ggl::count_launch();
+    unsigned long long h = 0;
+    cudaError_t err = cudaMemcpy(&h, d, sizeof(h), cudaMemcpyDeviceToHost);
+    cudaFree(d);
+    if (err != cudaSuccess) { ggl::set_error("contact_overflow -> %s", cudaGetErrorString(err)); return GGL_ERR_CUDA; }
+    *out = (uint64_t)h;
+    return GGL_OK;
+}
+
 extern "C" int ggl_debug_tick_stats(ggl_envset* e, uint32_t* out320) {
     ENV_CHECK(e);
     if (!out320) return GGL_ERR_INVALID;

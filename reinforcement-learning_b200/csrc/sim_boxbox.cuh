@@ -269,6 +269,7 @@ GGL_HD void car_car_callback(ArenaDev& A, int i1, int i2, V3 localA, V3 localB) 
                 if (lp.x * kBT2UU > rl::BUMP_MIN_FORWARD_DIST) {
                     bool isDemo = c1.isSupersonic && (c1.team != c2.team);
                     if (isDemo) {
+                        if (!c2.isDemoed) car_freeze_reported_basis(c2);
                         c2.isDemoed = 1; c2.demoRespawnTimer = rl::DEMO_RESPAWN_TIME;
                     } else {
                         bool groundHit = c2.isOnGround;

@@ -179,8 +179,8 @@ GGL_HD void car_tri_emit(ArenaDev& A, ContactSink& S, ManifoldCtx& m, int ci, co
     car.worldContactNormal = o.normalOnB;
     V3 n = o.normalOnB, pB = o.pointOnB;
     adjust_internal_edge(t, n, pB, pA, o.distance);
-    S.buf[row].normal = n;
-    S.buf[row].relB = pB;
+    S.at(row).normal = n;
+    S.at(row).relB = pB;
 }
 
 GGL_HD V3 car_box_pos(const CarDev& car) { return car.pos + mul(car.basis, car_hitbox_offset()); }

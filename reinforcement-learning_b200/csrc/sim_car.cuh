@@ -15,6 +15,7 @@
 //   libsrc/bullet3-3.24/BulletDynamics/ConstraintSolver/btContactConstraint.cpp:60-150 resolveSingleCollision/Bilateral
 //   libsrc/bullet3-3.24/BulletCollision/NarrowPhaseCollision/btRaycastCallback.cpp:34-110 ray vs triangle
 #pragma once
+#include "sim_gjk.cuh"
 #include "sim_types.cuh"
 
 namespace ggl {
@@ -99,6 +100,44 @@ GGL_HD V3 car_inv_inertia_local() {
 GGL_HD void car_update_inertia(CarDev& c) {
     c.invInertiaW = mul(scaled(c.basis, car_inv_inertia_local()), transpose(c.basis));
 }
+// World AABB of the car's compound shape (btCompoundShape::getAabb over the child box's local AABB, no compound margin)
+GGL_HD void car_world_aabb(V3 pos, const M3& basis, V3& mn, V3& mx) {
+    const V3 he = car_box_full_extents(), off = car_hitbox_offset();
+    const V3 lmin = off - he, lmax = off + he;
+    const V3 lhe = (lmax - lmin) * 0.5f, lc = (lmax + lmin) * 0.5f;
+    const V3 centre = pos + mul(basis, lc);
+    const V3 ext = v3(dot(vabs(basis.r0), lhe), dot(vabs(basis.r1), lhe), dot(vabs(basis.r2), lhe));
+    mn = centre - ext; mx = centre + ext;
+}
+// The broadphase AABB a suspension ray of the NEXT tick is tested against (btSingleRayCallback::process,
+// btCollisionWorld.cpp:913-945): btCollisionWorld::updateSingleAabb (:135-175) runs inside this tick's collision detection, on
+// the transform the tick started with, grown by the contact breaking threshold 0.02 and - continuous collision detection
+// being on - merged with the AABB at the predicted transform (btDiscreteDynamicsWorld::predictUnconstraintMotion). Nobody
+// refreshes it before the next tick's rays. Only kept when another car is close enough to be reached by a ray next tick
+// (6 bt = 300 uu between centres; cars close at most 92 uu per tick); otherwise the box is left empty.
+GGL_HD void car_update_ray_aabb(ArenaDev& A, int ci) {
+    CarDev& c = A.cars[ci];
+    bool near = false;
+    for (int j = 0; j < A.numCars; j++)
+        if (j != ci && len2(A.cars[j].pos - c.pos) < 36.f) near = true;
+    if (!near) { c.aabbMin = v3(1e30f, 1e30f, 1e30f); c.aabbMax = v3(-1e30f, -1e30f, -1e30f); return; }
+    const V3 thr = v3(0.02f, 0.02f, 0.02f);
+    V3 mn, mx, mn2, mx2, np; M3 nb;
+    car_world_aabb(c.pos, c.basis, mn, mx);
+    integrate_transform(c.pos, c.basis, c.vel, c.angVel, kTick, np, nb);
+    car_world_aabb(np, nb, mn2, mx2);
+    c.aabbMin = vmin(mn - thr, mn2 - thr); c.aabbMax = vmax(mx + thr, mx2 + thr);
+}
+// What Car::GetState reports as rotMat: the reference refreshes _internalState.rotMat at the start of _PostTickUpdate and
+// returns early from it while the car is demolished (Car.cpp:133-140), so from the tick of the demolition until the respawn
+// the reported orientation is the one the car had when that tick began, while the rigid body is still solved and moved in
+// that tick. The frozen matrix is parked in wheel 0's per-tick scratch, which nobody touches while isDemoed is set.
+GGL_HD void car_freeze_reported_basis(CarDev& c) { c.w[0].hardPoint = c.basis.r0; c.w[0].contactPoint = c.basis.r1; c.w[0].contactNormal = c.basis.r2; }
+GGL_HD M3 car_reported_basis(const CarDev& c) {
+    if (!c.isDemoed) return c.basis;
+    M3 m; m.r0 = c.w[0].hardPoint; m.r1 = c.w[0].contactPoint; m.r2 = c.w[0].contactNormal;
+    return m;
+}
 GGL_HD V3 car_fwd(const CarDev& c) { return col(c.basis, 0); }
 GGL_HD V3 car_right(const CarDev& c) { return col(c.basis, 1); }
 GGL_HD V3 car_up(const CarDev& c) { return col(c.basis, 2); }
@@ -181,52 +220,132 @@ GGL_HD void ray_vs_tri(V3 from, V3 to, const Tri& tr, RayHit& h) {
     }
 }
 
-GGL_HD void ray_vs_sphere(V3 from, V3 to, V3 center, float radius, int kind, RayHit& h) {
-    V3 d = to - from, m = from - center;
-    float a = dot(d, d), b = dot(m, d), c = dot(m, m) - radius * radius;
-    if (a <= 0.f) return;
-    if (c > 0.f && b > 0.f) return;
-    float disc = b * b - a * c;
-    if (disc < 0.f) return;
-    float t = (-b - sqrtf(disc)) / a;
-    if (t < 0.f) t = 0.f;
-    if (t < h.t) {
-        V3 p = from + d * t;
-        h.t = t;
-        h.normal = safe_normalized(p - center);
+// btSubsimplexConvexCast::calcTimeOfImpact (BT/BulletCollision/NarrowPhaseCollision/btSubSimplexConvexCast.cpp:31-160) for the
+// zero-radius point shape swept from -> to against a resting convex shape B given by its world-space support mapping: what
+// btCollisionWorld::rayTestSingleInternal (btCollisionWorld.cpp:267-312) runs for every convex shape a suspension ray meets
+// (the ball's sphere, the box child of a car's compound). The hit normal is the simplex's closest vector at the last advance
+// of lambda, NOT the geometric face normal, and the simplex is never re-centred when lambda moves, so the iteration is
+// restated step by step (32 iterations, epsilon 1e-4 on the squared distance, btConvexCast.h:28-29).
+template <class SupB>
+GGL_HD bool subsimplex_point_cast(V3 from, V3 to, SupB supB, float& fraction, V3& normal) {
+    Voronoi S;
+    vs_reset(S);
+    const V3 r = to - from;
+    const V3 originB = supB.origin;
+    float lambda = 0.f;
+    V3 ipA = from;
+    V3 supA = from;
+    V3 sB = supB(r);
+    V3 v = supA - sB;
+    int maxIter = 32;
+    V3 n = v3(0, 0, 0);
+    float dist2 = len2(v);
+    while (dist2 > 0.0001f && maxIter--) {
+        supA = ipA;
+        sB = supB(v);
+        V3 w = supA - sB;
+        const float VdotW = dot(v, w);
+        if (lambda > 1.f) return false;
+        if (VdotW > 0.f) {
+            const float VdotR = dot(v, r);
+            if (VdotR >= -(kEps * kEps)) return false;
+            lambda = lambda - VdotW / VdotR;
+            const float s1 = 1.f - lambda;          // btVector3::setInterpolate3, applied to BOTH transforms: B does not
+            ipA = v3(s1 * from.x + lambda * to.x, s1 * from.y + lambda * to.y, s1 * from.z + lambda * to.z);   // move, but
+            supB.origin = v3(s1 * originB.x + lambda * originB.x, s1 * originB.y + lambda * originB.y,         // s*o + l*o
+                             s1 * originB.z + lambda * originB.z);                                             // rounds
+            w = supA - sB;
+            n = v;
+        }
+        if (!vs_in_simplex(S, w)) vs_add(S, w, supA, sB);
+        vs_update(S);
+        v = S.cachedV;
+        dist2 = S.cachedValid ? len2(v) : 0.f;
+    }
+    fraction = lambda;
+    if (len2(n) >= kEps * kEps) normal = normalized(n);
+    else normal = v3(0, 0, 0);
+    if (dot(normal, r) >= -0.f) return false;
+    return true;
+}
+
+struct SupSphere {
+    V3 origin; float radius;
+    GGL_HD V3 operator()(V3 d) const {       // btSphereShape::localGetSupportingVertex (btSphereShape.cpp:36-48); identity basis (the
+        V3 nrm;                              // ball never rotates: btRigidBody m_noRot)
+        if (len2(d) < kEps * kEps) nrm = normalized(v3(-1.f, -1.f, -1.f));
+        else nrm = normalized(d);
+        return radius * nrm + origin;
+    }
+};
+struct SupBox {
+    V3 origin; M3 basis; V3 he;
+    GGL_HD V3 operator()(V3 d) const {       // btBoxShape::localGetSupportingVertex on the child's world transform
+        return mul(basis, box_support(he, tmul(basis, d))) + origin;
+    }
+};
+
+// rayTestSingleInternal's bookkeeping around the cast (btCollisionWorld.cpp:288-311) + ClosestRayResultCallback
+GGL_HD void ray_take_cast_hit(bool hit, float fraction, V3 normal, int kind, RayHit& h) {
+    if (!hit) return;
+    if (!(len2(normal) > 0.0001f)) return;
+    if (fraction < h.t) {
+        h.t = fraction;
+        h.normal = normalized(normal);
         h.ground = kind;
     }
 }
 
+GGL_HD void ray_vs_sphere(V3 from, V3 to, V3 center, float radius, int kind, RayHit& h) {
+    // cull (conservative): the cast stops within 0.01 of the surface, so a segment that stays 0.02 clear of it cannot hit
+    {
+        V3 d = to - from, m = from - center;
+        const float rr = radius + 0.02f;
+        float a = dot(d, d), b = dot(m, d), c = dot(m, m) - rr * rr;
+        if (a <= 0.f) return;
+        if (c > 0.f && b > 0.f) return;
+        if (c > 0.f && b * b - a * c < 0.f) return;
+        if (c > 0.f && -b > a + sqrtf(b * b - a * c)) return;        // first crossing beyond the end of the segment
+    }
+    SupSphere sup; sup.origin = center; sup.radius = radius;
+    float fr; V3 nrm;
+    const bool hit = subsimplex_point_cast(from, to, sup, fr, nrm);
+    ray_take_cast_hit(hit, fr, nrm, kind, h);
+}
+
 GGL_HD void ray_vs_car_box(V3 from, V3 to, const CarDev& oc, int kind, RayHit& h) {
-    // into the hitbox frame
-    V3 o = tmul(oc.basis, from - oc.pos) - car_hitbox_offset();
-    V3 e = tmul(oc.basis, to - oc.pos) - car_hitbox_offset();
-    V3 d = e - o, he = car_half_extents();
-    float t0 = 0.f, t1 = 1.f;
-    int axis = -1; float sign = 0.f;
-    for (int i = 0; i < 3; i++) {
-        float oi = comp(o, i), di = comp(d, i), hi = comp(he, i);
-        if (fabsf(di) < 1e-12f) {
-            if (oi < -hi || oi > hi) return;
-        } else {
-            float inv = 1.f / di;
-            float ta = (-hi - oi) * inv, tb = (hi - oi) * inv;
-            float s = -1.f;
-            if (ta > tb) { float tmp = ta; ta = tb; tb = tmp; s = 1.f; }
-            if (ta > t0) { t0 = ta; axis = i; sign = s; }
-            if (tb < t1) t1 = tb;
-            if (t0 > t1) return;
+    // The reference casts against every car whose broadphase AABB the segment crosses (btSingleRayCallback::process,
+    // btCollisionWorld.cpp:913-945; the car's compound has no AABB tree, Car.cpp:198). The cast itself can report a hit for a
+    // segment that misses the box (a degenerate simplex ends the iteration early), so this test must be the reference's:
+    // the AABB of the LAST tick's collision detection (car_update_ray_aabb). A state that was just injected has none yet
+    // (all zero): the AABB of the current transform stands in.
+    {
+        V3 mn = oc.aabbMin, mx = oc.aabbMax;
+        if (is_zero(mn) && is_zero(mx)) {
+            car_world_aabb(oc.pos, oc.basis, mn, mx);
+            mn = mn - v3(0.02f, 0.02f, 0.02f); mx = mx + v3(0.02f, 0.02f, 0.02f);
+        }
+        if (mn.x > mx.x) return;
+        const V3 d = to - from;
+        float t0 = 0.f, t1 = 1.f;
+        for (int i = 0; i < 3; i++) {
+            const float oi = comp(from, i), di = comp(d, i), lo = comp(mn, i), hi = comp(mx, i);
+            if (fabsf(di) < 1e-12f) {
+                if (oi < lo || oi > hi) return;
+            } else {
+                const float inv = 1.f / di;
+                float ta = (lo - oi) * inv, tb = (hi - oi) * inv;
+                if (ta > tb) { const float tmp = ta; ta = tb; tb = tmp; }
+                if (ta > t0) t0 = ta;
+                if (tb < t1) t1 = tb;
+                if (t0 > t1) return;
+            }
         }
     }
-    if (axis < 0) return;   // starts inside
-    if (t0 < h.t) {
-        V3 nl = v3(0, 0, 0);
-        set_comp(nl, axis, sign);
-        h.t = t0;
-        h.normal = mul(oc.basis, nl);
-        h.ground = kind;
-    }
+    SupBox sup; sup.basis = oc.basis; sup.origin = oc.pos + mul(oc.basis, car_hitbox_offset()); sup.he = car_box_full_extents();
+    float fr; V3 nrm;
+    const bool hit = subsimplex_point_cast(from, to, sup, fr, nrm);
+    ray_take_cast_hit(hit, fr, nrm, kind, h);
 }
 
 GGL_HD int grid_coord(float v, float mn, float inv, int n) {
@@ -269,6 +388,7 @@ GGL_HD void ray_cast_world(const ArenaDev& A, const WorldDev& W, int selfCar, V3
 // updateVehicleFirst for ONE wheel: ray cast + suspension contact info (btVehicleRL.cpp:64-92,118-212), then that wheel's
 // part of calcFrictionImpulses (:313-387). Wheels are independent of each other here, so the 4 x P wheel tasks of an arena
 // are spread over the lanes of the group.
+GGL_HD void wheel_friction(ArenaDev& A, int ci, int i, bool otherCurrent);
 GGL_HD void wheel_first(ArenaDev& A, const WorldDev& W, int ci, int i) {
     CarDev& c = A.cars[ci];
     const V3 up = car_up(c), right = car_right(c);
@@ -328,7 +448,32 @@ GGL_HD void wheel_first(ArenaDev& A, const WorldDev& W, int ci, int i) {
             w.extraPushback = 0.f;
         }
     }
-    // calcFrictionImpulses (btVehicleRL.cpp:313-387) with LAST tick's engine force / brake / friction factors
+    // A wheel standing on ANOTHER CAR reads that car's velocity in its friction impulse. The reference pre-ticks the cars one
+    // after the other in its car-set order (Arena.cpp:752-764 = players[] slot order), so a car that comes LATER sees the
+    // velocity the earlier car has AFTER its own pre-tick (wheel and jump impulses are applied to the body at once,
+    // btVehicleRL.cpp:390-402). Those wheels are flagged here and finished in slot order by the tick (sim_tick.cuh); every
+    // other wheel (world, ball, a car that comes later in the order) is independent of the other cars' pre-ticks.
+    if (c.w[i].ground >= GROUND_CAR0) {
+        const int o = c.w[i].ground - GROUND_CAR0;
+        int sc = 0, so = 0;
+        for (int s = 0; s < A.numCars; s++) { if (A.slotCar[s] == ci) sc = s; if (A.slotCar[s] == o) so = s; }
+        if (so < sc) {
+#if defined(__CUDA_ARCH__)
+            atomicOr(&A.wheelDefer, 1u << (ci * 4 + i));
+#else
+            A.wheelDefer |= 1u << (ci * 4 + i);
+#endif
+            return;
+        }
+    }
+    wheel_friction(A, ci, i, false);
+}
+
+// one wheel's part of calcFrictionImpulses (btVehicleRL.cpp:313-387) with LAST tick's engine force / brake / friction factors;
+// `otherCurrent`: a car the wheel stands on is read with its CURRENT velocity (it was pre-ticked before this car) instead
+// of the velocity it had when the tick began
+GGL_HD void wheel_friction(ArenaDev& A, int ci, int i, bool otherCurrent) {
+    CarDev& c = A.cars[ci];
     const float frictionScale = rl::CAR_MASS / 3;
     {
         Wheel& w = c.w[i];
@@ -349,7 +494,7 @@ GGL_HD void wheel_first(ArenaDev& A, const WorldDev& W, int ci, int i) {
             gInvI.r0 = v3(ii, 0, 0); gInvI.r1 = v3(0, ii, 0); gInvI.r2 = v3(0, 0, ii);
         } else if (w.ground >= GROUND_CAR0) {
             const CarDev& oc = A.cars[w.ground - GROUND_CAR0];
-            gPos = oc.pos; gVel = oc.velSnap; gAng = oc.angVelSnap; gInvMass = 1.f / rl::CAR_MASS; gInvI = oc.invInertiaW;
+            gPos = oc.pos; gVel = otherCurrent ? oc.vel : oc.velSnap; gAng = otherCurrent ? oc.angVel : oc.angVelSnap; gInvMass = 1.f / rl::CAR_MASS; gInvI = oc.invInertiaW;
         }
         // resolveSingleBilateral(chassis, cp, ground, cp, 0, axle) -> side impulse
         V3 rel1 = w.contactPoint - c.pos, rel2 = w.contactPoint - gPos;
@@ -712,6 +857,7 @@ GGL_HD void car_respawn(ArenaDev& A, CarDev& c) {
     float yaw = (float)(3.14159265358979323846 / 2) + (c.team == 0 ? 0.f : kPi);
     c.basis = m3_from_euler_ypr(yaw, -0.f, -0.f);
     car_update_inertia(c);
+    c.aabbMin = c.aabbMax = v3(0, 0, 0);
 }
 
 GGL_HD void clamp_controls(Controls& k) {

@@ -3,6 +3,7 @@
 // reference performs in Car::SetState/GetState (Sim/Car/Car.cpp:10-36) and Ball::SetState/GetState
 // (Sim/Ball/Ball.cpp:27-49): pos * UU_TO_BT on the way in, * BT_TO_UU on the way out.
 #pragma once
+#include <algorithm>
 #include <string.h>
 #include <vector>
 #include "../../include/gigaenv.h"
@@ -50,6 +51,7 @@ inline void car_from_host(const ggl_car_state& s, CarDev& c, int index, int numC
     c.hasFlipped = s.has_flipped; c.isFlipping = s.is_flipping; c.isJumping = s.is_jumping;
     c.isSupersonic = s.is_supersonic; c.isAutoFlipping = s.is_auto_flipping; c.worldContactHas = s.world_contact_has;
     c.isDemoed = s.is_demoed; c.hitValid = s.hit_valid;
+    if (c.isDemoed) car_freeze_reported_basis(c);      // an injected demolished car reports the orientation it was given
     for (int i = 0; i < 4; i++) c.wheelsWithContact[i] = s.wheels_with_contact[i];
     c.controls = controls_from_host(s.controls);
     c.lastControls = controls_from_host(s.last_controls);
@@ -65,7 +67,8 @@ inline void car_from_host(const ggl_car_state& s, CarDev& c, int index, int numC
 inline void car_to_host(const CarDev& c, ggl_car_state& s) {
     memset(&s, 0, sizeof(s));
     put3(s.pos, c.pos * kBT2UU);
-    put3(s.rot, col(c.basis, 0)); put3(s.rot + 3, col(c.basis, 1)); put3(s.rot + 6, col(c.basis, 2));
+    const M3 rb = car_reported_basis(c);
+    put3(s.rot, col(rb, 0)); put3(s.rot + 3, col(rb, 1)); put3(s.rot + 6, col(rb, 2));
     put3(s.vel, c.vel * kBT2UU);
     put3(s.ang_vel, c.angVel);
     put3(s.flip_rel_torque, c.flipRelTorque);
@@ -106,7 +109,7 @@ inline void arena_phys_from_host(const ggl_arena_state& st, ArenaDev& A) {
     for (int p = 0; p < kNumPads; p++) {
         A.pads[p].isActive = st.pads[p].is_active;
         A.pads[p].cooldown = st.pads[p].cooldown;
-        A.pads[p].prevLockedCarId = st.pads[p].prev_locked_car_id;
+        A.pads[p].prevLockedCarId = (uint8_t)st.pads[p].prev_locked_car_id;
         A.pads[p].curLockedCarId = 0;
     }
 }
@@ -224,9 +227,112 @@ inline void world_build_edge_info(WorldHost& W) {
     }
 }
 
+// The order in which the reference meets the triangles of ONE mesh: a box-vs-mesh or sphere-vs-mesh query walks the mesh's
+// quantized BVH (btBvhTriangleMeshShape(mesh, useQuantizedAabbCompression = true), RocketSim.cpp:167) and reports leaves in
+// the order they have in the node array, i.e. the order the leaf array is left in by the recursive partition of
+// btQuantizedBvh::buildTree (BT/BulletCollision/BroadphaseCollision/btQuantizedBvh.cpp:116-305) on the quantized triangle
+// boxes built by btOptimizedBvh::build (BT/BulletCollision/CollisionShapes/btOptimizedBvh.cpp:100-170, quantisation
+// btQuantizedBvh.cpp:76-105 + btQuantizedBvh.h:331-358). That order decides the row order inside a multi-triangle manifold and
+// which contact normal a car's worldContact keeps (the last one), so the triangles of every mesh are STORED in it: index order
+// on the device is then the reference's visiting order. Returns the permutation (new position -> old index within the mesh).
+struct BvhOrder {
+    V3 bmin, bmax, quant;
+    std::vector<uint16_t> qmin, qmax;     // [leaf][3]
+    std::vector<int> tri;                 // leaf -> triangle index within the mesh
+    void quantize(uint16_t* out, V3 p, bool isMax) const {
+        V3 v = v3((p.x - bmin.x) * quant.x, (p.y - bmin.y) * quant.y, (p.z - bmin.z) * quant.z);
+        if (isMax) {
+            out[0] = (uint16_t)((uint16_t)(v.x + 1.f) | 1); out[1] = (uint16_t)((uint16_t)(v.y + 1.f) | 1); out[2] = (uint16_t)((uint16_t)(v.z + 1.f) | 1);
+        } else {
+            out[0] = (uint16_t)((uint16_t)(v.x) & 0xfffe); out[1] = (uint16_t)((uint16_t)(v.y) & 0xfffe); out[2] = (uint16_t)((uint16_t)(v.z) & 0xfffe);
+        }
+    }
+    V3 unquantize(const uint16_t* q) const {
+        V3 v = v3((float)q[0] / quant.x, (float)q[1] / quant.y, (float)q[2] / quant.z);
+        return v + bmin;
+    }
+    void set_quantization(V3 aabbMin, V3 aabbMax) {
+        const V3 clamp = v3(1.f, 1.f, 1.f), k = v3(65533.f, 65533.f, 65533.f);
+        bmin = aabbMin - clamp; bmax = aabbMax + clamp;
+        V3 size = bmax - bmin;
+        quant = v3(k.x / size.x, k.y / size.y, k.z / size.z);
+        uint16_t q[3];
+        quantize(q, bmin, false);
+        V3 v = unquantize(q);
+        bmin = vmin(bmin, v - clamp);
+        size = bmax - bmin; quant = v3(k.x / size.x, k.y / size.y, k.z / size.z);
+        quantize(q, bmax, true);
+        v = unquantize(q);
+        bmax = vmax(bmax, v + clamp);
+        size = bmax - bmin; quant = v3(k.x / size.x, k.y / size.y, k.z / size.z);
+    }
+    V3 centre(int i) const { return (unquantize(&qmax[3 * i]) + unquantize(&qmin[3 * i])) * 0.5f; }
+    void swap_leaves(int a, int b) {
+        for (int k = 0; k < 3; k++) { std::swap(qmin[3 * a + k], qmin[3 * b + k]); std::swap(qmax[3 * a + k], qmax[3 * b + k]); }
+        std::swap(tri[a], tri[b]);
+    }
+    void build(int start, int end) {
+        const int n = end - start;
+        if (n == 1) return;
+        // calcSplittingAxis
+        V3 means = v3(0, 0, 0), var = v3(0, 0, 0);
+        for (int i = start; i < end; i++) means += centre(i);
+        means *= (1.f / (float)n);
+        for (int i = start; i < end; i++) { V3 d = centre(i) - means; var += v3(d.x * d.x, d.y * d.y, d.z * d.z); }
+        var *= (1.f / ((float)n - 1.f));
+        const int axis = var.x < var.y ? (var.y < var.z ? 2 : 1) : (var.x < var.z ? 2 : 0);        // btVector3::maxAxis
+        // sortAndCalcSplittingIndex
+        V3 m2 = v3(0, 0, 0);
+        for (int i = start; i < end; i++) m2 += centre(i);
+        m2 *= (1.f / (float)n);
+        const float splitValue = comp(m2, axis);
+        int split = start;
+        for (int i = start; i < end; i++)
+            if (comp(centre(i), axis) > splitValue) { swap_leaves(i, split); split++; }
+        const int range = n / 3;
+        if (split <= start + range || split >= end - 1 - range) split = start + (n >> 1);
+        build(start, split);
+        build(split, end);
+    }
+};
+
+inline std::vector<int> bvh_leaf_order(const Tri* t, int n) {
+    BvhOrder B;
+    // btTriangleMeshShape::recalcLocalAabb (btTriangleMeshShape.cpp:58-70): vertex extents, mesh margin 0
+    V3 mn = v3(1e18f, 1e18f, 1e18f), mx = v3(-1e18f, -1e18f, -1e18f);
+    for (int i = 0; i < n; i++) {
+        mn = vmin(mn, vmin(t[i].v0, vmin(t[i].v1, t[i].v2)));
+        mx = vmax(mx, vmax(t[i].v0, vmax(t[i].v1, t[i].v2)));
+    }
+    B.set_quantization(mn, mx);
+    B.qmin.resize(3 * n); B.qmax.resize(3 * n); B.tri.resize(n);
+    for (int i = 0; i < n; i++) {
+        V3 a = vmin(t[i].v0, vmin(t[i].v1, t[i].v2)), b = vmax(t[i].v0, vmax(t[i].v1, t[i].v2));
+        if (b.x - a.x < 0.002f) { b.x = b.x + 0.001f; a.x = a.x - 0.001f; }
+        if (b.y - a.y < 0.002f) { b.y = b.y + 0.001f; a.y = a.y - 0.001f; }
+        if (b.z - a.z < 0.002f) { b.z = b.z + 0.001f; a.z = a.z - 0.001f; }
+        B.quantize(&B.qmin[3 * i], a, false);
+        B.quantize(&B.qmax[3 * i], b, true);
+        B.tri[i] = i;
+    }
+    if (n > 0) B.build(0, n);
+    return B.tri;
+}
+
+inline void world_sort_bvh_order(WorldHost& W) {
+    for (int mesh = 0; mesh < W.numMeshes; mesh++) {
+        const int lo = mesh == 0 ? 0 : W.meshStart[mesh - 1], hi = W.meshStart[mesh];
+        if (hi - lo < 2) continue;
+        const std::vector<int> order = bvh_leaf_order(W.tris.data() + lo, hi - lo);
+        std::vector<Tri> tmp(W.tris.begin() + lo, W.tris.begin() + hi);
+        for (int k = 0; k < hi - lo; k++) W.tris[lo + k] = tmp[order[k]];
+    }
+}
+
 // Uniform grid (cell = 5 bt = 250 uu) over the triangles; a triangle is listed in every cell its AABB (+0.1) touches.
 inline void world_build_grid(WorldHost& W) {
     world_build_edge_info(W);
+    world_sort_bvh_order(W);
     W.cellSize = 5.f;
     W.gridMin = v3(-4500.f * kUU2BT, -6200.f * kUU2BT, -100.f * kUU2BT);
     V3 gmax = v3(4500.f * kUU2BT, 6200.f * kUU2BT, 2200.f * kUU2BT);

@@ -87,7 +87,7 @@ GGL_HD void pad_check_cars(ArenaDev& A, int p) {
             float dx = car.pos.x - pbt.x, dy = car.pos.y - pbt.y;
             if (dx * dx + dy * dy < rad * rad) colliding = fabsf(car.pos.z - pbt.z) < (rl::PAD_CYL_HEIGHT * kUU2BT);
         }
-        if (colliding) pd.curLockedCarId = car.id;
+        if (colliding) pd.curLockedCarId = (uint8_t)car.id;
     }
 }
 
@@ -146,7 +146,7 @@ GGL_HD void phase_finish(ArenaDev& A) {
                     pd.cooldown = p < 6 ? rl::PAD_COOLDOWN_BIG : rl::PAD_COOLDOWN_SMALL;
                 }
             }
-            pd.prevLockedCarId = locked;
+            pd.prevLockedCarId = (uint8_t)locked;
         }
     // Ball::_FinishPhysicsTick
     BallDev& b = A.ball;
@@ -161,7 +161,11 @@ GGL_HD void phase_finish(ArenaDev& A) {
 template <class Exec>
 GGL_HD void arena_tick(ArenaDev& A, const WorldDev& W, const Exec& ex) {
     GGL_PH_BEGIN();
-    if (ex.lane() == 0) A.ball.active = (len2(A.ball.vel) == 0.f && len2(A.ball.angVel) == 0.f) ? 0u : 1u;
+    if (ex.lane() == 0) {
+        A.ball.active = (len2(A.ball.vel) == 0.f && len2(A.ball.angVel) == 0.f) ? 0u : 1u;
+        A.wheelDefer = 0;
+        A.poolCount = 0;
+    }
     for (int c = ex.lane(); c < A.numCars; c += ex.lanes()) { A.cars[c].velSnap = A.cars[c].vel; A.cars[c].angVelSnap = A.cars[c].angVel; }
     if (A.numCars > 0)
         for (int p = ex.lane(); p < kNumPads; p += ex.lanes()) pad_pre_tick(A.pads[p]);
@@ -176,7 +180,21 @@ GGL_HD void arena_tick(ArenaDev& A, const WorldDev& W, const Exec& ex) {
     ex.sync();
     if (GGL_PSYNC_MASK & 4) ex.phase_sync();
     GGL_PH(2);
-    for (int c = ex.lane(); c < A.numCars; c += ex.lanes()) car_pre_tick_c(A, c);
+    if (A.wheelDefer == 0) {
+        for (int c = ex.lane(); c < A.numCars; c += ex.lanes()) car_pre_tick_c(A, c);
+    } else {
+        // some wheel stands on a car that the reference pre-ticks earlier (wheel_first): the rest of the pre-tick runs in the
+        // reference's car order, the flagged wheels reading the velocities the earlier cars have by then
+        for (int s = 0; s < A.numCars; s++) {
+            const int c = A.slotCar[s];
+            if (c % ex.lanes() == ex.lane()) {
+                for (int i = 0; i < 4; i++)
+                    if (A.wheelDefer & (1u << (c * 4 + i))) wheel_friction(A, c, i, true);
+                car_pre_tick_c(A, c);
+            }
+            ex.sync();
+        }
+    }
     ex.sync();
     if (GGL_PSYNC_MASK & 8) ex.phase_sync();
     GGL_PH(3);

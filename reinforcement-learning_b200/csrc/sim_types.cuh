@@ -15,7 +15,9 @@ namespace ggl {
 constexpr int kMaxCars = 6;
 constexpr int kNumPads = 34;
 constexpr int kNumActions = 90;
-constexpr int kMaxContacts = 32;        // solver rows per arena per tick (<= 4 per manifold); further points are dropped
+constexpr int kMaxContacts = 36;        // contact rows per arena per tick: per-body windows + a shared overflow pool (sim_world.cuh);
+                                        // a point that finds neither is dropped AND counted in ArenaDev::contactOverflow
+constexpr int kMaxPool = 16;            // largest overflow pool of the three layouts (contact_pool_size)
 constexpr int kMaxRewards = 16;
 constexpr int kMaxTerminals = 4;
 
@@ -112,11 +114,11 @@ struct BallDev {
     uint32_t active, _pad;
 };
 
-struct PadDev {
+struct PadDev {                  // 8 bytes: car ids are 1 .. kMaxCars
     float cooldown;
-    uint32_t prevLockedCarId;
-    uint32_t curLockedCarId;     // per tick (0 = none)
-    uint8_t isActive, _p[3];
+    uint8_t prevLockedCarId;
+    uint8_t curLockedCarId;      // per tick (0 = none)
+    uint8_t isActive, _p;
 };
 
 // One contact row handed from the narrow phase to the solver.
@@ -169,13 +171,17 @@ struct alignas(16) ArenaDev {
     int32_t numContacts;
     uint32_t bodiesInContact;                      // bit b: body b (0 ball, 1 + c car c) has a solver row this tick
     uint8_t cntWorld, ballAwake, cntBall[kMaxCars], cntRest[kMaxCars], _pad4[2];
-    uint8_t island[8], _pad5[8];                   // island[b] = lowest body index of the contact island body b belongs to
+    uint8_t island[8];                             // island[b] = lowest body index of the contact island body b belongs to
+    uint32_t wheelDefer;                           // per tick: bit 4c+i = wheel i of car c stands on a car pre-ticked before c
+    uint32_t contactOverflow;                      // STICKY: contact points dropped since create because windows and pool were full
     alignas(16) Contact contacts[kMaxContacts];    // from here to cars[]: per-tick scratch that never needs to travel to HBM
+    uint8_t contactOrder[kMaxContacts];           // solver row k = contacts[contactOrder[k]], k < numContacts (gather_contacts)
+    uint8_t poolOwner[kMaxPool];                   // who claimed overflow-pool slot j (POOL_* codes, sim_world.cuh)
+    uint32_t poolCount;                            // overflow-pool slots claimed this tick (atomic: the bodies' lanes race for them)
     // car-vs-mesh staging: candidates per car (gathered by the car's lane), hits found by all lanes of the group
     uint16_t meshCand[kMaxCars][kMaxMeshCand];
     uint8_t meshCandN[kMaxCars], meshHitOverflow[kMaxCars];
     uint32_t meshHitN[kMaxCars];
-    uint8_t _pad6[12];
     CarTriHit meshHit[kMaxCars][kMaxMeshHit];
     alignas(16) CarDev cars[kMaxCars];
 };

@@ -54,12 +54,53 @@ GGL_HD float car_cbt() {
 GGL_HD float ball_inv_inertia() { return 1.f / (0.4f * rl::BALL_MASS * kBallRadiusBT * kBallRadiusBT); }
 
 // ---------------------------------------------------------------------------------------------- contact emission
-// Where a body's contact generation writes: a private window of A.contacts (so that the lanes of a group can generate the
-// contacts of different bodies concurrently; the windows are compacted into solver order afterwards, see gather_contacts).
+// Where a body's contact generation writes: first a private WINDOW of A.contacts (so that the lanes of a group can generate
+// the contacts of different bodies concurrently), then slots claimed one by one from the arena's shared overflow POOL at the
+// end of A.contacts. Layout of A.contacts for P cars (contact_car_window / contact_pool_base):
+//   [0, 4)                 ball-world rows
+//   [4 + i R, 4 + (i+1) R) car i's world + car-car rows, R = 8 / 4 / 3 for 1v1 / 2v2 / 3v3
+//   [4 + P R, kMaxContacts) the pool: 16 / 16 / 14 slots; a car's single car-ball row always lives here
+// gather_contacts turns windows + pool into the solver's row order (A.contactOrder) without moving a row. A point that finds
+// neither a window row nor a pool slot is dropped and counted in A.contactOverflow (sticky; tests and smoke assert it is 0).
+enum : uint8_t { POOL_CAR_REST = 0x00, POOL_BALL_WORLD = 0x20, POOL_CAR_BALL = 0x40 };      // | car index
+GGL_HD int contact_car_window(int numCars) { return numCars <= 2 ? 8 : (numCars <= 4 ? 4 : 3); }
+GGL_HD int contact_pool_base(int numCars) { return 4 + numCars * contact_car_window(numCars); }
+GGL_HD int contact_pool_size(int numCars) { return kMaxContacts - contact_pool_base(numCars); }
+
 struct ContactSink {
-    Contact* buf;
-    int n, cap;
+    Contact* buf;           // the body's window
+    int n, cap;             // logical rows so far (window first, then pool), window size
+    ArenaDev* A;            // for the pool
+    uint8_t owner;          // POOL_* | car index
+    uint8_t mine[kMaxPool]; // pool slots this sink claimed, in claim order
+    GGL_HD Contact& at(int k) { return k < cap ? buf[k] : A->contacts[contact_pool_base(A->numCars) + mine[k - cap]]; }
 };
+GGL_HD ContactSink make_sink(ArenaDev& A, Contact* window, int cap, uint8_t owner) {
+    ContactSink S; S.buf = window; S.n = 0; S.cap = cap; S.A = &A; S.owner = owner;
+    return S;
+}
+// one more logical row: the next window row or a freshly claimed pool slot
+GGL_HD bool sink_grow(ContactSink& S) {
+    if (S.n < S.cap) { S.n++; return true; }
+    const int size = contact_pool_size(S.A->numCars);
+#if defined(__CUDA_ARCH__)
+    const uint32_t slot = atomicAdd(&S.A->poolCount, 1u);
+#else
+    const uint32_t slot = S.A->poolCount++;
+#endif
+    if ((int)slot >= size || S.n - S.cap >= kMaxPool) {
+#if defined(__CUDA_ARCH__)
+        atomicAdd(&S.A->contactOverflow, 1u);
+#else
+        S.A->contactOverflow++;
+#endif
+        return false;
+    }
+    S.A->poolOwner[slot] = S.owner;
+    S.mine[S.n - S.cap] = (uint8_t)slot;
+    S.n++;
+    return true;
+}
 struct ManifoldCtx {     // <= 4 points per body pair, rebuilt each tick
     int first;           // index of the manifold's first row in the sink
     int count;
@@ -72,14 +113,13 @@ GGL_HD float area3(V3 p, V3 q, V3 r, V3 s) { return len2(cross(p - q, s - r)); }
 GGL_HD int manifold_add(ContactSink& S, ManifoldCtx& m, const Contact& c, V3 localA) {
     int idx;
     if (m.count < 4) {
-        if (S.n >= S.cap) return -1;
+        if (!sink_grow(S)) return -1;
         idx = m.count++;
-        S.n++;
     } else {
         int deepest = -1;
         float maxPen = c.dist;
         for (int i = 0; i < 4; i++)
-            if (S.buf[m.first + i].dist < maxPen) { deepest = i; maxPen = S.buf[m.first + i].dist; }
+            if (S.at(m.first + i).dist < maxPen) { deepest = i; maxPen = S.at(m.first + i).dist; }
         float r0 = 0, r1 = 0, r2 = 0, r3 = 0;
         if (deepest != 0) r0 = area3(localA, m.localA[1], m.localA[2], m.localA[3]);
         if (deepest != 1) r1 = area3(localA, m.localA[0], m.localA[2], m.localA[3]);
@@ -90,7 +130,7 @@ GGL_HD int manifold_add(ContactSink& S, ManifoldCtx& m, const Contact& c, V3 loc
         if (fabsf(r2) > best) { best = fabsf(r2); idx = 2; }
         if (fabsf(r3) > best) { best = fabsf(r3); idx = 3; }
     }
-    S.buf[m.first + idx] = c;
+    S.at(m.first + idx) = c;
     m.localA[idx] = localA;
     return m.first + idx;
 }
@@ -224,8 +264,8 @@ GGL_HD void collide_ball_mesh(ArenaDev& A, ContactSink& S, const WorldDev& W) {
             int row = manifold_add(S, m, c, pA - b.pos);
             if (row < 0) continue;
             adjust_internal_edge(t, n, p, pA, depth);
-            S.buf[row].normal = n;
-            S.buf[row].relB = p;
+            S.at(row).normal = n;
+            S.at(row).relB = p;
         }
     }
 }
@@ -490,7 +530,7 @@ GGL_HDN void solve_island(ArenaDev& A, int rep) {
     // special (ball-world) accumulation
     int nSpecial = 0; V3 spNormal = v3(0, 0, 0); float spDist = 0.f, spFriction = 0.f, spRest = 0.f;
     for (int k = 0; k < A.numContacts; k++) {
-        const Contact& c = A.contacts[k];
+        const Contact& c = A.contacts[A.contactOrder[k]];
         int a = c.bodyA, b = c.bodyB;
         if (A.island[a] != rep) continue;
         setup_contact_row(rows[nr], sb, a, b, c.normal, c.relA, c.relB, c.dist, c.friction, c.restitution, c.special);
@@ -561,11 +601,6 @@ GGL_HDN void collide_car_car(ArenaDev& A, ContactSink& S, int lo, int hi);
 GGL_HDN void car_mesh_emit(ArenaDev& A, ContactSink& S, const WorldDev& W, int ci);
 GGL_HD void car_car_callback(ArenaDev& A, int i1, int i2, V3 localA, V3 localB);
 
-// Contact windows inside A.contacts: [0,4) ball-world, [4,4+P) one car-ball row per car, then P windows of
-// (kMaxContacts-4-P)/P rows for each car's world + car-car rows. Window order = solver row order of the reference
-// (pair-cache insertion order, SURVEY 7: ball's pairs first, then each car's statics, then its car-car pairs).
-GGL_HD int contact_car_window(int numCars) { return (kMaxContacts - 4 - numCars) / numCars; }
-
 // Velocity update of a body that no contact row touches: what the solver's write-back does with zero delta impulses.
 GGL_HD void body_free_velocity(ArenaDev& A, int b) {
     if (b == 0) {
@@ -587,7 +622,7 @@ GGL_HD void body_free_velocity(ArenaDev& A, int b) {
 GGL_HDN void collide_body(ArenaDev& A, const WorldDev& W, int b) {
     const float ex = rl::ARENA_EXTENT_X * kUU2BT, hz = rl::ARENA_HEIGHT * kUU2BT;
     if (b == 0) {
-        ContactSink S; S.buf = A.contacts; S.n = 0; S.cap = 4;
+        ContactSink S = make_sink(A, A.contacts, 4, POOL_BALL_WORLD);
         if (A.ball.active) {
             GGL_SUB_BEGIN();
             collide_ball_mesh(A, S, W);
@@ -602,9 +637,10 @@ GGL_HDN void collide_body(ArenaDev& A, const WorldDev& W, int b) {
     }
     const int i = b - 1, P = A.numCars, R = contact_car_window(P);
     A.cars[i].ballHitNew = 0;
-    ContactSink SB; SB.buf = A.contacts + 4 + i; SB.n = 0; SB.cap = 1;
-    ContactSink S; S.buf = A.contacts + 4 + P + i * R; S.n = 0; S.cap = R;
+    ContactSink SB = make_sink(A, A.contacts, 0, (uint8_t)(POOL_CAR_BALL | i));
+    ContactSink S = make_sink(A, A.contacts + 4 + i * R, R, (uint8_t)(POOL_CAR_REST | i));
     if (!A.cars[i].rbDisabled) {
+        car_update_ray_aabb(A, i);
         GGL_SUB_BEGIN();
         collide_car_ball(A, SB, i);
         GGL_SUB(0);
@@ -622,45 +658,63 @@ GGL_HDN void collide_body(ArenaDev& A, const WorldDev& W, int b) {
     A.cntRest[i] = (uint8_t)S.n;
 }
 
-// Leader: compacts the windows into solver order, runs the order-dependent contact callbacks (ball extra impulse in car
-// order, car-car bump/demo logic per point), the ball wake-up rule, and marks the bodies that have a row.
+// Leader: turns windows + pool into the solver's row order (A.contactOrder, nothing is moved), runs the order-dependent
+// contact callbacks (ball extra impulse in car order, car-car bump/demo logic per point), the ball wake-up rule, and marks the
+// bodies that have a row. Row order = the reference's (pair-cache insertion order): the ball's world rows, the
+// car-ball rows in car order, then every car's world + car-car rows; within a body, window rows before pool rows, pool rows in
+// claim order (a body's lane claims them one after the other, so claim order is its emission order).
+GGL_HD int pool_next(const ArenaDev& A, uint8_t owner, int& cursor) {
+    const int used = (int)A.poolCount < contact_pool_size(A.numCars) ? (int)A.poolCount : contact_pool_size(A.numCars);
+    while (cursor < used && A.poolOwner[cursor] != owner) cursor++;
+    return cursor < used ? contact_pool_base(A.numCars) + cursor++ : -1;
+}
 GGL_HDN void gather_contacts(ArenaDev& A) {
     const int P = A.numCars, R = contact_car_window(P);
-    int n = A.cntWorld;
+    int n = 0;
+    {
+        int cur = 0;
+        for (int k = 0; k < A.cntWorld; k++) {
+            const int row = k < 4 ? k : pool_next(A, POOL_BALL_WORLD, cur);
+            if (row >= 0) A.contactOrder[n++] = (uint8_t)row;
+        }
+    }
     for (int i = 0; i < P; i++)
         if (A.cntBall[i]) {
-            if (n != 4 + i) A.contacts[n] = A.contacts[4 + i];
-            n++;
+            int cur = 0;
+            const int row = pool_next(A, (uint8_t)(POOL_CAR_BALL | i), cur);
+            if (row >= 0) A.contactOrder[n++] = (uint8_t)row;
             if (A.cars[i].ballHitNew) A.ball.velImpulseCache += A.cars[i].hitExtraVel * kUU2BT;
         }
-    for (int i = 0; i < P; i++)
+    for (int i = 0; i < P; i++) {
+        int cur = 0;
         for (int k = 0; k < A.cntRest[i]; k++) {
-            const int src = 4 + P + i * R + k;
-            if (n != src) A.contacts[n] = A.contacts[src];
-            const Contact& c = A.contacts[n];
-            n++;
+            const int row = k < R ? 4 + i * R + k : pool_next(A, (uint8_t)(POOL_CAR_REST | i), cur);
+            if (row < 0) continue;
+            A.contactOrder[n++] = (uint8_t)row;
+            const Contact& c = A.contacts[row];
             if (c.bodyA > 0 && c.bodyB > 0) {
                 const CarDev& a = A.cars[c.bodyA - 1];
                 const CarDev& b = A.cars[c.bodyB - 1];
                 car_car_callback(A, c.bodyA - 1, c.bodyB - 1, tmul(a.basis, c.relA), tmul(b.basis, c.relB));
             }
         }
+    }
     A.numContacts = n;
     bool ballAwake = A.ball.active != 0;
     if (!ballAwake) {
         for (int k = 0; k < n; k++)
-            if (A.contacts[k].bodyB == 0) ballAwake = true;      // touched by an active car: the island wakes it up
+            if (A.contacts[A.contactOrder[k]].bodyB == 0) ballAwake = true;      // touched by an active car: the island wakes it up
         if (!ballAwake) {
             int w = 0;
             for (int k = 0; k < n; k++)
-                if (A.contacts[k].bodyA != 0) A.contacts[w++] = A.contacts[k];
+                if (A.contacts[A.contactOrder[k]].bodyA != 0) A.contactOrder[w++] = A.contactOrder[k];
             A.numContacts = w;
         }
     }
     A.ballAwake = ballAwake ? 1 : 0;
     uint32_t mask = 0;
     for (int k = 0; k < A.numContacts; k++) {
-        const Contact& c = A.contacts[k];
+        const Contact& c = A.contacts[A.contactOrder[k]];
         mask |= 1u << c.bodyA;
         if (c.bodyB >= 0) mask |= 1u << c.bodyB;
     }
@@ -670,7 +724,7 @@ GGL_HDN void gather_contacts(ArenaDev& A) {
     for (int pass = 0; pass < kMaxCars; pass++) {
         bool changed = false;
         for (int k = 0; k < A.numContacts; k++) {
-            const Contact& c = A.contacts[k];
+            const Contact& c = A.contacts[A.contactOrder[k]];
             if (c.bodyB < 0) continue;
             const uint8_t la = A.island[c.bodyA], lb = A.island[c.bodyB];
             if (la != lb) { const uint8_t m = la < lb ? la : lb; A.island[c.bodyA] = m; A.island[c.bodyB] = m; changed = true; }

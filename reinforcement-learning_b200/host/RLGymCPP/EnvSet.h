@@ -345,6 +345,10 @@ struct EnvSet {                                         // EnvSet.h:62-110
         _Check(ggl_envset_reset(_h, nullptr), "ggl_envset_reset");
         _Pull(true);
     }
+    void ResetArena(int index) {                        // EnvSet.cpp:275-331 called directly: unconditional
+        _Check(ggl_envset_reset_arena(_h, index, nullptr), "ggl_envset_reset_arena");
+        _Pull(true);
+    }
     // device buffers (what torch::from_blob wraps zero-copy), valid until the EnvSet is destroyed
     const ggl_envset_views& deviceViews() const { return _views; }
     ggl_envset* handle() const { return _h; }

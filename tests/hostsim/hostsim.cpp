@@ -11,6 +11,7 @@ using namespace ggl;
 struct HostSim {
     WorldHost world;
     ArenaDev arena;
+    bool orderSet = false;
 };
 
 extern "C" {
@@ -25,12 +26,26 @@ void* hostsim_create(const ggl_mesh_blob* meshes, int n) {
     return h;
 }
 void hostsim_destroy(void* p) { delete (HostSim*)p; }
+// vertices of stored triangle i (9 floats) and its mesh index: the storage order is the reference's BVH leaf order per mesh
+int hostsim_tri(void* p, int i, float* out9) {
+    const Tri& t = ((HostSim*)p)->world.tris[i];
+    out9[0] = t.v0.x; out9[1] = t.v0.y; out9[2] = t.v0.z; out9[3] = t.v1.x; out9[4] = t.v1.y; out9[5] = t.v1.z;
+    out9[6] = t.v2.x; out9[7] = t.v2.y; out9[8] = t.v2.z;
+    return (int)(t.flags >> TRI_MESH_SHIFT);
+}
 int hostsim_num_tris(void* p) { return (int)((HostSim*)p)->world.tris.size(); }
 
 void hostsim_set_state(void* p, const ggl_arena_state* st) {
     HostSim* h = (HostSim*)p;
     arena_phys_from_host(*st, h->arena);
-    for (int s = 0; s < h->arena.numCars; s++) h->arena.slotCar[s] = (uint8_t)(h->arena.numCars - 1 - s);
+    if (!h->orderSet)
+        for (int s = 0; s < h->arena.numCars; s++) h->arena.slotCar[s] = (uint8_t)(h->arena.numCars - 1 - s);
+}
+// players[] slot order (= the reference's car-set iteration order, which also orders the cars' pre-ticks): ids[slot] = carId
+void hostsim_set_slot_order(void* p, const int32_t* ids) {
+    HostSim* h = (HostSim*)p;
+    for (int s = 0; s < h->arena.numCars; s++) h->arena.slotCar[s] = (uint8_t)(ids[s] - 1);
+    h->orderSet = true;
 }
 void hostsim_get_state(void* p, ggl_arena_state* st) { arena_phys_to_host(((HostSim*)p)->arena, *st); }
 void hostsim_seed(void* p, uint32_t seed) { ((HostSim*)p)->arena.rng = seed; }
@@ -48,7 +63,7 @@ int hostsim_contacts(void* p, float* out, int max) {
     const ArenaDev& A = h->arena;
     int n = 0;
     for (int k = 0; k < A.numContacts && n < max; k++) {
-        const Contact& c = A.contacts[k];
+        const Contact& c = A.contacts[A.contactOrder[k]];
         float* o = out + 20 * n++;
         memset(o, 0, 80);
         o[0] = c.bodyA; o[1] = c.bodyB;
@@ -59,6 +74,37 @@ int hostsim_contacts(void* p, float* out, int max) {
     return n;
 }
 
+
+// same call as ref_convex_ray_cast (oracle/ref_harness.cpp): the device's ray-vs-hitbox / ray-vs-ball cast
+int hostsim_convex_ray_cast(int kind, const float* from, const float* to, const float* pos, const float* basis, float* out) {
+    RayHit h; h.t = 1.f; h.ground = GROUND_NONE; h.normal = v3(0, 0, 0);
+    V3 f = v3(from[0], from[1], from[2]), t = v3(to[0], to[1], to[2]);
+    if (kind == 0) {
+        CarDev c; memset(&c, 0, sizeof(c));
+        c.pos = v3(pos[0], pos[1], pos[2]);
+        c.basis.r0 = v3(basis[0], basis[1], basis[2]); c.basis.r1 = v3(basis[3], basis[4], basis[5]); c.basis.r2 = v3(basis[6], basis[7], basis[8]);
+        ray_vs_car_box(f, t, c, GROUND_CAR0, h);
+    } else {
+        ray_vs_sphere(f, t, v3(pos[0], pos[1], pos[2]), rl::BALL_RADIUS * kUU2BT, GROUND_BALL, h);
+    }
+    if (h.ground == GROUND_NONE) return 0;
+    out[0] = h.t; out[1] = h.normal.x; out[2] = h.normal.y; out[3] = h.normal.z;
+    return 1;
+}
+
+// same layout as ref_arena_wheel_info (oracle/ref_harness.cpp)
+void hostsim_wheel_info(void* p, int carId, float* out) {
+    HostSim* h = (HostSim*)p;
+    const CarDev& c = h->arena.cars[carId - 1];
+    for (int i = 0; i < 4; i++) {
+        const Wheel& w = c.w[i];
+        float* o = out + 12 * i;
+        o[0] = w.contactNormal.x; o[1] = w.contactNormal.y; o[2] = w.contactNormal.z;
+        o[3] = w.contactPoint.x; o[4] = w.contactPoint.y; o[5] = w.contactPoint.z;
+        o[6] = w.suspLen; o[7] = (float)w.ground;
+        o[8] = w.impulse.x; o[9] = w.impulse.y; o[10] = w.impulse.z; o[11] = w.suspRelVel;
+    }
+}
 
 void hostsim_set_controls(void* p, const ggl_arena_state* st) {
     HostSim* h = (HostSim*)p;
@@ -157,6 +203,17 @@ void hostenv_set_reset_state(void* p, int a, const ggl_arena_state* st) {
     memset(&h->resets[a], 0, sizeof(ArenaDev));
     arena_phys_from_host(*st, h->resets[a]);
     h->resets[a].hasResetState = 1;
+}
+uint64_t hostenv_contact_overflow(void* p) {
+    HostEnv* h = (HostEnv*)p;
+    uint64_t n = 0;
+    for (auto& A : h->arenas) n += A.contactOverflow;
+    return n;
+}
+void hostenv_reset_arena(void* p, int a) {
+    HostEnv* h = (HostEnv*)p;
+    for (int i = 0; i < h->cfg.numArenas; i++)
+        if (a < 0 || i == a) host_reset_arena(h, i, true, h->cfg.stateSetter);
 }
 void hostenv_set_slot_order(void* p, const int32_t* ids) {
     HostEnv* h = (HostEnv*)p;

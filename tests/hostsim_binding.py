@@ -69,6 +69,11 @@ class HostSim:
     def set_controls(self, st):
         lib().hostsim_set_controls(self.h, C.byref(st))
 
+    def set_slot_order(self, ids):
+        ids = np.ascontiguousarray(ids, np.int32)
+        lib().hostsim_set_slot_order.argtypes = [C.c_void_p, C.c_void_p]
+        lib().hostsim_set_slot_order(self.h, ids.ctypes.data)
+
     def step(self, ticks=1):
         lib().hostsim_step(self.h, ticks)
 
@@ -142,6 +147,16 @@ class HostEnvSet:
     def set_slot_order(self, ids):
         ids = np.ascontiguousarray(ids, np.int32)
         lib().hostenv_set_slot_order(self.h, ids.ctypes.data)
+
+    def contact_overflow(self):
+        lib().hostenv_contact_overflow.restype = C.c_uint64
+        lib().hostenv_contact_overflow.argtypes = [C.c_void_p]
+        return int(lib().hostenv_contact_overflow(self.h))
+
+    def reset_arena(self, a=-1):
+        lib().hostenv_reset_arena.argtypes = [C.c_void_p, C.c_int]
+        lib().hostenv_reset_arena(self.h, a)
+        self._refresh()
 
     def step_np(self, acts):
         acts = np.ascontiguousarray(acts, np.int32)

@@ -67,3 +67,94 @@ def test_contact_scenarios_per_tick(name):
         nbad += bad is not None
     assert nbad == 0 and worst <= 1e-3, (name, worst, nbad)
     env.close()
+
+
+def test_steady_state_scripted_events_match_reference():
+    """Host compile, ADVICE r1: parity where the game actually happens. The reference is pre-rolled 100 steps from the kickoff,
+    every arena is then put into a scripted situation (goal, shot, save attempt, bump, demolition, pad pickup, pile-up) or left
+    in mid-play, and 40 env steps are compared with the physics re-synchronised before every step. Integer outputs (masks,
+    terminals, all nine event flags) must be exact with goals, shots, bumps and demolitions actually occurring; obs / rewards
+    hold 1e-4 except on the arena-steps where contact ORDER differs from the reference's (rows of a
+    multi-triangle mesh manifold, manifolds of one island), which are counted and bounded."""
+    import scenarios
+    r = env_parity.run_steady_state(None, num_arenas=14, ppt=2, preroll=100, steps=40, seed=2, env_cls=hb.HostEnvSet,
+                                    scripts=scenarios.env_scripts(14, 2, 1))
+    assert r["mask_mismatch"] == 0 and r["term_mismatch"] == 0 and r["event_mismatch"] == 0, r
+    assert r["contact_overflow"] == 0, r
+    ev = r["events"]
+    assert ev[0] > 0 and ev[3] > 0 and ev[5] > 0 and ev[6] > 0, r          # goal, shot, bump, bumped
+    assert r["touches"] > 0 and r["goals_seen"] > 0 and r["terminals_seen"] > 0, r
+    assert r["bad_arena_steps"] <= 0.05 * r["arena_steps"], r
+
+
+def test_steady_state_3v3_pileups_do_not_overflow_contact_rows():
+    import scenarios
+    r = env_parity.run_steady_state(None, num_arenas=14, ppt=3, preroll=60, steps=30, seed=3, env_cls=hb.HostEnvSet,
+                                    scripts=scenarios.env_scripts(14, 3, 1), verbose=bool(__import__("os").environ.get("GGL_TEST_VERBOSE")))
+    assert r["mask_mismatch"] == 0 and r["term_mismatch"] == 0 and r["event_mismatch"] == 0, r
+    assert r["contact_overflow"] == 0, r
+    assert r["events"][7] > 0 and r["events"][8] > 0, r                      # demo, demoed
+    assert r["bad_arena_steps"] <= 0.06 * r["arena_steps"], r
+
+
+def test_suspension_ray_vs_car_hitbox_matches_reference_cast():
+    """The convex cast a suspension ray runs against another car's hitbox (btSubsimplexConvexCast through
+    btCollisionWorld::rayTestSingle, reference shapes) against the device's restatement: hit / miss, fraction and normal."""
+    import ctypes as C
+    import numpy as np
+    L = oracle_ref.lib(); L.ref_set_threads(1)
+    ref = oracle_ref.RefEnvSet(1, 1)
+    H = hb.lib()
+    fp = C.c_void_p
+    L.ref_convex_ray_cast.argtypes = [C.c_void_p, C.c_int, fp, fp, fp, fp, fp]
+    H.hostsim_convex_ray_cast.argtypes = [C.c_int, fp, fp, fp, fp, fp]
+    rng = np.random.default_rng(0)
+    hits = 0
+    for it in range(3000):
+        q = rng.standard_normal(4); q /= np.linalg.norm(q); w, x, y, z = q
+        basis = np.array([1 - 2 * (y * y + z * z), 2 * (x * y - z * w), 2 * (x * z + y * w), 2 * (x * y + z * w), 1 - 2 * (x * x + z * z),
+                          2 * (y * z - x * w), 2 * (x * z - y * w), 2 * (y * z + x * w), 1 - 2 * (x * x + y * y)], np.float32)
+        pos = (rng.standard_normal(3) * 20).astype(np.float32)
+        d = rng.standard_normal(3); d /= np.linalg.norm(d)
+        target = pos + (rng.standard_normal(3) * 0.7).astype(np.float32)
+        frm = (target - d * rng.uniform(0.2, 1.5)).astype(np.float32); to = (frm + d * 1.3).astype(np.float32)
+        o1 = np.zeros(4, np.float32); o2 = np.zeros(4, np.float32)
+        h1 = L.ref_convex_ray_cast(ref.h, 0, frm.ctypes.data, to.ctypes.data, pos.ctypes.data, basis.ctypes.data, o1.ctypes.data)
+        h2 = H.hostsim_convex_ray_cast(0, frm.ctypes.data, to.ctypes.data, pos.ctypes.data, basis.ctypes.data, o2.ctypes.data)
+        assert h1 == h2, (it, h1, h2)
+        if h1:
+            hits += 1
+            assert o1[0] == o2[0] and np.abs(o1[1:] - o2[1:]).max() <= 5e-7, (it, o1, o2)
+    assert hits > 500
+    ref.close()
+
+
+def test_mesh_triangles_are_stored_in_reference_bvh_leaf_order():
+    """The device meets the triangles of a mesh in index order; the reference in the leaf order of the mesh's quantized BVH
+    (row order inside a multi-triangle manifold, which contact normal a car keeps). The host build of the world stores every
+    mesh's triangles in that order (sim_convert.cuh: bvh_leaf_order): checked against the compiled reference's own trees."""
+    import ctypes as C
+    import struct
+    import numpy as np
+    L = oracle_ref.lib()
+    L.ref_mesh_leaf_order.argtypes = [C.c_int, C.c_void_p, C.c_int]
+    sim = hb.HostSim()
+    H = hb.lib()
+    H.hostsim_tri.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+    H.hostsim_num_tris.argtypes = [C.c_void_p]
+    meshes = oracle_ref.arena_mesh.soccar_meshes()
+    base, multi = 0, 0
+    for m, blob in enumerate(meshes):
+        nt, nv = struct.unpack_from("<ii", blob, 0)
+        idx = np.frombuffer(blob, np.int32, nt * 3, 8).reshape(nt, 3)
+        vert = np.frombuffer(blob, np.float32, nv * 3, 8 + nt * 12).reshape(nv, 3)
+        order = np.zeros(nt, np.int32)
+        assert L.ref_mesh_leaf_order(m, order.ctypes.data, nt) == nt
+        multi += int((order != np.arange(nt)).any())
+        for k in range(nt):
+            out = np.zeros(9, np.float32)
+            assert H.hostsim_tri(sim.h, base + k, out.ctypes.data) == m
+            assert np.array_equal(out.reshape(3, 3), vert[idx[order[k]]]), (m, k, order[k])
+        base += nt
+    assert base == H.hostsim_num_tris(sim.h)
+    assert multi > 0      # at least one mesh whose BVH order is not the file order, so the check means something
