@@ -22,6 +22,7 @@
 //
 // Compiled with -fmad=false: per-element arithmetic then rounds exactly like the reference's scalar loop; only
 // the cross-thread carry (composition order) differs, and its effect decays by gamma*lambda per step.
+#include <mutex>
 #include "common.cuh"
 
 namespace {
@@ -590,25 +591,27 @@ WsLayout ws_layout(long long L) {
     return w;
 }
 
+// The opt-in shared memory size is a per-device function attribute: one process may drive several GPUs (the reference's
+// Learner is one process), so it is set on every launch (cheap) rather than remembered per process.
 template <bool HT, bool NM, bool CL>
 int launch(const GaeParams& p, int grid, cudaStream_t s) {
-    static bool attr_done = false;
-    if (!attr_done) {
-        GGL_CUDA(cudaFuncSetAttribute(gae_scan_kernel<HT, NM, CL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gae_smem_bytes()));
-        attr_done = true;
-    }
+    GGL_CUDA(cudaFuncSetAttribute(gae_scan_kernel<HT, NM, CL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gae_smem_bytes()));
     gae_scan_kernel<HT, NM, CL><<<grid, GAE_THREADS, gae_smem_bytes(), s>>>(p);
     GGL_LAUNCH_CHECK();
     ggl::count_launch();
     return GGL_OK;
 }
 
-// cached per-device scratch for the host-buffer wrapper
+// scratch of the host-buffer wrapper and occupancy of the scan kernel, cached PER DEVICE ordinal behind a mutex
 struct HostScratch {
     void* d = nullptr;
     size_t bytes = 0;
     cudaStream_t stream = nullptr;
-} g_scratch;
+    int occ = 0;
+};
+constexpr int kMaxDevices = 64;
+HostScratch g_scratch_dev[kMaxDevices];
+std::mutex g_scratch_mutex, g_occ_mutex;
 
 }  // namespace
 
@@ -660,8 +663,9 @@ extern "C" int ggl_gae_compute(const float* d_rews, const int8_t* d_terminals, c
     GGL_CUDA(cudaGetDevice(&dev));
     GGL_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     int per_sm = GAE_CFG_MINBLOCKS;                                    // persistent: as many CTAs as stay resident
-    {
-        static int occ = 0;
+    if (dev >= 0 && dev < kMaxDevices) {
+        std::lock_guard<std::mutex> lock(g_occ_mutex);
+        int& occ = g_scratch_dev[dev].occ;
         if (!occ) {
             GGL_CUDA(cudaFuncSetAttribute(gae_scan_kernel<true, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gae_smem_bytes()));
             GGL_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, gae_scan_kernel<true, true, true>, GAE_THREADS, gae_smem_bytes()));
@@ -694,6 +698,11 @@ extern "C" int ggl_gae_compute_host(const float* h_rews, const int8_t* h_termina
                                     float* h_out_clip_portion) {
     if (L < 0 || K < 0) { ggl::set_error("ggl_gae_compute_host: negative size"); return GGL_ERR_INVALID; }
     if (L == 0) { if (h_out_clip_portion) *h_out_clip_portion = 0.f; return GGL_OK; }
+    int dev = 0;
+    GGL_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevices) { ggl::set_error("ggl_gae_compute_host: device ordinal %d not supported", dev); return GGL_ERR_INVALID; }
+    std::lock_guard<std::mutex> lock(g_scratch_mutex);      // one host-buffer call per process at a time: the scratch is shared
+    HostScratch& g_scratch = g_scratch_dev[dev];
     if (!g_scratch.stream) GGL_CUDA(cudaStreamCreateWithFlags(&g_scratch.stream, cudaStreamNonBlocking));
     cudaStream_t s = g_scratch.stream;
     const size_t nL = align_up((size_t)L * 4, 256), nT = align_up((size_t)L, 256), nK = align_up((size_t)(K ? K : 1) * 4, 256);

@@ -285,6 +285,17 @@ struct SupBox {
     }
 };
 
+// out of line: a wheel ray meets a ball or another car's AABB in well under 1 % of the ticks, and the iteration is ~4 K
+// instructions that would otherwise sit in the middle of the per-tick path of an instruction-fetch bound kernel
+GGL_HDN bool cast_point_vs_sphere(V3 from, V3 to, V3 center, float radius, float& fraction, V3& normal) {
+    SupSphere sup; sup.origin = center; sup.radius = radius;
+    return subsimplex_point_cast(from, to, sup, fraction, normal);
+}
+GGL_HDN bool cast_point_vs_box(V3 from, V3 to, V3 origin, const M3& basis, V3 he, float& fraction, V3& normal) {
+    SupBox sup; sup.basis = basis; sup.origin = origin; sup.he = he;
+    return subsimplex_point_cast(from, to, sup, fraction, normal);
+}
+
 // rayTestSingleInternal's bookkeeping around the cast (btCollisionWorld.cpp:288-311) + ClosestRayResultCallback
 GGL_HD void ray_take_cast_hit(bool hit, float fraction, V3 normal, int kind, RayHit& h) {
     if (!hit) return;
@@ -307,9 +318,8 @@ GGL_HD void ray_vs_sphere(V3 from, V3 to, V3 center, float radius, int kind, Ray
         if (c > 0.f && b * b - a * c < 0.f) return;
         if (c > 0.f && -b > a + sqrtf(b * b - a * c)) return;        // first crossing beyond the end of the segment
     }
-    SupSphere sup; sup.origin = center; sup.radius = radius;
     float fr; V3 nrm;
-    const bool hit = subsimplex_point_cast(from, to, sup, fr, nrm);
+    const bool hit = cast_point_vs_sphere(from, to, center, radius, fr, nrm);
     ray_take_cast_hit(hit, fr, nrm, kind, h);
 }
 
@@ -342,9 +352,8 @@ GGL_HD void ray_vs_car_box(V3 from, V3 to, const CarDev& oc, int kind, RayHit& h
             }
         }
     }
-    SupBox sup; sup.basis = oc.basis; sup.origin = oc.pos + mul(oc.basis, car_hitbox_offset()); sup.he = car_box_full_extents();
     float fr; V3 nrm;
-    const bool hit = subsimplex_point_cast(from, to, sup, fr, nrm);
+    const bool hit = cast_point_vs_box(from, to, oc.pos + mul(oc.basis, car_hitbox_offset()), oc.basis, car_box_full_extents(), fr, nrm);
     ray_take_cast_hit(hit, fr, nrm, kind, h);
 }
 

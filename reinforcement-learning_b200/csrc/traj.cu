@@ -213,6 +213,21 @@ extern "C" int ggl_traj_create(const ggl_traj_desc* d, ggl_traj** out) {
     T.cap = d->max_episode_length > 1 ? d->max_episode_length : 1;   // a buffer is flushed as soon as it holds maxEpisodeLength steps
     T.capL = d->capacity_timesteps; T.capK = d->capacity_truncated;
     const size_t rows = (size_t)T.N * T.cap;
+    {
+        // The per-player buffers are dense [numPlayers][maxEpisodeLength] rows (most of them never touched when episodes are
+        // short): refuse with the numbers instead of failing somewhere inside cudaMalloc. C2's shape (16 384 players x 1 800
+        // steps x obs 167) needs 22 GB; 98 304 players x 1 800 x obs 225 would need 177 GB and does not fit one B200.
+        const size_t perRow = (size_t)T.obs * 4 + (size_t)T.A + 4 + 4 + 4 + 1;
+        const size_t need = rows * perRow + (size_t)T.capL * perRow + (size_t)T.capK * T.obs * 4;
+        size_t freeB = 0, totalB = 0;
+        if (cudaMemGetInfo(&freeB, &totalB) == cudaSuccess && need > freeB) {
+            ggl::set_error("ggl_traj_create: %zu players x %d steps per episode x %zu B per step + the combined stream need %.1f GB, %.1f GB are free "
+                           "on device %d: lower max_episode_length (every player's buffer is allocated at full length)",
+                           (size_t)T.N, T.cap, perRow, need / 1e9, freeB / 1e9, d->device);
+            tfree(t);
+            return GGL_ERR_NOMEM;
+        }
+    }
     TRAJ_TRY(talloc(t, &T.pStates, rows * T.obs)); TRAJ_TRY(talloc(t, &T.pMasks, rows * T.A)); TRAJ_TRY(talloc(t, &T.pActions, rows));
     TRAJ_TRY(talloc(t, &T.pLogProbs, rows)); TRAJ_TRY(talloc(t, &T.pRewards, rows)); TRAJ_TRY(talloc(t, &T.pTerminals, rows));
     TRAJ_TRY(talloc(t, &T.pLen, (size_t)T.N)); TRAJ_TRY(talloc(t, &T.segLen, (size_t)T.N));

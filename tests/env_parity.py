@@ -170,10 +170,22 @@ def run_steady_state(ggl, num_arenas=16, ppt=2, preroll=160, steps=40, seed=0, o
     dev = (env_cls or ggl.EnvSet)(num_arenas, ppt, obs_kind=obs_kind, state_setter=oracle_ref.abi.SETTER_INJECTED, seed=seed, **kw)
     ids, teams = ref.slot_info()
     dev.set_slot_order(ids)
+    # The game event tracker keeps the ball update count of its last Update() across resets (GameEventTracker.cpp:48-158;
+    # ResetPersistentInfo does not clear it) and is not part of any state struct. Both sides have played before the hand-over
+    # (the device two idle steps) and the injected ball counter is 0, as after Ball::SetState in a real StateSetter: both
+    # trackers then see the count go DOWN in the first compared step, reset themselves and continue in step from there.
+    idle = np.full(num_arenas * 2 * ppt, 8, np.int32)
+    for _ in range(2):
+        if hasattr(dev, "step_np"):
+            dev.step_np(idle)
+        else:
+            import torch
+            dev.step(torch.from_numpy(idle).to(dev.device))
     for a in range(num_arenas):
         st = ref.get_state(a)
         if scripts and a in scripts:
             scripts[a](st)
+        st.ball.update_counter = 0
         ref.set_reset_state(a, st)
         dev.set_reset_state(a, st)
         ref.reset_arena(a)

@@ -25,6 +25,36 @@ def test_env_steps_match_reference(ggl, ppt, obs_kind):
     assert r["rew"] <= 1e-4, r
 
 
+@pytest.mark.parametrize("ppt,arenas,seed", [(2, 42, 2), (3, 28, 3), (1, 28, 4)])
+def test_steady_state_scripted_events_match_reference(ggl, ppt, arenas, seed):
+    """parity where the game happens. The reference is pre-rolled from the kickoff, every second arena is then put
+    into a scripted situation (goal, shot, save attempt, bump, demolition, pad pickup, pile-up of all cars), the others stay
+    in mid-play; both sides reset onto those states and 40 env steps are compared with the physics re-synchronised before
+    every step (env_parity.run_steady_state). Masks, terminals and all nine event flags are exact on every arena-step whose obs
+    hold the tolerance, with goals, shots, bumps and demolitions occurring; no contact point is dropped; the arena-steps whose
+    obs leave 1e-4 (contact order inside an island, knife-edge internal-edge decisions: DESIGN.md section 2) stay below 5 %."""
+    r = env_parity.run_steady_state(ggl, num_arenas=arenas, ppt=ppt, preroll=100, steps=40, seed=seed,
+                                    scripts=scenarios.env_scripts(arenas, ppt, 2))
+    print("steady state %dv%d: %s" % (ppt, ppt, {k: (v.tolist() if hasattr(v, "tolist") else v) for k, v in r.items()}))
+    assert r["mask_mismatch"] == 0 and r["term_mismatch"] == 0 and r["event_mismatch"] == 0, r
+    assert r["contact_overflow"] == 0, r
+    ev = r["events"]
+    assert ev[0] > 0 and ev[3] > 0 and ev[5] > 0 and ev[6] > 0, r          # goal, shot, bump, bumped
+    assert r["touches"] > 0 and r["goals_seen"] > 0 and r["terminals_seen"] > 0, r
+    assert r["rew"] <= 1e-4, r
+    assert r["bad_arena_steps"] <= 0.05 * r["arena_steps"], r
+
+
+def test_steady_state_unscripted_play_matches_reference(ggl):
+    """160 reference steps of random play from the kickoff, then 60 compared steps of 64 arenas 2v2 (no scripts): the state
+    bench.py times."""
+    r = env_parity.run_steady_state(ggl, num_arenas=64, ppt=2, preroll=160, steps=60, seed=11)
+    print("steady state unscripted:", {k: (v.tolist() if hasattr(v, "tolist") else v) for k, v in r.items()})
+    assert r["mask_mismatch"] == 0 and r["term_mismatch"] == 0 and r["event_mismatch"] == 0, r
+    assert r["contact_overflow"] == 0 and r["rew"] <= 1e-4, r
+    assert r["bad_arena_steps"] <= 0.01 * r["arena_steps"], r
+
+
 def test_all_stock_rewards_match(ggl):
     A = ggl.abi
     rewards = [(k, 0.5 + 0.1 * k) for k in range(22) if k not in (A.REW_GOAL, A.REW_SAVE_BOOST, A.REW_STRONG_TOUCH, A.REW_VELOCITY)]
@@ -114,17 +144,20 @@ def test_mesh_and_car_contact_scenarios_per_tick(ggl, name):
     st = ref.get_state(0)
     ctl = scenarios.SCEN[name](st)
     ref.set_state(0, st); sim.set_state(st)
-    worst_pos, worst_vel, nbad = 0.0, 0.0, 0
+    worst_pos, worst_vel, nbad, worst_tick = 0.0, 0.0, 0, -1
     for t in range(200):
         sim.set_state(ref.get_state(0))
         w, bad = ls.run_lockstep(ref, sim, 1, 2, controls_fn=(lambda tt, s: ctl(t, s)) if ctl else None, stop_at=1e9, verbose=False)
-        worst_pos = max(worst_pos, max(v for k, v in w.items() if k.endswith(".pos")))
+        p = max(v for k, v in w.items() if k.endswith(".pos"))
+        if p > worst_pos:
+            worst_pos, worst_tick = p, t
         worst_vel = max(worst_vel, max(v for k, v in w.items() if k.endswith(".vel")))
         nbad += bad is not None
     print("per-tick error [%s]: pos %.5f uu, vel %.4f uu/s" % (name, worst_pos, worst_vel))
     assert nbad == 0, name
-    # 1e-3 uu per tick (north star); wall_hit's ceiling impact at tick 191 is the known 2.4e-3 outlier
-    assert worst_pos <= (3e-3 if name == "wall_hit" else 1e-3), (name, worst_pos)
+    # 1e-3 uu per tick (north star). One documented outlier: the tick in which wall_hit's car meets the
+    # ceiling at 1277 uu/s with one box corner (tick 191) ends 2.4e-3 uu / 0.29 uu/s (2e-4 of the velocity change) off
+    assert worst_pos <= 1e-3 or (name == "wall_hit" and worst_pos <= 3e-3 and worst_tick == 191), (name, worst_pos, worst_tick)
     ref.close(); sim.env.close()
 
 
