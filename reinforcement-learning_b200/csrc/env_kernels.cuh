@@ -45,7 +45,13 @@ struct EnvDevPtrs {
     int32_t* slotCarId; uint8_t* slotTeam; uint8_t* events; float* lastRewards;
     const float* actionTable;        // [90*8]
     WorldDev world;
+    // load balancing between the blocks of the step kernel: position (block, lane group) -> arena, rebuilt after every env step
+    // from the arenas' work estimates of that step (balance_kernel); null = identity
+    const int32_t* arenaOfPos;
+    uint32_t* stepCost;              // [numArenas] ArenaDev::stepCost of the last completed env step
 };
+
+__device__ __forceinline__ int arena_of(const EnvDevPtrs& P, int pos) { return P.arenaOfPos ? __ldg(P.arenaOfPos + pos) : pos; }
 
 __device__ __forceinline__ ExecGroup make_exec() {
     ExecGroup ex;
@@ -128,8 +134,9 @@ __global__ void __launch_bounds__(kBlock) env_reset_kernel(EnvCfg cfg, EnvDevPtr
 __global__ void __launch_bounds__(32 * kMaxWarps, 1) env_step_kernel(EnvCfg cfg, EnvDevPtrs P, const int32_t* __restrict__ actions, int doFirst,
                                                           int doSecond, int slotBytes) {
     GGL_PH_BEGIN();
-    const int arena = blockIdx.x * (blockDim.x / kGroup) + threadIdx.x / kGroup;
-    if (arena >= cfg.numArenas) return;          // whole groups leave: nobody waits for them at a group or block barrier
+    const int pos = blockIdx.x * (blockDim.x / kGroup) + threadIdx.x / kGroup;
+    if (pos >= cfg.numArenas) return;            // whole groups leave: nobody waits for them at a group or block barrier
+    const int arena = arena_of(P, pos);
     const ExecGroup ex = make_exec();
     stage_in(P, arena, ex, slotBytes, 0);
     {
@@ -179,11 +186,54 @@ __global__ void __launch_bounds__(32 * kMaxWarps, 1) env_step_kernel(EnvCfg cfg,
                 for (int e = 0; e < 9; e++) P.events[(size_t)row * 9 + e] = A.players[slot].events[e];
             }
             ex.sync();
-            if (ex.lane() == 0) env_end_step(A);
+            if (ex.lane() == 0) {
+                env_end_step(A);
+                if (P.stepCost) P.stepCost[arena] = A.stepCost;
+            }
             GGL_PH(12);
         }
     }
     stage_out(P, arena, ex, slotBytes, 0);
+}
+
+// Which arena sits where in the next launch. The step kernel's time is that of its slowest block, and a block pays, phase by
+// phase, for the slowest of its 28 arenas (block barriers); with arenas in index order the blocks of a 4096-arena 2v2 rollout
+// spread from 0.78 M to 2.26 M cycles per step around a mean of 1.49 M (profiles/r2g_phase_profile.txt), and heavy situations
+// (a pile-up, a car on the wall, the ball rolling along the floor) last many steps. So the arenas are dealt to the blocks by
+// the work estimate of the step that just ended: sorted by cost (counting sort on a log scale), then
+// dealt round by round across the blocks in snake order, every round landing in another warp of the block, so that each block
+// and each warp gets the same mix. One block; runs on the step's stream right after the step kernel.
+constexpr int kBalanceBuckets = 64;
+__global__ void __launch_bounds__(1024) balance_kernel(const uint32_t* __restrict__ cost, int32_t* __restrict__ arenaOfPos, int numArenas,
+                                                        int groupsPerBlock, int numBlocks, int32_t* __restrict__ order) {
+    __shared__ int s_cnt[kBalanceBuckets], s_start[kBalanceBuckets];
+    const int tid = threadIdx.x;
+    if (tid < kBalanceBuckets) s_cnt[tid] = 0;
+    __syncthreads();
+    auto bucket = [](uint32_t c) { return c == 0 ? kBalanceBuckets - 1 : max(0, kBalanceBuckets - 2 - (int)(4.f * __log2f((float)c))); };   // heavy first
+    for (int a = tid; a < numArenas; a += blockDim.x) atomicAdd(&s_cnt[bucket(cost[a])], 1);
+    __syncthreads();
+    if (tid == 0) { int run = 0; for (int b = 0; b < kBalanceBuckets; b++) { s_start[b] = run; run += s_cnt[b]; } }
+    __syncthreads();
+    // arenas of one bucket in whatever order the atomics hand out (which block an arena runs in does not change its results:
+    // tests/test_env_gpu.py::test_block_geometry_does_not_change_results)
+    for (int a = tid; a < numArenas; a += blockDim.x) order[atomicAdd(&s_start[bucket(cost[a])], 1)] = a;
+    __syncthreads();
+    // deal: rounds over the lane groups of a block; round r sits in lane group (r % W) * G + r / W (W warps per block, G groups
+    // per warp), visits the blocks in snake order, and skips the groups of the last block that lie past numArenas
+    const int G = 32 / kGroup, W = groupsPerBlock / G;
+    const int rem = numArenas - (numBlocks - 1) * groupsPerBlock;         // valid groups of the last block
+    for (int i = tid; i < numArenas; i += blockDim.x) {
+        int r = 0, cum = 0, group = 0, nb = numBlocks;
+        for (; r < groupsPerBlock; r++) {
+            group = W > 0 ? (r % W) * G + r / W : r;
+            nb = numBlocks - (group >= rem ? 1 : 0);
+            if (i < cum + nb) break;
+            cum += nb;
+        }
+        const int j = i - cum, k = (r & 1) ? nb - 1 - j : j;
+        arenaOfPos[k * groupsPerBlock + group] = order[i];
+    }
 }
 
 // raw Arena::Step(ticks)

@@ -7,6 +7,7 @@ namespace ggl {
 
 // ---- StepFirstHalf bookkeeping (EnvSet.cpp:115-123): prev snapshot + clear event flags
 GGL_HD void env_begin_step(ArenaDev& A) {
+    A.stepCost = 0;
     A.prevBallVel = A.ball.vel * kBT2UU;
     for (int s = 0; s < A.numCars; s++) {
         const CarDev& c = A.cars[A.slotCar[s]];

@@ -23,6 +23,8 @@ struct ggl_envset {
     ArenaDev* d_reset;
     float* d_table;
     int32_t* d_actionsScratch;
+    int32_t* d_arenaOfPos; int32_t* d_balanceOrder; uint32_t* d_stepCost;      // block load balancing (balance_kernel)
+    bool balance;
     // pinned staging for the host-buffer wrapper
     int32_t* h_actions; float* h_obs; uint8_t* h_masks; float* h_rewards; uint8_t* h_terminals;
     cudaStream_t ownStream, copyStream;
@@ -71,6 +73,7 @@ void free_env(ggl_envset* e) {
     cudaFree(e->P.arenas); cudaFree(e->d_reset); cudaFree(e->P.obs); cudaFree(e->P.masks); cudaFree(e->P.rewards);
     cudaFree(e->P.terminals); cudaFree(e->P.slotCarId); cudaFree(e->P.slotTeam); cudaFree(e->P.events); cudaFree(e->P.lastRewards);
     cudaFree(e->d_tris); cudaFree(e->d_cellStart); cudaFree(e->d_cellTris); cudaFree(e->d_table); cudaFree(e->d_actionsScratch);
+    cudaFree(e->d_arenaOfPos); cudaFree(e->d_balanceOrder); cudaFree(e->d_stepCost);
     if (e->h_actions) cudaFreeHost(e->h_actions);
     if (e->h_obs) cudaFreeHost(e->h_obs);
     if (e->h_masks) cudaFreeHost(e->h_masks);
@@ -109,6 +112,7 @@ extern "C" int ggl_envset_create(const ggl_envset_desc* d, ggl_envset** out) {
     if (!e) return GGL_ERR_NOMEM;
     memset(&e->cfg, 0, sizeof(e->cfg)); memset(&e->P, 0, sizeof(e->P));
     e->d_tris = nullptr; e->d_cellStart = e->d_cellTris = nullptr; e->d_reset = nullptr; e->d_table = nullptr; e->d_actionsScratch = nullptr;
+    e->d_arenaOfPos = e->d_balanceOrder = nullptr; e->d_stepCost = nullptr; e->balance = false;
     e->h_actions = nullptr; e->h_obs = nullptr; e->h_masks = nullptr; e->h_rewards = nullptr; e->h_terminals = nullptr; e->ownStream = nullptr; e->copyStream = nullptr; e->evReset = nullptr; e->evCopied = nullptr;
     e->device = d->device; e->seed = d->seed;
     EnvCfg& c = e->cfg;
@@ -186,6 +190,20 @@ extern "C" int ggl_envset_create(const ggl_envset_desc* d, ggl_envset** out) {
         int sms = 148;
         GGL_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, d->device));
         e->geom = launch_geom(e->cfg, sms);
+        // Load balancing between blocks only matters once a launch has several multi-warp blocks; GGL_BALANCE=0 turns it off
+        // (arenas then sit in index order, as in round 1).
+        const char* bal = getenv("GGL_BALANCE");
+        e->balance = e->geom.grid > 1 && !(bal && atoi(bal) == 0);
+        if (e->balance) {
+            int rc2;
+            if ((rc2 = dmalloc(&e->d_arenaOfPos, (size_t)e->cfg.numArenas)) || (rc2 = dmalloc(&e->d_balanceOrder, (size_t)e->cfg.numArenas)) ||
+                (rc2 = dmalloc(&e->d_stepCost, (size_t)e->cfg.numArenas))) { free_env(e); return rc2; }
+            std::vector<int32_t> ident(e->cfg.numArenas);
+            for (int i = 0; i < e->cfg.numArenas; i++) ident[i] = i;
+            cudaMemcpy(e->d_arenaOfPos, ident.data(), ident.size() * sizeof(int32_t), cudaMemcpyHostToDevice);
+            cudaMemset(e->d_stepCost, 0, (size_t)e->cfg.numArenas * sizeof(uint32_t));
+            e->P.arenaOfPos = e->d_arenaOfPos; e->P.stepCost = e->d_stepCost;
+        }
         // the attribute is per function, not per envset: always allow the largest block any envset may ask for
         GGL_CUDA(cudaFuncSetAttribute(env_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024));
         GGL_CUDA(cudaFuncSetAttribute(arena_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024));
@@ -209,6 +227,14 @@ extern "C" int ggl_envset_destroy(ggl_envset* e) {
 }
 
 #define ENV_CHECK(e) if (!(e)) { ggl::set_error("null envset"); return GGL_ERR_INVALID; }
+
+// new arena -> block assignment from the work estimates of the env step that was just launched (same stream, no host sync)
+static int rebalance(ggl_envset* e, cudaStream_t s) {
+    if (!e->balance) return GGL_OK;
+    balance_kernel<<<1, 1024, 0, s>>>(e->d_stepCost, e->d_arenaOfPos, e->cfg.numArenas, e->geom.warps * kArenasPerWarp, e->geom.grid, e->d_balanceOrder);
+    GGL_LAUNCH_CHECK(); ggl::count_launch();
+    return GGL_OK;
+}
 
 extern "C" int ggl_envset_reset(ggl_envset* e, void* stream) {
     ENV_CHECK(e);
@@ -234,14 +260,14 @@ extern "C" int ggl_envset_step_second_half(ggl_envset* e, const int32_t* d_actio
     if (!d_actions) { ggl::set_error("null actions"); return GGL_ERR_INVALID; }
     env_step_kernel<<<e->geom.grid, 32 * e->geom.warps, e->geom.smem, (cudaStream_t)stream>>>(e->cfg, e->P, d_actions, 0, 1, slot_bytes(e->cfg));
     GGL_LAUNCH_CHECK(); ggl::count_launch();
-    return GGL_OK;
+    return rebalance(e, (cudaStream_t)stream);
 }
 extern "C" int ggl_envset_step(ggl_envset* e, const int32_t* d_actions, void* stream) {
     ENV_CHECK(e);
     if (!d_actions) { ggl::set_error("null actions"); return GGL_ERR_INVALID; }
     env_step_kernel<<<e->geom.grid, 32 * e->geom.warps, e->geom.smem, (cudaStream_t)stream>>>(e->cfg, e->P, d_actions, 1, 1, slot_bytes(e->cfg));
     GGL_LAUNCH_CHECK(); ggl::count_launch();
-    return GGL_OK;
+    return rebalance(e, (cudaStream_t)stream);
 }
 extern "C" int ggl_arena_step(ggl_envset* e, int ticks, void* stream) {
     ENV_CHECK(e);

@@ -187,7 +187,8 @@ GGL_HD V3 car_box_pos(const CarDev& car) { return car.pos + mul(car.basis, car_h
 
 // Stage 1 (the car's lane): candidate triangles of car `ci`, de-duplicated and in (mesh, triangle) index order -- one
 // manifold per mesh body, visited in the reference's order.
-GGL_HDN void car_mesh_gather(ArenaDev& A, const WorldDev& W, int ci) {
+GGL_HDN void car_mesh_gather_cells(ArenaDev& A, const WorldDev& W, int ci, V3 mn, V3 mx);
+GGL_HD void car_mesh_gather(ArenaDev& A, const WorldDev& W, int ci) {
     A.meshCandN[ci] = 0; A.meshHitN[ci] = 0; A.meshHitOverflow[ci] = 0;
     if (W.numTris <= 0 || A.cars[ci].rbDisabled) return;
     const CarDev& car = A.cars[ci];
@@ -195,6 +196,10 @@ GGL_HDN void car_mesh_gather(ArenaDev& A, const WorldDev& W, int ci) {
     V3 boxPos = car_box_pos(car);
     V3 ext = v3(dot(vabs(car.basis.r0), bg.full), dot(vabs(car.basis.r1), bg.full), dot(vabs(car.basis.r2), bg.full));
     V3 mn = boxPos - ext, mx = boxPos + ext;
+    if (world_aabb_is_free(W, mn, mx)) return;          // open play: every grid cell the box touches is empty
+    car_mesh_gather_cells(A, W, ci, mn, mx);
+}
+GGL_HDN void car_mesh_gather_cells(ArenaDev& A, const WorldDev& W, int ci, V3 mn, V3 mx) {
     int x0 = grid_coord(mn.x, W.gridMin.x, W.invCellSize, W.gx), x1 = grid_coord(mx.x, W.gridMin.x, W.invCellSize, W.gx);
     int y0 = grid_coord(mn.y, W.gridMin.y, W.invCellSize, W.gy), y1 = grid_coord(mx.y, W.gridMin.y, W.invCellSize, W.gy);
     int z0 = grid_coord(mn.z, W.gridMin.z, W.invCellSize, W.gz), z1 = grid_coord(mx.z, W.gridMin.z, W.invCellSize, W.gz);

@@ -372,8 +372,9 @@ GGL_HD void ray_cast_world(const ArenaDev& A, const WorldDev& W, int selfCar, V3
     ray_vs_plane(from - v3(-ex, 0, hz / 2), to - v3(-ex, 0, hz / 2), v3(1, 0, 0), 0.f, h);
     ray_vs_plane(from - v3(ex, 0, hz / 2), to - v3(ex, 0, hz / 2), v3(-1, 0, 0), 0.f, h);
     // mesh triangles through the uniform grid
-    if (W.numTris > 0) {
-        V3 mn = vmin(from, to), mx = vmax(from, to);
+    V3 rmn = vmin(from, to), rmx = vmax(from, to);
+    if (W.numTris > 0 && !world_aabb_is_free(W, rmn, rmx)) {
+        V3 mn = rmn, mx = rmx;
         int x0 = grid_coord(mn.x, W.gridMin.x, W.invCellSize, W.gx), x1 = grid_coord(mx.x, W.gridMin.x, W.invCellSize, W.gx);
         int y0 = grid_coord(mn.y, W.gridMin.y, W.invCellSize, W.gy), y1 = grid_coord(mx.y, W.gridMin.y, W.invCellSize, W.gy);
         int z0 = grid_coord(mn.z, W.gridMin.z, W.invCellSize, W.gz), z1 = grid_coord(mx.z, W.gridMin.z, W.invCellSize, W.gz);

@@ -138,6 +138,7 @@ struct WorldHost {
     int gx = 1, gy = 1, gz = 1;
     V3 gridMin = v3(0, 0, 0);
     float cellSize = 1.f;
+    V3 freeMin = v3(0, 0, 0), freeMax = v3(0, 0, 0);      // empty-cell box (WorldDev::freeMin / freeMax); empty itself when there is none
 };
 
 // .cmf layout (CollisionMeshFile.cpp:11-35): int32 numTris, int32 numVerts, int32 tri[numTris][3], float vert[numVerts][3]
@@ -329,6 +330,8 @@ inline void world_sort_bvh_order(WorldHost& W) {
     }
 }
 
+inline void world_find_free_box(WorldHost& W);
+
 // Uniform grid (cell = 5 bt = 250 uu) over the triangles; a triangle is listed in every cell its AABB (+0.1) touches.
 inline void world_build_grid(WorldHost& W) {
     world_build_edge_info(W);
@@ -359,6 +362,38 @@ inline void world_build_grid(WorldHost& W) {
         W.cellTris.insert(W.cellTris.end(), cells[c].begin(), cells[c].end());
     }
     W.cellStart[nc] = (int)W.cellTris.size();
+    world_find_free_box(W);
+}
+
+// Largest box of empty grid cells grown greedily from the cell above the centre spot (face by face, as long as the new slab of
+// cells is empty). Grid cells list every triangle whose AABB (+0.1) touches them, so nothing inside the box is near a triangle.
+inline void world_find_free_box(WorldHost& W) {
+    auto empty = [&](int x, int y, int z) { const int c = (z * W.gy + y) * W.gx + x; return W.cellStart[c] == W.cellStart[c + 1]; };
+    const float inv = 1.f / W.cellSize;
+    int lo[3] = {grid_coord(0.f, W.gridMin.x, inv, W.gx), grid_coord(0.f, W.gridMin.y, inv, W.gy), grid_coord(20.f, W.gridMin.z, inv, W.gz)};
+    int hi[3] = {lo[0], lo[1], lo[2]};
+    W.freeMin = W.freeMax = v3(0, 0, 0);
+    if (W.tris.empty() || !empty(lo[0], lo[1], lo[2])) return;
+    const int dim[3] = {W.gx, W.gy, W.gz};
+    bool grew = true;
+    while (grew) {
+        grew = false;
+        for (int face = 0; face < 6; face++) {
+            const int ax = face >> 1, up = face & 1;
+            const int layer = up ? hi[ax] + 1 : lo[ax] - 1;
+            if (layer < 0 || layer >= dim[ax]) continue;
+            bool ok = true;
+            int a[3];
+            for (a[0] = (ax == 0 ? layer : lo[0]); ok && a[0] <= (ax == 0 ? layer : hi[0]); a[0]++)
+                for (a[1] = (ax == 1 ? layer : lo[1]); ok && a[1] <= (ax == 1 ? layer : hi[1]); a[1]++)
+                    for (a[2] = (ax == 2 ? layer : lo[2]); ok && a[2] <= (ax == 2 ? layer : hi[2]); a[2]++) ok = empty(a[0], a[1], a[2]);
+            if (ok) { if (up) hi[ax] = layer; else lo[ax] = layer; grew = true; }
+        }
+    }
+    // grid_coord clamps: a coordinate outside the grid maps to the border cell, so the box may only be open-ended where the
+    // border cells themselves are empty (they are part of the box then); keep it finite and simple: cell bounds as they are
+    W.freeMin = v3(W.gridMin.x + lo[0] * W.cellSize, W.gridMin.y + lo[1] * W.cellSize, W.gridMin.z + lo[2] * W.cellSize);
+    W.freeMax = v3(W.gridMin.x + (hi[0] + 1) * W.cellSize, W.gridMin.y + (hi[1] + 1) * W.cellSize, W.gridMin.z + (hi[2] + 1) * W.cellSize);
 }
 
 inline WorldDev world_view(const WorldHost& W) {
@@ -366,6 +401,7 @@ inline WorldDev world_view(const WorldHost& W) {
     d.tris = W.tris.data(); d.numTris = (int)W.tris.size();
     d.cellStart = W.cellStart.data(); d.cellTris = W.cellTris.data();
     d.gx = W.gx; d.gy = W.gy; d.gz = W.gz; d.gridMin = W.gridMin; d.cellSize = W.cellSize; d.invCellSize = 1.f / W.cellSize;
+    d.freeMin = W.freeMin; d.freeMax = W.freeMax;
     return d;
 }
 

@@ -57,37 +57,60 @@ GGL_HD void car_aabb(const CarDev& c, V3& mn, V3& mx) {
     mn = centre - ext; mx = centre + ext;
 }
 
-// BoostPad::_CheckCollide (Sim/BoostPad/BoostPad.cpp:62-86) reached through BoostPadGrid::CheckCollision
-// (BoostPadGrid.cpp:5-25: 8 x 10 grid of 1024 uu cells, 3x3 neighbourhood of the car's cell), turned inside out: one pad
-// against every car in players[] slot order (the reference iterates its car set; a later car overwrites the lock), so that
-// pads can be spread over the lanes of the group.
-GGL_HD void pad_check_cars(ArenaDev& A, int p) {
-    const V3 pp = pad_pos_uu(p);
-    const int px = (int)(pp.x / 1024 + 4), py = (int)(pp.y / 1024 + 5);
-    const bool big = p < 6;
-    const V3 pbt = pp * kUU2BT;
-    PadDev& pd = A.pads[p];
-    for (int s = 0; s < A.numCars; s++) {
-        const CarDev& car = A.cars[A.slotCar[s]];
-        if (car.isDemoed || car.boost >= 100.f) continue;
-        V3 posUU = car.pos * kBT2UU;
-        if (posUU.z > rl::PAD_CYL_HEIGHT + 250.f) continue;
-        int ix = (int)(posUU.x / 1024 + 4), iy = (int)(posUU.y / 1024 + 5);
-        int lx0 = ix - 1 < 0 ? 0 : ix - 1, lx1 = ix + 1 > 7 ? 7 : ix + 1, ly0 = iy - 1 < 0 ? 0 : iy - 1, ly1 = iy + 1 > 9 ? 9 : iy + 1;
-        if (px < lx0 || px > lx1 || py < ly0 || py > ly1) continue;
-        bool colliding = false;
-        if (pd.prevLockedCarId == car.id) {
-            V3 amin, amax;
-            car_aabb(car, amin, amax);
-            float boxRad = (big ? rl::PAD_BOX_RAD_BIG : rl::PAD_BOX_RAD_SMALL) * kUU2BT;
-            V3 bmin = pbt - v3(boxRad, boxRad, 0), bmax = pbt + v3(boxRad, boxRad, rl::PAD_BOX_HEIGHT * kUU2BT);
-            colliding = (bmax.x > amin.x && bmax.y > amin.y && bmax.z > amin.z) && (bmin.x < amax.x && bmin.y < amax.y && bmin.z < amax.z);
-        } else {
-            float rad = (big ? rl::PAD_CYL_RAD_BIG : rl::PAD_CYL_RAD_SMALL) * kUU2BT;
-            float dx = car.pos.x - pbt.x, dy = car.pos.y - pbt.y;
-            if (dx * dx + dy * dy < rad * rad) colliding = fabsf(car.pos.z - pbt.z) < (rl::PAD_CYL_HEIGHT * kUU2BT);
+// BoostPadGrid: 8 x 10 cells of 1024 uu, at most one pad per cell (BoostPadGrid.cpp:27-38 on the pad table above): pad index
+// of cell (x, y) or -1
+GGL_TABLE signed char kCellPad[8][10] = {
+    {-1, -1, 12, -1, -1, 0, -1, 26, -1, -1}, {-1, 4, -1, -1, -1, -1, -1, -1, -1, 2}, {7, -1, 14, 16, -1, -1, 21, 24, -1, 31},
+    {-1, 9, -1, -1, -1, 19, -1, -1, 29, -1}, {6, 10, 11, -1, 17, -1, 22, 28, 30, 33}, {8, -1, 15, -1, -1, 20, -1, 25, -1, 32},
+    {-1, -1, -1, 18, -1, -1, 23, -1, -1, -1}, {-1, 5, 13, -1, -1, 1, -1, 27, -1, 3}};
+GGL_HD int cell_pad(int x, int y) {
+#if defined(__CUDACC__) && !defined(__CUDA_ARCH__)
+    (void)x; (void)y; return -1;          // host pass of nvcc (see pad_pos_uu)
+#else
+    return kCellPad[x][y];
+#endif
+}
+
+// BoostPadGrid::CheckCollision (BoostPadGrid.cpp:5-25) for one car: the pads of the 3 x 3 cells around the car, each through
+// BoostPad::_CheckCollide (Sim/BoostPad/BoostPad.cpp:62-86). A car can be inside at most one pad (cylinders of radius <= 208 uu
+// and lock boxes of half width <= 160 uu around pads that are >= 1000 uu apart), so the result is ONE pad index per car
+// (A.padHit); the locks themselves are written afterwards in players[] slot order, because the reference visits its cars one
+// after the other and a later car overwrites the lock of an earlier one (pads_apply_locks).
+GGL_HD void car_check_pads(ArenaDev& A, int ci) {
+    const CarDev& car = A.cars[ci];
+    A.padHit[ci] = -1;
+    if (car.isDemoed || car.boost >= 100.f) return;
+    const V3 posUU = car.pos * kBT2UU;
+    if (posUU.z > rl::PAD_CYL_HEIGHT + 250.f) return;
+    const int ix = (int)(posUU.x / 1024 + 4), iy = (int)(posUU.y / 1024 + 5);
+    const int lx0 = ix - 1 < 0 ? 0 : ix - 1, lx1 = ix + 1 > 7 ? 7 : ix + 1, ly0 = iy - 1 < 0 ? 0 : iy - 1, ly1 = iy + 1 > 9 ? 9 : iy + 1;
+    for (int i = lx0; i <= lx1; i++)
+        for (int j = ly0; j <= ly1; j++) {
+            const int p = cell_pad(i, j);
+            if (p < 0) continue;
+            const V3 pp = pad_pos_uu(p);
+            const bool big = p < 6;
+            const V3 pbt = pp * kUU2BT;
+            const PadDev& pd = A.pads[p];
+            bool colliding = false;
+            if (pd.prevLockedCarId == car.id) {
+                V3 amin, amax;
+                car_aabb(car, amin, amax);
+                const float boxRad = (big ? rl::PAD_BOX_RAD_BIG : rl::PAD_BOX_RAD_SMALL) * kUU2BT;
+                const V3 bmin = pbt - v3(boxRad, boxRad, 0), bmax = pbt + v3(boxRad, boxRad, rl::PAD_BOX_HEIGHT * kUU2BT);
+                colliding = (bmax.x > amin.x && bmax.y > amin.y && bmax.z > amin.z) && (bmin.x < amax.x && bmin.y < amax.y && bmin.z < amax.z);
+            } else {
+                const float rad = (big ? rl::PAD_CYL_RAD_BIG : rl::PAD_CYL_RAD_SMALL) * kUU2BT;
+                const float dx = car.pos.x - pbt.x, dy = car.pos.y - pbt.y;
+                if (dx * dx + dy * dy < rad * rad) colliding = fabsf(car.pos.z - pbt.z) < (rl::PAD_CYL_HEIGHT * kUU2BT);
+            }
+            if (colliding) A.padHit[ci] = (int8_t)p;
         }
-        if (colliding) pd.curLockedCarId = (uint8_t)car.id;
+}
+GGL_HD void pads_apply_locks(ArenaDev& A) {
+    for (int s = 0; s < A.numCars; s++) {
+        const int c = A.slotCar[s];
+        if (A.padHit[c] >= 0) A.pads[A.padHit[c]].curLockedCarId = (uint8_t)A.cars[c].id;
     }
 }
 
@@ -131,23 +154,24 @@ GGL_HD void world_integrate(ArenaDev& A, int b) {
     }
 }
 
-GGL_HD void phase_finish(ArenaDev& A) {
-    // pads post-tick (the per-pad collision checks ran lane-parallel just before)
-    if (A.numCars > 0)
-        for (int p = 0; p < kNumPads; p++) {
-            PadDev& pd = A.pads[p];
-            uint32_t locked = 0;
-            if (pd.curLockedCarId) {
-                locked = pd.curLockedCarId;
-                if (pd.isActive) {
-                    CarDev& c = A.cars[locked - 1];
-                    c.boost = fminf(c.boost + (p < 6 ? rl::PAD_BOOST_BIG : rl::PAD_BOOST_SMALL), rl::BOOST_MAX);
-                    pd.isActive = 0;
-                    pd.cooldown = p < 6 ? rl::PAD_COOLDOWN_BIG : rl::PAD_COOLDOWN_SMALL;
-                }
-            }
-            pd.prevLockedCarId = (uint8_t)locked;
+// BoostPad::_PostTickUpdate (BoostPad.cpp:88-105) of one pad. Pads are independent here: a car locks at most one pad per tick
+// (car_check_pads), so two pads never feed the same car.
+GGL_HD void pad_post_tick(ArenaDev& A, int p) {
+    PadDev& pd = A.pads[p];
+    uint32_t locked = 0;
+    if (pd.curLockedCarId) {
+        locked = pd.curLockedCarId;
+        if (pd.isActive) {
+            CarDev& c = A.cars[locked - 1];
+            c.boost = fminf(c.boost + (p < 6 ? rl::PAD_BOOST_BIG : rl::PAD_BOOST_SMALL), rl::BOOST_MAX);
+            pd.isActive = 0;
+            pd.cooldown = p < 6 ? rl::PAD_COOLDOWN_BIG : rl::PAD_COOLDOWN_SMALL;
         }
+    }
+    pd.prevLockedCarId = (uint8_t)locked;
+}
+
+GGL_HD void phase_finish(ArenaDev& A) {
     // Ball::_FinishPhysicsTick
     BallDev& b = A.ball;
     if (!is_zero(b.velImpulseCache)) { b.vel += b.velImpulseCache; b.velImpulseCache = v3(0, 0, 0); }
@@ -165,6 +189,7 @@ GGL_HD void arena_tick(ArenaDev& A, const WorldDev& W, const Exec& ex) {
         A.ball.active = (len2(A.ball.vel) == 0.f && len2(A.ball.angVel) == 0.f) ? 0u : 1u;
         A.wheelDefer = 0;
         A.poolCount = 0;
+        for (int j = 0; j < kMaxPool / 4; j++) reinterpret_cast<uint32_t*>(A.poolOwner)[j] = 0xFFFFFFFFu;   // unclaimed (ContactSink::at)
     }
     for (int c = ex.lane(); c < A.numCars; c += ex.lanes()) { A.cars[c].velSnap = A.cars[c].vel; A.cars[c].angVelSnap = A.cars[c].angVel; }
     if (A.numCars > 0)
@@ -220,7 +245,20 @@ GGL_HD void arena_tick(ArenaDev& A, const WorldDev& W, const Exec& ex) {
     ex.sync();
     if (GGL_PSYNC_MASK & 32) ex.phase_sync();
     GGL_PH(5);
-    if (ex.lane() == 0) gather_contacts(A);
+    if (ex.lane() == 0) {
+        int any = A.cntWorld;
+        for (int c = 0; c < A.numCars; c++) any += A.cntBall[c] + A.cntRest[c];
+        // work estimate of this tick for the launch geometry of the NEXT env step (env_kernels.cuh: arena_of): contact rows
+        // (narrow phase + 10 solver iterations each), triangle candidates (a GJK/EPA each), wheels on something
+        int cost = 4 * any;
+        for (int c = 0; c < A.numCars; c++) cost += 6 * A.meshCandN[c] + A.cars[c].isOnGround;
+        A.stepCost += (uint32_t)cost;
+        if (any) gather_contacts(A);
+        else {      // nothing touched anything this tick (88 % of the arena-ticks of the benchmark's rollout)
+            A.numContacts = 0; A.bodiesInContact = 0; A.ballAwake = A.ball.active ? 1 : 0;
+            for (int b = 0; b < 8; b++) A.island[b] = (uint8_t)b;
+        }
+    }
     ex.sync();
     if (GGL_PSYNC_MASK & 64) ex.phase_sync();
     GGL_PH(6);
@@ -240,8 +278,12 @@ GGL_HD void arena_tick(ArenaDev& A, const WorldDev& W, const Exec& ex) {
     ex.sync();
     if (GGL_PSYNC_MASK & 512) ex.phase_sync();
     GGL_PH(9);
-    for (int p = ex.lane(); p < kNumPads; p += ex.lanes()) pad_check_cars(A, p);
+    for (int c = ex.lane(); c < A.numCars; c += ex.lanes()) car_check_pads(A, c);
     ex.sync();
+    if (ex.lane() == 0) pads_apply_locks(A);
+    ex.sync();
+    if (A.numCars > 0)
+        for (int p = ex.lane(); p < kNumPads; p += ex.lanes()) pad_post_tick(A, p);
     if (GGL_PSYNC_MASK & 1024) ex.phase_sync();
     GGL_PH(10);
     if (ex.lane() == 0) phase_finish(A);

@@ -150,7 +150,8 @@ struct CarTriHit { V3 normalOnB, pointOnB; float distance; uint32_t cand; };
 
 struct alignas(16) ArenaDev {
     uint64_t tickCount;
-    int32_t numCars, _pad0;
+    int32_t numCars;
+    uint32_t stepCost;                             // work estimate of the current env step (rows, triangle candidates ...), see env_kernels.cuh
     BallDev ball;
     PadDev pads[kNumPads];
     // GameEventTracker (Sim/GameEventTracker/GameEventTracker.h:78-86)
@@ -176,8 +177,9 @@ struct alignas(16) ArenaDev {
     uint32_t contactOverflow;                      // STICKY: contact points dropped since create because windows and pool were full
     alignas(16) Contact contacts[kMaxContacts];    // from here to cars[]: per-tick scratch that never needs to travel to HBM
     uint8_t contactOrder[kMaxContacts];           // solver row k = contacts[contactOrder[k]], k < numContacts (gather_contacts)
-    uint8_t poolOwner[kMaxPool];                   // who claimed overflow-pool slot j (POOL_* codes, sim_world.cuh)
+    alignas(4) uint8_t poolOwner[kMaxPool];        // who claimed overflow-pool slot j (POOL_* codes, sim_world.cuh)
     uint32_t poolCount;                            // overflow-pool slots claimed this tick (atomic: the bodies' lanes race for them)
+    int8_t padHit[8];                              // per tick: the boost pad car c collides with (-1 = none), see car_check_pads
     // car-vs-mesh staging: candidates per car (gathered by the car's lane), hits found by all lanes of the group
     uint16_t meshCand[kMaxCars][kMaxMeshCand];
     uint8_t meshCandN[kMaxCars], meshHitOverflow[kMaxCars];
@@ -209,6 +211,12 @@ struct WorldDev {
     int gx, gy, gz;
     V3 gridMin;
     float cellSize, invCellSize;
+    // a box of EMPTY grid cells around the middle of the arena (sim_convert.cuh: world_find_free_box): an AABB inside it touches
+    // no triangle, so cars, ball and suspension rays in open play skip the grid walk (and its global loads) altogether
+    V3 freeMin, freeMax;
 };
+GGL_HD bool world_aabb_is_free(const WorldDev& W, V3 mn, V3 mx) {
+    return mn.x > W.freeMin.x && mn.y > W.freeMin.y && mn.z > W.freeMin.z && mx.x < W.freeMax.x && mx.y < W.freeMax.y && mx.z < W.freeMax.z;
+}
 
 }  // namespace ggl

@@ -33,6 +33,11 @@ int hostsim_tri(void* p, int i, float* out9) {
     out9[6] = t.v2.x; out9[7] = t.v2.y; out9[8] = t.v2.z;
     return (int)(t.flags >> TRI_MESH_SHIFT);
 }
+// the empty-cell box of the world (Bullet units): out6 = min xyz, max xyz
+void hostsim_free_box(void* p, float* out6) {
+    const WorldHost& W = ((HostSim*)p)->world;
+    out6[0] = W.freeMin.x; out6[1] = W.freeMin.y; out6[2] = W.freeMin.z; out6[3] = W.freeMax.x; out6[4] = W.freeMax.y; out6[5] = W.freeMax.z;
+}
 int hostsim_num_tris(void* p) { return (int)((HostSim*)p)->world.tris.size(); }
 
 void hostsim_set_state(void* p, const ggl_arena_state* st) {

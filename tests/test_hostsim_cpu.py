@@ -158,3 +158,25 @@ def test_mesh_triangles_are_stored_in_reference_bvh_leaf_order():
         base += nt
     assert base == H.hostsim_num_tris(sim.h)
     assert multi > 0      # at least one mesh whose BVH order is not the file order, so the check means something
+
+
+def test_free_box_of_the_world_touches_no_triangle():
+    """Cars, ball and suspension rays whose AABB lies inside the world's empty-cell box skip the triangle grid (WorldDev::freeMin /
+    freeMax): no triangle's AABB, grown by the 0.1 the grid registers it with, may reach into that box, and the box is not trivial."""
+    import ctypes as C
+    import numpy as np
+    sim = hb.HostSim()
+    H = hb.lib()
+    H.hostsim_free_box.argtypes = [C.c_void_p, C.c_void_p]
+    H.hostsim_tri.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+    H.hostsim_num_tris.argtypes = [C.c_void_p]
+    box = np.zeros(6, np.float32)
+    H.hostsim_free_box(sim.h, box.ctypes.data)
+    lo, hi = box[:3], box[3:]
+    assert (hi - lo > np.array([100.0, 100.0, 30.0])).all(), box          # > 5000 x 5000 x 1500 uu of open field
+    out = np.zeros(9, np.float32)
+    for i in range(H.hostsim_num_tris(sim.h)):
+        H.hostsim_tri(sim.h, i, out.ctypes.data)
+        v = out.reshape(3, 3)
+        mn, mx = v.min(0) - 0.1, v.max(0) + 0.1
+        assert not ((mx > lo).all() and (mn < hi).all()), (i, v, box)
