@@ -197,6 +197,7 @@ def bench_env(args, rank, world, local):
     t_wall = time.perf_counter() - t_wall0
     launches = ggl.launch_count() - l0
     clocks = sampler.stop() if rank == 0 else None
+    overflow = env.contact_overflow()          # contact rows exhausted anywhere since create (must be 0: same rows as the reference)
     dev_ms = sum(a.elapsed_time(b) for a, b in evs)
     kern_ms = sum(a.elapsed_time(b) for a, b in kev) / args.steps
     dev_ms = max_over_ranks(dev_ms, world)
@@ -245,7 +246,9 @@ def bench_env(args, rank, world, local):
                                "device random mask-valid actions (BASELINE.json configs[1])" % ARENAS_PER_GPU,
                    "arenas_per_gpu": ARENAS_PER_GPU, "agents_per_gpu": env.num_players, "l2": "flushed between steps (256 MiB write)",
                    "preroll_steps": PREROLL_STEPS,
-                   "arena_mesh": "synthetic soccar (real .cmf meshes are not redistributable)"},
+                   "arena_mesh": "synthetic soccar (real .cmf meshes are not redistributable)",
+                   "block_balancing": os.environ.get("GGL_BALANCE", "1") != "0",
+                   "contact_points_dropped": int(overflow)},
         "e2e": {"value": e2e_val, "unit": "agent-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "steps": e2e_steps, "api": "ggl_envset_begin_step_host + host action pick + ggl_envset_finish_step_host (pinned host buffers)"},
         "gpu_launches": int(launches),

@@ -41,13 +41,6 @@ constexpr int GAE_ITEMS = GAE_CFG_ITEMS;                // multiple of 16 (termi
 constexpr int GAE_TILE = GAE_THREADS * GAE_ITEMS;       // 4096 elements
 constexpr int GAE_PAD = GAE_TILE / 32;
 constexpr int GAE_WARPS = GAE_THREADS / 32;
-// Early carry-out publication by warp 0 (below): measured on B200 at L = 2^24 (profiles/r2f_gae_early_*): the wait on the carry
-// drops from 19 % to 5 % of the stall samples, but the seven other warps now wait for warp 0 at the tile's first barrier
-// (barrier stalls 26 % -> 39 %) and the call gets SLOWER, 0.118 -> 0.129 ms. Off by default; -DGAE_CFG_EARLY=512 enables it.
-#ifndef GAE_CFG_EARLY
-#define GAE_CFG_EARLY 0
-#endif
-constexpr int GAE_EARLY = GAE_CFG_EARLY;                // lowest elements of a tile warp 0 looks at for the early carry-out (0 or 512)
 
 struct Lin2 {            // x_adv' = Aa*x_adv + Ba ; x_ret' = Ar*x_ret + Br
     float Aa, Ba, Ar, Br;
@@ -336,88 +329,6 @@ __global__ void __launch_bounds__(GAE_THREADS, GAE_CFG_MINBLOCKS) gae_scan_kerne
         unsigned int next_ticket = 0;
         if (tid == 0) next_ticket = atomicAdd(&p.hdr->tile_ticket, 1u);
 
-        // ---- early carry-out (warp 0) ----
-        // What this tile hands to the next one in scan order is the (advantage, return) pair at its LOWEST element. If a
-        // terminal lies within the lowest GAE_EARLY elements, that pair does not depend on anything above the terminal: warp 0
-        // computes it from those elements alone and publishes the tile's INCLUSIVE record now, a few hundred nanoseconds into
-        // the tile instead of after the loads, the transposition and the block scan. The successor's look-back then finds
-        // the record long before it asks for it (ncu r1k: 26 % of the stall samples sat at the barrier behind that wait and
-        // 19 % on the first use of the carry). Tiles without a terminal that low publish after their block scan, as before.
-        bool early = false;
-        if (GAE_EARLY > 0 && warp == 0 && base + GAE_EARLY < p.L) {
-            const long long e0g = base + (long long)lane * 16;
-            const uint4 tw = __ldcs(reinterpret_cast<const uint4*>(p.terms + e0g));
-            float er[16], ev[16];
-#pragma unroll
-            for (int c = 0; c < 4; c++) {
-                const float4 a = __ldcs(reinterpret_cast<const float4*>(p.rews + e0g + 4 * c));
-                const float4 b = __ldcs(reinterpret_cast<const float4*>(p.vals + e0g + 4 * c));
-                er[4 * c] = a.x; er[4 * c + 1] = a.y; er[4 * c + 2] = a.z; er[4 * c + 3] = a.w;
-                ev[4 * c] = b.x; ev[4 * c + 1] = b.y; ev[4 * c + 2] = b.z; ev[4 * c + 3] = b.w;
-            }
-            const unsigned int ew[4] = {tw.x, tw.y, tw.z, tw.w};
-            int running = 0;
-            if (HAS_TRUNC) {
-                // TRUNCATED entries above this lane's span: the tiles before in scan order (pre-pass), the part of this tile
-                // above the early segment, and the lanes above in the segment
-                int c_up = 0;
-                for (int k = lane; k < (GAE_TILE - GAE_EARLY) / 16; k += 32) {
-                    const long long gi = base + GAE_EARLY + (long long)k * 16;
-                    if (gi + 15 < p.L) {
-                        const uint4 w = __ldcs(reinterpret_cast<const uint4*>(p.terms + gi));
-                        c_up += count_twos(w.x) + count_twos(w.y) + count_twos(w.z) + count_twos(w.w);
-                    } else {
-                        for (int e = 0; e < 16; e++)
-                            if (gi + e < p.L) c_up += p.terms[gi + e] == 2;
-                    }
-                }
-                c_up = __reduce_add_sync(0xffffffffu, c_up);
-                const int c_loc = count_twos(ew[0]) + count_twos(ew[1]) + count_twos(ew[2]) + count_twos(ew[3]);
-                int c = c_loc;
-#pragma unroll
-                for (int off = 1; off < 32; off <<= 1) {
-                    const int o = __shfl_down_sync(0xffffffffu, c, off);
-                    if (lane + off < 32) c += o;
-                }
-                running = (int)__ldg(&p.cnt_in[t]) + c_up + (c - c_loc);
-            }
-            float vnext = __shfl_down_sync(0xffffffffu, ev[0], 1);
-            if (lane == 31) vnext = p.vals[base + GAE_EARLY];
-            Lin2 loc = lin_identity();
-#pragma unroll
-            for (int j = 15; j >= 0; j--) {
-                const unsigned int term = (ew[j >> 2] >> (8 * (j & 3))) & 0xffu;
-                const float r = er[j], v = ev[j];
-                float rn = r;
-                if (NORM) {
-                    rn = r * p.inv_std;
-                    if (CLIP) rn = fminf(fmaxf(rn, -p.clip), p.clip);
-                }
-                float next_v = vnext;
-                if (term == 1u) next_v = 0.f;
-                if (HAS_TRUNC && term == 2u) {
-                    running++;
-                    const long long tidx = p.K - running;
-                    next_v = (tidx >= 0 && tidx < p.K) ? __ldg(p.trunc_vals + tidx) : 0.f;
-                }
-                const float nd = (term == 0u) ? 1.f : 0.f;
-                Lin2 e;
-                e.Aa = gl * nd; e.Ba = (rn + g * next_v) - v; e.Ar = g * nd; e.Br = r;
-                loc = compose(e, loc);
-                vnext = v;
-            }
-#pragma unroll
-            for (int off = 1; off < 32; off <<= 1) {
-                const Lin2 o = shfl_down_lin(loc, off);
-                if (lane + off < 32) loc = compose(loc, o);
-            }
-            const bool ok = __shfl_sync(0xffffffffu, (loc.Aa == 0.f && loc.Ar == 0.f) ? 1 : 0, 0) != 0;
-            if (ok) {
-                if (lane == 0) st_volatile_rec(&p.val_rec[t], enc_inc(loc.Ba, loc.Br));
-                early = true;
-            }
-        }
-
         // terminals first (1 B/element): the integer chain below only needs them, and resolves while the 8 B/element of
         // rewards and values are still in flight. Every thread owns GAE_ITEMS consecutive elements; the HIGHEST thread id comes first in scan order
         unsigned int tword[GAE_ITEMS / 4];
@@ -554,19 +465,31 @@ __global__ void __launch_bounds__(GAE_THREADS, GAE_CFG_MINBLOCKS) gae_scan_kerne
         // A tile that contains a terminal has multiplier 0 in both recurrences: what it hands on does not depend on its own
         // carry-in, so it publishes its INCLUSIVE record at once and later tiles stop their look-back right there (with
         // episodes shorter than a tile -- the usual PPO stream -- every look-back is one window deep).
-        // Warp 0 resolves the carry while the OTHER warps already replay the recurrence with a zero carry-in: a thread whose
-        // span lies behind a terminal of this tile (thread_in multipliers 0 -- all but the first few threads in scan order when
-        // episodes are shorter than the tile) gets its final values that way, and the few threads in front of the first terminal
-        // add carry x (running multiplier) afterwards. The look-back wait (ncu r1k: 26 % of the stall samples at the barrier
-        // behind it + 19 % on the first use of the carry) now overlaps seven eighths of pass 2.
-        const bool closed = (tile_agg.Aa == 0.f && tile_agg.Ar == 0.f);
-        if (warp == 0 && lane == 0 && t > 0 && !early)
-            st_volatile_rec(&p.val_rec[t], closed ? enc_inc(tile_agg.Ba, tile_agg.Br) : enc_agg(tile_agg));
+        if (warp == 0) {
+            float adv_in = 0.f, ret_in = 0.f;
+            const bool closed = (tile_agg.Aa == 0.f && tile_agg.Ar == 0.f);
+            if (t > 0) {
+                if (lane == 0) st_volatile_rec(&p.val_rec[t], closed ? enc_inc(tile_agg.Ba, tile_agg.Br) : enc_agg(tile_agg));
+#ifndef GAE_DBG_NOCHAIN2
+                lookback_vals(p.val_rec, t, lane, adv_in, ret_in);
+#endif
+            }
+            if (lane == 0) {
+                if (!closed || t == 0) {
+                    const float adv_out = tile_agg.Aa * adv_in + tile_agg.Ba;
+                    const float ret_out = tile_agg.Ar * ret_in + tile_agg.Br;
+                    st_volatile_rec(&p.val_rec[t], enc_inc(adv_out, ret_out));
+                }
+                s_x_in[0] = adv_in;
+                s_x_in[1] = ret_in;
+            }
+        }
+        __syncthreads();
 
-        // ---- per-thread pass 2 with a zero carry-in: replay the recurrence, stage outputs ----
+        // ---- per-thread pass 2: replay the recurrence with the exact carry-in, stage outputs ----
         {
-            float x_adv = thread_in.Ba;
-            float x_ret = thread_in.Br;
+            float x_adv = thread_in.Aa * s_x_in[0] + thread_in.Ba;
+            float x_ret = thread_in.Ar * s_x_in[1] + thread_in.Br;
             const int e0 = tid * GAE_ITEMS;
 #pragma unroll
             for (int j = GAE_ITEMS - 1; j >= 0; j--) {
@@ -581,41 +504,6 @@ __global__ void __launch_bounds__(GAE_THREADS, GAE_CFG_MINBLOCKS) gae_scan_kerne
                 s_r[pi] = x_adv;
                 s_v[pi] = x_ret;
                 s_o[pi] = v + x_adv;
-            }
-        }
-        // warp 0 asks for the carry only now, after its own zero-carry replay: the predecessor has had that long to publish
-        if (warp == 0) {
-            float adv_in = 0.f, ret_in = 0.f;
-#ifndef GAE_DBG_NOCHAIN2
-            if (t > 0) lookback_vals(p.val_rec, t, lane, adv_in, ret_in);
-#endif
-            if (lane == 0) {
-                if ((!closed || t == 0) && !early) {
-                    const float adv_out = tile_agg.Aa * adv_in + tile_agg.Ba;
-                    const float ret_out = tile_agg.Ar * ret_in + tile_agg.Br;
-                    st_volatile_rec(&p.val_rec[t], enc_inc(adv_out, ret_out));
-                }
-                s_x_in[0] = adv_in;
-                s_x_in[1] = ret_in;
-            }
-        }
-        __syncthreads();            // the carry (s_x_in) is known
-
-        // ---- the threads in front of the tile's first terminal: add carry x (multiplier from the tile start to the element) ----
-        if (thread_in.Aa != 0.f || thread_in.Ar != 0.f) {
-            float c_adv = thread_in.Aa * s_x_in[0];
-            float c_ret = thread_in.Ar * s_x_in[1];
-            const int e0 = tid * GAE_ITEMS;
-#pragma unroll
-            for (int j = GAE_ITEMS - 1; j >= 0; j--) {
-                const int pi = pidx(e0 + j);
-                const unsigned int term = (tword[j >> 2] >> (8 * (j & 3))) & 0xffu;
-                const float nd = (term == 0u) ? 1.f : 0.f;
-                c_ret = (c_ret * g) * nd;
-                c_adv = (gl * nd) * c_adv;
-                s_r[pi] += c_adv;
-                s_v[pi] += c_ret;
-                s_o[pi] += c_adv;
             }
         }
         __syncthreads();

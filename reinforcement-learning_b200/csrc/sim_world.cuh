@@ -501,8 +501,14 @@ constexpr int kMaxRows = kMaxContacts + 1;
 // and writes the solver bodies it connects, so islands that share no dynamic body are independent: solving them on
 // different lanes, each in the reference's row order restricted to the island, gives bit-identical results to the single
 // sequential sweep of btSequentialImpulseConstraintSolver (the host build does the same thing island after island).
+// The solver bodies of an arena live in its shared-memory scratch (the car-vs-mesh hit staging, which is dead once contact
+// generation is over): the Gauss-Seidel sweep is one dependent chain through dv / dw of the bodies a row connects, walked by ONE
+// lane per island, and a per-thread stack array costs that chain a local-memory round trip per step (words of one lane's stack
+// sit 128 bytes apart, so every float is its own sector in a 28 KB L1 that 224 threads share). Bodies belong to exactly one
+// island, so the lanes of different islands never touch the same entry.
+static_assert(sizeof(SolverBody) * (1 + kMaxCars) <= sizeof(CarTriHit) * kMaxCars * kMaxMeshHit, "solver bodies must fit the mesh-hit staging");
 GGL_HDN void solve_island(ArenaDev& A, int rep) {
-    SolverBody sb[1 + kMaxCars];
+    SolverBody* sb = reinterpret_cast<SolverBody*>(&A.meshHit[0][0]);
     const int nb = 1 + A.numCars;
     uint32_t inContact = 0;                            // bodies of this island that have a row
     for (int b = 0; b < nb; b++)

@@ -62,6 +62,11 @@ def main():
         if na % 4 == 0:
             w = tot_a.reshape(-1, 4).max(1)
             print("per-warp (max of 4 arenas) p50 %.0f p99 %.0f max %.0f" % tuple(np.percentile(w, [50, 99, 100])))
+        gpb = int(os.environ.get("GGL_GROUPS_PER_BLOCK", "28"))          # lane groups (arena positions) per block: 28 for 2v2
+        nblk = (na + gpb - 1) // gpb
+        blk = np.array([tot_a[b * gpb:(b + 1) * gpb].max() for b in range(nblk)])
+        print("per-BLOCK cycles/step (positions of a block end together): min %.0f p10 %.0f p50 %.0f p90 %.0f max %.0f mean %.0f  -> max/mean %.2f" %
+              (*np.percentile(blk, [0, 10, 50, 90, 100]), blk.mean(), blk.max() / blk.mean()))
         top = np.argsort(-tot_a)[: max(1, na // 100)]
         print("phase share in the slowest 1% of arenas vs all:")
         for i, n in enumerate(NAMES):
