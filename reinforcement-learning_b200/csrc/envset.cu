@@ -545,7 +545,7 @@ __global__ void tick_stats_kernel(const ArenaDev* arenas, int numArenas, unsigne
     int cand = 0, wheels = 0, carsRest = 0, hits = 0, maxWin = 0;
     for (int c = 0; c < A.numCars; c++) {
         cand += A.meshCandN[c]; hits += (int)A.meshHitN[c];
-        for (int w = 0; w < 4; w++) wheels += A.cars[c].w[w].ground != GROUND_NONE;
+        for (int w = 0; w < 4; w++) wheels += A.cars[c].wheelsWithContact[w] != 0;      // (the wheels' per-tick scratch holds solver rows by now)
         carsRest += A.cntRest[c] != 0;
         if (A.cntRest[c] > maxWin) maxWin = A.cntRest[c];
     }

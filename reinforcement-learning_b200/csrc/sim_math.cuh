@@ -3,6 +3,7 @@
 // GGL_HD lets the same header compile for the device (product) and for the host lock-step debugger used by the
 // CPU test-suite (tests/hostsim — test infrastructure, never loaded by the product library).
 #pragma once
+#include <string.h>
 #include <math.h>
 #include <stdint.h>
 
@@ -37,6 +38,9 @@ GGL_HD V3& operator+=(V3& a, V3 b) { a = a + b; return a; }
 GGL_HD V3& operator-=(V3& a, V3 b) { a = a - b; return a; }
 GGL_HD V3& operator*=(V3& a, float s) { a = a * s; return a; }
 GGL_HD float dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+// bit casts that compile on both sides (the host build of the simulator is g++)
+GGL_HD float __int_as_float_portable(int i) { float f; memcpy(&f, &i, 4); return f; }
+GGL_HD int __float_as_int_portable(float f) { int i; memcpy(&i, &f, 4); return i; }
 GGL_HD V3 cross(V3 a, V3 b) { return v3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x); }
 GGL_HD float len2(V3 a) { return dot(a, a); }
 GGL_HD float len(V3 a) { return sqrtf(len2(a)); }

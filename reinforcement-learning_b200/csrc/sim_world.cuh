@@ -376,18 +376,22 @@ struct SolverBody {
     int active;
 };
 
+// One solver row, 20 floats = 80 bytes: exactly the per-tick scratch of one wheel (Wheel::hardPoint .. Wheel::ground), which is
+// dead between the end of the car pre-tick and the next tick's ray casts. That is where the rows of an arena live while its
+// islands are solved (row_slot): like the solver bodies above, they are walked by one lane per island, and on a per-thread
+// stack every float of a row would be a sector of its own. n2 of a two-body row is -n1 and is not stored; limits, body indices
+// and the friction coefficient come from the contact (still in shared memory) or are arguments.
 struct Row {
-    V3 n1, rxn1, angA, n2, rxn2, angB;
-    float jacInv, rhs, rhsPen, applied, appliedPush, friction, lower, upper;
-    int a, b;          // solver body indices (b = -1: fixed)
-    int special, frictionOf;
+    V3 n1, rxn1, angA, rxn2, angB;
+    float jacInv, rhs, rhsPen, applied, appliedPush;
 };
+static_assert(sizeof(Row) == 80, "a solver row must fit the scratch part of a Wheel");
+static_assert(offsetof(Wheel, ground) + sizeof(int) - offsetof(Wheel, hardPoint) == sizeof(Row), "Wheel scratch layout changed");
 
 GGL_HD void sb_apply(SolverBody& s, V3 lin, V3 ang, float mag) { s.dv += lin * mag; s.dw += ang * mag; }
 GGL_HD void sb_push(SolverBody& s, V3 lin, V3 ang, float mag) { s.push += lin * mag; s.turn += ang * mag; }
 
-GGL_HD void setup_contact_row(Row& r, const SolverBody* sb, int a, int b, V3 n, V3 rel1, V3 rel2, float dist, float friction,
-                              float restitutionCoef, int special) {
+GGL_HD void setup_contact_row(Row& r, const SolverBody* sb, int a, int b, V3 n, V3 rel1, V3 rel2, float dist, float restitutionCoef) {
     const float invDt = 1.f / kTick;
     const SolverBody& A = sb[a];
     V3 t0 = cross(rel1, n);
@@ -399,18 +403,18 @@ GGL_HD void setup_contact_row(Row& r, const SolverBody* sb, int a, int b, V3 n, 
     if (b >= 0) denom1 = sb[b].invMass + dot(n, cross(-r.angB, rel2));
     r.jacInv = 1.f / (denom0 + denom1 + 0.f);
     r.n1 = n; r.rxn1 = t0;
-    if (b >= 0) { r.n2 = -n; r.rxn2 = -t1; } else { r.n2 = v3(0, 0, 0); r.rxn2 = v3(0, 0, 0); }
+    V3 n2;
+    if (b >= 0) { n2 = -n; r.rxn2 = -t1; } else { n2 = v3(0, 0, 0); r.rxn2 = v3(0, 0, 0); }
     float penetration = dist + 0.f;
     V3 vel1 = vel_at(A.vel, A.angVel, rel1);
     V3 vel2 = (b >= 0) ? vel_at(sb[b].vel, sb[b].angVel, rel2) : v3(0, 0, 0);
     float relVel0 = dot(n, vel1 - vel2);
     float restitution = (fabsf(relVel0) < 0.2f) ? 0.f : restitutionCoef * -relVel0;
     if (restitution <= 0.f) restitution = 0.f;
-    r.friction = friction;
     r.applied = 0.f; r.appliedPush = 0.f;
     V3 zero = v3(0, 0, 0);
     float v1n = dot(r.n1, A.vel + A.extF) + dot(r.rxn1, A.angVel + A.extT);
-    float v2n = (b >= 0) ? dot(r.n2, sb[b].vel + sb[b].extF) + dot(r.rxn2, sb[b].angVel + sb[b].extT) : dot(r.n2, zero);
+    float v2n = (b >= 0) ? dot(n2, sb[b].vel + sb[b].extF) + dot(r.rxn2, sb[b].angVel + sb[b].extT) : dot(n2, zero);
     float relVel = v1n + v2n;
     float posErr = 0.f;
     float velErr = restitution - relVel;
@@ -418,34 +422,30 @@ GGL_HD void setup_contact_row(Row& r, const SolverBody* sb, int a, int b, V3 n, 
     else posErr = -penetration * 0.8f * invDt;
     r.rhs = velErr * r.jacInv;
     r.rhsPen = posErr * r.jacInv;
-    r.lower = 0.f; r.upper = 1e10f;
-    r.a = a; r.b = b; r.special = special; r.frictionOf = -1;
 }
 
-GGL_HD void setup_friction_row(Row& r, const SolverBody* sb, int a, int b, V3 axis, V3 rel1, V3 rel2, float friction, int of) {
+GGL_HD void setup_friction_row(Row& r, const SolverBody* sb, int a, int b, V3 axis, V3 rel1, V3 rel2) {
     const SolverBody& A = sb[a];
     r.n1 = axis;
     r.rxn1 = cross(rel1, axis);
     r.angA = mul(A.invI, r.rxn1);
+    V3 n2;
     if (b >= 0) {
-        r.n2 = -axis;
-        r.rxn2 = cross(rel2, r.n2);
+        n2 = -axis;
+        r.rxn2 = cross(rel2, n2);
         r.angB = mul(sb[b].invI, r.rxn2);
     } else {
-        r.n2 = r.rxn2 = r.angB = v3(0, 0, 0);
+        n2 = r.rxn2 = r.angB = v3(0, 0, 0);
     }
     float denom0 = A.invMass + dot(axis, cross(r.angA, rel1));
     float denom1 = (b >= 0) ? sb[b].invMass + dot(axis, cross(-r.angB, rel2)) : 0.f;
     r.jacInv = 1.f / (denom0 + denom1);
     float v1n = dot(r.n1, A.vel + A.extF) + dot(r.rxn1, A.angVel);
-    float v2n = (b >= 0) ? dot(r.n2, sb[b].vel + sb[b].extF) + dot(r.rxn2, sb[b].angVel) : 0.f;
+    float v2n = (b >= 0) ? dot(n2, sb[b].vel + sb[b].extF) + dot(r.rxn2, sb[b].angVel) : 0.f;
     float relVel = v1n + v2n;
     r.rhs = (0.f - relVel) * r.jacInv;
     r.rhsPen = 0.f;
     r.applied = 0.f; r.appliedPush = 0.f;
-    r.friction = friction;
-    r.lower = -friction; r.upper = friction;
-    r.a = a; r.b = b; r.special = 0; r.frictionOf = of;
 }
 
 GGL_HD void friction_dir(const SolverBody* sb, int a, int b, V3 n, V3 rel1, V3 rel2, V3& dir) {
@@ -464,34 +464,36 @@ GGL_HD void friction_dir(const SolverBody* sb, int a, int b, V3 n, V3 rel1, V3 r
     }
 }
 
-GGL_HD void resolve_row(Row& c, SolverBody* sb, bool lowerOnly) {
+GGL_HD void resolve_row(Row& c, SolverBody* sb, int a, int b, float lower, float upper, bool lowerOnly) {
     float delta = c.rhs - c.applied * 0.f;
-    SolverBody& A = sb[c.a];
+    SolverBody& A = sb[a];
+    const V3 n2 = -c.n1;
     float d1 = dot(c.n1, A.dv) + dot(c.rxn1, A.dw);
-    float d2 = (c.b >= 0) ? dot(c.n2, sb[c.b].dv) + dot(c.rxn2, sb[c.b].dw) : 0.f;
+    float d2 = (b >= 0) ? dot(n2, sb[b].dv) + dot(c.rxn2, sb[b].dw) : 0.f;
     delta -= d1 * c.jacInv;
     delta -= d2 * c.jacInv;
     float sum = c.applied + delta;
-    if (sum < c.lower) { delta = c.lower - c.applied; c.applied = c.lower; }
-    else if (!lowerOnly && sum > c.upper) { delta = c.upper - c.applied; c.applied = c.upper; }
+    if (sum < lower) { delta = lower - c.applied; c.applied = lower; }
+    else if (!lowerOnly && sum > upper) { delta = upper - c.applied; c.applied = upper; }
     else c.applied = sum;
     sb_apply(A, c.n1 * A.invMass, c.angA, delta);
-    if (c.b >= 0) sb_apply(sb[c.b], c.n2 * sb[c.b].invMass, c.angB, delta);
+    if (b >= 0) sb_apply(sb[b], n2 * sb[b].invMass, c.angB, delta);
 }
 
-GGL_HD void resolve_push(Row& c, SolverBody* sb) {
+GGL_HD void resolve_push(Row& c, SolverBody* sb, int a, int b) {
     if (c.rhsPen == 0.f) return;
     float delta = c.rhsPen - c.appliedPush * 0.f;
-    SolverBody& A = sb[c.a];
+    SolverBody& A = sb[a];
+    const V3 n2 = -c.n1;
     float d1 = dot(c.n1, A.push) + dot(c.rxn1, A.turn);
-    float d2 = (c.b >= 0) ? dot(c.n2, sb[c.b].push) + dot(c.rxn2, sb[c.b].turn) : 0.f;
+    float d2 = (b >= 0) ? dot(n2, sb[b].push) + dot(c.rxn2, sb[b].turn) : 0.f;
     delta -= d1 * c.jacInv;
     delta -= d2 * c.jacInv;
     float sum = c.appliedPush + delta;
-    if (sum < c.lower) { delta = c.lower - c.appliedPush; c.appliedPush = c.lower; }
+    if (sum < 0.f) { delta = 0.f - c.appliedPush; c.appliedPush = 0.f; }
     else c.appliedPush = sum;
     sb_push(A, c.n1 * A.invMass, c.angA, delta);
-    if (c.b >= 0) sb_push(sb[c.b], c.n2 * sb[c.b].invMass, c.angB, delta);
+    if (b >= 0) sb_push(sb[b], n2 * sb[b].invMass, c.angB, delta);
 }
 
 constexpr int kMaxRows = kMaxContacts + 1;
@@ -501,12 +503,107 @@ constexpr int kMaxRows = kMaxContacts + 1;
 // and writes the solver bodies it connects, so islands that share no dynamic body are independent: solving them on
 // different lanes, each in the reference's row order restricted to the island, gives bit-identical results to the single
 // sequential sweep of btSequentialImpulseConstraintSolver (the host build does the same thing island after island).
-// The solver bodies of an arena live in its shared-memory scratch (the car-vs-mesh hit staging, which is dead once contact
-// generation is over): the Gauss-Seidel sweep is one dependent chain through dv / dw of the bodies a row connects, walked by ONE
-// lane per island, and a per-thread stack array costs that chain a local-memory round trip per step (words of one lane's stack
-// sit 128 bytes apart, so every float is its own sector in a 28 KB L1 that 224 threads share). Bodies belong to exactly one
-// island, so the lanes of different islands never touch the same entry.
+//
+// Where the data lives. The sweep is one dependent chain through dv / dw of the bodies a row connects, walked by ONE lane per
+// island; on a per-thread stack every float of that chain is a sector of its own (words of one lane's stack sit 128 bytes
+// apart) in a 28 KB L1 that 224 threads share, i.e. a local-memory round trip per step. So:
+//   * the solver bodies of an arena live in its shared-memory scratch, the car-vs-mesh hit staging, which is dead once contact
+//     generation is over (bodies belong to exactly one island, so the lanes of different islands never share an entry);
+//   * the rows live in the wheels' per-tick scratch (row 2k = contact k of the arena's solver order, 2k + 1 = its friction
+//     row, the averaged ball-world pair last; row s sits in wheel s & 3 of car s >> 2) as long as the arena has no more
+//     contacts than 2 x cars and no demolished car (a demolished car parks its reported orientation in wheel 0); otherwise
+//     (pile-ups) on the calling lane's stack. The friction row's two unused words carry the row's bodies and coefficient.
 static_assert(sizeof(SolverBody) * (1 + kMaxCars) <= sizeof(CarTriHit) * kMaxCars * kMaxMeshHit, "solver bodies must fit the mesh-hit staging");
+
+template <bool SMEM>
+struct RowStore {
+    ArenaDev& A;
+    Row lrows[SMEM ? 1 : 2 * kMaxRows];
+    GGL_HD explicit RowStore(ArenaDev& a) : A(a) {}
+    GGL_HD Row& at(int s) {
+        if (SMEM) return *reinterpret_cast<Row*>(&A.cars[s >> 2].w[s & 3].hardPoint);
+        return lrows[s];
+    }
+};
+
+template <bool SMEM>
+GGL_HD void solve_island_rows(ArenaDev& A, SolverBody* sb, int rep) {
+    RowStore<SMEM> R(A);
+    const int nc = A.numContacts;
+    // the island's rows as a packed list of contact indices (6 bits each would not fit 37 entries: the stack path keeps a byte
+    // list, the shared-memory path has at most 13 entries of 5 bits)
+    unsigned long long list = 0;
+    uint8_t llist[SMEM ? 1 : kMaxRows];
+    int nr = 0;
+    auto put = [&](int k) { if (SMEM) list |= (unsigned long long)k << (5 * nr); else llist[nr] = (uint8_t)k; nr++; };
+    auto get = [&](int j) -> int { return SMEM ? (int)((list >> (5 * j)) & 31ull) : (int)llist[j]; };
+    int nSpecial = 0; V3 spNormal = v3(0, 0, 0); float spDist = 0.f, spFriction = 0.f, spRest = 0.f;
+    for (int k = 0; k < nc; k++) {
+        const Contact& c = A.contacts[A.contactOrder[k]];
+        const int a = c.bodyA, b = c.bodyB;
+        if (A.island[a] != rep) continue;
+        Row& N = R.at(2 * k);
+        Row& F = R.at(2 * k + 1);
+        setup_contact_row(N, sb, a, b, c.normal, c.relA, c.relB, c.dist, c.restitution);
+        if (c.special) {
+            nSpecial++; spFriction = c.friction; spRest = c.restitution; spNormal += c.normal; spDist += len(c.relA);
+        }
+        V3 dir;
+        friction_dir(sb, a, b, c.normal, c.relA, c.relB, dir);
+        setup_friction_row(F, sb, a, b, dir, c.relA, c.relB);
+        F.rhsPen = c.friction;                                                                  // spare words of the friction row:
+        F.appliedPush = __int_as_float_portable((a & 0xff) | ((b & 0xff) << 8) | (c.special ? 0x10000 : 0));   // coefficient, bodies, flag
+        put(k);
+    }
+    if (nSpecial > 0) {
+        // averaged ball-world contact against a fixed body (convertContactSpecial)
+        float distance = spDist / nSpecial;
+        V3 normal = spNormal / (float)nSpecial;
+        V3 rel1 = normal * -distance, rel2 = v3(0, 0, 0);
+        Row& N = R.at(2 * nc);
+        Row& F = R.at(2 * nc + 1);
+        setup_contact_row(N, sb, 0, -1, normal, rel1, rel2, distance, spRest);
+        V3 dir;
+        friction_dir(sb, 0, -1, normal, rel1, rel2, dir);
+        setup_friction_row(F, sb, 0, -1, dir, rel1, rel2);
+        F.rhsPen = spFriction;
+        F.appliedPush = __int_as_float_portable(0 | (0xff << 8));
+        put(nc);
+    }
+    if (nr == 0) return;
+    for (int it = 0; it < 10; it++) {
+        bool any = false;
+        for (int j = 0; j < nr; j++) {
+            const int k = get(j);
+            Row& N = R.at(2 * k);
+            const int meta = __float_as_int_portable(R.at(2 * k + 1).appliedPush);
+            any |= N.rhsPen != 0.f;
+            resolve_push(N, sb, meta & 0xff, (int)(int8_t)((meta >> 8) & 0xff));
+        }
+        if (!any) break;
+    }
+    for (int it = 0; it < 10; it++) {
+        for (int j = 0; j < nr; j++) {
+            const int k = get(j);
+            const int meta = __float_as_int_portable(R.at(2 * k + 1).appliedPush);
+            if (meta & 0x10000) continue;
+            resolve_row(R.at(2 * k), sb, meta & 0xff, (int)(int8_t)((meta >> 8) & 0xff), 0.f, 1e10f, true);
+        }
+        for (int j = 0; j < nr; j++) {
+            const int k = get(j);
+            Row& F = R.at(2 * k + 1);
+            const float tot = R.at(2 * k).applied;
+            if (tot > 0.f) {
+                const int meta = __float_as_int_portable(F.appliedPush);
+                const float mu = F.rhsPen;
+                resolve_row(F, sb, meta & 0xff, (int)(int8_t)((meta >> 8) & 0xff), -(mu * tot), mu * tot, false);
+            }
+        }
+    }
+}
+
+GGL_HDN void solve_island_rows_on_stack(ArenaDev& A, SolverBody* sb, int rep) { solve_island_rows<false>(A, sb, rep); }   // pile-ups: out of line
+
 GGL_HDN void solve_island(ArenaDev& A, int rep) {
     SolverBody* sb = reinterpret_cast<SolverBody*>(&A.meshHit[0][0]);
     const int nb = 1 + A.numCars;
@@ -525,7 +622,9 @@ GGL_HDN void solve_island(ArenaDev& A, int rep) {
         s.extF = A.ball.force * kBallInvMass * kTick;
         s.extT = tmul(s.invI, A.ball.torque) * kTick;
     }
+    bool anyDemoed = false;
     for (int i = 0; i < A.numCars; i++) {
+        anyDemoed |= A.cars[i].isDemoed != 0;
         if (!(inContact & (2u << i))) continue;
         SolverBody& s = sb[1 + i];
         const CarDev& c = A.cars[i];
@@ -537,54 +636,9 @@ GGL_HDN void solve_island(ArenaDev& A, int rep) {
         s.extF = c.force * s.invMass * kTick;
         s.extT = tmul(c.invInertiaW, c.torque) * kTick;
     }
-    Row rows[kMaxRows];
-    Row fr[kMaxRows];
-    int nr = 0;
-    // special (ball-world) accumulation
-    int nSpecial = 0; V3 spNormal = v3(0, 0, 0); float spDist = 0.f, spFriction = 0.f, spRest = 0.f;
-    for (int k = 0; k < A.numContacts; k++) {
-        const Contact& c = A.contacts[A.contactOrder[k]];
-        int a = c.bodyA, b = c.bodyB;
-        if (A.island[a] != rep) continue;
-        setup_contact_row(rows[nr], sb, a, b, c.normal, c.relA, c.relB, c.dist, c.friction, c.restitution, c.special);
-        if (c.special) {
-            nSpecial++; spFriction = c.friction; spRest = c.restitution; spNormal += c.normal; spDist += len(c.relA);
-        }
-        V3 dir;
-        friction_dir(sb, a, b, c.normal, c.relA, c.relB, dir);
-        setup_friction_row(fr[nr], sb, a, b, dir, c.relA, c.relB, c.friction, nr);
-        nr++;
-    }
-    if (nSpecial > 0) {
-        // averaged ball-world contact against a fixed body (convertContactSpecial)
-        float distance = spDist / nSpecial;
-        V3 normal = spNormal / (float)nSpecial;
-        V3 rel1 = normal * -distance, rel2 = v3(0, 0, 0);
-        setup_contact_row(rows[nr], sb, 0, -1, normal, rel1, rel2, distance, spFriction, spRest, 0);
-        V3 dir;
-        friction_dir(sb, 0, -1, normal, rel1, rel2, dir);
-        setup_friction_row(fr[nr], sb, 0, -1, dir, rel1, rel2, spFriction, nr);
-        nr++;
-    }
-    if (nr > 0) {
-        for (int it = 0; it < 10; it++) {
-            bool any = false;
-            for (int k = 0; k < nr; k++) { any |= rows[k].rhsPen != 0.f; resolve_push(rows[k], sb); }
-            if (!any) break;
-        }
-        for (int it = 0; it < 10; it++) {
-            for (int k = 0; k < nr; k++)
-                if (!rows[k].special) resolve_row(rows[k], sb, true);
-            for (int k = 0; k < nr; k++) {
-                float tot = rows[fr[k].frictionOf].applied;
-                if (tot > 0.f) {
-                    fr[k].lower = -(fr[k].friction * tot);
-                    fr[k].upper = fr[k].friction * tot;
-                    resolve_row(fr[k], sb, false);
-                }
-            }
-        }
-    }
+    // (numContacts + the averaged pair) x 2 rows against 4 wheel slots per car; 5-bit entries in the packed list
+    if (!anyDemoed && A.numContacts + 1 <= 2 * A.numCars && A.numContacts < 31) solve_island_rows<true>(A, sb, rep);
+    else solve_island_rows_on_stack(A, sb, rep);
     // write back
     for (int i = 0; i < nb; i++) {
         if (!(inContact & (1u << i))) continue;
