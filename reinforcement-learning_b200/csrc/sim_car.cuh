@@ -22,60 +22,48 @@ namespace ggl {
 
 // ---------------------------------------------------------------------------------------------- curves
 // LinearPieceCurve::GetOutput (Math/Math.cpp:5-35) over the tables of RLConst.h:340-437
-template <int N>
-GGL_HD float curve_eval(const float (&xs)[N], const float (&ys)[N], float in) {
-    if (in <= xs[0]) return ys[0];
-#pragma unroll
-    for (int i = 1; i < N; i++) {
-        if (xs[i] > in) {
-            float range = xs[i] - xs[i - 1];
-            float diff = ys[i] - ys[i - 1];
-            float f = (in - xs[i - 1]) / range;
-            return ys[i - 1] + diff * f;
-        }
+// The tables are spelled out as nested comparisons on literals: as arrays handed to a generic evaluator they ended up on the
+// thread's stack (ncu: local loads on the steering curve, every car every tick). curve_seg is the interpolation of one piece
+// exactly as GetOutput writes it: range and difference of the piece's end points, then in - x0 over the range.
+GGL_HD float curve_seg(float in, float x0, float x1, float y0, float y1) {
+    float range = x1 - x0;
+    float diff = y1 - y0;
+    float f = (in - x0) / range;
+    return y0 + diff * f;
+}
+#define GGL_CURVE2(name, X0, X1, Y0, Y1) \
+    GGL_HD float name(float in) { if (in <= (X0)) return (Y0); if ((X1) > in) return curve_seg(in, X0, X1, Y0, Y1); return (Y1); }
+#define GGL_CURVE3(name, X0, X1, X2, Y0, Y1, Y2)                                                  \
+    GGL_HD float name(float in) {                                                                \
+        if (in <= (X0)) return (Y0);                                                             \
+        if ((X1) > in) return curve_seg(in, X0, X1, Y0, Y1);                                     \
+        if ((X2) > in) return curve_seg(in, X1, X2, Y1, Y2);                                     \
+        return (Y2);                                                                             \
     }
-    return ys[N - 1];
+GGL_HD float curve_steer_angle(float in) {
+    if (in <= 0.f) return 0.53356f;
+    if (500.f > in) return curve_seg(in, 0.f, 500.f, 0.53356f, 0.31930f);
+    if (1000.f > in) return curve_seg(in, 500.f, 1000.f, 0.31930f, 0.18203f);
+    if (1500.f > in) return curve_seg(in, 1000.f, 1500.f, 0.18203f, 0.10570f);
+    if (1750.f > in) return curve_seg(in, 1500.f, 1750.f, 0.10570f, 0.08507f);
+    if (3000.f > in) return curve_seg(in, 1750.f, 3000.f, 0.08507f, 0.03454f);
+    return 0.03454f;
 }
-GGL_HD float curve_steer_angle(float s) {
-    const float x[6] = {0, 500, 1000, 1500, 1750, 3000}, y[6] = {0.53356f, 0.31930f, 0.18203f, 0.10570f, 0.08507f, 0.03454f};
-    return curve_eval(x, y, s);
+GGL_CURVE2(curve_powerslide_steer, 0.f, 2500.f, 0.39235f, 0.12610f)
+GGL_CURVE3(curve_drive_torque, 0.f, 1400.f, 1410.f, 1.0f, 0.1f, 0.0f)
+GGL_CURVE3(curve_non_sticky, 0.f, 0.7075f, 1.f, 0.1f, 0.5f, 1.0f)
+GGL_CURVE2(curve_lat_friction, 0.f, 1.f, 1.0f, 0.2f)
+GGL_CURVE2(curve_handbrake_long, 0.f, 1.f, 0.5f, 0.9f)
+GGL_HD float curve_ball_extra_impulse(float in) {
+    if (in <= 0.f) return 0.65f;
+    if (500.f > in) return curve_seg(in, 0.f, 500.f, 0.65f, 0.65f);
+    if (2300.f > in) return curve_seg(in, 500.f, 2300.f, 0.65f, 0.55f);
+    if (4600.f > in) return curve_seg(in, 2300.f, 4600.f, 0.55f, 0.30f);
+    return 0.30f;
 }
-GGL_HD float curve_powerslide_steer(float s) {
-    const float x[2] = {0, 2500}, y[2] = {0.39235f, 0.12610f};
-    return curve_eval(x, y, s);
-}
-GGL_HD float curve_drive_torque(float s) {
-    const float x[3] = {0, 1400, 1410}, y[3] = {1.0f, 0.1f, 0.0f};
-    return curve_eval(x, y, s);
-}
-GGL_HD float curve_non_sticky(float z) {
-    const float x[3] = {0, 0.7075f, 1}, y[3] = {0.1f, 0.5f, 1.0f};
-    return curve_eval(x, y, z);
-}
-GGL_HD float curve_lat_friction(float v) {
-    const float x[2] = {0, 1}, y[2] = {1.0f, 0.2f};
-    return curve_eval(x, y, v);
-}
-GGL_HD float curve_handbrake_long(float v) {
-    const float x[2] = {0, 1}, y[2] = {0.5f, 0.9f};
-    return curve_eval(x, y, v);
-}
-GGL_HD float curve_ball_extra_impulse(float v) {
-    const float x[4] = {0, 500.f, 2300.f, 4600.f}, y[4] = {0.65f, 0.65f, 0.55f, 0.30f};
-    return curve_eval(x, y, v);
-}
-GGL_HD float curve_bump_ground(float v) {
-    const float x[3] = {0.f, 1400.f, 2200.f}, y[3] = {(5.f / 6.f), 1100.f, 1530.f};
-    return curve_eval(x, y, v);
-}
-GGL_HD float curve_bump_air(float v) {
-    const float x[3] = {0.f, 1400.f, 2200.f}, y[3] = {(5.f / 6.f), 1390.f, 1945.f};
-    return curve_eval(x, y, v);
-}
-GGL_HD float curve_bump_up(float v) {
-    const float x[3] = {0.f, 1400.f, 2200.f}, y[3] = {(2.f / 6.f), 278.f, 417.f};
-    return curve_eval(x, y, v);
-}
+GGL_CURVE3(curve_bump_ground, 0.f, 1400.f, 2200.f, (5.f / 6.f), 1100.f, 1530.f)
+GGL_CURVE3(curve_bump_air, 0.f, 1400.f, 2200.f, (5.f / 6.f), 1390.f, 1945.f)
+GGL_CURVE3(curve_bump_up, 0.f, 1400.f, 2200.f, (2.f / 6.f), 278.f, 417.f)
 
 // ---------------------------------------------------------------------------------------------- car constants
 GGL_HD V3 car_half_extents() { return v3(rl::HITBOX_X * kUU2BT / 2, rl::HITBOX_Y * kUU2BT / 2, rl::HITBOX_Z * kUU2BT / 2); }

@@ -134,28 +134,43 @@ GGL_HD M3 m3_from_quat(Q4 q) {
     m.r2 = v3(xz - wy, yz + wx, 1.f - (xx + yy));
     return m;
 }
+// btMatrix3x3::getRotation. The three cases of the non-positive-trace branch are written out (Bullet indexes m_el[i][j] with
+// run-time i, j, k): a dynamically indexed temporary would live on the thread's stack, and this runs for every car every tick.
 GGL_HD Q4 quat_from_m3(const M3& m) {
     float trace = m.r0.x + m.r1.y + m.r2.z;
-    float t[4];
+    Q4 q;
     if (trace > 0.f) {
         float s = sqrtf(trace + 1.f);
-        t[3] = s * 0.5f;
+        q.w = s * 0.5f;
         s = 0.5f / s;
-        t[0] = (m.r2.y - m.r1.z) * s;
-        t[1] = (m.r0.z - m.r2.x) * s;
-        t[2] = (m.r1.x - m.r0.y) * s;
+        q.x = (m.r2.y - m.r1.z) * s;
+        q.y = (m.r0.z - m.r2.x) * s;
+        q.z = (m.r1.x - m.r0.y) * s;
     } else {
-        int i = m.r0.x < m.r1.y ? (m.r1.y < m.r2.z ? 2 : 1) : (m.r0.x < m.r2.z ? 2 : 0);
-        int j = (i + 1) % 3, k = (i + 2) % 3;
-        const V3 rows[3] = {m.r0, m.r1, m.r2};
-        float s = sqrtf(comp(rows[i], i) - comp(rows[j], j) - comp(rows[k], k) + 1.f);
-        t[i] = s * 0.5f;
-        s = 0.5f / s;
-        t[3] = (comp(rows[k], j) - comp(rows[j], k)) * s;
-        t[j] = (comp(rows[j], i) + comp(rows[i], j)) * s;
-        t[k] = (comp(rows[k], i) + comp(rows[i], k)) * s;
+        const int i = m.r0.x < m.r1.y ? (m.r1.y < m.r2.z ? 2 : 1) : (m.r0.x < m.r2.z ? 2 : 0);
+        if (i == 0) {           // j = 1, k = 2
+            float s = sqrtf(m.r0.x - m.r1.y - m.r2.z + 1.f);
+            q.x = s * 0.5f;
+            s = 0.5f / s;
+            q.w = (m.r2.y - m.r1.z) * s;
+            q.y = (m.r1.x + m.r0.y) * s;
+            q.z = (m.r2.x + m.r0.z) * s;
+        } else if (i == 1) {    // j = 2, k = 0
+            float s = sqrtf(m.r1.y - m.r2.z - m.r0.x + 1.f);
+            q.y = s * 0.5f;
+            s = 0.5f / s;
+            q.w = (m.r0.z - m.r2.x) * s;
+            q.z = (m.r2.y + m.r1.z) * s;
+            q.x = (m.r0.y + m.r1.x) * s;
+        } else {                // j = 0, k = 1
+            float s = sqrtf(m.r2.z - m.r0.x - m.r1.y + 1.f);
+            q.z = s * 0.5f;
+            s = 0.5f / s;
+            q.w = (m.r1.x - m.r0.y) * s;
+            q.x = (m.r0.z + m.r2.x) * s;
+            q.y = (m.r1.z + m.r2.y) * s;
+        }
     }
-    Q4 q; q.x = t[0]; q.y = t[1]; q.z = t[2]; q.w = t[3];
     return q;
 }
 

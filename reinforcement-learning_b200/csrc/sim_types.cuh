@@ -180,6 +180,7 @@ struct alignas(16) ArenaDev {
     alignas(4) uint8_t poolOwner[kMaxPool];        // who claimed overflow-pool slot j (POOL_* codes, sim_world.cuh)
     uint32_t poolCount;                            // overflow-pool slots claimed this tick (atomic: the bodies' lanes race for them)
     int8_t padHit[8];                              // per tick: the boost pad car c collides with (-1 = none), see car_check_pads
+    uint16_t ballCand[24];                         // per tick: candidate triangles of the ball (collide_ball_mesh)
     // car-vs-mesh staging: candidates per car (gathered by the car's lane), hits found by all lanes of the group
     uint16_t meshCand[kMaxCars][kMaxMeshCand];
     uint8_t meshCandN[kMaxCars], meshHitOverflow[kMaxCars];

@@ -237,8 +237,9 @@ GGL_HD void collide_ball_mesh(ArenaDev& A, ContactSink& S, const WorldDev& W) {
     int x0 = grid_coord(mn.x, W.gridMin.x, W.invCellSize, W.gx), x1 = grid_coord(mx.x, W.gridMin.x, W.invCellSize, W.gx);
     int y0 = grid_coord(mn.y, W.gridMin.y, W.invCellSize, W.gy), y1 = grid_coord(mx.y, W.gridMin.y, W.invCellSize, W.gy);
     int z0 = grid_coord(mn.z, W.gridMin.z, W.invCellSize, W.gz), z1 = grid_coord(mx.z, W.gridMin.z, W.invCellSize, W.gz);
-    // candidate triangles in (mesh, triangle) index order; one manifold per mesh body
-    int cand[24]; int nc = 0;
+    // candidate triangles in (mesh, triangle) index order; one manifold per mesh body (the list lives in the arena's scratch: a
+    // stack array with run-time indices would be local memory, and this is a one-lane insertion sort)
+    uint16_t* cand = A.ballCand; int nc = 0;
     for (int z = z0; z <= z1; z++)
         for (int y = y0; y <= y1; y++)
             for (int x = x0; x <= x1; x++) {
@@ -246,10 +247,10 @@ GGL_HD void collide_ball_mesh(ArenaDev& A, ContactSink& S, const WorldDev& W) {
                 for (int k = W.cellStart[cell]; k < W.cellStart[cell + 1]; k++) {
                     int ti = W.cellTris[k];
                     int pos = 0; bool dup = false;
-                    while (pos < nc && cand[pos] <= ti) { dup |= cand[pos] == ti; pos++; }
+                    while (pos < nc && (int)cand[pos] <= ti) { dup |= (int)cand[pos] == ti; pos++; }
                     if (dup || nc >= 24) continue;
                     for (int q = nc; q > pos; q--) cand[q] = cand[q - 1];
-                    cand[pos] = ti; nc++;
+                    cand[pos] = (uint16_t)ti; nc++;
                 }
             }
     int curMesh = -1;
