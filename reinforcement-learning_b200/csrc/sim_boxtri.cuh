@@ -18,7 +18,9 @@ struct ClosestOut { V3 normalOnB, pointOnB; float distance; };
 
 // btGjkPairDetector::getClosestPointsNonVirtual for (box core, marginA) vs (triangle, margin 0).
 // `s` is given in world coordinates; the detector re-centres both transforms by positionOffset like the reference.
-GGL_HDN bool box_tri_closest(const BoxTri& world, float maxDistSq, ClosestOut& out) {
+// `vs` = working storage of the simplex solver, provided by the caller: its vertex arrays are indexed at run time, so as a
+// stack object they are local memory; the lane-parallel narrow phase hands in a slice of the arena's shared-memory scratch.
+GGL_HDN bool box_tri_closest(const BoxTri& world, float maxDistSq, ClosestOut& out, Voronoi& vs) {
     BoxTri s = world;
     const V3 positionOffset = (world.posA + world.posB) * 0.5f;
     s.posA = world.posA - positionOffset;
@@ -31,7 +33,6 @@ GGL_HDN bool box_tri_closest(const BoxTri& world, float maxDistSq, ClosestOut& o
     int degenerate = 0, curIter = 0;
     float squaredDistance = 1e18f;
     const float margin = marginA + marginB;
-    Voronoi vs;
     vs_reset(vs);
     while (true) {
         V3 sepInA = tmul(world.basisA, -axis);
@@ -144,7 +145,7 @@ GGL_HD bool tri_overlaps_aabb(const Tri& t, V3 mn, V3 mx) {
 }
 
 // Narrow phase of one (car, triangle) pair: pure function of the car's transform and the triangle. False = no contact point.
-GGL_HDN bool car_tri_narrow(const CarDev& car, const Tri& t, V3 boxPos, const BoxGeom& bg, float cbt, ClosestOut& o) {
+GGL_HDN bool car_tri_narrow(const CarDev& car, const Tri& t, V3 boxPos, const BoxGeom& bg, float cbt, ClosestOut& o, Voronoi& vs) {
     // early out: hitbox fully on one side of the triangle plane, further away than the breaking threshold
     V3 tn = normalized(cross(t.v1 - t.v0, t.v2 - t.v0));
     const M3 invB = inverse(car.basis);
@@ -159,7 +160,7 @@ GGL_HDN bool car_tri_narrow(const CarDev& car, const Tri& t, V3 boxPos, const Bo
     s.basisA = car.basis; s.posA = boxPos; s.he = bg.core; s.marginA = bg.margin;
     s.t0 = t.v0; s.t1 = t.v1; s.t2 = t.v2; s.posB = v3(0, 0, 0);
     float md = bg.margin + 0.f + cbt;
-    if (!box_tri_closest(s, md * md, o)) return false;
+    if (!box_tri_closest(s, md * md, o, vs)) return false;
     if (o.distance > cbt) return false;
     return true;
 }
@@ -223,10 +224,16 @@ GGL_HDN void car_mesh_gather_cells(ArenaDev& A, const WorldDev& W, int ci, V3 mn
 }
 
 // Stage 2 (any lane): narrow phase of candidate `k` of car `ci`; a hit is appended to the car's hit list (any order).
-GGL_HD void car_mesh_narrow(ArenaDev& A, const WorldDev& W, int ci, int k) {
+// The simplex solver's storage: lane l < 8 of the arena's group uses bytes [256 l, 256 l + 256) of the contact rows (+ the head of
+// the row-order list behind them), which nobody needs before contact generation starts; further lanes (16-lane builds) fall
+// back to their stack.
+static_assert(8 * sizeof(Voronoi) <= sizeof(Contact) * kMaxContacts + kMaxContacts, "simplex scratch must fit contacts[] + contactOrder[]");
+GGL_HD void car_mesh_narrow(ArenaDev& A, const WorldDev& W, int ci, int k, int lane) {
     const CarDev& car = A.cars[ci];
     ClosestOut o;
-    if (!car_tri_narrow(car, W.tris[A.meshCand[ci][k]], car_box_pos(car), car_box(), car_cbt(), o)) return;
+    Voronoi onStack;
+    Voronoi& vs = lane < 8 ? reinterpret_cast<Voronoi*>(A.contacts)[lane] : onStack;
+    if (!car_tri_narrow(car, W.tris[A.meshCand[ci][k]], car_box_pos(car), car_box(), car_cbt(), o, vs)) return;
 #if defined(__CUDA_ARCH__)
     const uint32_t slot = atomicAdd(&A.meshHitN[ci], 1u);
 #else
@@ -251,7 +258,8 @@ GGL_HDN void car_mesh_emit(ArenaDev& A, ContactSink& S, const WorldDev& W, int c
             int mesh = (int)(t.flags >> TRI_MESH_SHIFT);
             if (mesh != curMesh) { m = manifold_begin(S); curMesh = mesh; }
             ClosestOut o;
-            if (car_tri_narrow(car, t, car_box_pos(car), car_box(), car_cbt(), o)) car_tri_emit(A, S, m, ci, t, o);
+            Voronoi vs;        // serial redo while contact rows are being written: on the stack
+            if (car_tri_narrow(car, t, car_box_pos(car), car_box(), car_cbt(), o, vs)) car_tri_emit(A, S, m, ci, t, o);
         }
         return;
     }

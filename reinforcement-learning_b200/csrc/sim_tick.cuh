@@ -237,7 +237,7 @@ GGL_HD void arena_tick(ArenaDev& A, const WorldDev& W, const Exec& ex) {
         for (int p = ex.lane(); p < total; p += ex.lanes()) {
             int c = 0, k = p;
             while (k >= (int)A.meshCandN[c]) { k -= A.meshCandN[c]; c++; }
-            car_mesh_narrow(A, W, c, k);
+            car_mesh_narrow(A, W, c, k, ex.lane());
         }
     }
     ex.sync();
