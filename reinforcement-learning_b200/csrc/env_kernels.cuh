@@ -134,6 +134,12 @@ __global__ void __launch_bounds__(kBlock) env_reset_kernel(EnvCfg cfg, EnvDevPtr
 __global__ void __launch_bounds__(32 * kMaxWarps, 1) env_step_kernel(EnvCfg cfg, EnvDevPtrs P, const int32_t* __restrict__ actions, int doFirst,
                                                           int doSecond, int slotBytes) {
     GGL_PH_BEGIN();
+    // The world descriptor is handed by reference to out-of-line device functions; taking the address of a kernel parameter
+    // makes the compiler keep a copy on every thread's stack (ncu: local loads on every W.field access, e.g. the empty-cell box
+    // test of every ray). One copy per block in shared memory instead.
+    __shared__ WorldDev s_world;
+    if (threadIdx.x == 0) s_world = P.world;
+    __syncthreads();
     const int pos = blockIdx.x * (blockDim.x / kGroup) + threadIdx.x / kGroup;
     if (pos >= cfg.numArenas) return;            // whole groups leave: nobody waits for them at a group or block barrier
     const int arena = arena_of(P, pos);
@@ -141,7 +147,7 @@ __global__ void __launch_bounds__(32 * kMaxWarps, 1) env_step_kernel(EnvCfg cfg,
     stage_in(P, arena, ex, slotBytes, 0);
     {
         ArenaDev& A = my_arena(slotBytes);
-        const WorldDev& W = P.world;
+        const WorldDev& W = s_world;
         GGL_PH(13);
         // ONE tick loop (a single inlined copy of arena_tick keeps the kernel's code half the size, which matters at ~7 warps
         // per SM that all sit in different places of it): the parsed actions take effect at tick `actionDelay`.
@@ -238,12 +244,15 @@ __global__ void __launch_bounds__(1024) balance_kernel(const uint32_t* __restric
 
 // raw Arena::Step(ticks)
 __global__ void __launch_bounds__(32 * kMaxWarps, 1) arena_step_kernel(EnvCfg cfg, EnvDevPtrs P, int ticks, int slotBytes) {
+    __shared__ WorldDev s_world;
+    if (threadIdx.x == 0) s_world = P.world;
+    __syncthreads();
     const int arena = blockIdx.x * (blockDim.x / kGroup) + threadIdx.x / kGroup;
     if (arena >= cfg.numArenas) return;
     const ExecGroup ex = make_exec();
     stage_in(P, arena, ex, slotBytes, 1);
     ArenaDev& A = my_arena(slotBytes);
-    for (int t = 0; t < ticks; t++) arena_tick(A, P.world, ex);
+    for (int t = 0; t < ticks; t++) arena_tick(A, s_world, ex);
     stage_out(P, arena, ex, slotBytes, 1);
 }
 
