@@ -192,6 +192,13 @@ extern "C" int ggl_envset_create(const ggl_envset_desc* d, ggl_envset** out) {
         e->geom = launch_geom(e->cfg, sms);
         // Load balancing between blocks only matters once a launch has several multi-warp blocks; GGL_BALANCE=0 turns it off
         // (arenas then sit in index order, as in round 1).
+#if defined(GGL_COST_SWEEP)
+        if (const char* cw = getenv("GGL_COST_W")) {
+            int w[3] = {4, 6, 1};
+            sscanf(cw, "%d,%d,%d", &w[0], &w[1], &w[2]);
+            cudaMemcpyToSymbol(ggl::g_costW, w, sizeof(w));
+        }
+#endif
         const char* bal = getenv("GGL_BALANCE");
         e->balance = e->geom.grid > 1 && !(bal && atoi(bal) == 0);
         if (e->balance) {

@@ -18,6 +18,17 @@ namespace ggl {
 #define GGL_PSYNC_MASK (4 | 32 | 128 | 2048)
 #endif
 
+// weights of the per-tick work estimate (contact rows, triangle candidates, cars on their wheels); the experiment build reads
+// them from a device symbol set through GGL_COST_W="a,b,c" at create
+#if defined(GGL_COST_SWEEP) && defined(__CUDACC__)
+__device__ int g_costW[3] = {4, 6, 1};
+#endif
+#if defined(GGL_COST_SWEEP) && defined(__CUDA_ARCH__)
+#define GGL_COST_W(i) g_costW[i]
+#else
+#define GGL_COST_W(i) ((i) == 0 ? 4 : (i) == 1 ? 6 : 1)
+#endif
+
 struct ExecSerial {
     GGL_HD int lane() const { return 0; }
     GGL_HD int lanes() const { return 1; }
@@ -250,8 +261,8 @@ GGL_HD void arena_tick(ArenaDev& A, const WorldDev& W, const Exec& ex) {
         for (int c = 0; c < A.numCars; c++) any += A.cntBall[c] + A.cntRest[c];
         // work estimate of this tick for the launch geometry of the NEXT env step (env_kernels.cuh: arena_of): contact rows
         // (narrow phase + 10 solver iterations each), triangle candidates (a GJK/EPA each), wheels on something
-        int cost = 4 * any;
-        for (int c = 0; c < A.numCars; c++) cost += 6 * A.meshCandN[c] + A.cars[c].isOnGround;
+        int cost = GGL_COST_W(0) * any;
+        for (int c = 0; c < A.numCars; c++) cost += GGL_COST_W(1) * A.meshCandN[c] + GGL_COST_W(2) * A.cars[c].isOnGround;
         A.stepCost += (uint32_t)cost;
         if (any) gather_contacts(A);
         else {      // nothing touched anything this tick (88 % of the arena-ticks of the benchmark's rollout)
