@@ -44,7 +44,8 @@ GAE_BYTES_PER_ELEM = 21
 # at 4096 arenas 2v2 (state blobs in and out, outputs, mesh and instruction fetch) against 16.8 MB algorithmic; GAE scan:
 # 151.3 + 145.4 MB at L = 2^24 against 352 MB algorithmic (part of the 201 MB of outputs is still in the 126 MB L2 when the
 # kernel ends).
-ENV_TRAFFIC_BYTES_NCU = 36.2e6
+ENV_TRAFFIC_BYTES_NCU = 19.8e6      # profiles/r2v_env_step_ncu_summary.txt: 19.33 MB read + 0.46 MB written per launch (the 12.5 MB of outputs
+                                    # and the state written back are still in L2 when the kernel ends); round 1: 36.2 MB
 GAE_TRAFFIC_BYTES_NCU = 296.7e6
 # ExperienceBuffer gather (staged kernel, profiles/r1j_expbuf_ncu_summary.txt): 1.202 GB read + 0.773 GB written at 2^20 samples against
 # 1.63 GB algorithmic: a random row drags in whole 64-byte DRAM bursts around its unaligned ends, and each of the four scalars
@@ -255,8 +256,9 @@ def bench_env(args, rank, world, local):
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": ENV_TRAFFIC_BYTES_NCU, "kernel": "env_step_kernel", "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": ENV_BYTES_PER_AGENT_STEP * env.num_players,
-                     "note": "physics ticks are FP32-issue / barrier-latency bound (ncu: 11% issue utilisation, 50% of stall samples "
-                             "at the per-phase block barriers); the HBM floor is the obs/mask/reward write (SURVEY 8d)"},
+                     "note": "physics ticks are instruction-fetch / barrier-latency bound, not HBM bound (ncu r2v: 12% issue utilisation, "
+                             "4% of the FMA pipe, 50% of the stall samples at the per-phase block barriers, 14% instruction fetch; "
+                             "DESIGN.md section 4); the HBM floor is the obs/mask/reward write (SURVEY 8d)"},
         "wall_s": t_wall,
     }
     if rank == 0:

@@ -76,6 +76,8 @@ typedef enum ggl_reward_kind {   /* Rewards/CommonRewards.h */
     GGL_REW_AIR,                    /* :147-152 */
     GGL_REW_TOUCH_ACCEL,            /* :157-178 */
     GGL_REW_STRONG_TOUCH,           /* :180-202 params[0]=minRewardedVel params[1]=maxRewardedVel (uu/s) */
+    GGL_REW_KICKOFF_PROXIMITY_2V2,  /* Rewards/KickoffProximityReward2v2Enhanced.h:14-367 params = goerReward, cheaterReward,
+                                       dynamicWeight, rotationPrepWeight (defaults 1.2, 0.6, 0.3, 0.2) */
     GGL_REW_KIND_COUNT
 } ggl_reward_kind;
 

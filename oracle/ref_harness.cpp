@@ -12,6 +12,7 @@
 #include <RLGymCPP/ActionParsers/DefaultAction.h>
 #include <RLGymCPP/Rewards/CommonRewards.h>
 #include <RLGymCPP/Rewards/ZeroSumReward.h>
+#include <RLGymCPP/Rewards/KickoffProximityReward2v2Enhanced.h>
 #include <RLGymCPP/TerminalConditions/GoalScoreCondition.h>
 #include <RLGymCPP/TerminalConditions/NoTouchCondition.h>
 #include <RLGymCPP/StateSetters/KickoffState.h>
@@ -224,6 +225,11 @@ Reward* MakeReward(const ggl_reward_desc& d) {
         auto* s = new StrongTouchReward();
         s->minRewardedVel = d.params[0]; s->maxRewardedVel = d.params[1];
         r = s; break;
+    }
+    case GGL_REW_KICKOFF_PROXIMITY_2V2: {
+        auto* k = new KickoffProximityReward2v2Enhanced();
+        k->goerReward = d.params[0]; k->cheaterReward = d.params[1]; k->dynamicWeight = d.params[2]; k->rotationPrepWeight = d.params[3];
+        r = k; break;
     }
     default: return nullptr;
     }

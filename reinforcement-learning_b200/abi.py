@@ -13,7 +13,7 @@ OBS_DEFAULT, OBS_ADVANCED = 0, 1
 (REW_PLAYER_GOAL, REW_ASSIST, REW_SHOT, REW_SHOT_PASS, REW_SAVE, REW_BUMP, REW_BUMPED_PENALTY, REW_DEMO,
  REW_DEMOED_PENALTY, REW_GOAL, REW_VELOCITY, REW_VELOCITY_BALL_TO_GOAL, REW_VELOCITY_PLAYER_TO_BALL,
  REW_FACE_BALL, REW_TOUCH_BALL, REW_SPEED, REW_WAVEDASH, REW_PICKUP_BOOST, REW_SAVE_BOOST, REW_AIR,
- REW_TOUCH_ACCEL, REW_STRONG_TOUCH) = range(22)
+ REW_TOUCH_ACCEL, REW_STRONG_TOUCH, REW_KICKOFF_PROXIMITY_2V2) = range(23)
 
 TERM_GOAL_SCORE, TERM_NO_TOUCH = 0, 1
 SETTER_KICKOFF, SETTER_INJECTED = 0, 1

@@ -25,6 +25,129 @@ GGL_HD PlayerView player_view(const ArenaDev& A, int ci) {
     return p;
 }
 
+// KickoffProximityReward2v2Enhanced (RG/Rewards/KickoffProximityReward2v2Enhanced.h:14-367), statement by statement.
+// params: [0] goerReward, [1] cheaterReward (unused by the reference too), [2] dynamicWeight (unused), [3] rotationPrepWeight.
+// `state.players` is walked in slot order; the teammate is the LAST other player of the team the loop meets (:64-69).
+GGL_HD float rs_clampf(float v, float lo, float hi) { float a = (v > lo) ? v : lo; return (a < hi) ? a : hi; }   // RS_CLAMP = RS_MIN(RS_MAX(v, lo), hi)
+GGL_HD float reward_kickoff_proximity_2v2(const ArenaDev& A, const RewardCfg& r, const PlayerView& p, V3 ballPos, V3 ballVel) {
+    // IsKickoffActive :48-58
+    if (!(len(ballVel) < 2.f && ballPos.z < 150.f && len(v3(ballPos.x, ballPos.y, 0.f)) < 50.f)) return 0.f;
+    // AnalyzeTeamState :60-96
+    bool hasTeammate = false;
+    PlayerView mate = p;
+    float mateDist = 0.f, closestOpp = 3.402823466e+38f, secondOpp = 3.402823466e+38f, totalOppSpeed = 0.f;
+    V3 oppCom = v3(0, 0, 0);
+    int oppCount = 0;
+    for (int s = 0; s < A.numCars; s++) {
+        const PlayerView q = player_view(A, A.slotCar[s]);
+        if (q.team == p.team && q.carId != p.carId) {
+            mate = q; hasTeammate = true; mateDist = len(q.pos - ballPos);
+        } else if (q.team != p.team) {
+            const float d = len(q.pos - ballPos);
+            totalOppSpeed += len(q.vel);
+            oppCount++;
+            if (d < closestOpp) { secondOpp = closestOpp; closestOpp = d; }
+            else if (d < secondOpp) secondOpp = d;
+            oppCom = oppCom + q.pos;
+        }
+    }
+    if (oppCount > 0) oppCom = oppCom / (float)oppCount;
+    (void)secondOpp; (void)totalOppSpeed;
+    if (!hasTeammate) return 0.f;
+    const float playerDist = len(p.pos - ballPos);
+    // DeterminePlayerRole :98-122 (+ CalculateSpawnAdvantage :124-133)
+    const float distanceScore = (playerDist < mateDist) ? 0.4f : 0.f;
+    const V3 playerToBall = rs_normalized(ballPos - p.pos);
+    const V3 mateToBall = rs_normalized(ballPos - mate.pos);
+    const float playerVelToBall = dot(p.vel, playerToBall);
+    const float mateVelToBall = dot(mate.vel, mateToBall);
+    const float speedScore = (playerVelToBall > mateVelToBall) ? 0.3f : 0.f;
+    const float boostScore = (p.boost > mate.boost + 10.f) ? 0.2f : 0.f;
+    const float angP = atan2f(p.pos.y - ballPos.y, p.pos.x - ballPos.x), angM = atan2f(mate.pos.y - ballPos.y, mate.pos.x - ballPos.x);
+    const float spawnScore = ((fabsf(angP - angM) > (3.14159f / 3.f)) ? 1.f : 0.f) * 0.1f;
+    const float totalScore = distanceScore + speedScore + boostScore + spawnScore;
+    if (totalScore >= 0.5f) {
+        // CalculateGoerReward :135-161
+        const float goer = r.params[0];
+        const float baseReward = (playerDist < closestOpp) ? goer : -goer * 0.5f;
+        const float speedBonus = rs_clampf(playerVelToBall / 2300.f, -0.3f, 0.3f);
+        float boostEfficiency = 0.f;
+        if (p.boost > 50.f && playerDist > 1000.f) boostEfficiency = 0.1f;
+        else if (p.boost < 20.f && playerDist > 800.f) boostEfficiency = -0.15f;
+        const float approach = dot(playerToBall, rs_normalized(p.vel));
+        const float angleBonus = ((0.f > approach) ? 0.f : approach) * 0.2f;
+        return rs_clampf(baseReward + speedBonus + boostEfficiency + angleBonus, -1.5f, 1.5f);
+    }
+    // CalculateCheaterReward :163-188
+    const V3 ownGoal = (p.team == 0) ? v3(0.f, -6000.f, 642.775f / 2) : v3(0.f, 6000.f, 642.775f / 2);
+    // CalculateDynamicIdealPosition :190-228
+    const V3 fieldCenter = v3(0.f, 0.f, 100.f);
+    const V3 centerMul = v3(fieldCenter.x * 1.3f, fieldCenter.y * 1.3f, fieldCenter.z * 1.3f);
+    const V3 baseIdeal = (ownGoal + centerMul) * 0.5f;
+    V3 threat = rs_normalized(oppCom - ownGoal);
+    threat = v3(threat.x * 200.f, threat.y * 200.f, threat.z * 200.f);
+    V3 mateOffset = v3(0.f, 0.f, 0.f);
+    if (len(mate.pos - fieldCenter) > 1500.f) {
+        const V3 dir = rs_normalized(mate.pos - baseIdeal);
+        mateOffset = v3(dir.x * 300.f, dir.y * 300.f, dir.z * 300.f);
+    }
+    const V3 threatAdj = v3(threat.x * 0.3f, threat.y * 0.3f, threat.z * 0.3f);
+    const V3 mateAdj = v3(mateOffset.x * 0.2f, mateOffset.y * 0.2f, mateOffset.z * 0.2f);
+    V3 ideal = (baseIdeal + threatAdj) + mateAdj;
+    ideal.x = rs_clampf(ideal.x, -3000.f, 3000.f);
+    ideal.y = rs_clampf(ideal.y, -4000.f, 4000.f);
+    ideal.z = (ideal.z > 17.f) ? ideal.z : 17.f;
+    const float distToIdeal = len(p.pos - ideal);
+    // CalculatePositioningReward :230-254
+    float positioning;
+    if (distToIdeal <= 600.f) positioning = 0.5f * (1.f - (distToIdeal / 600.f));
+    else if (distToIdeal <= 1200.f) { const float ratio = (distToIdeal - 600.f) / (1200.f - 600.f); positioning = 0.5f * (1.f - ratio) * 0.7f; }
+    else if (distToIdeal <= 2000.f) { const float ratio = (distToIdeal - 1200.f) / (2000.f - 1200.f); positioning = -0.1f * ratio; }
+    else positioning = -0.3f;
+    // CalculateStrategicBoostReward :256-286: only the six large pads (z > 72) of CommonValues::BOOST_LOCATIONS, in table order
+    float bestBoost = 0.f;
+    for (int i = 0; i < 6; i++) {
+        const V3 bpz = v3((i & 1) ? ((i == 3) ? 3584.f : 3072.f) : ((i == 2) ? -3584.f : -3072.f), (i < 2) ? -4096.f : ((i < 4) ? 0.f : 4096.f), 73.f);
+        const float distToBoost = len(p.pos - bpz);
+        const float accessibility = 1.f - rs_clampf(distToBoost / 1500.f, 0.f, 1.f);
+        // CalculateBoostStrategicValue :288-300
+        const float distToBall = len(bpz - ballPos);
+        const bool corner = fabsf(bpz.x) > 2500.f && fabsf(bpz.y) > 3500.f;
+        const float baseValue = corner ? 0.8f : 0.6f;
+        const float proximity = 1.f - rs_clampf(distToBall / 3000.f, 0.f, 1.f);
+        const float strategic = baseValue * (0.3f + proximity * 0.7f);
+        // CalculateBoostDenialValue :302-307
+        const float deny = rs_clampf(1.f - (len(oppCom - bpz) / 2000.f), 0.f, 0.3f);
+        const float total = accessibility * (strategic + deny);
+        bestBoost = (bestBoost > total) ? bestBoost : total;
+    }
+    float boostLevel = 1.f;
+    if (p.boost < 30.f) boostLevel = 1.5f; else if (p.boost > 80.f) boostLevel = 0.5f;
+    const float boostReward = (bestBoost * boostLevel) * 0.25f;
+    // CalculateRotationPreparation :309-325 (+ CalculateOptimalSupportPosition :327-342)
+    const V3 mateToGoal = rs_normalized(ownGoal - mate.pos);
+    const V3 perp = rs_normalized(v3(-mateToGoal.y, mateToGoal.x, 0.f));
+    const V3 goalOff = v3(mateToGoal.x * 800.f, mateToGoal.y * 800.f, mateToGoal.z * 800.f);
+    const V3 perpOff = v3(perp.x * 600.f, perp.y * 600.f, perp.z * 600.f);
+    const V3 support = (mate.pos + goalOff) + perpOff;
+    const float supportReadiness = 1.f - rs_clampf(len(p.pos - support) / 1000.f, 0.f, 1.f);
+    const float align0 = dot(rs_normalized(p.vel), rs_normalized(support - p.pos));
+    const float velAlign = (0.f > align0) ? 0.f : align0;
+    const float rotation = (supportReadiness * 0.7f + velAlign * 0.3f) * r.params[3];
+    // CalculateOpponentAwareness :344-353
+    const float awareAngle = dot(rs_normalized(oppCom - p.pos), playerToBall);
+    const float awareness = rs_clampf(awareAngle * 0.5f + 0.5f, 0.f, 1.f) * 0.1f;
+    // CalculateDynamicCampingPenalty :355-366
+    const float distToGoal = len(p.pos - ownGoal);
+    float minDist = 800.f;
+    if (len(ballPos - ownGoal) < 2000.f) minDist *= 0.7f;
+    float camping = 0.f;
+    if (distToGoal < minDist) camping = -0.4f * (1.f - (distToGoal / minDist));
+    camping *= 0.05f;
+    const float totalReward = positioning + boostReward + rotation + awareness + camping;
+    return rs_clampf(totalReward, -0.8f, 0.8f);
+}
+
 // one reward function for one player (CommonRewards.h); `slot` indexes A.players
 GGL_HD float reward_value(const ArenaDev& A, const RewardCfg& r, const PlayerView& p, int slot, bool goalScored, V3 ballPos, V3 ballVel) {
     const EnvPlayer& ep = A.players[slot];
@@ -75,6 +198,7 @@ GGL_HD float reward_value(const ArenaDev& A, const RewardCfg& r, const PlayerVie
         if (hit < r.params[0]) return 0.f;
         return fminf(1.f, hit / r.params[1]);
     }
+    case GGL_REW_KICKOFF_PROXIMITY_2V2: return reward_kickoff_proximity_2v2(A, r, p, ballPos, ballVel);
     default: return 0.f;
     }
 }

@@ -162,6 +162,14 @@ class StrongTouchReward : public Reward { public:       // :180-202 (KPH -> uu/s
         d.kind = GGL_REW_STRONG_TOUCH; d.params[0] = minRewardedVel; d.params[1] = maxRewardedVel; return true; }
     std::string GetName() const override { return "StrongTouchReward"; } };
 
+class KickoffProximityReward2v2Enhanced : public Reward { public:     // Rewards/KickoffProximityReward2v2Enhanced.h:7-367
+    float goerReward = 1.2f, cheaterReward = 0.6f, dynamicWeight = 0.3f, rotationPrepWeight = 0.2f;
+    bool Describe(ggl_reward_desc& d) const override {
+        d.kind = GGL_REW_KICKOFF_PROXIMITY_2V2;
+        d.params[0] = goerReward; d.params[1] = cheaterReward; d.params[2] = dynamicWeight; d.params[3] = rotationPrepWeight;
+        return true; }
+    std::string GetName() const override { return "KickoffProximityReward2v2Enhanced"; } };
+
 // ZeroSumReward (ZeroSumReward.h:7-33). In the EnvSet path the reference calls GetReward() per player, which the wrapper
 // forwards to its child untouched (confirmed by running the compiled reference): a pass-through.
 class ZeroSumReward : public Reward { public:

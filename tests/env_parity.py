@@ -79,6 +79,8 @@ def _compare_steps(ref, dev, steps, rng, res, ppa, tick_skip=8, verbose=False, t
         res["obs"] = max(res["obs"], float(np.max(np.abs(obs_d - obs_r)[live_p]))) if live_p.any() else res["obs"]
         res["obs_bad"] += int((~ok)[live_p].sum())
         res["rew"] = max(res["rew"], float(np.max(np.abs(rew_d - rew_r)[clean_p]))) if clean_p.any() else res["rew"]
+        res["rew_abs_max"] = max(res["rew_abs_max"], float(np.abs(rew_r).max()))
+        res["rew_nonzero"] += int((rew_r != 0).sum())
         res["mask_mismatch"] += int((masks_d != masks_r)[clean_p].sum())
         res["term_mismatch"] += int((term_d != term_r)[clean].sum())
         res["event_mismatch"] += int((ev_d != ev_r)[clean_p].sum())
@@ -123,7 +125,7 @@ def _compare_steps(ref, dev, steps, rng, res, ppa, tick_skip=8, verbose=False, t
 def _new_result():
     return {"obs": 0.0, "rew": 0.0, "mask_mismatch": 0, "term_mismatch": 0, "event_mismatch": 0, "obs_bad": 0, "steps": 0,
             "terminals_seen": 0, "goals_seen": 0, "touches": 0, "bad_arenas": 0, "events": np.zeros(9, np.int64),
-            "masks_with_jump_reset": 0, "arena_steps": 0, "bad_arena_steps": 0, "respawn_arena_steps": 0, "int_mismatch_on_bad_steps": 0}
+            "masks_with_jump_reset": 0, "arena_steps": 0, "bad_arena_steps": 0, "respawn_arena_steps": 0, "int_mismatch_on_bad_steps": 0, "rew_abs_max": 0.0, "rew_nonzero": 0}
 
 
 def run_env_steps(ggl, num_arenas=8, ppt=2, steps=40, seed=0, obs_kind=1, verbose=False, env_cls=None, **kw):

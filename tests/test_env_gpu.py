@@ -64,6 +64,17 @@ def test_all_stock_rewards_match(ggl):
     assert r["rew"] <= 2e-4 and r["mask_mismatch"] == 0 and r["obs_bad"] == 0, r
 
 
+def test_kickoff_proximity_reward_matches_reference(ggl):
+    """KickoffProximityReward2v2Enhanced (Rewards/KickoffProximityReward2v2Enhanced.h): goer and cheater branches off
+    the kickoff, 2v2 and (the reference accepts it) 3v3, against the compiled reference."""
+    A = ggl.abi
+    for ppt in (2, 3):
+        r = env_parity.run_env_steps(ggl, num_arenas=8, ppt=ppt, steps=12, seed=7 + ppt, obs_kind=1,
+                                     rewards=[(A.REW_KICKOFF_PROXIMITY_2V2, 1.0, [1.2, 0.6, 0.3, 0.2]), (A.REW_TOUCH_BALL, 0.5)])
+        assert r["rew"] <= 1e-5 and r["rew_nonzero"] > 20 and r["rew_abs_max"] > 0.1, r
+        assert r["mask_mismatch"] == 0 and r["obs_bad"] == 0, r
+
+
 def _scenario_states():
     """(name, init(st), controls(t, st)) scripted scenarios on a 1v1 arena."""
     def ball_bounce(st):

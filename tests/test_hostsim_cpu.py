@@ -180,3 +180,12 @@ def test_free_box_of_the_world_touches_no_triangle():
         v = out.reshape(3, 3)
         mn, mx = v.min(0) - 0.1, v.max(0) + 0.1
         assert not ((mx > lo).all() and (mn < hi).all()), (i, v, box)
+
+
+def test_kickoff_proximity_reward_matches_reference():
+    """KickoffProximityReward2v2Enhanced (row a8): goer / cheater branches off the kickoff, 2v2, against the compiled reference."""
+    A = oracle_ref.abi
+    r = env_parity.run_env_steps(None, num_arenas=6, ppt=2, steps=12, seed=7, obs_kind=1, env_cls=hb.HostEnvSet,
+                                 rewards=[(A.REW_KICKOFF_PROXIMITY_2V2, 1.0, [1.2, 0.6, 0.3, 0.2])])
+    assert r["rew"] <= 1e-5 and r["rew_nonzero"] > 20 and r["rew_abs_max"] > 0.1, r
+    assert r["mask_mismatch"] == 0 and r["obs_bad"] == 0, r
