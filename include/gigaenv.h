@@ -277,6 +277,22 @@ int  ggl_gae_compute(const float* d_rews, const int8_t* d_terminals, const float
                      float* d_out_advantages, float* d_out_returns, float* d_out_target_values,
                      float* d_out_clip_portion, int32_t* d_out_trunc_count,
                      void* d_workspace, void* stream);
+/* ggl_gae_compute without a workspace argument and without any allocation. No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses
+ * that forbid it). The scan's scratch (tile look-back records and TRUNCATED counters) lives in a file-scope
+ * `static __device__ __align__(256)` array of GGL_GAE_STATIC_SCRATCH_BYTES that every GPU loading the library holds until exit;
+ * its device address is resolved once per device with cudaGetSymbolAddress. L > GGL_GAE_STATIC_MAX_L returns GGL_ERR_INVALID
+ * with a message. The call makes no cudaMalloc / cudaFree / allocating library call; inputs and outputs are the caller's, same
+ * meaning and alignment rules as ggl_gae_compute. All calls on one device share the array: the part that must start at zero
+ * is cleared on `stream` at the start of every call, and two calls that overlap on the GPU (different streams, no ordering
+ * between them) race on it - serialise them. */
+#define GGL_GAE_STATIC_MAX_L          (1ll << 24)     /* elements per call (4096 tiles of 4096) */
+#define GGL_GAE_STATIC_SCRATCH_BYTES  (128 * 1024)    /* per GPU, resident until the library is unloaded */
+int  ggl_gae_compute_static(const float* d_rews, const int8_t* d_terminals, const float* d_val_preds,
+                            const float* d_trunc_val_preds, int64_t L, int64_t K,
+                            float gamma, float lambda, float return_std, float clip_range,
+                            float* d_out_advantages, float* d_out_returns, float* d_out_target_values,
+                            float* d_out_clip_portion, int32_t* d_out_trunc_count, void* stream);
 /* Host-buffer wrapper (the reference-facing call: GAE::Compute takes CPU tensors). */
 int  ggl_gae_compute_host(const float* h_rews, const int8_t* h_terminals, const float* h_val_preds,
                           const float* h_trunc_val_preds, int64_t L, int64_t K,

@@ -691,6 +691,46 @@ extern "C" int ggl_gae_compute(const float* d_rews, const int8_t* d_terminals, c
     return launch<false, false, false>(p, grid, s);
 }
 
+// ---- allocation-free variant (no counterpart in the reference) ----
+// The scan's scratch in a file-scope device array: every GPU that loads the library holds GGL_GAE_STATIC_SCRATCH_BYTES until
+// exit. In HOST code the name `g_gae_static_scratch` is only the host-side stand-in of the symbol, not a device address: the
+// address a kernel may use comes from cudaGetSymbolAddress, resolved once per device with that device current.
+static __device__ __align__(256) unsigned char g_gae_static_scratch[GGL_GAE_STATIC_SCRATCH_BYTES];
+namespace {
+void* g_static_scratch_ptr[kMaxDevices];          // device address of the array on device i, null until resolved
+std::mutex g_static_scratch_mutex;
+}  // namespace
+
+extern "C" int ggl_gae_compute_static(const float* d_rews, const int8_t* d_terminals, const float* d_val_preds,
+                                      const float* d_trunc_val_preds, int64_t L, int64_t K,
+                                      float gamma, float lambda, float return_std, float clip_range,
+                                      float* d_out_advantages, float* d_out_returns, float* d_out_target_values,
+                                      float* d_out_clip_portion, int32_t* d_out_trunc_count, void* stream) {
+    if (L > (int64_t)GGL_GAE_STATIC_MAX_L || (L > 0 && ws_layout(L).total > (size_t)GGL_GAE_STATIC_SCRATCH_BYTES)) {
+        ggl::set_error("ggl_gae_compute_static: L = %lld exceeds GGL_GAE_STATIC_MAX_L = %lld (static scratch of %d bytes); use "
+                       "ggl_gae_compute with a caller workspace", (long long)L, (long long)GGL_GAE_STATIC_MAX_L, (int)GGL_GAE_STATIC_SCRATCH_BYTES);
+        return GGL_ERR_INVALID;
+    }
+    int dev = 0;
+    GGL_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevices) { ggl::set_error("ggl_gae_compute_static: device ordinal %d out of range", dev); return GGL_ERR_INVALID; }
+    void* scratch = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(g_static_scratch_mutex);
+        if (!g_static_scratch_ptr[dev]) {
+            void* ptr = nullptr;
+            GGL_CUDA(cudaGetSymbolAddress(&ptr, g_gae_static_scratch));
+            if (!ptr) { ggl::set_error("ggl_gae_compute_static: cudaGetSymbolAddress returned a null address"); return GGL_ERR_CUDA; }
+            g_static_scratch_ptr[dev] = ptr;
+        }
+        scratch = g_static_scratch_ptr[dev];
+    }
+    // ggl_gae_compute clears the part of the scratch that must start at zero (header + look-back records) on `stream` before
+    // its kernels and allocates nothing itself (memset, attribute queries and launches only)
+    return ggl_gae_compute(d_rews, d_terminals, d_val_preds, d_trunc_val_preds, L, K, gamma, lambda, return_std, clip_range,
+                           d_out_advantages, d_out_returns, d_out_target_values, d_out_clip_portion, d_out_trunc_count, scratch, stream);
+}
+
 extern "C" int ggl_gae_compute_host(const float* h_rews, const int8_t* h_terminals, const float* h_val_preds,
                                     const float* h_trunc_val_preds, int64_t L, int64_t K,
                                     float gamma, float lambda, float return_std, float clip_range,
