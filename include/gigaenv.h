@@ -44,6 +44,8 @@ extern "C" {
 #define GGL_NUM_ACTIONS   90     /* DefaultAction table */
 #define GGL_MAX_REWARDS   16
 #define GGL_MAX_TERMINALS 4
+#define GGL_MAX_SETTER_CHILDREN 4 /* CombinedState children */
+#define GGL_MAX_OBS_PLAYERS 6    /* upper bound of DefaultObsPadded::maxPlayers (players per team the row has room for) */
 
 typedef enum ggl_status {
     GGL_OK = 0,
@@ -57,7 +59,10 @@ typedef enum ggl_status {
 
 typedef enum ggl_obs_kind {
     GGL_OBS_DEFAULT = 0,    /* RLGC::DefaultObs   (ObsBuilders/DefaultObs.cpp:4-54)   51+19*P floats */
-    GGL_OBS_ADVANCED = 1    /* RLGC::AdvancedObs  (ObsBuilders/AdvancedObs.cpp:193-270) 51+29*P floats */
+    GGL_OBS_ADVANCED = 1,   /* RLGC::AdvancedObs  (ObsBuilders/AdvancedObs.cpp:193-270) 51+29*P floats */
+    GGL_OBS_DEFAULT_PADDED = 2 /* RLGC::DefaultObsPadded (ObsBuilders/DefaultObsPadded.cpp:4-68) 51+38*maxPlayers floats: self, then
+                               maxPlayers-1 teammate rows and maxPlayers opponent rows, zero rows for absent players, each list
+                               std::shuffle'd per call with the arena's stream (the reference: the calling thread's engine) */
 } ggl_obs_kind;
 
 typedef enum ggl_reward_kind {   /* Rewards/CommonRewards.h */
@@ -100,8 +105,19 @@ typedef struct ggl_terminal_desc {
 
 typedef enum ggl_state_setter_kind {
     GGL_SETTER_KICKOFF = 0,     /* StateSetters/KickoffState.h → Arena::ResetToRandomKickoff (Arena.cpp:112-216) */
-    GGL_SETTER_INJECTED = 1     /* reset states are supplied by the host through ggl_envset_set_reset_state */
+    GGL_SETTER_INJECTED = 1,    /* reset states are supplied by the host through ggl_envset_set_reset_state */
+    GGL_SETTER_FUZZED_KICKOFF = 2, /* StateSetters/FuzzedKickoffState.h:7-27: kickoff, then every car's position +- 0.1 uu per axis */
+    GGL_SETTER_RANDOM = 3,      /* StateSetters/RandomState.cpp:11-62, flags = ggl_random_state_flags */
+    GGL_SETTER_COMBINED = 4     /* StateSetters/CombinedState.h:10-46: one child per reset, drawn by weight */
 } ggl_state_setter_kind;
+typedef enum ggl_random_state_flags {   /* RandomState ctor arguments (RandomState.h:9-11) */
+    GGL_RANDOM_BALL_SPEED = 1, GGL_RANDOM_CAR_SPEED = 2, GGL_RANDOM_CARS_ON_GROUND = 4
+} ggl_random_state_flags;
+typedef struct ggl_setter_child {  /* one (StateSetter*, weight) pair of CombinedState's ctor */
+    int32_t kind;               /* GGL_SETTER_KICKOFF, _FUZZED_KICKOFF, _RANDOM or _INJECTED */
+    int32_t flags;              /* GGL_SETTER_RANDOM: ggl_random_state_flags */
+    float   weight;             /* >= 0, finite (CombinedState.h:25-27) */
+} ggl_setter_child;
 
 /* Arena collision meshes: the reference's .cmf layout (CollisionMeshFile.cpp:11-35):
  * int32 numTris, int32 numVerts, int32 tri[numTris][3], float vert[numVerts][3] (Bullet units). */
@@ -128,6 +144,10 @@ typedef struct ggl_envset_desc {
     int32_t slot_order_reversed;/* default players[] slot order: 1 = reverse AddCar order, 0 = AddCar order. The reference's
                                    order is the iteration order of std::unordered_set<Car*> — it depends on heap
                                    addresses and differs per arena, so it is DATA: override with ggl_envset_set_slot_order */
+    int32_t obs_max_players;    /* GGL_OBS_DEFAULT_PADDED: DefaultObsPadded::maxPlayers, players_per_team..GGL_MAX_OBS_PLAYERS */
+    int32_t state_setter_flags; /* GGL_SETTER_RANDOM: ggl_random_state_flags */
+    int32_t num_setter_children;/* GGL_SETTER_COMBINED: 1..GGL_MAX_SETTER_CHILDREN */
+    ggl_setter_child setter_children[GGL_MAX_SETTER_CHILDREN];
 } ggl_envset_desc;
 
 /* ---- host-visible state (mirrors RocketSim CarState/BallState/BoostPadState + hidden wheel state) ---- */
@@ -228,6 +248,14 @@ int  ggl_envset_contact_overflow(ggl_envset* env, uint64_t* out_dropped);
 /* players[] slot order of every arena: car_ids[num_players], car_ids[arena*P + slot] = carId (1-based AddCar order)
  * occupying GameState.players[slot] (GameState.cpp:82-86). Takes effect at the next reset/step. */
 int  ggl_envset_set_slot_order(ggl_envset* env, const int32_t* h_car_ids);
+/* The arena's random stream: one std::minstd_rand0 (= libstdc++'s std::default_random_engine, the reference's engine type,
+ * Math.cpp:59-64) per arena, seeded from desc.seed, drawn from in the reference's order by everything on the path that is
+ * random there: the respawn slot (Car.cpp:48), the kickoff shuffle (Arena.cpp:136), FuzzedKickoffState / RandomState /
+ * CombinedState, DefaultObsPadded's two shuffles per row. The reference shares one time-seeded engine per worker thread; with
+ * one arena per thread and the same engine state both sides draw the same numbers (how the parity tests pin these plugins).
+ * state is the engine's raw state, 1..2147483646; arena = -1 in set_rng sets every arena. */
+int  ggl_envset_set_rng(ggl_envset* env, int arena, uint32_t state);
+int  ggl_envset_get_rng(ggl_envset* env, int arena, uint32_t* out_state);
 /* state the next reset of `arena` will install when state_setter == GGL_SETTER_INJECTED */
 int  ggl_envset_set_reset_state(ggl_envset* env, int arena, const ggl_arena_state* host_state);
 /* raw Arena::Step(ticks) on every arena with the cars' current `controls` (no env bookkeeping) */

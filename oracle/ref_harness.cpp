@@ -16,6 +16,10 @@
 #include <RLGymCPP/TerminalConditions/GoalScoreCondition.h>
 #include <RLGymCPP/TerminalConditions/NoTouchCondition.h>
 #include <RLGymCPP/StateSetters/KickoffState.h>
+#include <RLGymCPP/StateSetters/FuzzedKickoffState.h>
+#include <RLGymCPP/StateSetters/RandomState.h>
+#include <RLGymCPP/StateSetters/CombinedState.h>
+#include <RLGymCPP/ObsBuilders/DefaultObsPadded.h>
 #include <RLGymCPP/ThreadPool.h>
 
 #include "gigaenv.h"
@@ -282,6 +286,17 @@ void ref_seed(uint64_t seed) {
     g_ThreadPool.WaitUntilDone();
 }
 
+// Where RocketSim's thread-local engine (Math.cpp:59-64) stands: the NEXT value a copy of it would yield (the state itself is
+// private; next = 16807 * state mod 2^31-1 identifies it). which = 0 the calling thread, 1 = the pool's worker (meaningful with
+// ref_set_threads(1)). Setting it: ref_seed(state) - minstd_rand0::seed(s) installs s itself for 1 <= s <= 2147483646.
+uint32_t ref_rng_peek(int which) {
+    uint32_t out = 0;
+    auto read = [&out]() { std::default_random_engine copy = RocketSim::Math::GetRandEngine(); out = (uint32_t)copy(); };
+    if (which == 0) read();
+    else { g_ThreadPool.StartJobAsync(read); g_ThreadPool.WaitUntilDone(); }
+    return out;
+}
+
 void* ref_envset_create(const ggl_envset_desc* d) {
     try {
         auto* env = new RefEnv();
@@ -310,14 +325,27 @@ void* ref_envset_create(const ggl_envset_desc* d) {
                 if (desc.terminals[i].kind == GGL_TERM_GOAL_SCORE) r.terminalConditions.push_back(new GoalScoreCondition());
                 else r.terminalConditions.push_back(new NoTouchCondition(desc.terminals[i].params[0]));
             }
-            r.obsBuilder = (desc.obs_kind == GGL_OBS_ADVANCED) ? (ObsBuilder*)new AdvancedObs() : (ObsBuilder*)new DefaultObs();
+            if (desc.obs_kind == GGL_OBS_DEFAULT_PADDED) r.obsBuilder = new DefaultObsPadded(desc.obs_max_players);
+            else r.obsBuilder = (desc.obs_kind == GGL_OBS_ADVANCED) ? (ObsBuilder*)new AdvancedObs() : (ObsBuilder*)new DefaultObs();
             r.actionParser = new DefaultAction();
-            if (desc.state_setter == GGL_SETTER_INJECTED) {
-                auto* s = new InjectedStateSetter();
-                s->env = env; s->arenaIdx = index;
-                r.stateSetter = s;
+            auto makeSetter = [env, index](int kind, int flags) -> StateSetter* {
+                if (kind == GGL_SETTER_INJECTED) {
+                    auto* s = new InjectedStateSetter();
+                    s->env = env; s->arenaIdx = index;
+                    return s;
+                }
+                if (kind == GGL_SETTER_FUZZED_KICKOFF) return new FuzzedKickoffState();
+                if (kind == GGL_SETTER_RANDOM)
+                    return new RandomState((flags & GGL_RANDOM_BALL_SPEED) != 0, (flags & GGL_RANDOM_CAR_SPEED) != 0, (flags & GGL_RANDOM_CARS_ON_GROUND) != 0);
+                return new KickoffState();
+            };
+            if (desc.state_setter == GGL_SETTER_COMBINED) {
+                std::vector<std::pair<StateSetter*, float>> kids;
+                for (int i = 0; i < desc.num_setter_children; i++)
+                    kids.push_back({makeSetter(desc.setter_children[i].kind, desc.setter_children[i].flags), desc.setter_children[i].weight});
+                r.stateSetter = new CombinedState(kids);
             } else {
-                r.stateSetter = new KickoffState();
+                r.stateSetter = makeSetter(desc.state_setter, desc.state_setter_flags);
             }
             r.userInfo = nullptr;
             return r;

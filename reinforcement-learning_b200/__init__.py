@@ -73,6 +73,8 @@ def lib():
             L.ggl_envset_set_reset_state.argtypes = [C.c_void_p, C.c_int, C.POINTER(abi.ArenaState)]
             L.ggl_envset_get_contacts.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int]
             L.ggl_envset_set_slot_order.argtypes = [C.c_void_p, C.c_void_p]
+            L.ggl_envset_set_rng.argtypes = [C.c_void_p, C.c_int, C.c_uint32]
+            L.ggl_envset_get_rng.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_uint32)]
             L.ggl_arena_step.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
             L.ggl_envset_random_actions.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
             L.ggl_envset_step_host.argtypes = [C.c_void_p] * 6
@@ -311,6 +313,15 @@ class EnvSet:
     def set_slot_order(self, car_ids):
         a = np.ascontiguousarray(car_ids, np.int32)
         _check(lib().ggl_envset_set_slot_order(self.h, a.ctypes.data))
+
+    def set_rng(self, arena, state):
+        """state of the arena's std::minstd_rand0 stream (1..2147483646); arena -1 = every arena"""
+        _check(lib().ggl_envset_set_rng(self.h, int(arena), int(state)))
+
+    def get_rng(self, arena):
+        s = C.c_uint32()
+        _check(lib().ggl_envset_get_rng(self.h, int(arena), C.byref(s)))
+        return int(s.value)
 
 
 class TrajectoryStore:

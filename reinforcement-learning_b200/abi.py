@@ -7,8 +7,10 @@ GGL_NUM_PADS = 34
 GGL_NUM_ACTIONS = 90
 GGL_MAX_REWARDS = 16
 GGL_MAX_TERMINALS = 4
+GGL_MAX_SETTER_CHILDREN = 4
+GGL_MAX_OBS_PLAYERS = 6
 
-OBS_DEFAULT, OBS_ADVANCED = 0, 1
+OBS_DEFAULT, OBS_ADVANCED, OBS_DEFAULT_PADDED = 0, 1, 2
 
 (REW_PLAYER_GOAL, REW_ASSIST, REW_SHOT, REW_SHOT_PASS, REW_SAVE, REW_BUMP, REW_BUMPED_PENALTY, REW_DEMO,
  REW_DEMOED_PENALTY, REW_GOAL, REW_VELOCITY, REW_VELOCITY_BALL_TO_GOAL, REW_VELOCITY_PLAYER_TO_BALL,
@@ -16,7 +18,8 @@ OBS_DEFAULT, OBS_ADVANCED = 0, 1
  REW_TOUCH_ACCEL, REW_STRONG_TOUCH, REW_KICKOFF_PROXIMITY_2V2) = range(23)
 
 TERM_GOAL_SCORE, TERM_NO_TOUCH = 0, 1
-SETTER_KICKOFF, SETTER_INJECTED = 0, 1
+SETTER_KICKOFF, SETTER_INJECTED, SETTER_FUZZED_KICKOFF, SETTER_RANDOM, SETTER_COMBINED = 0, 1, 2, 3, 4
+RANDOM_BALL_SPEED, RANDOM_CAR_SPEED, RANDOM_CARS_ON_GROUND = 1, 2, 4
 
 
 class RewardDesc(C.Structure):
@@ -31,6 +34,10 @@ class MeshBlob(C.Structure):
     _fields_ = [("data", C.c_void_p), ("size", C.c_size_t)]
 
 
+class SetterChild(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("flags", C.c_int32), ("weight", C.c_float)]
+
+
 class EnvSetDesc(C.Structure):
     _fields_ = [
         ("device", C.c_int32), ("num_arenas", C.c_int32), ("players_per_team", C.c_int32),
@@ -39,6 +46,8 @@ class EnvSetDesc(C.Structure):
         ("num_terminals", C.c_int32), ("terminals", TerminalDesc * GGL_MAX_TERMINALS),
         ("state_setter", C.c_int32), ("num_meshes", C.c_int32), ("meshes", C.POINTER(MeshBlob)),
         ("seed", C.c_uint64), ("slot_order_reversed", C.c_int32),
+        ("obs_max_players", C.c_int32), ("state_setter_flags", C.c_int32), ("num_setter_children", C.c_int32),
+        ("setter_children", SetterChild * GGL_MAX_SETTER_CHILDREN),
     ]
 
 
@@ -115,8 +124,9 @@ class EnvSetViews(C.Structure):
 
 def make_desc(num_arenas, players_per_team, obs_kind=OBS_ADVANCED, rewards=None, terminals=None,
               tick_skip=8, action_delay=7, state_setter=SETTER_KICKOFF, meshes=None, seed=0, device=0,
-              slot_order_reversed=1):
-    """rewards: list of (kind, weight[, params[, zero_sum]]); terminals: list of (kind[, params]).
+              slot_order_reversed=1, obs_max_players=0, state_setter_flags=0, setter_children=None):
+    """rewards: list of (kind, weight[, params[, zero_sum]]); terminals: list of (kind[, params]);
+    setter_children (SETTER_COMBINED): list of (kind, weight[, flags]).
     Returns (desc, keepalive) — keepalive holds the mesh buffers the desc points into."""
     d = EnvSetDesc()
     d.device = device
@@ -157,4 +167,12 @@ def make_desc(num_arenas, players_per_team, obs_kind=OBS_ADVANCED, rewards=None,
     d.meshes = C.cast(arr, C.POINTER(MeshBlob))
     d.seed = seed
     d.slot_order_reversed = slot_order_reversed
+    d.obs_max_players = obs_max_players
+    d.state_setter_flags = state_setter_flags
+    setter_children = setter_children or []
+    d.num_setter_children = len(setter_children)
+    for i, ch in enumerate(setter_children):
+        d.setter_children[i].kind = ch[0]
+        d.setter_children[i].weight = ch[1]
+        d.setter_children[i].flags = ch[2] if len(ch) > 2 else 0
     return d, keep

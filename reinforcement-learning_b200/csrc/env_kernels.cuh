@@ -67,10 +67,19 @@ __device__ __forceinline__ ExecGroup make_exec() {
 // obs row + mask row (+ slot identity) of one player
 __device__ __forceinline__ void write_player_rows(const ArenaDev& A, const EnvCfg& cfg, const EnvDevPtrs& P, int arena, int slot) {
     const int row = arena * cfg.numCars + slot;
-    build_obs_row(A, cfg, slot, P.obs + (size_t)row * cfg.obsSize);
+    uint32_t permMates = 0, permOpps = 0;
+    if (cfg.obsKind == GGL_OBS_DEFAULT_PADDED) padded_obs_draws_upto(A.rng, cfg.obsMaxPlayers, slot, permMates, permOpps);
+    build_obs_row(A, cfg, slot, P.obs + (size_t)row * cfg.obsSize, permMates, permOpps);
     action_mask_row(A.cars[A.slotCar[slot]], P.actionTable, P.masks + (size_t)row * kNumActions);
     P.slotCarId[row] = (int)A.cars[A.slotCar[slot]].id;
     P.slotTeam[row] = A.cars[A.slotCar[slot]].team;
+}
+
+// after every row of the arena is out: the stream moves past the draws of all of them (DefaultObsPadded only)
+__device__ __forceinline__ void rows_advance_rng(ArenaDev& A, const EnvCfg& cfg) {
+    if (cfg.obsKind != GGL_OBS_DEFAULT_PADDED) return;
+    uint32_t pm, po;
+    A.rng = padded_obs_draws_upto(A.rng, cfg.obsMaxPlayers, A.numCars - 1, pm, po);
 }
 
 // ---- blob staging: the whole warp moves each of its arenas with 16-byte accesses (512 contiguous bytes per instruction)
@@ -111,14 +120,7 @@ __global__ void __launch_bounds__(kBlock) env_reset_kernel(EnvCfg cfg, EnvDevPtr
     const bool doReset = force == 1 || (force >= 2 && arena == force - 2) || (force == 0 && A.terminal != 0);
     if (!doReset) return;
     if (ex.lane() == 0) {
-        if (cfg.stateSetter == GGL_SETTER_INJECTED && P.resetArenas && P.resetArenas[arena].hasResetState) {
-            const ArenaDev& R = P.resetArenas[arena];
-            A.tickCount = R.tickCount; A.ball = R.ball;
-            for (int c = 0; c < A.numCars; c++) A.cars[c] = R.cars[c];
-            for (int p = 0; p < kNumPads; p++) A.pads[p] = R.pads[p];
-        } else {
-            arena_reset_kickoff(A);
-        }
+        arena_state_set(A, cfg, P.resetArenas ? &P.resetArenas[arena] : nullptr);
         env_after_state_set(A);
         P.terminals[arena] = 0;
     }
@@ -126,6 +128,10 @@ __global__ void __launch_bounds__(kBlock) env_reset_kernel(EnvCfg cfg, EnvDevPtr
     if (ex.lane() < A.numCars) {
         write_player_rows(A, cfg, P, arena, ex.lane());
         for (int e = 0; e < 9; e++) P.events[(size_t)(arena * cfg.numCars + ex.lane()) * 9 + e] = 0;
+    }
+    if (cfg.obsKind == GGL_OBS_DEFAULT_PADDED) {
+        ex.sync();
+        if (ex.lane() == 0) rows_advance_rng(A, cfg);
     }
 }
 
@@ -194,6 +200,7 @@ __global__ void __launch_bounds__(32 * kMaxWarps, 1) env_step_kernel(EnvCfg cfg,
             ex.sync();
             if (ex.lane() == 0) {
                 env_end_step(A);
+                rows_advance_rng(A, cfg);
                 if (P.stepCost) P.stepCost[arena] = A.stepCost;
             }
             GGL_PH(12);

@@ -27,12 +27,53 @@ struct TerminalCfg {
     int kind;
     float params[2];
 };
+struct SetterCfg {
+    int kind, flags;
+    float cumWeight;        // CombinedState::cumulativeWeights (CombinedState.h:29-31)
+};
 struct EnvCfg {
     int numArenas, playersPerTeam, numCars, tickSkip, actionDelay, obsKind, obsSize;
     int numRewards, numTerminals, stateSetter;
+    int obsMaxPlayers, setterFlags, numSetterChildren;
+    float setterTotalWeight;
+    SetterCfg setterChildren[GGL_MAX_SETTER_CHILDREN];
     RewardCfg rewards[kMaxRewards];
     TerminalCfg terminals[kMaxTerminals];
 };
+
+// floats per obs row (DefaultObs.cpp:4-54, AdvancedObs.cpp:193-270, DefaultObsPadded.cpp:4-68)
+inline int env_obs_size(int kind, int cars, int maxPlayers) {
+    if (kind == GGL_OBS_DEFAULT_PADDED) return 51 + 19 * 2 * maxPlayers;
+    return 51 + (kind == GGL_OBS_ADVANCED ? 29 : 19) * cars;
+}
+// obs / state-setter part of the descriptor -> EnvCfg (shared by the product and the host compile of the parity tests);
+// returns a message for a descriptor with no device implementation, nullptr when fine
+inline const char* env_cfg_plugins(EnvCfg& c, const ggl_envset_desc* d) {
+    c.obsKind = d->obs_kind; c.obsMaxPlayers = 0;
+    if (d->obs_kind == GGL_OBS_DEFAULT_PADDED) {
+        if (d->obs_max_players < d->players_per_team || d->obs_max_players > GGL_MAX_OBS_PLAYERS)
+            return "DefaultObsPadded: obs_max_players must be players_per_team..GGL_MAX_OBS_PLAYERS (DefaultObsPadded.cpp:40-44)";
+        c.obsMaxPlayers = d->obs_max_players;
+    } else if (d->obs_kind != GGL_OBS_DEFAULT && d->obs_kind != GGL_OBS_ADVANCED) {
+        return "unsupported obs kind";
+    }
+    c.obsSize = env_obs_size(d->obs_kind, 2 * d->players_per_team, c.obsMaxPlayers);
+    c.stateSetter = d->state_setter; c.setterFlags = d->state_setter_flags; c.numSetterChildren = 0; c.setterTotalWeight = 0.f;
+    if (d->state_setter < GGL_SETTER_KICKOFF || d->state_setter > GGL_SETTER_COMBINED) return "unsupported state setter kind";
+    if (d->state_setter == GGL_SETTER_COMBINED) {
+        if (d->num_setter_children < 1 || d->num_setter_children > GGL_MAX_SETTER_CHILDREN)
+            return "CombinedState: 1..GGL_MAX_SETTER_CHILDREN children";
+        c.numSetterChildren = d->num_setter_children;
+        for (int i = 0; i < d->num_setter_children; i++) {
+            const ggl_setter_child& ch = d->setter_children[i];
+            if (ch.kind < GGL_SETTER_KICKOFF || ch.kind >= GGL_SETTER_COMBINED) return "CombinedState: unsupported child kind";
+            if (!(ch.weight >= 0.f) || ch.weight > 3.0e38f) return "CombinedState: negative or invalid weight (CombinedState.h:25-27)";
+            c.setterTotalWeight += ch.weight;
+            c.setterChildren[i].kind = ch.kind; c.setterChildren[i].flags = ch.flags; c.setterChildren[i].cumWeight = c.setterTotalWeight;
+        }
+    }
+    return nullptr;
+}
 
 // ---------------------------------------------------------------------------------------------- DefaultAction
 // 24 ground actions then 66 air actions; index -> (throttle, steer, pitch, yaw, roll, jump, boost, handbrake)

@@ -88,23 +88,18 @@ GGL_HD void car_set_spawn(CarDev& c, V3 posUU, float yaw) {
     c.aabbMin = c.aabbMax = v3(0, 0, 0);
 }
 
-// Arena::ResetToRandomKickoff (Arena.cpp:112-216). The permutation comes from the arena's own minstd stream
-// (Fisher-Yates); the reference uses libstdc++'s std::shuffle on a time-seeded engine, so kickoff assignment is
-// "a" uniformly random permutation on both sides, not the same one (parity tests inject reset states instead).
+// Arena::ResetToRandomKickoff (Arena.cpp:112-216): std::shuffle of the five spawn slots on the arena's stream (the draws
+// libstdc++ makes, std_shuffle_nib), the i-th car of each team (in _cars = slot order) on slot order[i], orange mirrored.
 GGL_HD void arena_reset_kickoff(ArenaDev& A) {
     const float sx[5] = {-2048, 2048, -256, 256, 0}, sy[5] = {-2560, -2560, -3840, -3840, -4608};
     const float q = 0.78539816339744830962f;
     const float syaw[5] = {q * 1, q * 3, q * 2, q * 2, q * 2};
-    int order[5] = {0, 1, 2, 3, 4};
-    for (int i = 4; i > 0; i--) {
-        int j = (int)(minstd_next(A.rng) % (uint32_t)(i + 1));
-        int t = order[i]; order[i] = order[j]; order[j] = t;
-    }
+    const uint32_t order = std_shuffle_nib(A.rng, 5);
     int nb = 0, no = 0;
     for (int s = 0; s < A.numCars; s++) {
         CarDev& c = A.cars[A.slotCar[s]];
         int i = (c.team == 0) ? nb++ : no++;
-        int k = order[i < 5 ? i : 4];
+        int k = (int)nib_get(order, i < 5 ? i : 4);
         V3 pos = v3(sx[k], sy[k], rl::CAR_SPAWN_REST_Z);
         float yaw = syaw[k];
         if (c.team != 0) { pos = pos * v3(-1, -1, 1); yaw = (float)((double)yaw + 3.14159265358979323846); }
@@ -114,6 +109,102 @@ GGL_HD void arena_reset_kickoff(ArenaDev& A) {
     b.pos = v3(0, 0, rl::BALL_REST_Z) * kUU2BT; b.vel = v3(0, 0, 0); b.angVel = v3(0, 0, 0);
     b.velImpulseCache = v3(0, 0, 0); b.force = v3(0, 0, 0); b.torque = v3(0, 0, 0); b.updateCounter = 0;
     for (int p = 0; p < kNumPads; p++) { A.pads[p].isActive = 1; A.pads[p].cooldown = 0.f; A.pads[p].prevLockedCarId = 0; A.pads[p].curLockedCarId = 0; }
+}
+
+// FuzzedKickoffState::ResetArena (FuzzedKickoffState.h:17-26): kickoff, then per car in _cars order GetState (position back in
+// uu), += RandFloat(-0.1, 0.1) per axis x, y, z, SetState (Car.cpp:10-36: to Bullet units again, everything else as spawned)
+GGL_HD void arena_reset_fuzzed_kickoff(ArenaDev& A) {
+    arena_reset_kickoff(A);
+    for (int s = 0; s < A.numCars; s++) {
+        CarDev& c = A.cars[A.slotCar[s]];
+        V3 p = c.pos * kBT2UU;
+        p.x += rand_float(A.rng, -0.1f, 0.1f);
+        p.y += rand_float(A.rng, -0.1f, 0.1f);
+        p.z += rand_float(A.rng, -0.1f, 0.1f);
+        c.pos = p * kUU2BT;
+    }
+}
+
+// RLGC::Math::RandVec (RLGymCPP/Math.cpp:3-9): `Vec(RandFloat(x), RandFloat(y), RandFloat(z))`. The three calls are constructor
+// arguments, whose evaluation order the language leaves open; the reference as built here (g++, x86-64) evaluates them last to
+// first, so z is drawn first. The same holds for Angle(yaw, pitch, roll) and for the operands of `vec * RandFloat()` below
+// (all pinned by tests/test_setters_cpu.py against the compiled reference).
+GGL_HD V3 rand_vec(uint32_t& s, V3 lo, V3 hi) {
+    V3 r;
+    r.z = rand_float(s, lo.z, hi.z);
+    r.y = rand_float(s, lo.y, hi.y);
+    r.x = rand_float(s, lo.x, hi.x);
+    return r;
+}
+GGL_HD V3 rand_norm_vec(uint32_t& s) { return rs_normalized(rand_vec(s, v3(-1, -1, -1), v3(1, 1, 1))); }
+
+// RandomState::ResetArena (RandomState.cpp:11-62), draw for draw
+GGL_HD void arena_reset_random(ArenaDev& A, int flags) {
+    arena_reset_kickoff(A);
+    const float X_MAX = 3500, Y_MAX = 4000, Z_MAX = 1820, CAR_Z_MIN = 150;
+    const float PITCH_MAX = (float)(3.14159265358979323846 / 2), YAW_MAX = (float)3.14159265358979323846, ROLL_MAX = YAW_MAX, ANGVEL_MAX = 5.5f;
+    uint32_t& g = A.rng;
+    {
+        BallDev& b = A.ball;
+        V3 pos = rand_vec(g, v3(-X_MAX, -Y_MAX, 92.75f), v3(X_MAX, Y_MAX, Z_MAX));     // CommonValues::BALL_RADIUS
+        V3 vel = v3(0, 0, 0), av = v3(0, 0, 0);
+        if (flags & GGL_RANDOM_BALL_SPEED) {
+            const float speed = rand_float(g, 0.f, 4000.f);       // `RandNormVec() * RandFloat(..)`: the right operand is drawn first
+            vel = rand_norm_vec(g) * speed;
+            av = rand_vec(g, v3(-4, -4, -4), v3(4, 4, 4));
+        }
+        b.pos = pos * kUU2BT; b.vel = vel * kUU2BT; b.angVel = av;
+    }
+    for (int s = 0; s < A.numCars; s++) {
+        CarDev& c = A.cars[A.slotCar[s]];
+        V3 pos = rand_vec(g, v3(-X_MAX, -Y_MAX, CAR_Z_MIN), v3(X_MAX, Y_MAX, Z_MAX));
+        V3 vel = v3(0, 0, 0), av = v3(0, 0, 0);
+        if (flags & GGL_RANDOM_CAR_SPEED) {
+            (void)rand_vec(g, v3(-1, -1, -1), v3(1, 1, 1));              // randVelDir: drawn, never used (:41)
+            const float speed = rand_float(g, 0.f, rl::CAR_MAX_SPEED);
+            vel = rand_norm_vec(g) * speed;
+            av = rand_norm_vec(g) * ANGVEL_MAX;
+        }
+        float roll = rand_float(g, -ROLL_MAX, ROLL_MAX);
+        float pitch = rand_float(g, -PITCH_MAX, PITCH_MAX);
+        const float yaw = rand_float(g, -YAW_MAX, YAW_MAX);
+        const bool onGround = (flags & GGL_RANDOM_CARS_ON_GROUND) ? true : (rand_float(g, 0.f, 1.f) > 0.5f);
+        if (onGround) { pos.z = 17.f; pitch = 0.f; roll = 0.f; vel.z = 0.f; av = v3(0, 0, 0); }
+        const float boost = rand_float(g, 0.f, 100.f);
+        car_reset_state_defaults(c);
+        c.pos = pos * kUU2BT;
+        c.basis = m3_from_euler_ypr(yaw, -pitch, -roll);              // Angle::ToRotMat (MathTypes.cpp:73-78)
+        c.vel = vel * kUU2BT; c.angVel = av; c.boost = boost;
+        car_update_inertia(c);
+        c.aabbMin = c.aabbMax = v3(0, 0, 0);
+    }
+}
+
+GGL_HD void arena_run_setter(ArenaDev& A, int kind, int flags) {
+    if (kind == GGL_SETTER_FUZZED_KICKOFF) arena_reset_fuzzed_kickoff(A);
+    else if (kind == GGL_SETTER_RANDOM) arena_reset_random(A, flags);
+    else arena_reset_kickoff(A);
+}
+
+// The StateSetter call of EnvSet::ResetArena (EnvSet.cpp:276). `injected` = the host-supplied reset state of this arena or
+// null. CombinedState (CombinedState.h:34-45): f = RandFloat(0, totalWeight), first child with f <= cumulative weight.
+GGL_HD void arena_state_set(ArenaDev& A, const EnvCfg& cfg, const ArenaDev* injected) {
+    int kind = cfg.stateSetter, flags = cfg.setterFlags;
+    if (kind == GGL_SETTER_COMBINED) {
+        const float f = rand_float(A.rng, 0.f, cfg.setterTotalWeight);
+        int pick = cfg.numSetterChildren - 1;
+        for (int i = 0; i < cfg.numSetterChildren; i++)
+            if (f <= cfg.setterChildren[i].cumWeight) { pick = i; break; }
+        kind = cfg.setterChildren[pick].kind; flags = cfg.setterChildren[pick].flags;
+    }
+    if (kind == GGL_SETTER_INJECTED && injected && injected->hasResetState) {
+        const ArenaDev& R = *injected;
+        A.tickCount = R.tickCount; A.ball = R.ball;
+        for (int c = 0; c < A.numCars; c++) A.cars[c] = R.cars[c];
+        for (int p = 0; p < kNumPads; p++) A.pads[p] = R.pads[p];
+    } else {
+        arena_run_setter(A, kind, flags);
+    }
 }
 
 // EnvSet::ResetArena bookkeeping after the StateSetter ran (EnvSet.cpp:276-303)

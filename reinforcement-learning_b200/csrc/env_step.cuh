@@ -249,8 +249,22 @@ GGL_HD void write_player_advanced(float*& o, const PlayerView& pl, bool inv, V3 
     o += 29;
 }
 
-// One observation row for players[slot]
-GGL_HD void build_obs_row(const ArenaDev& A, const EnvCfg& cfg, int slot, float* out) {
+// DefaultObsPadded's two std::shuffle calls for ONE row (DefaultObsPadded.cpp:59-60): teammates (maxPlayers-1 entries) first,
+// then opponents (maxPlayers entries); item k of a list before the shuffle = k-th such player in players[] order, zero rows after
+GGL_HD void padded_obs_draw(uint32_t& rng, int maxPlayers, uint32_t& permMates, uint32_t& permOpps) {
+    permMates = std_shuffle_nib(rng, maxPlayers - 1);
+    permOpps = std_shuffle_nib(rng, maxPlayers);
+}
+// The rows of an arena are built one after the other in players[] order on one engine (EnvSet.cpp:257-268), so row `slot` sees
+// the stream after the draws of rows 0..slot-1: replayed here (a handful of integer steps) so that every row's lane can work
+// on its own; returns the stream after row `slot`.
+GGL_HD uint32_t padded_obs_draws_upto(uint32_t rng, int maxPlayers, int slot, uint32_t& permMates, uint32_t& permOpps) {
+    for (int s = 0; s <= slot; s++) padded_obs_draw(rng, maxPlayers, permMates, permOpps);
+    return rng;
+}
+
+// One observation row for players[slot]. permMates / permOpps: DefaultObsPadded only.
+GGL_HD void build_obs_row(const ArenaDev& A, const EnvCfg& cfg, int slot, float* out, uint32_t permMates = 0, uint32_t permOpps = 0) {
     const int ci = A.slotCar[slot];
     const PlayerView me = player_view(A, ci);
     const bool inv = me.team == 1;
@@ -281,6 +295,24 @@ GGL_HD void build_obs_row(const ArenaDev& A, const EnvCfg& cfg, int slot, float*
     o += kNumPads;
     if (cfg.obsKind == GGL_OBS_ADVANCED) write_player_advanced(o, me, inv, bp, bv);
     else write_player_default(o, me, inv);
+    if (cfg.obsKind == GGL_OBS_DEFAULT_PADDED) {
+        // teammates then opponents, each list padded with zero rows and shuffled: list[j] = item nibble j of the permutation
+        const int nm = cfg.obsMaxPlayers - 1, no = cfg.obsMaxPlayers;
+        for (int i = 0; i < 19 * (nm + no); i++) o[i] = 0.f;
+        int km = 0, ko = 0;
+        for (int s = 0; s < A.numCars; s++) {
+            const int oc = A.slotCar[s];
+            if (oc == ci) continue;
+            const bool mate = A.cars[oc].team == me.team;
+            const int k = mate ? km++ : ko++;
+            const uint32_t perm = mate ? permMates : permOpps;
+            int j = 0;
+            while (j < 7 && (int)nib_get(perm, j) != k) j++;
+            float* dst = o + 19 * (mate ? j : nm + j);
+            write_player_default(dst, player_view(A, oc), inv);
+        }
+        return;
+    }
     for (int pass = 0; pass < 2; pass++)
         for (int s = 0; s < A.numCars; s++) {
             int oc = A.slotCar[s];

@@ -59,7 +59,6 @@ LaunchGeom launch_geom(const EnvCfg& cfg, int numSMs) {
     return g;
 }
 
-int obs_size(int kind, int cars) { return 51 + (kind == GGL_OBS_ADVANCED ? 29 : 19) * cars; }
 
 template <class T>
 int dmalloc(T** p, size_t n) {
@@ -102,7 +101,11 @@ extern "C" int ggl_envset_create(const ggl_envset_desc* d, ggl_envset** out) {
         d->num_terminals > GGL_MAX_TERMINALS) {
         ggl::set_error("ggl_envset_create: descriptor out of range"); return GGL_ERR_INVALID;
     }
-    if (d->obs_kind != GGL_OBS_DEFAULT && d->obs_kind != GGL_OBS_ADVANCED) { ggl::set_error("unsupported obs kind %d", d->obs_kind); return GGL_ERR_UNSUPPORTED; }
+    {
+        EnvCfg probe;
+        memset(&probe, 0, sizeof(probe));
+        if (const char* why = env_cfg_plugins(probe, d)) { ggl::set_error("ggl_envset_create: %s", why); return GGL_ERR_UNSUPPORTED; }
+    }
     for (int i = 0; i < d->num_rewards; i++)
         if (d->rewards[i].kind < 0 || d->rewards[i].kind >= GGL_REW_KIND_COUNT) { ggl::set_error("unsupported reward kind %d", d->rewards[i].kind); return GGL_ERR_UNSUPPORTED; }
     for (int i = 0; i < d->num_terminals; i++)
@@ -117,8 +120,8 @@ extern "C" int ggl_envset_create(const ggl_envset_desc* d, ggl_envset** out) {
     e->device = d->device; e->seed = d->seed;
     EnvCfg& c = e->cfg;
     c.numArenas = d->num_arenas; c.playersPerTeam = d->players_per_team; c.numCars = 2 * d->players_per_team;
-    c.tickSkip = d->tick_skip; c.actionDelay = d->action_delay; c.obsKind = d->obs_kind; c.obsSize = obs_size(d->obs_kind, c.numCars);
-    c.numRewards = d->num_rewards; c.numTerminals = d->num_terminals; c.stateSetter = d->state_setter;
+    c.tickSkip = d->tick_skip; c.actionDelay = d->action_delay; env_cfg_plugins(c, d);
+    c.numRewards = d->num_rewards; c.numTerminals = d->num_terminals;
     for (int i = 0; i < d->num_rewards; i++) {
         c.rewards[i].kind = d->rewards[i].kind; c.rewards[i].weight = d->rewards[i].weight;
         for (int k = 0; k < 4; k++) c.rewards[i].params[k] = d->rewards[i].params[k];
@@ -216,7 +219,8 @@ extern "C" int ggl_envset_create(const ggl_envset_desc* d, ggl_envset** out) {
         GGL_CUDA(cudaFuncSetAttribute(arena_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024));
     }
     // EnvSet ctor: reset every arena once (EnvSet.cpp:106-110)
-    EnvCfg kc = e->cfg; kc.stateSetter = GGL_SETTER_KICKOFF;
+    EnvCfg kc = e->cfg;
+    if (kc.stateSetter == GGL_SETTER_INJECTED) kc.stateSetter = GGL_SETTER_KICKOFF;     // no states supplied yet
     env_reset_kernel<<<grid_for(e->cfg), kBlock, 0, 0>>>(kc, e->P, 1);
     ggl::count_launch();
     cudaError_t err = cudaDeviceSynchronize();
@@ -376,6 +380,25 @@ extern "C" int ggl_envset_set_reset_state(ggl_envset* e, int arena, const ggl_ar
     cudaError_t err = cudaMemcpy(e->d_reset + arena, A, sizeof(ArenaDev), cudaMemcpyHostToDevice);
     delete A;
     if (err != cudaSuccess) { ggl::set_error("set_reset_state -> %s", cudaGetErrorString(err)); return GGL_ERR_CUDA; }
+    return GGL_OK;
+}
+
+extern "C" int ggl_envset_set_rng(ggl_envset* e, int arena, uint32_t state) {
+    ENV_CHECK(e);
+    if (arena < -1 || arena >= e->cfg.numArenas || state < 1u || state > 2147483646u) { ggl::set_error("set_rng: bad argument"); return GGL_ERR_INVALID; }
+    GGL_CUDA(cudaSetDevice(e->device));
+    GGL_CUDA(cudaDeviceSynchronize());
+    for (int a = (arena < 0 ? 0 : arena); a < (arena < 0 ? e->cfg.numArenas : arena + 1); a++)
+        GGL_CUDA(cudaMemcpy((char*)(e->P.arenas + a) + offsetof(ArenaDev, rng), &state, sizeof(uint32_t), cudaMemcpyHostToDevice));
+    return GGL_OK;
+}
+
+extern "C" int ggl_envset_get_rng(ggl_envset* e, int arena, uint32_t* out_state) {
+    ENV_CHECK(e);
+    if (!out_state || arena < 0 || arena >= e->cfg.numArenas) { ggl::set_error("get_rng: bad argument"); return GGL_ERR_INVALID; }
+    GGL_CUDA(cudaSetDevice(e->device));
+    GGL_CUDA(cudaDeviceSynchronize());
+    GGL_CUDA(cudaMemcpy(out_state, (const char*)(e->P.arenas + arena) + offsetof(ArenaDev, rng), sizeof(uint32_t), cudaMemcpyDeviceToHost));
     return GGL_OK;
 }
 

@@ -829,6 +829,40 @@ GGL_HD uint32_t minstd_next(uint32_t& s) {
     return s;
 }
 
+// The libstdc++ / RocketSim pieces the reference draws through, restated so that an arena's stream yields exactly what the
+// reference's thread engine would from the same state (pinned against the compiled reference, tests/test_setters_cpu.py):
+//  * std::uniform_int_distribution<unsigned long>{0, n-1} over minstd_rand0: the engine's range 2^31-3 is neither 2^32-1 nor
+//    2^64-1, so bits/uniform_int_dist.h takes its "2 divisions" downscaling branch (scale, reject the tail, divide);
+//  * std::shuffle (bits/stl_algo.h): one leading swap when the count is even, then two swap positions per draw;
+//  * RocketSim::Math::RandFloat (Math.cpp:54-57): min + (engine() / (float)engine.max()) * (max - min).
+GGL_HD uint32_t std_uniform_below(uint32_t& s, uint32_t n) {
+    const uint32_t scaling = 2147483645u / n, past = n * scaling;
+    uint32_t r;
+    do r = minstd_next(s) - 1u; while (r >= past);
+    return r / scaling;
+}
+// a permutation of up to 8 items, 4 bits each (item at position i = nibble i): no indexed local array, no stack
+GGL_HD uint32_t nib_get(uint32_t p, int i) { return (p >> (4 * i)) & 15u; }
+GGL_HD uint32_t nib_swap(uint32_t p, int i, int j) {
+    const uint32_t a = nib_get(p, i), b = nib_get(p, j);
+    p &= ~((15u << (4 * i)) | (15u << (4 * j)));
+    return p | (b << (4 * i)) | (a << (4 * j));
+}
+GGL_HD uint32_t std_shuffle_nib(uint32_t& s, int n) {
+    uint32_t p = 0x76543210u;
+    if (n < 2) return p;
+    int i = 1;
+    if ((n & 1) == 0) { p = nib_swap(p, i, (int)std_uniform_below(s, 2u)); i++; }
+    while (i < n) {
+        const uint32_t sr = (uint32_t)i + 1u;
+        const uint32_t x = std_uniform_below(s, sr * (sr + 1u));
+        p = nib_swap(p, i, (int)(x / (sr + 1u))); i++;
+        p = nib_swap(p, i, (int)(x % (sr + 1u))); i++;
+    }
+    return p;
+}
+GGL_HD float rand_float(uint32_t& s, float lo, float hi) { return lo + ((float)minstd_next(s) / 2147483648.0f) * (hi - lo); }
+
 // Car::SetState(CarState()) part of Car::Respawn (Car.cpp:43-56, 20-36)
 GGL_HD void car_reset_state_defaults(CarDev& c) {
     c.vel = v3(0, 0, 0); c.angVel = v3(0, 0, 0); c.velImpulseCache = v3(0, 0, 0);

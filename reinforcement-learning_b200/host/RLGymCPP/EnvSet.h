@@ -23,6 +23,7 @@
 // buffers libtorch would wrap zero-copy are in deviceViews().
 #pragma once
 #include <algorithm>
+#include <cmath>
 #include <cstdint>
 #include <cstdio>
 #include <cstring>
@@ -196,9 +197,15 @@ class NoTouchCondition : public TerminalCondition { public:     // NoTouchCondit
 
 class ObsBuilder { public:                              // ObsBuilders/ObsBuilder.h:8-14
     virtual int DescribeKind() const { return -1; }
+    virtual int DescribeMaxPlayers() const { return 0; }
     virtual ~ObsBuilder() {} };
 class DefaultObs : public ObsBuilder { public: int DescribeKind() const override { return GGL_OBS_DEFAULT; } };
 class AdvancedObs : public ObsBuilder { public: int DescribeKind() const override { return GGL_OBS_ADVANCED; } };
+class DefaultObsPadded : public ObsBuilder { public:    // ObsBuilders/DefaultObsPadded.h:9-24 (default coefficients)
+    int maxPlayers;
+    DefaultObsPadded(int maxPlayers) : maxPlayers(maxPlayers) {}
+    int DescribeKind() const override { return GGL_OBS_DEFAULT_PADDED; }
+    int DescribeMaxPlayers() const override { return maxPlayers; } };
 
 class ActionParser { public:                            // ActionParsers/ActionParser.h:9-19
     virtual bool IsDefaultAction() const { return false; }
@@ -210,10 +217,27 @@ class DefaultAction : public ActionParser { public:     // DefaultAction.h:8-24 
 
 class StateSetter { public:                             // StateSetters/StateSetter.h:5-8
     virtual int DescribeKind() const { return -1; }
+    virtual int DescribeFlags() const { return 0; }
     virtual ~StateSetter() {} };
 class KickoffState : public StateSetter { public: int DescribeKind() const override { return GGL_SETTER_KICKOFF; } };
 // Reset states supplied by the host (EnvSet::SetResetState): the route for user StateSetters whose output is data.
 class InjectedState : public StateSetter { public: int DescribeKind() const override { return GGL_SETTER_INJECTED; } };
+class FuzzedKickoffState : public StateSetter { public: int DescribeKind() const override { return GGL_SETTER_FUZZED_KICKOFF; } };   // FuzzedKickoffState.h:7-27
+class RandomState : public StateSetter { public:        // RandomState.h:5-16
+    bool randBallSpeed, randCarSpeed, carsOnGround;
+    RandomState(bool randBallSpeed, bool randCarSpeed, bool carsOnGround)
+        : randBallSpeed(randBallSpeed), randCarSpeed(randCarSpeed), carsOnGround(carsOnGround) {}
+    int DescribeKind() const override { return GGL_SETTER_RANDOM; }
+    int DescribeFlags() const override {
+        return (randBallSpeed ? GGL_RANDOM_BALL_SPEED : 0) | (randCarSpeed ? GGL_RANDOM_CAR_SPEED : 0) | (carsOnGround ? GGL_RANDOM_CARS_ON_GROUND : 0); } };
+class CombinedState : public StateSetter { public:      // CombinedState.h:10-46 (children are not owned, as in the reference)
+    std::vector<std::pair<StateSetter*, float>> setters;
+    CombinedState(const std::vector<std::pair<StateSetter*, float>>& setters) : setters(setters) {
+        if (setters.empty()) _Fatal("CombinedState: no setters");
+        for (auto& p : setters)
+            if (p.second < 0 || std::isnan(p.second) || std::isinf(p.second)) _Fatal("CombinedState: a state setter has a negative or invalid weight");
+    }
+    int DescribeKind() const override { return GGL_SETTER_COMBINED; } };
 
 // ---------------------------------------------------------------------------------------------- EnvSet
 struct EnvCreateResult {                                // EnvSet.h:14-23
@@ -262,11 +286,27 @@ inline ggl_envset_desc DescribeEnv(const EnvCreateResult& r, const EnvSetConfig&
         _Fatal("the device EnvSet needs N blue cars added first, then N orange cars, N in 1..3");
     d.device = cfg.device; d.num_arenas = cfg.numArenas; d.players_per_team = blue;
     d.tick_skip = cfg.tickSkip; d.action_delay = cfg.actionDelay; d.seed = cfg.seed;
-    if (!r.obsBuilder || r.obsBuilder->DescribeKind() < 0) _Fatal("ObsBuilder subclass has no device implementation (stock: DefaultObs, AdvancedObs)");
+    if (!r.obsBuilder || r.obsBuilder->DescribeKind() < 0) _Fatal("ObsBuilder subclass has no device implementation (stock: DefaultObs, AdvancedObs, DefaultObsPadded)");
     d.obs_kind = r.obsBuilder->DescribeKind();
+    d.obs_max_players = r.obsBuilder->DescribeMaxPlayers();
+    if (d.obs_kind == GGL_OBS_DEFAULT_PADDED && blue > d.obs_max_players)        // DefaultObsPadded.cpp:40-44
+        _Fatal("DefaultObsPadded: too many players per team for maxPlayers");
     if (!r.actionParser || !r.actionParser->IsDefaultAction()) _Fatal("ActionParser subclass has no device implementation (stock: DefaultAction)");
-    if (!r.stateSetter || r.stateSetter->DescribeKind() < 0) _Fatal("StateSetter subclass has no device implementation (stock: KickoffState; data: InjectedState)");
+    if (!r.stateSetter || r.stateSetter->DescribeKind() < 0) _Fatal("StateSetter subclass has no device implementation (stock: KickoffState, FuzzedKickoffState, RandomState, CombinedState; data: InjectedState)");
     d.state_setter = r.stateSetter->DescribeKind();
+    d.state_setter_flags = r.stateSetter->DescribeFlags();
+    if (d.state_setter == GGL_SETTER_COMBINED) {
+        auto* comb = static_cast<const CombinedState*>(r.stateSetter);
+        if (comb->setters.size() > GGL_MAX_SETTER_CHILDREN) _Fatal("CombinedState: more children than GGL_MAX_SETTER_CHILDREN");
+        d.num_setter_children = (int)comb->setters.size();
+        for (size_t i = 0; i < comb->setters.size(); i++) {
+            const StateSetter* ch = comb->setters[i].first;
+            if (!ch || ch->DescribeKind() < 0 || ch->DescribeKind() == GGL_SETTER_COMBINED)
+                _Fatal("CombinedState: child has no device implementation (stock: KickoffState, FuzzedKickoffState, RandomState; data: InjectedState)");
+            d.setter_children[i].kind = ch->DescribeKind(); d.setter_children[i].flags = ch->DescribeFlags();
+            d.setter_children[i].weight = comb->setters[i].second;
+        }
+    }
     if (r.rewards.size() > GGL_MAX_REWARDS) _Fatal("too many reward functions");
     d.num_rewards = (int)r.rewards.size();
     for (size_t i = 0; i < r.rewards.size(); i++) {

@@ -34,6 +34,20 @@ static int Describe() {
               d.rewards[2].weight == 10.f && d.rewards[3].kind == GGL_REW_STRONG_TOUCH && d.rewards[3].zero_sum == 1 &&
               std::fabs(d.rewards[3].params[0] - 20 * 250.f / 9.f) < 1e-3f && d.terminals[1].kind == GGL_TERM_NO_TOUCH &&
               d.terminals[1].params[0] == 10.f && d.state_setter == GGL_SETTER_KICKOFF && d.tick_skip == 8 && d.action_delay == 7;
+    {   // the random plugins of SURVEY 8 f4: DefaultObsPadded, CombinedState over { KickoffState, RandomState, FuzzedKickoffState }
+        EnvCreateResult r = MakeEnv(2, false);
+        r.obsBuilder = new DefaultObsPadded(3);
+        r.stateSetter = new CombinedState({{new KickoffState(), 1.f}, {new RandomState(true, false, true), 2.5f}, {new FuzzedKickoffState(), 0.5f}});
+        ggl_envset_desc p = DescribeEnv(r, cfg);
+        ok = ok && p.obs_kind == GGL_OBS_DEFAULT_PADDED && p.obs_max_players == 3 && p.state_setter == GGL_SETTER_COMBINED &&
+             p.num_setter_children == 3 && p.setter_children[1].kind == GGL_SETTER_RANDOM &&
+             p.setter_children[1].flags == (GGL_RANDOM_BALL_SPEED | GGL_RANDOM_CARS_ON_GROUND) && p.setter_children[1].weight == 2.5f &&
+             p.setter_children[2].kind == GGL_SETTER_FUZZED_KICKOFF;
+        bool tooMany = false;
+        r.obsBuilder = new DefaultObsPadded(1);
+        try { DescribeEnv(r, cfg); } catch (const std::runtime_error&) { tooMany = true; }
+        ok = ok && tooMany;
+    }
     bool threw = false;
     try { DescribeEnv(MakeEnv(1, false, new MyReward()), cfg); } catch (const std::runtime_error& e) {
         threw = std::string(e.what()).find("no device implementation") != std::string::npos;

@@ -3,6 +3,7 @@
 // can be lock-stepped against the compiled reference (oracle/_ref) in a container WITHOUT a GPU.  The product
 // library (libgigaenv_cuda.so) never links or loads this; it only launches CUDA kernels built from the same headers.
 //   g++ -O2 -ffp-contract=off -shared -fPIC -I../../include hostsim.cpp -o _build/libhostsim.so
+#include <cstdio>
 #include "../../reinforcement-learning_b200/csrc/sim_convert.cuh"
 #include "../../reinforcement-learning_b200/csrc/env_reset.cuh"
 
@@ -134,7 +135,9 @@ static void host_write_rows(HostEnv* h, int a) {
     ArenaDev& A = h->arenas[a];
     for (int s = 0; s < A.numCars; s++) {
         int row = a * h->cfg.numCars + s;
-        build_obs_row(A, h->cfg, s, h->obs.data() + (size_t)row * h->cfg.obsSize);
+        uint32_t pm = 0, po = 0;
+        if (h->cfg.obsKind == GGL_OBS_DEFAULT_PADDED) padded_obs_draw(A.rng, h->cfg.obsMaxPlayers, pm, po);
+        build_obs_row(A, h->cfg, s, h->obs.data() + (size_t)row * h->cfg.obsSize, pm, po);
         action_mask_row(A.cars[A.slotCar[s]], h->table.data(), h->masks.data() + (size_t)row * kNumActions);
     }
 }
@@ -142,14 +145,9 @@ static void host_write_rows(HostEnv* h, int a) {
 static void host_reset_arena(HostEnv* h, int a, bool force, int setter) {
     ArenaDev& A = h->arenas[a];
     if (!force && A.terminal == 0) return;
-    if (setter == GGL_SETTER_INJECTED && h->resets[a].hasResetState) {
-        const ArenaDev& R = h->resets[a];
-        A.tickCount = R.tickCount; A.ball = R.ball;
-        for (int c = 0; c < A.numCars; c++) A.cars[c] = R.cars[c];
-        for (int p = 0; p < kNumPads; p++) A.pads[p] = R.pads[p];
-    } else {
-        arena_reset_kickoff(A);
-    }
+    EnvCfg cfg = h->cfg;
+    cfg.stateSetter = setter;
+    arena_state_set(A, cfg, &h->resets[a]);
     env_after_state_set(A);
     h->terminals[a] = 0;
     host_write_rows(h, a);
@@ -164,9 +162,9 @@ void* hostenv_create(const ggl_envset_desc* d) {
     EnvCfg& c = h->cfg;
     memset(&c, 0, sizeof(c));
     c.numArenas = d->num_arenas; c.playersPerTeam = d->players_per_team; c.numCars = 2 * d->players_per_team;
-    c.tickSkip = d->tick_skip; c.actionDelay = d->action_delay; c.obsKind = d->obs_kind;
-    c.obsSize = 51 + (d->obs_kind == GGL_OBS_ADVANCED ? 29 : 19) * c.numCars;
-    c.numRewards = d->num_rewards; c.numTerminals = d->num_terminals; c.stateSetter = d->state_setter;
+    c.tickSkip = d->tick_skip; c.actionDelay = d->action_delay;
+    if (const char* why = env_cfg_plugins(c, d)) { fprintf(stderr, "hostenv_create: %s\n", why); delete h; return nullptr; }
+    c.numRewards = d->num_rewards; c.numTerminals = d->num_terminals;
     for (int i = 0; i < d->num_rewards; i++) {
         c.rewards[i].kind = d->rewards[i].kind; c.rewards[i].weight = d->rewards[i].weight;
         for (int k = 0; k < 4; k++) c.rewards[i].params[k] = d->rewards[i].params[k];
@@ -195,7 +193,7 @@ void* hostenv_create(const ggl_envset_desc* d) {
         }
         for (int s = 0; s < c.numCars; s++) A.slotCar[s] = (uint8_t)(d->slot_order_reversed ? c.numCars - 1 - s : s);
         A.lastTouchCarId = -1;
-        host_reset_arena(h, a, true, GGL_SETTER_KICKOFF);
+        host_reset_arena(h, a, true, c.stateSetter == GGL_SETTER_INJECTED ? GGL_SETTER_KICKOFF : c.stateSetter);
     }
     return h;
 }
@@ -220,6 +218,11 @@ void hostenv_reset_arena(void* p, int a) {
     for (int i = 0; i < h->cfg.numArenas; i++)
         if (a < 0 || i == a) host_reset_arena(h, i, true, h->cfg.stateSetter);
 }
+void hostenv_set_rng(void* p, int a, uint32_t state) {
+    HostEnv* h = (HostEnv*)p;
+    for (int i = 0; i < h->cfg.numArenas; i++) if (a < 0 || i == a) h->arenas[i].rng = state;
+}
+uint32_t hostenv_get_rng(void* p, int a) { return ((HostEnv*)p)->arenas[a].rng; }
 void hostenv_set_slot_order(void* p, const int32_t* ids) {
     HostEnv* h = (HostEnv*)p;
     for (int a = 0; a < h->cfg.numArenas; a++)

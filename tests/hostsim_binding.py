@@ -117,7 +117,10 @@ class HostEnvSet:
         self.h = L.hostenv_create(C.byref(self.desc))
         self.num_arenas = num_arenas
         self.num_players = num_arenas * 2 * players_per_team
-        self.obs_size = 51 + (29 if self.desc.obs_kind == abi.OBS_ADVANCED else 19) * 2 * players_per_team
+        if self.desc.obs_kind == abi.OBS_DEFAULT_PADDED:
+            self.obs_size = 51 + 38 * self.desc.obs_max_players
+        else:
+            self.obs_size = 51 + (29 if self.desc.obs_kind == abi.OBS_ADVANCED else 19) * 2 * players_per_team
         self.num_actions = 90
         self.num_rewards = self.desc.num_rewards
         self.device = "cpu"
@@ -147,6 +150,15 @@ class HostEnvSet:
     def set_slot_order(self, ids):
         ids = np.ascontiguousarray(ids, np.int32)
         lib().hostenv_set_slot_order(self.h, ids.ctypes.data)
+
+    def set_rng(self, a, state):
+        lib().hostenv_set_rng.argtypes = [C.c_void_p, C.c_int, C.c_uint32]
+        lib().hostenv_set_rng(self.h, a, state)
+
+    def get_rng(self, a):
+        lib().hostenv_get_rng.restype = C.c_uint32
+        lib().hostenv_get_rng.argtypes = [C.c_void_p, C.c_int]
+        return int(lib().hostenv_get_rng(self.h, a))
 
     def contact_overflow(self):
         lib().hostenv_contact_overflow.restype = C.c_uint64

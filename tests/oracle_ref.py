@@ -49,6 +49,8 @@ def lib():
         L.ref_arena_step.argtypes = [C.c_void_p, C.c_int, C.c_int]
         L.ref_envset_set_controls.argtypes = [C.c_void_p, C.c_int, C.POINTER(abi.ArenaState)]
         L.ref_action_table.argtypes = [C.c_void_p, C.POINTER(C.c_int)]
+        L.ref_rng_peek.argtypes = [C.c_int]
+        L.ref_rng_peek.restype = C.c_uint32
         meshes = arena_mesh.soccar_meshes()
         arr = (abi.MeshBlob * len(meshes))()
         keep = []

@@ -278,3 +278,59 @@ def test_block_geometry_does_not_change_results(ggl):
             terms += int((small.terminals != 0).sum())
     assert terms > 0
     big.close(); small.close()
+
+
+# ---- the random plugins, draw for draw against the compiled reference (tests/setter_parity.py) ----
+# On the GPU sinf/cosf of the spawn yaw and the uu<->bt round trips differ from x86 in the last bits: 1e-3 uu on state, 1e-5 on obs.
+SETTER_STATE_ATOL, SETTER_OBS_ATOL = 1e-3, 1e-5
+
+
+@pytest.mark.parametrize("setter,flags,ppt", [(0, 0, 2), (2, 0, 3), (3, 0, 2), (3, 3, 2), (3, 7, 3), (3, 4, 1)])
+def test_state_setters_match_reference(ggl, setter, flags, ppt):
+    import setter_parity
+    r = setter_parity.run_resets(ggl.EnvSet, ppt, trials=25, seed=100 + setter + flags, state_setter=setter, state_setter_flags=flags)
+    assert r["state"] <= SETTER_STATE_ATOL and r["obs"] <= SETTER_OBS_ATOL, r
+
+
+def test_combined_state_matches_reference(ggl):
+    import setter_parity
+    abi = ggl.abi
+    kids = [(abi.SETTER_KICKOFF, 1.0), (abi.SETTER_RANDOM, 2.0, 3), (abi.SETTER_FUZZED_KICKOFF, 0.5), (abi.SETTER_RANDOM, 1.5, 4)]
+    r = setter_parity.run_resets(ggl.EnvSet, 2, trials=50, seed=131, state_setter=abi.SETTER_COMBINED, setter_children=kids)
+    assert r["state"] <= SETTER_STATE_ATOL and r["obs"] <= SETTER_OBS_ATOL, r
+    assert r["ball_z_values"] > 8
+
+
+@pytest.mark.parametrize("ppt,maxp", [(1, 3), (2, 2), (2, 3), (3, 3), (2, 6)])
+def test_default_obs_padded_matches_reference(ggl, ppt, maxp):
+    import setter_parity
+    abi = ggl.abi
+    r = setter_parity.run_resets(ggl.EnvSet, ppt, trials=25, seed=140 + ppt + maxp, state_setter=abi.SETTER_RANDOM, state_setter_flags=3,
+                                 obs_kind=abi.OBS_DEFAULT_PADDED, obs_max_players=maxp)
+    assert r["state"] <= SETTER_STATE_ATOL and r["obs"] <= SETTER_OBS_ATOL, r
+    r = setter_parity.run_padded_steps(ggl.EnvSet, ppt, maxp, steps=20, seed=150 + ppt)
+    assert r["obs"] <= 2e-4, r
+
+
+def test_random_setters_at_scale_stay_in_the_arena(ggl):
+    """4096 arenas on CombinedState{Kickoff, RandomState(all random)} + DefaultObsPadded(3): every arena draws from its own stream
+    (no two arenas alike), states are inside RandomState's box, 100 steps with resets stay finite."""
+    import torch
+    abi = ggl.abi
+    env = ggl.EnvSet(4096, 2, obs_kind=abi.OBS_DEFAULT_PADDED, obs_max_players=3, state_setter=abi.SETTER_COMBINED,
+                     setter_children=[(abi.SETTER_KICKOFF, 1.0), (abi.SETTER_RANDOM, 3.0, 3)], seed=9)
+    assert env.obs_size == 51 + 38 * 3
+    o = env.obs.cpu().numpy().reshape(4096, 4, -1)
+    ballz = o[:, 0, 2] * 2044.0
+    rnd = np.abs(ballz - 93.15) > 0.01
+    assert 0.6 < rnd.mean() < 0.9                                      # weight 3 of 4
+    assert len(np.unique(np.round(o[rnd, 0, 0], 6))) > 0.99 * rnd.sum()   # ball x: one stream per arena
+    assert np.all(np.abs(o[:, 0, 0]) <= 3500 / 4096 + 1e-6) and np.all(np.abs(o[:, 0, 1]) <= 4000 / 5120 + 1e-6)
+    a = torch.zeros(env.num_players, dtype=torch.int32, device="cuda")
+    for i in range(100):
+        env.random_actions(a, seed=500 + i)
+        env.step(a)
+    env.sync()
+    assert torch.isfinite(env.obs).all() and torch.isfinite(env.rewards).all()
+    assert env.contact_overflow() == 0
+    env.close()
