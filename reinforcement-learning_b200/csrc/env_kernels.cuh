@@ -21,12 +21,20 @@ namespace ggl {
 #endif
 constexpr int kGroup = GGL_GROUP;                // lanes per arena (8 or 16)
 constexpr int kArenasPerWarp = 32 / kGroup;
-constexpr int kMaxWarps = 7 * kGroup / 8;        // warps per block of the step kernels (chosen per launch, see launch_geom)
+constexpr int kMaxWarps = (7 * kGroup + 7) / 8;  // warps per block of the step kernels: 7 units of 4 arenas (see launch_geom)
 constexpr int kBlock = 32;                       // the reset kernel: one warp per block
 constexpr int kArenasPerBlock = kBlock / kGroup;
 
+// GGL_PSYNC_GROUPS > 1 (experiment): the warps of a block meet in that many independent sets (warp w in set w % G, named
+// barriers 1..G) instead of all together: fewer arenas wait for the slowest one, more code regions live at once.
+#ifndef GGL_PSYNC_GROUPS
+#define GGL_PSYNC_GROUPS 1
+#endif
 struct ExecGroup {
     int lane_, mask_;
+#if GGL_PSYNC_GROUPS > 1
+    int barId_, barThreads_;
+#endif
 #if defined(GGL_PHASE_TIMING)
     int arena_;
 #endif
@@ -35,7 +43,11 @@ struct ExecGroup {
     __device__ __forceinline__ void sync() const { __syncwarp(mask_); }
     // The warps of a block meet at a few phase boundaries of the tick, so that the warps of an SM walk through the same code
     // together and share the instruction cache. Lane groups of arenas past the end have left the kernel before the first one.
+#if GGL_PSYNC_GROUPS > 1
+    __device__ __forceinline__ void phase_sync() const { asm volatile("bar.sync %0, %1;" ::"r"(barId_), "r"(barThreads_) : "memory"); }
+#else
     __device__ __forceinline__ void phase_sync() const { __syncthreads(); }
+#endif
 };
 
 struct EnvDevPtrs {
@@ -53,11 +65,19 @@ struct EnvDevPtrs {
 
 __device__ __forceinline__ int arena_of(const EnvDevPtrs& P, int pos) { return P.arenaOfPos ? __ldg(P.arenaOfPos + pos) : pos; }
 
-__device__ __forceinline__ ExecGroup make_exec() {
+// liveWarps: warps of this block that hold at least one arena (the others have left the kernel and never reach a barrier)
+__device__ __forceinline__ ExecGroup make_exec(int liveWarps = 0) {
     ExecGroup ex;
     ex.lane_ = threadIdx.x % kGroup;
     int base = (threadIdx.x % 32) / kGroup * kGroup;
     ex.mask_ = (int)(((1u << kGroup) - 1u) << base);
+#if GGL_PSYNC_GROUPS > 1
+    {
+        const int w = threadIdx.x / 32, g = w % GGL_PSYNC_GROUPS;
+        ex.barId_ = 1 + g;
+        ex.barThreads_ = 32 * ((liveWarps - g + GGL_PSYNC_GROUPS - 1) / GGL_PSYNC_GROUPS);
+    }
+#endif
 #if defined(GGL_PHASE_TIMING)
     ex.arena_ = blockIdx.x * (blockDim.x / kGroup) + threadIdx.x / kGroup;
 #endif
@@ -149,7 +169,8 @@ __global__ void __launch_bounds__(32 * kMaxWarps, 1) env_step_kernel(EnvCfg cfg,
     const int pos = blockIdx.x * (blockDim.x / kGroup) + threadIdx.x / kGroup;
     if (pos >= cfg.numArenas) return;            // whole groups leave: nobody waits for them at a group or block barrier
     const int arena = arena_of(P, pos);
-    const ExecGroup ex = make_exec();
+    const int groupsHere = min((int)(blockDim.x / kGroup), cfg.numArenas - (int)(blockIdx.x * (blockDim.x / kGroup)));
+    const ExecGroup ex = make_exec((groupsHere + kArenasPerWarp - 1) / kArenasPerWarp);
     stage_in(P, arena, ex, slotBytes, 0);
     {
         ArenaDev& A = my_arena(slotBytes);
@@ -234,7 +255,7 @@ __global__ void __launch_bounds__(1024) balance_kernel(const uint32_t* __restric
     __syncthreads();
     // deal: rounds over the lane groups of a block; round r sits in lane group (r % W) * G + r / W (W warps per block, G groups
     // per warp), visits the blocks in snake order, and skips the groups of the last block that lie past numArenas
-    const int G = 32 / kGroup, W = groupsPerBlock / G;
+    const int G = 4, W = groupsPerBlock / G;          // units of 4 arenas (a warp at 8 lanes per arena)
     const int rem = numArenas - (numBlocks - 1) * groupsPerBlock;         // valid groups of the last block
     for (int i = tid; i < numArenas; i += blockDim.x) {
         int r = 0, cum = 0, group = 0, nb = numBlocks;
@@ -256,7 +277,8 @@ __global__ void __launch_bounds__(32 * kMaxWarps, 1) arena_step_kernel(EnvCfg cf
     __syncthreads();
     const int arena = blockIdx.x * (blockDim.x / kGroup) + threadIdx.x / kGroup;
     if (arena >= cfg.numArenas) return;
-    const ExecGroup ex = make_exec();
+    const int groupsHere = min((int)(blockDim.x / kGroup), cfg.numArenas - (int)(blockIdx.x * (blockDim.x / kGroup)));
+    const ExecGroup ex = make_exec((groupsHere + kArenasPerWarp - 1) / kArenasPerWarp);
     stage_in(P, arena, ex, slotBytes, 1);
     ArenaDev& A = my_arena(slotBytes);
     for (int t = 0; t < ticks; t++) arena_tick(A, s_world, ex);

@@ -10,7 +10,7 @@
 
 using namespace ggl;
 
-struct LaunchGeom { int warps, grid; size_t smem; };
+struct LaunchGeom { int warps, threads, grid; size_t smem; };
 
 struct ggl_envset {
     EnvCfg cfg;
@@ -40,22 +40,25 @@ int slot_bytes(const EnvCfg& cfg) { return (int)arena_slot_bytes(cfg.numCars); }
 // Launch geometry of the step kernels: as many warps per block (<= kMaxWarps, <= what fits in 227 KB of shared memory) as it
 // takes to cover the arenas with one block per SM, so that 4096 arenas of 2v2 run as 147 blocks of 7 warps in a single wave.
 LaunchGeom launch_geom(const EnvCfg& cfg, int numSMs) {
-    const int totalWarps = (cfg.numArenas + kArenasPerWarp - 1) / kArenasPerWarp;
-    const size_t perWarp = (size_t)kArenasPerWarp * slot_bytes(cfg);
-    int fit = (int)((227 * 1024 - 1024) / perWarp);
-    if (fit > kMaxWarps) fit = kMaxWarps;
+    // unit = 4 arenas (one warp at 8 lanes per arena, half a warp at 4, two warps at 16); at most 7 units per block
+    const int unitThreads = 4 * kGroup;
+    const int totalUnits = (cfg.numArenas + 3) / 4;
+    const size_t perUnit = (size_t)4 * slot_bytes(cfg);
+    int fit = (int)((227 * 1024 - 1024) / perUnit);
+    if (fit > 7) fit = 7;
     if (fit < 1) fit = 1;
-    int warps = (totalWarps + numSMs - 1) / numSMs;
-    if (warps > fit) warps = fit;
+    int units = (totalUnits + numSMs - 1) / numSMs;
+    if (units > fit) units = fit;
     if (const char* cap = getenv("GGL_DEBUG_MAX_BLOCK_WARPS")) {     // test hook: same arenas under another block geometry
         const int c = atoi(cap);
-        if (c >= 1 && c < warps) warps = c;
+        if (c >= 1 && c < units) units = c;
     }
-    if (warps < 1) warps = 1;
+    if (units < 1) units = 1;
     LaunchGeom g;
-    g.warps = warps;
-    g.grid = (totalWarps + warps - 1) / warps;
-    g.smem = perWarp * warps;
+    g.warps = units;
+    g.threads = units * unitThreads;
+    g.grid = (totalUnits + units - 1) / units;
+    g.smem = perUnit * units;
     return g;
 }
 
@@ -242,7 +245,7 @@ extern "C" int ggl_envset_destroy(ggl_envset* e) {
 // new arena -> block assignment from the work estimates of the env step that was just launched (same stream, no host sync)
 static int rebalance(ggl_envset* e, cudaStream_t s) {
     if (!e->balance) return GGL_OK;
-    balance_kernel<<<1, 1024, 0, s>>>(e->d_stepCost, e->d_arenaOfPos, e->cfg.numArenas, e->geom.warps * kArenasPerWarp, e->geom.grid, e->d_balanceOrder);
+    balance_kernel<<<1, 1024, 0, s>>>(e->d_stepCost, e->d_arenaOfPos, e->cfg.numArenas, e->geom.threads / kGroup, e->geom.grid, e->d_balanceOrder);
     GGL_LAUNCH_CHECK(); ggl::count_launch();
     return GGL_OK;
 }
@@ -262,27 +265,27 @@ extern "C" int ggl_envset_reset_arena(ggl_envset* e, int arena, void* stream) {
 }
 extern "C" int ggl_envset_step_first_half(ggl_envset* e, void* stream) {
     ENV_CHECK(e);
-    env_step_kernel<<<e->geom.grid, 32 * e->geom.warps, e->geom.smem, (cudaStream_t)stream>>>(e->cfg, e->P, nullptr, 1, 0, slot_bytes(e->cfg));
+    env_step_kernel<<<e->geom.grid, e->geom.threads, e->geom.smem, (cudaStream_t)stream>>>(e->cfg, e->P, nullptr, 1, 0, slot_bytes(e->cfg));
     GGL_LAUNCH_CHECK(); ggl::count_launch();
     return GGL_OK;
 }
 extern "C" int ggl_envset_step_second_half(ggl_envset* e, const int32_t* d_actions, void* stream) {
     ENV_CHECK(e);
     if (!d_actions) { ggl::set_error("null actions"); return GGL_ERR_INVALID; }
-    env_step_kernel<<<e->geom.grid, 32 * e->geom.warps, e->geom.smem, (cudaStream_t)stream>>>(e->cfg, e->P, d_actions, 0, 1, slot_bytes(e->cfg));
+    env_step_kernel<<<e->geom.grid, e->geom.threads, e->geom.smem, (cudaStream_t)stream>>>(e->cfg, e->P, d_actions, 0, 1, slot_bytes(e->cfg));
     GGL_LAUNCH_CHECK(); ggl::count_launch();
     return rebalance(e, (cudaStream_t)stream);
 }
 extern "C" int ggl_envset_step(ggl_envset* e, const int32_t* d_actions, void* stream) {
     ENV_CHECK(e);
     if (!d_actions) { ggl::set_error("null actions"); return GGL_ERR_INVALID; }
-    env_step_kernel<<<e->geom.grid, 32 * e->geom.warps, e->geom.smem, (cudaStream_t)stream>>>(e->cfg, e->P, d_actions, 1, 1, slot_bytes(e->cfg));
+    env_step_kernel<<<e->geom.grid, e->geom.threads, e->geom.smem, (cudaStream_t)stream>>>(e->cfg, e->P, d_actions, 1, 1, slot_bytes(e->cfg));
     GGL_LAUNCH_CHECK(); ggl::count_launch();
     return rebalance(e, (cudaStream_t)stream);
 }
 extern "C" int ggl_arena_step(ggl_envset* e, int ticks, void* stream) {
     ENV_CHECK(e);
-    arena_step_kernel<<<e->geom.grid, 32 * e->geom.warps, e->geom.smem, (cudaStream_t)stream>>>(e->cfg, e->P, ticks, slot_bytes(e->cfg));
+    arena_step_kernel<<<e->geom.grid, e->geom.threads, e->geom.smem, (cudaStream_t)stream>>>(e->cfg, e->P, ticks, slot_bytes(e->cfg));
     GGL_LAUNCH_CHECK(); ggl::count_launch();
     return GGL_OK;
 }
