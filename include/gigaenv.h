@@ -366,6 +366,10 @@ typedef struct ggl_traj_desc {
     int32_t max_episode_length;   /* (int)(maxEpisodeDuration * 120 / tickSkip), Learner.cpp:550; also the per-player buffer depth */
     int64_t capacity_timesteps;   /* rows of the combined stream: >= tsPerItr + what one step can append */
     int64_t capacity_truncated;   /* rows of nextStates */
+    int64_t capacity_player_rows; /* steps the per-player buffers hold IN TOTAL (a pool of 16-step pages shared by all players):
+                                     0 = worst case, num_players x max_episode_length (22 GB at 16 384 players x 1 800 steps x
+                                     obs 167); > 0 = the steps in flight one expects (players x episode length, with margin).
+                                     A pool that runs out makes ggl_traj_counts fail - nothing is dropped silently */
 } ggl_traj_desc;
 typedef struct ggl_traj_views {   /* DEVICE pointers into the combined stream, valid until destroy; rows [0, length) are defined */
     float*   states;        /* [capacity_timesteps, obs_size]   Trajectory::states      */

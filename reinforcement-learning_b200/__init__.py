@@ -329,12 +329,13 @@ class TrajectoryStore:
     `tensors()` returns torch views of the first `length` rows of the combined stream (zero-copy)."""
 
     def __init__(self, num_players, players_per_arena, obs_size, num_actions, max_episode_length, capacity_timesteps,
-                 capacity_truncated=None, device=0):
+                 capacity_truncated=None, device=0, capacity_player_rows=0):
         import torch
         d = abi.TrajDesc()
         d.device, d.num_players, d.players_per_arena, d.obs_size, d.num_actions = device, num_players, players_per_arena, obs_size, num_actions
         d.max_episode_length, d.capacity_timesteps = max_episode_length, capacity_timesteps
         d.capacity_truncated = capacity_truncated if capacity_truncated is not None else capacity_timesteps
+        d.capacity_player_rows = capacity_player_rows      # 0 = worst case (players x max_episode_length); else the steps in flight
         self.desc = d
         self.device = torch.device("cuda", device)
         h = C.c_void_p()

@@ -106,7 +106,7 @@ class ExpBufTensors(C.Structure):
 class TrajDesc(C.Structure):
     _fields_ = [("device", C.c_int32), ("num_players", C.c_int32), ("players_per_arena", C.c_int32), ("obs_size", C.c_int32),
                 ("num_actions", C.c_int32), ("max_episode_length", C.c_int32), ("capacity_timesteps", C.c_int64),
-                ("capacity_truncated", C.c_int64)]
+                ("capacity_truncated", C.c_int64), ("capacity_player_rows", C.c_int64)]
 
 
 class TrajViews(C.Structure):

@@ -5,7 +5,11 @@
 // terminal decision and `combinedTraj.Append`). The reference keeps one std::vector-backed buffer per player, copies every obs
 // row into it on the host, and appends a finished buffer to the combined vectors (a second host copy of every row).
 // Here the per-player buffers and the combined stream are device tensors:
-//   per player   pStates f32[N][cap][obs]  pMasks u8[N][cap][A]  pActions i32 / pLogProbs f32 / pRewards f32 / pTerminals i8 [N][cap]
+//   per player   PAGES of TRAJ_ROWS steps out of one pool (pStates f32[pool rows][obs], pMasks u8[pool rows][A], pActions i32 /
+//                pLogProbs f32 / pRewards f32 / pTerminals i8 [pool rows]); pageOf[N][pages per episode] says which page holds
+//                steps 16 k .. 16 k + 15 of a player's running episode. A page is taken off the free stack when a player's
+//                length reaches a multiple of TRAJ_ROWS and goes back when the finished buffer has been moved, so the pool
+//                holds what is in flight (players x mean episode length), not players x maxEpisodeLength
 //   combined     the same six tensors with capacity_timesteps rows + nextStates f32[capacity_truncated][obs]
 // and a step costs four small launches: the row append (HBM-bound, one row in and out per player), the scalar append, an
 // ordered scan over the players that finished this step (segment offsets in player order, exactly the order of the
@@ -19,6 +23,9 @@ constexpr int TRAJ_ROWS = 16;           // rows of a finished segment one warp m
 
 struct TrajDev {
     int N, ppa, obs, A, cap, maxEpLen;
+    int pagesPerPlayer, numPages;                       // page table width; pages in the pool
+    int* pageOf;                                        // [N][pagesPerPlayer] page of the player's k-th run of TRAJ_ROWS steps
+    int* freePages; int* freeTop;                       // stack of free pages; allocation and release never share a launch
     long long capL, capK;
     float* pStates; uint8_t* pMasks; int32_t* pActions; float* pLogProbs; float* pRewards; int8_t* pTerminals; int* pLen;
     int* segLen;                                        // per player, this step: length of the finished buffer (0 = still running)
@@ -51,7 +58,22 @@ __global__ void __launch_bounds__(256) traj_push_obs_kernel(TrajDev T, const flo
     const int lane = threadIdx.x & 31;
     const int p = (int)(((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
     if (p >= T.N) return;
-    const long long row = (long long)p * T.cap + T.pLen[p];
+    const int len = T.pLen[p];
+    int page;
+    if (len % TRAJ_ROWS == 0) {                                     // first step of a page: take one off the free stack
+        page = 0;
+        if (lane == 0) {
+            const int top = atomicSub(T.freeTop, 1) - 1;
+            if (top >= 0) page = T.freePages[top];
+            else { page = -1; T.counts[2] = 2; }                    // pool exhausted: sticky, the host call fails (ggl_traj_counts)
+            T.pageOf[(long long)p * T.pagesPerPlayer + len / TRAJ_ROWS] = page;
+        }
+        page = __shfl_sync(0xffffffffu, page, 0);
+    } else {
+        page = T.pageOf[(long long)p * T.pagesPerPlayer + len / TRAJ_ROWS];
+    }
+    if (page < 0) return;
+    const long long row = (long long)page * TRAJ_ROWS + len % TRAJ_ROWS;
     warp_copy(T.pStates + row * T.obs, obs + (long long)p * T.obs, T.obs, lane);
     warp_copy_bytes(T.pMasks + row * T.A, masks + (long long)p * T.A, T.A, lane);
 }
@@ -60,14 +82,17 @@ __global__ void __launch_bounds__(256) traj_push_obs_kernel(TrajDev T, const flo
 __device__ __forceinline__ int traj_push_scalars(const TrajDev& T, int p, const int32_t* __restrict__ actions, const float* __restrict__ logProbs,
                                                  const float* __restrict__ rewards, const uint8_t* __restrict__ terminals, int8_t& termOut) {
     const int len = T.pLen[p];
-    const long long row = (long long)p * T.cap + len;
-    T.pActions[row] = actions[p];
-    T.pRewards[row] = rewards[p];
-    T.pLogProbs[row] = logProbs[p];
+    const int page = T.pageOf[(long long)p * T.pagesPerPlayer + len / TRAJ_ROWS];
+    const long long row = (long long)(page < 0 ? 0 : page) * TRAJ_ROWS + len % TRAJ_ROWS;
+    if (page >= 0) {
+        T.pActions[row] = actions[p];
+        T.pRewards[row] = rewards[p];
+        T.pLogProbs[row] = logProbs[p];
+    }
     const int newLen = len + 1;                                     // traj.Length() after the push_backs of :826-828
     int8_t term = (int8_t)terminals[p / T.ppa];                     // :831-841
     if (!term && newLen >= T.maxEpLen) term = 2;                    // :848-850 forced TRUNCATED
-    T.pTerminals[row] = term;
+    if (page >= 0) T.pTerminals[row] = term;
     T.segLen[p] = term == 2 ? -newLen : (term ? newLen : 0);        // TRUNCATED rides in the sign
     T.pLen[p] = term ? 0 : newLen;                                  // traj.Clear() at :861
     termOut = term;
@@ -126,7 +151,7 @@ __global__ void __launch_bounds__(1024) traj_scan_kernel(TrajDev T) {
     }
     if (tid == 0) {
         if (baseLen + carryLen > T.capL || baseK + carryTr > T.capK) {
-            T.counts[2] = 1;                                        // out of capacity: nothing is copied, the host call fails
+            if (T.counts[2] == 0) T.counts[2] = 1;                  // out of capacity: nothing is copied, the host call fails
             T.counts[3] = 0;
         } else {
             T.counts[0] = baseLen + carryLen;
@@ -141,7 +166,7 @@ __global__ void __launch_bounds__(256) traj_move_kernel(TrajDev T, const float* 
     const int lane = threadIdx.x & 31;
     const long long warp = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
-    const int chunks = (T.cap + TRAJ_ROWS - 1) / TRAJ_ROWS;
+    const int chunks = T.pagesPerPlayer;
     const long long items = T.counts[3] * chunks;
     for (long long item = warp; item < items; item += nwarps) {
         const int k = (int)(item / chunks), c = (int)(item - (long long)k * chunks);
@@ -150,7 +175,9 @@ __global__ void __launch_bounds__(256) traj_move_kernel(TrajDev T, const float* 
         const int r0 = c * TRAJ_ROWS;
         if (r0 >= len) continue;
         const int rows = min(TRAJ_ROWS, len - r0);
-        const long long src = (long long)p * T.cap + r0, dst = T.finOff[k] + r0;
+        const int page = T.pageOf[(long long)p * T.pagesPerPlayer + c];
+        if (page < 0) continue;                                     // pool was exhausted while this buffer grew (flagged)
+        const long long src = (long long)page * TRAJ_ROWS, dst = T.finOff[k] + r0;
         warp_copy(T.cStates + dst * T.obs, T.pStates + src * T.obs, rows * T.obs, lane);
         warp_copy_bytes(T.cMasks + dst * T.A, T.pMasks + src * T.A, rows * T.A, lane);
         if (lane < rows) {
@@ -164,7 +191,15 @@ __global__ void __launch_bounds__(256) traj_move_kernel(TrajDev T, const float* 
             float* d = T.cNext + T.finNext[k] * T.obs;
             warp_copy(d, s, T.obs, lane);
         }
+        __syncwarp();
+        if (lane == 0) T.freePages[atomicAdd(T.freeTop, 1)] = page;     // the page is free again (no allocation runs in this launch)
     }
+}
+
+__global__ void traj_init_pages_kernel(TrajDev T) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < T.numPages) T.freePages[i] = T.numPages - 1 - i;        // page 0 on top
+    if (i == 0) *T.freeTop = T.numPages;
 }
 
 }  // namespace
@@ -212,22 +247,35 @@ extern "C" int ggl_traj_create(const ggl_traj_desc* d, ggl_traj** out) {
     T.maxEpLen = d->max_episode_length;
     T.cap = d->max_episode_length > 1 ? d->max_episode_length : 1;   // a buffer is flushed as soon as it holds maxEpisodeLength steps
     T.capL = d->capacity_timesteps; T.capK = d->capacity_truncated;
-    const size_t rows = (size_t)T.N * T.cap;
+    // Per-player storage: pages of TRAJ_ROWS steps from one pool. capacity_player_rows = 0 sizes the pool for the worst case
+    // (every player at maxEpisodeLength: C2's shape, 16 384 players x 1 800 steps x obs 167, is 22 GB; 98 304 players x 1 800 x
+    // obs 225 would be 177 GB); a positive value sizes it for the steps that are in flight at any one time (players x the
+    // episode length one expects, with margin) - running out of pages is reported by ggl_traj_counts, not silently dropped.
+    T.pagesPerPlayer = (T.cap + TRAJ_ROWS - 1) / TRAJ_ROWS;
+    const long long worstPages = (long long)T.N * T.pagesPerPlayer;
+    long long pages = worstPages;
+    if (d->capacity_player_rows > 0) {
+        pages = (d->capacity_player_rows + TRAJ_ROWS - 1) / TRAJ_ROWS;
+        if (pages < T.N) pages = T.N;                                // every player holds at least its current page
+        if (pages > worstPages) pages = worstPages;
+    }
+    if (pages > 0x7FFFFFF0ll / TRAJ_ROWS) { ggl::set_error("ggl_traj_create: per-player pool of %lld pages is too large", pages); tfree(t); return GGL_ERR_INVALID; }
+    T.numPages = (int)pages;
+    const size_t rows = (size_t)pages * TRAJ_ROWS;
     {
-        // The per-player buffers are dense [numPlayers][maxEpisodeLength] rows (most of them never touched when episodes are
-        // short): refuse with the numbers instead of failing somewhere inside cudaMalloc. C2's shape (16 384 players x 1 800
-        // steps x obs 167) needs 22 GB; 98 304 players x 1 800 x obs 225 would need 177 GB and does not fit one B200.
         const size_t perRow = (size_t)T.obs * 4 + (size_t)T.A + 4 + 4 + 4 + 1;
-        const size_t need = rows * perRow + (size_t)T.capL * perRow + (size_t)T.capK * T.obs * 4;
+        const size_t need = rows * perRow + (size_t)T.capL * perRow + (size_t)T.capK * T.obs * 4 + (size_t)worstPages * 4;
         size_t freeB = 0, totalB = 0;
         if (cudaMemGetInfo(&freeB, &totalB) == cudaSuccess && need > freeB) {
-            ggl::set_error("ggl_traj_create: %zu players x %d steps per episode x %zu B per step + the combined stream need %.1f GB, %.1f GB are free "
-                           "on device %d: lower max_episode_length (every player's buffer is allocated at full length)",
-                           (size_t)T.N, T.cap, perRow, need / 1e9, freeB / 1e9, d->device);
+            ggl::set_error("ggl_traj_create: a per-player pool of %zu steps (%zu players, up to %d steps per episode) x %zu B per step + the "
+                           "combined stream need %.1f GB, %.1f GB are free on device %d: set capacity_player_rows to the steps in flight "
+                           "(players x expected episode length) or lower max_episode_length",
+                           rows, (size_t)T.N, T.cap, perRow, need / 1e9, freeB / 1e9, d->device);
             tfree(t);
             return GGL_ERR_NOMEM;
         }
     }
+    TRAJ_TRY(talloc(t, &T.pageOf, (size_t)worstPages)); TRAJ_TRY(talloc(t, &T.freePages, (size_t)pages)); TRAJ_TRY(talloc(t, &T.freeTop, (size_t)1));
     TRAJ_TRY(talloc(t, &T.pStates, rows * T.obs)); TRAJ_TRY(talloc(t, &T.pMasks, rows * T.A)); TRAJ_TRY(talloc(t, &T.pActions, rows));
     TRAJ_TRY(talloc(t, &T.pLogProbs, rows)); TRAJ_TRY(talloc(t, &T.pRewards, rows)); TRAJ_TRY(talloc(t, &T.pTerminals, rows));
     TRAJ_TRY(talloc(t, &T.pLen, (size_t)T.N)); TRAJ_TRY(talloc(t, &T.segLen, (size_t)T.N));
@@ -236,7 +284,8 @@ extern "C" int ggl_traj_create(const ggl_traj_desc* d, ggl_traj** out) {
     TRAJ_TRY(talloc(t, &T.cActions, (size_t)T.capL)); TRAJ_TRY(talloc(t, &T.cLogProbs, (size_t)T.capL)); TRAJ_TRY(talloc(t, &T.cRewards, (size_t)T.capL));
     TRAJ_TRY(talloc(t, &T.cTerminals, (size_t)T.capL)); TRAJ_TRY(talloc(t, &T.cNext, (size_t)T.capK * T.obs));
     TRAJ_TRY(talloc(t, &T.counts, (size_t)4));
-    if (cudaMemset(T.pLen, 0, sizeof(int) * T.N) != cudaSuccess || cudaMemset(T.counts, 0, sizeof(long long) * 4) != cudaSuccess ||
+    traj_init_pages_kernel<<<(T.numPages + 255) / 256, 256>>>(T);
+    if (cudaMemset(T.pageOf, 0xFF, sizeof(int) * (size_t)worstPages) != cudaSuccess || cudaMemset(T.pLen, 0, sizeof(int) * T.N) != cudaSuccess || cudaMemset(T.counts, 0, sizeof(long long) * 4) != cudaSuccess ||
         cudaMallocHost((void**)&t->h_counts, sizeof(long long) * 4) != cudaSuccess || cudaDeviceSynchronize() != cudaSuccess) {
         ggl::set_error("ggl_traj_create: initialisation failed: %s", cudaGetErrorString(cudaGetLastError())); tfree(t); return GGL_ERR_CUDA;
     }
@@ -296,7 +345,11 @@ extern "C" int ggl_traj_counts(ggl_traj* t, void* stream, int64_t* out_length, i
     GGL_CUDA(cudaMemcpyAsync(t->h_counts, t->T.counts, sizeof(long long) * 4, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
     GGL_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
     if (t->h_counts[2]) {
-        ggl::set_error("trajectory store out of capacity (%lld timesteps / %lld truncated rows)", t->T.capL, t->T.capK);
+        if (t->h_counts[2] == 2)
+            ggl::set_error("trajectory store: the per-player pool ran out of pages (%d pages of %d steps for %d players): raise "
+                           "capacity_player_rows", t->T.numPages, TRAJ_ROWS, t->T.N);
+        else
+            ggl::set_error("trajectory store out of capacity (%lld timesteps / %lld truncated rows)", t->T.capL, t->T.capK);
         return GGL_ERR_INVALID;
     }
     if (out_length) *out_length = t->h_counts[0];

@@ -106,8 +106,9 @@ private:
 class TrajectoryStore {
 public:
     TrajectoryStore(int device, int numPlayers, int playersPerArena, int obsSize, int numActions, int maxEpisodeLength, int64_t capacityTimesteps,
-                    int64_t capacityTruncated) {
-        ggl_traj_desc d = {device, numPlayers, playersPerArena, obsSize, numActions, maxEpisodeLength, capacityTimesteps, capacityTruncated};
+                    int64_t capacityTruncated, int64_t capacityPlayerRows = 0) {
+        // capacityPlayerRows: steps all per-player buffers hold together (0 = numPlayers x maxEpisodeLength, the worst case)
+        ggl_traj_desc d = {device, numPlayers, playersPerArena, obsSize, numActions, maxEpisodeLength, capacityTimesteps, capacityTruncated, capacityPlayerRows};
         Check(ggl_traj_create(&d, &h), "TrajectoryStore");
         Check(ggl_traj_views_get(h, &views), "TrajectoryStore views");
     }

@@ -27,12 +27,16 @@ def _compare(store, oracle, obs, na):
     assert np.array_equal(store.player_lengths(), oracle.player_lengths())
 
 
+@pytest.mark.parametrize("pool", ["worst_case", "in_flight"])
 @pytest.mark.parametrize("ci", range(len(tc.CASES)))
-def test_store_matches_oracle(ggl, ci):
+def test_store_matches_oracle(ggl, ci, pool):
+    """pool = in_flight: the per-player pages come from a pool sized for the steps in flight (players x the longest episode the
+    run can reach, page-rounded) instead of players x max_episode_length; pages are recycled as buffers flush."""
     case = tc.CASES[ci]
     arenas, ppa, obs, na, max_len, steps, _, _ = case
     n = arenas * ppa
-    store = ggl.TrajectoryStore(n, ppa, obs, na, max_len, capacity_timesteps=n * steps + 16)
+    rows = 0 if pool == "worst_case" else n * ((min(max_len, steps) + 15) // 16 * 16)
+    store = ggl.TrajectoryStore(n, ppa, obs, na, max_len, capacity_timesteps=n * steps + 16, capacity_player_rows=rows)
     oracle = to.TrajOracle(n, ppa, max_len)
     store.begin_iteration(); oracle.begin_iteration()
     for t, step in enumerate(tc.rollout(case, seed=ci)):
@@ -55,6 +59,39 @@ def test_capacity_is_enforced_loudly(ggl):
         store.push_obs(_dev(step[0]), _dev(step[1])); store.push_result(*[_dev(x) for x in step[2:]])
     with pytest.raises(ggl.GigaEnvError):
         store.counts()
+    store.close()
+
+
+def test_player_pool_exhaustion_is_reported(ggl):
+    """A pool of one 16-step page per player and episodes that run longer: the 17th step finds no page, ggl_traj_counts fails
+    with the pool named (nothing is written out of bounds, nothing is dropped silently)."""
+    store = ggl.TrajectoryStore(8, 2, 5, 3, 1000, capacity_timesteps=4096, capacity_player_rows=8 * 16)
+    store.begin_iteration()
+    case = (4, 2, 5, 3, 1000, 20, 0.0, 0.0)
+    for t, step in enumerate(tc.rollout(case)):
+        store.push_obs(_dev(step[0]), _dev(step[1])); store.push_result(*[_dev(x) for x in step[2:]])
+        if t < 16:
+            assert store.counts()[0] == 0
+    with pytest.raises(ggl.GigaEnvError, match="pages"):
+        store.counts()
+    store.close()
+
+
+def test_pages_are_recycled_over_many_episodes(ggl):
+    """2000 steps of 64 players with episodes of at most 24 steps through a pool of 2 pages per player: every page is handed out
+    and returned dozens of times; the stream still matches the oracle bit for bit."""
+    case = (16, 4, 12, 6, 24, 2000, 0.04, 0.04)
+    n = 64
+    store = ggl.TrajectoryStore(n, 4, 12, 6, 24, capacity_timesteps=n * 250, capacity_player_rows=n * 32)
+    oracle = to.TrajOracle(n, 4, 24)
+    store.begin_iteration(); oracle.begin_iteration()
+    for t, step in enumerate(tc.rollout(case, seed=3)):
+        if t % 200 == 199:
+            _compare(store, oracle, 12, 6)
+            store.begin_iteration(); oracle.begin_iteration()
+        oracle.push_obs(step[0], step[1]); oracle.push_result(*step[2:])
+        store.push_obs(_dev(step[0]), _dev(step[1])); store.push_result(*[_dev(x) for x in step[2:]])
+    _compare(store, oracle, 12, 6)
     store.close()
 
 
