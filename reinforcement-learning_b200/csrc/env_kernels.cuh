@@ -90,7 +90,7 @@ __device__ __forceinline__ void write_player_rows(const ArenaDev& A, const EnvCf
     uint32_t permMates = 0, permOpps = 0;
     if (cfg.obsKind == GGL_OBS_DEFAULT_PADDED) padded_obs_draws_upto(A.rng, cfg.obsMaxPlayers, slot, permMates, permOpps);
     build_obs_row(A, cfg, slot, P.obs + (size_t)row * cfg.obsSize, permMates, permOpps);
-    action_mask_row(A.cars[A.slotCar[slot]], P.actionTable, P.masks + (size_t)row * kNumActions);
+    action_mask_row(A.cars[A.slotCar[slot]], cfg.actionBits, P.masks + (size_t)row * kNumActions);
     P.slotCarId[row] = (int)A.cars[A.slotCar[slot]].id;
     P.slotTeam[row] = A.cars[A.slotCar[slot]].team;
 }

@@ -27,6 +27,9 @@ struct TerminalCfg {
     int kind;
     float params[2];
 };
+struct ActionBits {         // DefaultAction's ground / air / boost / jump action sets as bit sets over the 90 actions
+    uint32_t ground[3], air[3], boost[3], jump[3];
+};
 struct SetterCfg {
     int kind, flags;
     float cumWeight;        // CombinedState::cumulativeWeights (CombinedState.h:29-31)
@@ -37,6 +40,7 @@ struct EnvCfg {
     int obsMaxPlayers, setterFlags, numSetterChildren;
     float setterTotalWeight;
     SetterCfg setterChildren[GGL_MAX_SETTER_CHILDREN];
+    ActionBits actionBits;
     RewardCfg rewards[kMaxRewards];
     TerminalCfg terminals[kMaxTerminals];
 };
@@ -114,22 +118,36 @@ GGL_HD bool car_has_flip_or_jump(const CarDev& c) {
     return c.isOnGround || (!c.hasFlipped && !c.hasDoubleJumped && c.airTimeSinceJump < rl::DOUBLEJUMP_MAX_DELAY);
 }
 
-// DefaultAction::GetActionMask with the masks the constructor derives from the table
-GGL_HD void action_mask_row(const CarDev& c, const float* table /* [90*8] */, uint8_t* out) {
+// DefaultAction::GetActionMask with the masks the constructor derives from the table. The four sets the
+// constructor builds (ground, air, boost, jump actions) are 90-bit constants of the table: computed once (action_bits_from_table,
+// host side, at create) instead of per player and step from 450 table loads.
+GGL_HD void action_bits_from_table(const float* table /* [90*8] */, ActionBits& B) {
+    for (int w = 0; w < 3; w++) B.ground[w] = B.air[w] = B.boost[w] = B.jump[w] = 0u;
+    for (int i = 0; i < kNumActions; i++) {
+        const float* a = table + 8 * i;
+        const bool jump = a[5] != 0.f, boost = a[6] != 0.f;
+        const bool ground = i < kNumGroundActions;
+        bool air = (i > kNumGroundActions && !jump);
+        if (i < kNumGroundActions && a[0] == a[6] && ((a[3] != 0.f) == (a[7] != 0.f))) air = true;
+        const uint32_t bit = 1u << (i & 31);
+        if (ground) B.ground[i >> 5] |= bit;
+        if (air) B.air[i >> 5] |= bit;
+        if (boost) B.boost[i >> 5] |= bit;
+        if (jump) B.jump[i >> 5] |= bit;
+    }
+}
+GGL_HD void action_mask_row(const CarDev& c, const ActionBits& B, uint8_t* out /* 2-byte aligned: rows are 90 bytes */) {
     const bool onGround = c.isOnGround != 0;
     const bool noBoost = c.boost == 0.f;
     const bool turtled = c.worldContactHas && c.worldContactNormal.z > 0.9f;
     const bool jumpOk = car_has_flip_or_jump(c) || turtled;
-    for (int i = 0; i < kNumActions; i++) {
-        const float* a = table + 8 * i;
-        bool jump = a[5] != 0.f, boost = a[6] != 0.f;
-        bool ground = i < kNumGroundActions;
-        bool air = (i > kNumGroundActions && !jump);
-        if (i < kNumGroundActions && a[0] == a[6] && ((a[3] != 0.f) == (a[7] != 0.f))) air = true;
-        uint8_t m = onGround ? (ground ? 1 : 0) : (air ? 1 : 0);
-        if (noBoost && boost) m = 0;
-        if (jumpOk && jump) m = 1;
-        out[i] = m;
+    uint16_t* o = reinterpret_cast<uint16_t*>(out);
+    for (int w = 0; w < 3; w++) {
+        uint32_t m = onGround ? B.ground[w] : B.air[w];
+        if (noBoost) m &= ~B.boost[w];
+        if (jumpOk) m |= B.jump[w];
+        const int n = w < 2 ? 16 : (kNumActions - 64) / 2;          // byte pairs of this word: 16, 16, 13
+        for (int k = 0; k < n; k++) o[16 * w + k] = (uint16_t)(((m >> (2 * k)) & 1u) | (((m >> (2 * k + 1)) & 1u) << 8));
     }
 }
 

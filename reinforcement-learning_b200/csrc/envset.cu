@@ -160,6 +160,7 @@ extern "C" int ggl_envset_create(const ggl_envset_desc* d, ggl_envset** out) {
     e->P.world = w;
     float table[kNumActions * 8];
     ggl_action_table(table, nullptr);
+    action_bits_from_table(table, e->cfg.actionBits);
     cudaMemcpy(e->d_table, table, sizeof(table), cudaMemcpyHostToDevice);
     e->P.actionTable = e->d_table;
     // initial arena blobs: cars exist (AddCar order: blue first), everything else comes from the first reset

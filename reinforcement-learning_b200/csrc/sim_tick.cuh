@@ -94,7 +94,18 @@ GGL_HD void car_check_pads(ArenaDev& A, int ci) {
     const V3 posUU = car.pos * kBT2UU;
     if (posUU.z > rl::PAD_CYL_HEIGHT + 250.f) return;
     const int ix = (int)(posUU.x / 1024 + 4), iy = (int)(posUU.y / 1024 + 5);
-    const int lx0 = ix - 1 < 0 ? 0 : ix - 1, lx1 = ix + 1 > 7 ? 7 : ix + 1, ly0 = iy - 1 < 0 ? 0 : iy - 1, ly1 = iy + 1 > 9 ? 9 : iy + 1;
+    int lx0 = ix - 1 < 0 ? 0 : ix - 1, lx1 = ix + 1 > 7 ? 7 : ix + 1, ly0 = iy - 1 < 0 ? 0 : iy - 1, ly1 = iy + 1 > 9 ? 9 : iy + 1;
+    {   // cull (exact): a pad lies inside its own cell, and neither test below can pass for a pad further than 300 uu from the
+        // car along x or y (cylinder radius <= 208; lock box half width 160 + the car's AABB reach, < 100 uu for the hitbox
+        // half diagonal 75 plus its offset 25) - so only the cells that the car's 300 uu surroundings touch can matter
+        const float R = 300.f;
+        const int cx0 = (int)((posUU.x - R) / 1024 + 4), cx1 = (int)((posUU.x + R) / 1024 + 4);
+        const int cy0 = (int)((posUU.y - R) / 1024 + 5), cy1 = (int)((posUU.y + R) / 1024 + 5);
+        if (cx0 > lx0) lx0 = cx0;
+        if (cx1 < lx1) lx1 = cx1;
+        if (cy0 > ly0) ly0 = cy0;
+        if (cy1 < ly1) ly1 = cy1;
+    }
     for (int i = lx0; i <= lx1; i++)
         for (int j = ly0; j <= ly1; j++) {
             const int p = cell_pad(i, j);

@@ -138,7 +138,7 @@ static void host_write_rows(HostEnv* h, int a) {
         uint32_t pm = 0, po = 0;
         if (h->cfg.obsKind == GGL_OBS_DEFAULT_PADDED) padded_obs_draw(A.rng, h->cfg.obsMaxPlayers, pm, po);
         build_obs_row(A, h->cfg, s, h->obs.data() + (size_t)row * h->cfg.obsSize, pm, po);
-        action_mask_row(A.cars[A.slotCar[s]], h->table.data(), h->masks.data() + (size_t)row * kNumActions);
+        action_mask_row(A.cars[A.slotCar[s]], h->cfg.actionBits, h->masks.data() + (size_t)row * kNumActions);
     }
 }
 
@@ -182,6 +182,7 @@ void* hostenv_create(const ggl_envset_desc* d) {
     h->masks.assign((size_t)np * kNumActions, 0); h->terminals.assign(c.numArenas, 0); h->events.assign((size_t)np * 9, 0);
     h->table.resize(kNumActions * 8);
     for (int i = 0; i < kNumActions; i++) action_from_index(i, h->table.data() + 8 * i);
+    action_bits_from_table(h->table.data(), c.actionBits);
     for (int a = 0; a < c.numArenas; a++) {
         ArenaDev& A = h->arenas[a];
         A.numCars = c.numCars; A.rng = (uint32_t)(d->seed * 7919u + a * 104729u + 1u) % 2147483646u + 1u;
