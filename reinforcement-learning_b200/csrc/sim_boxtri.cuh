@@ -134,16 +134,6 @@ GGL_HDN bool box_tri_closest(const BoxTri& world, float maxDistSq, ClosestOut& o
 }
 
 // ---------------------------------------------------------------------------------------------- car vs mesh
-GGL_HD bool tri_overlaps_aabb(const Tri& t, V3 mn, V3 mx) {
-    if (fminf(fminf(t.v0.x, t.v1.x), t.v2.x) > mx.x) return false;
-    if (fmaxf(fmaxf(t.v0.x, t.v1.x), t.v2.x) < mn.x) return false;
-    if (fminf(fminf(t.v0.z, t.v1.z), t.v2.z) > mx.z) return false;
-    if (fmaxf(fmaxf(t.v0.z, t.v1.z), t.v2.z) < mn.z) return false;
-    if (fminf(fminf(t.v0.y, t.v1.y), t.v2.y) > mx.y) return false;
-    if (fmaxf(fmaxf(t.v0.y, t.v1.y), t.v2.y) < mn.y) return false;
-    return true;
-}
-
 // Narrow phase of one (car, triangle) pair: pure function of the car's transform and the triangle. False = no contact point.
 GGL_HDN bool car_tri_narrow(const CarDev& car, const Tri& t, V3 boxPos, const BoxGeom& bg, float cbt, ClosestOut& o, Voronoi& vs) {
     // early out: hitbox fully on one side of the triangle plane, further away than the breaking threshold

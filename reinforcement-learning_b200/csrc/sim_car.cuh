@@ -324,6 +324,9 @@ GGL_HD void ray_vs_car_box(V3 from, V3 to, const CarDev& oc, int kind, RayHit& h
             mn = mn - v3(0.02f, 0.02f, 0.02f); mx = mx + v3(0.02f, 0.02f, 0.02f);
         }
         if (mn.x > mx.x) return;
+        // the usual case first: the segment's own box misses the car's (then the slab test below fails on that axis too)
+        if (fminf(from.x, to.x) > mx.x || fmaxf(from.x, to.x) < mn.x || fminf(from.y, to.y) > mx.y || fmaxf(from.y, to.y) < mn.y ||
+            fminf(from.z, to.z) > mx.z || fmaxf(from.z, to.z) < mn.z) return;
         const V3 d = to - from;
         float t0 = 0.f, t1 = 1.f;
         for (int i = 0; i < 3; i++) {

@@ -228,6 +228,16 @@ GGL_HD bool sphere_triangle(V3 centre, const Tri& t, float radius, float cbt, V3
     return false;
 }
 
+GGL_HD bool tri_overlaps_aabb(const Tri& t, V3 mn, V3 mx) {
+    if (fminf(fminf(t.v0.x, t.v1.x), t.v2.x) > mx.x) return false;
+    if (fmaxf(fmaxf(t.v0.x, t.v1.x), t.v2.x) < mn.x) return false;
+    if (fminf(fminf(t.v0.z, t.v1.z), t.v2.z) > mx.z) return false;
+    if (fmaxf(fmaxf(t.v0.z, t.v1.z), t.v2.z) < mn.z) return false;
+    if (fminf(fminf(t.v0.y, t.v1.y), t.v2.y) > mx.y) return false;
+    if (fmaxf(fmaxf(t.v0.y, t.v1.y), t.v2.y) < mn.y) return false;
+    return true;
+}
+
 GGL_HD void collide_ball_mesh(ArenaDev& A, ContactSink& S, const WorldDev& W) {
     if (W.numTris <= 0) return;
     const BallDev& b = A.ball;
@@ -249,6 +259,9 @@ GGL_HD void collide_ball_mesh(ArenaDev& A, ContactSink& S, const WorldDev& W) {
                     int pos = 0; bool dup = false;
                     while (pos < nc && (int)cand[pos] <= ti) { dup |= (int)cand[pos] == ti; pos++; }
                     if (dup || nc >= 24) continue;
+                    // cull (exact): a triangle whose box misses the ball's box is further than radius + 0.08 away, and
+                    // sphere_triangle reports nothing beyond radius + kBallCBT (0.038)
+                    if (!tri_overlaps_aabb(W.tris[ti], mn, mx)) continue;
                     for (int q = nc; q > pos; q--) cand[q] = cand[q - 1];
                     cand[pos] = (uint16_t)ti; nc++;
                 }
