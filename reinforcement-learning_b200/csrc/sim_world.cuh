@@ -292,10 +292,9 @@ GGL_HD void collide_ball_mesh(ArenaDev& A, ContactSink& S, const WorldDev& W) {
 }
 
 // car hitbox vs plane: the single deepest support vertex (perturbation iterations are off in the reference)
-GGL_HD void collide_car_plane(ArenaDev& A, ContactSink& S, int ci, V3 n, V3 origin) {
+GGL_HD void collide_car_plane(ArenaDev& A, ContactSink& S, int ci, V3 n, V3 origin, V3 boxPos /* car.pos + basis * hitbox offset */) {
     CarDev& car = A.cars[ci];
     const BoxGeom bg = car_box();
-    V3 boxPos = car.pos + mul(car.basis, car_hitbox_offset());
     // cull (exact): the support vertex is never further inside than the box centre minus the half diagonal
     if (dot(n, boxPos - origin) - len(bg.full) * 1.0001f > car_cbt()) return;
     V3 dirLocal = tmul(car.basis, -n);
@@ -683,6 +682,10 @@ GGL_HDN void collide_car_car(ArenaDev& A, ContactSink& S, int lo, int hi);
 // has no margin; a disabled body's manifold is never solved)
 GGL_HD bool car_car_may_touch(const CarDev& a, const CarDev& b) {
     if (a.rbDisabled || b.rbDisabled) return false;
+    {   // the usual case first: the cars' origins alone are too far apart (the box centres sit |offset| from them)
+        const float far = 2.0002f * len(car_box().full) + 2.f * len(car_hitbox_offset()) + 0.01f;
+        if (len2(a.pos - b.pos) > far * far) return false;
+    }
     const V3 pa = a.pos + mul(a.basis, car_hitbox_offset()), pb = b.pos + mul(b.basis, car_hitbox_offset());
     const float r2 = 2.0002f * len(car_box().full);
     return !(len2(pa - pb) > r2 * r2);
@@ -735,10 +738,16 @@ GGL_HDN void collide_body(ArenaDev& A, const WorldDev& W, int b) {
         GGL_SUB(0);
         if (A.meshCandN[i]) car_mesh_emit(A, S, W, i);      // candidates and narrow phase ran in the two stages before (sim_tick.cuh)
         GGL_SUB(1);
-        collide_car_plane(A, S, i, v3(0, 0, 1), v3(0, 0, 0));
-        collide_car_plane(A, S, i, v3(0, 0, -1), v3(0, 0, hz));
-        collide_car_plane(A, S, i, v3(1, 0, 0), v3(-ex, 0, hz / 2));
-        collide_car_plane(A, S, i, v3(-1, 0, 0), v3(ex, 0, hz / 2));
+        {
+            // the four arena planes are axis-aligned: dot(n, boxPos - origin) is one component difference (the products with the
+            // normal's 0 and 1 components add nothing), so the cull of collide_car_plane is evaluated here without the call
+            const V3 boxPos = A.cars[i].pos + mul(A.cars[i].basis, car_hitbox_offset());
+            const float lim = len(car_box().full) * 1.0001f, cbt = car_cbt();
+            if (!((boxPos.z - 0.f) - lim > cbt)) collide_car_plane(A, S, i, v3(0, 0, 1), v3(0, 0, 0), boxPos);
+            if (!(-(boxPos.z - hz) - lim > cbt)) collide_car_plane(A, S, i, v3(0, 0, -1), v3(0, 0, hz), boxPos);
+            if (!((boxPos.x - (-ex)) - lim > cbt)) collide_car_plane(A, S, i, v3(1, 0, 0), v3(-ex, 0, hz / 2), boxPos);
+            if (!(-(boxPos.x - ex) - lim > cbt)) collide_car_plane(A, S, i, v3(-1, 0, 0), v3(ex, 0, hz / 2), boxPos);
+        }
         GGL_SUB(2);
         for (int j = i + 1; j < P; j++)
             if (car_car_may_touch(A.cars[i], A.cars[j])) collide_car_car(A, S, i, j);
