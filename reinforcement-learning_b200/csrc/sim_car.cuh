@@ -318,6 +318,7 @@ GGL_HD void ray_vs_car_box(V3 from, V3 to, const CarDev& oc, int kind, RayHit& h
     // the AABB of the LAST tick's collision detection (car_update_ray_aabb). A state that was just injected has none yet
     // (all zero): the AABB of the current transform stands in.
     {
+        if (oc.aabbMin.x > oc.aabbMax.x) return;        // the usual case: no other car was within reach last tick (car_update_ray_aabb)
         V3 mn = oc.aabbMin, mx = oc.aabbMax;
         if (is_zero(mn) && is_zero(mx)) {
             car_world_aabb(oc.pos, oc.basis, mn, mx);

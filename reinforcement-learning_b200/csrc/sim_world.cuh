@@ -477,7 +477,8 @@ GGL_HD void friction_dir(const SolverBody* sb, int a, int b, V3 n, V3 rel1, V3 r
     }
 }
 
-GGL_HD void resolve_row(Row& c, SolverBody* sb, int a, int b, float lower, float upper, bool lowerOnly) {
+// returns the impulse change it applied
+GGL_HD float resolve_row(Row& c, SolverBody* sb, int a, int b, float lower, float upper, bool lowerOnly) {
     float delta = c.rhs - c.applied * 0.f;
     SolverBody& A = sb[a];
     const V3 n2 = -c.n1;
@@ -491,6 +492,7 @@ GGL_HD void resolve_row(Row& c, SolverBody* sb, int a, int b, float lower, float
     else c.applied = sum;
     sb_apply(A, c.n1 * A.invMass, c.angA, delta);
     if (b >= 0) sb_apply(sb[b], n2 * sb[b].invMass, c.angB, delta);
+    return delta;
 }
 
 GGL_HD void resolve_push(Row& c, SolverBody* sb, int a, int b) {
@@ -595,12 +597,17 @@ GGL_HD void solve_island_rows(ArenaDev& A, SolverBody* sb, int rep) {
         }
         if (!any) break;
     }
+    // The reference always runs its 10 iterations (RocketSim's solveGroupCacheFriendlyIterations has no residual test). An
+    // iteration in which EVERY row's impulse change is exactly zero leaves every applied impulse and every body's delta velocity
+    // as it found them, so all later iterations would repeat it: stopping there changes nothing. Islands with one or two
+    // active rows reach that fixed point after a few iterations; rows that only sit inside the breaking threshold at once.
     for (int it = 0; it < 10; it++) {
+        bool moved = false;
         for (int j = 0; j < nr; j++) {
             const int k = get(j);
             const int meta = __float_as_int_portable(R.at(2 * k + 1).appliedPush);
             if (meta & 0x10000) continue;
-            resolve_row(R.at(2 * k), sb, meta & 0xff, (int)(int8_t)((meta >> 8) & 0xff), 0.f, 1e10f, true);
+            moved |= resolve_row(R.at(2 * k), sb, meta & 0xff, (int)(int8_t)((meta >> 8) & 0xff), 0.f, 1e10f, true) != 0.f;
         }
         for (int j = 0; j < nr; j++) {
             const int k = get(j);
@@ -609,9 +616,10 @@ GGL_HD void solve_island_rows(ArenaDev& A, SolverBody* sb, int rep) {
             if (tot > 0.f) {
                 const int meta = __float_as_int_portable(F.appliedPush);
                 const float mu = F.rhsPen;
-                resolve_row(F, sb, meta & 0xff, (int)(int8_t)((meta >> 8) & 0xff), -(mu * tot), mu * tot, false);
+                moved |= resolve_row(F, sb, meta & 0xff, (int)(int8_t)((meta >> 8) & 0xff), -(mu * tot), mu * tot, false) != 0.f;
             }
         }
+        if (!moved) break;
     }
 }
 
