@@ -398,8 +398,12 @@ GGL_HD void wheel_first(ArenaDev& A, const WorldDev& W, int ci, int i) {
         Wheel& w = c.w[i];
         const WheelGeom g = wheel_geom(i);
         // wheel frame with LAST tick's steer angle
-        Q4 q = quat_axis_angle(up, w.steerAngle);
-        w.latDir = mul(m3_from_quat(q), right);
+        if (w.steerAngle == 0.f) {
+            w.latDir = right;           // the rotation by angle 0 is the identity matrix (up to the sign of zeros): rear wheels always
+        } else {
+            Q4 q = quat_axis_angle(up, w.steerAngle);
+            w.latDir = mul(m3_from_quat(q), right);
+        }
         w.hardPoint = c.pos + mul(c.basis, g.conn);
         const V3 wheelDir = -up;
         const float rayLen = g.restLen + kSuspTravel + g.radius - rl::SUSP_SUBTRACTION;

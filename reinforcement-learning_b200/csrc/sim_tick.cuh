@@ -222,8 +222,13 @@ GGL_HD void arena_tick(ArenaDev& A, const WorldDev& W, const Exec& ex) {
     ex.sync();
     if (GGL_PSYNC_MASK & 2) ex.phase_sync();
     GGL_PH(1);
-    for (int r = ex.lane(); r < 4 * A.numCars; r += ex.lanes())
-        if (!A.cars[r >> 2].isDemoed) wheel_first(A, W, r >> 2, r & 3);
+    // the front wheels of all cars first, then the rear wheels (which never steer): with 8 lanes and 4 cars a round of the loop is
+    // all front or all rear, and the rear round skips the steering frame as a whole
+    for (int t = ex.lane(); t < 4 * A.numCars; t += ex.lanes()) {
+        const int rear = t >= 2 * A.numCars ? 1 : 0, u = t - 2 * A.numCars * rear;
+        const int car = u >> 1, wheel = (u & 1) + 2 * rear;
+        if (!A.cars[car].isDemoed) wheel_first(A, W, car, wheel);
+    }
     ex.sync();
     if (GGL_PSYNC_MASK & 4) ex.phase_sync();
     GGL_PH(2);
