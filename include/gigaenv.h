@@ -148,6 +148,8 @@ typedef struct ggl_envset_desc {
     int32_t state_setter_flags; /* GGL_SETTER_RANDOM: ggl_random_state_flags */
     int32_t num_setter_children;/* GGL_SETTER_COMBINED: 1..GGL_MAX_SETTER_CHILDREN */
     ggl_setter_child setter_children[GGL_MAX_SETTER_CHILDREN];
+    float   obs_coefs[5];       /* GGL_OBS_DEFAULT / _DEFAULT_PADDED: the constructor's posCoef x, y, z, velCoef, angVelCoef
+                                   (DefaultObs.h:9-17); all five 0 = the defaults 1/4096, 1/5120, 1/2044, 1/2300, 1/5.5 */
 } ggl_envset_desc;
 
 /* ---- host-visible state (mirrors RocketSim CarState/BallState/BoostPadState + hidden wheel state) ---- */

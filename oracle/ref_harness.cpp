@@ -325,8 +325,13 @@ void* ref_envset_create(const ggl_envset_desc* d) {
                 if (desc.terminals[i].kind == GGL_TERM_GOAL_SCORE) r.terminalConditions.push_back(new GoalScoreCondition());
                 else r.terminalConditions.push_back(new NoTouchCondition(desc.terminals[i].params[0]));
             }
-            if (desc.obs_kind == GGL_OBS_DEFAULT_PADDED) r.obsBuilder = new DefaultObsPadded(desc.obs_max_players);
-            else r.obsBuilder = (desc.obs_kind == GGL_OBS_ADVANCED) ? (ObsBuilder*)new AdvancedObs() : (ObsBuilder*)new DefaultObs();
+            bool customCoefs = false;
+            for (int i = 0; i < 5; i++) customCoefs = customCoefs || desc.obs_coefs[i] != 0.f;
+            const Vec pc(desc.obs_coefs[0], desc.obs_coefs[1], desc.obs_coefs[2]);
+            if (desc.obs_kind == GGL_OBS_DEFAULT_PADDED)
+                r.obsBuilder = customCoefs ? new DefaultObsPadded(desc.obs_max_players, pc, desc.obs_coefs[3], desc.obs_coefs[4]) : new DefaultObsPadded(desc.obs_max_players);
+            else if (desc.obs_kind == GGL_OBS_ADVANCED) r.obsBuilder = new AdvancedObs();
+            else r.obsBuilder = customCoefs ? new DefaultObs(pc, desc.obs_coefs[3], desc.obs_coefs[4]) : new DefaultObs();
             r.actionParser = new DefaultAction();
             auto makeSetter = [env, index](int kind, int flags) -> StateSetter* {
                 if (kind == GGL_SETTER_INJECTED) {

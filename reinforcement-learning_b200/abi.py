@@ -47,7 +47,7 @@ class EnvSetDesc(C.Structure):
         ("state_setter", C.c_int32), ("num_meshes", C.c_int32), ("meshes", C.POINTER(MeshBlob)),
         ("seed", C.c_uint64), ("slot_order_reversed", C.c_int32),
         ("obs_max_players", C.c_int32), ("state_setter_flags", C.c_int32), ("num_setter_children", C.c_int32),
-        ("setter_children", SetterChild * GGL_MAX_SETTER_CHILDREN),
+        ("setter_children", SetterChild * GGL_MAX_SETTER_CHILDREN), ("obs_coefs", C.c_float * 5),
     ]
 
 
@@ -124,7 +124,7 @@ class EnvSetViews(C.Structure):
 
 def make_desc(num_arenas, players_per_team, obs_kind=OBS_ADVANCED, rewards=None, terminals=None,
               tick_skip=8, action_delay=7, state_setter=SETTER_KICKOFF, meshes=None, seed=0, device=0,
-              slot_order_reversed=1, obs_max_players=0, state_setter_flags=0, setter_children=None):
+              slot_order_reversed=1, obs_max_players=0, state_setter_flags=0, setter_children=None, obs_coefs=None):
     """rewards: list of (kind, weight[, params[, zero_sum]]); terminals: list of (kind[, params]);
     setter_children (SETTER_COMBINED): list of (kind, weight[, flags]).
     Returns (desc, keepalive) — keepalive holds the mesh buffers the desc points into."""
@@ -169,6 +169,8 @@ def make_desc(num_arenas, players_per_team, obs_kind=OBS_ADVANCED, rewards=None,
     d.slot_order_reversed = slot_order_reversed
     d.obs_max_players = obs_max_players
     d.state_setter_flags = state_setter_flags
+    for i, k in enumerate(obs_coefs or []):      # DefaultObs(posCoef xyz, velCoef, angVelCoef); None = the defaults
+        d.obs_coefs[i] = k
     setter_children = setter_children or []
     d.num_setter_children = len(setter_children)
     for i, ch in enumerate(setter_children):

@@ -39,6 +39,7 @@ struct EnvCfg {
     int numRewards, numTerminals, stateSetter;
     int obsMaxPlayers, setterFlags, numSetterChildren;
     float setterTotalWeight;
+    float obsCoef[5];           // DefaultObs / DefaultObsPadded: posCoef x y z, velCoef, angVelCoef
     SetterCfg setterChildren[GGL_MAX_SETTER_CHILDREN];
     ActionBits actionBits;
     RewardCfg rewards[kMaxRewards];
@@ -62,6 +63,13 @@ inline const char* env_cfg_plugins(EnvCfg& c, const ggl_envset_desc* d) {
         return "unsupported obs kind";
     }
     c.obsSize = env_obs_size(d->obs_kind, 2 * d->players_per_team, c.obsMaxPlayers);
+    {
+        bool any = false;
+        for (int i = 0; i < 5; i++) any = any || d->obs_coefs[i] != 0.f;
+        const float dflt[5] = {1 / 4096.f, 1 / 5120.f, 1 / 2044.f, 1 / 2300.f, 1 / 5.5f};      // CommonValues.h: SIDE_WALL_X, BACK_WALL_Y, CEILING_Z, CAR_MAX_SPEED, CAR_MAX_ANG_VEL
+        for (int i = 0; i < 5; i++) c.obsCoef[i] = any ? d->obs_coefs[i] : dflt[i];
+        if (any && d->obs_kind == GGL_OBS_ADVANCED) return "AdvancedObs has no coefficient arguments (AdvancedObs.h:10-13)";
+    }
     c.stateSetter = d->state_setter; c.setterFlags = d->state_setter_flags; c.numSetterChildren = 0; c.setterTotalWeight = 0.f;
     if (d->state_setter < GGL_SETTER_KICKOFF || d->state_setter > GGL_SETTER_COMBINED) return "unsupported state setter kind";
     if (d->state_setter == GGL_SETTER_COMBINED) {

@@ -209,16 +209,14 @@ GGL_HD int pad_index_map(int i) {
     return map[i];
 }
 
-GGL_HD void write_player_default(float*& o, const PlayerView& p, bool inv) {
-    float sx = inv ? -1.f : 1.f;
-    const float pcx = 1 / 4096.f, pcy = 1 / 5120.f, pcz = 1 / 2044.f, vc = 1 / 2300.f, ac = 1 / 5.5f;
+GGL_HD void write_player_default(float*& o, const PlayerView& p, bool inv, const float* coef /* EnvCfg::obsCoef */) {
+    const float pcx = coef[0], pcy = coef[1], pcz = coef[2], vc = coef[3], ac = coef[4];
     o[0] = (inv ? -p.pos.x : p.pos.x) * pcx; o[1] = (inv ? -p.pos.y : p.pos.y) * pcy; o[2] = p.pos.z * pcz;
     o[3] = inv ? -p.fwd.x : p.fwd.x; o[4] = inv ? -p.fwd.y : p.fwd.y; o[5] = p.fwd.z;
     o[6] = inv ? -p.up.x : p.up.x; o[7] = inv ? -p.up.y : p.up.y; o[8] = p.up.z;
     o[9] = (inv ? -p.vel.x : p.vel.x) * vc; o[10] = (inv ? -p.vel.y : p.vel.y) * vc; o[11] = p.vel.z * vc;
     o[12] = (inv ? -p.angVel.x : p.angVel.x) * ac; o[13] = (inv ? -p.angVel.y : p.angVel.y) * ac; o[14] = p.angVel.z * ac;
     o[15] = p.boost / 100; o[16] = p.onGround ? 1.f : 0.f; o[17] = p.hasFlipOrJump ? 1.f : 0.f; o[18] = p.demoed ? 1.f : 0.f;
-    (void)sx;
     o += 19;
 }
 
@@ -275,9 +273,10 @@ GGL_HD void build_obs_row(const ArenaDev& A, const EnvCfg& cfg, int slot, float*
         o[0] = bp.x * PC; o[1] = bp.y * PC; o[2] = bp.z * PC; o[3] = bv.x * VC; o[4] = bv.y * VC; o[5] = bv.z * VC;
         o[6] = bw.x * AC; o[7] = bw.y * AC; o[8] = bw.z * AC;
     } else {
-        o[0] = bp.x * (1 / 4096.f); o[1] = bp.y * (1 / 5120.f); o[2] = bp.z * (1 / 2044.f);
-        o[3] = bv.x * (1 / 2300.f); o[4] = bv.y * (1 / 2300.f); o[5] = bv.z * (1 / 2300.f);
-        o[6] = bw.x * (1 / 5.5f); o[7] = bw.y * (1 / 5.5f); o[8] = bw.z * (1 / 5.5f);
+        const float* k = cfg.obsCoef;
+        o[0] = bp.x * k[0]; o[1] = bp.y * k[1]; o[2] = bp.z * k[2];
+        o[3] = bv.x * k[3]; o[4] = bv.y * k[3]; o[5] = bv.z * k[3];
+        o[6] = bw.x * k[4]; o[7] = bw.y * k[4]; o[8] = bw.z * k[4];
     }
     o += 9;
     for (int i = 0; i < 8; i++) o[i] = A.players[slot].prevAction[i];
@@ -294,7 +293,7 @@ GGL_HD void build_obs_row(const ArenaDev& A, const EnvCfg& cfg, int slot, float*
     }
     o += kNumPads;
     if (cfg.obsKind == GGL_OBS_ADVANCED) write_player_advanced(o, me, inv, bp, bv);
-    else write_player_default(o, me, inv);
+    else write_player_default(o, me, inv, cfg.obsCoef);
     if (cfg.obsKind == GGL_OBS_DEFAULT_PADDED) {
         // teammates then opponents, each list padded with zero rows and shuffled: list[j] = item nibble j of the permutation
         const int nm = cfg.obsMaxPlayers - 1, no = cfg.obsMaxPlayers;
@@ -309,7 +308,7 @@ GGL_HD void build_obs_row(const ArenaDev& A, const EnvCfg& cfg, int slot, float*
             int j = 0;
             while (j < 7 && (int)nib_get(perm, j) != k) j++;
             float* dst = o + 19 * (mate ? j : nm + j);
-            write_player_default(dst, player_view(A, oc), inv);
+            write_player_default(dst, player_view(A, oc), inv, cfg.obsCoef);
         }
         return;
     }
@@ -321,7 +320,7 @@ GGL_HD void build_obs_row(const ArenaDev& A, const EnvCfg& cfg, int slot, float*
             if (mate != (pass == 0)) continue;
             PlayerView ov = player_view(A, oc);
             if (cfg.obsKind == GGL_OBS_ADVANCED) write_player_advanced(o, ov, inv, bp, bv);
-            else write_player_default(o, ov, inv);
+            else write_player_default(o, ov, inv, cfg.obsCoef);
         }
 }
 

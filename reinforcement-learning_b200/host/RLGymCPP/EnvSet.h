@@ -69,6 +69,11 @@ inline void Init(const std::string& collisionMeshesFolder) {
 }  // namespace RocketSim
 
 struct Car { uint32_t id; Team team; };
+struct Vec {                                            // RocketSim Math/MathTypes/MathTypes.h:8-17 (what plugin constructors take)
+    float x = 0, y = 0, z = 0;
+    Vec() = default;
+    Vec(float x, float y, float z) : x(x), y(y), z(z) {}
+};
 
 // Arena::Create + AddCar record the roster; the physics state lives on the device (one blob per arena).
 struct Arena {
@@ -198,12 +203,24 @@ class NoTouchCondition : public TerminalCondition { public:     // NoTouchCondit
 class ObsBuilder { public:                              // ObsBuilders/ObsBuilder.h:8-14
     virtual int DescribeKind() const { return -1; }
     virtual int DescribeMaxPlayers() const { return 0; }
+    virtual void DescribeCoefs(float out[5]) const { for (int i = 0; i < 5; i++) out[i] = 0.f; }    // all 0 = the stock defaults
     virtual ~ObsBuilder() {} };
-class DefaultObs : public ObsBuilder { public: int DescribeKind() const override { return GGL_OBS_DEFAULT; } };
+namespace CommonValues {                                // CommonValues.h:20-40 (the values the obs defaults are built from)
+constexpr float SIDE_WALL_X = 4096, BACK_WALL_Y = 5120, CEILING_Z = 2044, CAR_MAX_SPEED = 2300, CAR_MAX_ANG_VEL = 5.5f;
+}
+class DefaultObs : public ObsBuilder { public:          // ObsBuilders/DefaultObs.h:6-22
+    Vec posCoef; float velCoef, angVelCoef;
+    DefaultObs(Vec posCoef = Vec(1 / CommonValues::SIDE_WALL_X, 1 / CommonValues::BACK_WALL_Y, 1 / CommonValues::CEILING_Z),
+               float velCoef = 1 / CommonValues::CAR_MAX_SPEED, float angVelCoef = 1 / CommonValues::CAR_MAX_ANG_VEL)
+        : posCoef(posCoef), velCoef(velCoef), angVelCoef(angVelCoef) {}
+    int DescribeKind() const override { return GGL_OBS_DEFAULT; }
+    void DescribeCoefs(float out[5]) const override { out[0] = posCoef.x; out[1] = posCoef.y; out[2] = posCoef.z; out[3] = velCoef; out[4] = angVelCoef; } };
 class AdvancedObs : public ObsBuilder { public: int DescribeKind() const override { return GGL_OBS_ADVANCED; } };
-class DefaultObsPadded : public ObsBuilder { public:    // ObsBuilders/DefaultObsPadded.h:9-24 (default coefficients)
+class DefaultObsPadded : public DefaultObs { public:    // ObsBuilders/DefaultObsPadded.h:9-24
     int maxPlayers;
-    DefaultObsPadded(int maxPlayers) : maxPlayers(maxPlayers) {}
+    DefaultObsPadded(int maxPlayers, Vec posCoef = Vec(1 / CommonValues::SIDE_WALL_X, 1 / CommonValues::BACK_WALL_Y, 1 / CommonValues::CEILING_Z),
+                     float velCoef = 1 / CommonValues::CAR_MAX_SPEED, float angVelCoef = 1 / CommonValues::CAR_MAX_ANG_VEL)
+        : DefaultObs(posCoef, velCoef, angVelCoef), maxPlayers(maxPlayers) {}
     int DescribeKind() const override { return GGL_OBS_DEFAULT_PADDED; }
     int DescribeMaxPlayers() const override { return maxPlayers; } };
 
@@ -289,6 +306,7 @@ inline ggl_envset_desc DescribeEnv(const EnvCreateResult& r, const EnvSetConfig&
     if (!r.obsBuilder || r.obsBuilder->DescribeKind() < 0) _Fatal("ObsBuilder subclass has no device implementation (stock: DefaultObs, AdvancedObs, DefaultObsPadded)");
     d.obs_kind = r.obsBuilder->DescribeKind();
     d.obs_max_players = r.obsBuilder->DescribeMaxPlayers();
+    r.obsBuilder->DescribeCoefs(d.obs_coefs);
     if (d.obs_kind == GGL_OBS_DEFAULT_PADDED && blue > d.obs_max_players)        // DefaultObsPadded.cpp:40-44
         _Fatal("DefaultObsPadded: too many players per team for maxPlayers");
     if (!r.actionParser || !r.actionParser->IsDefaultAction()) _Fatal("ActionParser subclass has no device implementation (stock: DefaultAction)");

@@ -36,13 +36,15 @@ static int Describe() {
               d.terminals[1].params[0] == 10.f && d.state_setter == GGL_SETTER_KICKOFF && d.tick_skip == 8 && d.action_delay == 7;
     {   // the random plugins of SURVEY 8 f4: DefaultObsPadded, CombinedState over { KickoffState, RandomState, FuzzedKickoffState }
         EnvCreateResult r = MakeEnv(2, false);
-        r.obsBuilder = new DefaultObsPadded(3);
+        r.obsBuilder = new DefaultObsPadded(3, Vec(1 / 5000.f, 1 / 6000.f, 1 / 2500.f), 1 / 3000.f, 0.25f);
         r.stateSetter = new CombinedState({{new KickoffState(), 1.f}, {new RandomState(true, false, true), 2.5f}, {new FuzzedKickoffState(), 0.5f}});
         ggl_envset_desc p = DescribeEnv(r, cfg);
         ok = ok && p.obs_kind == GGL_OBS_DEFAULT_PADDED && p.obs_max_players == 3 && p.state_setter == GGL_SETTER_COMBINED &&
              p.num_setter_children == 3 && p.setter_children[1].kind == GGL_SETTER_RANDOM &&
              p.setter_children[1].flags == (GGL_RANDOM_BALL_SPEED | GGL_RANDOM_CARS_ON_GROUND) && p.setter_children[1].weight == 2.5f &&
-             p.setter_children[2].kind == GGL_SETTER_FUZZED_KICKOFF;
+             p.setter_children[2].kind == GGL_SETTER_FUZZED_KICKOFF && p.obs_coefs[1] == 1 / 6000.f && p.obs_coefs[4] == 0.25f;
+        ggl_envset_desc q = DescribeEnv(MakeEnv(2, false), cfg);        // stock DefaultObs(): its own default coefficients
+        ok = ok && q.obs_coefs[0] == 1 / 4096.f && q.obs_coefs[3] == 1 / 2300.f && q.obs_coefs[4] == 1 / 5.5f;
         bool tooMany = false;
         r.obsBuilder = new DefaultObsPadded(1);
         try { DescribeEnv(r, cfg); } catch (const std::runtime_error&) { tooMany = true; }

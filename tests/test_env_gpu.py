@@ -334,3 +334,15 @@ def test_random_setters_at_scale_stay_in_the_arena(ggl):
     assert torch.isfinite(env.obs).all() and torch.isfinite(env.rewards).all()
     assert env.contact_overflow() == 0
     env.close()
+
+
+def test_custom_obs_coefficients_match_reference(ggl):
+    """DefaultObs / DefaultObsPadded constructed with non-default posCoef / velCoef / angVelCoef."""
+    import setter_parity
+    abi = ggl.abi
+    coefs = [1 / 5000.0, 1 / 6000.0, 1 / 2500.0, 1 / 3000.0, 0.25]
+    r = env_parity.run_env_steps(ggl, num_arenas=4, ppt=2, steps=16, seed=9, obs_kind=abi.OBS_DEFAULT, obs_coefs=coefs)
+    assert r["obs_bad"] == 0 and r["mask_mismatch"] == 0 and r["rew"] <= 1e-4, r
+    r = setter_parity.run_resets(ggl.EnvSet, 2, trials=15, seed=177, state_setter=abi.SETTER_RANDOM, state_setter_flags=3,
+                                 obs_kind=abi.OBS_DEFAULT_PADDED, obs_max_players=3, obs_coefs=coefs)
+    assert r["state"] <= SETTER_STATE_ATOL and r["obs"] <= SETTER_OBS_ATOL, r

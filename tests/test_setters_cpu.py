@@ -53,3 +53,14 @@ def test_default_obs_padded_steps(ppt, maxp):
     assert r["obs"] <= 2e-4, r
     if maxp > ppt:          # with every slot occupied the layout is one; the values still tell players apart
         assert r["distinct_layouts"] > 5
+
+
+def test_custom_obs_coefficients():
+    """DefaultObs(posCoef, velCoef, angVelCoef) and DefaultObsPadded(maxPlayers, ...) with non-default coefficients (DefaultObs.h:9-17)."""
+    import env_parity
+    coefs = [1 / 5000.0, 1 / 6000.0, 1 / 2500.0, 1 / 3000.0, 0.25]
+    r = env_parity.run_env_steps(None, num_arenas=3, ppt=2, steps=12, seed=3, obs_kind=abi.OBS_DEFAULT, env_cls=hostsim_binding.HostEnvSet, obs_coefs=coefs)
+    assert r["obs_bad"] == 0 and r["mask_mismatch"] == 0, r
+    r = setter_parity.run_resets(hostsim_binding.HostEnvSet, 2, trials=20, seed=77, state_setter=abi.SETTER_RANDOM, state_setter_flags=3,
+                                 obs_kind=abi.OBS_DEFAULT_PADDED, obs_max_players=3, obs_coefs=coefs)
+    assert r["state"] <= STATE_ATOL and r["obs"] <= OBS_ATOL, r
