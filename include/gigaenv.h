@@ -103,6 +103,12 @@ typedef struct ggl_terminal_desc {
     float   params[2];
 } ggl_terminal_desc;
 
+typedef enum ggl_game_mode {     /* RocketSim GameMode (RocketSim.h); the device integrator has these two */
+    GGL_MODE_SOCCAR = 0,
+    GGL_MODE_HEATSEEKER = 1      /* soccar arena; the ball steers towards a goal (Sim/Ball/Ball.cpp:152-253), unlimited boost and
+                                    respawns at 100 (MutatorConfig.cpp:29-33), 4 kickoff slots and a moving kickoff ball (Arena.cpp:132-200) */
+} ggl_game_mode;
+
 typedef enum ggl_state_setter_kind {
     GGL_SETTER_KICKOFF = 0,     /* StateSetters/KickoffState.h → Arena::ResetToRandomKickoff (Arena.cpp:112-216) */
     GGL_SETTER_INJECTED = 1,    /* reset states are supplied by the host through ggl_envset_set_reset_state */
@@ -148,6 +154,7 @@ typedef struct ggl_envset_desc {
     int32_t state_setter_flags; /* GGL_SETTER_RANDOM: ggl_random_state_flags */
     int32_t num_setter_children;/* GGL_SETTER_COMBINED: 1..GGL_MAX_SETTER_CHILDREN */
     ggl_setter_child setter_children[GGL_MAX_SETTER_CHILDREN];
+    int32_t game_mode;          /* ggl_game_mode */
     float   obs_coefs[5];       /* GGL_OBS_DEFAULT / _DEFAULT_PADDED: the constructor's posCoef x, y, z, velCoef, angVelCoef
                                    (DefaultObs.h:9-17); all five 0 = the defaults 1/4096, 1/5120, 1/2044, 1/2300, 1/5.5 */
 } ggl_envset_desc;
@@ -189,9 +196,11 @@ typedef struct ggl_car_state {   /* Sim/Car/Car.h:17-115 */
     uint64_t update_counter;
 } ggl_car_state;
 
-typedef struct ggl_ball_state {  /* Sim/Ball/Ball.h:16-41 (soccar: no heatseeker info) */
+typedef struct ggl_ball_state {  /* Sim/Ball/Ball.h:16-41 */
     float pos[3], vel[3], ang_vel[3];
     uint64_t update_counter;
+    float hs_y_target_dir, hs_cur_target_speed, hs_time_since_hit;   /* BallState::HeatseekerInfo (:23-32); a default ball has 0, 2900, 0 */
+    float _pad;
 } ggl_ball_state;
 
 typedef struct ggl_pad_state {   /* Sim/BoostPad/BoostPad.h:23-34, RocketSim pad order (6 big then 28 small) */

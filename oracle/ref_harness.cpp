@@ -166,6 +166,7 @@ void ApplyArenaState(Arena* arena, const ggl_arena_state& st) {
     arena->tickCount = st.tick_count;
     BallState bs;
     bs.pos = V3(st.ball.pos); bs.vel = V3(st.ball.vel); bs.angVel = V3(st.ball.ang_vel);
+    bs.hsInfo.yTargetDir = st.ball.hs_y_target_dir; bs.hsInfo.curTargetSpeed = st.ball.hs_cur_target_speed; bs.hsInfo.timeSinceHit = st.ball.hs_time_since_hit;
     arena->ball->SetState(bs);
     arena->ball->_internalState.updateCounter = st.ball.update_counter;
     for (int i = 0; i < st.num_cars; i++) {
@@ -189,6 +190,7 @@ void ReadArenaState(Arena* arena, ggl_arena_state& st) {
     BallState bs = arena->ball->GetState();
     Put3(st.ball.pos, bs.pos); Put3(st.ball.vel, bs.vel); Put3(st.ball.ang_vel, bs.angVel);
     st.ball.update_counter = bs.updateCounter;
+    st.ball.hs_y_target_dir = bs.hsInfo.yTargetDir; st.ball.hs_cur_target_speed = bs.hsInfo.curTargetSpeed; st.ball.hs_time_since_hit = bs.hsInfo.timeSinceHit;
     for (int i = 0; i < st.num_cars && i < GGL_MAX_CARS; i++) {
         Car* car = CarById(arena, i + 1);
         if (car) ReadCarState(car, st.cars[i]);
@@ -312,7 +314,7 @@ void* ref_envset_create(const ggl_envset_desc* d) {
         ggl_envset_desc desc = *d;
         cfg.envCreateFn = [desc, env](int index) {
             EnvCreateResult r = {};
-            Arena* arena = Arena::Create(GameMode::SOCCAR);
+            Arena* arena = Arena::Create(desc.game_mode == GGL_MODE_HEATSEEKER ? GameMode::HEATSEEKER : GameMode::SOCCAR);
             for (int i = 0; i < desc.players_per_team; i++) arena->AddCar(Team::BLUE);
             for (int i = 0; i < desc.players_per_team; i++) arena->AddCar(Team::ORANGE);
             r.arena = arena;

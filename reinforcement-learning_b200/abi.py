@@ -18,6 +18,7 @@ OBS_DEFAULT, OBS_ADVANCED, OBS_DEFAULT_PADDED = 0, 1, 2
  REW_TOUCH_ACCEL, REW_STRONG_TOUCH, REW_KICKOFF_PROXIMITY_2V2) = range(23)
 
 TERM_GOAL_SCORE, TERM_NO_TOUCH = 0, 1
+MODE_SOCCAR, MODE_HEATSEEKER = 0, 1
 SETTER_KICKOFF, SETTER_INJECTED, SETTER_FUZZED_KICKOFF, SETTER_RANDOM, SETTER_COMBINED = 0, 1, 2, 3, 4
 RANDOM_BALL_SPEED, RANDOM_CAR_SPEED, RANDOM_CARS_ON_GROUND = 1, 2, 4
 
@@ -47,7 +48,7 @@ class EnvSetDesc(C.Structure):
         ("state_setter", C.c_int32), ("num_meshes", C.c_int32), ("meshes", C.POINTER(MeshBlob)),
         ("seed", C.c_uint64), ("slot_order_reversed", C.c_int32),
         ("obs_max_players", C.c_int32), ("state_setter_flags", C.c_int32), ("num_setter_children", C.c_int32),
-        ("setter_children", SetterChild * GGL_MAX_SETTER_CHILDREN), ("obs_coefs", C.c_float * 5),
+        ("setter_children", SetterChild * GGL_MAX_SETTER_CHILDREN), ("game_mode", C.c_int32), ("obs_coefs", C.c_float * 5),
     ]
 
 
@@ -86,7 +87,8 @@ class CarState(C.Structure):
 
 
 class BallState(C.Structure):
-    _fields_ = [("pos", C.c_float * 3), ("vel", C.c_float * 3), ("ang_vel", C.c_float * 3), ("update_counter", C.c_uint64)]
+    _fields_ = [("pos", C.c_float * 3), ("vel", C.c_float * 3), ("ang_vel", C.c_float * 3), ("update_counter", C.c_uint64),
+                ("hs_y_target_dir", C.c_float), ("hs_cur_target_speed", C.c_float), ("hs_time_since_hit", C.c_float), ("_pad", C.c_float)]
 
 
 class PadState(C.Structure):
@@ -124,7 +126,7 @@ class EnvSetViews(C.Structure):
 
 def make_desc(num_arenas, players_per_team, obs_kind=OBS_ADVANCED, rewards=None, terminals=None,
               tick_skip=8, action_delay=7, state_setter=SETTER_KICKOFF, meshes=None, seed=0, device=0,
-              slot_order_reversed=1, obs_max_players=0, state_setter_flags=0, setter_children=None, obs_coefs=None):
+              slot_order_reversed=1, obs_max_players=0, state_setter_flags=0, setter_children=None, obs_coefs=None, game_mode=0):
     """rewards: list of (kind, weight[, params[, zero_sum]]); terminals: list of (kind[, params]);
     setter_children (SETTER_COMBINED): list of (kind, weight[, flags]).
     Returns (desc, keepalive) — keepalive holds the mesh buffers the desc points into."""
@@ -169,6 +171,7 @@ def make_desc(num_arenas, players_per_team, obs_kind=OBS_ADVANCED, rewards=None,
     d.slot_order_reversed = slot_order_reversed
     d.obs_max_players = obs_max_players
     d.state_setter_flags = state_setter_flags
+    d.game_mode = game_mode
     for i, k in enumerate(obs_coefs or []):      # DefaultObs(posCoef xyz, velCoef, angVelCoef); None = the defaults
         d.obs_coefs[i] = k
     setter_children = setter_children or []

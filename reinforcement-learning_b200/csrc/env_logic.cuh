@@ -16,6 +16,7 @@
 #include "sim_tick.cuh"
 
 namespace ggl {
+static_assert(kModeSoccar == GGL_MODE_SOCCAR && kModeHeatseeker == GGL_MODE_HEATSEEKER, "game mode codes");
 
 
 struct RewardCfg {
@@ -37,7 +38,7 @@ struct SetterCfg {
 struct EnvCfg {
     int numArenas, playersPerTeam, numCars, tickSkip, actionDelay, obsKind, obsSize;
     int numRewards, numTerminals, stateSetter;
-    int obsMaxPlayers, setterFlags, numSetterChildren;
+    int obsMaxPlayers, setterFlags, numSetterChildren, gameMode;
     float setterTotalWeight;
     float obsCoef[5];           // DefaultObs / DefaultObsPadded: posCoef x y z, velCoef, angVelCoef
     SetterCfg setterChildren[GGL_MAX_SETTER_CHILDREN];
@@ -70,6 +71,8 @@ inline const char* env_cfg_plugins(EnvCfg& c, const ggl_envset_desc* d) {
         for (int i = 0; i < 5; i++) c.obsCoef[i] = any ? d->obs_coefs[i] : dflt[i];
         if (any && d->obs_kind == GGL_OBS_ADVANCED) return "AdvancedObs has no coefficient arguments (AdvancedObs.h:10-13)";
     }
+    if (d->game_mode != GGL_MODE_SOCCAR && d->game_mode != GGL_MODE_HEATSEEKER) return "unsupported game mode (soccar and heatseeker have a device integrator)";
+    c.gameMode = d->game_mode;
     c.stateSetter = d->state_setter; c.setterFlags = d->state_setter_flags; c.numSetterChildren = 0; c.setterTotalWeight = 0.f;
     if (d->state_setter < GGL_SETTER_KICKOFF || d->state_setter > GGL_SETTER_COMBINED) return "unsupported state setter kind";
     if (d->state_setter == GGL_SETTER_COMBINED) {
@@ -167,6 +170,9 @@ GGL_HD bool ball_scored(const ArenaDev& A) {
 
 // Arena::IsBallProbablyGoingIn for soccar (Arena.cpp:827-860)
 GGL_HD bool ball_probably_going_in(const ArenaDev& A, float maxTime, float extraMargin, int* goalTeam) {
+    // heatseeker: the reference has no prediction for this mode and raises a fatal error as soon as the tracker asks for one
+    // (Arena.cpp:867-870, i.e. on the first fast ball); here the tracker simply sees no shot, so shot / save events stay off
+    if (A.gameMode == kModeHeatseeker) return false;
     V3 p = A.ball.pos * kBT2UU, v = A.ball.vel * kBT2UU;
     if (fabsf(v.y) < kEps) return false;
     float sgn = fsgn(v.y);

@@ -94,20 +94,31 @@ GGL_HD void arena_reset_kickoff(ArenaDev& A) {
     const float sx[5] = {-2048, 2048, -256, 256, 0}, sy[5] = {-2560, -2560, -3840, -3840, -4608};
     const float q = 0.78539816339744830962f;
     const float syaw[5] = {q * 1, q * 3, q * 2, q * 2, q * 2};
-    const uint32_t order = std_shuffle_nib(A.rng, 5);
+    // heatseeker: four slots on one line (RLConst.h:306-311), only the first four entries of the order are shuffled and an
+    // entry is clamped to the last slot (Arena.cpp:132-136, 159)
+    const float hx[4] = {-1000, 1000, -2000, 2000};
+    const bool heat = A.gameMode == kModeHeatseeker;
+    const uint32_t order = std_shuffle_nib(A.rng, heat ? 4 : 5);
     int nb = 0, no = 0;
     for (int s = 0; s < A.numCars; s++) {
         CarDev& c = A.cars[A.slotCar[s]];
         int i = (c.team == 0) ? nb++ : no++;
         int k = (int)nib_get(order, i < 5 ? i : 4);
-        V3 pos = v3(sx[k], sy[k], rl::CAR_SPAWN_REST_Z);
-        float yaw = syaw[k];
+        if (heat && k > 3) k = 3;
+        V3 pos = heat ? v3(hx[k], -4620.f, rl::CAR_SPAWN_REST_Z) : v3(sx[k], sy[k], rl::CAR_SPAWN_REST_Z);
+        float yaw = heat ? q * 2 : syaw[k];
         if (c.team != 0) { pos = pos * v3(-1, -1, 1); yaw = (float)((double)yaw + 3.14159265358979323846); }
         car_set_spawn(c, pos, yaw);
     }
     BallDev& b = A.ball;
     b.pos = v3(0, 0, rl::BALL_REST_Z) * kUU2BT; b.vel = v3(0, 0, 0); b.angVel = v3(0, 0, 0);
     b.velImpulseCache = v3(0, 0, 0); b.force = v3(0, 0, 0); b.torque = v3(0, 0, 0); b.updateCounter = 0;
+    b.hsTargetDir = 0.f; b.hsTargetSpeed = rl::hs::INITIAL_TARGET_SPEED; b.hsTimeSinceHit = 0.f;        // BallState() defaults (Ball.h:23-32)
+    if (heat) {   // one more raw draw decides the side the ball starts on (Arena.cpp:196-200)
+        const float sgn = (minstd_next(A.rng) % 2u) ? 1.f : -1.f;
+        b.pos = (v3(-1000.f, -2220.f, 92.75f) * v3(1, sgn, 1)) * kUU2BT;
+        b.vel = (v3(0.f, -65.f, 650.f) * v3(1, sgn, 1)) * kUU2BT;
+    }
     for (int p = 0; p < kNumPads; p++) { A.pads[p].isActive = 1; A.pads[p].cooldown = 0.f; A.pads[p].prevLockedCarId = 0; A.pads[p].curLockedCarId = 0; }
 }
 

@@ -170,6 +170,7 @@ extern "C" int ggl_envset_create(const ggl_envset_desc* d, ggl_envset** out) {
         for (int a = 0; a < c.numArenas; a++) {
             ArenaDev& A = init[a];
             A.numCars = c.numCars;
+            A.gameMode = (uint8_t)c.gameMode;
             uint64_t s = (d->seed * 6364136223846793005ull + 1442695040888963407ull) ^ ((uint64_t)(a + 1) * 0x9E3779B97F4A7C15ull);
             A.rng = (uint32_t)(s % 2147483646ull) + 1u;
             for (int i = 0; i < c.numCars; i++) {

@@ -647,7 +647,7 @@ GGL_HD void update_wheels(CarDev& c, int numWheels, float fwdSpeedUU) {
     }
 }
 
-GGL_HD void update_boost(CarDev& c) {
+GGL_HD void update_boost(CarDev& c, float usedPerSecond /* MutatorConfig::boostUsedPerSecond: 0 in heatseeker */) {
     if (c.timeSpentBoosting > 0.f) {
         if (!c.controls.boost && c.timeSpentBoosting >= rl::BOOST_MIN_TIME) c.timeSpentBoosting = 0.f;
         else c.timeSpentBoosting += kTick;
@@ -655,7 +655,7 @@ GGL_HD void update_boost(CarDev& c) {
         c.timeSpentBoosting = kTick;
     }
     if (c.boost > 0.f && c.timeSpentBoosting > 0.f) {
-        c.boost = fmaxf(c.boost - rl::BOOST_USED_PER_SECOND * kTick, 0.f);
+        c.boost = fmaxf(c.boost - usedPerSecond * kTick, 0.f);
         float accel = (c.isOnGround ? rl::BOOST_ACCEL_GROUND : rl::BOOST_ACCEL_AIR) * kUU2BT;
         c.force += accel * car_fwd(c) * rl::CAR_MASS;
     }
@@ -896,6 +896,7 @@ GGL_HD void car_respawn(ArenaDev& A, CarDev& c) {
     c.pos = v3(rx[idx], -4608.f * sy, rl::CAR_RESPAWN_Z) * kUU2BT;
     float yaw = (float)(3.14159265358979323846 / 2) + (c.team == 0 ? 0.f : kPi);
     c.basis = m3_from_euler_ypr(yaw, -0.f, -0.f);
+    if (A.gameMode == kModeHeatseeker) c.boost = 100.f;         // MutatorConfig::carSpawnBoostAmount (MutatorConfig.cpp:29-33, Car.cpp:72)
     car_update_inertia(c);
     c.aabbMin = c.aabbMax = v3(0, 0, 0);
 }
@@ -939,7 +940,7 @@ GGL_HD void car_pre_tick_c(ArenaDev& A, int ci) {
     if (c.controls.throttle != 0.f && ((numWheels > 0 && numWheels < 4) || c.worldContactHas)) update_auto_roll(c, numWheels);
     c.worldContactHas = 0;
     vehicle_second(c);
-    update_boost(c);
+    update_boost(c, A.gameMode == kModeHeatseeker ? 0.f : rl::BOOST_USED_PER_SECOND);
 }
 
 GGL_HD void car_post_tick(CarDev& c) {

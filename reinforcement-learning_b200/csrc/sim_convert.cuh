@@ -105,6 +105,7 @@ inline void arena_phys_from_host(const ggl_arena_state& st, ArenaDev& A) {
     b.vel = v3p(st.ball.vel) * kUU2BT;
     b.angVel = v3p(st.ball.ang_vel);
     b.updateCounter = st.ball.update_counter;
+    b.hsTargetDir = st.ball.hs_y_target_dir; b.hsTargetSpeed = st.ball.hs_cur_target_speed; b.hsTimeSinceHit = st.ball.hs_time_since_hit;
     for (int i = 0; i < st.num_cars && i < kMaxCars; i++) car_from_host(st.cars[i], A.cars[i], i, st.num_cars);
     for (int p = 0; p < kNumPads; p++) {
         A.pads[p].isActive = st.pads[p].is_active;
@@ -122,6 +123,7 @@ inline void arena_phys_to_host(const ArenaDev& A, ggl_arena_state& st) {
     put3(st.ball.vel, A.ball.vel * kBT2UU);
     put3(st.ball.ang_vel, A.ball.angVel);
     st.ball.update_counter = A.ball.updateCounter;
+    st.ball.hs_y_target_dir = A.ball.hsTargetDir; st.ball.hs_cur_target_speed = A.ball.hsTargetSpeed; st.ball.hs_time_since_hit = A.ball.hsTimeSinceHit;
     for (int i = 0; i < A.numCars && i < kMaxCars; i++) car_to_host(A.cars[i], st.cars[i]);
     for (int p = 0; p < kNumPads; p++) {
         st.pads[p].is_active = A.pads[p].isActive;

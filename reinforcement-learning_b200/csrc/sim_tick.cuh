@@ -152,6 +152,7 @@ GGL_HD void pad_pre_tick(PadDev& pd) {
 GGL_HD void world_forces(ArenaDev& A, int b) {
     const V3 g = v3(0, 0, rl::GRAVITY_Z * kUU2BT);
     if (b == 0) {
+        if (A.gameMode == kModeHeatseeker) ball_heatseeker_pre_tick(A.ball);      // Ball::_PreTickUpdate, before the world steps (Arena.cpp:778)
         if (A.ball.active) A.ball.force += g * (1.f / kBallInvMass);
         A.ball.vel *= powf(1.f - rl::BALL_DRAG, kTick);
         A.ball.angVel *= powf(1.f - 0.f, kTick);

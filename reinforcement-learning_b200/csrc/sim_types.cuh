@@ -15,6 +15,7 @@ namespace ggl {
 constexpr int kMaxCars = 6;
 constexpr int kNumPads = 34;
 constexpr int kNumActions = 90;
+constexpr int kModeSoccar = 0, kModeHeatseeker = 1;     // ArenaDev::gameMode = ggl_game_mode (include/gigaenv.h)
 constexpr int kMaxContacts = 36;        // contact rows per arena per tick: per-body windows + a shared overflow pool (sim_world.cuh);
                                         // a point that finds neither is dropped AND counted in ArenaDev::contactOverflow
 constexpr int kMaxPool = 16;            // largest overflow pool of the three layouts (contact_pool_size)
@@ -70,6 +71,12 @@ constexpr float BACK_WHEEL_X = -33.75f, BACK_WHEEL_Y = 29.50f, BACK_WHEEL_Z = 20
 constexpr float DODGE_DEADZONE = 0.5f;
 // collision margins of the reference's Bullet shapes
 constexpr float CONVEX_MARGIN = 0.04f;        // btBoxShape default (CONVEX_DISTANCE_MARGIN)
+namespace hs {   // RLConst.h:151-174 namespace Heatseeker
+constexpr float INITIAL_TARGET_SPEED = 2900, TARGET_SPEED_INCREMENT = 85, MIN_SPEEDUP_INTERVAL = 1, TARGET_Y = 5120, TARGET_Z = 320;
+constexpr float HORIZONTAL_BLEND = 1.45f, VERTICAL_BLEND = 0.78f, SPEED_BLEND = 0.3f, MAX_SPEED = 4600;
+constexpr float MAX_TURN_PITCH = (float)(7000 * 3.14159265358979323846 / (1 << 15));
+constexpr float WALL_BOUNCE_CHANGE_Y_THRESH = 300, WALL_BOUNCE_CHANGE_Y_NORMAL = 0.5f, WALL_BOUNCE_FORCE_SCALE = 1 / 3.f, WALL_BOUNCE_UP_FRAC = 0.3f;
+}
 }  // namespace rl
 
 struct Controls {
@@ -111,7 +118,9 @@ struct alignas(16) CarDev {
 struct BallDev {
     V3 pos, vel, angVel, force, torque, velImpulseCache, aabbMin, aabbMax;
     uint64_t updateCounter;
-    uint32_t active, _pad;
+    uint32_t active;
+    // BallState::HeatseekerInfo (Sim/Ball/Ball.h:23-32): which net the ball seeks (0 = none), its target speed, time since the last hit
+    float hsTargetDir, hsTargetSpeed, hsTimeSinceHit;
 };
 
 struct PadDev {                  // 8 bytes: car ids are 1 .. kMaxCars
@@ -167,7 +176,7 @@ struct alignas(16) ArenaDev {
     EnvPlayer players[kMaxCars];                   // indexed by SLOT
     uint32_t rng;                                  // minstd_rand0 state (respawn slot / kickoff permutation)
     float stepDeltaTime;                           // GameState.deltaTime of the current env step
-    uint8_t stepGoalScored, hasResetState, _pad3[2];
+    uint8_t stepGoalScored, hasResetState, gameMode /* ggl_game_mode, set at create */, _pad3;
     // per-tick scratch
     int32_t numContacts;
     uint32_t bodiesInContact;                      // bit b: body b (0 ball, 1 + c car c) has a solver row this tick

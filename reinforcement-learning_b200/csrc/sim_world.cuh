@@ -143,6 +143,83 @@ GGL_HD int manifold_add(ContactSink& S, ManifoldCtx& m, const Contact& c, V3 loc
 
 GGL_HD ManifoldCtx manifold_begin(const ContactSink& S) { ManifoldCtx m; m.first = S.n; m.count = 0; return m; }
 
+// ---- GameMode::HEATSEEKER: the ball steers towards a goal (Sim/Ball/Ball.cpp:152-253) ----
+// Angle helpers of RocketSim (Math/MathTypes/MathTypes.cpp:80-120, Math/Math.cpp:66-98), yaw / pitch only (roll stays 0)
+GGL_HD float wrap_normalize(float val, float minmax) {
+    float r = fmodf(val, minmax * 2);
+    if (r > minmax) r -= minmax * 2;
+    else if (r < -minmax) r += minmax * 2;
+    return r;
+}
+GGL_HD void angle_from_vec(V3 f, float& yaw, float& pitch) {
+    const float eps = 1.1920929e-7f;
+    if (fabsf(f.y) > eps || fabsf(f.x) > eps) {
+        yaw = atan2f(f.y, f.x);
+        const float d2 = sqrtf(f.x * f.x + f.y * f.y);
+        pitch = -atan2f(-f.z, d2);
+    } else {
+        yaw = 0.f;
+        pitch = f.z > eps ? (float)(3.14159265358979323846 / 2) : (f.z < -eps ? (float)(-3.14159265358979323846 / 2) : 0.f);
+    }
+}
+// Ball::_PreTickUpdate for HEATSEEKER (:153-201)
+GGL_HD void ball_heatseeker_pre_tick(BallDev& b) {
+    const float dirY = b.hsTargetDir;
+    if (dirY == 0.f) return;
+    const float kPiF2 = (float)3.14159265358979323846, kHalf = (float)(3.14159265358979323846 / 2);
+    const V3 pos = b.pos * kBT2UU, vel = b.vel * kBT2UU;
+    float vy, vp, gy, gp;
+    angle_from_vec(vel, vy, vp);
+    angle_from_vec(v3(0.f, rl::hs::TARGET_Y * dirY, rl::hs::TARGET_Z) - pos, gy, gp);
+    // deltaAngle = angleToGoal - velAngle = velAngle.GetDeltaTo(angleToGoal), NormalizeFix'd
+    const float dy = wrap_normalize(gy - vy, kPiF2), dp = wrap_normalize(gp - vp, kHalf);
+    const float l2 = vel.x * vel.x + vel.y * vel.y + vel.z * vel.z;
+    const float curSpeed = l2 > 0.f ? sqrtf(l2) : 0.f;                      // Vec::Length
+    const float speedRatio = curSpeed / rl::hs::MAX_SPEED;
+    const float base = speedRatio * kTick;
+    float ny = vy + dy * base * rl::hs::HORIZONTAL_BLEND;
+    float np = vp + dp * base * rl::hs::VERTICAL_BLEND;
+    ny = wrap_normalize(ny, kPiF2); np = wrap_normalize(np, kHalf);
+    np = np < -rl::hs::MAX_TURN_PITCH ? -rl::hs::MAX_TURN_PITCH : (np > rl::hs::MAX_TURN_PITCH ? rl::hs::MAX_TURN_PITCH : np);   // RS_CLAMP = max(min, min(v, max))
+    {   // Math::RoundAngleUE3
+        const float TO_INTS = (float)((double)(float)(1 << 15) / 3.14159265358979323846);
+        const float BACK = (1.f / TO_INTS) * 4.f;
+        const int ry = ((int)(ny * TO_INTS) >> 2) & 0x3FFF, rp = ((int)(np * TO_INTS) >> 2) & 0x3FFF;
+        ny = ry * BACK; np = rp * BACK;
+    }
+    const float newSpeed = curSpeed + ((b.hsTargetSpeed - curSpeed) * rl::hs::SPEED_BLEND);
+    const float cp = cosf(-np), cy = cosf(ny), sy = sinf(ny), sp = sinf(-np);   // Angle::GetForwardVec
+    const V3 dir = v3(cp * cy, cp * sy, -sp);
+    b.vel = (dir * newSpeed) * kUU2BT;
+    b.hsTimeSinceHit += kTick;
+}
+// Ball::_OnHit (:203-214)
+GGL_HD void ball_heatseeker_on_hit(BallDev& b, int carTeam) {
+    const bool canIncrease = (b.hsTimeSinceHit > rl::hs::MIN_SPEEDUP_INTERVAL) || (b.hsTargetDir == 0.f);
+    const float newDir = carTeam == 0 ? 1.f : -1.f;
+    if (canIncrease && newDir != b.hsTargetDir) {
+        b.hsTimeSinceHit = 0.f;
+        b.hsTargetSpeed = fminf(b.hsTargetSpeed + rl::hs::TARGET_SPEED_INCREMENT, rl::hs::MAX_SPEED);
+    }
+    b.hsTargetDir = newDir;
+}
+// Ball::_OnWorldCollision (:216-246): called for every ball-world contact point as it is added, with the contact normal
+GGL_HD void ball_heatseeker_on_world(BallDev& b, V3 normal) {
+    if (b.hsTargetDir == 0.f) return;
+    const V3 pos = b.pos * kBT2UU;
+    const float relNormalY = normal.y * b.hsTargetDir, relY = pos.y * b.hsTargetDir;
+    if (relNormalY <= -rl::hs::WALL_BOUNCE_CHANGE_Y_NORMAL && relY >= rl::ARENA_EXTENT_Y - rl::hs::WALL_BOUNCE_CHANGE_Y_THRESH) {
+        b.hsTargetDir *= -1.f;
+        const V3 vel = b.vel * kBT2UU;
+        const V3 goal = v3(0.f, rl::hs::TARGET_Y * b.hsTargetDir, rl::hs::TARGET_Z);
+        const V3 toGoal = rs_normalized(goal - pos);
+        const V3 bounceDir = toGoal * (1 - rl::hs::WALL_BOUNCE_UP_FRAC) + v3(0, 0, 1) * rl::hs::WALL_BOUNCE_UP_FRAC;
+        const float l2 = vel.x * vel.x + vel.y * vel.y + vel.z * vel.z;
+        const V3 impulse = bounceDir * (l2 > 0.f ? sqrtf(l2) : 0.f) * rl::hs::WALL_BOUNCE_FORCE_SCALE;
+        b.velImpulseCache += impulse * kUU2BT;
+    }
+}
+
 // ---------------------------------------------------------------------------------------------- narrow phase
 // ball vs the 4 planes and the mesh; every contact is flagged special (Arena.cpp:265-273)
 GGL_HD void collide_ball_plane(ArenaDev& A, ContactSink& S, V3 n, V3 origin) {
@@ -161,7 +238,7 @@ GGL_HD void collide_ball_plane(ArenaDev& A, ContactSink& S, V3 n, V3 origin) {
         c.friction = rl::BALL_FRICTION < rl::WORLD_FRICTION ? rl::BALL_FRICTION : rl::WORLD_FRICTION;
         c.restitution = rl::BALL_RESTITUTION > rl::WORLD_RESTITUTION ? rl::BALL_RESTITUTION : rl::WORLD_RESTITUTION;
         c.bodyA = 0; c.bodyB = -1; c.special = 1; c._pad = 0;
-        manifold_add(S, m, c, pA - b.pos);
+        if (manifold_add(S, m, c, pA - b.pos) >= 0 && A.gameMode == kModeHeatseeker) ball_heatseeker_on_world(A.ball, n);
     }
 }
 
@@ -284,6 +361,7 @@ GGL_HD void collide_ball_mesh(ArenaDev& A, ContactSink& S, const WorldDev& W) {
             c.bodyA = 0; c.bodyB = -1; c.special = 1; c._pad = 0;
             int row = manifold_add(S, m, c, pA - b.pos);
             if (row < 0) continue;
+            if (A.gameMode == kModeHeatseeker) ball_heatseeker_on_world(A.ball, n);     // before the internal-edge adjustment (Arena.cpp:268-277)
             adjust_internal_edge(t, n, p, pA, depth);
             S.at(row).normal = n;
             S.at(row).relB = p;
@@ -367,6 +445,7 @@ GGL_HD void collide_car_ball(ArenaDev& A, ContactSink& S, int ci) {
     } else {
         return;
     }
+    car.ballHitNew = 2;             // Ball::_OnHit runs whenever the extra impulse was not skipped (Arena.cpp:333), in car order (gather_contacts)
     V3 fwd = car_fwd(car);
     V3 relPos = ballPosUU - carPosUU, relVel = ballVelUU - carVelUU;
     float relSpeed = fminf(len(relVel), rl::BALL_CAR_EXTRA_IMPULSE_MAXDELTAVEL);
@@ -376,7 +455,7 @@ GGL_HD void collide_car_ball(ArenaDev& A, ContactSink& S, int ci) {
         hitDir = safe_normalized(hitDir - adj);
         V3 added = (hitDir * relSpeed) * curve_ball_extra_impulse(relSpeed) * 1.f;
         car.hitExtraVel = added;
-        car.ballHitNew = 1;         // ball.velImpulseCache += added: done in car order by gather_contacts
+        car.ballHitNew = 3;         // bit 0: ball.velImpulseCache += added, done in car order by gather_contacts
     }
 }
 
@@ -799,7 +878,8 @@ GGL_HDN void gather_contacts(ArenaDev& A) {
             int cur = 0;
             const int row = pool_next(A, (uint8_t)(POOL_CAR_BALL | i), cur);
             if (row >= 0) A.contactOrder[n++] = (uint8_t)row;
-            if (A.cars[i].ballHitNew) A.ball.velImpulseCache += A.cars[i].hitExtraVel * kUU2BT;
+            if (A.cars[i].ballHitNew & 1) A.ball.velImpulseCache += A.cars[i].hitExtraVel * kUU2BT;
+            if ((A.cars[i].ballHitNew & 2) && A.gameMode == kModeHeatseeker) ball_heatseeker_on_hit(A.ball, A.cars[i].team);
         }
     for (int i = 0; i < P; i++) {
         int cur = 0;

@@ -37,7 +37,7 @@
 #include "../../../include/gigaenv.h"
 
 // ---------------------------------------------------------------------------------------------- RocketSim stand-ins
-enum class GameMode : uint8_t { SOCCAR = 0 };          // the device integrator implements soccar (SURVEY 8f4 lists the rest as next)
+enum class GameMode : uint8_t { SOCCAR = 0, HOOPS, HEATSEEKER, SNOWDAY, THE_VOID };   // Sim/GameMode.h:6-16; the device integrates SOCCAR and HEATSEEKER
 enum class Team : uint8_t { BLUE = 0, ORANGE = 1 };
 struct CarConfig {};
 static const CarConfig CAR_CONFIG_OCTANE = {};
@@ -294,7 +294,9 @@ inline ggl_envset_desc DescribeEnv(const EnvCreateResult& r, const EnvSetConfig&
     ggl_envset_desc d;
     std::memset(&d, 0, sizeof(d));
     if (!r.arena) _Fatal("EnvCreateResult.arena is null");
-    if (r.arena->gameMode != GameMode::SOCCAR) _Fatal("only GameMode::SOCCAR has a device integrator");
+    if (r.arena->gameMode != GameMode::SOCCAR && r.arena->gameMode != GameMode::HEATSEEKER)
+        _Fatal("only GameMode::SOCCAR and GameMode::HEATSEEKER have a device integrator");
+    d.game_mode = r.arena->gameMode == GameMode::HEATSEEKER ? GGL_MODE_HEATSEEKER : GGL_MODE_SOCCAR;
     int blue = 0, orange = 0; bool blueFirst = true;
     for (auto& c : r.arena->_cars) {
         if (c.team == Team::BLUE) { blue++; if (orange) blueFirst = false; } else orange++;

@@ -54,6 +54,7 @@ void hostsim_set_slot_order(void* p, const int32_t* ids) {
     h->orderSet = true;
 }
 void hostsim_get_state(void* p, ggl_arena_state* st) { arena_phys_to_host(((HostSim*)p)->arena, *st); }
+void hostsim_set_game_mode(void* p, int mode) { ((HostSim*)p)->arena.gameMode = (uint8_t)mode; }
 void hostsim_seed(void* p, uint32_t seed) { ((HostSim*)p)->arena.rng = seed; }
 
 void hostsim_step(void* p, int ticks) {
@@ -185,7 +186,7 @@ void* hostenv_create(const ggl_envset_desc* d) {
     action_bits_from_table(h->table.data(), c.actionBits);
     for (int a = 0; a < c.numArenas; a++) {
         ArenaDev& A = h->arenas[a];
-        A.numCars = c.numCars; A.rng = (uint32_t)(d->seed * 7919u + a * 104729u + 1u) % 2147483646u + 1u;
+        A.numCars = c.numCars; A.gameMode = (uint8_t)c.gameMode; A.rng = (uint32_t)(d->seed * 7919u + a * 104729u + 1u) % 2147483646u + 1u;
         for (int i = 0; i < c.numCars; i++) {
             CarDev& car = A.cars[i];
             car.id = i + 1; car.team = i < c.playersPerTeam ? 0 : 1; car.basis = m3_identity();

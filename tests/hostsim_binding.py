@@ -80,6 +80,10 @@ class HostSim:
     def seed(self, s):
         lib().hostsim_seed(self.h, s)
 
+    def set_game_mode(self, mode):
+        lib().hostsim_set_game_mode.argtypes = [C.c_void_p, C.c_int]
+        lib().hostsim_set_game_mode(self.h, mode)
+
     def contacts(self, maxn=64):
         out = np.zeros((maxn, 20), np.float32)
         n = lib().hostsim_contacts(self.h, out.ctypes.data, maxn)

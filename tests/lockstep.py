@@ -26,6 +26,8 @@ def diff_states(a, b, ncars):
     bad = []
     for f in ("pos", "vel", "ang_vel"):
         d["ball." + f] = float(np.max(np.abs(_val(getattr(a.ball, f)) - _val(getattr(b.ball, f)))))
+    for f in ("hs_y_target_dir", "hs_cur_target_speed", "hs_time_since_hit"):     # BallState::HeatseekerInfo
+        d["ball." + f] = abs(getattr(a.ball, f) - getattr(b.ball, f))
     for i in range(ncars):
         ca, cb = a.cars[i], b.cars[i]
         for f in CAR_FLOAT_FIELDS:

@@ -189,3 +189,47 @@ def test_kickoff_proximity_reward_matches_reference():
                                  rewards=[(A.REW_KICKOFF_PROXIMITY_2V2, 1.0, [1.2, 0.6, 0.3, 0.2])])
     assert r["rew"] <= 1e-5 and r["rew_nonzero"] > 20 and r["rew_abs_max"] > 0.1, r
     assert r["mask_mismatch"] == 0 and r["obs_bad"] == 0, r
+
+
+def heatseeker_per_tick(make_sim, ticks=900):
+    """One blue car drives into the kickoff-side ball; the ball then seeks the orange goal, hits the back wall, turns round ...
+    Every tick starts from the reference's state (re-synchronised); returns the worst per-tick differences and what happened."""
+    L = oracle_ref.lib(); L.ref_set_threads(1); L.ref_seed(11)
+    ref = oracle_ref.RefEnvSet(1, 1, game_mode=oracle_ref.abi.MODE_HEATSEEKER)
+    sim = make_sim()
+    st = ref.get_state(0)
+    st.ball.pos[:] = [0.0, -1500.0, 92.75]; st.ball.vel[:] = [0.0, 0.0, 0.0]
+    c = st.cars[0]; c.pos[:] = [100.0, -2600.0, 17.0]; c.rot[:] = [0, 1, 0, -1, 0, 0, 0, 0, 1]; c.vel[:] = [0, 1200.0, 0]
+    ref.set_state(0, st)
+    worst = {}
+    flips, speedups, nbad, last_dir, last_speed = 0, 0, 0, 0.0, st.ball.hs_cur_target_speed
+    for t in range(ticks):
+        cur = ref.get_state(0)
+        sim.set_state(cur)
+        ls.set_controls(cur, 0, throttle=1 if t < 150 else -1, boost=1 if t < 150 else 0, steer=0.02 if t < 150 else 1.0)      # hit the ball, then circle in reverse
+        ls.set_controls(cur, 1, throttle=1, boost=1, steer=-0.3 if t > 300 else 0)
+        ref.set_controls(0, cur); sim.set_controls(cur)
+        ref.arena_step(1, 0); sim.step(1)
+        a, b = ref.get_state(0), sim.get_state()
+        d, bad = ls.diff_states(a, b, 2)
+        nbad += len(bad) > 0
+        for k, v in d.items():
+            worst[k] = max(worst.get(k, 0.0), v)
+        if a.ball.hs_y_target_dir != last_dir:
+            flips += 1; last_dir = a.ball.hs_y_target_dir
+        if a.ball.hs_cur_target_speed != last_speed:
+            speedups += 1; last_speed = a.ball.hs_cur_target_speed
+    boost_end = ref.get_state(0).cars[1].boost
+    ref.close()
+    return worst, nbad, flips, speedups, boost_end
+
+
+def test_heatseeker_ball_per_tick():
+    def make():
+        s = hb.HostSim(); s.set_game_mode(oracle_ref.abi.MODE_HEATSEEKER); return s
+    worst, nbad, flips, speedups, boost_end = heatseeker_per_tick(make)
+    assert nbad == 0
+    assert flips >= 2 and speedups >= 1, (flips, speedups)          # the car's hit, then at least one back-wall turn
+    assert max(v for k, v in worst.items() if k.endswith(".pos")) <= 2e-3, worst
+    assert worst["ball.hs_y_target_dir"] == 0 and worst["ball.hs_cur_target_speed"] == 0 and worst["ball.hs_time_since_hit"] <= 1e-5, worst
+    assert boost_end >= 100.0 / 3 - 1e-3                             # unlimited boost: 900 ticks of boosting used nothing (pads may add)

@@ -64,3 +64,11 @@ def test_custom_obs_coefficients():
     r = setter_parity.run_resets(hostsim_binding.HostEnvSet, 2, trials=20, seed=77, state_setter=abi.SETTER_RANDOM, state_setter_flags=3,
                                  obs_kind=abi.OBS_DEFAULT_PADDED, obs_max_players=3, obs_coefs=coefs)
     assert r["state"] <= STATE_ATOL and r["obs"] <= OBS_ATOL, r
+
+
+# ---- GameMode::HEATSEEKER: kickoff, seeking ball, hit and wall-bounce rules, unlimited boost ----
+def test_heatseeker_kickoff_matches_reference():
+    """Arena::ResetToRandomKickoff in heatseeker mode: four slots, partial shuffle, ball start side from one more draw."""
+    for ppt in (1, 2, 3):
+        r = setter_parity.run_resets(hostsim_binding.HostEnvSet, ppt, trials=40, seed=60 + ppt, state_setter=abi.SETTER_KICKOFF, game_mode=abi.MODE_HEATSEEKER)
+        assert r["state"] <= STATE_ATOL and r["obs"] <= OBS_ATOL, r
