@@ -184,9 +184,8 @@ GGL_HD void ray_vs_plane(V3 from, V3 to, V3 n, float c, RayHit& h) {
 }
 
 GGL_HD void ray_vs_tri(V3 from, V3 to, const Tri& tr, RayHit& h) {
-    V3 v10 = tr.v1 - tr.v0, v20 = tr.v2 - tr.v0;
-    V3 tn = cross(v10, v20);
-    float dist = dot(tr.v0, tn);
+    const V3 tn = tr.rayN;
+    const float dist = tr.rayD;
     float da = dot(tn, from) - dist;
     float db = dot(tn, to) - dist;
     if (da * db >= 0.f) return;
@@ -379,8 +378,14 @@ GGL_HD void ray_cast_world(const ArenaDev& A, const WorldDev& W, int selfCar, V3
     }
     // dynamic bodies
     ray_vs_sphere(from, to, A.ball.pos, rl::BALL_RADIUS * kUU2BT, GROUND_BALL, h);
-    for (int c = 0; c < A.numCars; c++)
-        if (c != selfCar) ray_vs_car_box(from, to, A.cars[c], GROUND_CAR0 + c, h);
+    for (uint32_t m = A.rayBoxMask & ~(1u << selfCar); m; m &= m - 1) {      // cars with a tracked box, in index order (usually none)
+#if defined(__CUDA_ARCH__)
+        const int c = __ffs((int)m) - 1;
+#else
+        const int c = __builtin_ctz(m);
+#endif
+        ray_vs_car_box(from, to, A.cars[c], GROUND_CAR0 + c, h);
+    }
     // a hit on a body without contact response (a demolished car) reports nothing at all
     // (btDefaultVehicleRaycaster::castRay, BulletDynamics/Vehicle/btDefaultVehicleRaycaster.cpp)
     if (h.ground >= GROUND_CAR0 && A.cars[h.ground - GROUND_CAR0].isDemoed) h.ground = GROUND_NONE;

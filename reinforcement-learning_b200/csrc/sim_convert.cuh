@@ -338,6 +338,11 @@ inline void world_find_free_box(WorldHost& W);
 inline void world_build_grid(WorldHost& W) {
     world_build_edge_info(W);
     world_sort_bvh_order(W);
+    for (Tri& t : W.tris) {
+        const V3 v10 = t.v1 - t.v0, v20 = t.v2 - t.v0;
+        t.rayN = cross(v10, v20);
+        t.rayD = dot(t.v0, t.rayN);
+    }
     W.cellSize = 5.f;
     W.gridMin = v3(-4500.f * kUU2BT, -6200.f * kUU2BT, -100.f * kUU2BT);
     V3 gmax = v3(4500.f * kUU2BT, 6200.f * kUU2BT, 2200.f * kUU2BT);

@@ -221,6 +221,13 @@ GGL_HD void arena_tick(ArenaDev& A, const WorldDev& W, const Exec& ex) {
     GGL_PH(0);
     for (int c = ex.lane(); c < A.numCars; c += ex.lanes()) car_pre_tick_a(A, c);
     ex.sync();
+    if (ex.lane() == 0) {       // after the respawns of car_pre_tick_a (a respawned car has the all-zero box = "use the current transform")
+        uint32_t m = 0;
+        for (int c = 0; c < A.numCars; c++)
+            if (!(A.cars[c].aabbMin.x > A.cars[c].aabbMax.x)) m |= 1u << c;      // not the empty box car_update_ray_aabb leaves for far cars
+        A.rayBoxMask = (uint8_t)m;
+    }
+    ex.sync();
     if (GGL_PSYNC_MASK & 2) ex.phase_sync();
     GGL_PH(1);
     // the front wheels of all cars first, then the rear wheels (which never steer): with 8 lanes and 4 cars a round of the loop is

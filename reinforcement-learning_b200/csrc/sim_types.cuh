@@ -180,7 +180,8 @@ struct alignas(16) ArenaDev {
     // per-tick scratch
     int32_t numContacts;
     uint32_t bodiesInContact;                      // bit b: body b (0 ball, 1 + c car c) has a solver row this tick
-    uint8_t cntWorld, ballAwake, cntBall[kMaxCars], cntRest[kMaxCars], _pad4[2];
+    uint8_t cntWorld, ballAwake, cntBall[kMaxCars], cntRest[kMaxCars];
+    uint8_t rayBoxMask, _pad4;                     // per tick: bit c = car c has a tracked box a suspension ray could meet (sim_tick.cuh prologue)
     uint8_t island[8];                             // island[b] = lowest body index of the contact island body b belongs to
     uint32_t wheelDefer;                           // per tick: bit 4c+i = wheel i of car c stands on a car pre-ticked before c
     uint32_t contactOverflow;                      // STICKY: contact points dropped since create because windows and pool were full
@@ -211,6 +212,10 @@ struct Tri {
     V3 v0, v1, v2;
     float edgeAngle[3];      // V0V1, V1V2, V2V0 (2*pi = no neighbour)
     uint32_t flags;          // TRI_* | meshIndex << TRI_MESH_SHIFT
+    // what every suspension ray computes first about a triangle (btTriangleRaycastCallback::processTriangle): the unnormalised
+    // normal (v1 - v0) x (v2 - v0) and dot(v0, normal), evaluated once at mesh load with the same float operations
+    V3 rayN;
+    float rayD;
 };
 struct WorldDev {
     const Tri* tris;       // all mesh triangles (Bullet units)
