@@ -194,6 +194,11 @@ typedef struct ggl_car_state {   /* Sim/Car/Car.h:17-115 */
     ggl_controls controls;
     ggl_wheel_state wheels[4];
     uint64_t update_counter;
+    /* Hidden state like the wheels': the car's broadphase box as the LAST tick's collision detection left it (Bullet units). The
+     * suspension rays of the next tick are tested against it before the car's shape (btCollisionWorld.cpp:913-945), and nothing
+     * refreshes it in between - so it decides which rays can meet this car at all. All six 0 = unknown: the box of the current
+     * transform stands in. min.x > max.x = no other car was within reach (the device does not track the box then). */
+    float ray_aabb_min[3], ray_aabb_max[3];
 } ggl_car_state;
 
 typedef struct ggl_ball_state {  /* Sim/Ball/Ball.h:16-41 */

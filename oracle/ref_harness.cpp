@@ -149,6 +149,10 @@ void ReadCarState(Car* car, ggl_car_state& s) {
     s.last_controls = FromControls(cs.lastControls);
     s.controls = FromControls(car->controls);
     s.update_counter = cs.updateCounter;
+    if (btBroadphaseProxy* px = car->_rigidBody.getBroadphaseHandle()) {
+        s.ray_aabb_min[0] = px->m_aabbMin.x(); s.ray_aabb_min[1] = px->m_aabbMin.y(); s.ray_aabb_min[2] = px->m_aabbMin.z();
+        s.ray_aabb_max[0] = px->m_aabbMax.x(); s.ray_aabb_max[1] = px->m_aabbMax.y(); s.ray_aabb_max[2] = px->m_aabbMax.z();
+    }
     s.id = car->id;
     s.team = (uint8_t)car->team;
     for (int i = 0; i < 4; i++) {
@@ -171,7 +175,20 @@ void ApplyArenaState(Arena* arena, const ggl_arena_state& st) {
     arena->ball->_internalState.updateCounter = st.ball.update_counter;
     for (int i = 0; i < st.num_cars; i++) {
         Car* car = CarById(arena, i + 1);
-        if (car) ApplyCarState(car, st.cars[i]);
+        if (car) {
+            ApplyCarState(car, st.cars[i]);
+            // the broadphase box the next tick's suspension rays are tested against (ggl_car_state::ray_aabb_*): the given one, or
+            // - unknown / "nobody within reach" - the box of the transform just set
+            btBroadphaseProxy* px = car->_rigidBody.getBroadphaseHandle();
+            if (px) {
+                const float* a = st.cars[i].ray_aabb_min; const float* b = st.cars[i].ray_aabb_max;
+                bool zero = true;
+                for (int k = 0; k < 3; k++) zero = zero && a[k] == 0.f && b[k] == 0.f;
+                btVector3 mn(a[0], a[1], a[2]), mx(b[0], b[1], b[2]);
+                if (zero || a[0] > b[0]) car->_rigidBody.getAabb(mn, mx);
+                arena->_bulletWorld.getBroadphase()->setAabb(px, mn, mx, arena->_bulletWorld.getDispatcher());
+            }
+        }
     }
     for (int i = 0; i < GGL_NUM_PADS && i < (int)arena->_boostPads.size(); i++) {
         BoostPadState ps;

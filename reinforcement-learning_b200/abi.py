@@ -82,7 +82,7 @@ class CarState(C.Structure):
         ("wheels_with_contact", C.c_uint8 * 4),
         ("last_controls", Controls), ("controls", Controls),
         ("wheels", WheelState * 4),
-        ("update_counter", C.c_uint64),
+        ("update_counter", C.c_uint64), ("ray_aabb_min", C.c_float * 3), ("ray_aabb_max", C.c_float * 3),
     ]
 
 

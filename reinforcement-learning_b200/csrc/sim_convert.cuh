@@ -44,6 +44,7 @@ inline void car_from_host(const ggl_car_state& s, CarDev& c, int index, int numC
     c.carContactCooldown = s.car_contact_cooldown; c.demoRespawnTimer = s.demo_respawn_timer;
     c.hitRelPos = v3p(s.hit_rel_pos); c.hitBallPos = v3p(s.hit_ball_pos); c.hitExtraVel = v3p(s.hit_extra_vel);
     c.hitTick = s.hit_tick; c.hitTickExtra = s.hit_tick_extra; c.updateCounter = s.update_counter;
+    c.aabbMin = v3p(s.ray_aabb_min); c.aabbMax = v3p(s.ray_aabb_max);       // all zero = unknown (ray_vs_car_box)
     c.carContactOtherId = s.car_contact_other_id;
     c.id = (uint32_t)(index + 1);
     c.team = (index < numCars / 2) ? 0 : 1;
@@ -79,6 +80,7 @@ inline void car_to_host(const CarDev& c, ggl_car_state& s) {
     s.car_contact_cooldown = c.carContactCooldown; s.demo_respawn_timer = c.demoRespawnTimer;
     put3(s.hit_rel_pos, c.hitRelPos); put3(s.hit_ball_pos, c.hitBallPos); put3(s.hit_extra_vel, c.hitExtraVel);
     s.hit_tick = c.hitTick; s.hit_tick_extra = c.hitTickExtra; s.update_counter = c.updateCounter;
+    put3(s.ray_aabb_min, c.aabbMin); put3(s.ray_aabb_max, c.aabbMax);
     s.car_contact_other_id = c.carContactOtherId; s.id = c.id; s.team = c.team;
     s.is_on_ground = c.isOnGround; s.has_jumped = c.hasJumped; s.has_double_jumped = c.hasDoubleJumped;
     s.has_flipped = c.hasFlipped; s.is_flipping = c.isFlipping; s.is_jumping = c.isJumping;
