@@ -535,6 +535,19 @@ int ref_arena_contacts(void* p, int arena, float* out, int max) {
     return n;
 }
 
+// Every manifold of the dispatcher after the last tick, empty ones included, in array order: out[i] = {body0, body1, points}
+int ref_arena_manifolds(void* p, int arena, int* out, int max) {
+    Arena* a = ((RefEnv*)p)->envSet->arenas[arena];
+    auto* disp = a->_bulletWorld.getDispatcher();
+    int n = 0;
+    for (int i = 0; i < disp->getNumManifolds() && n < max; i++) {
+        btPersistentManifold* m = disp->getManifoldByIndexInternal(i);
+        out[3 * n] = BodyCode(m->getBody0()); out[3 * n + 1] = BodyCode(m->getBody1()); out[3 * n + 2] = m->getNumContacts();
+        n++;
+    }
+    return n;
+}
+
 // wheels of car `carId` after the last tick: out[4][12] = contact normal xyz, contact point xyz, suspension length,
 // ground kind (-1 none, 0 static world, 1 ball, 2 + carId-1 car), impulse xyz, suspension relative velocity
 void ref_arena_wheel_info(void* p, int arena, int carId, float* out) {
