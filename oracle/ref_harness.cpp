@@ -542,7 +542,16 @@ int ref_arena_manifolds(void* p, int arena, int* out, int max) {
     int n = 0;
     for (int i = 0; i < disp->getNumManifolds() && n < max; i++) {
         btPersistentManifold* m = disp->getManifoldByIndexInternal(i);
-        out[3 * n] = BodyCode(m->getBody0()); out[3 * n + 1] = BodyCode(m->getBody1()); out[3 * n + 2] = m->getNumContacts();
+        auto code = [a](const btCollisionObject* o) -> int {
+            const int c = BodyCode(o);
+            if (c >= 0) return c;
+            // a static body: -(100 + its index in the world's collision object array), planes 1000 further down
+            const btCollisionObjectArray& arr = a->_bulletWorld.getCollisionObjectArray();
+            int idx = 0;
+            for (int q = 0; q < arr.size(); q++) if (arr[q] == o) { idx = q; break; }
+            return -(100 + idx) - (o->getCollisionShape()->getShapeType() == STATIC_PLANE_PROXYTYPE ? 1000 : 0);
+        };
+        out[3 * n] = code(m->getBody0()); out[3 * n + 1] = code(m->getBody1()); out[3 * n + 2] = m->getNumContacts();
         n++;
     }
     return n;
