@@ -557,6 +557,30 @@ int ref_arena_manifolds(void* p, int arena, int* out, int max) {
     return n;
 }
 
+// Broadphase boxes of the static bodies, in world-array order (the order of ref_arena_manifolds' static codes): out[i][6] = min
+// xyz, max xyz in Bullet units. Returns their number.
+int ref_arena_static_boxes(void* p, int arena, float* out, int max) {
+    Arena* a = ((RefEnv*)p)->envSet->arenas[arena];
+    const btCollisionObjectArray& arr = a->_bulletWorld.getCollisionObjectArray();
+    int n = 0;
+    for (int q = 0; q < arr.size() && n < max; q++) {
+        if (!arr[q]->isStaticObject()) continue;
+        btBroadphaseProxy* px = arr[q]->getBroadphaseHandle();
+        float* o = out + 6 * n++;
+        o[0] = px->m_aabbMin.x(); o[1] = px->m_aabbMin.y(); o[2] = px->m_aabbMin.z();
+        o[3] = px->m_aabbMax.x(); o[4] = px->m_aabbMax.y(); o[5] = px->m_aabbMax.z();
+    }
+    return n;
+}
+
+// Broadphase box of the ball after the last tick (min xyz, max xyz, Bullet units)
+void ref_arena_ball_box(void* p, int arena, float* o) {
+    Arena* a = ((RefEnv*)p)->envSet->arenas[arena];
+    btBroadphaseProxy* px = a->ball->_rigidBody.getBroadphaseHandle();
+    o[0] = px->m_aabbMin.x(); o[1] = px->m_aabbMin.y(); o[2] = px->m_aabbMin.z();
+    o[3] = px->m_aabbMax.x(); o[4] = px->m_aabbMax.y(); o[5] = px->m_aabbMax.z();
+}
+
 // wheels of car `carId` after the last tick: out[4][12] = contact normal xyz, contact point xyz, suspension length,
 // ground kind (-1 none, 0 static world, 1 ball, 2 + carId-1 car), impulse xyz, suspension relative velocity
 void ref_arena_wheel_info(void* p, int arena, int carId, float* out) {

@@ -19,7 +19,7 @@ struct ggl_envset {
     int numPlayers;
     LaunchGeom geom;
     WorldHost worldHost;
-    Tri* d_tris; int* d_cellStart; int* d_cellTris;
+    Tri* d_tris; int* d_cellStart; int* d_cellTris; uint32_t* d_bpCellStatics; float* d_bpStaticBox;
     ArenaDev* d_reset;
     float* d_table;
     int32_t* d_actionsScratch;
@@ -74,7 +74,7 @@ void free_env(ggl_envset* e) {
     if (!e) return;
     cudaFree(e->P.arenas); cudaFree(e->d_reset); cudaFree(e->P.obs); cudaFree(e->P.masks); cudaFree(e->P.rewards);
     cudaFree(e->P.terminals); cudaFree(e->P.slotCarId); cudaFree(e->P.slotTeam); cudaFree(e->P.events); cudaFree(e->P.lastRewards);
-    cudaFree(e->d_tris); cudaFree(e->d_cellStart); cudaFree(e->d_cellTris); cudaFree(e->d_table); cudaFree(e->d_actionsScratch);
+    cudaFree(e->d_tris); cudaFree(e->d_cellStart); cudaFree(e->d_cellTris); cudaFree(e->d_bpCellStatics); cudaFree(e->d_bpStaticBox); cudaFree(e->d_table); cudaFree(e->d_actionsScratch);
     cudaFree(e->d_arenaOfPos); cudaFree(e->d_balanceOrder); cudaFree(e->d_stepCost);
     if (e->h_actions) cudaFreeHost(e->h_actions);
     if (e->h_obs) cudaFreeHost(e->h_obs);
@@ -117,7 +117,7 @@ extern "C" int ggl_envset_create(const ggl_envset_desc* d, ggl_envset** out) {
     ggl_envset* e = new (std::nothrow) ggl_envset();
     if (!e) return GGL_ERR_NOMEM;
     memset(&e->cfg, 0, sizeof(e->cfg)); memset(&e->P, 0, sizeof(e->P));
-    e->d_tris = nullptr; e->d_cellStart = e->d_cellTris = nullptr; e->d_reset = nullptr; e->d_table = nullptr; e->d_actionsScratch = nullptr;
+    e->d_tris = nullptr; e->d_cellStart = e->d_cellTris = nullptr; e->d_bpCellStatics = nullptr; e->d_bpStaticBox = nullptr; e->d_reset = nullptr; e->d_table = nullptr; e->d_actionsScratch = nullptr;
     e->d_arenaOfPos = e->d_balanceOrder = nullptr; e->d_stepCost = nullptr; e->balance = false;
     e->h_actions = nullptr; e->h_obs = nullptr; e->h_masks = nullptr; e->h_rewards = nullptr; e->h_terminals = nullptr; e->ownStream = nullptr; e->copyStream = nullptr; e->evReset = nullptr; e->evCopied = nullptr;
     e->device = d->device; e->seed = d->seed;
@@ -143,7 +143,7 @@ extern "C" int ggl_envset_create(const ggl_envset_desc* d, ggl_envset** out) {
     int rc = GGL_OK;
     const size_t nt = e->worldHost.tris.size() ? e->worldHost.tris.size() : 1, ncs = e->worldHost.cellStart.size(),
                  nct = e->worldHost.cellTris.size() ? e->worldHost.cellTris.size() : 1;
-    if ((rc = dmalloc(&e->d_tris, nt)) || (rc = dmalloc(&e->d_cellStart, ncs)) || (rc = dmalloc(&e->d_cellTris, nct)) ||
+    if ((rc = dmalloc(&e->d_bpCellStatics, e->worldHost.bpCellStatics.size())) || (rc = dmalloc(&e->d_bpStaticBox, e->worldHost.bpStaticBox.size())) || (rc = dmalloc(&e->d_tris, nt)) || (rc = dmalloc(&e->d_cellStart, ncs)) || (rc = dmalloc(&e->d_cellTris, nct)) ||
         (rc = dmalloc(&e->P.arenas, (size_t)c.numArenas)) || (rc = dmalloc(&e->P.obs, (size_t)e->numPlayers * c.obsSize)) ||
         (rc = dmalloc(&e->P.masks, (size_t)e->numPlayers * kNumActions)) || (rc = dmalloc(&e->P.rewards, (size_t)e->numPlayers)) ||
         (rc = dmalloc(&e->P.terminals, (size_t)c.numArenas)) || (rc = dmalloc(&e->P.slotCarId, (size_t)e->numPlayers)) ||
@@ -157,6 +157,9 @@ extern "C" int ggl_envset_create(const ggl_envset_desc* d, ggl_envset** out) {
     if (e->worldHost.cellTris.size()) cudaMemcpy(e->d_cellTris, e->worldHost.cellTris.data(), e->worldHost.cellTris.size() * sizeof(int), cudaMemcpyHostToDevice);
     WorldDev w = world_view(e->worldHost);
     w.tris = e->d_tris; w.cellStart = e->d_cellStart; w.cellTris = e->d_cellTris;
+    cudaMemcpy(e->d_bpCellStatics, e->worldHost.bpCellStatics.data(), e->worldHost.bpCellStatics.size() * sizeof(uint32_t), cudaMemcpyHostToDevice);
+    cudaMemcpy(e->d_bpStaticBox, e->worldHost.bpStaticBox.data(), e->worldHost.bpStaticBox.size() * sizeof(float), cudaMemcpyHostToDevice);
+    w.bpCellStatics = e->d_bpCellStatics; w.bpStaticBox = e->d_bpStaticBox;
     e->P.world = w;
     float table[kNumActions * 8];
     ggl_action_table(table, nullptr);

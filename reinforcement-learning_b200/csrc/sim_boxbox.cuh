@@ -326,7 +326,7 @@ GGL_HDN void collide_car_car(ArenaDev& A, ContactSink& S, int lo, int hi) {
         c.normal = o.normalOnB; c.dist = o.depth[k];
         c.relA = pA - a.pos; c.relB = pB - b.pos;
         c.friction = rl::CARCAR_FRICTION; c.restitution = rl::CARCAR_RESTITUTION;
-        c.bodyA = (int16_t)(1 + i); c.bodyB = (int16_t)(1 + j); c.special = 0; c._pad = 0;
+        c.bodyA = (int16_t)(1 + i); c.bodyB = (int16_t)(1 + j); c.special = 0; c.staticId = 0;
         // the bump / demo callback of this point runs in gather_contacts (leader, solver order): it writes to BOTH cars
         manifold_add(S, m, c, tmul(a.basis, pA - a.pos));
     }

@@ -163,7 +163,7 @@ GGL_HD void car_tri_emit(ArenaDev& A, ContactSink& S, ManifoldCtx& m, int ci, co
     c.normal = o.normalOnB; c.dist = o.distance;
     c.relA = pA - car.pos; c.relB = o.pointOnB;
     c.friction = rl::CARWORLD_FRICTION; c.restitution = rl::CARWORLD_RESTITUTION;
-    c.bodyA = (int16_t)(1 + ci); c.bodyB = -1; c.special = 0; c._pad = 0;
+    c.bodyA = (int16_t)(1 + ci); c.bodyB = -1; c.special = 0; c.staticId = (int16_t)(1 + (int)(t.flags >> TRI_MESH_SHIFT));
     int row = manifold_add(S, m, c, tmul(car.basis, pA - car.pos));
     if (row < 0) return;
     car.worldContactHas = 1;

@@ -138,6 +138,11 @@ inline void arena_phys_to_host(const ArenaDev& A, ggl_arena_state& st) {
 struct WorldHost {
     std::vector<Tri> tris;
     std::vector<int> cellStart, cellTris, meshStart;   // meshStart[m] = one past the last triangle of mesh m
+    std::vector<uint32_t> bpCellStatics;               // WorldDev::bpCellStatics / bpStaticBox
+    std::vector<float> bpStaticBox;
+    int bpX = 0, bpY = 0, bpZ = 0, numStatics = 0;
+    V3 bpMin = v3(0, 0, 0);
+    float bpCell = 7.4f;
     int numMeshes = 0;
     int gx = 1, gy = 1, gz = 1;
     V3 gridMin = v3(0, 0, 0);
@@ -335,6 +340,7 @@ inline void world_sort_bvh_order(WorldHost& W) {
 }
 
 inline void world_find_free_box(WorldHost& W);
+inline void world_build_broadphase_registry(WorldHost& W);
 
 // Uniform grid (cell = 5 bt = 250 uu) over the triangles; a triangle is listed in every cell its AABB (+0.1) touches.
 inline void world_build_grid(WorldHost& W) {
@@ -372,6 +378,7 @@ inline void world_build_grid(WorldHost& W) {
     }
     W.cellStart[nc] = (int)W.cellTris.size();
     world_find_free_box(W);
+    world_build_broadphase_registry(W);
 }
 
 // Largest box of empty grid cells grown greedily from the cell above the centre spot (face by face, as long as the new slab of
@@ -405,12 +412,74 @@ inline void world_find_free_box(WorldHost& W) {
     W.freeMax = v3(W.gridMin.x + (hi[0] + 1) * W.cellSize, W.gridMin.y + (hi[1] + 1) * W.cellSize, W.gridMin.z + (hi[2] + 1) * W.cellSize);
 }
 
+// btRSBroadphase's static registry (see WorldDev::bpCellStatics). Grid: ArenaConfig.h:22-29 (minPos, maxPos, maxAABBLen 370 uu),
+// cells per axis = ceil(range / cell) (btRSBroadphase.cpp:78-81). A static is entered, for every cell of its box's cell range
+// (a mesh: only the cells one of its triangles reaches), into that cell and its neighbours (:97-180; "reaches" = the triangle's
+// box overlaps the cell - the reference asks its quantized BVH, which is a little more generous at cell borders). Boxes: a mesh's
+// is its vertex box (the arena meshes have no collision margin), a plane's the half space of btStaticPlaneShape.cpp:40-54 (0.2
+// past the plane); the proxies are these grown by the contact breaking threshold 0.02 (btCollisionWorld::updateSingleAabb),
+// checked against the reference's (oracle/ref_harness.cpp: ref_arena_static_boxes, tools/manifold_order_check.py).
+// bpStaticBox keeps the shapes' own boxes.
+inline void world_build_broadphase_registry(WorldHost& W) {
+    W.bpMin = v3(-4500.f, -6000.f, 0.f) * kUU2BT;
+    const V3 mx = v3(4500.f, 6000.f, 2500.f) * kUU2BT;
+    W.bpCell = 370.f * kUU2BT;
+    auto cells = [&](float range) { int n = (int)ceilf(range / W.bpCell); return n < 1 ? 1 : n; };
+    W.bpX = cells(mx.x - W.bpMin.x); W.bpY = cells(mx.y - W.bpMin.y); W.bpZ = cells(mx.z - W.bpMin.z);
+    const int nc = W.bpX * W.bpY * W.bpZ, M = W.numMeshes < kMaxWorldMeshes ? W.numMeshes : kMaxWorldMeshes;
+    W.numStatics = M + 4;
+    std::vector<uint32_t> own(nc, 0u);
+    std::vector<V3> lo(W.numStatics, v3(1e30f, 1e30f, 1e30f)), hi(W.numStatics, v3(-1e30f, -1e30f, -1e30f));
+    auto coord = [&](float v, float mn, int n) { int c = (int)((v - mn) / W.bpCell); return c < 0 ? 0 : (c >= n ? n - 1 : c); };
+    auto enter = [&](V3 a, V3 b, int s) {
+        for (int i = coord(a.x, W.bpMin.x, W.bpX); i <= coord(b.x, W.bpMin.x, W.bpX); i++)
+            for (int j = coord(a.y, W.bpMin.y, W.bpY); j <= coord(b.y, W.bpMin.y, W.bpY); j++)
+                for (int k = coord(a.z, W.bpMin.z, W.bpZ); k <= coord(b.z, W.bpMin.z, W.bpZ); k++) own[(i * W.bpY + j) * W.bpZ + k] |= 1u << s;
+    };
+    for (const Tri& t : W.tris) {
+        const int m = (int)(t.flags >> TRI_MESH_SHIFT);
+        if (m >= M) continue;
+        const V3 a = vmin(t.v0, vmin(t.v1, t.v2)), b = vmax(t.v0, vmax(t.v1, t.v2));
+        lo[m] = vmin(lo[m], a); hi[m] = vmax(hi[m], b);
+        enter(a, b, m);
+    }
+    const float grow = 0.02f, big = 1e18f;
+    const float ex = rl::ARENA_EXTENT_X * kUU2BT, hz = rl::ARENA_HEIGHT * kUU2BT, off = 0.2f;
+    lo[M + 0] = v3(-big, -big, -big); hi[M + 0] = v3(big, big, 0.f + off);            // floor
+    lo[M + 1] = v3(-big, -big, hz - off); hi[M + 1] = v3(big, big, big);             // ceiling
+    lo[M + 2] = v3(-big, -big, -big); hi[M + 2] = v3(-ex + off, big, big);           // left wall (normal +x)
+    lo[M + 3] = v3(ex - off, -big, -big); hi[M + 3] = v3(big, big, big);             // right wall
+    for (int p = 0; p < 4; p++) enter(lo[M + p] - v3(grow, grow, grow), vmin(hi[M + p] + v3(grow, grow, grow), mx), M + p);
+    W.bpCellStatics.assign(nc, 0u);
+    for (int i = 0; i < W.bpX; i++)
+        for (int j = 0; j < W.bpY; j++)
+            for (int k = 0; k < W.bpZ; k++) {
+                uint32_t bits = 0;
+                for (int a = -1; a <= 1; a++)
+                    for (int b = -1; b <= 1; b++)
+                        for (int c = -1; c <= 1; c++) {
+                            const int x = i + a, y = j + b, z = k + c;
+                            if (x < 0 || y < 0 || z < 0 || x >= W.bpX || y >= W.bpY || z >= W.bpZ) continue;
+                            bits |= own[(x * W.bpY + y) * W.bpZ + z];
+                        }
+                W.bpCellStatics[(i * W.bpY + j) * W.bpZ + k] = bits;
+            }
+    W.bpStaticBox.resize(6 * W.numStatics);
+    for (int s2 = 0; s2 < W.numStatics; s2++) {
+        float* o = &W.bpStaticBox[6 * s2];
+        o[0] = lo[s2].x; o[1] = lo[s2].y; o[2] = lo[s2].z; o[3] = hi[s2].x; o[4] = hi[s2].y; o[5] = hi[s2].z;
+    }
+}
+
 inline WorldDev world_view(const WorldHost& W) {
     WorldDev d;
     d.tris = W.tris.data(); d.numTris = (int)W.tris.size();
     d.cellStart = W.cellStart.data(); d.cellTris = W.cellTris.data();
     d.gx = W.gx; d.gy = W.gy; d.gz = W.gz; d.gridMin = W.gridMin; d.cellSize = W.cellSize; d.invCellSize = 1.f / W.cellSize;
     d.freeMin = W.freeMin; d.freeMax = W.freeMax;
+    d.bpCellStatics = W.bpCellStatics.empty() ? nullptr : W.bpCellStatics.data();
+    d.bpStaticBox = W.bpStaticBox.empty() ? nullptr : W.bpStaticBox.data();
+    d.bpX = W.bpX; d.bpY = W.bpY; d.bpZ = W.bpZ; d.numStatics = W.numStatics; d.bpMin = W.bpMin; d.bpCell = W.bpCell;
     return d;
 }
 

@@ -288,7 +288,7 @@ GGL_HD void arena_tick(ArenaDev& A, const WorldDev& W, const Exec& ex) {
         int cost = GGL_COST_W(0) * any;
         for (int c = 0; c < A.numCars; c++) cost += GGL_COST_W(1) * A.meshCandN[c] + GGL_COST_W(2) * A.cars[c].isOnGround;
         A.stepCost += (uint32_t)cost;
-        if (any) gather_contacts(A);
+        if (any) gather_contacts(A, W);
         else {      // nothing touched anything this tick (88 % of the arena-ticks of the benchmark's rollout)
             A.numContacts = 0; A.bodiesInContact = 0; A.ballAwake = A.ball.active ? 1 : 0;
             for (int b = 0; b < 8; b++) A.island[b] = (uint8_t)b;

@@ -136,7 +136,7 @@ struct Contact {
     V3 relA, relB;     // contact point relative to each body origin
     float dist, friction, restitution;
     int16_t bodyA, bodyB;    // 0 = ball, 1+c = car c, -1 = static world
-    int16_t special, _pad;
+    int16_t special, staticId;   // staticId: which static body a world row touches (plane_static_code, sim_world.cuh), 0 otherwise
 };
 
 // PlayerEventState slots (RLGymCPP Gamestates/Player.h), written by the event tracker and by the bump callback
@@ -208,6 +208,7 @@ GGL_HD size_t arena_slot_bytes(int numCars) { return offsetof(ArenaDev, cars) + 
 // edgeAngle / flags = btTriangleInfo of Bullet's internal-edge utility (btTriangleInfoMap.h), generated on the host at mesh load
 enum : uint32_t { TRI_CONVEX_V0V1 = 1, TRI_CONVEX_V1V2 = 2, TRI_CONVEX_V2V0 = 4, TRI_SWAP_V0V1 = 8, TRI_SWAP_V1V2 = 16, TRI_SWAP_V2V0 = 32,
                   TRI_HAS_INFO = 0x100, TRI_MESH_SHIFT = 16 };
+constexpr int kMaxWorldMeshes = 28;           // + 4 planes = the 32 bits of WorldDev::bpCellStatics
 struct Tri {
     V3 v0, v1, v2;
     float edgeAngle[3];      // V0V1, V1V2, V2V0 (2*pi = no neighbour)
@@ -229,6 +230,17 @@ struct WorldDev {
     // a box of EMPTY grid cells around the middle of the arena (sim_convert.cuh: world_find_free_box): an AABB inside it touches
     // no triangle, so cars, ball and suspension rays in open play skip the grid walk (and its global loads) altogether
     V3 freeMin, freeMax;
+    // The reference's broadphase registry (btRSBroadphase.cpp:97-180): per broadphase cell (7.4 bt = ArenaConfig::maxAABBLen, grid
+    // over ArenaConfig::minPos..maxPos) the static bodies entered in it, as a bit set (bit s = static s: the meshes in creation
+    // order, then floor, ceiling, left wall, right wall - Arena.cpp:1036-1101), and every static's broadphase box (6 floats each).
+    // Together they say which (body, static) pairs - and so which manifolds, empty ones included - the reference creates in a
+    // tick, which decides the order its solver sees the rows in (solver_order, sim_world.cuh). Global memory: read on the rare
+    // ticks in which one island holds rows of more than one manifold.
+    const uint32_t* bpCellStatics;
+    const float* bpStaticBox;
+    int bpX, bpY, bpZ, numStatics;
+    V3 bpMin;
+    float bpCell;
 };
 GGL_HD bool world_aabb_is_free(const WorldDev& W, V3 mn, V3 mx) {
     return mn.x > W.freeMin.x && mn.y > W.freeMin.y && mn.z > W.freeMin.z && mx.x < W.freeMax.x && mx.y < W.freeMax.y && mx.z < W.freeMax.z;

@@ -222,6 +222,10 @@ GGL_HD void ball_heatseeker_on_world(BallDev& b, V3 normal) {
 
 // ---------------------------------------------------------------------------------------------- narrow phase
 // ball vs the 4 planes and the mesh; every contact is flagged special (Arena.cpp:265-273)
+// Contact::staticId of a row against the static world says which static body it touches (the reference has one manifold per body
+// pair; solver_order needs to tell them apart): 1 + mesh for an arena mesh, -1 .. -4 for floor, ceiling, left wall, right wall.
+GGL_HD int16_t plane_static_code(V3 n) { return (int16_t)(n.z > 0.f ? -1 : (n.z < 0.f ? -2 : (n.x > 0.f ? -3 : -4))); }
+
 GGL_HD void collide_ball_plane(ArenaDev& A, ContactSink& S, V3 n, V3 origin) {
     const BallDev& b = A.ball;
     V3 vtx = (-n) * kBallRadiusBT;            // support point of the sphere towards the plane
@@ -237,7 +241,7 @@ GGL_HD void collide_ball_plane(ArenaDev& A, ContactSink& S, V3 n, V3 origin) {
         c.relA = pA - b.pos; c.relB = pOnB - origin;
         c.friction = rl::BALL_FRICTION < rl::WORLD_FRICTION ? rl::BALL_FRICTION : rl::WORLD_FRICTION;
         c.restitution = rl::BALL_RESTITUTION > rl::WORLD_RESTITUTION ? rl::BALL_RESTITUTION : rl::WORLD_RESTITUTION;
-        c.bodyA = 0; c.bodyB = -1; c.special = 1; c._pad = 0;
+        c.bodyA = 0; c.bodyB = -1; c.special = 1; c.staticId = plane_static_code(n);
         if (manifold_add(S, m, c, pA - b.pos) >= 0 && A.gameMode == kModeHeatseeker) ball_heatseeker_on_world(A.ball, n);
     }
 }
@@ -358,7 +362,7 @@ GGL_HD void collide_ball_mesh(ArenaDev& A, ContactSink& S, const WorldDev& W) {
             c.relA = pA - b.pos; c.relB = p;
             c.friction = rl::BALL_FRICTION < rl::WORLD_FRICTION ? rl::BALL_FRICTION : rl::WORLD_FRICTION;
             c.restitution = rl::BALL_RESTITUTION > rl::WORLD_RESTITUTION ? rl::BALL_RESTITUTION : rl::WORLD_RESTITUTION;
-            c.bodyA = 0; c.bodyB = -1; c.special = 1; c._pad = 0;
+            c.bodyA = 0; c.bodyB = -1; c.special = 1; c.staticId = (int16_t)(1 + mesh);
             int row = manifold_add(S, m, c, pA - b.pos);
             if (row < 0) continue;
             if (A.gameMode == kModeHeatseeker) ball_heatseeker_on_world(A.ball, n);     // before the internal-edge adjustment (Arena.cpp:268-277)
@@ -387,7 +391,7 @@ GGL_HD void collide_car_plane(ArenaDev& A, ContactSink& S, int ci, V3 n, V3 orig
         c.normal = n; c.dist = dist;
         c.relA = pA - car.pos; c.relB = pOnB - origin;
         c.friction = rl::CARWORLD_FRICTION; c.restitution = rl::CARWORLD_RESTITUTION;
-        c.bodyA = (int16_t)(1 + ci); c.bodyB = -1; c.special = 0; c._pad = 0;
+        c.bodyA = (int16_t)(1 + ci); c.bodyB = -1; c.special = 0; c.staticId = plane_static_code(n);
         if (manifold_add(S, m, c, tmul(car.basis, pA - car.pos)) >= 0) {
             car.worldContactHas = 1;
             car.worldContactNormal = n;
@@ -429,7 +433,7 @@ GGL_HD void collide_car_ball(ArenaDev& A, ContactSink& S, int ci) {
     c.normal = n; c.dist = dist;
     c.relA = pA - car.pos; c.relB = pOnB - ball.pos;
     c.friction = rl::CARBALL_FRICTION; c.restitution = rl::CARBALL_RESTITUTION;
-    c.bodyA = (int16_t)(1 + ci); c.bodyB = 0; c.special = 0; c._pad = 0;
+    c.bodyA = (int16_t)(1 + ci); c.bodyB = 0; c.special = 0; c.staticId = 0;
     if (manifold_add(S, m, c, tmul(car.basis, pA - car.pos)) < 0) return;
 
     // Arena::_BtCallback_OnCarBallCollision (Arena.cpp:283-334)
@@ -844,6 +848,160 @@ GGL_HDN void collide_body(ArenaDev& A, const WorldDev& W, int b) {
     A.cntRest[i] = (uint8_t)S.n;
 }
 
+// ---------------------------------------------------------------------------------------------- the reference's row order
+// The order in which the reference's solver sees the contact rows of one island is not the order they were found in. Bullet
+// hands the solver the dispatcher's manifold array sorted by island id with btAlignedObjectArray::quickSort
+// (btSimulationIslandManager.cpp:370-384, predicate :177-184): an unstable sort, run over ALL manifolds of the tick - the ones
+// without a contact point included - so the permutation of the manifolds that share an island id depends on how many manifolds
+// there are and where they sit. Projected Gauss-Seidel is order-dependent, so whenever one island holds rows of two or more
+// manifolds (a car that touches the ball while its hitbox rests on the floor ...) the order has to be reproduced:
+//   1. broadphase boxes of the ball and the cars (btCollisionWorld::updateSingleAabb: the shape's box at the tick's transform,
+//      grown by 0.02, merged with the box at the predicted transform) and their grid cell (btRSBroadphase.h:90-108, the cell of
+//      the box's minimum corner);
+//   2. the pair list of btRSBroadphase::calculateOverlappingPairs (:393-470; every pair is dropped and found again each tick):
+//      per dynamic body in handle order (ball, then cars by id), the statics entered in its cell whose box overlaps, in creation
+//      order, then the dynamic bodies entered in its cell (= whose cell is a neighbour) whose box overlaps and that have no pair
+//      with it yet. The reference walks that last list in the order the bodies ARRIVED in the cell (history); handle order is
+//      used here, which can only differ when a body has pairs with two or more other dynamic bodies;
+//   3. the manifold array in dispatch order = pair order: the ball's manifolds with meshes and planes are made with the pair's
+//      algorithm (constructors of btConvexConcave / btConvexPlaneCollisionAlgorithm); every manifold of a car - with a static,
+//      the ball or another car - only if the hitbox's own box at the tick's transform overlaps the other shape's own box
+//      (the child test of btCompoundCollisionAlgorithm.cpp:128-139; thresholds measured on the reference);
+//   4. island ids: union-find over the dynamic-dynamic pairs in pair order, unite(p, q) hanging p's root under q's
+//      (btUnionFind.h:76-98 with USE_PATH_COMPRESSION), element index = ball 0, cars 1.. by id; a manifold's id is that of its
+//      dynamic body (:167-174); manifolds of a car without contact response (demolished) never reach the sort
+//      (btCollisionDispatcher::needsResponse);
+//   5. the quickSort itself (middle pivot, Hoare partition that swaps equal keys), on the array of ids;
+//   6. rows re-emitted manifold by manifold, rows of one manifold keeping their order.
+// If a row's manifold is not in the predicted array (the registry is an approximation at cell borders) the order is left alone.
+constexpr int kMaxOrderManifolds = 64;
+struct OrderManifold { int8_t dyn, other; };    // other: >= 0 dynamic body, < 0: -(1 + static)
+#if defined(GGL_ORDER_DEBUG) && !defined(__CUDA_ARCH__)
+// host test builds: the last predicted manifold array (tests/hostsim)
+struct OrderDebug { int n; OrderManifold mf[kMaxOrderManifolds]; uint8_t key[kMaxOrderManifolds]; int reordered, unknownRow, always, off; V3 mn[1 + kMaxCars], mx[1 + kMaxCars]; };
+inline OrderDebug& order_debug() { static thread_local OrderDebug d; return d; }
+#endif
+
+GGL_HD bool order_boxes_overlap(V3 amn, V3 amx, V3 bmn, V3 bmx) {
+    return !(amn.x > bmx.x || amx.x < bmn.x || amn.y > bmx.y || amx.y < bmn.y || amn.z > bmx.z || amx.z < bmn.z);
+}
+// btAlignedObjectArray::quickSort restated on an array of keys: middle element as pivot, Hoare partition that also swaps equal
+// keys, then both parts. The parts are disjoint, so the order in which they are taken up (the reference recurses, here a stack
+// of pending ranges) does not change the result.
+GGL_HD void order_sort_keys(uint8_t* key, uint8_t* idx, int n) {
+    uint8_t stLo[kMaxOrderManifolds], stHi[kMaxOrderManifolds];
+    int sp = 0;
+    stLo[0] = 0; stHi[0] = (uint8_t)(n - 1); sp = 1;
+    while (sp > 0) {
+        sp--;
+        const int lo = stLo[sp], hi = stHi[sp];
+        int i = lo, j = hi;
+        const uint8_t x = key[(lo + hi) / 2];
+        do {
+            while (key[i] < x) i++;
+            while (x < key[j]) j--;
+            if (i <= j) {
+                const uint8_t tk = key[i]; key[i] = key[j]; key[j] = tk;
+                const uint8_t ti = idx[i]; idx[i] = idx[j]; idx[j] = ti;
+                i++; j--;
+            }
+        } while (i <= j);
+        if (lo < j) { stLo[sp] = (uint8_t)lo; stHi[sp] = (uint8_t)j; sp++; }
+        if (i < hi) { stLo[sp] = (uint8_t)i; stHi[sp] = (uint8_t)hi; sp++; }
+    }
+}
+// Builds the manifold array of steps 1-4 into mf[] / key[]; returns its length (0: too many manifolds to say)
+GGL_HDN int order_predict_manifolds(const ArenaDev& A, const WorldDev& W, OrderManifold* mf, uint8_t* key) {
+    const int P = A.numCars, nb = 1 + P;
+    V3 mn[1 + kMaxCars], mx[1 + kMaxCars], tmn[1 + kMaxCars], tmx[1 + kMaxCars];
+    int cell[1 + kMaxCars][3];
+    uint8_t handle[1 + kMaxCars];          // handle[r] = body with the r-th broadphase handle
+    uint8_t rankOf[1 + kMaxCars];
+    handle[0] = 0;
+    for (int r = 1; r < nb; r++) {
+        int best = -1;                      // the car with the (r-1)-th smallest id
+        for (int c = 0; c < P; c++) {
+            int below = 0;
+            for (int d = 0; d < P; d++) below += A.cars[d].id < A.cars[c].id ? 1 : 0;
+            if (below == r - 1) best = c;
+        }
+        handle[r] = (uint8_t)(1 + (best < 0 ? r - 1 : best));
+    }
+    for (int r = 0; r < nb; r++) rankOf[handle[r]] = (uint8_t)r;
+    const V3 thr = v3(0.02f, 0.02f, 0.02f);
+    for (int b = 0; b < nb; b++) {
+        V3 a0, a1, b0, b1;
+        if (b == 0) {
+            const float re = kBallRadiusBT + 0.08f;        // btSphereShape::getAabb of the reference's Bullet adds 0.08 (btSphereShape.cpp:55)
+            const V3 r3 = v3(re, re, re);
+            const V3 np = A.ball.pos + A.ball.vel * kTick;
+            a0 = A.ball.pos - r3; a1 = A.ball.pos + r3; b0 = np - r3; b1 = np + r3;
+        } else {
+            const CarDev& c = A.cars[b - 1];
+            V3 np; M3 nbs;
+            car_world_aabb(c.pos, c.basis, a0, a1);
+            integrate_transform(c.pos, c.basis, c.vel, c.angVel, kTick, np, nbs);
+            car_world_aabb(np, nbs, b0, b1);
+        }
+        tmn[b] = a0; tmx[b] = a1;
+        mn[b] = vmin(a0 - thr, b0 - thr); mx[b] = vmax(a1 + thr, b1 + thr);
+        int ci = (int)((mn[b].x - W.bpMin.x) / W.bpCell), cj = (int)((mn[b].y - W.bpMin.y) / W.bpCell), ck = (int)((mn[b].z - W.bpMin.z) / W.bpCell);
+        cell[b][0] = ci < 0 ? 0 : (ci >= W.bpX ? W.bpX - 1 : ci);
+        cell[b][1] = cj < 0 ? 0 : (cj >= W.bpY ? W.bpY - 1 : cj);
+        cell[b][2] = ck < 0 ? 0 : (ck >= W.bpZ ? W.bpZ - 1 : ck);
+    }
+#if defined(GGL_ORDER_DEBUG) && !defined(__CUDA_ARCH__)
+    for (int b = 0; b < nb; b++) { order_debug().mn[b] = mn[b]; order_debug().mx[b] = mx[b]; }
+#endif
+    uint8_t parent[1 + kMaxCars];
+    for (int r = 0; r < nb; r++) parent[r] = (uint8_t)r;
+    int n = 0;
+    for (int r = 0; r < nb; r++) {
+        const int p = handle[r];
+        const bool response = p == 0 || !A.cars[p - 1].rbDisabled;
+        uint32_t bits = W.bpCellStatics[(cell[p][0] * W.bpY + cell[p][1]) * W.bpZ + cell[p][2]];
+        if (p == 0 && !A.ball.active) bits = 0;      // a sleeping ball against a static (asleep by construction): no algorithm (btCollisionDispatcher::needsCollision)
+        while (bits) {
+#if defined(__CUDA_ARCH__)
+            const int s = __ffs((int)bits) - 1;
+#else
+            const int s = __builtin_ctz(bits);
+#endif
+            bits &= bits - 1;
+            // bpStaticBox holds the statics' own boxes; their proxies are 0.02 larger. The ball's manifold is made with the pair
+            // (proxy boxes overlap); a car's, by the compound algorithm, only if the hitbox's tight box at the tick's transform
+            // overlaps the static's own box (btCompoundCollisionAlgorithm.cpp:128-139; measured on the reference: a car box
+            // 0.1996 above the floor has a (car, floor) manifold, one 0.2046 above has none, whatever its velocity)
+            const float* bx = W.bpStaticBox + 6 * s;
+            const V3 smn = v3(bx[0], bx[1], bx[2]), smx = v3(bx[3], bx[4], bx[5]);
+            if (p == 0 ? !order_boxes_overlap(mn[0] - thr, mx[0] + thr, smn, smx) : !order_boxes_overlap(tmn[p], tmx[p], smn, smx)) continue;
+            if (!response) continue;
+            if (n >= kMaxOrderManifolds) return 0;
+            mf[n].dyn = (int8_t)p; mf[n].other = (int8_t)(-(1 + s)); n++;
+        }
+        // a body with a lower handle found its pair with p when it was walked (the conditions are symmetric)
+        for (int r2 = r + 1; r2 < nb; r2++) {
+            const int q = handle[r2];
+            if (abs(cell[q][0] - cell[p][0]) > 1 || abs(cell[q][1] - cell[p][1]) > 1 || abs(cell[q][2] - cell[p][2]) > 1) continue;
+            if (!order_boxes_overlap(mn[p], mx[p], mn[q], mx[q])) continue;
+            if (!response || A.cars[q - 1].rbDisabled) continue;     // no island merge, and no manifold that reaches the sort
+            int i = r, j = r2;
+            while (parent[i] != i) i = parent[i];
+            while (parent[j] != j) j = parent[j];
+            if (i != j) parent[i] = (uint8_t)j;
+            if (!order_boxes_overlap(tmn[q], tmx[q], tmn[p], tmx[p])) continue;      // compound child test on the bodies' own boxes
+            if (n >= kMaxOrderManifolds) return 0;
+            mf[n].dyn = (int8_t)p; mf[n].other = (int8_t)q; n++;
+        }
+    }
+    for (int k = 0; k < n; k++) {
+        int i = rankOf[mf[k].dyn];
+        while (parent[i] != i) i = parent[i];
+        key[k] = (uint8_t)i;
+    }
+    return n;
+}
+
 // Leader: turns windows + pool into the solver's row order (A.contactOrder, nothing is moved), runs the order-dependent
 // contact callbacks (ball extra impulse in car order, car-car bump/demo logic per point), the ball wake-up rule, and marks the
 // bodies that have a row. Row order = the reference's (pair-cache insertion order): the ball's world rows, the
@@ -854,7 +1012,56 @@ GGL_HD int pool_next(const ArenaDev& A, uint8_t owner, int& cursor) {
     while (cursor < used && A.poolOwner[cursor] != owner) cursor++;
     return cursor < used ? contact_pool_base(A.numCars) + cursor++ : -1;
 }
-GGL_HDN void gather_contacts(ArenaDev& A) {
+
+// The manifold a row belongs to, as an OrderManifold (the (ball, car) manifold is listed under the ball)
+GGL_HD OrderManifold order_row_manifold(const Contact& c, int planeBase) {
+    OrderManifold m;
+    if (c.bodyB < 0) {
+        const int s = c.staticId > 0 ? c.staticId - 1 : planeBase + (-c.staticId - 1);
+        m.dyn = (int8_t)c.bodyA; m.other = (int8_t)(-(1 + s));
+    } else if (c.bodyB == 0) { m.dyn = 0; m.other = (int8_t)c.bodyA; }
+    else { m.dyn = (int8_t)c.bodyA; m.other = (int8_t)c.bodyB; }
+    return m;
+}
+
+// Steps 5 and 6: re-emits A.contactOrder in the reference's order. Leader, after the islands are labelled.
+GGL_HDN void solver_order(ArenaDev& A, const WorldDev& W) {
+    OrderManifold mf[kMaxOrderManifolds];
+    uint8_t key[kMaxOrderManifolds], idx[kMaxOrderManifolds], rowM[kMaxContacts], out[kMaxContacts];
+    const int n = order_predict_manifolds(A, W, mf, key);
+#if defined(GGL_ORDER_DEBUG) && !defined(__CUDA_ARCH__)
+    OrderDebug& D = order_debug();
+    D.n = n; D.reordered = 0; D.unknownRow = 0;
+    for (int k = 0; k < n; k++) { D.mf[k] = mf[k]; D.key[k] = key[k]; }
+#endif
+    if (n < 2) return;
+    const int planeBase = W.numStatics - 4;
+    for (int k = 0; k < A.numContacts; k++) {
+        const OrderManifold r = order_row_manifold(A.contacts[A.contactOrder[k]], planeBase);
+        int found = -1;
+        for (int q = 0; q < n; q++)
+            if ((mf[q].dyn == r.dyn && mf[q].other == r.other) || (r.other > 0 && mf[q].dyn == r.other && mf[q].other == r.dyn)) { found = q; break; }
+        if (found < 0) {
+#if defined(GGL_ORDER_DEBUG) && !defined(__CUDA_ARCH__)
+            D.unknownRow = 1;
+#endif
+            return;
+        }
+        rowM[k] = (uint8_t)found;
+    }
+    for (int q = 0; q < n; q++) idx[q] = (uint8_t)q;
+    order_sort_keys(key, idx, n);
+    int w = 0;
+    for (int q = 0; q < n; q++)
+        for (int k = 0; k < A.numContacts; k++)
+            if (rowM[k] == idx[q]) out[w++] = A.contactOrder[k];
+#if defined(GGL_ORDER_DEBUG) && !defined(__CUDA_ARCH__)
+    for (int k = 0; k < w; k++) D.reordered |= out[k] != A.contactOrder[k];
+#endif
+    for (int k = 0; k < w; k++) A.contactOrder[k] = out[k];
+}
+
+GGL_HDN void gather_contacts(ArenaDev& A, const WorldDev& W) {
     const int P = A.numCars, R = contact_car_window(P);
     {   // nothing touched anything this tick (the usual case: 88 % of the arena-ticks of the benchmark's rollout)
         int any = A.cntWorld;
@@ -927,6 +1134,25 @@ GGL_HDN void gather_contacts(ArenaDev& A) {
         }
         if (!changed) break;
     }
+    // rows of two or more manifolds in one island: the reference's order is not the order of discovery (solver_order)
+    bool mixed = false;
+    {
+        int8_t first[8];
+        for (int b = 0; b < 8; b++) first[b] = -1;
+        for (int k = 0; k < A.numContacts; k++) {
+            const Contact& c = A.contacts[A.contactOrder[k]];
+            const int isl = A.island[c.bodyA];
+            if (first[isl] < 0) { first[isl] = (int8_t)k; continue; }
+            const Contact& f = A.contacts[A.contactOrder[first[isl]]];
+            mixed |= f.bodyA != c.bodyA || f.bodyB != c.bodyB || f.staticId != c.staticId;
+        }
+    }
+#if defined(GGL_ORDER_DEBUG) && !defined(__CUDA_ARCH__)
+    order_debug().n = -1;
+    if (order_debug().always) mixed = true;
+    if (order_debug().off) mixed = false;
+#endif
+    if (mixed && W.bpCellStatics) solver_order(A, W);
 }
 
 }  // namespace ggl

@@ -4,6 +4,7 @@
 // library (libgigaenv_cuda.so) never links or loads this; it only launches CUDA kernels built from the same headers.
 //   g++ -O2 -ffp-contract=off -shared -fPIC -I../../include hostsim.cpp -o _build/libhostsim.so
 #include <cstdio>
+#define GGL_ORDER_DEBUG 1      // keeps the manifold array solver_order predicted (hostsim_predicted_manifolds)
 #include "../../reinforcement-learning_b200/csrc/sim_convert.cuh"
 #include "../../reinforcement-learning_b200/csrc/env_reset.cuh"
 
@@ -61,7 +62,7 @@ void hostsim_step(void* p, int ticks) {
     HostSim* h = (HostSim*)p;
     WorldDev W = world_view(h->world);
     ExecSerial ex;
-    for (int i = 0; i < ticks; i++) arena_tick(h->arena, W, ex);
+    for (int i = 0; i < ticks; i++) { order_debug().n = -1; arena_tick(h->arena, W, ex); }
 }
 
 // contacts of the last tick: [n][20] like ref_arena_contacts (bodyA, bodyB, normal, posA, posB, dist, friction, restitution, special)
@@ -81,6 +82,39 @@ int hostsim_contacts(void* p, float* out, int max) {
     return n;
 }
 
+
+// The manifold array solver_order (sim_world.cuh) predicted for the last tick, coded like ref_arena_manifolds: out[i] = {body0,
+// body1, island key}; body = 0 ball, car id, or -(100 + static index) (planes 1000 further down). mode: 0 = as shipped (only
+// when an island mixes manifolds), 1 = predict on every tick with a contact, 2 = never reorder. Returns -1 if the last tick
+// did not predict; flags[0] = rows were reordered, flags[1] = a row's manifold was not in the array.
+void hostsim_order_mode(int mode) { order_debug().always = mode == 1; order_debug().off = mode == 2; }
+int hostsim_predicted_manifolds(void* p, int* out, int max, int* flags) {
+    HostSim* h = (HostSim*)p;
+    const OrderDebug& D = order_debug();
+    flags[0] = D.reordered; flags[1] = D.unknownRow;
+    if (D.n < 0) return -1;
+    const int planeBase = h->world.numStatics - 4;
+    auto code = [&](int b) { return b == 0 ? 0 : (b > 0 ? (int)h->arena.cars[b - 1].id : (-(1 + b) >= planeBase ? -(1100 + (-(1 + b))) : -(100 + (-(1 + b))))); };
+    for (int k = 0; k < D.n && k < max; k++) { out[3 * k] = code(D.mf[k].dyn); out[3 * k + 1] = code(D.mf[k].other); out[3 * k + 2] = D.key[k]; }
+    return D.n;
+}
+
+// the registry's static boxes ([n][6], like ref_arena_static_boxes) and the boxes the last prediction used for the ball and the
+// cars in slot order ([1 + cars][6])
+int hostsim_static_boxes(void* p, float* out, int max) {
+    HostSim* h = (HostSim*)p;
+    int n = h->world.numStatics < max ? h->world.numStatics : max;
+    memcpy(out, h->world.bpStaticBox.data(), sizeof(float) * 6 * n);
+    return n;
+}
+void hostsim_predicted_boxes(void* p, float* out) {
+    HostSim* h = (HostSim*)p;
+    const OrderDebug& D = order_debug();
+    for (int b = 0; b <= h->arena.numCars; b++) {
+        float* o = out + 6 * b;
+        o[0] = D.mn[b].x; o[1] = D.mn[b].y; o[2] = D.mn[b].z; o[3] = D.mx[b].x; o[4] = D.mx[b].y; o[5] = D.mx[b].z;
+    }
+}
 
 // same call as ref_convex_ray_cast (oracle/ref_harness.cpp): the device's ray-vs-hitbox / ray-vs-ball cast
 int hostsim_convex_ray_cast(int kind, const float* from, const float* to, const float* pos, const float* basis, float* out) {

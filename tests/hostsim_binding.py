@@ -25,6 +25,11 @@ def build():
                            os.path.join(_DIR, "hostsim.cpp"), "-o", _SO])
 
 
+def order_mode(mode):
+    """0 = as shipped, 1 = predict the reference's manifold array on every tick with a contact, 2 = never reorder"""
+    lib().hostsim_order_mode(int(mode))
+
+
 def lib():
     global _lib
     if _lib is None:
@@ -83,6 +88,13 @@ class HostSim:
     def set_game_mode(self, mode):
         lib().hostsim_set_game_mode.argtypes = [C.c_void_p, C.c_int]
         lib().hostsim_set_game_mode(self.h, mode)
+
+    def predicted_manifolds(self, maxn=64):
+        """(array [n][3] of body0, body1, island key; reordered?, unknown row?) of the last tick, or None if it predicted nothing"""
+        out = np.zeros((maxn, 3), np.int32)
+        flags = np.zeros(2, np.int32)
+        n = lib().hostsim_predicted_manifolds(C.c_void_p(self.h), out.ctypes.data_as(C.c_void_p), maxn, flags.ctypes.data_as(C.c_void_p))
+        return None if n < 0 else (out[:n], bool(flags[0]), bool(flags[1]))
 
     def contacts(self, maxn=64):
         out = np.zeros((maxn, 20), np.float32)

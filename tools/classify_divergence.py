@@ -105,6 +105,7 @@ def main():
     steps = int(sys.argv[3]) if len(sys.argv) > 3 else 40
     scripted = (int(sys.argv[4]) if len(sys.argv) > 4 else 1) != 0
     ppa = 2 * ppt
+    hb.order_mode(int(os.environ.get("GGL_ORDER_MODE", "0")))      # 2 = without the reference's manifold order (solver_order)
     L = oracle_ref.lib(); L.ref_set_threads(1); L.ref_seed(21 + ppt)
     kw = dict(obs_kind=1, state_setter=abi.SETTER_INJECTED)
     ref = oracle_ref.RefEnvSet(arenas, ppt, **kw)
