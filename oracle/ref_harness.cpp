@@ -573,6 +573,17 @@ int ref_arena_static_boxes(void* p, int arena, float* out, int max) {
     return n;
 }
 
+// btAlignedObjectArray::quickSort itself, on (key, index) pairs compared by key only like btPersistentManifoldSortPredicate
+// compares island ids: idx[] comes back as the permutation the reference's sort applies to n manifolds with these keys.
+struct KeyIdx { int key, idx; };
+struct KeyLess { bool operator()(const KeyIdx& a, const KeyIdx& b) const { return a.key < b.key; } };
+void ref_quicksort_keys(const int* keys, int* idx, int n) {
+    btAlignedObjectArray<KeyIdx> arr;
+    for (int i = 0; i < n; i++) { KeyIdx k; k.key = keys[i]; k.idx = i; arr.push_back(k); }
+    arr.quickSort(KeyLess());
+    for (int i = 0; i < n; i++) idx[i] = arr[i].idx;
+}
+
 // Broadphase box of the ball after the last tick (min xyz, max xyz, Bullet units)
 void ref_arena_ball_box(void* p, int arena, float* o) {
     Arena* a = ((RefEnv*)p)->envSet->arenas[arena];

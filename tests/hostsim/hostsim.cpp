@@ -99,6 +99,14 @@ int hostsim_predicted_manifolds(void* p, int* out, int max, int* flags) {
     return D.n;
 }
 
+// order_sort_keys (sim_world.cuh) on its own: idx[] = the permutation it applies to n manifolds with these island ids
+void hostsim_sort_keys(const int* keys, int* idx, int n) {
+    uint8_t k[kMaxOrderManifolds], ix[kMaxOrderManifolds];
+    for (int i = 0; i < n; i++) { k[i] = (uint8_t)keys[i]; ix[i] = (uint8_t)i; }
+    if (n > 1) order_sort_keys(k, ix, n);
+    for (int i = 0; i < n; i++) idx[i] = ix[i];
+}
+
 // the registry's static boxes ([n][6], like ref_arena_static_boxes) and the boxes the last prediction used for the ball and the
 // cars in slot order ([1 + cars][6])
 int hostsim_static_boxes(void* p, float* out, int max) {

@@ -45,11 +45,8 @@ def canon(rows, num_meshes_offset):
     return out
 
 
-def main():
-    ppt = int(sys.argv[1]) if len(sys.argv) > 1 else 2
-    arenas = int(sys.argv[2]) if len(sys.argv) > 2 else 32
-    steps = int(sys.argv[3]) if len(sys.argv) > 3 else 30
-    scripted = (int(sys.argv[4]) if len(sys.argv) > 4 else 1) != 0
+def run(ppt=2, arenas=32, steps=30, scripted=True, show=0, show_state=False):
+    """Counter of outcomes over every tick with a contact (see the module text)"""
     ppa = 2 * ppt
     L = oracle_ref.lib(); L.ref_set_threads(1); L.ref_seed(33 + ppt)
     ref = oracle_ref.RefEnvSet(arenas, ppt, obs_kind=1, state_setter=abi.SETTER_INJECTED)
@@ -93,6 +90,9 @@ def main():
                     stats["ticks without a device contact"] += 1
                     if nonempty:
                         stats["  ... but the reference has points"] += 1
+                        if shown < show:
+                            shown += 1
+                            print("step %d tick %d arena %d: no device contact, reference manifolds %s" % (s_i, t, a, rm.tolist()), flush=True)
                     continue
                 pm, reordered, unknown = pred
                 stats["ticks with a contact"] += 1
@@ -108,17 +108,17 @@ def main():
                     stats["array predicted exactly"] += 1
                 elif sorted(want) == sorted(got):
                     stats["same manifolds, other order"] += 1
-                    if shown < int(os.environ.get("GGL_SHOW", "12")):
+                    if shown < show:
                         shown += 1
                         print("step %d tick %d arena %d (order)\n  ref  %s\n  pred %s" % (s_i, t, a, want, got), flush=True)
                 else:
                     stats["other manifolds"] += 1
                     extra = sorted(set(got) - set(want)); missing = sorted(set(want) - set(got))
                     stats["  predicted but absent: %d, present but not predicted: %d" % (min(len(extra), 3), min(len(missing), 3))] += 1
-                    if shown < int(os.environ.get("GGL_SHOW", "12")):
+                    if shown < show:
                         shown += 1
                         print("step %d tick %d arena %d\n  ref  %s\n  pred %s" % (s_i, t, a, want, got), flush=True)
-                        if os.environ.get("GGL_SHOW_STATE"):
+                        if show_state:
                             for x, y in extra + missing:
                                 for b in (x, y):
                                     if b == 0:
@@ -134,6 +134,19 @@ def main():
                                         print("    car %d pos %s vel %s angvel %s demoed %d fwd %s up %s" % (b, list(c.pos), list(c.vel), list(c.ang_vel), c.is_demoed, list(c.rot[0:3]), list(c.rot[6:9])))
                 if reordered:
                     stats["ticks whose rows were reordered"] += 1
+    hb.order_mode(0)
+    for s in sims:
+        s.close() if hasattr(s, "close") else None
+    ref.close()
+    return stats
+
+
+def main():
+    ppt = int(sys.argv[1]) if len(sys.argv) > 1 else 2
+    arenas = int(sys.argv[2]) if len(sys.argv) > 2 else 32
+    steps = int(sys.argv[3]) if len(sys.argv) > 3 else 30
+    scripted = (int(sys.argv[4]) if len(sys.argv) > 4 else 1) != 0
+    stats = run(ppt, arenas, steps, scripted, show=int(os.environ.get("GGL_SHOW", "12")), show_state=bool(os.environ.get("GGL_SHOW_STATE")))
     print("\n%dv%d, %d arenas x %d env steps (%s)" % (ppt, ppt, arenas, steps, "scripted" if scripted else "unscripted"))
     for k, v in sorted(stats.items()):
         print("  %-60s %d" % (k, v))
