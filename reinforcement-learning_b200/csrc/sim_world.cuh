@@ -874,8 +874,22 @@ GGL_HDN void collide_body(ArenaDev& A, const WorldDev& W, int b) {
 //   5. the quickSort itself (middle pivot, Hoare partition that swaps equal keys), on the array of ids;
 //   6. rows re-emitted manifold by manifold, rows of one manifold keeping their order.
 // If a row's manifold is not in the predicted array (the registry is an approximation at cell borders) the order is left alone.
-constexpr int kMaxOrderManifolds = 64;
+constexpr int kMaxOrderManifolds = 48;
 struct OrderManifold { int8_t dyn, other; };    // other: >= 0 dynamic body, < 0: -(1 + static)
+// Working set of solver_order. It lives in the arena's car-vs-mesh hit staging (shared memory, dead between contact generation
+// and the solver's bodies): as per-thread arrays every word would be a cold local-memory line of its own for the one lane that
+// runs this.
+struct OrderScratch {
+    V3 mn[1 + kMaxCars], mx[1 + kMaxCars], tmn[1 + kMaxCars], tmx[1 + kMaxCars];     // proxy boxes, the shapes' own boxes
+    OrderManifold mf[kMaxOrderManifolds];
+    uint8_t key[kMaxOrderManifolds], idx[kMaxOrderManifolds], stLo[kMaxOrderManifolds], stHi[kMaxOrderManifolds];
+    uint8_t rowM[kMaxContacts], out[kMaxContacts];
+    uint8_t cell[1 + kMaxCars][4];
+    uint8_t parent[8];
+    int8_t first[8];
+};
+static_assert(sizeof(OrderScratch) <= sizeof(CarTriHit) * kMaxCars * kMaxMeshHit, "solver_order's working set must fit the mesh-hit staging");
+GGL_HD OrderScratch& order_scratch(ArenaDev& A) { return *reinterpret_cast<OrderScratch*>(&A.meshHit[0][0]); }
 #if defined(GGL_ORDER_DEBUG) && !defined(__CUDA_ARCH__)
 // host test builds: the last predicted manifold array (tests/hostsim)
 struct OrderDebug { int n; OrderManifold mf[kMaxOrderManifolds]; uint8_t key[kMaxOrderManifolds]; int reordered, unknownRow, always, off; V3 mn[1 + kMaxCars], mx[1 + kMaxCars]; };
@@ -888,17 +902,20 @@ GGL_HD bool order_boxes_overlap(V3 amn, V3 amx, V3 bmn, V3 bmx) {
 // btAlignedObjectArray::quickSort restated on an array of keys: middle element as pivot, Hoare partition that also swaps equal
 // keys, then both parts. The parts are disjoint, so the order in which they are taken up (the reference recurses, here a stack
 // of pending ranges) does not change the result.
-GGL_HD void order_sort_keys(uint8_t* key, uint8_t* idx, int n) {
-    uint8_t stLo[kMaxOrderManifolds], stHi[kMaxOrderManifolds];
+GGL_HD void order_sort_keys(uint8_t* key, uint8_t* idx, int n, uint8_t* stLo, uint8_t* stHi) {
     int sp = 0;
     stLo[0] = 0; stHi[0] = (uint8_t)(n - 1); sp = 1;
+#pragma unroll 1
     while (sp > 0) {
         sp--;
         const int lo = stLo[sp], hi = stHi[sp];
         int i = lo, j = hi;
         const uint8_t x = key[(lo + hi) / 2];
+#pragma unroll 1
         do {
+#pragma unroll 1
             while (key[i] < x) i++;
+#pragma unroll 1
             while (x < key[j]) j--;
             if (i <= j) {
                 const uint8_t tk = key[i]; key[i] = key[j]; key[j] = tk;
@@ -910,57 +927,54 @@ GGL_HD void order_sort_keys(uint8_t* key, uint8_t* idx, int n) {
         if (i < hi) { stLo[sp] = (uint8_t)i; stHi[sp] = (uint8_t)hi; sp++; }
     }
 }
-// Builds the manifold array of steps 1-4 into mf[] / key[]; returns its length (0: too many manifolds to say)
-GGL_HDN int order_predict_manifolds(const ArenaDev& A, const WorldDev& W, OrderManifold* mf, uint8_t* key) {
-    const int P = A.numCars, nb = 1 + P;
-    V3 mn[1 + kMaxCars], mx[1 + kMaxCars], tmn[1 + kMaxCars], tmx[1 + kMaxCars];
-    int cell[1 + kMaxCars][3];
-    uint8_t handle[1 + kMaxCars];          // handle[r] = body with the r-th broadphase handle
-    uint8_t rankOf[1 + kMaxCars];
-    handle[0] = 0;
-    for (int r = 1; r < nb; r++) {
-        int best = -1;                      // the car with the (r-1)-th smallest id
-        for (int c = 0; c < P; c++) {
-            int below = 0;
-            for (int d = 0; d < P; d++) below += A.cars[d].id < A.cars[c].id ? 1 : 0;
-            if (below == r - 1) best = c;
-        }
-        handle[r] = (uint8_t)(1 + (best < 0 ? r - 1 : best));
-    }
-    for (int r = 0; r < nb; r++) rankOf[handle[r]] = (uint8_t)r;
+// Builds the manifold array of steps 1-4 into mf[] / key[]; returns its length (0: too many manifolds to say). Written for
+// SIZE: this is cold code in a kernel that is bound by instruction fetch - every 128-byte line of it is a miss that the whole
+// block waits for at the next barrier (a first version of 34 KB cost 5 % of the env step while running in 0.08 % of the
+// arena-ticks, tools/gpu_r2ay*.sh) - so loops are not unrolled, and a car's proxy box is the one car_update_ray_aabb left this
+// tick when there is one (another car within 300 uu), else its own box moved by vel * dt: the turn of the predicted transform
+// (<= 0.07 bt at the corners) is left out, which can only misplace a pair whose boxes are that close to touching.
+GGL_HDN int order_predict_manifolds(const ArenaDev& A, const WorldDev& W, OrderScratch& S) {
+    const int nb = 1 + A.numCars;           // body b has the b-th broadphase handle: ball, then cars by id (= index + 1)
+    V3* mn = S.mn; V3* mx = S.mx; V3* tmn = S.tmn; V3* tmx = S.tmx;
+    uint8_t (*cell)[4] = S.cell;
+    OrderManifold* mf = S.mf;
+    uint8_t* key = S.key;
     const V3 thr = v3(0.02f, 0.02f, 0.02f);
+#pragma unroll 1
     for (int b = 0; b < nb; b++) {
-        V3 a0, a1, b0, b1;
+        V3 a0, a1, step;
+        bool tracked = false;
         if (b == 0) {
             const float re = kBallRadiusBT + 0.08f;        // btSphereShape::getAabb of the reference's Bullet adds 0.08 (btSphereShape.cpp:55)
-            const V3 r3 = v3(re, re, re);
-            const V3 np = A.ball.pos + A.ball.vel * kTick;
-            a0 = A.ball.pos - r3; a1 = A.ball.pos + r3; b0 = np - r3; b1 = np + r3;
+            a0 = A.ball.pos - v3(re, re, re); a1 = A.ball.pos + v3(re, re, re);
+            step = A.ball.vel * kTick;
         } else {
             const CarDev& c = A.cars[b - 1];
-            V3 np; M3 nbs;
             car_world_aabb(c.pos, c.basis, a0, a1);
-            integrate_transform(c.pos, c.basis, c.vel, c.angVel, kTick, np, nbs);
-            car_world_aabb(np, nbs, b0, b1);
+            step = c.vel * kTick;
+            if (!(c.aabbMin.x > c.aabbMax.x) && !c.rbDisabled) { mn[b] = c.aabbMin; mx[b] = c.aabbMax; tracked = true; }
         }
         tmn[b] = a0; tmx[b] = a1;
-        mn[b] = vmin(a0 - thr, b0 - thr); mx[b] = vmax(a1 + thr, b1 + thr);
-        int ci = (int)((mn[b].x - W.bpMin.x) / W.bpCell), cj = (int)((mn[b].y - W.bpMin.y) / W.bpCell), ck = (int)((mn[b].z - W.bpMin.z) / W.bpCell);
-        cell[b][0] = ci < 0 ? 0 : (ci >= W.bpX ? W.bpX - 1 : ci);
-        cell[b][1] = cj < 0 ? 0 : (cj >= W.bpY ? W.bpY - 1 : cj);
-        cell[b][2] = ck < 0 ? 0 : (ck >= W.bpZ ? W.bpZ - 1 : ck);
+        if (!tracked) { mn[b] = vmin(a0, a0 + step) - thr; mx[b] = vmax(a1, a1 + step) + thr; }
+        const int ci = (int)((mn[b].x - W.bpMin.x) / W.bpCell), cj = (int)((mn[b].y - W.bpMin.y) / W.bpCell), ck = (int)((mn[b].z - W.bpMin.z) / W.bpCell);
+        cell[b][0] = (uint8_t)(ci < 0 ? 0 : (ci >= W.bpX ? W.bpX - 1 : ci));
+        cell[b][1] = (uint8_t)(cj < 0 ? 0 : (cj >= W.bpY ? W.bpY - 1 : cj));
+        cell[b][2] = (uint8_t)(ck < 0 ? 0 : (ck >= W.bpZ ? W.bpZ - 1 : ck));
     }
 #if defined(GGL_ORDER_DEBUG) && !defined(__CUDA_ARCH__)
     for (int b = 0; b < nb; b++) { order_debug().mn[b] = mn[b]; order_debug().mx[b] = mx[b]; }
 #endif
-    uint8_t parent[1 + kMaxCars];
+    uint8_t* parent = S.parent;
+#pragma unroll 1
     for (int r = 0; r < nb; r++) parent[r] = (uint8_t)r;
     int n = 0;
-    for (int r = 0; r < nb; r++) {
-        const int p = handle[r];
+#pragma unroll 1
+    for (int p = 0; p < nb; p++) {
         const bool response = p == 0 || !A.cars[p - 1].rbDisabled;
         uint32_t bits = W.bpCellStatics[(cell[p][0] * W.bpY + cell[p][1]) * W.bpZ + cell[p][2]];
         if (p == 0 && !A.ball.active) bits = 0;      // a sleeping ball against a static (asleep by construction): no algorithm (btCollisionDispatcher::needsCollision)
+        if (!response) bits = 0;                      // a demolished car's manifolds never reach the sort
+#pragma unroll 1
         while (bits) {
 #if defined(__CUDA_ARCH__)
             const int s = __ffs((int)bits) - 1;
@@ -974,18 +988,18 @@ GGL_HDN int order_predict_manifolds(const ArenaDev& A, const WorldDev& W, OrderM
             // 0.1996 above the floor has a (car, floor) manifold, one 0.2046 above has none, whatever its velocity)
             const float* bx = W.bpStaticBox + 6 * s;
             const V3 smn = v3(bx[0], bx[1], bx[2]), smx = v3(bx[3], bx[4], bx[5]);
-            if (p == 0 ? !order_boxes_overlap(mn[0] - thr, mx[0] + thr, smn, smx) : !order_boxes_overlap(tmn[p], tmx[p], smn, smx)) continue;
-            if (!response) continue;
+            const V3 lo = p == 0 ? mn[0] - thr : tmn[p], hi = p == 0 ? mx[0] + thr : tmx[p];
+            if (!order_boxes_overlap(lo, hi, smn, smx)) continue;
             if (n >= kMaxOrderManifolds) return 0;
             mf[n].dyn = (int8_t)p; mf[n].other = (int8_t)(-(1 + s)); n++;
         }
         // a body with a lower handle found its pair with p when it was walked (the conditions are symmetric)
-        for (int r2 = r + 1; r2 < nb; r2++) {
-            const int q = handle[r2];
-            if (abs(cell[q][0] - cell[p][0]) > 1 || abs(cell[q][1] - cell[p][1]) > 1 || abs(cell[q][2] - cell[p][2]) > 1) continue;
+#pragma unroll 1
+        for (int q = p + 1; q < nb; q++) {
+            if (abs((int)cell[q][0] - (int)cell[p][0]) > 1 || abs((int)cell[q][1] - (int)cell[p][1]) > 1 || abs((int)cell[q][2] - (int)cell[p][2]) > 1) continue;
             if (!order_boxes_overlap(mn[p], mx[p], mn[q], mx[q])) continue;
             if (!response || A.cars[q - 1].rbDisabled) continue;     // no island merge, and no manifold that reaches the sort
-            int i = r, j = r2;
+            int i = p, j = q;
             while (parent[i] != i) i = parent[i];
             while (parent[j] != j) j = parent[j];
             if (i != j) parent[i] = (uint8_t)j;
@@ -994,8 +1008,9 @@ GGL_HDN int order_predict_manifolds(const ArenaDev& A, const WorldDev& W, OrderM
             mf[n].dyn = (int8_t)p; mf[n].other = (int8_t)q; n++;
         }
     }
+#pragma unroll 1
     for (int k = 0; k < n; k++) {
-        int i = rankOf[mf[k].dyn];
+        int i = mf[k].dyn;
         while (parent[i] != i) i = parent[i];
         key[k] = (uint8_t)i;
     }
@@ -1026,19 +1041,44 @@ GGL_HD OrderManifold order_row_manifold(const Contact& c, int planeBase) {
 
 // Steps 5 and 6: re-emits A.contactOrder in the reference's order. Leader, after the islands are labelled.
 GGL_HDN void solver_order(ArenaDev& A, const WorldDev& W) {
-    OrderManifold mf[kMaxOrderManifolds];
-    uint8_t key[kMaxOrderManifolds], idx[kMaxOrderManifolds], rowM[kMaxContacts], out[kMaxContacts];
-    const int n = order_predict_manifolds(A, W, mf, key);
+    OrderScratch& S = order_scratch(A);
+    {   // only if two rows of ONE island belong to different manifolds
+        bool mixed = false;
+        int8_t* first = S.first;
+#pragma unroll 1
+        for (int b = 0; b < 8; b++) first[b] = -1;
+#pragma unroll 1
+        for (int k = 0; k < A.numContacts; k++) {
+            const Contact& c = A.contacts[A.contactOrder[k]];
+            const int isl = A.island[c.bodyA];
+            if (first[isl] < 0) { first[isl] = (int8_t)k; continue; }
+            const Contact& f = A.contacts[A.contactOrder[first[isl]]];
+            mixed |= f.bodyA != c.bodyA || f.bodyB != c.bodyB || f.staticId != c.staticId;
+        }
+#if defined(GGL_ORDER_DEBUG) && !defined(__CUDA_ARCH__)
+        if (order_debug().always) mixed = true;
+#endif
+#if defined(GGL_ORDER_COUNT) && defined(__CUDA_ARCH__)      // experiment: calls in the high half, runs in the low half of the overflow counter
+        atomicAdd(&A.contactOverflow, mixed ? 0x10001u : 0x10000u);
+#endif
+        if (!mixed) return;
+    }
+    OrderManifold* mf = S.mf;
+    uint8_t* key = S.key; uint8_t* idx = S.idx; uint8_t* rowM = S.rowM; uint8_t* out = S.out;
+    const int n = order_predict_manifolds(A, W, S);
 #if defined(GGL_ORDER_DEBUG) && !defined(__CUDA_ARCH__)
     OrderDebug& D = order_debug();
     D.n = n; D.reordered = 0; D.unknownRow = 0;
+#pragma unroll 1
     for (int k = 0; k < n; k++) { D.mf[k] = mf[k]; D.key[k] = key[k]; }
 #endif
     if (n < 2) return;
     const int planeBase = W.numStatics - 4;
+#pragma unroll 1
     for (int k = 0; k < A.numContacts; k++) {
         const OrderManifold r = order_row_manifold(A.contacts[A.contactOrder[k]], planeBase);
         int found = -1;
+#pragma unroll 1
         for (int q = 0; q < n; q++)
             if ((mf[q].dyn == r.dyn && mf[q].other == r.other) || (r.other > 0 && mf[q].dyn == r.other && mf[q].other == r.dyn)) { found = q; break; }
         if (found < 0) {
@@ -1049,15 +1089,20 @@ GGL_HDN void solver_order(ArenaDev& A, const WorldDev& W) {
         }
         rowM[k] = (uint8_t)found;
     }
+#pragma unroll 1
     for (int q = 0; q < n; q++) idx[q] = (uint8_t)q;
-    order_sort_keys(key, idx, n);
+    order_sort_keys(key, idx, n, S.stLo, S.stHi);
     int w = 0;
+#pragma unroll 1
     for (int q = 0; q < n; q++)
+#pragma unroll 1
         for (int k = 0; k < A.numContacts; k++)
             if (rowM[k] == idx[q]) out[w++] = A.contactOrder[k];
 #if defined(GGL_ORDER_DEBUG) && !defined(__CUDA_ARCH__)
+#pragma unroll 1
     for (int k = 0; k < w; k++) D.reordered |= out[k] != A.contactOrder[k];
 #endif
+#pragma unroll 1
     for (int k = 0; k < w; k++) A.contactOrder[k] = out[k];
 }
 
@@ -1116,11 +1161,19 @@ GGL_HDN void gather_contacts(ArenaDev& A, const WorldDev& W) {
     }
     A.ballAwake = ballAwake ? 1 : 0;
     uint32_t mask = 0;
+    // Can one island hold rows of two manifolds (solver_order)? Only if a body touches two different statics (its world rows are
+    // contiguous) or a row joins two dynamic bodies and is not alone. Decided here, in the loop that reads the rows anyway:
+    // this is the leader's serial path of every tick with a contact, and an instruction costs ~24 cycles at this kernel's
+    // issue rate (a 400-instruction test here measured 4 % of the env step, tools/gpu_r2ay.sh).
+    bool twoStatics = false, anyDyn = false;
+    int prevA = -1, prevS = 0;
     for (int k = 0; k < A.numContacts; k++) {
         const Contact& c = A.contacts[A.contactOrder[k]];
         mask |= 1u << c.bodyA;
-        if (c.bodyB >= 0) mask |= 1u << c.bodyB;
+        if (c.bodyB >= 0) { mask |= 1u << c.bodyB; anyDyn = true; }
+        else { twoStatics |= c.bodyA == prevA && c.staticId != prevS; prevA = c.bodyA; prevS = c.staticId; }
     }
+    bool several = twoStatics || (anyDyn && A.numContacts >= 2);
     A.bodiesInContact = mask;
     // contact islands: bodies connected through rows between two dynamic bodies (car-ball, car-car) share a label
     for (int b = 0; b < 8; b++) A.island[b] = (uint8_t)b;
@@ -1134,25 +1187,15 @@ GGL_HDN void gather_contacts(ArenaDev& A, const WorldDev& W) {
         }
         if (!changed) break;
     }
-    // rows of two or more manifolds in one island: the reference's order is not the order of discovery (solver_order)
-    bool mixed = false;
-    {
-        int8_t first[8];
-        for (int b = 0; b < 8; b++) first[b] = -1;
-        for (int k = 0; k < A.numContacts; k++) {
-            const Contact& c = A.contacts[A.contactOrder[k]];
-            const int isl = A.island[c.bodyA];
-            if (first[isl] < 0) { first[isl] = (int8_t)k; continue; }
-            const Contact& f = A.contacts[A.contactOrder[first[isl]]];
-            mixed |= f.bodyA != c.bodyA || f.bodyB != c.bodyB || f.staticId != c.staticId;
-        }
-    }
+    // rows of more than one manifold: if two of them share an island, the reference's order is not the order of discovery
 #if defined(GGL_ORDER_DEBUG) && !defined(__CUDA_ARCH__)
     order_debug().n = -1;
-    if (order_debug().always) mixed = true;
-    if (order_debug().off) mixed = false;
+    if (order_debug().always) several = true;
+    if (order_debug().off) several = false;
 #endif
-    if (mixed && W.bpCellStatics) solver_order(A, W);
+#if !defined(GGL_NO_SOLVER_ORDER)       // experiment builds only (tools/gpu_r2ay.sh: what the reordering costs)
+    if (several && W.bpCellStatics) solver_order(A, W);
+#endif
 }
 
 }  // namespace ggl

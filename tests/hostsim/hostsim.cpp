@@ -101,9 +101,9 @@ int hostsim_predicted_manifolds(void* p, int* out, int max, int* flags) {
 
 // order_sort_keys (sim_world.cuh) on its own: idx[] = the permutation it applies to n manifolds with these island ids
 void hostsim_sort_keys(const int* keys, int* idx, int n) {
-    uint8_t k[kMaxOrderManifolds], ix[kMaxOrderManifolds];
+    uint8_t k[kMaxOrderManifolds], ix[kMaxOrderManifolds], lo[kMaxOrderManifolds], hi[kMaxOrderManifolds];
     for (int i = 0; i < n; i++) { k[i] = (uint8_t)keys[i]; ix[i] = (uint8_t)i; }
-    if (n > 1) order_sort_keys(k, ix, n);
+    if (n > 1) order_sort_keys(k, ix, n, lo, hi);
     for (int i = 0; i < n; i++) idx[i] = ix[i];
 }
 
