@@ -1063,6 +1063,7 @@ GGL_HDN void solver_order(ArenaDev& A, const WorldDev& W) {
 #endif
         if (!mixed) return;
     }
+    A.stepCost += 24u;      // work estimate for the next step's block balancing (sim_tick.cuh): about three contact rows' worth, on the leader alone
     OrderManifold* mf = S.mf;
     uint8_t* key = S.key; uint8_t* idx = S.idx; uint8_t* rowM = S.rowM; uint8_t* out = S.out;
     const int n = order_predict_manifolds(A, W, S);
