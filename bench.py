@@ -40,12 +40,12 @@ OBS_SIZE_ADV_2V2 = 167
 ENV_BYTES_PER_AGENT_STEP = 1026
 GAE_BYTES_PER_ELEM = 21
 # DRAM traffic per launch of the dominant kernels from one `ncu --set full` capture each (dram__bytes_read.sum +
-# dram__bytes_write.sum; profiles/r2au_env_step_ncu_summary.txt, profiles/r2au_gae_scan_ncu_summary.txt). Env step at 4096 arenas
-# 2v2: state blobs in, mesh and instruction fetch against 16.8 MB algorithmic; GAE scan: 151.3 + 145.4 MB at L = 2^24 against
+# dram__bytes_write.sum; profiles/r2ba_env_step_ncu_summary.txt, profiles/r2ba_gae_scan_ncu_summary.txt). Env step at 4096 arenas
+# 2v2: state blobs in, mesh and instruction fetch against 16.8 MB algorithmic; GAE scan: 151.3 + 144.6 MB at L = 2^24 against
 # 352 MB algorithmic (part of the 201 MB of outputs is still in the 126 MB L2 when the kernel ends).
-ENV_TRAFFIC_BYTES_NCU = 19.7e6      # profiles/r2au_env_step_ncu_summary.txt: 19.28 MB read + 0.42 MB written per launch (the 12.5 MB of outputs
+ENV_TRAFFIC_BYTES_NCU = 19.7e6      # profiles/r2ba_env_step_ncu_summary.txt: 19.33 MB read + 0.42 MB written per launch (the 12.5 MB of outputs
                                     # and the state written back are still in L2 when the kernel ends); round 1: 36.2 MB
-GAE_TRAFFIC_BYTES_NCU = 296.7e6
+GAE_TRAFFIC_BYTES_NCU = 296.0e6
 # ExperienceBuffer gather (staged kernel, profiles/r1j_expbuf_ncu_summary.txt): 1.202 GB read + 0.773 GB written at 2^20 samples against
 # 1.63 GB algorithmic: a random row drags in whole 64-byte DRAM bursts around its unaligned ends, and each of the four scalars
 # costs a burst of its own.
