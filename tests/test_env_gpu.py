@@ -32,7 +32,8 @@ def test_steady_state_scripted_events_match_reference(ggl, ppt, arenas, seed):
     in mid-play; both sides reset onto those states and 40 env steps are compared with the physics re-synchronised before
     every step (env_parity.run_steady_state). Masks, terminals and all nine event flags are exact on every arena-step whose obs
     hold the tolerance, with goals, shots, bumps and demolitions occurring; no contact point is dropped; the arena-steps whose
-    obs leave 1e-4 (contact order inside an island, knife-edge internal-edge decisions: DESIGN.md section 2) stay below 5 %."""
+    obs leave 1e-4 (state the reference keeps outside its snapshots, knife-edge internal-edge decisions: DESIGN.md section 2)
+    stay below 2 % (measured with the reference's manifold order reproduced: 6 of 1 680, 8 of 1 120, 5 of 1 120)."""
     r = env_parity.run_steady_state(ggl, num_arenas=arenas, ppt=ppt, preroll=100, steps=40, seed=seed,
                                     scripts=scenarios.env_scripts(arenas, ppt, 2))
     print("steady state %dv%d: %s" % (ppt, ppt, {k: (v.tolist() if hasattr(v, "tolist") else v) for k, v in r.items()}))
@@ -42,17 +43,17 @@ def test_steady_state_scripted_events_match_reference(ggl, ppt, arenas, seed):
     assert ev[0] > 0 and ev[3] > 0 and ev[5] > 0 and ev[6] > 0, r          # goal, shot, bump, bumped
     assert r["touches"] > 0 and r["goals_seen"] > 0 and r["terminals_seen"] > 0, r
     assert r["rew"] <= 1e-4, r
-    assert r["bad_arena_steps"] <= 0.05 * r["arena_steps"], r
+    assert r["bad_arena_steps"] <= 0.02 * r["arena_steps"], r
 
 
 def test_steady_state_unscripted_play_matches_reference(ggl):
     """160 reference steps of random play from the kickoff, then 60 compared steps of 64 arenas 2v2 (no scripts): the state
-    bench.py times."""
+    bench.py times. Arena-steps outside the obs tolerance: 8 of 3 840 measured, 0.5 % allowed."""
     r = env_parity.run_steady_state(ggl, num_arenas=64, ppt=2, preroll=160, steps=60, seed=11)
     print("steady state unscripted:", {k: (v.tolist() if hasattr(v, "tolist") else v) for k, v in r.items()})
     assert r["mask_mismatch"] == 0 and r["term_mismatch"] == 0 and r["event_mismatch"] == 0, r
     assert r["contact_overflow"] == 0 and r["rew"] <= 1e-4, r
-    assert r["bad_arena_steps"] <= 0.01 * r["arena_steps"], r
+    assert r["bad_arena_steps"] <= 0.005 * r["arena_steps"], r
 
 
 def test_all_stock_rewards_match(ggl):

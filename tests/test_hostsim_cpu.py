@@ -74,8 +74,9 @@ def test_steady_state_scripted_events_match_reference():
     every arena is then put into a scripted situation (goal, shot, save attempt, bump, demolition, pad pickup, pile-up) or left
     in mid-play, and 40 env steps are compared with the physics re-synchronised before every step. Integer outputs (masks,
     terminals, all nine event flags) must be exact with goals, shots, bumps and demolitions actually occurring; obs / rewards
-    hold 1e-4 except on the arena-steps where contact ORDER differs from the reference's (rows of a
-    multi-triangle mesh manifold, manifolds of one island), which are counted and bounded."""
+    hold 1e-4 except on the arena-steps that depend on state the reference keeps outside its snapshots or on a knife-edge
+    decision, which are counted and bounded: 3 of 560 measured with the reference's manifold order
+    reproduced (solver_order), 2 % allowed."""
     import scenarios
     r = env_parity.run_steady_state(None, num_arenas=14, ppt=2, preroll=100, steps=40, seed=2, env_cls=hb.HostEnvSet,
                                     scripts=scenarios.env_scripts(14, 2, 1))
@@ -84,7 +85,7 @@ def test_steady_state_scripted_events_match_reference():
     ev = r["events"]
     assert ev[0] > 0 and ev[3] > 0 and ev[5] > 0 and ev[6] > 0, r          # goal, shot, bump, bumped
     assert r["touches"] > 0 and r["goals_seen"] > 0 and r["terminals_seen"] > 0, r
-    assert r["bad_arena_steps"] <= 0.05 * r["arena_steps"], r
+    assert r["bad_arena_steps"] <= 0.02 * r["arena_steps"], r
 
 
 def test_steady_state_3v3_pileups_do_not_overflow_contact_rows():
@@ -94,7 +95,7 @@ def test_steady_state_3v3_pileups_do_not_overflow_contact_rows():
     assert r["mask_mismatch"] == 0 and r["term_mismatch"] == 0 and r["event_mismatch"] == 0, r
     assert r["contact_overflow"] == 0, r
     assert r["events"][7] > 0 and r["events"][8] > 0, r                      # demo, demoed
-    assert r["bad_arena_steps"] <= 0.06 * r["arena_steps"], r
+    assert r["bad_arena_steps"] <= 0.03 * r["arena_steps"], r                 # 2 of 420 measured
 
 
 def test_suspension_ray_vs_car_hitbox_matches_reference_cast():
