@@ -1021,7 +1021,9 @@ GGL_HDN int order_predict_manifolds(const ArenaDev& A, const WorldDev& W, OrderS
 // contact callbacks (ball extra impulse in car order, car-car bump/demo logic per point), the ball wake-up rule, and marks the
 // bodies that have a row. Row order = the reference's (pair-cache insertion order): the ball's world rows, the
 // car-ball rows in car order, then every car's world + car-car rows; within a body, window rows before pool rows, pool rows in
-// claim order (a body's lane claims them one after the other, so claim order is its emission order).
+// claim order (a body's lane claims them one after the other, so claim order is its emission order). That is the order of the
+// reference's dispatcher array; when an island holds rows of more than one manifold the solver's order is another one, and
+// solver_order (above) re-emits the list.
 GGL_HD int pool_next(const ArenaDev& A, uint8_t owner, int& cursor) {
     const int used = (int)A.poolCount < contact_pool_size(A.numCars) ? (int)A.poolCount : contact_pool_size(A.numCars);
     while (cursor < used && A.poolOwner[cursor] != owner) cursor++;
