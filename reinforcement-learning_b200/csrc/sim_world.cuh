@@ -1065,7 +1065,10 @@ GGL_HDN void solver_order(ArenaDev& A, const WorldDev& W) {
 #endif
         if (!mixed) return;
     }
-    A.stepCost += 24u;      // work estimate for the next step's block balancing (sim_tick.cuh): about three contact rows' worth, on the leader alone
+#if !defined(GGL_ORDER_COST)
+#define GGL_ORDER_COST 24u
+#endif
+    A.stepCost += GGL_ORDER_COST;      // work estimate for the next step's block balancing (sim_tick.cuh): about three contact rows' worth, on the leader alone
     OrderManifold* mf = S.mf;
     uint8_t* key = S.key; uint8_t* idx = S.idx; uint8_t* rowM = S.rowM; uint8_t* out = S.out;
     const int n = order_predict_manifolds(A, W, S);
